@@ -1,0 +1,479 @@
+// C ABI implementation (include/beluga_b200.h): context, weight staging, layer launches.
+// Reference path replaced: chromatin.py:102-106 (model load), :262-279 (encode + batched forward),
+// :281-286 (diff/ref/alt), compute_expecto_features.py:113-124, predict.py:87-136.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cudaTypedefs.h>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <atomic>
+#include <algorithm>
+#include <vector>
+
+#include "../../include/beluga_b200.h"
+#include "gemm_tc.cuh"
+#include "kernels_misc.cuh"
+
+using namespace bx;
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CK(expr)                                                                                      \
+  do {                                                                                                \
+    cudaError_t _e = (expr);                                                                          \
+    if (_e != cudaSuccess)                                                                            \
+      return fail(BX_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+
+int load_driver_entry() {
+  if (g_encode) return 0;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+    return fail(BX_E_CUDA, "cuTensorMapEncodeTiled not available from the driver (%s)", cudaGetErrorString(e));
+  g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+  return 0;
+}
+
+// 2D K-major 16-bit matrix [rows, cols] (row pitch ld elements), box [box_rows, 64 cols], SWIZZLE_128B.
+int make_tmap(CUtensorMap* tm, int dtype, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+              uint32_t box_rows) {
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(tm, dtype == BX_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                        2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(BX_E_CUDA, "cuTensorMapEncodeTiled failed: %d (rows=%llu cols=%llu ld=%llu box_rows=%u)", (int)r,
+                (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows);
+  return 0;
+}
+
+}  // namespace
+
+// Layer table (SURVEY §3.2 / Beluga.py:23-45).  Row pitches per window are chosen so that pooled
+// layers see a pitch that is a multiple of 4 and everything else carries as few junk rows as possible.
+struct LayerDef {
+  int taps, cin, cout, block_n, epi;
+  int pitch_in, pitch_out, l_store;
+};
+static const LayerDef kLayers[6] = {
+    {1, 64, 320, 160, EPI_BIAS_RELU, 1996, 1996, 1996},       // conv1 on the im2col one-hot (K = 32 valid)
+    {8, 320, 320, 160, EPI_POOL4_BIAS_RELU, 1996, 496, 496},  // conv2 + ReLU + MaxPool4
+    {8, 320, 480, 240, EPI_BIAS_RELU, 496, 492, 492},         // conv3 + ReLU (489 valid)
+    {8, 480, 480, 240, EPI_POOL4_BIAS_RELU, 492, 120, 120},   // conv4 + ReLU + MaxPool4
+    {8, 480, 640, 160, EPI_BIAS_RELU, 120, 113, 113},         // conv5 + ReLU
+    {8, 640, 640, 160, EPI_BIAS_RELU, 113, 106, 106},         // conv6 + ReLU
+};
+
+struct bx_ctx {
+  int device = 0, dtype = 0, cg = 2, cap = 0, num_sms = 0;
+  bool weights_ready = false;
+  void* wconv[6] = {};   // 16-bit [taps*cout, cin]
+  float* bconv[6] = {};
+  void* wfc1 = nullptr;  // 16-bit [2048, 67840]
+  float* bfc1 = nullptr; // [2048]
+  void* wfc2 = nullptr;  // 16-bit [2048, 2048]
+  float* bfc2 = nullptr; // [2048]
+  void* act[7] = {};     // act[0] = im2col one-hot [cap*1996,64]; act[i] = output of conv i
+  float* acc1 = nullptr; // fp32 [cap, 2048]
+  void* hid = nullptr;   // 16-bit [cap, 2048]
+  const uint32_t* bases2 = nullptr;
+  const uint32_t* nmask = nullptr;
+  int64_t n_bases = 0;
+};
+
+static size_t act_rows(int i) { return i == 0 ? kLayers[0].pitch_in : kLayers[i - 1].pitch_out; }
+static size_t act_cols(int i) { return i == 0 ? 64 : kLayers[i - 1].cout; }
+
+// ------------------------------------------------------------------ GEMM launch
+template <typename T, int TAPS, int BN, int CG, int EPI>
+static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64_t a_cols, const void* b,
+                         uint64_t b_rows, GemmParams p, cudaStream_t st) {
+  using Cfg = GemmCfg<TAPS, BN, CG>;
+  CUtensorMap tmA, tmB;
+  if (int r = make_tmap(&tmA, c->dtype, a, a_rows, a_cols, a_cols, Cfg::A_ROWS)) return r;
+  if (int r = make_tmap(&tmB, c->dtype, b, b_rows, a_cols, a_cols, Cfg::B_ROWS)) return r;
+  auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  p.m_tiles = (p.m_rows + 128 * CG - 1) / (128 * CG);
+  p.n_chunks = p.n_total / BN;
+  const int units = p.m_tiles * p.n_chunks * p.k_splits;
+  int clusters = std::min(units, c->num_sms / CG);
+  if (clusters < 1) clusters = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(clusters * CG);
+  cfg.blockDim = dim3(192);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
+  g_launches++;
+  return 0;
+}
+
+template <typename T, int CG>
+static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void* a, uint64_t a_rows,
+                          uint64_t a_cols, const void* b, uint64_t b_rows, const GemmParams& p, cudaStream_t st) {
+#define BX_CASE(TP, N, E) \
+  if (taps == TP && bn == N && epi == E) return launch_gemm_t<T, TP, N, CG, E>(c, a, a_rows, a_cols, b, b_rows, p, st)
+  BX_CASE(1, 160, EPI_BIAS_RELU);
+  BX_CASE(8, 160, EPI_POOL4_BIAS_RELU);
+  BX_CASE(8, 240, EPI_BIAS_RELU);
+  BX_CASE(8, 240, EPI_POOL4_BIAS_RELU);
+  BX_CASE(8, 160, EPI_BIAS_RELU);
+  BX_CASE(1, 256, EPI_ATOMIC_F32);
+  BX_CASE(1, 256, EPI_BIAS_SIGMOID);
+#undef BX_CASE
+  return fail(BX_E_ARG, "no kernel instance for taps=%d block_n=%d epi=%d", taps, bn, epi);
+}
+
+static int launch_gemm(const bx_ctx* c, int taps, int bn, int epi, const void* a, uint64_t a_rows, uint64_t a_cols,
+                       const void* b, uint64_t b_rows, const GemmParams& p, cudaStream_t st) {
+  if (c->dtype == BX_DTYPE_F16) {
+    if (c->cg == 1) return launch_gemm_tc<__half, 1>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
+    return launch_gemm_tc<__half, 2>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
+  }
+  if (c->cg == 1) return launch_gemm_tc<__nv_bfloat16, 1>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
+  return launch_gemm_tc<__nv_bfloat16, 2>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
+}
+
+// conv layer i (0..5) over n windows: act[i] -> act[i+1]
+static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st) {
+  const LayerDef& L = kLayers[i];
+  GemmParams p = {};
+  p.m_rows = n * L.pitch_in;
+  p.k_valid = (i == 0) ? 32 : L.cin;
+  p.n_total = L.cout;
+  p.k_splits = 1;
+  p.k_blocks = (p.k_valid + 63) / 64;
+  p.kb_per_split = p.k_blocks;
+  p.pitch_in = L.pitch_in;
+  p.pitch_out = L.pitch_out;
+  p.l_store = L.l_store;
+  p.ld_out = L.cout;
+  p.n_store = L.cout;
+  p.bias = c->bconv[i];
+  p.out = c->act[i + 1];
+  return launch_gemm(c, L.taps, L.block_n, L.epi, c->act[i], (uint64_t)n * L.pitch_in, L.cin, c->wconv[i],
+                     (uint64_t)L.taps * L.cout, p, st);
+}
+
+template <typename T>
+static int run_fc1_finalize(bx_ctx* c, int n, cudaStream_t st) {
+  const size_t total = (size_t)n * 2048;
+  fc1_finalize_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(c->acc1, c->bfc1, (T*)c->hid, total);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// conv1..conv6, fc1, fc2 over n windows whose conv1 operand is already in act[0].
+static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st) {
+  for (int i = 0; i < 6; ++i)
+    if (int r = run_conv(c, i, n, st)) return r;
+  // fc1: [n, 67840] x [2048, 67840]^T, split-K partial sums reduced with fp32 atomics
+  CK(cudaMemsetAsync(c->acc1, 0, (size_t)n * 2048 * sizeof(float), st));
+  {
+    GemmParams p = {};
+    p.m_rows = n;
+    p.k_valid = 67840;
+    p.n_total = 2048;
+    p.k_blocks = 67840 / 64;
+    const int m_tiles = (n + 128 * c->cg - 1) / (128 * c->cg);
+    const int clusters = c->num_sms / c->cg;
+    int ks = (3 * clusters + m_tiles * 8 - 1) / (m_tiles * 8);
+    ks = std::max(1, std::min(ks, 20));
+    p.kb_per_split = (p.k_blocks + ks - 1) / ks;
+    p.k_splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+    p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
+    p.ld_out = 2048;
+    p.n_store = 2048;
+    p.bias = nullptr;
+    p.out = c->acc1;
+    if (int r = launch_gemm(c, 1, 256, EPI_ATOMIC_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st)) return r;
+  }
+  if (int r = (c->dtype == BX_DTYPE_F16) ? run_fc1_finalize<__half>(c, n, st) : run_fc1_finalize<__nv_bfloat16>(c, n, st))
+    return r;
+  {
+    GemmParams p = {};
+    p.m_rows = n;
+    p.k_valid = 2048;
+    p.n_total = 2048;
+    p.k_blocks = 32;
+    p.kb_per_split = 32;
+    p.k_splits = 1;
+    p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
+    p.ld_out = BX_FEATURES;
+    p.n_store = BX_FEATURES;
+    p.bias = c->bfc2;
+    p.out = probs;
+    if (int r = launch_gemm(c, 1, 256, EPI_BIAS_SIGMOID, c->hid, n, 2048, c->wfc2, 2048, p, st)) return r;
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------ C ABI
+extern "C" {
+
+int bx_version(void) { return 100; }
+const char* bx_last_error(void) { return g_err; }
+int64_t bx_launch_count(void) { return g_launches.load(); }
+
+int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx_ctx** out) {
+  if (!out) return fail(BX_E_ARG, "out is null");
+  *out = nullptr;
+  if (dtype != BX_DTYPE_F16 && dtype != BX_DTYPE_BF16) return fail(BX_E_ARG, "dtype must be 0 (f16) or 1 (bf16)");
+  if (cta_group != 1 && cta_group != 2) return fail(BX_E_ARG, "cta_group must be 1 or 2");
+  if (capacity_windows < 1) return fail(BX_E_ARG, "capacity_windows must be >= 1");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(BX_E_CUDA, "no CUDA device (%s): this library has no CPU fallback", cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail(BX_E_ARG, "device %d out of range (%d devices)", device, ndev);
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(BX_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major,
+                prop.minor);
+  CK(cudaSetDevice(device));
+  if (int r = load_driver_entry()) return r;
+  bx_ctx* c = new bx_ctx();
+  c->device = device;
+  c->dtype = dtype;
+  c->cg = cta_group;
+  c->cap = capacity_windows;
+  c->num_sms = prop.multiProcessorCount;
+  const size_t cap = capacity_windows;
+  for (int i = 0; i < 7; ++i) {
+    // +256 rows of slack is not needed: TMA zero-fills rows past the tensor end.
+    const size_t bytes = cap * act_rows(i) * act_cols(i) * 2;
+    if (cudaMalloc(&c->act[i], bytes) != cudaSuccess) {
+      bx_ctx_destroy(c);
+      return fail(BX_E_CUDA, "cudaMalloc of activation %d (%zu bytes) failed", i, bytes);
+    }
+    cudaMemset(c->act[i], 0, bytes);
+  }
+  if (cudaMalloc(&c->acc1, cap * 2048 * 4) != cudaSuccess || cudaMalloc(&c->hid, cap * 2048 * 2) != cudaSuccess) {
+    bx_ctx_destroy(c);
+    return fail(BX_E_CUDA, "cudaMalloc of fc scratch failed");
+  }
+  *out = c;
+  return 0;
+}
+
+int bx_ctx_destroy(bx_ctx* c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  for (int i = 0; i < 6; ++i) { cudaFree(c->wconv[i]); cudaFree(c->bconv[i]); }
+  cudaFree(c->wfc1); cudaFree(c->bfc1); cudaFree(c->wfc2); cudaFree(c->bfc2);
+  for (int i = 0; i < 7; ++i) cudaFree(c->act[i]);
+  cudaFree(c->acc1); cudaFree(c->hid);
+  delete c;
+  return 0;
+}
+
+}  // extern "C"
+
+template <typename T>
+static int load_weights_t(bx_ctx* c, const float* const w[8], const float* const b[8]) {
+  cudaStream_t st = 0;
+  float* tmp = nullptr;
+  const size_t fc1_elems = (size_t)2003 * 67840;
+  CK(cudaMalloc(&tmp, fc1_elems * sizeof(float)));
+  auto cleanup = [&]() { cudaFree(tmp); };
+  for (int i = 0; i < 6; ++i) {
+    const LayerDef& L = kLayers[i];
+    const int cin_real = (i == 0) ? 4 : L.cin;
+    const size_t src_elems = (size_t)L.cout * cin_real * 8;
+    const size_t dst_elems = (size_t)L.taps * L.cout * L.cin;
+    if (!c->wconv[i]) CK(cudaMalloc(&c->wconv[i], dst_elems * 2));
+    if (!c->bconv[i]) CK(cudaMalloc(&c->bconv[i], L.cout * sizeof(float)));
+    CK(cudaMemcpy(tmp, w[i], src_elems * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->bconv[i], b[i], L.cout * sizeof(float), cudaMemcpyHostToDevice));
+    if (i == 0)
+      prep_conv1_kernel<T><<<(L.cout * 64 + 255) / 256, 256, 0, st>>>(tmp, (T*)c->wconv[i], L.cout);
+    else
+      prep_conv_kernel<T><<<(unsigned)((dst_elems + 255) / 256), 256, 0, st>>>(tmp, (T*)c->wconv[i], L.cout, L.cin);
+    g_launches++;
+    CK(cudaStreamSynchronize(st));
+  }
+  if (!c->wfc1) CK(cudaMalloc(&c->wfc1, (size_t)2048 * 67840 * 2));
+  if (!c->bfc1) CK(cudaMalloc(&c->bfc1, 2048 * sizeof(float)));
+  if (!c->wfc2) CK(cudaMalloc(&c->wfc2, (size_t)2048 * 2048 * 2));
+  if (!c->bfc2) CK(cudaMalloc(&c->bfc2, 2048 * sizeof(float)));
+  CK(cudaMemcpy(tmp, w[6], fc1_elems * sizeof(float), cudaMemcpyHostToDevice));
+  prep_fc1_kernel<T><<<(unsigned)(((size_t)2048 * 67840 + 255) / 256), 256, 0, st>>>(tmp, (T*)c->wfc1);
+  g_launches++;
+  CK(cudaStreamSynchronize(st));
+  CK(cudaMemcpy(tmp, w[7], (size_t)2002 * 2003 * sizeof(float), cudaMemcpyHostToDevice));
+  prep_fc2_kernel<T><<<(2048 * 2048 + 255) / 256, 256, 0, st>>>(tmp, (T*)c->wfc2);
+  g_launches++;
+  CK(cudaMemset(c->bfc1, 0, 2048 * sizeof(float)));
+  CK(cudaMemset(c->bfc2, 0, 2048 * sizeof(float)));
+  CK(cudaMemcpy(c->bfc1, b[6], 2003 * sizeof(float), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(c->bfc2, b[7], 2002 * sizeof(float), cudaMemcpyHostToDevice));
+  CK(cudaStreamSynchronize(st));
+  CK(cudaGetLastError());
+  cleanup();
+  c->weights_ready = true;
+  return 0;
+}
+
+extern "C" {
+
+int bx_ctx_load_weights(bx_ctx* c, const float* const w[8], const float* const b[8]) {
+  if (!c || !w || !b) return fail(BX_E_ARG, "null argument");
+  for (int i = 0; i < 8; ++i)
+    if (!w[i] || !b[i]) return fail(BX_E_ARG, "weight/bias %d is null", i);
+  CK(cudaSetDevice(c->device));
+  return c->dtype == BX_DTYPE_F16 ? load_weights_t<__half>(c, w, b) : load_weights_t<__nv_bfloat16>(c, w, b);
+}
+
+int bx_ctx_set_genome(bx_ctx* c, const uint32_t* bases2_dev, const uint32_t* nmask_dev, int64_t n_bases) {
+  if (!c || !bases2_dev || !nmask_dev || n_bases <= 0) return fail(BX_E_ARG, "invalid genome arguments");
+  c->bases2 = bases2_dev;
+  c->nmask = nmask_dev;
+  c->n_bases = n_bases;
+  return 0;
+}
+
+int bx_encode_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n,
+                      uint8_t* out_dev, void* stream) {
+  if (!c || !descs_dev || !alleles_dev || !out_dev || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
+  if (n == 0) return 0;
+  CK(cudaSetDevice(c->device));
+  encode_onehot_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(descs_dev, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                             out_dev);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int bx_forward_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n,
+                       float* probs_dev, void* stream) {
+  if (!c || !descs_dev || !alleles_dev || !probs_dev || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  CK(cudaSetDevice(c->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int off = 0; off < n; off += c->cap) {
+    const int m = std::min(c->cap, n - off);
+    if (c->dtype == BX_DTYPE_F16)
+      encode_im2col_kernel<__half><<<m, 256, 0, st>>>(descs_dev + off, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                      (__half*)c->act[0]);
+    else
+      encode_im2col_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(descs_dev + off, alleles_dev, c->bases2, c->nmask,
+                                                             c->n_bases, (__nv_bfloat16*)c->act[0]);
+    g_launches++;
+    CK(cudaGetLastError());
+    if (int r = run_network(c, m, probs_dev + (size_t)off * BX_FEATURES, st)) return r;
+  }
+  return 0;
+}
+
+int bx_forward_onehot(bx_ctx* c, const uint8_t* onehot_dev, int n, float* probs_dev, void* stream) {
+  if (!c || !onehot_dev || !probs_dev || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  CK(cudaSetDevice(c->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int off = 0; off < n; off += c->cap) {
+    const int m = std::min(c->cap, n - off);
+    const uint8_t* x = onehot_dev + (size_t)off * 4 * BX_WINDOW;
+    if (c->dtype == BX_DTYPE_F16)
+      onehot_im2col_kernel<__half><<<m, 256, 0, st>>>(x, (__half*)c->act[0]);
+    else
+      onehot_im2col_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(x, (__nv_bfloat16*)c->act[0]);
+    g_launches++;
+    CK(cudaGetLastError());
+    if (int r = run_network(c, m, probs_dev + (size_t)off * BX_FEATURES, st)) return r;
+  }
+  return 0;
+}
+
+int bx_debug_activation(bx_ctx* c, int layer, int n, void* dst_dev, int64_t* count, void* stream) {
+  if (!c || layer < 0 || layer > 7 || n < 1 || n > c->cap || !dst_dev) return fail(BX_E_ARG, "invalid arguments");
+  const void* src = layer == 7 ? c->hid : c->act[layer];
+  const size_t elems = layer == 7 ? (size_t)n * 2048 : (size_t)n * act_rows(layer) * act_cols(layer);
+  CK(cudaMemcpyAsync(dst_dev, src, elems * 2, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  if (count) *count = (int64_t)elems;
+  return 0;
+}
+
+int bx_chromatin_outputs(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,
+                         void* stream) {
+  if (!probs_dev || !ref_dev || !alt_dev || !diff_dev || n_var < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n_var == 0) return 0;
+  chromatin_outputs_kernel<<<n_var, 256, 0, (cudaStream_t)stream>>>(probs_dev, n_var, ref_dev, alt_dev, diff_dev);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int bx_chromatin_outputs_avg(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,
+                             void* stream) {
+  if (!probs_dev || !ref_dev || !alt_dev || !diff_dev || n_var < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n_var == 0) return 0;
+  chromatin_outputs_avg_kernel<<<n_var, 256, 0, (cudaStream_t)stream>>>(probs_dev, n_var, ref_dev, alt_dev,
+                                                                       diff_dev);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, int n_genes, int n_shifts,
+                             float* out_dev, void* stream) {
+  if (!probs_dev || !weights_dev || !out_dev || n_genes < 0 || n_shifts < 1 || n_shifts > 1024)
+    return fail(BX_E_ARG, "invalid arguments");
+  if (n_genes == 0) return 0;
+  const size_t smem = (size_t)(10 * n_shifts + (kTfSlices - 1) * 10 * kTfF) * sizeof(float);
+  dim3 grid((kFeat + kTfF - 1) / kTfF, n_genes), block(kTfF, kTfSlices);
+  decay_fixed_kernel<<<grid, block, smem, (cudaStream_t)stream>>>(probs_dev, weights_dev, n_shifts, out_dev);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int bx_decay_transform_variant(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+                               const int32_t* shifts_dev, int n, int n_shifts, float* out_dev, void* stream) {
+  if (!x_dev || !dist_dev || !strand_dev || !shifts_dev || !out_dev || n < 0 || n_shifts < 1 || n_shifts > 25)
+    return fail(BX_E_ARG, "invalid arguments (n_shifts must be 1..25)");
+  if (n == 0) return 0;
+  dim3 grid((kFeat + 255) / 256, n);
+  decay_variant_kernel<<<grid, 256, n_shifts * 10 * sizeof(float), (cudaStream_t)stream>>>(
+      x_dev, dist_dev, strand_dev, shifts_dev, n, n_shifts, out_dev);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

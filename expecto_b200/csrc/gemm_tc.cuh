@@ -1,0 +1,342 @@
+// Persistent, warp-specialised tcgen05 implicit-GEMM kernel used for every dense contraction of the
+// Beluga forward (reference: Beluga.py:23-45 — six Conv2d(1,8) layers and two Linear layers).
+//
+// Data layout (HBM): activations are channels-last fp16/bf16 matrices [rows, C] where rows is the
+// flattened (window, position) axis with a fixed per-window pitch.  A Conv2d(Cin,Cout,(1,8)) is then
+//     out[r, co] = sum_{t<8} sum_{ci} act[r + t, ci] * W_t[co, ci]
+// i.e. eight GEMMs whose A operands are the SAME activation tile shifted by t rows.  The producer
+// TMA-loads one [128+8 rows x 64 ch] slab per K-block (SWIZZLE_128B) and the MMA thread addresses
+// tap t as a +t*128-byte view of that slab, so activations cross L2->SMEM once, not eight times.
+// Weights are stored tap-major [TAPS*Cout, Cin] (K-major) and stream through their own ring.
+//
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM allocator,
+// warps 2..5 = epilogue (TMEM -> registers -> bias/ReLU/pool/sigmoid -> global).
+// CTA_GROUP == 2 runs a CTA pair (cluster of 2): M = 256 per pair, each CTA stages its own 128 A
+// rows and half of the B rows, the leader CTA issues tcgen05.mma.cta_group::2.
+// Accumulators live in a TMEM ring of 512/BLOCK_N buffers so the epilogue overlaps the next tile.
+#pragma once
+#include <type_traits>
+#include "ptx.cuh"
+
+namespace bx {
+
+enum EpiKind : int {
+  EPI_BIAS_RELU = 0,       // y = relu(acc + b) -> 16-bit, rows remapped pitch_in -> pitch_out
+  EPI_POOL4_BIAS_RELU = 1, // y = max over 4 consecutive rows of relu(acc + b) -> 16-bit (MaxPool(1,4))
+  EPI_ATOMIC_F32 = 2,      // split-K partial sums: red.add.f32 into an fp32 [rows, ld_out] buffer
+  EPI_BIAS_SIGMOID = 3,    // y = sigmoid(acc + b) -> fp32
+};
+
+struct GemmParams {
+  int m_rows;        // valid rows of A (flattened window x position)
+  int k_valid;       // K extent actually multiplied (per tap)
+  int n_total;       // output channels (rows of B per tap)
+  int m_tiles;       // ceil(m_rows / (128*CTA_GROUP))
+  int n_chunks;      // n_total / BLOCK_N
+  int k_splits;      // split-K factor (EPI_ATOMIC_F32 only, else 1)
+  int k_blocks;      // ceil(k_valid / 64)
+  int kb_per_split;  // ceil(k_blocks / k_splits)
+  int pitch_in;      // rows per window in the accumulator row space
+  int pitch_out;     // rows per window in the output
+  int l_store;       // output rows stored per window
+  int ld_out;        // output leading dimension in elements
+  int n_store;       // columns >= n_store are not stored
+  const float* bias; // [n_total] fp32 (unused for EPI_ATOMIC_F32)
+  void* out;
+};
+
+template <int TAPS, int BLOCK_N, int CG>
+struct GemmCfg {
+  static constexpr int A_ROWS = 128 + (TAPS > 1 ? 8 : 0);
+  static constexpr int A_BYTES = A_ROWS * 128;
+  static constexpr int B_ROWS = BLOCK_N / CG;
+  static constexpr int B_BYTES = B_ROWS * 128;
+  static constexpr int SMEM_BUDGET = 227 * 1024 - 2048;  // barriers + 1 KB alignment slack
+  static constexpr int SA = (TAPS > 1) ? 3 : 4;
+  static constexpr int SB_MAX = (SMEM_BUDGET - SA * A_BYTES) / B_BYTES;
+  static constexpr int SB = (TAPS > 1) ? (SB_MAX > 16 ? 16 : SB_MAX) : (SB_MAX > SA ? SA : SB_MAX);
+  static constexpr int NBUF = 512 / BLOCK_N;
+  static constexpr int SMEM_BYTES = SA * A_BYTES + SB * B_BYTES + 1024 /*barriers*/ + 1024 /*align*/;
+  static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment (SWIZZLE_128B)");
+  static_assert(A_BYTES % 1024 == 0, "A stage must keep 1024-byte alignment (SWIZZLE_128B)");
+  static_assert(SB >= 2 && NBUF >= 1, "pipeline too shallow");
+  static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "invalid UMMA N");
+};
+
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float a, float b);
+template <>
+__device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+  __half2 h = __floats2half2_rn(fminf(a, 65504.f), fminf(b, 65504.f));
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+template <>
+__device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+template <typename T>
+__device__ __forceinline__ uint32_t max2(uint32_t a, uint32_t b);
+template <>
+__device__ __forceinline__ uint32_t max2<__half>(uint32_t a, uint32_t b) {
+  __half2 r = __hmax2(*reinterpret_cast<__half2*>(&a), *reinterpret_cast<__half2*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+template <>
+__device__ __forceinline__ uint32_t max2<__nv_bfloat16>(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+struct RingState {
+  uint32_t idx = 0, phase = 0;
+  template <int N>
+  __device__ __forceinline__ void advance() {
+    if (++idx == N) { idx = 0; phase ^= 1; }
+  }
+};
+
+template <typename T, int TAPS, int BLOCK_N, int CG, int EPI>
+__global__ void __launch_bounds__(192, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const GemmParams p) {
+  using Cfg = GemmCfg<TAPS, BLOCK_N, CG>;
+  constexpr int SA = Cfg::SA, SB = Cfg::SB, NBUF = Cfg::NBUF;
+  constexpr int FMT = sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+  constexpr uint32_t IDESC = make_idesc_f16(FMT, 128 * CG, BLOCK_N);
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;  // identical in both CTAs of a pair
+  const uint32_t sA = base;
+  const uint32_t sB = sA + SA * Cfg::A_BYTES;
+  const uint32_t bars = sB + SB * Cfg::B_BYTES;
+  auto fullA = [&](uint32_t i) { return bars + 8u * i; };
+  auto emptyA = [&](uint32_t i) { return bars + 8u * (SA + i); };
+  auto fullB = [&](uint32_t i) { return bars + 8u * (2 * SA + i); };
+  auto emptyB = [&](uint32_t i) { return bars + 8u * (2 * SA + SB + i); };
+  auto tfull = [&](uint32_t i) { return bars + 8u * (2 * SA + 2 * SB + i); };
+  auto tempty = [&](uint32_t i) { return bars + 8u * (2 * SA + 2 * SB + NBUF + i); };
+  const uint32_t tmem_slot = bars + 8u * (2 * SA + 2 * SB + 2 * NBUF);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = (CG == 1) ? 0u : cluster_ctarank();
+  const int num_clusters = gridDim.x / CG;
+  const int cluster_id = blockIdx.x / CG;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmA);
+    prefetch_tensormap(&tmB);
+    for (int i = 0; i < SA; ++i) { mbar_init(fullA(i), 1); mbar_init(emptyA(i), 1); }
+    for (int i = 0; i < SB; ++i) { mbar_init(fullB(i), 1); mbar_init(emptyB(i), 1); }
+    for (int i = 0; i < NBUF; ++i) { mbar_init(tfull(i), 1); mbar_init(tempty(i), 4 * CG); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<CG>(tmem_slot, 512);
+  tc_fence_before();
+  if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int tiles_mn = p.m_tiles * p.n_chunks;
+  const int total_units = tiles_mn * p.k_splits;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      RingState ra, rb;
+      for (int u = cluster_id; u < total_units; u += num_clusters) {
+        const int ks = u / tiles_mn, rem = u - ks * tiles_mn;
+        const int mt = rem / p.n_chunks, nc = rem - mt * p.n_chunks;
+        const int kb0 = ks * p.kb_per_split;
+        const int kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
+        const int row0 = mt * 128 * CG + (int)rank * 128;
+        const int ncol0 = nc * BLOCK_N + (int)rank * Cfg::B_ROWS;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
+          if constexpr (CG == 1) {
+            mbar_arrive_expect_tx(fullA(ra.idx), Cfg::A_BYTES);
+            tma_load_2d(sA + ra.idx * Cfg::A_BYTES, &tmA, fullA(ra.idx), kb * 64, row0);
+          } else {
+            if (rank == 0) mbar_arrive_expect_tx(fullA(ra.idx), 2 * Cfg::A_BYTES);
+            tma_load_2d_pair(sA + ra.idx * Cfg::A_BYTES, &tmA, mapa(fullA(ra.idx), 0), kb * 64, row0);
+          }
+          ra.advance<SA>();
+#pragma unroll 1
+          for (int t = 0; t < TAPS; ++t) {
+            mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
+            if constexpr (CG == 1) {
+              mbar_arrive_expect_tx(fullB(rb.idx), Cfg::B_BYTES);
+              tma_load_2d(sB + rb.idx * Cfg::B_BYTES, &tmB, fullB(rb.idx), kb * 64, t * p.n_total + ncol0);
+            } else {
+              if (rank == 0) mbar_arrive_expect_tx(fullB(rb.idx), 2 * Cfg::B_BYTES);
+              tma_load_2d_pair(sB + rb.idx * Cfg::B_BYTES, &tmB, mapa(fullB(rb.idx), 0), kb * 64,
+                               t * p.n_total + ncol0);
+            }
+            rb.advance<SB>();
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA, one thread)
+    if (rank == 0 && lane == 0) {
+      RingState ra, rb, rt;
+      for (int u = cluster_id; u < total_units; u += num_clusters) {
+        const int ks = u / tiles_mn;
+        const int kb0 = ks * p.kb_per_split;
+        const int kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
+        mbar_wait(tempty(rt.idx), rt.phase ^ 1, 3);
+        tc_fence_after();
+        const uint32_t d = tmem_base + rt.idx * BLOCK_N;
+        uint32_t accum = 0;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          const int kcount = min(4, (p.k_valid - kb * 64 + 15) >> 4);
+          mbar_wait(fullA(ra.idx), ra.phase, 4);
+          tc_fence_after();
+          const uint32_t a_base = sA + ra.idx * Cfg::A_BYTES;
+#pragma unroll 1
+          for (int t = 0; t < TAPS; ++t) {
+            mbar_wait(fullB(rb.idx), rb.phase, 5);
+            tc_fence_after();
+            const uint32_t b_base = sB + rb.idx * Cfg::B_BYTES;
+            for (int k = 0; k < kcount; ++k) {
+              umma_f16<CG>(d, make_sw128_desc(a_base + t * 128 + k * 32), make_sw128_desc(b_base + k * 32), IDESC,
+                           accum);
+              accum = 1;
+            }
+            umma_commit<CG>(emptyB(rb.idx));
+            rb.advance<SB>();
+          }
+          umma_commit<CG>(emptyA(ra.idx));
+          ra.advance<SA>();
+        }
+        umma_commit<CG>(tfull(rt.idx));
+        rt.advance<NBUF>();
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps 2..5
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    RingState rt;
+    for (int u = cluster_id; u < total_units; u += num_clusters) {
+      const int ks = u / tiles_mn, rem = u - ks * tiles_mn;
+      const int mt = rem / p.n_chunks, nc = rem - mt * p.n_chunks;
+      const int r = mt * 128 * CG + (int)rank * 128 + q * 32 + lane;
+      const int wb = r / p.pitch_in;
+      const int l = r - wb * p.pitch_in;
+      mbar_wait(tfull(rt.idx), rt.phase, 6);
+      tc_fence_after();
+      const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + rt.idx * BLOCK_N;
+      const int n0 = nc * BLOCK_N;
+
+      if constexpr (EPI == EPI_BIAS_RELU) {
+        const bool valid = (r < p.m_rows) && (l < p.l_store);
+        T* orow = reinterpret_cast<T*>(p.out) + (size_t)(wb * p.pitch_out + l) * p.ld_out + n0;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 16; ++c) {
+          uint32_t v[16];
+          tmem_ld16(t0 + c * 16, v);
+          tmem_ld_wait();
+          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c * 16);
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 b4 = __ldg(bp + i);
+            pk[2 * i] = pack2<T>(fmaxf(__uint_as_float(v[4 * i]) + b4.x, 0.f),
+                                 fmaxf(__uint_as_float(v[4 * i + 1]) + b4.y, 0.f));
+            pk[2 * i + 1] = pack2<T>(fmaxf(__uint_as_float(v[4 * i + 2]) + b4.z, 0.f),
+                                     fmaxf(__uint_as_float(v[4 * i + 3]) + b4.w, 0.f));
+          }
+          if (valid) {
+            uint4* dst = reinterpret_cast<uint4*>(orow + c * 16);
+            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          }
+        }
+      } else if constexpr (EPI == EPI_POOL4_BIAS_RELU) {
+        const int lp = l >> 2;
+        const bool valid = (r < p.m_rows) && (lp < p.l_store);
+        const int j = lane & 3;
+        T* orow = reinterpret_cast<T*>(p.out) + (size_t)(wb * p.pitch_out + lp) * p.ld_out + n0 + 4 * j;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 16; ++c) {
+          uint32_t v[16];
+          tmem_ld16(t0 + c * 16, v);
+          tmem_ld_wait();
+          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c * 16);
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 b4 = __ldg(bp + i);
+            pk[2 * i] = pack2<T>(fmaxf(__uint_as_float(v[4 * i]) + b4.x, 0.f),
+                                 fmaxf(__uint_as_float(v[4 * i + 1]) + b4.y, 0.f));
+            pk[2 * i + 1] = pack2<T>(fmaxf(__uint_as_float(v[4 * i + 2]) + b4.z, 0.f),
+                                     fmaxf(__uint_as_float(v[4 * i + 3]) + b4.w, 0.f));
+          }
+          // MaxPool over the 4 rows held by lanes 4g..4g+3 (rounding is monotonic, so max after rounding
+          // equals rounding after max).
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            pk[i] = max2<T>(pk[i], __shfl_xor_sync(0xffffffffu, pk[i], 1));
+            pk[i] = max2<T>(pk[i], __shfl_xor_sync(0xffffffffu, pk[i], 2));
+          }
+          uint32_t w0 = pk[0], w1 = pk[1];
+          if (j == 1) { w0 = pk[2]; w1 = pk[3]; }
+          if (j == 2) { w0 = pk[4]; w1 = pk[5]; }
+          if (j == 3) { w0 = pk[6]; w1 = pk[7]; }
+          if (valid) *reinterpret_cast<uint2*>(orow + c * 16) = make_uint2(w0, w1);
+        }
+      } else if constexpr (EPI == EPI_ATOMIC_F32) {
+        const bool valid = r < p.m_rows;
+        float* orow = reinterpret_cast<float*>(p.out) + (size_t)r * p.ld_out + n0;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 16; ++c) {
+          uint32_t v[16];
+          tmem_ld16(t0 + c * 16, v);
+          tmem_ld_wait();
+          if (valid) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (n0 + c * 16 + i < p.n_store) atomicAdd(orow + c * 16 + i, __uint_as_float(v[i]));
+          }
+        }
+      } else {  // EPI_BIAS_SIGMOID
+        const bool valid = r < p.m_rows;
+        float* orow = reinterpret_cast<float*>(p.out) + (size_t)r * p.ld_out + n0;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 16; ++c) {
+          uint32_t v[16];
+          tmem_ld16(t0 + c * 16, v);
+          tmem_ld_wait();
+          if (valid) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int n = n0 + c * 16 + i;
+              if (n < p.n_store) {
+                const float z = __uint_as_float(v[i]) + __ldg(p.bias + n);
+                orow[c * 16 + i] = 1.f / (1.f + __expf(-z));
+              }
+            }
+          }
+        }
+      }
+      // Release the TMEM buffer to the MMA thread (leader CTA's barrier).
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(CG == 1 ? tempty(rt.idx) : mapa(tempty(rt.idx), 0));
+      rt.advance<NBUF>();
+    }
+  }
+
+  // ------------------------------------------------------------------ teardown
+  tc_fence_before();
+  if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<CG>(tmem_base, 512);
+  }
+}
+
+}  // namespace bx

@@ -1,0 +1,284 @@
+// Non-GEMM kernels of the hot path: window extraction / one-hot / reverse complement from the 2-bit
+// packed genome (reference: fetchSeqs chromatin.py:175-209, encodeSeqs chromatin.py:138-172),
+// weight re-layout, small element-wise finalisers and the decay-weighted shift reductions
+// (reference: compute_expecto_features.py:123-124, predict.py:87-136).  All are HBM-bound byte/float
+// streaming kernels: coalesced along the innermost axis, no tensor cores.
+#pragma once
+#include <cstdint>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include "../../include/beluga_b200.h"
+
+namespace bx {
+
+constexpr int kWin = 2000;
+constexpr int kP1 = 1996;   // row pitch of the conv1 operand / conv1 output per window (1993 valid)
+constexpr int kFeat = 2002;
+
+// Channel code (A=0,G=1,C=2,T=3; 4 = all-zero column) of forward-strand position i of a window.
+__device__ __forceinline__ int window_code(const bx_window_desc& d, int i, const uint32_t* __restrict__ bases2,
+                                           const uint32_t* __restrict__ nmask, const uint8_t* __restrict__ alleles,
+                                           int64_t n_bases) {
+  int64_t g;
+  if (i < d.len1) {
+    g = d.g1 + i;
+  } else if (i < d.len1 + d.alen) {
+    return alleles[d.aoff + (i - d.len1)];
+  } else if (i < d.len1 + d.alen + d.len2) {
+    g = d.g2 + (i - d.len1 - d.alen);
+  } else {
+    return 4;
+  }
+  if (g < 0 || g >= n_bases) return 4;
+  if ((__ldg(nmask + (g >> 5)) >> (g & 31)) & 1u) return 4;
+  return (__ldg(bases2 + (g >> 4)) >> ((g & 15) * 2)) & 3u;
+}
+
+// Codes of one window in strand orientation into shared memory (2000 + 8 pad entries of 4).
+__device__ __forceinline__ void load_window_codes(uint8_t* codes, const bx_window_desc& d,
+                                                  const uint32_t* __restrict__ bases2,
+                                                  const uint32_t* __restrict__ nmask,
+                                                  const uint8_t* __restrict__ alleles, int64_t n_bases) {
+  const bool rc = d.flags & 1;
+  for (int i = threadIdx.x; i < kWin + 8; i += blockDim.x) {
+    int c = 4;
+    if (i < kWin) {
+      c = window_code(d, rc ? (kWin - 1 - i) : i, bases2, nmask, alleles, n_bases);
+      if (rc && c < 4) c = 3 - c;  // A<->T, G<->C: encodeSeqs' [:, ::-1, ::-1]
+    }
+    codes[i] = (uint8_t)c;
+  }
+}
+
+// encodeSeqs materialised: out uint8 [n,4,2000].  One block per window.
+__global__ void encode_onehot_kernel(const bx_window_desc* __restrict__ descs, const uint8_t* __restrict__ alleles,
+                                     const uint32_t* __restrict__ bases2, const uint32_t* __restrict__ nmask,
+                                     int64_t n_bases, uint8_t* __restrict__ out) {
+  __shared__ uint8_t codes[kWin + 8];
+  const bx_window_desc d = descs[blockIdx.x];
+  load_window_codes(codes, d, bases2, nmask, alleles, n_bases);
+  __syncthreads();
+  uint8_t* o = out + (size_t)blockIdx.x * 4 * kWin;
+  for (int idx = threadIdx.x; idx < 4 * kWin; idx += blockDim.x) {
+    const int ch = idx / kWin, i = idx - ch * kWin;
+    o[idx] = codes[i] == ch ? 1 : 0;
+  }
+}
+
+// 16-bit 1.0 in the operand format.
+template <typename T> __device__ __forceinline__ uint32_t one_bits();
+template <> __device__ __forceinline__ uint32_t one_bits<__half>() { return 0x3C00u; }
+template <> __device__ __forceinline__ uint32_t one_bits<__nv_bfloat16>() { return 0x3F80u; }
+
+// Write the conv1 operand rows of one window from its codes: row l = [onehot(l), ..., onehot(l+7), 0 x32]
+// (k = tap*4 + channel), 128 bytes per row, one thread per row.
+template <typename T>
+__device__ __forceinline__ void write_im2col_rows(const uint8_t* codes, uint4* __restrict__ dst_rows) {
+  const uint32_t one = one_bits<T>();
+  for (int l = threadIdx.x; l < kP1; l += blockDim.x) {
+    uint32_t w[16];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const int c = (l + t < kWin + 8) ? codes[l + t] : 4;
+      // channels 0,1 -> word 2t ; channels 2,3 -> word 2t+1
+      w[2 * t] = (c == 0) ? one : (c == 1) ? (one << 16) : 0u;
+      w[2 * t + 1] = (c == 2) ? one : (c == 3) ? (one << 16) : 0u;
+    }
+    uint4* o = dst_rows + (size_t)l * 8;
+    o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    o[2] = make_uint4(w[8], w[9], w[10], w[11]);
+    o[3] = make_uint4(w[12], w[13], w[14], w[15]);
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    o[4] = z; o[5] = z; o[6] = z; o[7] = z;
+  }
+}
+
+// Kernel 1 fused form: packed genome + descriptors -> conv1 operand [n*1996, 64] (never a one-hot in HBM).
+template <typename T>
+__global__ void encode_im2col_kernel(const bx_window_desc* __restrict__ descs, const uint8_t* __restrict__ alleles,
+                                     const uint32_t* __restrict__ bases2, const uint32_t* __restrict__ nmask,
+                                     int64_t n_bases, T* __restrict__ a0) {
+  __shared__ uint8_t codes[kWin + 8];
+  const bx_window_desc d = descs[blockIdx.x];
+  load_window_codes(codes, d, bases2, nmask, alleles, n_bases);
+  __syncthreads();
+  write_im2col_rows<T>(codes, reinterpret_cast<uint4*>(a0) + (size_t)blockIdx.x * kP1 * 8);
+}
+
+// Same from an explicit one-hot uint8 [n,4,2000] (all-zero column -> code 4).
+template <typename T>
+__global__ void onehot_im2col_kernel(const uint8_t* __restrict__ onehot, T* __restrict__ a0) {
+  __shared__ uint8_t codes[kWin + 8];
+  const uint8_t* x = onehot + (size_t)blockIdx.x * 4 * kWin;
+  for (int i = threadIdx.x; i < kWin + 8; i += blockDim.x) {
+    int c = 4;
+    if (i < kWin) {
+      if (x[i]) c = 0;
+      else if (x[kWin + i]) c = 1;
+      else if (x[2 * kWin + i]) c = 2;
+      else if (x[3 * kWin + i]) c = 3;
+    }
+    codes[i] = (uint8_t)c;
+  }
+  __syncthreads();
+  write_im2col_rows<T>(codes, reinterpret_cast<uint4*>(a0) + (size_t)blockIdx.x * kP1 * 8);
+}
+
+// ------------------------------------------------------------------ weight re-layout (run once)
+template <typename T> __device__ __forceinline__ T to_t(float v);
+template <> __device__ __forceinline__ __half to_t<__half>(float v) { return __float2half_rn(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 to_t<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// conv1: src [320,4,1,8] -> dst [320,64], k = t*4 + c, k >= 32 zero.
+template <typename T>
+__global__ void prep_conv1_kernel(const float* __restrict__ src, T* __restrict__ dst, int cout) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= cout * 64) return;
+  const int co = idx >> 6, k = idx & 63;
+  float v = 0.f;
+  if (k < 32) { const int t = k >> 2, c = k & 3; v = src[(co * 4 + c) * 8 + t]; }
+  dst[idx] = to_t<T>(v);
+}
+// conv2..6: src [Cout,Cin,1,8] -> dst [8*Cout, Cin] (tap-major, K-major rows).
+template <typename T>
+__global__ void prep_conv_kernel(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (size_t)8 * cout * cin) return;
+  const int ci = idx % cin;
+  const int co = (idx / cin) % cout;
+  const int t = idx / ((size_t)cin * cout);
+  dst[idx] = to_t<T>(src[((size_t)co * cin + ci) * 8 + t]);
+}
+// fc1: src [2003, 67840] with column c*106+l -> dst [2048, 67840] with column l*640+c, rows >= 2003 zero.
+template <typename T>
+__global__ void prep_fc1_kernel(const float* __restrict__ src, T* __restrict__ dst) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (size_t)2048 * 67840) return;
+  const int col = idx % 67840;
+  const int n = idx / 67840;
+  const int l = col / 640, c = col - l * 640;
+  dst[idx] = to_t<T>(n < 2003 ? src[(size_t)n * 67840 + c * 106 + l] : 0.f);
+}
+// fc2: src [2002, 2003] -> dst [2048, 2048] zero padded.
+template <typename T>
+__global__ void prep_fc2_kernel(const float* __restrict__ src, T* __restrict__ dst) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 2048 * 2048) return;
+  const int k = idx & 2047, n = idx >> 11;
+  dst[idx] = to_t<T>((n < 2002 && k < 2003) ? src[(size_t)n * 2003 + k] : 0.f);
+}
+
+// fc1 finaliser: h = relu(acc + b1) -> 16-bit [n, 2048].
+template <typename T>
+__global__ void fc1_finalize_kernel(const float* __restrict__ acc, const float* __restrict__ bias,
+                                    T* __restrict__ h, size_t total) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const float v = fmaxf(acc[idx] + bias[idx & 2047], 0.f);
+  h[idx] = to_t<T>(fminf(v, 65504.f));
+}
+
+// ------------------------------------------------------------------ chromatin.py:281-286 outputs
+// probs [4N, 2002] in (variant, {ref fwd, ref rc, alt fwd, alt rc}) order.
+__global__ void chromatin_outputs_kernel(const float* __restrict__ probs, int n_var, float* __restrict__ ref,
+                                         float* __restrict__ alt, float* __restrict__ diff) {
+  const int v = blockIdx.x;
+  const float* p = probs + (size_t)v * 4 * kFeat;
+  for (int f = threadIdx.x; f < kFeat; f += blockDim.x) {
+    const float rf = p[f], rr = p[kFeat + f], af = p[2 * kFeat + f], ar = p[3 * kFeat + f];
+    const size_t of = (size_t)v * kFeat + f, orc = (size_t)(n_var + v) * kFeat + f;
+    ref[of] = rf; ref[orc] = rr;
+    alt[of] = af; alt[orc] = ar;
+    diff[of] = af - rf; diff[orc] = ar - rr;
+  }
+}
+// predict.py:186-190 folded in: (fwd + rc) / 2 of diff/ref/alt, where diff halves are formed first as the
+// reference does (alt - ref per strand, chromatin.py:281).
+__global__ void chromatin_outputs_avg_kernel(const float* __restrict__ probs, int n_var, float* __restrict__ ref,
+                                             float* __restrict__ alt, float* __restrict__ diff) {
+  const int v = blockIdx.x;
+  const float* p = probs + (size_t)v * 4 * kFeat;
+  for (int f = threadIdx.x; f < kFeat; f += blockDim.x) {
+    const float rf = p[f], rr = p[kFeat + f], af = p[2 * kFeat + f], ar = p[3 * kFeat + f];
+    const size_t o = (size_t)v * kFeat + f;
+    ref[o] = (rf + rr) / 2.0f;
+    alt[o] = (af + ar) / 2.0f;
+    diff[o] = ((af - rf) + (ar - rr)) / 2.0f;
+  }
+}
+
+// ------------------------------------------------------------------ kernel 4: decay-weighted shift reductions
+// Fixed weights (compute_expecto_features.py:123-124).  Block = (gene, 128-feature tile) x 4 shift slices;
+// loads are coalesced along the feature axis, each thread keeps 10 partial sums, slices are combined
+// through shared memory.  probs [G, S, 2, 2002], w [10, S], out [G, 10, 2002].
+constexpr int kTfF = 128, kTfSlices = 4;
+__global__ void __launch_bounds__(kTfF * kTfSlices)
+decay_fixed_kernel(const float* __restrict__ probs, const float* __restrict__ w, int n_shifts,
+                   float* __restrict__ out) {
+  extern __shared__ float sm[];                 // w[10*S] then partials [slices-1][10][128]
+  float* sw = sm;
+  float* part = sm + 10 * n_shifts;
+  const int g = blockIdx.y;
+  const int f = blockIdx.x * kTfF + threadIdx.x;
+  const int slice = threadIdx.y;
+  for (int i = threadIdx.y * kTfF + threadIdx.x; i < 10 * n_shifts; i += kTfF * kTfSlices) sw[i] = w[i];
+  __syncthreads();
+  float acc[10];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) acc[k] = 0.f;
+  if (f < kFeat) {
+    const float* p = probs + (size_t)g * n_shifts * 2 * kFeat + f;
+    for (int s = slice; s < n_shifts; s += kTfSlices) {
+      const float x = 0.5f * (__ldg(p + (size_t)(2 * s) * kFeat) + __ldg(p + (size_t)(2 * s + 1) * kFeat));
+#pragma unroll
+      for (int k = 0; k < 10; ++k) acc[k] = fmaf(sw[k * n_shifts + s], x, acc[k]);
+    }
+  }
+  if (slice > 0) {
+#pragma unroll
+    for (int k = 0; k < 10; ++k) part[((slice - 1) * 10 + k) * kTfF + threadIdx.x] = acc[k];
+  }
+  __syncthreads();
+  if (slice == 0 && f < kFeat) {
+#pragma unroll
+    for (int k = 0; k < 10; ++k) {
+      float v = acc[k];
+      for (int sl = 0; sl < kTfSlices - 1; ++sl) v += part[(sl * 10 + k) * kTfF + threadIdx.x];
+      out[((size_t)g * 10 + k) * kFeat + f] = v;
+    }
+  }
+}
+
+// Per-variant weights (predict.py:87-109) computed in-kernel in fp64, then the same reduction over S
+// shifts.  x [S, n, 2002], out [n, 10, 2002].  Block = (variant, 256-feature tile).
+__global__ void __launch_bounds__(256)
+decay_variant_kernel(const float* __restrict__ x, const double* __restrict__ dist, const int8_t* __restrict__ strand,
+                     const int32_t* __restrict__ shifts, int n, int n_shifts, float* __restrict__ out) {
+  extern __shared__ float sw[];  // [S][10]
+  const int v = blockIdx.y;
+  if (threadIdx.x < n_shifts * 10) {
+    const int j = threadIdx.x / 10, k = threadIdx.x - j * 10;
+    const double sgn = strand[v] > 0 ? 1.0 : -1.0;
+    const double pos = dist[v] * sgn + (double)shifts[j] * sgn;
+    const double rate[5] = {0.01, 0.02, 0.05, 0.1, 0.2};
+    const double e = exp(-rate[k % 5] * floor(fabs(pos / 200.0)));
+    const bool on = (k < 5) ? (pos <= 0.0) : (pos >= 0.0);
+    sw[j * 10 + k] = on ? (float)e : 0.f;
+  }
+  __syncthreads();
+  const int f = blockIdx.x * 256 + threadIdx.x;
+  if (f >= kFeat) return;
+  float acc[10];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) acc[k] = 0.f;
+  for (int j = 0; j < n_shifts; ++j) {
+    const float xv = __ldg(x + ((size_t)j * n + v) * kFeat + f);
+#pragma unroll
+    for (int k = 0; k < 10; ++k) acc[k] = fmaf(sw[j * 10 + k], xv, acc[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < 10; ++k) out[((size_t)v * 10 + k) * kFeat + f] = acc[k];
+}
+
+}  // namespace bx

@@ -1,0 +1,108 @@
+/* beluga_b200 — C ABI of the B200-native Beluga chromatin-effect hot path.
+ *
+ * The reference (richardshuai/ExPecto) has no FFI: its boundary is Python scripts + files.  This
+ * header is what a binding for that path would call; each entry point cites the reference code it
+ * replaces.  All functions return 0 on success or a negative code (see BX_E_*); bx_last_error()
+ * gives the message.  No exceptions cross the boundary, the caller owns every buffer, device
+ * pointers are plain `void*` (e.g. torch.Tensor.data_ptr()), streams are cudaStream_t as `void*`.
+ * There is NO CPU fallback: every compute entry point fails with BX_E_CUDA when no sm_100 device
+ * is present.
+ */
+#ifndef BELUGA_B200_H
+#define BELUGA_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BX_OK 0
+#define BX_E_ARG (-1)     /* invalid argument */
+#define BX_E_CUDA (-2)    /* CUDA runtime/driver error, or no sm_100 device */
+#define BX_E_STATE (-3)   /* weights / genome not set */
+#define BX_E_BASE (-4)    /* a window touched a base the reference's encodeSeqs would raise KeyError on */
+
+#define BX_DTYPE_F16 0
+#define BX_DTYPE_BF16 1
+
+#define BX_WINDOW 2000     /* Beluga input length, chromatin.py:35-36 */
+#define BX_FEATURES 2002   /* Beluga outputs, Beluga.py:45 */
+#define BX_NBASIS 10       /* decay bases, predict.py:88-109 */
+
+/* One 2000-bp model input, described as  genome[g1 : g1+len1] + allele[aoff : aoff+alen] +
+ * genome[g2 : g2+len2]  (positions past the total are all-zero columns).  This is the result of
+ * fetchSeqs' splice (chromatin.py:175-209) followed by encodeSeqs' centre crop (chromatin.py:164),
+ * or a plain TSS window (compute_expecto_features.py:107-111, alen = len2 = 0).
+ * g1/g2 index the packed genome set with bx_ctx_set_genome.  flags bit 0: emit the reverse
+ * complement (encodeSeqs' [:, ::-1, ::-1], chromatin.py:170). */
+typedef struct bx_window_desc {
+  int64_t g1;
+  int64_t g2;
+  int32_t len1;
+  int32_t alen;
+  int32_t len2;
+  int32_t aoff;
+  int32_t flags;
+  int32_t reserved;
+} bx_window_desc;
+
+typedef struct bx_ctx bx_ctx;
+
+int bx_version(void);
+const char* bx_last_error(void);
+/* Number of kernels this library has launched since load (bench.py's gpu_launches). */
+int64_t bx_launch_count(void);
+
+/* One context per GPU; a context is single-threaded.  capacity_windows bounds the windows per
+ * forward call chunk (activation scratch is sized once here).  cta_group: 1 or 2 (CTA pairs). */
+int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx_ctx** out);
+int bx_ctx_destroy(bx_ctx* ctx);
+
+/* Weights in the reference's state_dict order and layouts (Beluga.py:23-45), HOST fp32:
+ * w[0..5]  conv weights [Cout,Cin,1,8], b[0..5] conv biases,
+ * w[6] Linear(67840,2003).weight [2003,67840] (flatten index c*106+l), b[6] its bias,
+ * w[7] Linear(2003,2002).weight [2002,2003], b[7] its bias.
+ * Replaces model.load_state_dict(...) + .cuda(), chromatin.py:102-106. */
+int bx_ctx_load_weights(bx_ctx* ctx, const float* const w[8], const float* const b[8]);
+
+/* Packed genome resident in HBM: bases2 holds 16 bases per uint32 (2 bits each, code A=0 G=1 C=2 T=3,
+ * base i in bits 2*(i%16)); nmask holds 1 bit per base (1 = all-zero column: N, n, H, -), 32 per uint32.
+ * Replaces pyfasta.Fasta('./resources/hg19.fa'), chromatin.py:44. */
+int bx_ctx_set_genome(bx_ctx* ctx, const uint32_t* bases2_dev, const uint32_t* nmask_dev, int64_t n_bases);
+
+/* encodeSeqs (chromatin.py:138-172 / expecto_utils.py:5-39), materialised: out_dev is uint8 [n,4,2000],
+ * channel order A,G,C,T.  alleles_dev: codes 0..3 = A,G,C,T, 4 = zero column. */
+int bx_encode_windows(bx_ctx* ctx, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n,
+                      uint8_t* out_dev, void* stream);
+
+/* Beluga.forward (Beluga.py:50-51) over n windows, encode fused in front: probs_dev is fp32 [n,2002]. */
+int bx_forward_windows(bx_ctx* ctx, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n,
+                       float* probs_dev, void* stream);
+/* Same, from an explicit one-hot uint8 [n,4,2000] (the tensor chromatin.py:267 feeds the model). */
+int bx_forward_onehot(bx_ctx* ctx, const uint8_t* onehot_dev, int n, float* probs_dev, void* stream);
+
+/* Copy an internal activation (test hook): layer 0 = im2col one-hot, 1..6 = conv outputs, 7 = fc1 hidden.
+ * Writes rows*cols 16-bit elements for n windows to dst_dev; returns the element count through *count. */
+int bx_debug_activation(bx_ctx* ctx, int layer, int n, void* dst_dev, int64_t* count, void* stream);
+
+/* chromatin.py:281-286 layout: probs_dev is fp32 [4*n_var,2002] in window order
+ * (variant, {ref fwd, ref rc, alt fwd, alt rc}); writes ref/alt/diff fp32 [2*n_var,2002]
+ * (rows 0..n_var-1 forward, n_var..2n_var-1 reverse complement), diff = alt - ref. */
+int bx_chromatin_outputs(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,
+                         void* stream);
+/* predict.py:186-190 fused on device: strand-averaged diff/ref/alt fp32 [n_var,2002] from the same probs. */
+int bx_chromatin_outputs_avg(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,
+                             void* stream);
+
+/* compute_expecto_features.py:123-124: probs_dev fp32 [n_genes, S, 2, 2002] (shift-major, fwd then rc),
+ * weights_dev fp32 [10,S]; out_dev fp32 [n_genes, 10*2002] = sum_s w[k,s] * 0.5*(fwd+rc)[s,f]. */
+int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, int n_genes, int n_shifts,
+                             float* out_dev, void* stream);
+/* predict.py:87-136 (compute_effects): x_dev fp32 [S, n, 2002]; dist_dev fp64 [n] (variant - TSS);
+ * strand_dev int8 [n] (+1/-1); shifts_dev int32 [S]; out_dev fp32 [n, 10*2002]. */
+int bx_decay_transform_variant(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+                               const int32_t* shifts_dev, int n, int n_shifts, float* out_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
