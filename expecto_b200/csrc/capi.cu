@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <atomic>
 #include <algorithm>
 #include <vector>
@@ -118,6 +119,10 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
+  {
+    const char* e = getenv("BX_TAP_BO");
+    p.tap_bo_mode = e ? atoi(e) : 0;
+  }
   p.m_tiles = (p.m_rows + 128 * CG - 1) / (128 * CG);
   p.n_chunks = p.n_total / BN;
   const int units = p.m_tiles * p.n_chunks * p.k_splits;
@@ -196,49 +201,51 @@ static int run_fc1_finalize(bx_ctx* c, int n, cudaStream_t st) {
   return 0;
 }
 
+static int run_fc1(bx_ctx* c, int n, cudaStream_t st) {
+  // fc1: [n, 67840] x [2048, 67840]^T, split-K partial sums reduced with fp32 atomics
+  CK(cudaMemsetAsync(c->acc1, 0, (size_t)n * 2048 * sizeof(float), st));
+  GemmParams p = {};
+  p.m_rows = n;
+  p.k_valid = 67840;
+  p.n_total = 2048;
+  p.k_blocks = 67840 / 64;
+  const int m_tiles = (n + 128 * c->cg - 1) / (128 * c->cg);
+  const int clusters = c->num_sms / c->cg;
+  int ks = (3 * clusters + m_tiles * 8 - 1) / (m_tiles * 8);
+  ks = std::max(1, std::min(ks, 20));
+  p.kb_per_split = (p.k_blocks + ks - 1) / ks;
+  p.k_splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+  p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
+  p.ld_out = 2048;
+  p.n_store = 2048;
+  p.bias = nullptr;
+  p.out = c->acc1;
+  if (int r = launch_gemm(c, 1, 256, EPI_ATOMIC_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st)) return r;
+  return (c->dtype == BX_DTYPE_F16) ? run_fc1_finalize<__half>(c, n, st) : run_fc1_finalize<__nv_bfloat16>(c, n, st);
+}
+
+static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
+  GemmParams p = {};
+  p.m_rows = n;
+  p.k_valid = 2048;
+  p.n_total = 2048;
+  p.k_blocks = 32;
+  p.kb_per_split = 32;
+  p.k_splits = 1;
+  p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
+  p.ld_out = BX_FEATURES;
+  p.n_store = BX_FEATURES;
+  p.bias = c->bfc2;
+  p.out = probs;
+  return launch_gemm(c, 1, 256, EPI_BIAS_SIGMOID, c->hid, n, 2048, c->wfc2, 2048, p, st);
+}
+
 // conv1..conv6, fc1, fc2 over n windows whose conv1 operand is already in act[0].
 static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st) {
   for (int i = 0; i < 6; ++i)
     if (int r = run_conv(c, i, n, st)) return r;
-  // fc1: [n, 67840] x [2048, 67840]^T, split-K partial sums reduced with fp32 atomics
-  CK(cudaMemsetAsync(c->acc1, 0, (size_t)n * 2048 * sizeof(float), st));
-  {
-    GemmParams p = {};
-    p.m_rows = n;
-    p.k_valid = 67840;
-    p.n_total = 2048;
-    p.k_blocks = 67840 / 64;
-    const int m_tiles = (n + 128 * c->cg - 1) / (128 * c->cg);
-    const int clusters = c->num_sms / c->cg;
-    int ks = (3 * clusters + m_tiles * 8 - 1) / (m_tiles * 8);
-    ks = std::max(1, std::min(ks, 20));
-    p.kb_per_split = (p.k_blocks + ks - 1) / ks;
-    p.k_splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
-    p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
-    p.ld_out = 2048;
-    p.n_store = 2048;
-    p.bias = nullptr;
-    p.out = c->acc1;
-    if (int r = launch_gemm(c, 1, 256, EPI_ATOMIC_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st)) return r;
-  }
-  if (int r = (c->dtype == BX_DTYPE_F16) ? run_fc1_finalize<__half>(c, n, st) : run_fc1_finalize<__nv_bfloat16>(c, n, st))
-    return r;
-  {
-    GemmParams p = {};
-    p.m_rows = n;
-    p.k_valid = 2048;
-    p.n_total = 2048;
-    p.k_blocks = 32;
-    p.kb_per_split = 32;
-    p.k_splits = 1;
-    p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
-    p.ld_out = BX_FEATURES;
-    p.n_store = BX_FEATURES;
-    p.bias = c->bfc2;
-    p.out = probs;
-    if (int r = launch_gemm(c, 1, 256, EPI_BIAS_SIGMOID, c->hid, n, 2048, c->wfc2, 2048, p, st)) return r;
-  }
-  return 0;
+  if (int r = run_fc1(c, n, st)) return r;
+  return run_fc2(c, n, probs, st);
 }
 
 // ------------------------------------------------------------------ C ABI
@@ -427,6 +434,17 @@ int bx_debug_activation(bx_ctx* c, int layer, int n, void* dst_dev, int64_t* cou
   CK(cudaMemcpyAsync(dst_dev, src, elems * 2, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   if (count) *count = (int64_t)elems;
   return 0;
+}
+
+int bx_debug_run_layer(bx_ctx* c, int layer, int n, float* probs_dev, void* stream) {
+  if (!c || layer < 0 || layer > 7 || n < 1 || n > c->cap) return fail(BX_E_ARG, "invalid arguments");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded");
+  CK(cudaSetDevice(c->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (layer < 6) return run_conv(c, layer, n, st);
+  if (layer == 6) return run_fc1(c, n, st);
+  if (!probs_dev) return fail(BX_E_ARG, "probs_dev is null");
+  return run_fc2(c, n, probs_dev, st);
 }
 
 int bx_chromatin_outputs(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,

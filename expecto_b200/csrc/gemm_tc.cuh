@@ -43,6 +43,7 @@ struct GemmParams {
   int n_store;       // columns >= n_store are not stored
   const float* bias; // [n_total] fp32 (unused for EPI_ATOMIC_F32)
   void* out;
+  int tap_bo_mode;   // experiment switch: descriptor base_offset for tap-shifted A views (0 = none)
 };
 
 template <int TAPS, int BLOCK_N, int CG>
@@ -202,8 +203,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tc_fence_after();
             const uint32_t b_base = sB + rb.idx * Cfg::B_BYTES;
             for (int k = 0; k < kcount; ++k) {
-              umma_f16<CG>(d, make_sw128_desc(a_base + t * 128 + k * 32), make_sw128_desc(b_base + k * 32), IDESC,
-                           accum);
+              uint64_t da = make_sw128_desc(a_base + t * 128 + k * 32);
+              if (TAPS > 1 && p.tap_bo_mode == 1) da |= (uint64_t)(t & 7) << 49;
+              if (TAPS > 1 && p.tap_bo_mode == 2) da |= (uint64_t)((8 - t) & 7) << 49;
+              umma_f16<CG>(d, da, make_sw128_desc(b_base + k * 32), IDESC, accum);
               accum = 1;
             }
             umma_commit<CG>(emptyB(rb.idx));
@@ -331,6 +334,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   // ------------------------------------------------------------------ teardown
+  __syncwarp();
   tc_fence_before();
   if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
   if (warp == 1) {

@@ -1,0 +1,159 @@
+"""Host-side handle on the CUDA Beluga engine (one per GPU).
+
+Mirrors what the reference scripts do with ``model = Beluga(); model.load_state_dict(...); model.cuda()``
+(chromatin.py:102-106) and ``model.forward(input)`` (chromatin.py:270), but every FLOP runs in the
+hand-written sm_100a kernels behind the C ABI.  PyTorch is used only for device buffers and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check, lib
+
+N_FEATURES = 2002
+WINDOW = 2000
+_ACT_SHAPES = {0: (1996, 64), 1: (1996, 320), 2: (496, 320), 3: (492, 480), 4: (120, 480), 5: (113, 640),
+               6: (106, 640), 7: (1, 2048)}
+# rows of each activation that hold valid reference values (the rest of the pitch is junk by design)
+_ACT_VALID = {0: 1993, 1: 1993, 2: 496, 3: 489, 4: 120, 5: 113, 6: 106, 7: 1}
+
+
+def _stream_ptr(device: torch.device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+class BelugaEngine:
+    """Beluga forward on one B200.  ``dtype`` is the tensor-core operand type ("f16" or "bf16");
+    accumulation, bias, ReLU/MaxPool inputs, sigmoid and all outputs are fp32."""
+
+    def __init__(self, device: int | str | torch.device = 0, dtype: str = "f16", cta_group: int = 2,
+                 capacity: int = 1024):
+        if not torch.cuda.is_available():
+            raise RuntimeError("BelugaEngine needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self.dtype = dtype
+        self.capacity = int(capacity)
+        self._ctx = C.c_void_p()
+        code = {"f16": _lib.DTYPE_F16, "bf16": _lib.DTYPE_BF16}[dtype]
+        check(lib().bx_ctx_create(self.device.index or 0, code, cta_group, self.capacity, C.byref(self._ctx)))
+        self._genome = None
+        self._keep = []
+
+    def close(self) -> None:
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            lib().bx_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ weights
+    def load_state_dict(self, sd) -> None:
+        """``sd``: mapping with the reference's keys (``model.0.0.weight`` ...), torch tensors or numpy."""
+        from .synth import STATE_KEYS
+
+        ws, bs = [], []
+        for key, shape in STATE_KEYS:
+            w = sd[key + ".weight"]
+            b = sd[key + ".bias"]
+            w = w.detach().cpu().numpy() if isinstance(w, torch.Tensor) else np.asarray(w)
+            b = b.detach().cpu().numpy() if isinstance(b, torch.Tensor) else np.asarray(b)
+            w = np.ascontiguousarray(w, dtype=np.float32)
+            b = np.ascontiguousarray(b, dtype=np.float32)
+            if tuple(w.shape) != tuple(shape) or b.shape != (shape[0],):
+                raise ValueError(f"{key}: expected weight {shape}, got {w.shape} / bias {b.shape}")
+            ws.append(w)
+            bs.append(b)
+        wp = (C.c_void_p * 8)(*[w.ctypes.data for w in ws])
+        bp = (C.c_void_p * 8)(*[b.ctypes.data for b in bs])
+        with torch.cuda.device(self.device):
+            check(lib().bx_ctx_load_weights(self._ctx, wp, bp))
+
+    def load_weights_file(self, path: str) -> None:
+        """``torch.load(path)`` of a Beluga state_dict (chromatin.py:103)."""
+        self.load_state_dict(torch.load(path, map_location="cpu"))
+
+    # ------------------------------------------------------------------ genome
+    def set_genome(self, packed) -> None:
+        """``packed``: expecto_b200.genome.PackedGenome; uploads the 2-bit planes once."""
+        self._genome = packed
+        self._bases2 = torch.from_numpy(packed.bases2.view(np.int32)).to(self.device)
+        self._nmask = torch.from_numpy(packed.nmask.view(np.int32)).to(self.device)
+        check(lib().bx_ctx_set_genome(self._ctx, self._bases2.data_ptr(), self._nmask.data_ptr(), packed.n_bases))
+
+    # ------------------------------------------------------------------ compute
+    def _upload_descs(self, descs: np.ndarray, alleles: np.ndarray):
+        d = torch.from_numpy(np.ascontiguousarray(descs).view(np.uint8)).to(self.device, non_blocking=True)
+        if alleles.size == 0:
+            alleles = np.zeros(1, dtype=np.uint8)
+        a = torch.from_numpy(np.ascontiguousarray(alleles, dtype=np.uint8)).to(self.device, non_blocking=True)
+        return d, a
+
+    def encode_windows(self, descs: np.ndarray, alleles: np.ndarray) -> torch.Tensor:
+        """encodeSeqs materialised on the GPU: uint8 [n,4,2000] (bit-exact test hook)."""
+        n = len(descs)
+        d, a = self._upload_descs(descs, alleles)
+        out = torch.empty((n, 4, WINDOW), dtype=torch.uint8, device=self.device)
+        check(lib().bx_encode_windows(self._ctx, d.data_ptr(), a.data_ptr(), n, out.data_ptr(),
+                                      _stream_ptr(self.device)))
+        return out
+
+    def forward_windows(self, descs, alleles, out: torch.Tensor | None = None) -> torch.Tensor:
+        """Beluga probabilities fp32 [n,2002] for windows described against the packed genome.
+        ``descs``/``alleles`` may be numpy (uploaded here) or device tensors already resident in HBM."""
+        if isinstance(descs, np.ndarray):
+            n = len(descs)
+            d, a = self._upload_descs(descs, alleles)
+        else:
+            d, a = descs, alleles
+            n = d.numel() // 40
+        if out is None:
+            out = torch.empty((n, N_FEATURES), dtype=torch.float32, device=self.device)
+        check(lib().bx_forward_windows(self._ctx, d.data_ptr(), a.data_ptr(), n, out.data_ptr(),
+                                       _stream_ptr(self.device)))
+        return out
+
+    def forward_onehot(self, onehot: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        """``onehot``: uint8/bool [n,4,2000] (or [n,4,1,2000]) on this device -> fp32 [n,2002]."""
+        x = onehot.reshape(-1, 4, WINDOW)
+        if x.dtype == torch.bool:
+            x = x.view(torch.uint8)
+        if x.dtype != torch.uint8 or x.device != self.device:
+            raise ValueError("onehot must be a uint8/bool tensor on the engine's device")
+        x = x.contiguous()
+        n = x.shape[0]
+        if out is None:
+            out = torch.empty((n, N_FEATURES), dtype=torch.float32, device=self.device)
+        check(lib().bx_forward_onehot(self._ctx, x.data_ptr(), n, out.data_ptr(), _stream_ptr(self.device)))
+        return out
+
+    __call__ = forward_onehot
+
+    def debug_activation(self, layer: int, n: int) -> torch.Tensor:
+        """Internal activation after the last forward: [n, pitch, C] in the operand dtype (test hook)."""
+        rows, cols = _ACT_SHAPES[layer]
+        tdt = torch.float16 if self.dtype == "f16" else torch.bfloat16
+        dst = torch.empty((n, rows, cols), dtype=tdt, device=self.device)
+        cnt = C.c_int64()
+        check(lib().bx_debug_activation(self._ctx, layer, n, dst.data_ptr(), C.byref(cnt), _stream_ptr(self.device)))
+        assert cnt.value == dst.numel()
+        return dst
+
+
+def chromatin_outputs(probs: torch.Tensor, n_var: int, average: bool = False):
+    """ref/alt/diff in chromatin.py:281-286 layout (or strand-averaged as predict.py:186-190 reads them)
+    from probabilities ordered (variant, {ref fwd, ref rc, alt fwd, alt rc})."""
+    rows = n_var if average else 2 * n_var
+    ref = torch.empty((rows, N_FEATURES), dtype=torch.float32, device=probs.device)
+    alt = torch.empty_like(ref)
+    diff = torch.empty_like(ref)
+    fn = lib().bx_chromatin_outputs_avg if average else lib().bx_chromatin_outputs
+    check(fn(probs.data_ptr(), n_var, ref.data_ptr(), alt.data_ptr(), diff.data_ptr(), _stream_ptr(probs.device)))
+    return ref, alt, diff

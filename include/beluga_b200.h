@@ -84,6 +84,10 @@ int bx_forward_onehot(bx_ctx* ctx, const uint8_t* onehot_dev, int n, float* prob
  * Writes rows*cols 16-bit elements for n windows to dst_dev; returns the element count through *count. */
 int bx_debug_activation(bx_ctx* ctx, int layer, int n, void* dst_dev, int64_t* count, void* stream);
 
+/* Re-run one stage on the scratch left by the last forward (profiling hook): 0..5 = conv1..conv6,
+ * 6 = fc1 (+ReLU), 7 = fc2 (+sigmoid, writes probs_dev fp32 [n,2002]). */
+int bx_debug_run_layer(bx_ctx* ctx, int layer, int n, float* probs_dev, void* stream);
+
 /* chromatin.py:281-286 layout: probs_dev is fp32 [4*n_var,2002] in window order
  * (variant, {ref fwd, ref rc, alt fwd, alt rc}); writes ref/alt/diff fp32 [2*n_var,2002]
  * (rows 0..n_var-1 forward, n_var..2n_var-1 reverse complement), diff = alt - ref. */
