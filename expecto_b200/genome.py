@@ -1,0 +1,165 @@
+"""2-bit packed genome (replaces ``pyfasta.Fasta('./resources/hg19.fa')``, chromatin.py:44).
+
+Layout handed to the kernels (include/beluga_b200.h, bx_ctx_set_genome):
+
+* ``bases2``  uint32, 16 bases per word, 2 bits each, code A=0 G=1 C=2 T=3 — the channel order of
+  ``encodeSeqs``' ``mydict`` (chromatin.py:155-160), so reverse complement is ``3 - code``;
+* ``nmask``   uint32, 1 bit per base; 1 = all-zero column (``N n H -`` in ``mydict``).
+
+Contigs are concatenated in file order, each starting on a 32-base boundary after ``PAD`` bases of
+N, so a window that runs off a contig reads zero columns.  (The reference's behaviour there is
+accidental — negative Python slice indices / short strings from pyfasta — and is not reproduced;
+SURVEY §7 hard part 2.)  Characters outside ``mydict`` make the reference raise ``KeyError`` when a
+window touches them; they are recorded in ``invalid`` and checked on the host before any launch.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+PAD = 4096
+_CODE = np.full(256, 255, dtype=np.uint8)
+for _i, _c in enumerate("AGCT"):
+    _CODE[ord(_c)] = _i
+    _CODE[ord(_c.lower())] = _i
+for _c in "NnH-":
+    _CODE[ord(_c)] = 4
+_DECODE = np.frombuffer(b"AGCTN", dtype=np.uint8)
+
+
+def encode_bases(seq: str | bytes) -> np.ndarray:
+    """Allele / sequence string -> codes 0..3 (A,G,C,T), 4 (zero column); KeyError like ``mydict[c]``."""
+    b = seq.encode("ascii", "replace") if isinstance(seq, str) else seq
+    codes = _CODE[np.frombuffer(b, dtype=np.uint8)]
+    bad = np.flatnonzero(codes == 255)
+    if bad.size:
+        raise KeyError(chr(b[int(bad[0])]))
+    return codes
+
+
+class PackedGenome:
+    def __init__(self):
+        self.names: list[str] = []
+        self.offsets: dict[str, int] = {}   # global index of base 0 of each contig
+        self.lengths: dict[str, int] = {}
+        self.bases2 = np.zeros(0, dtype=np.uint32)
+        self.nmask = np.zeros(0, dtype=np.uint32)
+        self.n_bases = 0
+        self.invalid = np.zeros(0, dtype=np.int64)  # sorted global indices of characters outside mydict
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def from_sequences(cls, seqs: dict[str, str | bytes]) -> "PackedGenome":
+        g = cls()
+        total = PAD
+        for name, s in seqs.items():
+            total = (total + 31) // 32 * 32
+            g.names.append(name)
+            g.offsets[name] = total
+            g.lengths[name] = len(s)
+            total += len(s) + PAD
+        total = (total + 31) // 32 * 32
+        g.n_bases = total
+        g.bases2 = np.zeros(total // 16, dtype=np.uint32)
+        g.nmask = np.full(total // 32, 0xFFFFFFFF, dtype=np.uint32)  # padding is N
+        invalid = []
+        for name, s in seqs.items():
+            raw = np.frombuffer(s.encode("ascii", "replace") if isinstance(s, str) else s, dtype=np.uint8)
+            g._pack_contig(g.offsets[name], raw, invalid)
+        g.invalid = np.sort(np.concatenate(invalid)) if invalid else np.zeros(0, dtype=np.int64)
+        return g
+
+    def _pack_contig(self, off: int, raw: np.ndarray, invalid: list) -> None:
+        n = raw.size
+        if n == 0:
+            return
+        codes = _CODE[raw]
+        bad = np.flatnonzero(codes == 255)
+        if bad.size:
+            invalid.append(bad.astype(np.int64) + off)
+            codes = codes.copy()
+            codes[bad] = 4
+        # off is a multiple of 32: pack whole words, tail padded with N
+        n32 = (n + 31) // 32 * 32
+        full = np.full(n32, 4, dtype=np.uint8)
+        full[:n] = codes
+        two = (full & 3).astype(np.uint32).reshape(-1, 16)
+        two[full.reshape(-1, 16) == 4] = 0
+        sh = (np.arange(16, dtype=np.uint32) * 2)[None, :]
+        self.bases2[off // 16: off // 16 + n32 // 16] = np.bitwise_or.reduce(two << sh, axis=1)
+        m = (full == 4).astype(np.uint32).reshape(-1, 32)
+        sh1 = np.arange(32, dtype=np.uint32)[None, :]
+        self.nmask[off // 32: off // 32 + n32 // 32] = np.bitwise_or.reduce(m << sh1, axis=1)
+
+    @classmethod
+    def from_fasta(cls, path: str, cache: bool = True) -> "PackedGenome":
+        """Parse a (multi-)FASTA; a ``<path>.bx2.npz`` cache is written next to it when possible."""
+        cpath = path + ".bx2.npz"
+        if cache and os.path.exists(cpath) and os.path.getmtime(cpath) >= os.path.getmtime(path):
+            return cls.load(cpath)
+        buf = np.fromfile(path, dtype=np.uint8)
+        starts = np.flatnonzero(buf == ord(">"))
+        # keep only '>' at line starts
+        starts = starts[(starts == 0) | (buf[np.maximum(starts - 1, 0)] == 10)]
+        seqs: dict[str, bytes] = {}
+        for i, s in enumerate(starts):
+            e = int(starts[i + 1]) if i + 1 < len(starts) else buf.size
+            nl = int(s) + int(np.argmax(buf[s:e] == 10)) if np.any(buf[s:min(e, s + 4096)] == 10) else e
+            header = buf[s + 1:nl].tobytes().decode("ascii", "replace").strip()
+            name = header.split()[0] if header else f"contig{i}"
+            body = buf[nl + 1:e]
+            body = body[(body != 10) & (body != 13)]
+            seqs[name] = body.tobytes()
+        g = cls.from_sequences(seqs)
+        if cache:
+            try:
+                g.save(cpath)
+            except OSError:
+                pass
+        return g
+
+    def save(self, path: str) -> None:
+        np.savez(path, bases2=self.bases2, nmask=self.nmask, invalid=self.invalid,
+                 names=np.array(self.names), offsets=np.array([self.offsets[n] for n in self.names], dtype=np.int64),
+                 lengths=np.array([self.lengths[n] for n in self.names], dtype=np.int64))
+
+    @classmethod
+    def load(cls, path: str) -> "PackedGenome":
+        z = np.load(path, allow_pickle=False)
+        g = cls()
+        g.names = [str(x) for x in z["names"]]
+        g.offsets = {n: int(o) for n, o in zip(g.names, z["offsets"])}
+        g.lengths = {n: int(o) for n, o in zip(g.names, z["lengths"])}
+        g.bases2, g.nmask, g.invalid = z["bases2"], z["nmask"], z["invalid"]
+        g.n_bases = int(g.nmask.size) * 32
+        return g
+
+    # ------------------------------------------------------------------ host-side reads (diagnostics, tests)
+    def codes(self, gstart: int, n: int) -> np.ndarray:
+        """Codes 0..4 of global positions [gstart, gstart+n); outside the array -> 4."""
+        idx = np.arange(gstart, gstart + n, dtype=np.int64)
+        ok = (idx >= 0) & (idx < self.n_bases)
+        j = np.where(ok, idx, 0)
+        two = (self.bases2[j >> 4] >> ((j & 15) * 2).astype(np.uint32)) & 3
+        msk = (self.nmask[j >> 5] >> (j & 31).astype(np.uint32)) & 1
+        out = np.where((msk == 1) | ~ok, 4, two).astype(np.uint8)
+        return out
+
+    def upper_string(self, gstart: int, n: int) -> str:
+        """Upper-case bases (N for any zero column) — what ``seq[...].upper()`` compares against
+        (chromatin.py:207-208) for genomes made of ACGTN."""
+        return _DECODE[self.codes(gstart, n)].tobytes().decode("ascii")
+
+    def global_index(self, chrom: str, pos0: np.ndarray | int):
+        """0-based contig coordinate -> global index (may fall in the N padding)."""
+        return self.offsets[chrom] + pos0
+
+    def any_invalid(self, gstart: np.ndarray, length: np.ndarray) -> int:
+        """Index of the first window [gstart, gstart+length) touching an invalid base, or -1."""
+        if self.invalid.size == 0:
+            return -1
+        lo = np.searchsorted(self.invalid, gstart, side="left")
+        hi = np.searchsorted(self.invalid, gstart + length, side="left")
+        hit = np.flatnonzero(hi > lo)
+        return int(hit[0]) if hit.size else -1
