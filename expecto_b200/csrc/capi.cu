@@ -119,10 +119,6 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
-  {
-    const char* e = getenv("BX_TAP_BO");
-    p.tap_bo_mode = e ? atoi(e) : 0;
-  }
   p.m_tiles = (p.m_rows + 128 * CG - 1) / (128 * CG);
   p.n_chunks = p.n_total / BN;
   const int units = p.m_tiles * p.n_chunks * p.k_splits;

@@ -43,7 +43,6 @@ struct GemmParams {
   int n_store;       // columns >= n_store are not stored
   const float* bias; // [n_total] fp32 (unused for EPI_ATOMIC_F32)
   void* out;
-  int tap_bo_mode;   // experiment switch: descriptor base_offset for tap-shifted A views (0 = none)
 };
 
 template <int TAPS, int BLOCK_N, int CG>
@@ -143,19 +142,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int tiles_mn = p.m_tiles * p.n_chunks;
   const int total_units = tiles_mn * p.k_splits;
 
+  // Producer and MMA warps run their loops warp-uniformly (all 32 lanes wait on the barriers) and only
+  // the elected lane issues the async instruction: descriptors, coordinates and barrier addresses then
+  // live in uniform registers and one tcgen05.mma costs a handful of issue slots.  (A first version
+  // ran these loops under `if (lane == 0)`; ncu showed ~40 SASS instructions per MMA from the
+  // divergent-code UR waterfall and the single thread became the bottleneck at ~195 cycles/MMA.)
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      RingState ra, rb;
-      for (int u = cluster_id; u < total_units; u += num_clusters) {
-        const int ks = u / tiles_mn, rem = u - ks * tiles_mn;
-        const int mt = rem / p.n_chunks, nc = rem - mt * p.n_chunks;
-        const int kb0 = ks * p.kb_per_split;
-        const int kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
-        const int row0 = mt * 128 * CG + (int)rank * 128;
-        const int ncol0 = nc * BLOCK_N + (int)rank * Cfg::B_ROWS;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
+    RingState ra, rb;
+    for (int u = cluster_id; u < total_units; u += num_clusters) {
+      const int ks = u / tiles_mn, rem = u - ks * tiles_mn;
+      const int mt = rem / p.n_chunks, nc = rem - mt * p.n_chunks;
+      const int kb0 = ks * p.kb_per_split;
+      const int kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
+      const int row0 = mt * 128 * CG + (int)rank * 128;
+      const int ncol0 = nc * BLOCK_N + (int)rank * Cfg::B_ROWS;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
+        if (elect_one()) {
           if constexpr (CG == 1) {
             mbar_arrive_expect_tx(fullA(ra.idx), Cfg::A_BYTES);
             tma_load_2d(sA + ra.idx * Cfg::A_BYTES, &tmA, fullA(ra.idx), kb * 64, row0);
@@ -163,10 +167,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (rank == 0) mbar_arrive_expect_tx(fullA(ra.idx), 2 * Cfg::A_BYTES);
             tma_load_2d_pair(sA + ra.idx * Cfg::A_BYTES, &tmA, mapa(fullA(ra.idx), 0), kb * 64, row0);
           }
-          ra.advance<SA>();
+        }
+        __syncwarp();
+        ra.advance<SA>();
 #pragma unroll 1
-          for (int t = 0; t < TAPS; ++t) {
-            mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
+        for (int t = 0; t < TAPS; ++t) {
+          mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
+          if (elect_one()) {
             if constexpr (CG == 1) {
               mbar_arrive_expect_tx(fullB(rb.idx), Cfg::B_BYTES);
               tma_load_2d(sB + rb.idx * Cfg::B_BYTES, &tmB, fullB(rb.idx), kb * 64, t * p.n_total + ncol0);
@@ -175,14 +182,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               tma_load_2d_pair(sB + rb.idx * Cfg::B_BYTES, &tmB, mapa(fullB(rb.idx), 0), kb * 64,
                                t * p.n_total + ncol0);
             }
-            rb.advance<SB>();
           }
+          __syncwarp();
+          rb.advance<SB>();
         }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (leader CTA, one thread)
-    if (rank == 0 && lane == 0) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA, elected lane)
+    if (rank == 0) {
       RingState ra, rb, rt;
       for (int u = cluster_id; u < total_units; u += num_clusters) {
         const int ks = u / tiles_mn;
@@ -195,27 +203,36 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = kb0; kb < kb1; ++kb) {
           const int kcount = min(4, (p.k_valid - kb * 64 + 15) >> 4);
           mbar_wait(fullA(ra.idx), ra.phase, 4);
-          tc_fence_after();
-          const uint32_t a_base = sA + ra.idx * Cfg::A_BYTES;
+          const uint32_t a_lo = sw128_desc_lo(sA + ra.idx * Cfg::A_BYTES);
 #pragma unroll 1
           for (int t = 0; t < TAPS; ++t) {
             mbar_wait(fullB(rb.idx), rb.phase, 5);
             tc_fence_after();
-            const uint32_t b_base = sB + rb.idx * Cfg::B_BYTES;
-            for (int k = 0; k < kcount; ++k) {
-              uint64_t da = make_sw128_desc(a_base + t * 128 + k * 32);
-              if (TAPS > 1 && p.tap_bo_mode == 1) da |= (uint64_t)(t & 7) << 49;
-              if (TAPS > 1 && p.tap_bo_mode == 2) da |= (uint64_t)((8 - t) & 7) << 49;
-              umma_f16<CG>(d, da, make_sw128_desc(b_base + k * 32), IDESC, accum);
-              accum = 1;
+            // tap t = the A slab viewed t rows (t*128 B) further down; K advances 32 B per UMMA_K=16
+            const uint32_t at_lo = a_lo + t * 8;
+            const uint32_t b_lo = sw128_desc_lo(sB + rb.idx * Cfg::B_BYTES);
+            if (elect_one()) {
+              if (kcount == 4) {
+                umma_f16<CG>(d, sw128_desc(at_lo), sw128_desc(b_lo), IDESC, accum);
+                umma_f16<CG>(d, sw128_desc(at_lo + 2), sw128_desc(b_lo + 2), IDESC, 1u);
+                umma_f16<CG>(d, sw128_desc(at_lo + 4), sw128_desc(b_lo + 4), IDESC, 1u);
+                umma_f16<CG>(d, sw128_desc(at_lo + 6), sw128_desc(b_lo + 6), IDESC, 1u);
+              } else {
+                for (int k = 0; k < kcount; ++k)
+                  umma_f16<CG>(d, sw128_desc(at_lo + 2 * k), sw128_desc(b_lo + 2 * k), IDESC, k ? 1u : accum);
+              }
+              umma_commit<CG>(emptyB(rb.idx));
             }
-            umma_commit<CG>(emptyB(rb.idx));
+            __syncwarp();
+            accum = 1;
             rb.advance<SB>();
           }
-          umma_commit<CG>(emptyA(ra.idx));
+          if (elect_one()) umma_commit<CG>(emptyA(ra.idx));
+          __syncwarp();
           ra.advance<SA>();
         }
-        umma_commit<CG>(tfull(rt.idx));
+        if (elect_one()) umma_commit<CG>(tfull(rt.idx));
+        __syncwarp();
         rt.advance<NBUF>();
       }
     }

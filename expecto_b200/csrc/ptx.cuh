@@ -173,8 +173,20 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 // K-major operand tile in shared memory, 128-byte rows, SWIZZLE_128B (what TMA wrote):
 // rows are 128 B apart, 8-row groups 1024 B apart (SBO), descriptor version 1 (Blackwell).
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
-  return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+// The swizzle is a function of the absolute shared-memory address (verified on B200: a start address
+// offset by t*128 B inside a 1024-B-aligned slab addresses rows t.. correctly with base_offset = 0, and
+// any non-zero base_offset breaks it), which is what makes the tap-shifted A views of gemm_tc.cuh legal.
+__device__ __forceinline__ uint32_t sw128_desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3FFF) | (1u << 16); }
+__device__ __forceinline__ uint64_t sw128_desc(uint32_t lo) {
+  return ((uint64_t)(64u | (1u << 14) | (2u << 29)) << 32) | lo;
+}
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) { return sw128_desc(sw128_desc_lo(saddr)); }
+
+// Warp-uniform single-lane election (all 32 lanes must be converged).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 
 // Instruction descriptor, kind::f16: fp32 accumulate, A/B both K-major, same 16-bit format.

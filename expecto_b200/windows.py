@@ -1,0 +1,127 @@
+"""Window descriptors: the host half of kernel 1.
+
+``fetchSeqs`` (chromatin.py:175-209) fetches 2100 bp around ``pos+shift``, splices the VCF allele in at
+``mutpos = 1049 - shift`` and ``encodeSeqs`` (chromatin.py:164) centre-crops the result to 2000 bp.
+Both are pure index arithmetic, so each model input is described to the GPU as
+``genome[g1:g1+len1] + allele[aoff:aoff+alen] + genome[g2:g2+len2]`` (bx_window_desc) and the bases
+themselves never leave HBM.  Everything here is vectorised numpy over the variant axis.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from ._lib import DESC_DTYPE
+from .genome import PackedGenome, encode_bases
+
+INPUTSIZE = 2000
+WINDOWSIZE = INPUTSIZE + 100  # chromatin.py:117,202
+
+
+def crop_bounds(total: np.ndarray, inputsize: int = INPUTSIZE):
+    """``line[int(floor((len-inputsize)/2.0)) : int(floor(len-(len-inputsize)/2.0))]`` with Python slice
+    semantics (negative start counts from the end), chromatin.py:164."""
+    total = np.asarray(total, dtype=np.int64)
+    a = np.floor_divide(total - inputsize, 2)
+    b = np.floor_divide(total + inputsize, 2)  # floor(len - (len - inputsize)/2) == floor((len + inputsize)/2)
+    a = np.where(a < 0, np.maximum(a + total, 0), a)
+    a = np.minimum(a, total)
+    b = np.clip(b, 0, total)
+    b = np.maximum(b, a)
+    return a, b
+
+
+class AlleleTable:
+    """Concatenated allele codes (0..3 = A,G,C,T; 4 = zero column) with per-allele offsets."""
+
+    def __init__(self, alleles: list[str]):
+        lens = np.fromiter((len(a) for a in alleles), dtype=np.int64, count=len(alleles))
+        self.lengths = lens
+        self.offsets = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64) if len(alleles) else lens
+        joined = "".join(alleles)
+        self.codes = encode_bases(joined) if joined else np.zeros(0, dtype=np.uint8)  # KeyError on bad chars
+
+
+def variant_descs(genome: PackedGenome, chroms, pos, ref_len: np.ndarray, allele_len: np.ndarray,
+                  allele_off: np.ndarray, shift: int, rc: bool, inputsize: int = INPUTSIZE) -> np.ndarray:
+    """Descriptors of the windows fetchSeqs+encodeSeqs build for one allele (ref or alt) of each variant.
+
+    chroms: sequence of contig names (already normalised to ``chr*``); pos: 1-based positions;
+    ref_len: len(ref) per variant (the spliced-out span is always len(ref), chromatin.py:209);
+    allele_len/off: the allele that is spliced in (ref itself for the ref window)."""
+    n = len(pos)
+    windowsize = inputsize + 100
+    pos = np.asarray(pos, dtype=np.int64)
+    ref_len = np.asarray(ref_len, dtype=np.int64)
+    la = np.asarray(allele_len, dtype=np.int64)
+    coff = np.fromiter((genome.offsets[c] for c in chroms), dtype=np.int64, count=n)
+    half = int(windowsize / 2 - 1)                       # 1049
+    mutpos = int(windowsize / 2 - 1 - shift)             # chromatin.py:203
+    s0 = coff + pos + shift - half - 1                   # global index of seq[0] (1-based start -> 0-based)
+    len_p = np.full(n, mutpos, dtype=np.int64)           # seq[:mutpos]
+    len_s = np.maximum(0, windowsize - mutpos - ref_len)  # seq[mutpos+len(ref):]
+    total = len_p + la + len_s
+    a, b = crop_bounds(total, inputsize)
+    d = np.zeros(n, dtype=DESC_DTYPE)
+    p_lo, p_hi = np.minimum(a, len_p), np.minimum(b, len_p)
+    d["len1"] = np.maximum(0, p_hi - p_lo)
+    d["g1"] = s0 + p_lo
+    al_lo, al_hi = np.clip(a - len_p, 0, la), np.clip(b - len_p, 0, la)
+    d["alen"] = np.maximum(0, al_hi - al_lo)
+    d["aoff"] = np.asarray(allele_off, dtype=np.int64) + al_lo
+    s_lo, s_hi = np.clip(a - len_p - la, 0, len_s), np.clip(b - len_p - la, 0, len_s)
+    d["len2"] = np.maximum(0, s_hi - s_lo)
+    d["g2"] = s0 + mutpos + ref_len + s_lo
+    d["flags"] = 1 if rc else 0
+    return d
+
+
+def tss_descs(genome: PackedGenome, chroms, tss, strand, shifts, windowsize: int = INPUTSIZE) -> np.ndarray:
+    """compute_expecto_features.py:105-111: for gene g and shift s the window is
+    ``start = tss + s*strand - 999 .. stop = tss + s*strand + 1000`` (1-based inclusive), NOT reverse
+    complemented for '-' genes.  Returns descriptors ordered (gene, shift, {fwd, rc})."""
+    n = len(tss)
+    tss = np.asarray(tss, dtype=np.int64)
+    strand = np.asarray(strand, dtype=np.int64)
+    shifts = np.asarray(shifts, dtype=np.int64)
+    coff = np.fromiter((genome.offsets[c] for c in chroms), dtype=np.int64, count=n)
+    start0 = (coff + tss)[:, None] + shifts[None, :] * strand[:, None] - int(windowsize / 2 - 1) - 1
+    d = np.zeros((n, len(shifts), 2), dtype=DESC_DTYPE)
+    d["g1"] = start0[:, :, None]
+    d["len1"] = windowsize
+    d["flags"][:, :, 1] = 1
+    return d.reshape(-1)
+
+
+def chromatin_window_descs(genome: PackedGenome, chroms, pos, refs: list[str], alts: list[str], shift: int):
+    """All four windows per variant in the order the fused output kernels expect:
+    (variant, {ref fwd, ref rc, alt fwd, alt rc}).  Returns (descs [4N], allele codes)."""
+    n = len(pos)
+    tab = AlleleTable(list(refs) + list(alts))
+    rl, al = tab.lengths[:n], tab.lengths[n:]
+    ro, ao = tab.offsets[:n], tab.offsets[n:]
+    out = np.zeros((n, 4), dtype=DESC_DTYPE)
+    out[:, 0] = variant_descs(genome, chroms, pos, rl, rl, ro, shift, rc=False)
+    out[:, 1] = variant_descs(genome, chroms, pos, rl, rl, ro, shift, rc=True)
+    out[:, 2] = variant_descs(genome, chroms, pos, rl, al, ao, shift, rc=False)
+    out[:, 3] = variant_descs(genome, chroms, pos, rl, al, ao, shift, rc=True)
+    return out.reshape(-1), tab.codes
+
+
+def check_valid_bases(genome: PackedGenome, descs: np.ndarray) -> None:
+    """Raise KeyError, as ``mydict[c]`` would (chromatin.py:166), if any window touches a genome
+    character outside encodeSeqs' dictionary."""
+    for gs, ln in ((descs["g1"], descs["len1"]), (descs["g2"], descs["len2"])):
+        i = genome.any_invalid(gs.astype(np.int64), ln.astype(np.int64))
+        if i >= 0:
+            raise KeyError(f"window {i} covers a base that encodeSeqs cannot encode")
+
+
+def allele_match_counts(genome: PackedGenome, chroms, pos, refs: list[str], alts: list[str]):
+    """The three diagnostics chromatin.py:256-260 prints at shift 0: how many variants have
+    ``seq[mutpos:mutpos+len(ref)].upper() == ref.upper()`` / ``== alt.upper()``, and the count."""
+    ref_ok = alt_ok = 0
+    for c, p, r, a in zip(chroms, pos, refs, alts):
+        g = genome.upper_string(genome.offsets[c] + int(p) - 1, len(r))
+        ref_ok += g == r.upper()
+        alt_ok += g == a.upper()
+    return ref_ok, alt_ok, len(refs)

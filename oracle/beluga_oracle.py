@@ -1,0 +1,173 @@
+"""CPU restatement of the reference's algorithm for the Beluga chromatin-effect hot path.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``expecto_b200/`` imports this module; it is used by
+``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs
+as the checker and the timed CPU baseline, never as the product path.
+
+Pinned against the reference itself: ``oracle/make_golden.py`` runs the UNMODIFIED reference code
+(``/root/reference/expecto_utils.py``, ``Beluga.py``, and ``chromatin.py`` /
+``compute_expecto_features.py`` as subprocesses behind import shims) on seeded synthetic inputs,
+asserts these restatements agree, and commits the outputs under ``tests/golden/``.  The reference has
+no tests and its own example fixtures need hg19 + trained weights that are not in the repository
+(SURVEY §4), so parity with the *trained* model is unpinned; parity with the reference *code* is pinned.
+
+Each function cites the reference lines it follows.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+
+INPUTSIZE = 2000
+SHIFTS_CHROMATIN = lambda maxshift=800: [0] + list(range(-200, -maxshift - 1, -200)) + list(  # noqa: E731
+    range(200, maxshift + 1, 200))  # chromatin.py:243 / predict.py:173
+CHRS = ["chr%d" % i for i in range(1, 23)] + ["chrX", "chrY"]  # chromatin.py:108-110
+
+_ROW = {"A": 0, "G": 1, "C": 2, "T": 3, "a": 0, "g": 1, "c": 2, "t": 3}  # chromatin.py:155-160
+_ZERO = set("NHn-")
+
+
+def encode_seqs(seqs, inputsize=INPUTSIZE, concat_rc=True):
+    """encodeSeqs, chromatin.py:138-172 == expecto_utils.py:5-39 (``concat_rc=False`` is the variant at
+    compute_expecto_features.py:184-218).  bool [2n (or n), 4, inputsize], channel order A,G,C,T."""
+    out = np.zeros((len(seqs), 4, inputsize), np.bool_)
+    for n, line in enumerate(seqs):
+        lo = int(math.floor((len(line) - inputsize) / 2.0))
+        hi = int(math.floor(len(line) - (len(line) - inputsize) / 2.0))
+        cline = line[lo:hi]
+        for i, c in enumerate(cline):
+            if c in _ROW:
+                out[n, _ROW[c], i] = True
+            elif c not in _ZERO:
+                raise KeyError(c)  # mydict[c], chromatin.py:166
+    if concat_rc:
+        out = np.concatenate([out, out[:, ::-1, ::-1]], axis=0)  # chromatin.py:170-171
+    return out
+
+
+class DictGenome:
+    """pyfasta.Fasta stand-in over in-memory strings: ``sequence({'chr','start','stop'})`` is 1-based
+    inclusive and case preserving (pyfasta 0.5.2, call sites chromatin.py:205, compute_expecto_features.py:108)."""
+
+    def __init__(self, seqs):
+        self.seqs = seqs
+
+    def sequence(self, f):
+        return self.seqs[f["chr"]][f["start"] - 1:f["stop"]]
+
+
+def fetch_seqs(genome, chr, pos, ref, alt, shift=0, inputsize=INPUTSIZE):
+    """fetchSeqs, chromatin.py:175-209."""
+    windowsize = inputsize + 100
+    mutpos = int(windowsize / 2 - 1 - shift)
+    seq = genome.sequence({"chr": chr, "start": pos + shift - int(windowsize / 2 - 1),
+                           "stop": pos + shift + int(windowsize / 2)})
+    ref_matched = seq[mutpos:(mutpos + len(ref))].upper() == ref.upper()
+    alt_matched = seq[mutpos:(mutpos + len(ref))].upper() == alt.upper()
+    return (seq[:mutpos] + ref + seq[(mutpos + len(ref)):], seq[:mutpos] + alt + seq[(mutpos + len(ref)):],
+            ref_matched, alt_matched)
+
+
+def normalise_vcf_rows(rows):
+    """chromatin.py:240-241: chrom <- 'chr' + str(chrom).replace('chr',''), keep chr1-22,X,Y."""
+    out = []
+    for r in rows:
+        c = "chr" + str(r[0]).replace("chr", "")
+        if c in CHRS:
+            out.append([c] + list(r[1:]))
+    return out
+
+
+def beluga_forward(x, sd):
+    """Beluga.forward, Beluga.py:21-51, as fp32 torch functional ops on CPU.  ``x``: float32 [B,4,2000]
+    (the reference's [B,4,1,2000] without the dummy axis); ``sd``: state_dict-keyed numpy/torch arrays."""
+    import torch
+    import torch.nn.functional as F
+
+    t = lambda k: sd[k] if isinstance(sd[k], torch.Tensor) else torch.from_numpy(np.asarray(sd[k]))  # noqa: E731
+    y = torch.as_tensor(x, dtype=torch.float32)
+    convs = ["model.0.0", "model.0.2", "model.0.6", "model.0.8", "model.0.12", "model.0.14"]
+    pool_after = {1, 3}  # MaxPool2d((1,4),(1,4)) after conv2 and conv4, Beluga.py:28,34 (Dropout = identity in eval)
+    with torch.no_grad():
+        for i, k in enumerate(convs):
+            y = F.relu(F.conv1d(y, t(k + ".weight")[:, :, 0, :], t(k + ".bias")))
+            if i in pool_after:
+                y = F.max_pool1d(y, 4, 4)
+        y = y.reshape(y.shape[0], -1)  # x.view(x.size(0), -1): channel-major flatten, Beluga.py:42
+        y = F.relu(F.linear(y, t("model.1.2.1.weight"), t("model.1.2.1.bias")))
+        y = torch.sigmoid(F.linear(y, t("model.1.4.1.weight"), t("model.1.4.1.bias")))
+    return y.numpy()
+
+
+def chromatin_shift(genome, rows, sd, shift, inputsize=INPUTSIZE, batchsize=32):
+    """One iteration of the shift loop, chromatin.py:244-281: returns (diff, ref, alt, counters)."""
+    refseqs, altseqs, rm, am = [], [], [], []
+    for r in rows:
+        a, b, c, d = fetch_seqs(genome, r[0], int(r[1]), r[3], r[4], shift=shift, inputsize=inputsize)
+        refseqs.append(a), altseqs.append(b), rm.append(c), am.append(d)
+    ref_enc = encode_seqs(refseqs, inputsize).astype(np.float32)
+    alt_enc = encode_seqs(altseqs, inputsize).astype(np.float32)
+
+    def run(enc):
+        outs = [beluga_forward(enc[i:i + batchsize], sd) for i in range(0, enc.shape[0], batchsize)]
+        return np.vstack(outs)
+
+    ref_p, alt_p = run(ref_enc), run(alt_enc)
+    return alt_p - ref_p, ref_p, alt_p, (int(np.sum(rm)), int(np.sum(am)), len(rm))
+
+
+def fixed_pos_weights(shifts=None):
+    """compute_expecto_features.py:88-101: float64 [10, S]."""
+    s = np.array(list(range(-20000, 20000, 200))) if shifts is None else np.asarray(shifts)
+    rates = [0.01, 0.02, 0.05, 0.1, 0.2]
+    return np.vstack([np.exp(-k * np.abs(s) / 200) * (s <= 0) for k in rates] +
+                     [np.exp(-k * np.abs(s) / 200) * (s >= 0) for k in rates])
+
+
+def fixed_transform(pred_fwd, pred_rc, pos_weights):
+    """compute_expecto_features.py:123-124: float64 [10*2002] from fp32 [S,2002] forward / rc predictions."""
+    pred = 0.5 * (pred_fwd + pred_rc)
+    return np.sum(pos_weights[:, :, None] * pred[None, :, :], axis=1).flatten()
+
+
+def tss_windows(genome, chrom, tss, strand, shifts=None, windowsize=INPUTSIZE):
+    """compute_expecto_features.py:106-111."""
+    s = list(range(-20000, 20000, 200)) if shifts is None else shifts
+    return [genome.sequence({"chr": chrom, "start": tss + (sh * strand) - int(windowsize / 2 - 1),
+                             "stop": tss + (sh * strand) + int(windowsize / 2)}) for sh in s]
+
+
+def variant_weights(snpdists, snpstrands, maxshift=800):
+    """predict.py:87-109: list over shifts of float64 [n,10]."""
+    sgn = (np.asarray(snpstrands) == "+") * 2 - 1
+    d0 = np.asarray(snpdists) * sgn
+    rates = [0.01, 0.02, 0.05, 0.1, 0.2]
+    out = []
+    for dist in SHIFTS_CHROMATIN(maxshift):
+        p = d0 + dist * sgn
+        w = [np.exp(-k * np.floor(np.abs(p / 200.0))) * (p <= 0) for k in rates] + \
+            [np.exp(-k * np.floor(np.abs(p / 200.0))) * (p >= 0) for k in rates]
+        out.append(np.vstack(w).T)
+    return out
+
+
+def variant_transform(x_by_shift, weights, nfeatures=2002):
+    """predict.py:123-124: reduce(+, tile(X_j,10) * repeat(W_j, nfeatures)) -> float64 [n, 10*nfeatures]."""
+    acc = None
+    for xj, wj in zip(x_by_shift, weights):
+        term = np.tile(np.asarray(xj), 10) * np.repeat(wj, nfeatures, axis=1)
+        acc = term if acc is None else acc + term
+    return acc
+
+
+def strand_average(d):
+    """predict.py:183-190: (top half + bottom half) / 2.0."""
+    n = int(d.shape[0] / 2)
+    return (np.asarray(d[0:n, :]) + np.asarray(d[n:2 * n, :])) / 2.0
+
+
+def gblinear_predict(features, weights, bias, base_score=0.0):
+    """xgboost 0.7 gblinear Booster.predict (predict.py:150-160; dump layout predict_by_cluster.py:73-75):
+    base_score + bias + w . x  (xgboost==0.7.post4 is a pinned third-party dependency, requirements.txt:38)."""
+    return base_score + bias + np.asarray(features) @ np.asarray(weights)
