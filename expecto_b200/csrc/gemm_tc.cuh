@@ -51,12 +51,13 @@ struct GemmCfg {
   static constexpr int A_BYTES = A_ROWS * 128;
   static constexpr int B_ROWS = BLOCK_N / CG;
   static constexpr int B_BYTES = B_ROWS * 128;
-  static constexpr int SMEM_BUDGET = 227 * 1024 - 2048;  // barriers + 1 KB alignment slack
+  static constexpr int BIAS_BYTES = 8192;                // fp32 bias vector staged once per CTA
+  static constexpr int SMEM_BUDGET = 227 * 1024 - 2048 - BIAS_BYTES;  // barriers + 1 KB alignment slack + bias
   static constexpr int SA = (TAPS > 1) ? 3 : 4;
   static constexpr int SB_MAX = (SMEM_BUDGET - SA * A_BYTES) / B_BYTES;
   static constexpr int SB = (TAPS > 1) ? (SB_MAX > 16 ? 16 : SB_MAX) : (SB_MAX > SA ? SA : SB_MAX);
   static constexpr int NBUF = 512 / BLOCK_N;
-  static constexpr int SMEM_BYTES = SA * A_BYTES + SB * B_BYTES + 1024 /*barriers*/ + 1024 /*align*/;
+  static constexpr int SMEM_BYTES = SA * A_BYTES + SB * B_BYTES + 1024 /*barriers*/ + BIAS_BYTES + 1024 /*align*/;
   static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment (SWIZZLE_128B)");
   static_assert(A_BYTES % 1024 == 0, "A stage must keep 1024-byte alignment (SWIZZLE_128B)");
   static_assert(SB >= 2 && NBUF >= 1, "pipeline too shallow");
@@ -118,6 +119,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   auto tfull = [&](uint32_t i) { return bars + 8u * (2 * SA + 2 * SB + i); };
   auto tempty = [&](uint32_t i) { return bars + 8u * (2 * SA + 2 * SB + NBUF + i); };
   const uint32_t tmem_slot = bars + 8u * (2 * SA + 2 * SB + 2 * NBUF);
+  float* sbias = reinterpret_cast<float*>(smem_raw + (bars + 1024 - raw));  // [n_total] fp32, n_total <= 2048
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -134,6 +136,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<CG>(tmem_slot, 512);
+  if (p.bias != nullptr)
+    for (int i = threadIdx.x; i < p.n_total; i += blockDim.x) sbias[i] = p.bias[i];
   tc_fence_before();
   if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
   tc_fence_after();
@@ -251,101 +255,93 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + rt.idx * BLOCK_N;
       const int n0 = nc * BLOCK_N;
 
+      // Per-thread output row and validity.
+      int orow_idx;
+      bool valid;
       if constexpr (EPI == EPI_BIAS_RELU) {
-        const bool valid = (r < p.m_rows) && (l < p.l_store);
-        T* orow = reinterpret_cast<T*>(p.out) + (size_t)(wb * p.pitch_out + l) * p.ld_out + n0;
-#pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 16; ++c) {
-          uint32_t v[16];
-          tmem_ld16(t0 + c * 16, v);
-          tmem_ld_wait();
-          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c * 16);
-          uint32_t pk[8];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float4 b4 = __ldg(bp + i);
-            pk[2 * i] = pack2<T>(fmaxf(__uint_as_float(v[4 * i]) + b4.x, 0.f),
-                                 fmaxf(__uint_as_float(v[4 * i + 1]) + b4.y, 0.f));
-            pk[2 * i + 1] = pack2<T>(fmaxf(__uint_as_float(v[4 * i + 2]) + b4.z, 0.f),
-                                     fmaxf(__uint_as_float(v[4 * i + 3]) + b4.w, 0.f));
-          }
-          if (valid) {
-            uint4* dst = reinterpret_cast<uint4*>(orow + c * 16);
-            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-          }
-        }
+        valid = (r < p.m_rows) && (l < p.l_store);
+        orow_idx = wb * p.pitch_out + l;
       } else if constexpr (EPI == EPI_POOL4_BIAS_RELU) {
-        const int lp = l >> 2;
-        const bool valid = (r < p.m_rows) && (lp < p.l_store);
-        const int j = lane & 3;
-        T* orow = reinterpret_cast<T*>(p.out) + (size_t)(wb * p.pitch_out + lp) * p.ld_out + n0 + 4 * j;
-#pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 16; ++c) {
-          uint32_t v[16];
-          tmem_ld16(t0 + c * 16, v);
-          tmem_ld_wait();
-          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c * 16);
+        valid = (r < p.m_rows) && ((l >> 2) < p.l_store);
+        orow_idx = wb * p.pitch_out + (l >> 2);
+      } else {
+        valid = r < p.m_rows;
+        orow_idx = r;
+      }
+      const size_t obase = (size_t)orow_idx * p.ld_out + n0;
+      const int j = lane & 3;
+
+      // One 16-column chunk: registers -> bias/activation -> global.
+      auto process = [&](const uint32_t (&v)[16], int c) {
+        const float4* bp = reinterpret_cast<const float4*>(sbias + n0 + c * 16);
+        if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU) {
           uint32_t pk[8];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const float4 b4 = __ldg(bp + i);
+            const float4 b4 = bp[i];
             pk[2 * i] = pack2<T>(fmaxf(__uint_as_float(v[4 * i]) + b4.x, 0.f),
                                  fmaxf(__uint_as_float(v[4 * i + 1]) + b4.y, 0.f));
             pk[2 * i + 1] = pack2<T>(fmaxf(__uint_as_float(v[4 * i + 2]) + b4.z, 0.f),
                                      fmaxf(__uint_as_float(v[4 * i + 3]) + b4.w, 0.f));
           }
-          // MaxPool over the 4 rows held by lanes 4g..4g+3 (rounding is monotonic, so max after rounding
-          // equals rounding after max).
+          T* o = reinterpret_cast<T*>(p.out) + obase + c * 16;
+          if constexpr (EPI == EPI_BIAS_RELU) {
+            if (valid) {
+              uint4* dst = reinterpret_cast<uint4*>(o);
+              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+          } else {
+            // MaxPool over the 4 rows held by lanes 4g..4g+3 (rounding is monotonic, so max after
+            // rounding equals rounding after max); lane j of the group stores columns 4j..4j+3.
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            pk[i] = max2<T>(pk[i], __shfl_xor_sync(0xffffffffu, pk[i], 1));
-            pk[i] = max2<T>(pk[i], __shfl_xor_sync(0xffffffffu, pk[i], 2));
+            for (int i = 0; i < 8; ++i) {
+              pk[i] = max2<T>(pk[i], __shfl_xor_sync(0xffffffffu, pk[i], 1));
+              pk[i] = max2<T>(pk[i], __shfl_xor_sync(0xffffffffu, pk[i], 2));
+            }
+            uint32_t w0 = pk[0], w1 = pk[1];
+            if (j == 1) { w0 = pk[2]; w1 = pk[3]; }
+            if (j == 2) { w0 = pk[4]; w1 = pk[5]; }
+            if (j == 3) { w0 = pk[6]; w1 = pk[7]; }
+            if (valid) *reinterpret_cast<uint2*>(o + 4 * j) = make_uint2(w0, w1);
           }
-          uint32_t w0 = pk[0], w1 = pk[1];
-          if (j == 1) { w0 = pk[2]; w1 = pk[3]; }
-          if (j == 2) { w0 = pk[4]; w1 = pk[5]; }
-          if (j == 3) { w0 = pk[6]; w1 = pk[7]; }
-          if (valid) *reinterpret_cast<uint2*>(orow + c * 16) = make_uint2(w0, w1);
-        }
-      } else if constexpr (EPI == EPI_ATOMIC_F32) {
-        const bool valid = r < p.m_rows;
-        float* orow = reinterpret_cast<float*>(p.out) + (size_t)r * p.ld_out + n0;
-#pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 16; ++c) {
-          uint32_t v[16];
-          tmem_ld16(t0 + c * 16, v);
-          tmem_ld_wait();
+        } else if constexpr (EPI == EPI_ATOMIC_F32) {
+          float* o = reinterpret_cast<float*>(p.out) + obase + c * 16;
           if (valid) {
 #pragma unroll
             for (int i = 0; i < 16; ++i)
-              if (n0 + c * 16 + i < p.n_store) atomicAdd(orow + c * 16 + i, __uint_as_float(v[i]));
+              if (n0 + c * 16 + i < p.n_store) atomicAdd(o + i, __uint_as_float(v[i]));
           }
-        }
-      } else {  // EPI_BIAS_SIGMOID
-        const bool valid = r < p.m_rows;
-        float* orow = reinterpret_cast<float*>(p.out) + (size_t)r * p.ld_out + n0;
-#pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 16; ++c) {
-          uint32_t v[16];
-          tmem_ld16(t0 + c * 16, v);
-          tmem_ld_wait();
+        } else {  // EPI_BIAS_SIGMOID
+          float* o = reinterpret_cast<float*>(p.out) + obase + c * 16;
           if (valid) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const int n = n0 + c * 16 + i;
-              if (n < p.n_store) {
-                const float z = __uint_as_float(v[i]) + __ldg(p.bias + n);
-                orow[c * 16 + i] = 1.f / (1.f + __expf(-z));
+              if (n0 + c * 16 + i < p.n_store) {
+                const float z = __uint_as_float(v[i]) + sbias[n0 + c * 16 + i];
+                o[i] = 1.f / (1.f + __expf(-z));
               }
             }
           }
         }
+      };
+
+      // Software-pipelined TMEM reads: the load of chunk c+1 / c+2 is in flight while chunk c is processed.
+      constexpr int NC = BLOCK_N / 16;
+      uint32_t va[16], vb[16];
+      tmem_ld16(t0, va);
+#pragma unroll 1
+      for (int c = 0; c < NC; c += 2) {
+        if (c + 1 < NC) tmem_ld16(t0 + (c + 1) * 16, vb);
+        tmem_ld_wait();
+        process(va, c);
+        if (c + 2 < NC) tmem_ld16(t0 + (c + 2) * 16, va);
+        if (c + 1 < NC) process(vb, c + 1);
       }
       // Release the TMEM buffer to the MMA thread (leader CTA's barrier).
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(CG == 1 ? tempty(rt.idx) : mapa(tempty(rt.idx), 0));
+      if (lane == 0) mbar_arrive_remote(CG == 1 ? tempty(rt.idx) : mapa(tempty(rt.idx), 0));
       rt.advance<NBUF>();
     }
   }

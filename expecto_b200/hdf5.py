@@ -1,0 +1,300 @@
+"""Dependency-free reader/writer for the small HDF5 subset the ExPecto pipeline exchanges.
+
+chromatin.py:282-286 writes ``snps.shift_{s}.diff.h5`` with contiguous float32 datasets ``diff``, ``ref``,
+``alt`` ([2N,2002], default h5py layout: no chunks, no compression, no attributes); upstream ExPecto writes a
+single ``pred`` dataset (example/*.h5).  predict.py:173-190 reads them back.  h5py / libhdf5 are not in this
+image, so this module emits exactly that on-disk form (superblock v0, one symbol-table group, v1 object
+headers, contiguous layout — decoded byte-by-byte from example/example.vcf.shift_0.diff.h5) and
+any h5py/libhdf5 >= 1.8 reads it.  The reader walks root -> B-tree -> SNOD -> object header -> layout.
+"""
+from __future__ import annotations
+
+import struct
+import time
+
+import numpy as np
+
+_SIG = b"\x89HDF\r\n\x1a\n"
+_UNDEF = 0xFFFFFFFFFFFFFFFF
+_DATA_START = 0x800
+_LEAF_K, _INTERNAL_K = 4, 16
+
+
+def _pad8(b: bytes) -> bytes:
+    return b + b"\x00" * ((-len(b)) % 8)
+
+
+def _msg(mtype: int, data: bytes, flags: int = 0) -> bytes:
+    data = _pad8(data)
+    return struct.pack("<HHB3x", mtype, len(data), flags) + data
+
+
+def _dataset_header(shape, data_addr: int, nbytes: int, mtime: int) -> bytes:
+    rank = len(shape)
+    dataspace = struct.pack("<BBB5x", 1, rank, 1) + b"".join(struct.pack("<Q", d) for d in shape) * 2
+    # IEEE little-endian float32: class 1 version 1; bit fields 0x20,0x1f,0x00; size 4;
+    # bit offset 0, precision 32, exp loc 23, exp size 8, mantissa loc 0, mantissa size 23, bias 127
+    datatype = struct.pack("<BBBBI", 0x11, 0x20, 0x1F, 0x00, 4) + struct.pack("<HHBBBBI", 0, 32, 23, 8, 0, 23, 127)
+    fill = struct.pack("<BBBBI", 2, 2, 2, 1, 0)
+    layout = struct.pack("<BBQQ", 3, 1, data_addr, nbytes)
+    mt = struct.pack("<B3xI", 1, mtime & 0xFFFFFFFF)
+    msgs = _msg(1, dataspace) + _msg(3, datatype, 1) + _msg(5, fill, 1) + _msg(8, layout) + _msg(0x12, mt)
+    total = 0x100
+    nil = total - len(msgs) - 8
+    assert nil >= 0, "dataset rank too large for the fixed header"
+    msgs += struct.pack("<HHB3x", 0, nil, 0) + b"\x00" * nil
+    return struct.pack("<BBHII4x", 1, 0, 6, 1, total) + msgs
+
+
+class H5Writer:
+    """Write float32 datasets (<= 8, names sorted as HDF5 requires) into one v0-superblock file.
+
+    ``create(name, shape)`` reserves space; ``write_rows(name, row0, array)`` pwrite()s row slabs, so several
+    producers (GPU ranks, pipeline stages) can fill one contiguous dataset without an in-memory copy."""
+
+    def __init__(self, path: str, datasets: dict[str, tuple[int, ...]]):
+        if not 1 <= len(datasets) <= 2 * _LEAF_K:
+            raise ValueError("1..8 datasets per file")
+        self.path = path
+        self.names = sorted(datasets)
+        self.shapes = {n: tuple(int(x) for x in datasets[n]) for n in self.names}
+        self.addr, off = {}, _DATA_START
+        for n in self.names:
+            self.addr[n] = off
+            off += int(np.prod(self.shapes[n])) * 4
+            off += (-off) % 8
+        self.eof = off
+        self._f = open(path, "wb+")
+        self._f.write(self._metadata())
+        self._f.truncate(self.eof)
+
+    def _metadata(self) -> bytes:
+        btree_addr, heap_addr = 0x88, 0x2A8
+        heap_data_addr = heap_addr + 32
+        # local heap: "" at 0, then each name NUL-terminated padded to 8
+        heap = bytearray(8)
+        name_off = {}
+        for n in self.names:
+            name_off[n] = len(heap)
+            heap += _pad8(n.encode("ascii") + b"\x00")
+        free_off = len(heap)
+        heap_size = max(88, free_off + 16)
+        heap_size += (-heap_size) % 8
+        heap += struct.pack("<QQ", 1, heap_size - free_off)
+        heap += b"\x00" * (heap_size - len(heap))
+        snod_addr = heap_data_addr + heap_size
+        snod_size = 8 + 2 * _LEAF_K * 40
+        hdr_addr = {}
+        a = snod_addr + snod_size
+        a += (-a) % 8
+        for n in self.names:
+            hdr_addr[n] = a
+            a += 0x110
+        if a > _DATA_START:
+            raise ValueError("metadata block overflow")
+        mtime = int(time.time())
+
+        out = bytearray(_DATA_START)
+        sb = _SIG + struct.pack("<BBBBBBBBHHI", 0, 0, 0, 0, 0, 8, 8, 0, _LEAF_K, _INTERNAL_K, 0)
+        sb += struct.pack("<QQQQ", 0, _UNDEF, self.eof, _UNDEF)
+        sb += struct.pack("<QQII", 0, 0x60, 1, 0) + struct.pack("<QQ", btree_addr, heap_addr)  # root symbol entry
+        out[0:len(sb)] = sb
+        root = struct.pack("<BBHII4x", 1, 0, 1, 1, 0x18) + _msg(0x11, struct.pack("<QQ", btree_addr, heap_addr))
+        out[0x60:0x60 + len(root)] = root
+        bt = b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, _UNDEF, _UNDEF)
+        bt += struct.pack("<QQQ", 0, snod_addr, name_off[self.names[-1]])
+        out[btree_addr:btree_addr + len(bt)] = bt
+        hp = b"HEAP" + struct.pack("<B3xQQQ", 0, heap_size, free_off, heap_data_addr)
+        out[heap_addr:heap_addr + len(hp)] = hp
+        out[heap_data_addr:heap_data_addr + heap_size] = heap
+        sn = b"SNOD" + struct.pack("<BBH", 1, 0, len(self.names))
+        for n in self.names:
+            sn += struct.pack("<QQII16x", name_off[n], hdr_addr[n], 0, 0)
+        out[snod_addr:snod_addr + len(sn)] = sn
+        for n in self.names:
+            nbytes = int(np.prod(self.shapes[n])) * 4
+            h = _dataset_header(self.shapes[n], self.addr[n], nbytes, mtime)
+            out[hdr_addr[n]:hdr_addr[n] + len(h)] = h
+        return bytes(out)
+
+    def write_rows(self, name: str, row0: int, arr: np.ndarray) -> None:
+        shape = self.shapes[name]
+        arr = np.ascontiguousarray(arr, dtype="<f4")
+        row_elems = int(np.prod(shape[1:])) if len(shape) > 1 else 1
+        if arr.size % row_elems or row0 * row_elems + arr.size > int(np.prod(shape)):
+            raise ValueError("slab does not fit the dataset")
+        self._f.seek(self.addr[name] + row0 * row_elems * 4)
+        self._f.write(memoryview(arr).cast("B"))
+
+    def write(self, name: str, arr: np.ndarray) -> None:
+        if tuple(arr.shape) != self.shapes[name]:
+            raise ValueError(f"{name}: shape {arr.shape} != {self.shapes[name]}")
+        self.write_rows(name, 0, arr)
+
+    def close(self) -> None:
+        if self._f:
+            self._f.close()
+            self._f = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+def write_datasets(path: str, arrays: dict[str, np.ndarray]) -> None:
+    """``h5py.File(path,'w'); create_dataset(name, data=...)`` for float32 arrays (chromatin.py:282-286)."""
+    with H5Writer(path, {k: v.shape for k, v in arrays.items()}) as w:
+        for k, v in arrays.items():
+            w.write(k, v)
+
+
+class H5Dataset:
+    """Lazy view of one contiguous dataset: ``.shape`` and row slicing, as predict.py:174-190 uses h5py."""
+
+    def __init__(self, path: str, shape, dtype, addr: int):
+        self.path, self.shape, self.dtype, self.addr = path, tuple(shape), np.dtype(dtype), addr
+        self._mm = None
+
+    def _map(self):
+        if self._mm is None:
+            self._mm = np.memmap(self.path, dtype=self.dtype, mode="r", offset=self.addr, shape=self.shape)
+        return self._mm
+
+    def __getitem__(self, idx):
+        return np.asarray(self._map()[idx])
+
+    def __array__(self, dtype=None, copy=None):
+        a = np.asarray(self._map())
+        return a.astype(dtype) if dtype is not None else a
+
+
+class H5File:
+    """Minimal ``h5py.File(path,'r')``: ``f['diff']`` -> H5Dataset, ``list(f)`` -> dataset names."""
+
+    def __init__(self, path: str, mode: str = "r"):
+        if mode != "r":
+            raise ValueError("H5File is read-only; use H5Writer / write_datasets to write")
+        self.path = path
+        with open(path, "rb") as f:
+            self._meta = f.read(1 << 20)
+        b = self._meta
+        if b[:8] != _SIG or b[8] != 0:
+            raise ValueError("not an HDF5 file with a version-0 superblock")
+        if b[13] != 8 or b[14] != 8:
+            raise ValueError("only 8-byte offsets/lengths are supported")
+        self._base = struct.unpack_from("<Q", b, 24)[0]
+        btree, heap = struct.unpack_from("<QQ", b, 24 + 32 + 24)  # scratch pad of the root symbol table entry
+        if struct.unpack_from("<I", b, 24 + 32 + 16)[0] != 1:
+            btree, heap = self._symbol_table_message(struct.unpack_from("<Q", b, 24 + 32 + 8)[0])
+        self._datasets = {}
+        heap_data = struct.unpack_from("<Q", b, heap + 24)[0]
+        self._walk_btree(btree, heap_data)
+
+    def _bytes(self, addr: int, n: int) -> bytes:
+        if addr + n <= len(self._meta):
+            return self._meta[addr:addr + n]
+        with open(self.path, "rb") as f:
+            f.seek(addr)
+            return f.read(n)
+
+    def _messages(self, addr: int):
+        ver, _, nmsg, _, hsize = struct.unpack_from("<BBHII", self._bytes(addr, 16))
+        if ver != 1:
+            raise ValueError("only version-1 object headers are supported")
+        blocks = [(addr + 16, hsize)]
+        out = []
+        while blocks and len(out) < nmsg:
+            pos, size = blocks.pop(0)
+            end = pos + size
+            while pos + 8 <= end and len(out) < nmsg:
+                mtype, msize, _flags = struct.unpack_from("<HHB", self._bytes(pos, 8))
+                data = self._bytes(pos + 8, msize)
+                if mtype == 0x10:  # continuation
+                    blocks.append(struct.unpack_from("<QQ", data))
+                out.append((mtype, data))
+                pos += 8 + msize
+        return out
+
+    def _symbol_table_message(self, addr: int):
+        for mtype, data in self._messages(addr):
+            if mtype == 0x11:
+                return struct.unpack_from("<QQ", data)
+        raise ValueError("root group has no symbol table")
+
+    def _walk_btree(self, addr: int, heap_data: int) -> None:
+        b = self._bytes(addr, 24)
+        if b[:4] != b"TREE":
+            raise ValueError("bad B-tree node")
+        level, used = b[5], struct.unpack_from("<H", b, 6)[0]
+        body = self._bytes(addr + 24, (2 * used + 1) * 8)
+        for i in range(used):
+            child = struct.unpack_from("<Q", body, 8 + 16 * i)[0]
+            if level > 0:
+                self._walk_btree(child, heap_data)
+            else:
+                self._read_snod(child, heap_data)
+
+    def _read_snod(self, addr: int, heap_data: int) -> None:
+        b = self._bytes(addr, 8)
+        if b[:4] != b"SNOD":
+            raise ValueError("bad symbol node")
+        n = struct.unpack_from("<H", b, 6)[0]
+        ents = self._bytes(addr + 8, 40 * n)
+        for i in range(n):
+            name_off, hdr = struct.unpack_from("<QQ", ents, 40 * i)
+            raw = self._bytes(heap_data + name_off, 256)
+            name = raw[:raw.index(b"\x00")].decode("ascii")
+            ds = self._read_dataset(hdr)
+            if ds is not None:
+                self._datasets[name] = ds
+
+    def _read_dataset(self, addr: int):
+        shape = dtype = data_addr = None
+        for mtype, data in self._messages(addr):
+            if mtype == 1:
+                rank = data[1]
+                off = 8 if data[0] == 1 else 4
+                shape = struct.unpack_from("<%dQ" % rank, data, off)
+            elif mtype == 3:
+                cls, size = data[0] & 0x0F, struct.unpack_from("<I", data, 4)[0]
+                big = data[1] & 1
+                if cls == 1:
+                    dtype = (">f%d" if big else "<f%d") % size
+                elif cls == 0:
+                    signed = (data[1] >> 3) & 1
+                    dtype = (">" if big else "<") + ("i" if signed else "u") + str(size)
+            elif mtype == 8:
+                if data[0] != 3 or data[1] != 1:
+                    raise ValueError("only contiguous (layout v3 class 1) datasets are supported")
+                data_addr = struct.unpack_from("<Q", data, 2)[0]
+        if shape is None or dtype is None or data_addr is None:
+            return None
+        return H5Dataset(self.path, shape, dtype, self._base + data_addr)
+
+    def __getitem__(self, name: str) -> H5Dataset:
+        return self._datasets[name]
+
+    def __contains__(self, name: str) -> bool:
+        return name in self._datasets
+
+    def __iter__(self):
+        return iter(self._datasets)
+
+    def keys(self):
+        return self._datasets.keys()
+
+    def close(self) -> None:
+        pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+def File(path: str, mode: str = "r"):
+    """``h5py.File`` look-alike for reading; writing goes through :func:`write_datasets`."""
+    return H5File(path, mode)
