@@ -1,0 +1,177 @@
+"""Drop-in for the reference's ``chromatin.py`` (same CLI, same files out), computed on a B200.
+
+    python -m expecto_b200.chromatin ./example/example.vcf [--maxshift 800 --output_dir chromatin_out ...]
+
+Reference behaviour reproduced (file:line into /root/reference/chromatin.py):
+  * arguments and defaults                                                     :26-42
+  * VCF read, optional ``--chunk_i/--chunk_size`` row slice                    :211-214
+  * ``{out}/snps_hg19.vcf`` = two header lines + ALL rows (before filtering)   :232-237
+  * chromosome normalisation ``'chr'+str(c).replace('chr','')`` and CHRS filter :240-241
+  * shift order ``[0,-200..-maxshift,200..maxshift]``                          :243
+  * the three allele-match counters printed at shift 0                         :256-260
+  * ``{out}/snps.shift_{s}.diff.h5`` with float32 ``diff``/``ref``/``alt`` [2N,2002], forward rows then
+    reverse-complement rows, diff = alt - ref                                   :281-286
+What differs by design: the windows are never built as strings — descriptors index a 2-bit genome in HBM
+(expecto_b200/windows.py) and kernel 1 encodes them inside the forward; ``--cuda`` is accepted and ignored
+(there is no CPU path); ``--hg38`` needs the third-party ``liftover`` package + chain files and is refused.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import numpy as np
+
+CHRS = ["chr%d" % i for i in range(1, 23)] + ["chrX", "chrY"]  # chromatin.py:108-110
+
+
+def shift_list(maxshift: int) -> list[int]:
+    return [0] + list(range(-200, -maxshift - 1, -200)) + list(range(200, maxshift + 1, 200))  # chromatin.py:243
+
+
+def build_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(description="Predict variant chromatin effects")
+    p.add_argument("inputfile", type=str, help="Input file in vcf format")
+    p.add_argument("--hg38", action="store_true", help="(unsupported here: needs the liftover package)")
+    p.add_argument("--chunk_size", action="store", dest="chunk_size", type=int, default=int(1e5))
+    p.add_argument("--chunk_i", action="store", dest="chunk_i", type=int, default=None)
+    p.add_argument("--maxshift", action="store", dest="maxshift", type=int, default=800)
+    p.add_argument("--inputsize", action="store", dest="inputsize", type=int, default=2000)
+    p.add_argument("--batchsize", action="store", dest="batchsize", type=int, default=32,
+                   help="accepted for compatibility; the GPU batch is --gpu_batch variants")
+    p.add_argument("--output_dir", action="store", dest="output_dir", type=str, default="chromatin_out")
+    p.add_argument("--cuda", action="store_true", help="accepted for compatibility (always on)")
+    # extensions
+    p.add_argument("--genome", default="./resources/hg19.fa", help="FASTA (chromatin.py:44 hard-codes this path)")
+    p.add_argument("--weights", default="./resources/deepsea.beluga.pth", help="state_dict (chromatin.py:103)")
+    p.add_argument("--dtype", default="f16", choices=["f16", "bf16"], help="tensor-core operand type")
+    p.add_argument("--device", type=int, default=0)
+    p.add_argument("--gpu_batch", type=int, default=2048, help="variants per GPU sub-batch (x4 windows)")
+    p.add_argument("--upstream_layout", action="store_true",
+                   help="also write upstream ExPecto's {inputfile}.shift_{s}.diff.h5 with one 'pred' dataset")
+    return p
+
+
+def read_vcf(path: str, chunk_i=None, chunk_size=int(1e5)):
+    """chromatin.py:211-214."""
+    import pandas as pd
+
+    vcf = pd.read_csv(path, sep="\t", header=None, comment="#")
+    if chunk_i is not None:
+        vcf = vcf.iloc[chunk_i * chunk_size:(chunk_i + 1) * chunk_size]
+    return vcf
+
+
+def write_snps_vcf(vcf, output_dir: str) -> str:
+    """chromatin.py:232-237 — the same pandas call, so the bytes are identical."""
+    path = f"{output_dir}/snps_hg19.vcf"
+    with open(path, "w") as f:
+        print("##fileformat=VCFv4.3", file=f)
+        print("#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO", file=f)
+    vcf.to_csv(path, sep="\t", header=False, index=False, mode="a")
+    return path
+
+
+def normalise_and_filter(vcf):
+    """chromatin.py:240-241."""
+    vcf = vcf.copy()
+    vcf[vcf.columns[0]] = "chr" + vcf.iloc[:, 0].map(str).str.replace("chr", "")
+    return vcf[vcf.iloc[:, 0].isin(CHRS)]
+
+
+def variant_columns(vcf):
+    chroms = [str(c) for c in vcf.iloc[:, 0]]
+    pos = np.asarray([int(p) for p in vcf.iloc[:, 1]], dtype=np.int64)
+    refs = [str(x) for x in vcf.iloc[:, 3]]
+    alts = [str(x) for x in vcf.iloc[:, 4]]
+    return chroms, pos, refs, alts
+
+
+def predict_shift(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int, sink) -> None:
+    """One iteration of chromatin.py:243-286 for all variants.  ``sink(name, row0, array)`` receives
+    float32 row slabs of the [2N,2002] datasets (forward rows at v, reverse-complement rows at N+v)."""
+    import torch
+
+    from .engine import chromatin_outputs
+    from .windows import check_valid_bases, chromatin_window_descs
+
+    n = len(pos)
+    for v0 in range(0, n, gpu_batch):
+        v1 = min(n, v0 + gpu_batch)
+        descs, alleles = chromatin_window_descs(genome, chroms[v0:v1], pos[v0:v1], refs[v0:v1], alts[v0:v1], shift)
+        check_valid_bases(genome, descs)
+        probs = engine.forward_windows(descs, alleles)
+        ref, alt, diff = chromatin_outputs(probs, v1 - v0)
+        m = v1 - v0
+        for name, t in (("diff", diff), ("ref", ref), ("alt", alt)):
+            h = t.cpu().numpy()
+            sink(name, v0, h[:m])
+            sink(name, n + v0, h[m:])
+        del probs, ref, alt, diff
+    torch.cuda.synchronize(engine.device)
+
+
+def run(args, engine=None, genome=None) -> dict:
+    """The whole script; returns {'n_variants', 'counters', 'files'} for callers (tests, bench)."""
+    from .genome import PackedGenome
+    from .hdf5 import H5Writer
+    from .windows import allele_match_counts
+
+    if args.hg38:
+        raise NotImplementedError("--hg38 needs the third-party `liftover` package and UCSC chain files, neither of "
+                                  "which is available offline; lift the VCF to hg19 first (out of scope, SURVEY §8b)")
+    if args.inputsize != 2000:
+        raise ValueError("Beluga's architecture fixes --inputsize at 2000 (Linear(67840,...) = 640*106, Beluga.py:43)")
+    os.makedirs(args.output_dir, exist_ok=True)
+    if genome is None:
+        genome = PackedGenome.from_fasta(args.genome)
+    if engine is None:
+        from .engine import BelugaEngine
+        engine = BelugaEngine(args.device, dtype=args.dtype, capacity=min(4096, 4 * args.gpu_batch))
+        engine.load_weights_file(args.weights)
+    if engine._genome is not genome:
+        engine.set_genome(genome)
+
+    vcf = read_vcf(args.inputfile, args.chunk_i, args.chunk_size)
+    write_snps_vcf(vcf, args.output_dir)
+    vcf = normalise_and_filter(vcf)
+    chroms, pos, refs, alts = variant_columns(vcf)
+    missing = sorted({c for c in chroms if c not in genome.offsets})
+    if missing:
+        raise KeyError(f"contig(s) {missing} are not in the genome")  # pyfasta raises KeyError too
+    n = len(pos)
+    files, counters = [], None
+    for shift in shift_list(args.maxshift):
+        if shift == 0:
+            counters = allele_match_counts(genome, chroms, pos, refs, alts)
+            print(f"Number of variants with reference allele matched with reference genome: {counters[0]}")
+            print(f"Number of variants with alternate allele matched with reference genome: {counters[1]}")
+            print(f"Number of input variants: {counters[2]}")
+        path = f"{args.output_dir}/snps.shift_{str(shift)}.diff.h5"
+        shapes = {k: (2 * n, 2002) for k in ("diff", "ref", "alt")}
+        with H5Writer(path, shapes) as w:
+            up = None
+            if args.upstream_layout:
+                up = H5Writer(f"{args.inputfile}.shift_{str(shift)}.diff.h5", {"pred": (2 * n, 2002)})
+
+            def sink(name, row0, arr, w=w, up=up):
+                w.write_rows(name, row0, arr)
+                if up is not None and name == "diff":
+                    up.write_rows("pred", row0, arr)
+
+            predict_shift(engine, genome, chroms, pos, refs, alts, shift, args.gpu_batch, sink)
+            if up is not None:
+                up.close()
+        files.append(path)
+    return {"n_variants": n, "counters": counters, "files": files}
+
+
+def main(argv=None) -> int:
+    args = build_parser().parse_args(argv)
+    run(args)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,252 @@
+#!/usr/bin/env python
+"""Pin the oracle against the reference itself and write the golden fixtures under tests/golden/.
+
+Runs ONLY in the build container (needs /root/reference; the GPU box does not have it).  Everything the
+reference computes here is computed by the reference's own, unmodified code:
+
+* ``expecto_utils.encodeSeqs`` and ``Beluga.Beluga`` are imported from /root/reference;
+* ``fetchSeqs`` is lifted out of chromatin.py with ``ast`` and exec'd (chromatin.py is a module-level script
+  and cannot be imported) — executed, not copied: no reference source enters this repository;
+* ``chromatin.py``, ``compute_expecto_features.py`` and ``predict.py`` run as subprocesses in a scratch
+  directory holding synthetic ``resources/hg19.fa`` + ``resources/deepsea.beluga.pth``, behind the import shims in
+  oracle/shims (pyfasta, h5py, liftover, xgboost, matplotlib — third-party packages absent from this image).
+
+Every stage asserts that oracle/beluga_oracle.py reproduces the reference output, then stores a small slice
+as a fixture.  Usage:  python oracle/make_golden.py [--workdir /tmp/bx_golden] [--skip-scripts]
+"""
+from __future__ import annotations
+
+import argparse
+import ast
+import os
+import shutil
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+GOLD = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, ROOT)
+
+from expecto_b200 import synth  # noqa: E402
+from oracle import beluga_oracle as O  # noqa: E402
+from oracle import golden_inputs as GI  # noqa: E402
+
+
+def load_reference_fetchseqs(genome):
+    """exec the reference's own fetchSeqs (chromatin.py:175-209) against ``genome``."""
+    src = open(os.path.join(REF, "chromatin.py")).read()
+    tree = ast.parse(src)
+    fn = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "fetchSeqs"][0]
+    ns = {"genome": genome}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), "chromatin.py", "exec"), ns)
+    return ns["fetchSeqs"]
+
+
+def stage_encode():
+    sys.path.insert(0, REF)
+    from expecto_utils import encodeSeqs as ref_encode  # the reference's canonical encoder
+
+    genome = synth.make_genome(GI.SMALL_CONTIGS, seed=GI.SMALL_GENOME_SEED)
+    g = O.DictGenome(genome)
+    ref_fetch = load_reference_fetchseqs(g)
+    rows = GI.edge_variants(genome)
+    packed, meta = [], []
+    for shift in GI.ENCODE_SHIFTS:
+        refseqs, altseqs = [], []
+        for chrom, pos, _id, ref, alt in rows:
+            a = ref_fetch(chrom, pos, ref, alt, shift=shift)
+            b = O.fetch_seqs(g, chrom, pos, ref, alt, shift=shift)
+            assert a == b, ("fetchSeqs restatement differs", chrom, pos, ref, alt, shift)
+            refseqs.append(a[0]), altseqs.append(a[1])
+        for name, seqs in (("ref", refseqs), ("alt", altseqs)):
+            r = ref_encode(seqs)
+            o = O.encode_seqs(seqs)
+            assert r.dtype == np.bool_ and np.array_equal(r, o), "encodeSeqs restatement differs"
+            packed.append(np.packbits(r.reshape(r.shape[0], -1), axis=1))
+            meta.append((shift, name))
+    # odd-length / short strings straight into the encoder (crop arithmetic, chromatin.py:164)
+    rng = np.random.default_rng(5)
+    odd = [synth.random_sequence(rng, n) for n in (2000, 2001, 2099, 2100, 2101, 2103, 2110, 1990, 1999)]
+    assert np.array_equal(ref_encode(odd), O.encode_seqs(odd))
+    np.savez_compressed(os.path.join(GOLD, "encode_golden.npz"),
+                        rows=np.array([[str(x) for x in r] for r in rows]),
+                        shifts=np.array([m[0] for m in meta]), which=np.array([m[1] for m in meta]),
+                        packed=np.stack(packed), odd=np.array(odd),
+                        odd_packed=np.packbits(ref_encode(odd).reshape(2 * len(odd), -1), axis=1))
+    print(f"[encode] {len(rows)} variants x {len(GI.ENCODE_SHIFTS)} shifts: oracle == reference, fixture written")
+
+
+def stage_beluga(sd):
+    import torch
+    sys.path.insert(0, REF)
+    from Beluga import Beluga
+
+    model = Beluga()
+    model.load_state_dict({k: torch.from_numpy(v) for k, v in sd.items()})
+    model.eval()
+    x = synth.random_onehot(GI.BELUGA_N, seed=GI.BELUGA_SEED)
+    x[0, :, 100:110] = 0
+    with torch.no_grad():
+        ref = model.forward(torch.from_numpy(x.astype(np.float32)).unsqueeze(2)).numpy()
+    ours = O.beluga_forward(x.astype(np.float32), sd)
+    err = np.abs(ref - ours).max()
+    assert err < 2e-6, f"Beluga restatement differs by {err}"
+    np.savez_compressed(os.path.join(GOLD, "beluga_golden.npz"), probs=ref.astype(np.float32))
+    print(f"[beluga] {GI.BELUGA_N} windows: |oracle - reference| max {err:.2e}; p mean {ref.mean():.3f}, "
+          f"frac>0.5 {np.mean(ref > 0.5):.3f}")
+
+
+def run_ref_script(script, args, cwd):
+    env = dict(os.environ)
+    env["PYTHONPATH"] = os.path.join(ROOT, "oracle", "shims")
+    env["BX_REPO_ROOT"] = ROOT
+    t0 = time.time()
+    r = subprocess.run([sys.executable, os.path.join(REF, script)] + args, cwd=cwd, env=env, capture_output=True,
+                       text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"{script} failed:\n{r.stdout[-2000:]}\n{r.stderr[-4000:]}")
+    print(f"[{script}] ok in {time.time() - t0:.1f}s")
+    return r.stdout
+
+
+def prepare_workdir(work, sd):
+    import torch
+    os.makedirs(os.path.join(work, "resources"), exist_ok=True)
+    genome = GI.cfg1_genome()
+    fa = os.path.join(work, "resources", "hg19.fa")
+    if not os.path.exists(fa):
+        synth.write_fasta(fa, genome)
+    pth = os.path.join(work, "resources", "deepsea.beluga.pth")
+    if not os.path.exists(pth):
+        torch.save({k: torch.from_numpy(v) for k, v in sd.items()}, pth)
+    return genome
+
+
+def stage_chromatin(work, sd, genome):
+    shutil.copy(os.path.join(REF, "example", "example.vcf"), os.path.join(work, "example.vcf"))
+    out = run_ref_script("chromatin.py", ["example.vcf", "--output_dir", "out_example"], work)
+    counters = [int(l.rsplit(":", 1)[1]) for l in out.splitlines() if l.startswith("Number of")]
+    g = O.DictGenome(genome)
+    rows = O.normalise_vcf_rows([l.rstrip("\n").split("\t") for l in open(os.path.join(work, "example.vcf"))])
+    shifts = O.SHIFTS_CHROMATIN(800)
+    sums = np.zeros((len(shifts), 3, 20), dtype=np.float64)
+    keep = {}
+    for si, s in enumerate(shifts):
+        z = np.load(os.path.join(work, "out_example", f"snps.shift_{s}.diff.h5.npz"))
+        assert np.array_equal(z["diff"], z["alt"] - z["ref"])
+        for di, k in enumerate(("diff", "ref", "alt")):
+            sums[si, di] = z[k].astype(np.float64).sum(axis=1)
+        if s in GI.CFG1_KEEP_SHIFTS:
+            d, r, a, cnt = O.chromatin_shift(g, rows, sd, s)
+            err = max(np.abs(r - z["ref"]).max(), np.abs(a - z["alt"]).max())
+            assert err < 2e-6, f"chromatin restatement differs at shift {s}: {err}"
+            if s == 0:
+                assert list(cnt) == counters, (cnt, counters)
+            keep[f"ref_{s}"], keep[f"alt_{s}"] = z["ref"], z["alt"]
+    vcf_text = open(os.path.join(work, "out_example", "snps_hg19.vcf")).read()
+    np.savez_compressed(os.path.join(GOLD, "chromatin_cfg1_golden.npz"), row_sums=sums, counters=np.array(counters),
+                        snps_hg19_vcf=np.array(vcf_text), **keep)
+    print(f"[chromatin cfg1] counters {counters}; oracle == reference on shifts {GI.CFG1_KEEP_SHIFTS}")
+
+    # edge-case VCF (indels, ref mismatch, lower-case alleles, un-prefixed and non-CHRS contigs), 3 shifts
+    rows_e = GI.cfg1_edge_variants(genome)
+    synth.write_vcf(os.path.join(work, "edge.vcf"), rows_e, header=True)
+    out = run_ref_script("chromatin.py", ["edge.vcf", "--output_dir", "out_edge", "--maxshift", "200"], work)
+    counters_e = [int(l.rsplit(":", 1)[1]) for l in out.splitlines() if l.startswith("Number of")]
+    rows_n = O.normalise_vcf_rows(rows_e)
+    keep = {}
+    for s in O.SHIFTS_CHROMATIN(200):
+        z = np.load(os.path.join(work, "out_edge", f"snps.shift_{s}.diff.h5.npz"))
+        d, r, a, cnt = O.chromatin_shift(g, rows_n, sd, s)
+        err = max(np.abs(r - z["ref"]).max(), np.abs(a - z["alt"]).max())
+        assert err < 2e-6 and z["ref"].shape[0] == 2 * len(rows_n), (s, err)
+        if s == 0:
+            assert list(cnt) == counters_e
+        keep[f"ref_{s}"], keep[f"alt_{s}"] = z["ref"], z["alt"]
+    np.savez_compressed(os.path.join(GOLD, "chromatin_edge_golden.npz"),
+                        rows=np.array([[str(x) for x in r] for r in rows_e]), counters=np.array(counters_e),
+                        snps_hg19_vcf=np.array(open(os.path.join(work, "out_edge", "snps_hg19.vcf")).read()), **keep)
+    print(f"[chromatin edge] {len(rows_e)} rows -> {len(rows_n)} kept; counters {counters_e}")
+
+
+def stage_features(work, sd, genome):
+    genes = GI.cfg4_genes()
+    with open(os.path.join(work, "geneanno_small.csv"), "w") as f:
+        f.write("id,symbol,seqnames,strand,TSS,CAGE_representative_TSS,type\n")
+        for gid, chrom, strand, tss in genes:
+            f.write(f"{gid},SYM,{chrom},{strand},{tss},{tss},protein_coding\n")
+    with open(os.path.join(work, "tss_none.tsv"), "w") as f:
+        f.write("\tens_id\tchrom\ttss\tstrand\tx\tis_default_tss\n0\tENSG_NOMATCH\tchr1\t1000000\t+\t0\tTrue\n")
+    run_ref_script("compute_expecto_features.py", ["geneanno_small.csv", "tss_none.tsv", "-o", "out_features"], work)
+    ref = np.load(os.path.join(work, "out_features", "Xreducedall.2002.representative_tss_top.npy"))
+    g = O.DictGenome(genome)
+    pw = O.fixed_pos_weights()
+    for i, (gid, chrom, strand, tss) in enumerate(genes):
+        seqs = O.tss_windows(g, chrom, tss, 1 if strand == "+" else -1)
+        enc = O.encode_seqs(seqs, concat_rc=False)
+        fwd = O.beluga_forward(enc.astype(np.float32), sd)
+        rc = O.beluga_forward(np.ascontiguousarray(enc[:, ::-1, ::-1]).astype(np.float32), sd)
+        ours = O.fixed_transform(fwd, rc, pw)
+        rel = np.abs(ours - ref[i]).max() / np.abs(ref[i]).max()
+        assert rel < 1e-6, f"feature restatement differs for gene {i}: {rel}"
+    np.savez_compressed(os.path.join(GOLD, "features_golden.npz"), features=ref,
+                        genes=np.array([[str(x) for x in gg] for gg in genes]))
+    print(f"[features] {len(genes)} genes: oracle == reference, shape {ref.shape} {ref.dtype}")
+
+
+def stage_predict(work):
+    rng = np.random.default_rng(GI.GBLINEAR_SEED)
+    w = (rng.standard_normal(20020) * 0.01).astype(np.float32)
+    np.savez(os.path.join(work, "model.npz"), weights=w, bias=np.float32(0.25), base_score=np.float32(0.5))
+    shutil.copy(os.path.join(REF, "example", "example.vcf.bed.sorted.bed.closestgene"), work)
+    run_ref_script("predict.py", [
+        "--model_save_file", "model.npz", "--belugaFeatures",
+        os.path.join(REF, "resources", "deepsea_beluga_2002_features.tsv"), "--coorFile_chromatin",
+        "out_example/snps_hg19.vcf", "--geneFile", "example.vcf.bed.sorted.bed.closestgene",
+        "--snpEffectFilePattern", "out_example/snps.shift_SHIFT.diff.h5", "-o", "out_predict"], work)
+    import pandas as pd
+    sed = pd.read_csv(os.path.join(work, "out_predict", "sed.tsv"), sep="\t")
+    # restatement: strand average -> weights -> transform -> gblinear
+    shifts = O.SHIFTS_CHROMATIN(800)
+    data = {k: [] for k in ("diff", "ref", "alt")}
+    for s in shifts:
+        z = np.load(os.path.join(work, "out_example", f"snps.shift_{s}.diff.h5.npz"))
+        for k in data:
+            data[k].append(O.strand_average(z[k]))
+    gene = pd.read_csv(os.path.join(work, "example.vcf.bed.sorted.bed.closestgene"), sep="\t", header=None)
+    dist = -np.asarray(gene.iloc[:, -1])
+    strand = np.asarray(gene.iloc[:, -3])
+    wts = O.variant_weights(dist, strand)
+    ref_s = O.gblinear_predict(O.variant_transform(data["ref"], wts), w, 0.25, 0.5)
+    alt_s = O.gblinear_predict(O.variant_transform(data["alt"], wts), w, 0.25, 0.5)
+    assert np.abs(ref_s - sed["REF"].values).max() < 1e-4 and np.abs(alt_s - sed["ALT"].values).max() < 1e-4
+    feats = O.variant_transform(data["diff"], wts)
+    np.savez_compressed(os.path.join(GOLD, "predict_golden.npz"),
+                        sed_tsv=np.array(open(os.path.join(work, "out_predict", "sed.tsv")).read()),
+                        diff_features_row0=feats[0], model_w=w)
+    print(f"[predict] sed.tsv rows {len(sed)}; oracle == reference (REF/ALT within 1e-4)")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workdir", default="/tmp/bx_golden")
+    ap.add_argument("--skip-scripts", action="store_true", help="only the import-level stages (fast)")
+    args = ap.parse_args()
+    os.makedirs(GOLD, exist_ok=True)
+    stage_encode()
+    sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
+    stage_beluga(sd)
+    if not args.skip_scripts:
+        genome = prepare_workdir(args.workdir, sd)
+        stage_chromatin(args.workdir, sd, genome)
+        stage_features(args.workdir, sd, genome)
+        stage_predict(args.workdir)
+    print("golden fixtures written to", GOLD)
+
+
+if __name__ == "__main__":
+    main()

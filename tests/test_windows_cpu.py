@@ -1,0 +1,91 @@
+"""Host logic of kernel 1 against the oracle and the reference-generated fixture (bit-exact)."""
+import numpy as np
+import pytest
+
+from expecto_b200.genome import PackedGenome, encode_bases
+from expecto_b200.windows import (AlleleTable, allele_match_counts, chromatin_window_descs, crop_bounds, tss_descs,
+                                  variant_descs)
+from helpers import decode_descs
+from oracle import beluga_oracle as O
+from oracle import golden_inputs as GI
+
+
+def test_crop_bounds_matches_python_slice():
+    import math
+    for total in list(range(0, 40)) + list(range(1960, 2300)):
+        lo = int(math.floor((total - 2000) / 2.0))
+        hi = int(math.floor(total - (total - 2000) / 2.0))
+        s, e, _ = slice(lo, hi).indices(total)
+        a, b = crop_bounds(np.array([total]))
+        assert (int(a[0]), int(max(b[0], a[0]))) == (s, max(e, s)), total
+
+
+def test_descriptors_match_reference_fixture(small_genome, golden):
+    g = golden("encode_golden.npz")
+    rows = [[r[0], int(r[1]), r[2], r[3], r[4]] for r in g["rows"]]
+    assert rows == GI.edge_variants(small_genome), "fixture inputs drifted"
+    pg = PackedGenome.from_sequences(small_genome)
+    chroms = [r[0] for r in rows]
+    pos = np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    tab = AlleleTable(refs + alts)
+    n = len(rows)
+    for k, (shift, which) in enumerate(zip(g["shifts"], g["which"])):
+        la, lo = (tab.lengths[:n], tab.offsets[:n]) if which == "ref" else (tab.lengths[n:], tab.offsets[n:])
+        fwd = variant_descs(pg, chroms, pos, tab.lengths[:n], la, lo, int(shift), rc=False)
+        rc = variant_descs(pg, chroms, pos, tab.lengths[:n], la, lo, int(shift), rc=True)
+        ours = decode_descs(pg, np.concatenate([fwd, rc]), tab.codes)
+        want = np.unpackbits(g["packed"][k], axis=1)[:, :8000].reshape(2 * n, 4, 2000)
+        assert np.array_equal(ours, want), (shift, which)
+
+
+def test_descriptors_match_oracle_all_shifts(small_genome):
+    rows = GI.edge_variants(small_genome)
+    pg = PackedGenome.from_sequences(small_genome)
+    dg = O.DictGenome(small_genome)
+    chroms = [r[0] for r in rows]
+    pos = np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    for shift in O.SHIFTS_CHROMATIN(800):
+        descs, codes = chromatin_window_descs(pg, chroms, pos, refs, alts, shift)
+        ours = decode_descs(pg, descs, codes).reshape(len(rows), 4, 4, 2000)
+        seqs = [O.fetch_seqs(dg, c, int(p), r, a, shift=shift) for c, p, r, a in zip(chroms, pos, refs, alts)]
+        ref_enc = O.encode_seqs([s[0] for s in seqs])
+        alt_enc = O.encode_seqs([s[1] for s in seqs])
+        n = len(rows)
+        assert np.array_equal(ours[:, 0], ref_enc[:n]) and np.array_equal(ours[:, 1], ref_enc[n:])
+        assert np.array_equal(ours[:, 2], alt_enc[:n]) and np.array_equal(ours[:, 3], alt_enc[n:])
+    want = (sum(s[2] for s in [O.fetch_seqs(dg, c, int(p), r, a) for c, p, r, a in zip(chroms, pos, refs, alts)]),
+            sum(s[3] for s in [O.fetch_seqs(dg, c, int(p), r, a) for c, p, r, a in zip(chroms, pos, refs, alts)]),
+            len(rows))
+    assert allele_match_counts(pg, chroms, pos, refs, alts) == want
+
+
+def test_tss_windows_match_oracle(small_genome):
+    pg = PackedGenome.from_sequences(small_genome)
+    dg = O.DictGenome(small_genome)
+    shifts = list(range(-2000, 2000, 200))
+    descs = tss_descs(pg, ["chr1", "chr2"], [30000, 20000], [1, -1], shifts)
+    ours = decode_descs(pg, descs, np.zeros(1, np.uint8)).reshape(2, len(shifts), 2, 4, 2000)
+    for gi, (chrom, tss, strand) in enumerate([("chr1", 30000, 1), ("chr2", 20000, -1)]):
+        enc = O.encode_seqs(O.tss_windows(dg, chrom, tss, strand, shifts), concat_rc=False)
+        assert np.array_equal(ours[gi, :, 0], enc)
+        assert np.array_equal(ours[gi, :, 1], enc[:, ::-1, ::-1])
+
+
+def test_bad_allele_raises_keyerror():
+    with pytest.raises(KeyError):
+        encode_bases("ACGR")
+    assert list(encode_bases("AGCTNnH-acgt")) == [0, 1, 2, 3, 4, 4, 4, 4, 0, 2, 1, 3]
+
+
+def test_invalid_genome_char_detected():
+    from expecto_b200.windows import check_valid_bases
+    seq = "ACGT" * 2000
+    seq = seq[:5000] + "R" + seq[5001:]
+    pg = PackedGenome.from_sequences({"chr1": seq})
+    d_ok = tss_descs(pg, ["chr1"], [2000], [1], [0])
+    check_valid_bases(pg, d_ok)
+    d_bad = tss_descs(pg, ["chr1"], [5200], [1], [0])
+    with pytest.raises(KeyError):
+        check_valid_bases(pg, d_bad)
