@@ -100,6 +100,39 @@ struct bx_ctx {
   const uint32_t* bases2 = nullptr;
   const uint32_t* nmask = nullptr;
   int64_t n_bases = 0;
+  // per-stage CUDA-event timing (bx_ctx_profile): stage 0 = encode/im2col, 1..6 = conv1..6, 7 = fc1, 8 = fc2
+  bool prof_on = false;
+  struct ProfRec { int stage; cudaEvent_t e0, e1; };
+  std::vector<ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
+  double prof_ms[BX_NSTAGES] = {};
+  int64_t prof_cnt[BX_NSTAGES] = {};
+  // host-buffer pipeline (bx_*_host): copy streams, double-buffered staging
+  cudaStream_t s_comp = nullptr, s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_in[2] = {}, ev_comp[2] = {}, ev_out[2] = {};
+  void* stage_in[2] = {};
+  size_t stage_in_bytes = 0;
+  float* stage_out[2] = {};
+  size_t stage_out_bytes = 0;
+  float* probs_scratch = nullptr;
+  size_t probs_scratch_bytes = 0;
+};
+
+// RAII-ish stage timer: records an event pair around a stage when profiling is on.
+struct StageTimer {
+  bx_ctx* c; cudaStream_t st; cudaEvent_t e1 = nullptr;
+  StageTimer(bx_ctx* ctx, int stage, cudaStream_t s) : c(ctx), st(s) {
+    if (!c->prof_on) return;
+    cudaEvent_t ev[2];
+    for (int i = 0; i < 2; ++i) {
+      if (!c->prof_pool.empty()) { ev[i] = c->prof_pool.back(); c->prof_pool.pop_back(); }
+      else cudaEventCreate(&ev[i]);
+    }
+    cudaEventRecord(ev[0], st);
+    e1 = ev[1];
+    c->prof_recs.push_back({stage, ev[0], ev[1]});
+  }
+  ~StageTimer() { if (e1) cudaEventRecord(e1, st); }
 };
 
 static size_t act_rows(int i) { return i == 0 ? kLayers[0].pitch_in : kLayers[i - 1].pitch_out; }
@@ -238,9 +271,15 @@ static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
 
 // conv1..conv6, fc1, fc2 over n windows whose conv1 operand is already in act[0].
 static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st) {
-  for (int i = 0; i < 6; ++i)
+  for (int i = 0; i < 6; ++i) {
+    StageTimer t(c, 1 + i, st);
     if (int r = run_conv(c, i, n, st)) return r;
-  if (int r = run_fc1(c, n, st)) return r;
+  }
+  {
+    StageTimer t(c, 7, st);
+    if (int r = run_fc1(c, n, st)) return r;
+  }
+  StageTimer t(c, 8, st);
   return run_fc2(c, n, probs, st);
 }
 
@@ -300,6 +339,18 @@ int bx_ctx_destroy(bx_ctx* c) {
   cudaFree(c->wfc1); cudaFree(c->bfc1); cudaFree(c->wfc2); cudaFree(c->bfc2);
   for (int i = 0; i < 7; ++i) cudaFree(c->act[i]);
   cudaFree(c->acc1); cudaFree(c->hid);
+  for (int i = 0; i < 2; ++i) {
+    cudaFree(c->stage_in[i]); cudaFree(c->stage_out[i]);
+    if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
+    if (c->ev_comp[i]) cudaEventDestroy(c->ev_comp[i]);
+    if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
+  }
+  cudaFree(c->probs_scratch);
+  if (c->s_comp) cudaStreamDestroy(c->s_comp);
+  if (c->s_in) cudaStreamDestroy(c->s_in);
+  if (c->s_out) cudaStreamDestroy(c->s_out);
+  for (auto& r : c->prof_recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  for (auto e : c->prof_pool) cudaEventDestroy(e);
   delete c;
   return 0;
 }
@@ -382,6 +433,68 @@ int bx_encode_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t*
   return 0;
 }
 
+}  // extern "C"
+
+// One chunk (m <= cap windows): kernel 1 fused into the conv1 operand, then the network.
+static int forward_chunk_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int m,
+                                 float* probs_dev, cudaStream_t st) {
+  {
+    StageTimer t(c, 0, st);
+    if (c->dtype == BX_DTYPE_F16)
+      encode_im2col_kernel<__half><<<m, 256, 0, st>>>(descs_dev, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                      (__half*)c->act[0]);
+    else
+      encode_im2col_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(descs_dev, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                             (__nv_bfloat16*)c->act[0]);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
+  return run_network(c, m, probs_dev, st);
+}
+
+static int forward_chunk_onehot(bx_ctx* c, const uint8_t* x, int m, float* probs_dev, cudaStream_t st) {
+  {
+    StageTimer t(c, 0, st);
+    if (c->dtype == BX_DTYPE_F16)
+      onehot_im2col_kernel<__half><<<m, 256, 0, st>>>(x, (__half*)c->act[0]);
+    else
+      onehot_im2col_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(x, (__nv_bfloat16*)c->act[0]);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
+  return run_network(c, m, probs_dev, st);
+}
+
+// Lazily created streams / events / staging buffers of the host-buffer entry points.
+static int ensure_pipe(bx_ctx* c, size_t in_bytes, size_t out_bytes, size_t probs_bytes) {
+  if (!c->s_comp) {
+    CK(cudaStreamCreateWithFlags(&c->s_comp, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      CK(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&c->ev_comp[i], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&c->ev_out[i], cudaEventDisableTiming));
+    }
+  }
+  if (in_bytes > c->stage_in_bytes) {
+    for (int i = 0; i < 2; ++i) { cudaFree(c->stage_in[i]); c->stage_in[i] = nullptr; CK(cudaMalloc(&c->stage_in[i], in_bytes)); }
+    c->stage_in_bytes = in_bytes;
+  }
+  if (out_bytes > c->stage_out_bytes) {
+    for (int i = 0; i < 2; ++i) { cudaFree(c->stage_out[i]); c->stage_out[i] = nullptr; CK(cudaMalloc(&c->stage_out[i], out_bytes)); }
+    c->stage_out_bytes = out_bytes;
+  }
+  if (probs_bytes > c->probs_scratch_bytes) {
+    cudaFree(c->probs_scratch); c->probs_scratch = nullptr;
+    CK(cudaMalloc(&c->probs_scratch, probs_bytes));
+    c->probs_scratch_bytes = probs_bytes;
+  }
+  return 0;
+}
+
+extern "C" {
+
 int bx_forward_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n,
                        float* probs_dev, void* stream) {
   if (!c || !descs_dev || !alleles_dev || !probs_dev || n < 0) return fail(BX_E_ARG, "invalid arguments");
@@ -391,15 +504,8 @@ int bx_forward_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t
   cudaStream_t st = (cudaStream_t)stream;
   for (int off = 0; off < n; off += c->cap) {
     const int m = std::min(c->cap, n - off);
-    if (c->dtype == BX_DTYPE_F16)
-      encode_im2col_kernel<__half><<<m, 256, 0, st>>>(descs_dev + off, alleles_dev, c->bases2, c->nmask, c->n_bases,
-                                                      (__half*)c->act[0]);
-    else
-      encode_im2col_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(descs_dev + off, alleles_dev, c->bases2, c->nmask,
-                                                             c->n_bases, (__nv_bfloat16*)c->act[0]);
-    g_launches++;
-    CK(cudaGetLastError());
-    if (int r = run_network(c, m, probs_dev + (size_t)off * BX_FEATURES, st)) return r;
+    if (int r = forward_chunk_windows(c, descs_dev + off, alleles_dev, m, probs_dev + (size_t)off * BX_FEATURES, st))
+      return r;
   }
   return 0;
 }
@@ -411,15 +517,135 @@ int bx_forward_onehot(bx_ctx* c, const uint8_t* onehot_dev, int n, float* probs_
   cudaStream_t st = (cudaStream_t)stream;
   for (int off = 0; off < n; off += c->cap) {
     const int m = std::min(c->cap, n - off);
-    const uint8_t* x = onehot_dev + (size_t)off * 4 * BX_WINDOW;
-    if (c->dtype == BX_DTYPE_F16)
-      onehot_im2col_kernel<__half><<<m, 256, 0, st>>>(x, (__half*)c->act[0]);
-    else
-      onehot_im2col_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(x, (__nv_bfloat16*)c->act[0]);
-    g_launches++;
-    CK(cudaGetLastError());
-    if (int r = run_network(c, m, probs_dev + (size_t)off * BX_FEATURES, st)) return r;
+    if (int r = forward_chunk_onehot(c, onehot_dev + (size_t)off * 4 * BX_WINDOW, m,
+                                     probs_dev + (size_t)off * BX_FEATURES, st))
+      return r;
   }
+  return 0;
+}
+
+int bx_forward_onehot_host(bx_ctx* c, const uint8_t* onehot_host, int n, float* probs_host) {
+  if (!c || !onehot_host || !probs_host || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  CK(cudaSetDevice(c->device));
+  const size_t in_chunk = (size_t)c->cap * 4 * BX_WINDOW, out_chunk = (size_t)c->cap * BX_FEATURES * sizeof(float);
+  if (int r = ensure_pipe(c, in_chunk, out_chunk, 0)) return r;
+  int i = 0;
+  for (int off = 0; off < n; off += c->cap, ++i) {
+    const int m = std::min(c->cap, n - off), b = i & 1;
+    // H2D of chunk i overlaps the compute of chunk i-1; its staging buffer was last read by chunk i-2.
+    CK(cudaStreamWaitEvent(c->s_in, c->ev_comp[b], 0));
+    CK(cudaMemcpyAsync(c->stage_in[b], onehot_host + (size_t)off * 4 * BX_WINDOW, (size_t)m * 4 * BX_WINDOW,
+                       cudaMemcpyHostToDevice, c->s_in));
+    CK(cudaEventRecord(c->ev_in[b], c->s_in));
+    CK(cudaStreamWaitEvent(c->s_comp, c->ev_in[b], 0));
+    CK(cudaStreamWaitEvent(c->s_comp, c->ev_out[b], 0));
+    if (int r = forward_chunk_onehot(c, (const uint8_t*)c->stage_in[b], m, c->stage_out[b], c->s_comp)) return r;
+    CK(cudaEventRecord(c->ev_comp[b], c->s_comp));
+    CK(cudaStreamWaitEvent(c->s_out, c->ev_comp[b], 0));
+    CK(cudaMemcpyAsync(probs_host + (size_t)off * BX_FEATURES, c->stage_out[b], (size_t)m * BX_FEATURES * sizeof(float),
+                       cudaMemcpyDeviceToHost, c->s_out));
+    CK(cudaEventRecord(c->ev_out[b], c->s_out));
+  }
+  CK(cudaStreamSynchronize(c->s_out));
+  CK(cudaStreamSynchronize(c->s_comp));
+  return 0;
+}
+
+int bx_chromatin_shift_host(bx_ctx* c, const bx_window_desc* descs_host, const uint8_t* alleles_host,
+                            int64_t n_alleles, int n_var, int average, float* ref_host, float* alt_host,
+                            float* diff_host) {
+  if (!c || !descs_host || !ref_host || !alt_host || !diff_host || n_var < 0 || n_alleles < 0 ||
+      (n_alleles > 0 && !alleles_host))
+    return fail(BX_E_ARG, "invalid arguments");
+  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  if (c->cap < 4) return fail(BX_E_ARG, "context capacity must be >= 4 windows");
+  CK(cudaSetDevice(c->device));
+  const int vcap = c->cap / 4;  // variants per chunk (4 windows each)
+  const size_t rows_chunk = (size_t)(average ? 1 : 2) * vcap;
+  const size_t out_chunk = 3 * rows_chunk * BX_FEATURES * sizeof(float);
+  const size_t in_chunk = (size_t)4 * vcap * sizeof(bx_window_desc);
+  if (int r = ensure_pipe(c, in_chunk, out_chunk, (size_t)4 * vcap * BX_FEATURES * sizeof(float))) return r;
+  // allele codes: one upload for the whole call (descriptor aoff values index this table)
+  uint8_t* alleles_dev = nullptr;
+  CK(cudaMalloc(&alleles_dev, (size_t)std::max<int64_t>(n_alleles, 1)));
+  if (n_alleles > 0) CK(cudaMemcpyAsync(alleles_dev, alleles_host, (size_t)n_alleles, cudaMemcpyHostToDevice, c->s_in));
+  CK(cudaStreamSynchronize(c->s_in));
+  const size_t F = BX_FEATURES;
+  int i = 0, rc = 0;
+  for (int v0 = 0; v0 < n_var && rc == 0; v0 += vcap, ++i) {
+    const int m = std::min(vcap, n_var - v0), b = i & 1;
+    const size_t rows = (size_t)(average ? 1 : 2) * m;
+    float* o_ref = c->stage_out[b];
+    float* o_alt = o_ref + rows * F;
+    float* o_diff = o_alt + rows * F;
+    auto step = [&]() -> int {
+      CK(cudaStreamWaitEvent(c->s_in, c->ev_comp[b], 0));
+      CK(cudaMemcpyAsync(c->stage_in[b], descs_host + (size_t)4 * v0, (size_t)4 * m * sizeof(bx_window_desc),
+                         cudaMemcpyHostToDevice, c->s_in));
+      CK(cudaEventRecord(c->ev_in[b], c->s_in));
+      CK(cudaStreamWaitEvent(c->s_comp, c->ev_in[b], 0));
+      CK(cudaStreamWaitEvent(c->s_comp, c->ev_out[b], 0));
+      if (int r = forward_chunk_windows(c, (const bx_window_desc*)c->stage_in[b], alleles_dev, 4 * m, c->probs_scratch,
+                                        c->s_comp))
+        return r;
+      {
+        StageTimer t(c, 9, c->s_comp);
+        if (average)
+          chromatin_outputs_avg_kernel<<<m, 256, 0, c->s_comp>>>(c->probs_scratch, m, o_ref, o_alt, o_diff);
+        else
+          chromatin_outputs_kernel<<<m, 256, 0, c->s_comp>>>(c->probs_scratch, m, o_ref, o_alt, o_diff);
+        g_launches++;
+        CK(cudaGetLastError());
+      }
+      CK(cudaEventRecord(c->ev_comp[b], c->s_comp));
+      CK(cudaStreamWaitEvent(c->s_out, c->ev_comp[b], 0));
+      float* dst[3] = {ref_host, alt_host, diff_host};
+      const float* src[3] = {o_ref, o_alt, o_diff};
+      for (int k = 0; k < 3; ++k) {
+        // forward-strand rows land at v, reverse-complement rows at n_var + v (chromatin.py:170-171 row order)
+        CK(cudaMemcpyAsync(dst[k] + (size_t)v0 * F, src[k], (size_t)m * F * sizeof(float), cudaMemcpyDeviceToHost,
+                           c->s_out));
+        if (!average)
+          CK(cudaMemcpyAsync(dst[k] + ((size_t)n_var + v0) * F, src[k] + (size_t)m * F, (size_t)m * F * sizeof(float),
+                             cudaMemcpyDeviceToHost, c->s_out));
+      }
+      CK(cudaEventRecord(c->ev_out[b], c->s_out));
+      return 0;
+    };
+    rc = step();
+  }
+  cudaStreamSynchronize(c->s_out);
+  cudaError_t e = cudaStreamSynchronize(c->s_comp);
+  cudaFree(alleles_dev);
+  if (rc) return rc;
+  if (e != cudaSuccess) return fail(BX_E_CUDA, "pipeline failed: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+int bx_ctx_profile(bx_ctx* c, int enable) {
+  if (!c) return fail(BX_E_ARG, "ctx is null");
+  c->prof_on = enable != 0;
+  return 0;
+}
+
+int bx_ctx_profile_read(bx_ctx* c, double* ms_out, int64_t* count_out, int reset) {
+  if (!c || !ms_out || !count_out) return fail(BX_E_ARG, "null argument");
+  CK(cudaSetDevice(c->device));
+  for (auto& r : c->prof_recs) {
+    CK(cudaEventSynchronize(r.e1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, r.e0, r.e1));
+    c->prof_ms[r.stage] += ms;
+    c->prof_cnt[r.stage] += 1;
+    c->prof_pool.push_back(r.e0);
+    c->prof_pool.push_back(r.e1);
+  }
+  c->prof_recs.clear();
+  for (int i = 0; i < BX_NSTAGES; ++i) { ms_out[i] = c->prof_ms[i]; count_out[i] = c->prof_cnt[i]; }
+  if (reset)
+    for (int i = 0; i < BX_NSTAGES; ++i) { c->prof_ms[i] = 0; c->prof_cnt[i] = 0; }
   return 0;
 }
 

@@ -136,6 +136,52 @@ class BelugaEngine:
 
     __call__ = forward_onehot
 
+    # ------------------------------------------------------------------ host-buffer entry points
+    def forward_onehot_host(self, onehot: np.ndarray | torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        """``model.forward`` as chromatin.py:266-270 uses it, host to host: ``onehot`` uint8/bool [n,4,2000] in
+        HOST memory (pinned for asynchronous copies) -> fp32 [n,2002] in pinned host memory.  H2D, compute and
+        D2H of consecutive chunks overlap inside the library."""
+        x = torch.from_numpy(onehot) if isinstance(onehot, np.ndarray) else onehot
+        if x.is_cuda:
+            raise ValueError("forward_onehot_host takes host memory; use forward_onehot for device tensors")
+        x = x.reshape(-1, 4, WINDOW)
+        if x.dtype == torch.bool:
+            x = x.view(torch.uint8)
+        if x.dtype != torch.uint8:
+            raise ValueError("onehot must be uint8/bool")
+        x = x.contiguous()
+        n = x.shape[0]
+        if out is None:
+            out = torch.empty((n, N_FEATURES), dtype=torch.float32, pin_memory=True)
+        check(lib().bx_forward_onehot_host(self._ctx, x.data_ptr(), n, out.data_ptr()))
+        return out
+
+    def chromatin_shift_host(self, descs: np.ndarray, alleles: np.ndarray, n_var: int, average: bool = False,
+                             out=None):
+        """One shift of chromatin.py:243-286 from host descriptors to host (pinned) ref/alt/diff arrays."""
+        descs = np.ascontiguousarray(descs)
+        assert descs.size == 4 * n_var and descs.dtype.itemsize == 40
+        alleles = np.ascontiguousarray(alleles, dtype=np.uint8)
+        rows = n_var if average else 2 * n_var
+        if out is None:
+            out = tuple(torch.empty((rows, N_FEATURES), dtype=torch.float32, pin_memory=True) for _ in range(3))
+        ref, alt, diff = out
+        check(lib().bx_chromatin_shift_host(self._ctx, descs.ctypes.data, alleles.ctypes.data if alleles.size else None,
+                                            alleles.size, n_var, 1 if average else 0, ref.data_ptr(), alt.data_ptr(),
+                                            diff.data_ptr()))
+        return ref, alt, diff
+
+    # ------------------------------------------------------------------ per-stage device timing
+    def profile(self, enable: bool = True) -> None:
+        check(lib().bx_ctx_profile(self._ctx, 1 if enable else 0))
+
+    def profile_read(self, reset: bool = True) -> dict[str, tuple[float, int]]:
+        """{stage: (summed ms, count)} measured with CUDA events around each stage's launches."""
+        ms = (C.c_double * _lib.NSTAGES)()
+        cnt = (C.c_int64 * _lib.NSTAGES)()
+        check(lib().bx_ctx_profile_read(self._ctx, ms, cnt, 1 if reset else 0))
+        return {name: (ms[i], cnt[i]) for i, name in enumerate(_lib.STAGE_NAMES)}
+
     def debug_activation(self, layer: int, n: int) -> torch.Tensor:
         """Internal activation after the last forward: [n, pitch, C] in the operand dtype (test hook)."""
         rows, cols = _ACT_SHAPES[layer]

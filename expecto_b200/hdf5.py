@@ -123,8 +123,10 @@ class H5Writer:
         row_elems = int(np.prod(shape[1:])) if len(shape) > 1 else 1
         if arr.size % row_elems or row0 * row_elems + arr.size > int(np.prod(shape)):
             raise ValueError("slab does not fit the dataset")
+        if arr.size == 0:
+            return
         self._f.seek(self.addr[name] + row0 * row_elems * 4)
-        self._f.write(memoryview(arr).cast("B"))
+        self._f.write(memoryview(arr.reshape(-1)).cast("B"))
 
     def write(self, name: str, arr: np.ndarray) -> None:
         if tuple(arr.shape) != self.shapes[name]:

@@ -27,6 +27,7 @@ extern "C" {
 #define BX_WINDOW 2000     /* Beluga input length, chromatin.py:35-36 */
 #define BX_FEATURES 2002   /* Beluga outputs, Beluga.py:45 */
 #define BX_NBASIS 10       /* decay bases, predict.py:88-109 */
+#define BX_NSTAGES 10      /* timed stages: 0 encode, 1..6 conv1..6, 7 fc1, 8 fc2, 9 ref/alt/diff outputs */
 
 /* One 2000-bp model input, described as  genome[g1 : g1+len1] + allele[aoff : aoff+alen] +
  * genome[g2 : g2+len2]  (positions past the total are all-zero columns).  This is the result of
@@ -79,6 +80,26 @@ int bx_forward_windows(bx_ctx* ctx, const bx_window_desc* descs_dev, const uint8
                        float* probs_dev, void* stream);
 /* Same, from an explicit one-hot uint8 [n,4,2000] (the tensor chromatin.py:267 feeds the model). */
 int bx_forward_onehot(bx_ctx* ctx, const uint8_t* onehot_dev, int n, float* probs_dev, void* stream);
+
+/* Host-buffer form of bx_forward_onehot — the call chromatin.py:266-270 makes per batch
+ * (torch.from_numpy(...).cuda() -> model.forward -> .cpu()): onehot_host uint8 [n,4,2000] and probs_host fp32
+ * [n,2002] are HOST memory (pinned memory makes the copies asynchronous).  Chunks of `capacity_windows` are
+ * pipelined over three streams (H2D of chunk i+1 and D2H of chunk i-1 overlap the compute of chunk i); the
+ * call returns when probs_host is complete. */
+int bx_forward_onehot_host(bx_ctx* ctx, const uint8_t* onehot_host, int n, float* probs_host);
+
+/* One iteration of chromatin.py:243-286 for n_var variants from HOST descriptors (4 per variant, order
+ * {ref fwd, ref rc, alt fwd, alt rc}) to HOST ref/alt/diff arrays: fp32 [2*n_var,2002] each (forward rows
+ * then reverse-complement rows, diff = alt - ref), or, with average != 0, the strand-averaged fp32
+ * [n_var,2002] predict.py:186-190 derives from them.  Same three-stream pipeline as above. */
+int bx_chromatin_shift_host(bx_ctx* ctx, const bx_window_desc* descs_host, const uint8_t* alleles_host,
+                            int64_t n_alleles, int n_var, int average, float* ref_host, float* alt_host,
+                            float* diff_host);
+
+/* Per-stage device timing with CUDA events on the launching stream (bench.py's roofline numbers).
+ * bx_ctx_profile_read fills ms_out[BX_NSTAGES] (summed milliseconds) and count_out[BX_NSTAGES] (launch groups). */
+int bx_ctx_profile(bx_ctx* ctx, int enable);
+int bx_ctx_profile_read(bx_ctx* ctx, double* ms_out, int64_t* count_out, int reset);
 
 /* Copy an internal activation (test hook): layer 0 = im2col one-hot, 1..6 = conv outputs, 7 = fc1 hidden.
  * Writes rows*cols 16-bit elements for n windows to dst_dev; returns the element count through *count. */
