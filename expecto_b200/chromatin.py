@@ -88,27 +88,29 @@ def variant_columns(vcf):
     return chroms, pos, refs, alts
 
 
-def predict_shift(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int, sink) -> None:
+def predict_shift(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int, sink, pinned=None) -> None:
     """One iteration of chromatin.py:243-286 for all variants.  ``sink(name, row0, array)`` receives
-    float32 row slabs of the [2N,2002] datasets (forward rows at v, reverse-complement rows at N+v)."""
+    float32 row slabs of the [2N,2002] datasets (forward rows at v, reverse-complement rows at N+v).
+    Each slab of ``gpu_batch`` variants goes through the library's three-stream host pipeline
+    (bx_chromatin_shift_host): descriptors H2D, kernel 1 + forward + diff, ref/alt/diff D2H."""
     import torch
 
-    from .engine import chromatin_outputs
     from .windows import check_valid_bases, chromatin_window_descs
 
     n = len(pos)
     for v0 in range(0, n, gpu_batch):
         v1 = min(n, v0 + gpu_batch)
+        m = v1 - v0
         descs, alleles = chromatin_window_descs(genome, chroms[v0:v1], pos[v0:v1], refs[v0:v1], alts[v0:v1], shift)
         check_valid_bases(genome, descs)
-        probs = engine.forward_windows(descs, alleles)
-        ref, alt, diff = chromatin_outputs(probs, v1 - v0)
-        m = v1 - v0
+        out = None
+        if pinned is not None:
+            out = tuple(t[:2 * m] for t in pinned)
+        ref, alt, diff = engine.chromatin_shift_host(descs, alleles, m, average=False, out=out)
         for name, t in (("diff", diff), ("ref", ref), ("alt", alt)):
-            h = t.cpu().numpy()
+            h = t.numpy()
             sink(name, v0, h[:m])
-            sink(name, n + v0, h[m:])
-        del probs, ref, alt, diff
+            sink(name, n + v0, h[m:2 * m])
     torch.cuda.synchronize(engine.device)
 
 
@@ -142,6 +144,9 @@ def run(args, engine=None, genome=None) -> dict:
         raise KeyError(f"contig(s) {missing} are not in the genome")  # pyfasta raises KeyError too
     n = len(pos)
     files, counters = [], None
+    import torch
+    gb = max(1, min(args.gpu_batch, n))
+    pinned = tuple(torch.empty((2 * gb, 2002), dtype=torch.float32, pin_memory=True) for _ in range(3))
     for shift in shift_list(args.maxshift):
         if shift == 0:
             counters = allele_match_counts(genome, chroms, pos, refs, alts)
@@ -160,7 +165,7 @@ def run(args, engine=None, genome=None) -> dict:
                 if up is not None and name == "diff":
                     up.write_rows("pred", row0, arr)
 
-            predict_shift(engine, genome, chroms, pos, refs, alts, shift, args.gpu_batch, sink)
+            predict_shift(engine, genome, chroms, pos, refs, alts, shift, gb, sink, pinned)
             if up is not None:
                 up.close()
         files.append(path)

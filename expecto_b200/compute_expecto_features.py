@@ -1,0 +1,119 @@
+"""Drop-in for the reference's ``compute_expecto_features.py`` (same CLI, same ``.npy`` out) on B200s.
+
+    python -m expecto_b200.compute_expecto_features resources/geneanno.csv tss.tsv [-o out_dir]
+
+Reference behaviour reproduced (file:line into /root/reference/compute_expecto_features.py):
+  * arguments ``annoFile tss_file --windowsize -o --cuda``                               :18-27
+  * annoFile parsed by ``line.rstrip().split(",")`` (7 columns, header skipped)            :51-54
+  * optional per-gene TSS override from ``tss_file`` (strand taken from that table)       :43-44,55-69
+  * 200 shifts -20000..19800, window ``tss + shift*strand - 999 .. + 1000``, forward and
+    ``[:, ::-1, ::-1]`` predictions averaged, ``pos_weights[10,200]`` reduction            :88-124
+  * ``{out}/Xreducedall.2002.representative_tss_top.npy`` float64 [n_genes, 20020]         :126-128
+The hg38->hg19 conversion (:45,58-66) needs the third-party ``liftover`` package and chain files that are not
+available offline: rows of ``tss_file`` that would trigger it are refused unless ``--tss_is_hg19`` declares
+their coordinates already lifted.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import numpy as np
+
+
+def build_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(description="Compute ExPecto chromatin features for TSS list")
+    p.add_argument("annoFile")
+    p.add_argument("tss_file")
+    p.add_argument("--windowsize", action="store", dest="windowsize", type=int, default=2000)
+    p.add_argument("-o", dest="out_dir", type=str, default="temp_compute_expecto_features")
+    p.add_argument("--cuda", action="store_true", help="accepted for compatibility (always on)")
+    # extensions
+    p.add_argument("--genome", default="./resources/hg19.fa")
+    p.add_argument("--weights", default="./resources/deepsea.beluga.pth")
+    p.add_argument("--dtype", default="f16", choices=["f16", "bf16"])
+    p.add_argument("--device", type=int, default=0)
+    p.add_argument("--genes_per_batch", type=int, default=32, help="genes per GPU batch (x400 windows)")
+    p.add_argument("--tss_is_hg19", action="store_true", help="tss_file coordinates are already hg19 (no liftover)")
+    return p
+
+
+def read_genes(anno_file: str, tss_file: str, tss_is_hg19: bool = False):
+    """compute_expecto_features.py:43-69 -> list of (gene_id, chrom, tss, strand +-1)."""
+    import pandas as pd
+
+    tss_df = pd.read_csv(tss_file, sep="\t", index_col=0).set_index("ens_id")
+    genes, found = [], 0
+    for i, line in enumerate(open(anno_file)):
+        if i == 0:
+            continue
+        gene_id, _, chrom, strand, _, rep_tss, _ = line.rstrip().split(",")
+        if gene_id in tss_df.index:
+            found += 1
+            chrom_new, tss_new, strand, _, is_default = tss_df.loc[gene_id]
+            if not is_default:
+                if not tss_is_hg19:
+                    raise NotImplementedError(
+                        f"gene {gene_id}: the TSS override needs an hg38->hg19 liftover (third-party `liftover` + chain "
+                        "files, unavailable offline); pre-lift the table and pass --tss_is_hg19")
+                chrom, rep_tss = chrom_new, tss_new
+        genes.append((gene_id, chrom, int(rep_tss), 1 if strand == "+" else -1))
+    print(f"Found {found} genes in geneAnno file that match a TSS in provided TSS file...")
+    return genes
+
+
+def gene_features(engine, genome, genes, shifts, weights, genes_per_batch: int = 32) -> np.ndarray:
+    """float64 [len(genes), 20020] for (id, chrom, tss, strand) tuples — the loop at :105-124, batched."""
+    import torch
+
+    from .transform import decay_transform_fixed
+    from .windows import check_valid_bases, tss_descs
+
+    S = len(shifts)
+    out = np.empty((len(genes), 10 * 2002), dtype=np.float64)
+    no_alleles = np.zeros(1, dtype=np.uint8)
+    for g0 in range(0, len(genes), genes_per_batch):
+        part = genes[g0:g0 + genes_per_batch]
+        descs = tss_descs(genome, [g[1] for g in part], [g[2] for g in part], [g[3] for g in part], shifts)
+        check_valid_bases(genome, descs)
+        probs = engine.forward_windows(descs, no_alleles).view(len(part), S, 2, 2002)
+        feats = decay_transform_fixed(probs, weights)
+        out[g0:g0 + len(part)] = feats.cpu().numpy()
+        del probs, feats
+    torch.cuda.synchronize(engine.device)
+    return out
+
+
+def run(args, engine=None, genome=None) -> str:
+    from .genome import PackedGenome
+    from .transform import TSS_SHIFTS, fixed_pos_weights
+
+    if args.windowsize != 2000:
+        raise ValueError("Beluga's architecture fixes --windowsize at 2000 (Beluga.py:43)")
+    os.makedirs(args.out_dir, exist_ok=True)
+    if genome is None:
+        genome = PackedGenome.from_fasta(args.genome)
+    if engine is None:
+        from .engine import BelugaEngine
+        engine = BelugaEngine(args.device, dtype=args.dtype, capacity=4096)
+        engine.load_weights_file(args.weights)
+    if engine._genome is not genome:
+        engine.set_genome(genome)
+    genes = read_genes(args.annoFile, args.tss_file, args.tss_is_hg19)
+    missing = sorted({g[1] for g in genes if g[1] not in genome.offsets})
+    if missing:
+        raise KeyError(f"contig(s) {missing} are not in the genome")
+    feats = gene_features(engine, genome, genes, TSS_SHIFTS, fixed_pos_weights(TSS_SHIFTS), args.genes_per_batch)
+    path = f"{args.out_dir}/Xreducedall.2002.representative_tss_top"
+    np.save(path, feats)
+    return path + ".npy"
+
+
+def main(argv=None) -> int:
+    run(build_parser().parse_args(argv))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

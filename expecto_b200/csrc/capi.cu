@@ -184,7 +184,7 @@ static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void
   BX_CASE(8, 240, EPI_BIAS_RELU);
   BX_CASE(8, 240, EPI_POOL4_BIAS_RELU);
   BX_CASE(8, 160, EPI_BIAS_RELU);
-  BX_CASE(1, 256, EPI_ATOMIC_F32);
+  BX_CASE(1, 256, EPI_PARTIAL_F32);
   BX_CASE(1, 256, EPI_BIAS_SIGMOID);
 #undef BX_CASE
   return fail(BX_E_ARG, "no kernel instance for taps=%d block_n=%d epi=%d", taps, bn, epi);
@@ -222,35 +222,39 @@ static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st) {
 }
 
 template <typename T>
-static int run_fc1_finalize(bx_ctx* c, int n, cudaStream_t st) {
+static int run_fc1_finalize(bx_ctx* c, int n, int k_splits, size_t split_stride, cudaStream_t st) {
   const size_t total = (size_t)n * 2048;
-  fc1_finalize_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(c->acc1, c->bfc1, (T*)c->hid, total);
+  fc1_finalize_kernel<T><<<(unsigned)((total / 4 + 255) / 256), 256, 0, st>>>(c->acc1, k_splits, split_stride, c->bfc1,
+                                                                             (T*)c->hid, total);
   g_launches++;
   CK(cudaGetLastError());
   return 0;
 }
 
+// fc1 always splits K into the same kFc1Splits slices, whatever the batch: the fp32 summation order of every
+// output is then independent of batch size and position (bit-identical results across batchings).
+constexpr int kFc1Splits = 8;
+static size_t fc1_scratch_rows(int cap) { return (size_t)cap * kFc1Splits; }
+
 static int run_fc1(bx_ctx* c, int n, cudaStream_t st) {
-  // fc1: [n, 67840] x [2048, 67840]^T, split-K partial sums reduced with fp32 atomics
-  CK(cudaMemsetAsync(c->acc1, 0, (size_t)n * 2048 * sizeof(float), st));
+  // fc1: [n, 67840] x [2048, 67840]^T; each K slice writes its own fp32 partial and the finaliser adds the
+  // slices in index order (deterministic, no atomics).
   GemmParams p = {};
   p.m_rows = n;
   p.k_valid = 67840;
   p.n_total = 2048;
   p.k_blocks = 67840 / 64;
-  const int m_tiles = (n + 128 * c->cg - 1) / (128 * c->cg);
-  const int clusters = c->num_sms / c->cg;
-  int ks = (3 * clusters + m_tiles * 8 - 1) / (m_tiles * 8);
-  ks = std::max(1, std::min(ks, 20));
-  p.kb_per_split = (p.k_blocks + ks - 1) / ks;
+  p.kb_per_split = (p.k_blocks + kFc1Splits - 1) / kFc1Splits;
   p.k_splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+  p.split_stride = (long long)n * 2048;
   p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
   p.ld_out = 2048;
   p.n_store = 2048;
   p.bias = nullptr;
   p.out = c->acc1;
-  if (int r = launch_gemm(c, 1, 256, EPI_ATOMIC_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st)) return r;
-  return (c->dtype == BX_DTYPE_F16) ? run_fc1_finalize<__half>(c, n, st) : run_fc1_finalize<__nv_bfloat16>(c, n, st);
+  if (int r = launch_gemm(c, 1, 256, EPI_PARTIAL_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st)) return r;
+  return (c->dtype == BX_DTYPE_F16) ? run_fc1_finalize<__half>(c, n, p.k_splits, (size_t)p.split_stride, st)
+                                    : run_fc1_finalize<__nv_bfloat16>(c, n, p.k_splits, (size_t)p.split_stride, st);
 }
 
 static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
@@ -324,7 +328,7 @@ int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx
     }
     cudaMemset(c->act[i], 0, bytes);
   }
-  if (cudaMalloc(&c->acc1, cap * 2048 * 4) != cudaSuccess || cudaMalloc(&c->hid, cap * 2048 * 2) != cudaSuccess) {
+  if (cudaMalloc(&c->acc1, fc1_scratch_rows(capacity_windows) * 2048 * 4) != cudaSuccess || cudaMalloc(&c->hid, cap * 2048 * 2) != cudaSuccess) {
     bx_ctx_destroy(c);
     return fail(BX_E_CUDA, "cudaMalloc of fc scratch failed");
   }
@@ -422,9 +426,10 @@ int bx_ctx_set_genome(bx_ctx* c, const uint32_t* bases2_dev, const uint32_t* nma
 
 int bx_encode_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n,
                       uint8_t* out_dev, void* stream) {
-  if (!c || !descs_dev || !alleles_dev || !out_dev || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n == 0) return 0;  // empty input: nothing to do, buffers may be null
+  if (!descs_dev || !alleles_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
-  if (n == 0) return 0;
   CK(cudaSetDevice(c->device));
   encode_onehot_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(descs_dev, alleles_dev, c->bases2, c->nmask, c->n_bases,
                                                              out_dev);
@@ -497,7 +502,9 @@ extern "C" {
 
 int bx_forward_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n,
                        float* probs_dev, void* stream) {
-  if (!c || !descs_dev || !alleles_dev || !probs_dev || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n == 0) return 0;
+  if (!descs_dev || !alleles_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
   CK(cudaSetDevice(c->device));
@@ -511,7 +518,9 @@ int bx_forward_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t
 }
 
 int bx_forward_onehot(bx_ctx* c, const uint8_t* onehot_dev, int n, float* probs_dev, void* stream) {
-  if (!c || !onehot_dev || !probs_dev || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n == 0) return 0;
+  if (!onehot_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
   CK(cudaSetDevice(c->device));
   cudaStream_t st = (cudaStream_t)stream;
@@ -525,7 +534,9 @@ int bx_forward_onehot(bx_ctx* c, const uint8_t* onehot_dev, int n, float* probs_
 }
 
 int bx_forward_onehot_host(bx_ctx* c, const uint8_t* onehot_host, int n, float* probs_host) {
-  if (!c || !onehot_host || !probs_host || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (!c || n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n == 0) return 0;
+  if (!onehot_host || !probs_host) return fail(BX_E_ARG, "invalid arguments");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
   CK(cudaSetDevice(c->device));
   const size_t in_chunk = (size_t)c->cap * 4 * BX_WINDOW, out_chunk = (size_t)c->cap * BX_FEATURES * sizeof(float);
@@ -555,8 +566,9 @@ int bx_forward_onehot_host(bx_ctx* c, const uint8_t* onehot_host, int n, float* 
 int bx_chromatin_shift_host(bx_ctx* c, const bx_window_desc* descs_host, const uint8_t* alleles_host,
                             int64_t n_alleles, int n_var, int average, float* ref_host, float* alt_host,
                             float* diff_host) {
-  if (!c || !descs_host || !ref_host || !alt_host || !diff_host || n_var < 0 || n_alleles < 0 ||
-      (n_alleles > 0 && !alleles_host))
+  if (!c || n_var < 0 || n_alleles < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n_var == 0) return 0;
+  if (!descs_host || !ref_host || !alt_host || !diff_host || (n_alleles > 0 && !alleles_host))
     return fail(BX_E_ARG, "invalid arguments");
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
@@ -671,8 +683,9 @@ int bx_debug_run_layer(bx_ctx* c, int layer, int n, float* probs_dev, void* stre
 
 int bx_chromatin_outputs(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,
                          void* stream) {
-  if (!probs_dev || !ref_dev || !alt_dev || !diff_dev || n_var < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n_var < 0) return fail(BX_E_ARG, "invalid arguments");
   if (n_var == 0) return 0;
+  if (!probs_dev || !ref_dev || !alt_dev || !diff_dev) return fail(BX_E_ARG, "invalid arguments");
   chromatin_outputs_kernel<<<n_var, 256, 0, (cudaStream_t)stream>>>(probs_dev, n_var, ref_dev, alt_dev, diff_dev);
   g_launches++;
   CK(cudaGetLastError());
@@ -681,8 +694,9 @@ int bx_chromatin_outputs(const float* probs_dev, int n_var, float* ref_dev, floa
 
 int bx_chromatin_outputs_avg(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,
                              void* stream) {
-  if (!probs_dev || !ref_dev || !alt_dev || !diff_dev || n_var < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n_var < 0) return fail(BX_E_ARG, "invalid arguments");
   if (n_var == 0) return 0;
+  if (!probs_dev || !ref_dev || !alt_dev || !diff_dev) return fail(BX_E_ARG, "invalid arguments");
   chromatin_outputs_avg_kernel<<<n_var, 256, 0, (cudaStream_t)stream>>>(probs_dev, n_var, ref_dev, alt_dev,
                                                                        diff_dev);
   g_launches++;
@@ -692,9 +706,9 @@ int bx_chromatin_outputs_avg(const float* probs_dev, int n_var, float* ref_dev, 
 
 int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, int n_genes, int n_shifts,
                              float* out_dev, void* stream) {
-  if (!probs_dev || !weights_dev || !out_dev || n_genes < 0 || n_shifts < 1 || n_shifts > 1024)
-    return fail(BX_E_ARG, "invalid arguments");
+  if (n_genes < 0 || n_shifts < 1 || n_shifts > 1024) return fail(BX_E_ARG, "invalid arguments");
   if (n_genes == 0) return 0;
+  if (!probs_dev || !weights_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
   const size_t smem = (size_t)(10 * n_shifts + (kTfSlices - 1) * 10 * kTfF) * sizeof(float);
   dim3 grid((kFeat + kTfF - 1) / kTfF, n_genes), block(kTfF, kTfSlices);
   decay_fixed_kernel<<<grid, block, smem, (cudaStream_t)stream>>>(probs_dev, weights_dev, n_shifts, out_dev);
@@ -705,9 +719,9 @@ int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, i
 
 int bx_decay_transform_variant(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
                                const int32_t* shifts_dev, int n, int n_shifts, float* out_dev, void* stream) {
-  if (!x_dev || !dist_dev || !strand_dev || !shifts_dev || !out_dev || n < 0 || n_shifts < 1 || n_shifts > 25)
-    return fail(BX_E_ARG, "invalid arguments (n_shifts must be 1..25)");
+  if (n < 0 || n_shifts < 1 || n_shifts > 25) return fail(BX_E_ARG, "invalid arguments (n_shifts must be 1..25)");
   if (n == 0) return 0;
+  if (!x_dev || !dist_dev || !strand_dev || !shifts_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
   dim3 grid((kFeat + 255) / 256, n);
   decay_variant_kernel<<<grid, 256, n_shifts * 10 * sizeof(float), (cudaStream_t)stream>>>(
       x_dev, dist_dev, strand_dev, shifts_dev, n, n_shifts, out_dev);

@@ -23,7 +23,8 @@ namespace bx {
 enum EpiKind : int {
   EPI_BIAS_RELU = 0,       // y = relu(acc + b) -> 16-bit, rows remapped pitch_in -> pitch_out
   EPI_POOL4_BIAS_RELU = 1, // y = max over 4 consecutive rows of relu(acc + b) -> 16-bit (MaxPool(1,4))
-  EPI_ATOMIC_F32 = 2,      // split-K partial sums: red.add.f32 into an fp32 [rows, ld_out] buffer
+  EPI_PARTIAL_F32 = 2,     // split-K partial sums: plain fp32 stores into slice ks of [k_splits, rows, ld_out]
+                           // (summed in fixed order by the finaliser: deterministic, no atomics)
   EPI_BIAS_SIGMOID = 3,    // y = sigmoid(acc + b) -> fp32
 };
 
@@ -33,7 +34,7 @@ struct GemmParams {
   int n_total;       // output channels (rows of B per tap)
   int m_tiles;       // ceil(m_rows / (128*CTA_GROUP))
   int n_chunks;      // n_total / BLOCK_N
-  int k_splits;      // split-K factor (EPI_ATOMIC_F32 only, else 1)
+  int k_splits;      // split-K factor (EPI_PARTIAL_F32 only, else 1)
   int k_blocks;      // ceil(k_valid / 64)
   int kb_per_split;  // ceil(k_blocks / k_splits)
   int pitch_in;      // rows per window in the accumulator row space
@@ -41,7 +42,8 @@ struct GemmParams {
   int l_store;       // output rows stored per window
   int ld_out;        // output leading dimension in elements
   int n_store;       // columns >= n_store are not stored
-  const float* bias; // [n_total] fp32 (unused for EPI_ATOMIC_F32)
+  long long split_stride;  // elements between split-K slices of the output (EPI_PARTIAL_F32)
+  const float* bias; // [n_total] fp32 (unused for EPI_PARTIAL_F32)
   void* out;
 };
 
@@ -305,12 +307,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (j == 3) { w0 = pk[6]; w1 = pk[7]; }
             if (valid) *reinterpret_cast<uint2*>(o + 4 * j) = make_uint2(w0, w1);
           }
-        } else if constexpr (EPI == EPI_ATOMIC_F32) {
-          float* o = reinterpret_cast<float*>(p.out) + obase + c * 16;
+        } else if constexpr (EPI == EPI_PARTIAL_F32) {
+          float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)ks * p.split_stride +
+                                                obase + c * 16);
           if (valid) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (n0 + c * 16 + i < p.n_store) atomicAdd(o + i, __uint_as_float(v[i]));
+            for (int i = 0; i < 4; ++i)
+              o[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                 __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
           }
         } else {  // EPI_BIAS_SIGMOID
           float* o = reinterpret_cast<float*>(p.out) + obase + c * 16;

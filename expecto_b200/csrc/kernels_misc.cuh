@@ -169,14 +169,24 @@ __global__ void prep_fc2_kernel(const float* __restrict__ src, T* __restrict__ d
   dst[idx] = to_t<T>((n < 2002 && k < 2003) ? src[(size_t)n * 2003 + k] : 0.f);
 }
 
-// fc1 finaliser: h = relu(acc + b1) -> 16-bit [n, 2048].
+// fc1 finaliser: h = relu(sum_ks part[ks] + b1) -> 16-bit [n, 2048]; slices are summed in a fixed order so
+// the result does not depend on scheduling (the split-K GEMM writes plain stores, no atomics).
 template <typename T>
-__global__ void fc1_finalize_kernel(const float* __restrict__ acc, const float* __restrict__ bias,
-                                    T* __restrict__ h, size_t total) {
-  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void fc1_finalize_kernel(const float* __restrict__ part, int k_splits, size_t split_stride,
+                                    const float* __restrict__ bias, T* __restrict__ h, size_t total) {
+  const size_t idx = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (idx >= total) return;
-  const float v = fmaxf(acc[idx] + bias[idx & 2047], 0.f);
-  h[idx] = to_t<T>(fminf(v, 65504.f));
+  float4 a = *reinterpret_cast<const float4*>(part + idx);
+  for (int k = 1; k < k_splits; ++k) {
+    const float4 b = *reinterpret_cast<const float4*>(part + (size_t)k * split_stride + idx);
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+  }
+  const float4 b4 = *reinterpret_cast<const float4*>(bias + (idx & 2047));
+  T* o = h + idx;
+  o[0] = to_t<T>(fminf(fmaxf(a.x + b4.x, 0.f), 65504.f));
+  o[1] = to_t<T>(fminf(fmaxf(a.y + b4.y, 0.f), 65504.f));
+  o[2] = to_t<T>(fminf(fmaxf(a.z + b4.z, 0.f), 65504.f));
+  o[3] = to_t<T>(fminf(fmaxf(a.w + b4.w, 0.f), 65504.f));
 }
 
 // ------------------------------------------------------------------ chromatin.py:281-286 outputs

@@ -1,0 +1,81 @@
+"""Host wrappers of kernel 4, the decay-weighted shift reductions (include/beluga_b200.h:
+bx_decay_transform_fixed / bx_decay_transform_variant).
+
+* fixed weights   — compute_expecto_features.py:88-101,123-124: ``pos_weights float64[10,S]`` applied to the
+  strand-averaged predictions of the S shifted windows of one gene;
+* per-variant weights — predict.py:87-136 (``compute_effects``): weights derived from each variant's signed
+  distance to the TSS and the gene strand, applied to the 9 per-shift diff/ref/alt matrices.
+
+Outputs are fp32 [n, 10*2002] with column index ``basis*2002 + feature`` as in the reference; callers widen to
+float64 where the reference stores float64 (the ``.npy`` of compute_expecto_features.py:128).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from ._lib import check, lib
+
+N_FEATURES = 2002
+N_BASIS = 10
+RATES = (0.01, 0.02, 0.05, 0.1, 0.2)
+TSS_SHIFTS = np.arange(-20000, 20000, 200)  # compute_expecto_features.py:88
+
+
+def fixed_pos_weights(shifts=TSS_SHIFTS) -> np.ndarray:
+    """float64 [10,S]: exp(-k|s|/200) masked to s<=0 (first five) / s>=0 (last five),
+    compute_expecto_features.py:90-101."""
+    s = np.asarray(shifts, dtype=np.float64)
+    decay = np.stack([np.exp(-k * np.abs(s) / 200) for k in RATES])
+    return np.concatenate([decay * (s <= 0), decay * (s >= 0)], axis=0)
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def decay_transform_fixed(probs: torch.Tensor, weights, out: torch.Tensor | None = None) -> torch.Tensor:
+    """``probs`` fp32 CUDA [G,S,2,2002] (shift-major; forward then reverse-complement prediction);
+    ``weights`` [10,S] -> fp32 [G,20020] = sum_s w[k,s] * 0.5*(fwd+rc)[s,f]."""
+    if not probs.is_cuda or probs.dtype != torch.float32 or probs.dim() != 4 or probs.shape[2:] != (2, N_FEATURES):
+        raise ValueError("probs must be a CUDA float32 tensor [G,S,2,2002]")
+    G, S = probs.shape[:2]
+    w = torch.as_tensor(np.ascontiguousarray(np.asarray(weights, dtype=np.float32))).to(probs.device)
+    if tuple(w.shape) != (N_BASIS, S):
+        raise ValueError(f"weights must be [10,{S}]")
+    probs = probs.contiguous()
+    if out is None:
+        out = torch.empty((G, N_BASIS * N_FEATURES), dtype=torch.float32, device=probs.device)
+    check(lib().bx_decay_transform_fixed(probs.data_ptr(), w.data_ptr(), G, S, out.data_ptr(), _stream(probs)))
+    return out
+
+
+def chromatin_shifts(maxshift: int = 800) -> list[int]:
+    return [0] + list(range(-200, -maxshift - 1, -200)) + list(range(200, maxshift + 1, 200))  # predict.py:173
+
+
+def decay_transform_variant(x: torch.Tensor, dist, strand, shifts=None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """``x`` fp32 CUDA [S,n,2002] (one matrix per shift, in ``shifts`` order); ``dist`` = variant - TSS
+    (predict.py:241 ``-gene[:, -1]``); ``strand`` array of '+'/'-' (or +1/-1) -> fp32 [n,20020]."""
+    if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 3 or x.shape[2] != N_FEATURES:
+        raise ValueError("x must be a CUDA float32 tensor [S,n,2002]")
+    S, n = x.shape[:2]
+    shifts = chromatin_shifts((S - 1) // 2 * 200) if shifts is None else list(shifts)
+    if len(shifts) != S:
+        raise ValueError("len(shifts) must equal x.shape[0]")
+    st = np.asarray(strand)
+    if st.dtype.kind in "USO":  # '+' / '-' as predict.py:90 compares them (pandas 3 hands back object arrays)
+        sgn = np.where(np.asarray([str(v) for v in st.ravel()]) == "+", 1, -1).astype(np.int8)
+    else:
+        sgn = np.where(st > 0, 1, -1).astype(np.int8)
+    d = torch.from_numpy(np.ascontiguousarray(np.asarray(dist, dtype=np.float64))).to(x.device)
+    sg = torch.from_numpy(np.ascontiguousarray(sgn)).to(x.device)
+    sh = torch.tensor(shifts, dtype=torch.int32, device=x.device)
+    if d.numel() != n or sg.numel() != n:
+        raise ValueError("dist/strand must have one entry per variant")
+    x = x.contiguous()
+    if out is None:
+        out = torch.empty((n, N_BASIS * N_FEATURES), dtype=torch.float32, device=x.device)
+    check(lib().bx_decay_transform_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), n, S,
+                                           out.data_ptr(), _stream(x)))
+    return out

@@ -67,5 +67,7 @@ def test_argument_errors(library):
     assert library.bx_ctx_create(0, 0, 3, 64, C.byref(ctx)) == _lib.BX_E_ARG
     assert library.bx_ctx_create(0, 0, 2, 0, C.byref(ctx)) == _lib.BX_E_ARG
     assert library.bx_chromatin_outputs(None, 1, None, None, None, None) == _lib.BX_E_ARG
+    assert library.bx_chromatin_outputs(None, 0, None, None, None, None) == 0   # empty input is a no-op
+    assert library.bx_chromatin_outputs(None, -1, None, None, None, None) == _lib.BX_E_ARG
     assert library.bx_decay_transform_fixed(None, None, 1, 200, None, None) == _lib.BX_E_ARG
     assert library.bx_version() >= 100

@@ -1,0 +1,145 @@
+"""Parity of the CUDA path (through the C ABI) with the reference-generated fixtures and the CPU oracle.
+
+Bars (BASELINE.json north_star): window extraction/encoding bit-exact; probabilities within 2e-3 absolute;
+Pearson >= 0.999 on ref-alt diffs; spatial features within 1e-4 relative (relative to the feature scale, with
+a floor, because the masked half of the basis is exactly 0 — SURVEY §8c)."""
+import numpy as np
+import pytest
+import torch
+
+from expecto_b200.genome import PackedGenome
+from expecto_b200.windows import AlleleTable, chromatin_window_descs, tss_descs, variant_descs
+from helpers import pearson
+from oracle import beluga_oracle as O
+from oracle import golden_inputs as GI
+
+pytestmark = pytest.mark.gpu
+PROB_TOL = 2e-3
+
+
+def _vcf_rows(text):
+    return [l.split("\t") for l in str(text).splitlines() if l and not l.startswith("#")]
+
+
+# ---------------------------------------------------------------- kernel 1: bit-exact
+def test_encode_kernel_bit_exact_vs_reference_fixture(engine, small_genome, golden):
+    g = golden("encode_golden.npz")
+    rows = [[r[0], int(r[1]), r[2], r[3], r[4]] for r in g["rows"]]
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    tab = AlleleTable([r[3] for r in rows] + [r[4] for r in rows])
+    n = len(rows)
+    for k, (shift, which) in enumerate(zip(g["shifts"], g["which"])):
+        la, lo = (tab.lengths[:n], tab.offsets[:n]) if which == "ref" else (tab.lengths[n:], tab.offsets[n:])
+        descs = np.concatenate([variant_descs(pg, chroms, pos, tab.lengths[:n], la, lo, int(shift), rc=rc)
+                                for rc in (False, True)])
+        ours = engine.encode_windows(descs, tab.codes).cpu().numpy()
+        want = np.unpackbits(g["packed"][k], axis=1)[:, :8000].reshape(2 * n, 4, 2000)
+        assert np.array_equal(ours, want), (shift, which)
+
+
+def test_encode_kernel_tss_windows_vs_oracle(engine, small_genome):
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    dg = O.DictGenome(small_genome)
+    shifts = list(range(-20000, 20000, 200))
+    descs = tss_descs(pg, ["chr1", "chr2"], [30000, 20000], [1, -1], shifts)
+    ours = engine.encode_windows(descs, np.zeros(1, np.uint8)).cpu().numpy().reshape(2, len(shifts), 2, 4, 2000)
+    for gi, (chrom, tss, strand) in enumerate([("chr1", 30000, 1), ("chr2", 20000, -1)]):
+        # chr2 is 40 kb long: windows beyond either end are N-padded here (the reference's behaviour there is
+        # accidental, SURVEY §7 hard part 2), so only compare shifts whose window lies inside the contig
+        ok = [i for i, s in enumerate(shifts)
+              if tss + s * strand - 999 >= 1 and tss + s * strand + 1000 <= len(small_genome[chrom])]
+        enc = O.encode_seqs(O.tss_windows(dg, chrom, tss, strand, [shifts[i] for i in ok]), concat_rc=False)
+        assert np.array_equal(ours[gi, ok, 0], enc)
+        assert np.array_equal(ours[gi, ok, 1], enc[:, ::-1, ::-1])
+
+
+def test_empty_inputs(engine, small_genome):
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    descs = tss_descs(pg, [], [], [], [0])
+    assert engine.encode_windows(descs, np.zeros(0, np.uint8)).shape == (0, 4, 2000)
+    assert engine.forward_windows(descs, np.zeros(0, np.uint8)).shape == (0, 2002)
+    ref, alt, diff = engine.chromatin_shift_host(descs, np.zeros(0, np.uint8), 0)
+    assert ref.shape == (0, 2002)
+
+
+# ---------------------------------------------------------------- kernels 2+3: Beluga forward
+def test_forward_matches_reference_beluga_fixture(engine, golden):
+    from expecto_b200 import synth
+    x = synth.random_onehot(GI.BELUGA_N, seed=GI.BELUGA_SEED)
+    x[0, :, 100:110] = 0
+    want = golden("beluga_golden.npz")["probs"]
+    ours = engine.forward_onehot(torch.from_numpy(x).cuda()).cpu().numpy()
+    assert ours.shape == want.shape and ours.dtype == np.float32
+    assert np.abs(ours - want).max() <= PROB_TOL
+    host = engine.forward_onehot_host(x).numpy()
+    assert np.array_equal(host, ours), "host-buffer pipeline must give the same bits as the device-buffer call"
+
+
+def test_fused_encode_equals_materialised_onehot(engine, small_genome):
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    rows = GI.edge_variants(small_genome)
+    descs, codes = chromatin_window_descs(pg, [r[0] for r in rows], np.array([r[1] for r in rows]),
+                                          [r[3] for r in rows], [r[4] for r in rows], 200)
+    onehot = engine.encode_windows(descs, codes)
+    a = engine.forward_windows(descs, codes).cpu().numpy()
+    b = engine.forward_onehot(onehot).cpu().numpy()
+    assert np.array_equal(a, b)
+
+
+def _run_cli(tmp_path, engine, genome_dict, vcf_text_rows, maxshift):
+    from expecto_b200 import chromatin
+    vcf = tmp_path / "in.vcf"
+    vcf.write_text("".join("\t".join(r) + "\n" for r in vcf_text_rows))
+    pg = PackedGenome.from_sequences(genome_dict)
+    args = chromatin.build_parser().parse_args([str(vcf), "--output_dir", str(tmp_path / "out"), "--maxshift",
+                                                str(maxshift)])
+    info = chromatin.run(args, engine=engine, genome=pg)
+    return info, tmp_path / "out"
+
+
+def test_chromatin_cli_cfg1_matches_reference_script(engine, cfg1_genome, golden, tmp_path, capsys):
+    """BASELINE configs[0]: chromatin.py on example/example.vcf, 9 shifts, vs the reference subprocess run."""
+    from expecto_b200 import hdf5
+    g = golden("chromatin_cfg1_golden.npz")
+    rows = _vcf_rows(g["snps_hg19_vcf"])
+    info, out = _run_cli(tmp_path, engine, cfg1_genome, rows, 800)
+    assert info["n_variants"] == 10 and list(info["counters"]) == list(g["counters"])
+    printed = capsys.readouterr().out
+    assert "Number of variants with reference allele matched with reference genome: %d" % g["counters"][0] in printed
+    assert (out / "snps_hg19.vcf").read_text() == str(g["snps_hg19_vcf"])
+    shifts = O.SHIFTS_CHROMATIN(800)
+    assert [p.rsplit("/", 1)[1] for p in info["files"]] == [f"snps.shift_{s}.diff.h5" for s in shifts]
+    for si, s in enumerate(shifts):
+        with hdf5.File(str(out / f"snps.shift_{s}.diff.h5")) as f:
+            d, r, a = (np.asarray(f[k]) for k in ("diff", "ref", "alt"))
+        assert d.shape == r.shape == a.shape == (20, 2002) and d.dtype == np.float32
+        assert np.array_equal(d, a - r)
+        # row sums of 2002 probabilities pin every shift (fixtures for all 9 would be 9x larger)
+        for di, arr in enumerate((d, r, a)):
+            assert np.abs(arr.astype(np.float64).sum(axis=1) - g["row_sums"][si, di]).max() <= 2002 * 2e-4
+        if f"ref_{s}" in g.files:
+            assert np.abs(r - g[f"ref_{s}"]).max() <= PROB_TOL
+            assert np.abs(a - g[f"alt_{s}"]).max() <= PROB_TOL
+            want = g[f"alt_{s}"] - g[f"ref_{s}"]
+            assert pearson(d, want) >= 0.999, s
+            assert np.abs(d - want).max() <= 2 * PROB_TOL
+
+
+def test_chromatin_cli_edge_vcf_matches_reference_script(engine, cfg1_genome, golden, tmp_path):
+    """Indels (incl. a 120-bp deletion), ref mismatch, lower-case alleles, un-prefixed and filtered contigs."""
+    from expecto_b200 import hdf5
+    g = golden("chromatin_edge_golden.npz")
+    rows = [[str(x) for x in r] for r in g["rows"]]
+    info, out = _run_cli(tmp_path, engine, cfg1_genome, rows, 200)
+    assert info["n_variants"] == 6 and list(info["counters"]) == list(g["counters"])
+    for s in (0, -200, 200):
+        with hdf5.File(str(out / f"snps.shift_{s}.diff.h5")) as f:
+            d, r, a = (np.asarray(f[k]) for k in ("diff", "ref", "alt"))
+        assert r.shape == (12, 2002)
+        assert np.abs(r - g[f"ref_{s}"]).max() <= PROB_TOL and np.abs(a - g[f"alt_{s}"]).max() <= PROB_TOL
+        assert pearson(d, g[f"alt_{s}"] - g[f"ref_{s}"]) >= 0.999
