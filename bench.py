@@ -148,8 +148,9 @@ def run_reference(args) -> int:
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"Beluga forward, batch sweep point B={args.batch} per GPU (BASELINE configs[1]); "
-                               f"CPU arm times a bounded sample of {b} windows per step"},
+        "config": {"workload": f"Beluga forward over {args.batch} synthetic 2000-bp one-hot windows per GPU per step "
+                               f"(BASELINE configs[1] batch sweep point B={args.batch}), calibrated random-init weights",
+                   "sample": f"CPU arm times a bounded sample of {b} windows per step (the reference's default batch)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -257,7 +258,8 @@ def run_gpu(args) -> int:
     tpath = os.path.join(ROOT, "profiles", "dram_traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(f"{top}@{chunk}")
+            per_window = json.load(open(tpath))["per_window_bytes"].get(top)
+            traffic = None if per_window is None else int(per_window * chunk)  # conv traffic is linear in windows
         except Exception:
             traffic = None
     fwd_tf = value / world * FLOP_PER_WINDOW / 1e12
