@@ -47,7 +47,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--weights", default="./resources/deepsea.beluga.pth", help="state_dict (chromatin.py:103)")
     p.add_argument("--dtype", default="f16", choices=["f16", "bf16"], help="tensor-core operand type")
     p.add_argument("--device", type=int, default=0)
-    p.add_argument("--gpu_batch", type=int, default=2048, help="variants per GPU sub-batch (x4 windows)")
+    p.add_argument("--gpu_batch", type=int, default=8192, help="variants per GPU sub-batch (x4 windows)")
+    p.add_argument("--gather", default="nccl", choices=["nccl", "file"],
+                   help="multi-GPU (torchrun) only: gather rows to rank 0 over NCCL, or every rank writes its slabs")
     p.add_argument("--upstream_layout", action="store_true",
                    help="also write upstream ExPecto's {inputfile}.shift_{s}.diff.h5 with one 'pred' dataset")
     return p
@@ -114,8 +116,37 @@ def predict_shift(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch
     torch.cuda.synchronize(engine.device)
 
 
+def predict_shift_device(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int):
+    """Same computation with the results left in HBM: (ref, alt, diff) device tensors [2n,2002] in the strand-
+    stacked row order — the operands of the end-of-shift NCCL gather when variants are sharded over GPUs."""
+    import torch
+
+    from .engine import chromatin_outputs
+    from .windows import check_valid_bases, chromatin_window_descs
+
+    n = len(pos)
+    outs = [torch.empty((2 * n, 2002), dtype=torch.float32, device=engine.device) for _ in range(3)]
+    for v0 in range(0, n, gpu_batch):
+        v1 = min(n, v0 + gpu_batch)
+        m = v1 - v0
+        descs, alleles = chromatin_window_descs(genome, chroms[v0:v1], pos[v0:v1], refs[v0:v1], alts[v0:v1], shift)
+        check_valid_bases(genome, descs)
+        probs = engine.forward_windows(descs, alleles)
+        for full, part in zip(outs, chromatin_outputs(probs, m)):
+            full[v0:v1] = part[:m]
+            full[n + v0:n + v1] = part[m:]
+    return tuple(outs)
+
+
 def run(args, engine=None, genome=None) -> dict:
-    """The whole script; returns {'n_variants', 'counters', 'files'} for callers (tests, bench)."""
+    """The whole script; returns {'n_variants', 'counters', 'files'} for callers (tests, bench).
+
+    Under torchrun (one process per GPU) the filtered variants are split into contiguous per-rank shards
+    (expecto_b200/shard.py); ``--gather nccl`` collects each shift's ref/alt/diff rows on rank 0 over NVLink and
+    rank 0 writes the file, ``--gather file`` has every rank pwrite() its own row slabs (no collective)."""
+    import torch
+
+    from . import shard
     from .genome import PackedGenome
     from .hdf5 import H5Writer
     from .windows import allele_match_counts
@@ -125,51 +156,81 @@ def run(args, engine=None, genome=None) -> dict:
                                   "which is available offline; lift the VCF to hg19 first (out of scope, SURVEY §8b)")
     if args.inputsize != 2000:
         raise ValueError("Beluga's architecture fixes --inputsize at 2000 (Linear(67840,...) = 640*106, Beluga.py:43)")
+    rank, world, local = shard.init_distributed()
     os.makedirs(args.output_dir, exist_ok=True)
     if genome is None:
         genome = PackedGenome.from_fasta(args.genome)
     if engine is None:
         from .engine import BelugaEngine
-        engine = BelugaEngine(args.device, dtype=args.dtype, capacity=min(4096, 4 * args.gpu_batch))
+        engine = BelugaEngine(local if world > 1 else args.device, dtype=args.dtype,
+                              capacity=min(4096, 4 * args.gpu_batch))
         engine.load_weights_file(args.weights)
     if engine._genome is not genome:
         engine.set_genome(genome)
 
     vcf = read_vcf(args.inputfile, args.chunk_i, args.chunk_size)
-    write_snps_vcf(vcf, args.output_dir)
+    if rank == 0:
+        write_snps_vcf(vcf, args.output_dir)
     vcf = normalise_and_filter(vcf)
     chroms, pos, refs, alts = variant_columns(vcf)
     missing = sorted({c for c in chroms if c not in genome.offsets})
     if missing:
         raise KeyError(f"contig(s) {missing} are not in the genome")  # pyfasta raises KeyError too
     n = len(pos)
+    lo, hi = shard.shard_range(n, rank, world)
+    chroms, pos, refs, alts = chroms[lo:hi], pos[lo:hi], refs[lo:hi], alts[lo:hi]
+    n_local = hi - lo
     files, counters = [], None
-    import torch
-    gb = max(1, min(args.gpu_batch, n))
-    pinned = tuple(torch.empty((2 * gb, 2002), dtype=torch.float32, pin_memory=True) for _ in range(3))
+    gb = max(1, min(args.gpu_batch, max(n_local, 1)))
+    pinned = None
+    if world == 1 or args.gather == "file":
+        pinned = tuple(torch.empty((2 * gb, 2002), dtype=torch.float32, pin_memory=True) for _ in range(3))
+    shapes = {k: (2 * n, 2002) for k in ("diff", "ref", "alt")}
     for shift in shift_list(args.maxshift):
         if shift == 0:
-            counters = allele_match_counts(genome, chroms, pos, refs, alts)
-            print(f"Number of variants with reference allele matched with reference genome: {counters[0]}")
-            print(f"Number of variants with alternate allele matched with reference genome: {counters[1]}")
-            print(f"Number of input variants: {counters[2]}")
+            mine = allele_match_counts(genome, chroms, pos, refs, alts)
+            counters = tuple(shard.allreduce_sum_ints(mine, device=engine.device if world > 1 else None))
+            if rank == 0:
+                print(f"Number of variants with reference allele matched with reference genome: {counters[0]}")
+                print(f"Number of variants with alternate allele matched with reference genome: {counters[1]}")
+                print(f"Number of input variants: {counters[2]}")
         path = f"{args.output_dir}/snps.shift_{str(shift)}.diff.h5"
-        shapes = {k: (2 * n, 2002) for k in ("diff", "ref", "alt")}
-        with H5Writer(path, shapes) as w:
-            up = None
-            if args.upstream_layout:
-                up = H5Writer(f"{args.inputfile}.shift_{str(shift)}.diff.h5", {"pred": (2 * n, 2002)})
+        up_path = f"{args.inputfile}.shift_{str(shift)}.diff.h5"
+        if world > 1 and args.gather == "nccl":
+            local_out = predict_shift_device(engine, genome, chroms, pos, refs, alts, shift, gb)
+            full = [shard.gather_strand_rows(t, n) for t in local_out]  # ref, alt, diff
+            if rank == 0:
+                with H5Writer(path, shapes) as w:
+                    for name, t in zip(("ref", "alt", "diff"), full):
+                        w.write(name, t.cpu().numpy())
+                if args.upstream_layout:
+                    with H5Writer(up_path, {"pred": (2 * n, 2002)}) as up:
+                        up.write("pred", full[2].cpu().numpy())
+            del local_out, full
+        else:
+            # single process, or every rank writing its own slabs: rank 0 creates the files, the others attach
+            if rank == 0:
+                w = H5Writer(path, shapes)
+                up = H5Writer(up_path, {"pred": (2 * n, 2002)}) if args.upstream_layout else None
+            shard.barrier()
+            if rank != 0:
+                w = H5Writer(path, shapes, create=False)
+                up = H5Writer(up_path, {"pred": (2 * n, 2002)}, create=False) if args.upstream_layout else None
 
             def sink(name, row0, arr, w=w, up=up):
-                w.write_rows(name, row0, arr)
+                # local strand-stacked row -> global row: forward rows at lo+v, reverse-complement rows at n+lo+v
+                g0 = lo + row0 if row0 < n_local else n + lo + (row0 - n_local)
+                w.write_rows(name, g0, arr)
                 if up is not None and name == "diff":
-                    up.write_rows("pred", row0, arr)
+                    up.write_rows("pred", g0, arr)
 
             predict_shift(engine, genome, chroms, pos, refs, alts, shift, gb, sink, pinned)
+            w.close()
             if up is not None:
                 up.close()
+            shard.barrier()
         files.append(path)
-    return {"n_variants": n, "counters": counters, "files": files}
+    return {"n_variants": n, "counters": counters, "files": files, "rank": rank, "world": world}
 
 
 def main(argv=None) -> int:

@@ -730,4 +730,21 @@ int bx_decay_transform_variant(const float* x_dev, const double* dist_dev, const
   return 0;
 }
 
+int bx_decay_score_variant(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+                            const int32_t* shifts_dev, const float* w_dev, const float* offset_dev, int n,
+                            int n_shifts, int n_models, float* out_dev, void* stream) {
+  if (n < 0 || n_models < 1 || n_shifts < 1 || n_shifts > 25)
+    return fail(BX_E_ARG, "invalid arguments (n_shifts must be 1..25, n_models >= 1)");
+  if (n == 0) return 0;
+  if (!x_dev || !dist_dev || !strand_dev || !shifts_dev || !w_dev || !offset_dev || !out_dev)
+    return fail(BX_E_ARG, "invalid arguments");
+  dim3 grid(n, (n_models + kScoreModels - 1) / kScoreModels);
+  const size_t smem = (size_t)(n_shifts * 10 + 8 * kScoreModels) * sizeof(float);
+  decay_score_variant_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(x_dev, dist_dev, strand_dev, shifts_dev, w_dev,
+                                                                        offset_dev, n, n_shifts, n_models, out_dev);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
 }  // extern "C"

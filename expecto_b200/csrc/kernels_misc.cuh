@@ -291,4 +291,67 @@ decay_variant_kernel(const float* __restrict__ x, const double* __restrict__ dis
   for (int k = 0; k < 10; ++k) out[((size_t)v * 10 + k) * kFeat + f] = acc[k];
 }
 
+// Per-variant transform fused with gblinear scoring (predict.py:123-160): the 20020 features of a variant are
+// formed in registers and immediately contracted with the model weights, so the float64[n,20020] feature
+// matrices of the reference (480 KB per variant for diff/ref/alt) never exist.
+// x [S, n, 2002]; w [m, 10*2002] (column k*2002+f; columns dropped by the keep mask are zero);
+// offset [m] = base_score + bias; out [n, m].  Block = (variant, group of kScoreModels models).
+constexpr int kScoreModels = 8;
+__global__ void __launch_bounds__(256)
+decay_score_variant_kernel(const float* __restrict__ x, const double* __restrict__ dist,
+                           const int8_t* __restrict__ strand, const int32_t* __restrict__ shifts,
+                           const float* __restrict__ w, const float* __restrict__ offset, int n, int n_shifts, int m,
+                           float* __restrict__ out) {
+  extern __shared__ float sw[];  // [S][10] then [8 warps][kScoreModels]
+  float* red = sw + n_shifts * 10;
+  const int v = blockIdx.x;
+  const int m0 = blockIdx.y * kScoreModels;
+  if (threadIdx.x < n_shifts * 10) {
+    const int j = threadIdx.x / 10, k = threadIdx.x - j * 10;
+    const double sgn = strand[v] > 0 ? 1.0 : -1.0;
+    const double pos = dist[v] * sgn + (double)shifts[j] * sgn;
+    const double rate[5] = {0.01, 0.02, 0.05, 0.1, 0.2};
+    const double e = exp(-rate[k % 5] * floor(fabs(pos / 200.0)));
+    const bool on = (k < 5) ? (pos <= 0.0) : (pos >= 0.0);
+    sw[j * 10 + k] = on ? (float)e : 0.f;
+  }
+  __syncthreads();
+  float acc[kScoreModels];
+#pragma unroll
+  for (int i = 0; i < kScoreModels; ++i) acc[i] = 0.f;
+  for (int f = threadIdx.x; f < kFeat; f += 256) {
+    float feat[10];
+#pragma unroll
+    for (int k = 0; k < 10; ++k) feat[k] = 0.f;
+    for (int j = 0; j < n_shifts; ++j) {
+      const float xv = __ldg(x + ((size_t)j * n + v) * kFeat + f);
+#pragma unroll
+      for (int k = 0; k < 10; ++k) feat[k] = fmaf(sw[j * 10 + k], xv, feat[k]);
+    }
+#pragma unroll
+    for (int i = 0; i < kScoreModels; ++i) {
+      if (m0 + i < m) {
+        const float* wi = w + (size_t)(m0 + i) * 10 * kFeat + f;
+#pragma unroll
+        for (int k = 0; k < 10; ++k) acc[i] = fmaf(feat[k], __ldg(wi + k * kFeat), acc[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < kScoreModels; ++i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0)
+#pragma unroll
+    for (int i = 0; i < kScoreModels; ++i) red[warp * kScoreModels + i] = acc[i];
+  __syncthreads();
+  if (threadIdx.x < kScoreModels && m0 + threadIdx.x < m) {
+    float s = 0.f;
+    for (int wp = 0; wp < 8; ++wp) s += red[wp * kScoreModels + threadIdx.x];
+    out[(size_t)v * m + m0 + threadIdx.x] = s + offset[m0 + threadIdx.x];
+  }
+}
+
 }  // namespace bx

@@ -1,0 +1,96 @@
+"""Loader for xgboost ``gblinear`` expression models (predict.py:165-166 ``xgb.Booster().load_model``).
+
+xgboost==0.7.post4 is a pinned third-party dependency of the reference (requirements.txt:38) that is not in
+this image, and the reference's ``models/*.save`` files are not in its repository, so nothing here can be
+checked against a real model file: the binary layout below restates xgboost 0.7's published serialisation
+(learner.cc ``LearnerModelParam`` + gblinear ``GBLinearModelParam`` + weight vector) and is UNPINNED.  The
+text-dump and ``.npz`` forms are pinned by the tests (the ``.npz`` form is what the oracle's xgboost shim
+reads, oracle/shims/xgboost.py).
+
+A gblinear model scores ``base_score + bias + w . x`` (dump layout: predict_by_cluster.py:73-75).
+"""
+from __future__ import annotations
+
+import struct
+from dataclasses import dataclass
+
+import numpy as np
+
+
+@dataclass
+class GBLinearModel:
+    weights: np.ndarray  # float32 [n_features]
+    bias: float
+    base_score: float = 0.5
+
+    @property
+    def offset(self) -> float:
+        return float(self.base_score) + float(self.bias)
+
+
+def load_npz(path: str) -> GBLinearModel:
+    z = np.load(path)
+    return GBLinearModel(np.ascontiguousarray(z["weights"], dtype=np.float32), float(z["bias"]),
+                         float(z["base_score"]) if "base_score" in z.files else 0.5)
+
+
+def load_text_dump(path: str, base_score: float = 0.5) -> GBLinearModel:
+    """``bst.dump_model(path)`` of a gblinear booster: ``booster[0]:`` / ``bias:`` / value / ``weight:`` / values."""
+    bias, weights, mode = [], [], None
+    for line in open(path):
+        t = line.strip()
+        if not t or t.startswith("booster"):
+            continue
+        if t.startswith("bias"):
+            mode = bias
+        elif t.startswith("weight"):
+            mode = weights
+        elif mode is not None:
+            mode.append(float(t))
+    if len(bias) != 1 or not weights:
+        raise ValueError(f"{path}: not a single-output gblinear dump")
+    return GBLinearModel(np.asarray(weights, dtype=np.float32), bias[0], base_score)
+
+
+def load_binary(path: str) -> GBLinearModel:
+    """xgboost 0.7 binary model (UNPINNED restatement, see module docstring)."""
+    b = open(path, "rb").read()
+    off = 4 if b[:4] == b"binf" else 0
+    base_score, num_feature, num_class, extra_attrs, eval_metrics = struct.unpack_from("<fIiii", b, off)
+    off += 136  # LearnerModelParam: 5 fields + int reserved[29]
+    names = []
+    for _ in range(2):  # objective name, booster name
+        (ln,) = struct.unpack_from("<Q", b, off)
+        names.append(b[off + 8:off + 8 + ln].decode("ascii", "replace"))
+        off += 8 + ln
+    if names[1] != "gblinear":
+        raise ValueError(f"{path}: booster is {names[1]!r}, not gblinear")
+    gb_features, groups = struct.unpack_from("<Ii", b, off)
+    off += 136  # GBLinearModelParam: 2 fields + int reserved[32]
+    (n,) = struct.unpack_from("<Q", b, off)
+    off += 8
+    if groups != 1 or n != (gb_features + 1) * groups:
+        raise ValueError(f"{path}: unexpected gblinear shape (features {gb_features}, groups {groups}, weights {n})")
+    w = np.frombuffer(b, dtype="<f4", count=n, offset=off)
+    return GBLinearModel(np.ascontiguousarray(w[:gb_features]), float(w[gb_features]), float(base_score))
+
+
+def save_binary(path: str, model: GBLinearModel, objective: str = "reg:linear") -> None:
+    """Writer of the same layout (round-trip tests, synthetic ``modellist`` files)."""
+    nf = int(model.weights.size)
+    out = struct.pack("<fIiii", model.base_score, nf, 0, 0, 0) + b"\x00" * (136 - 20)
+    for name in (objective, "gblinear"):
+        out += struct.pack("<Q", len(name)) + name.encode("ascii")
+    out += struct.pack("<Ii", nf, 1) + b"\x00" * (136 - 8)
+    out += struct.pack("<Q", nf + 1) + np.asarray(model.weights, dtype="<f4").tobytes() + struct.pack("<f", model.bias)
+    open(path, "wb").write(out)
+
+
+def load_model(path: str) -> GBLinearModel:
+    path = path.strip()
+    if path.endswith(".npz"):
+        return load_npz(path)
+    head = open(path, "rb").read(16)
+    if head.startswith(b"booster") or head.startswith(b"bias"):
+        return load_text_dump(path)
+    return load_binary(path)

@@ -9,6 +9,7 @@ any h5py/libhdf5 >= 1.8 reads it.  The reader walks root -> B-tree -> SNOD -> ob
 """
 from __future__ import annotations
 
+import os
 import struct
 import time
 
@@ -52,7 +53,9 @@ class H5Writer:
     ``create(name, shape)`` reserves space; ``write_rows(name, row0, array)`` pwrite()s row slabs, so several
     producers (GPU ranks, pipeline stages) can fill one contiguous dataset without an in-memory copy."""
 
-    def __init__(self, path: str, datasets: dict[str, tuple[int, ...]]):
+    def __init__(self, path: str, datasets: dict[str, tuple[int, ...]], create: bool = True):
+        """``create=False`` attaches to a file another process already created with the same datasets (a GPU
+        rank writing its own row slab; the layout is a pure function of the dataset shapes)."""
         if not 1 <= len(datasets) <= 2 * _LEAF_K:
             raise ValueError("1..8 datasets per file")
         self.path = path
@@ -64,9 +67,14 @@ class H5Writer:
             off += int(np.prod(self.shapes[n])) * 4
             off += (-off) % 8
         self.eof = off
-        self._f = open(path, "wb+")
-        self._f.write(self._metadata())
-        self._f.truncate(self.eof)
+        if create:
+            self._f = open(path, "wb+")
+            self._f.write(self._metadata())
+            self._f.truncate(self.eof)
+        else:
+            self._f = open(path, "rb+")
+            if self._f.read(8) != _SIG or os.fstat(self._f.fileno()).st_size != self.eof:
+                raise ValueError(f"{path} was not created with these datasets")
 
     def _metadata(self) -> bytes:
         btree_addr, heap_addr = 0x88, 0x2A8

@@ -1,0 +1,188 @@
+"""Drop-in for the reference's ``predict.py`` (same CLI, same ``sed*.tsv`` out), transform + scoring on a B200.
+
+    python -m expecto_b200.predict --model_save_file M --belugaFeatures resources/deepsea_beluga_2002_features.tsv \\
+        --coorFile_chromatin out/snps_hg19.vcf --geneFile snps.closestgene \\
+        --snpEffectFilePattern out/snps.shift_SHIFT.diff.h5 -o out_dir
+
+Reference behaviour reproduced (file:line into /root/reference/predict.py):
+  * arguments and defaults                                                               :15-58
+  * per-shift HDF5 read of ``diff``/``ref``/``alt`` and the (fwd + rc) / 2.0 strand average :173-194
+  * duplicate handling, variant <-> gene expansion with ``get_num_repeats`` / ``np.repeat`` :197-235
+  * ``dist = -gene[:, -1]`` (or ``--fixeddist``), gene name, strand                          :238-246
+  * ``compute_effects``: decay weights, 10 x 2002 features, keep-mask column subset, gblinear
+    scores for ref and alt features; ``SED = ALT - REF``                                     :70-162,264
+  * ``sed.tsv``, ``sed_sorted_by_magnitude.tsv``, ``sed_sorted_by_proportion.tsv``            :255-280
+By design the [n,20020] float64 feature matrices are never built: kernel ``decay_score_variant`` forms each
+variant's features in registers and contracts them with the model weights; columns dropped by
+the keep mask are zero-weighted, which is the same sum.  ``--modelList`` (upstream ExPecto's interface, README.md:25)
+scores every model of a list in the same launch and appends one column per model.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import numpy as np
+
+from .chromatin import shift_list
+
+
+def build_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(description="Process some integers.")
+    p.add_argument("--model_save_file", action="store", dest="model_save_file")
+    p.add_argument("--belugaFeatures", action="store", dest="belugaFeatures")
+    p.add_argument("--coorFile_chromatin", action="store", dest="coorFile_chromatin")
+    p.add_argument("--geneFile", action="store", dest="geneFile")
+    p.add_argument("--snpEffectFilePattern", action="store", dest="snpEffectFilePattern")
+    p.add_argument("--rsat_clusters_tab", action="store", dest="rsat_clusters_tab")
+    p.add_argument("--nfeatures", action="store", dest="nfeatures", type=int, default=2002)
+    p.add_argument("--fixeddist", action="store", dest="fixeddist", default=0, type=int)
+    p.add_argument("--maxshift", action="store", dest="maxshift", type=int, default=800)
+    p.add_argument("--batchSize", action="store", dest="batchSize", type=int, default=500)
+    p.add_argument("--splitIndex", action="store", dest="splitIndex", type=int, default=0)
+    p.add_argument("--splitFold", action="store", dest="splitFold", type=int, default=10)
+    p.add_argument("--threads", action="store", dest="threads", type=int, default=16)
+    p.add_argument("--no_tf_features", action="store_true", dest="no_tf_features", default=False)
+    p.add_argument("--no_dnase_features", action="store_true", dest="no_dnase_features", default=False)
+    p.add_argument("--no_histone_features", action="store_true", dest="no_histone_features", default=False)
+    p.add_argument("--intersect_with_lambert", action="store_true", dest="intersect_with_lambert", default=False)
+    p.add_argument("--no_pol2", action="store_true", dest="no_pol2", default=False)
+    p.add_argument("-o", action="store", dest="out_dir")
+    # extensions
+    p.add_argument("--modelList", default=None, help="file with one model path per line (upstream interface)")
+    p.add_argument("--device", type=int, default=0)
+    return p
+
+
+def keep_mask(features_tsv: str, args) -> np.ndarray:
+    """cluster_utils.get_keep_mask (cluster_utils.py:8-49) for the flags that need no extra resource files."""
+    import pandas as pd
+
+    df = pd.read_csv(features_tsv, sep="\t", index_col=0)
+    mask = np.ones(df.shape[0], dtype=bool)
+    if args.no_tf_features:
+        print("not including TF features")
+        mask &= (df["Assay type"] != "TF").values
+    if args.no_dnase_features:
+        print("not including DNase features")
+        mask &= (df["Assay type"] != "DNase").values
+    if args.no_histone_features:
+        print("not including histone features")
+        mask &= (df["Assay type"] != "Histone").values
+    if args.intersect_with_lambert:
+        raise NotImplementedError("--intersect_with_lambert needs resources/Lambert-hgnc-symbol-check.csv and "
+                                  "beluga_hgnc_mapping.csv, which are not part of the reference repository")
+    if args.no_pol2:
+        print("taking out Pol2*")
+        mask &= ~df["Assay"].astype(str).str.startswith("Pol").values
+    print(f"Number of features included in model: {int(mask.sum())}")
+    return mask
+
+
+def num_repeats(gene_df) -> list[int]:
+    """get_num_repeats, predict.py:202-213: run lengths of consecutive rows sharing columns 0-4."""
+    keys = gene_df.iloc[:, 0:5].astype(str).agg(":".join, axis=1).values
+    if len(keys) == 0:
+        return [0]
+    change = np.flatnonzero(keys[1:] != keys[:-1]) + 1
+    edges = np.concatenate([[0], change, [len(keys)]])
+    return [int(x) for x in np.diff(edges)]
+
+
+def load_strand_averaged(pattern: str, maxshift: int):
+    """predict.py:173-194 -> dict of float32 [S, N, 2002] for diff / ref / alt."""
+    from . import hdf5
+
+    out = {"diff": [], "ref": [], "alt": []}
+    for s in shift_list(maxshift):
+        with hdf5.File(pattern.replace("SHIFT", str(s))) as f:
+            for k in out:
+                d = f[k]
+                n = int(d.shape[0] / 2)
+                out[k].append((np.asarray(d[0:n, :]) + np.asarray(d[n:2 * n, :])) / 2.0)
+    return {k: np.array(v) for k, v in out.items()}
+
+
+def expand_weights(models, mask: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
+    """Model weights over the kept columns (10 x n_marks, predict.py:139-147) -> zero-filled [m, 10*2002]."""
+    n_marks = int(mask.sum())
+    W = np.zeros((len(models), 10, mask.size), dtype=np.float32)
+    for i, m in enumerate(models):
+        if m.weights.size != 10 * n_marks:
+            raise ValueError(f"model {i} has {m.weights.size} weights, expected 10 x {n_marks}")
+        W[i][:, mask] = m.weights.reshape(10, n_marks)
+    return W.reshape(len(models), -1), np.array([m.offset for m in models], dtype=np.float32)
+
+
+def run(args) -> dict:
+    import pandas as pd
+    import torch
+
+    from .gblinear import load_model
+    from .transform import decay_score_variant
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("predict needs a CUDA device (B200); there is no CPU fallback")
+    os.makedirs(args.out_dir, exist_ok=True)
+    mask = keep_mask(args.belugaFeatures, args)
+    paths = [args.model_save_file.strip()] if args.model_save_file else []
+    if args.modelList:
+        paths += [l.strip() for l in open(args.modelList) if l.strip() and not l.startswith("#")]
+    if not paths:
+        raise ValueError("give --model_save_file or --modelList")
+    W, offsets = expand_weights([load_model(p) for p in paths], mask)
+
+    data = load_strand_averaged(args.snpEffectFilePattern, int(args.maxshift))
+    coor = pd.read_csv(args.coorFile_chromatin, sep="\t", header=None, comment="#")
+    gene = pd.read_csv(args.geneFile, sep="\t", header=None, comment="#")
+    gene = gene.drop_duplicates(keep="first")
+    coor_mask = ~coor.duplicated(keep="first").values
+    coor = coor[coor_mask]
+    repeats = num_repeats(gene)
+    idx = np.repeat(np.flatnonzero(coor_mask), repeats)  # row of the prediction arrays for every gene row
+    coor = pd.DataFrame(np.repeat(coor.values, repeats, axis=0), columns=coor.columns)
+    if len(idx) != gene.shape[0]:
+        raise ValueError("Gene association file does not match the vcf file.")
+    if args.fixeddist == 0:
+        dist = -np.asarray(gene.iloc[:, -1], dtype=np.float64)
+    else:
+        dist = np.full(gene.shape[0], float(args.fixeddist))
+    genename, strand = np.asarray(gene.iloc[:, -2]), np.asarray(gene.iloc[:, -3])
+
+    dev = torch.device("cuda", args.device)
+    sel = torch.from_numpy(idx).to(dev)
+    scores = {}
+    for key in ("ref", "alt"):
+        x = torch.from_numpy(np.ascontiguousarray(data[key], dtype=np.float32)).to(dev).index_select(1, sel)
+        scores[key] = decay_score_variant(x, dist, strand, W, offsets, shifts=shift_list(int(args.maxshift))).cpu().numpy()
+    ref, alt = scores["ref"], scores["alt"]
+
+    df = coor
+    df["dist"] = dist if args.fixeddist else -np.asarray(gene.iloc[:, -1])
+    df["gene"] = genename
+    df["strand"] = strand
+    cols = {"REF": ref[:, 0], "ALT": alt[:, 0], "SED": alt[:, 0] - ref[:, 0]}
+    for i, p in enumerate(paths[1:], start=1):  # --modelList: one SED column per extra model
+        cols[f"SED_{os.path.basename(p)}"] = alt[:, i] - ref[:, i]
+    df = pd.concat([df.reset_index()] + [pd.DataFrame(v, columns=[k]) for k, v in cols.items()], axis=1,
+                   ignore_index=False)
+    df.to_csv(f"{args.out_dir}/sed.tsv", header=True, sep="\t", index=False)
+    s = df.copy()
+    s["SED_MAGNITUDES"] = np.abs(s["SED"])
+    s.sort_values(by="SED_MAGNITUDES", axis=0, ascending=False).to_csv(
+        f"{args.out_dir}/sed_sorted_by_magnitude.tsv", header=True, sep="\t", index=False)
+    s = df.copy()
+    s["SED_PROPORTION"] = np.abs(s["SED"] / ((s["REF"] + s["ALT"]) / 2))
+    s.sort_values(by="SED_PROPORTION", axis=0, ascending=False).to_csv(
+        f"{args.out_dir}/sed_sorted_by_proportion.tsv", header=True, sep="\t", index=False)
+    return {"n_rows": len(df), "ref": ref, "alt": alt, "models": paths}
+
+
+def main(argv=None) -> int:
+    run(build_parser().parse_args(argv))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -54,9 +54,7 @@ def chromatin_shifts(maxshift: int = 800) -> list[int]:
     return [0] + list(range(-200, -maxshift - 1, -200)) + list(range(200, maxshift + 1, 200))  # predict.py:173
 
 
-def decay_transform_variant(x: torch.Tensor, dist, strand, shifts=None, out: torch.Tensor | None = None) -> torch.Tensor:
-    """``x`` fp32 CUDA [S,n,2002] (one matrix per shift, in ``shifts`` order); ``dist`` = variant - TSS
-    (predict.py:241 ``-gene[:, -1]``); ``strand`` array of '+'/'-' (or +1/-1) -> fp32 [n,20020]."""
+def _variant_args(x: torch.Tensor, dist, strand, shifts):
     if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 3 or x.shape[2] != N_FEATURES:
         raise ValueError("x must be a CUDA float32 tensor [S,n,2002]")
     S, n = x.shape[:2]
@@ -73,9 +71,30 @@ def decay_transform_variant(x: torch.Tensor, dist, strand, shifts=None, out: tor
     sh = torch.tensor(shifts, dtype=torch.int32, device=x.device)
     if d.numel() != n or sg.numel() != n:
         raise ValueError("dist/strand must have one entry per variant")
-    x = x.contiguous()
+    return x.contiguous(), d, sg, sh, n, S
+
+
+def decay_transform_variant(x: torch.Tensor, dist, strand, shifts=None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """``x`` fp32 CUDA [S,n,2002] (one matrix per shift, in ``shifts`` order); ``dist`` = variant - TSS
+    (predict.py:241 ``-gene[:, -1]``); ``strand`` array of '+'/'-' (or +1/-1) -> fp32 [n,20020]."""
+    x, d, sg, sh, n, S = _variant_args(x, dist, strand, shifts)
     if out is None:
         out = torch.empty((n, N_BASIS * N_FEATURES), dtype=torch.float32, device=x.device)
     check(lib().bx_decay_transform_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), n, S,
                                            out.data_ptr(), _stream(x)))
+    return out
+
+
+def decay_score_variant(x: torch.Tensor, dist, strand, weights, offsets, shifts=None) -> torch.Tensor:
+    """predict.py:123-160 fused (transform + gblinear scoring): ``weights`` [m,20020] (dropped columns = 0),
+    ``offsets`` [m] = base_score + bias -> fp32 [n,m] scores; the feature matrix is never materialised."""
+    x, d, sg, sh, n, S = _variant_args(x, dist, strand, shifts)
+    w = torch.as_tensor(np.ascontiguousarray(np.asarray(weights, dtype=np.float32))).to(x.device).reshape(-1, N_BASIS * N_FEATURES)
+    m = w.shape[0]
+    off = torch.as_tensor(np.ascontiguousarray(np.asarray(offsets, dtype=np.float32)).reshape(-1)).to(x.device)
+    if off.numel() != m:
+        raise ValueError("one offset per model")
+    out = torch.empty((n, m), dtype=torch.float32, device=x.device)
+    check(lib().bx_decay_score_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), w.data_ptr(),
+                                       off.data_ptr(), n, S, m, out.data_ptr(), _stream(x)))
     return out

@@ -127,6 +127,14 @@ int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, i
 int bx_decay_transform_variant(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
                                const int32_t* shifts_dev, int n, int n_shifts, float* out_dev, void* stream);
 
+/* predict.py:123-160 fused: per-variant decay features contracted with n_models gblinear weight vectors
+ * (xgboost Booster.predict = base_score + bias + w.x) without materialising the [n,20020] feature matrix.
+ * w_dev fp32 [n_models, 10*2002] (columns removed by cluster_utils.get_keep_mask set to 0), offset_dev fp32
+ * [n_models] = base_score + bias, out_dev fp32 [n, n_models]. */
+int bx_decay_score_variant(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+                            const int32_t* shifts_dev, const float* w_dev, const float* offset_dev, int n,
+                            int n_shifts, int n_models, float* out_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -174,3 +174,59 @@ def test_state_errors(small_genome):
     with pytest.raises(_lib.BelugaError):
         eng.forward_onehot(torch.zeros((1, 4, 2000), dtype=torch.uint8, device="cuda"))
     eng.close()
+
+
+def test_fused_transform_scoring_kernel_vs_oracle():
+    """decay_score_variant == gblinear(variant_transform(x)) for several models incl. a keep-mask-style zero block."""
+    from expecto_b200.transform import decay_score_variant
+    rng = np.random.default_rng(3)
+    n, m = 131, 11
+    x = (rng.standard_normal((9, n, 2002)) * 0.05).astype(np.float32)
+    dist = rng.integers(-30000, 30000, size=n).astype(np.float64)
+    strand = np.where(rng.random(n) < 0.5, "+", "-")
+    W = (rng.standard_normal((m, 20020)) * 0.01).astype(np.float32)
+    W[3].reshape(10, 2002)[:, 100:700] = 0
+    off = rng.standard_normal(m).astype(np.float32)
+    ours = decay_score_variant(torch.from_numpy(x).cuda(), dist, strand, W, off).cpu().numpy()
+    feats = O.variant_transform(list(x), O.variant_weights(dist, strand))
+    want = feats @ W.astype(np.float64).T + off[None, :]
+    assert ours.shape == (n, m)
+    assert np.abs(ours - want).max() <= 1e-4 * max(1.0, np.abs(want).max())
+
+
+def test_predict_cli_matches_predict_script(engine, cfg1_genome, golden, tmp_path):
+    """chromatin CLI -> predict CLI (fused transform + scoring) vs the reference predict.py's sed.tsv."""
+    import pandas as pd
+    from expecto_b200 import chromatin, predict
+    g = golden("predict_golden.npz")
+    want = pd.read_csv(io.StringIO(str(g["sed_tsv"])), sep="\t")
+    rows = [l.split("\t") for l in str(golden("chromatin_cfg1_golden.npz")["snps_hg19_vcf"]).splitlines()[2:]]
+    vcf = tmp_path / "example.vcf"
+    vcf.write_text("".join("\t".join(r) + "\n" for r in rows))
+    out = tmp_path / "chromatin_out"
+    chromatin.run(chromatin.build_parser().parse_args([str(vcf), "--output_dir", str(out)]), engine=engine,
+                  genome=PackedGenome.from_sequences(cfg1_genome))
+    genefile = tmp_path / "closestgene"
+    with open(genefile, "w") as f:
+        for r, (_, w) in zip(rows, want.iterrows()):
+            f.write("\t".join([r[0], str(int(r[1]) - 1), r[1], r[3], r[4], w["strand"], w["gene"], str(-int(w["dist"]))]) + "\n")
+    np.savez(tmp_path / "model.npz", weights=g["model_w"], bias=np.float32(0.25), base_score=np.float32(0.5))
+    feats_tsv = tmp_path / "features.tsv"
+    with open(feats_tsv, "w") as f:
+        f.write("\tCell type\tAssay\tTreatment\tAssay type\tSource\n")
+        for i in range(2002):
+            f.write(f"{i}\tcell{i}\tassay{i}\tNone\t{'DNase' if i % 3 == 0 else 'TF'}\tsrc\n")
+    args = predict.build_parser().parse_args([
+        "--model_save_file", str(tmp_path / "model.npz"), "--belugaFeatures", str(feats_tsv), "--coorFile_chromatin",
+        str(out / "snps_hg19.vcf"), "--geneFile", str(genefile), "--snpEffectFilePattern",
+        str(out / "snps.shift_SHIFT.diff.h5"), "-o", str(tmp_path / "pred")])
+    predict.run(args)
+    ours = pd.read_csv(tmp_path / "pred" / "sed.tsv", sep="\t")
+    assert list(ours.columns) == list(want.columns)
+    for c in ("index", "0", "1", "2", "3", "4", "dist", "gene", "strand"):
+        assert [str(v) for v in ours[c]] == [str(v) for v in want[c]], c
+    assert np.abs(ours["REF"].values - want["REF"].values).max() <= 2e-2
+    assert np.abs(ours["ALT"].values - want["ALT"].values).max() <= 2e-2
+    assert np.abs(ours["SED"].values - want["SED"].values).max() <= 5e-3
+    for name in ("sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
+        assert (tmp_path / "pred" / name).exists()

@@ -1,0 +1,64 @@
+"""Host logic of the predict.py drop-in: model loaders, gene-row run lengths, keep-mask expansion."""
+import numpy as np
+import pandas as pd
+import pytest
+
+from expecto_b200 import gblinear
+from expecto_b200.predict import build_parser, expand_weights, num_repeats
+from expecto_b200.transform import chromatin_shifts, fixed_pos_weights
+from oracle import beluga_oracle as O
+
+
+def test_gblinear_formats_roundtrip(tmp_path):
+    rng = np.random.default_rng(0)
+    m = gblinear.GBLinearModel(rng.standard_normal(20020).astype(np.float32), bias=0.25, base_score=0.5)
+    gblinear.save_binary(str(tmp_path / "m.save"), m)
+    b = gblinear.load_model(str(tmp_path / "m.save"))
+    assert np.array_equal(b.weights, m.weights) and b.bias == 0.25 and b.base_score == 0.5
+    np.savez(tmp_path / "m.npz", weights=m.weights, bias=np.float32(0.25), base_score=np.float32(0.5))
+    z = gblinear.load_model(str(tmp_path / "m.npz"))
+    assert np.array_equal(z.weights, m.weights) and z.offset == 0.75
+    with open(tmp_path / "m.dump", "w") as f:
+        f.write("booster[0]:\nbias:\n0.25\nweight:\n" + "\n".join(repr(float(v)) for v in m.weights[:50]) + "\n")
+    t = gblinear.load_model(str(tmp_path / "m.dump"))
+    assert np.array_equal(t.weights, m.weights[:50]) and t.bias == 0.25
+    x = rng.standard_normal((3, 20020))
+    assert np.allclose(O.gblinear_predict(x, b.weights, b.bias, b.base_score), 0.75 + x @ m.weights.astype(np.float64))
+
+
+def test_binary_loader_rejects_other_boosters(tmp_path):
+    p = tmp_path / "tree.save"
+    import struct
+    blob = struct.pack("<fIiii", 0.5, 10, 0, 0, 0) + b"\x00" * 116
+    for name in ("reg:linear", "gbtree"):
+        blob += struct.pack("<Q", len(name)) + name.encode()
+    p.write_bytes(blob + b"\x00" * 200)
+    with pytest.raises(ValueError):
+        gblinear.load_binary(str(p))
+
+
+def test_num_repeats_matches_reference_loop():
+    rows = [["chr1", 1, 2, "A", "C", "+", "g1", 5], ["chr1", 1, 2, "A", "C", "-", "g2", -7],
+            ["chr1", 9, 10, "G", "T", "+", "g3", 1], ["chr2", 9, 10, "G", "T", "+", "g3", 1],
+            ["chr2", 9, 10, "G", "T", "-", "g4", 2], ["chr2", 9, 10, "G", "T", "-", "g5", 3]]
+    assert num_repeats(pd.DataFrame(rows)) == [2, 1, 3]
+    assert num_repeats(pd.DataFrame(rows[:1])) == [1]
+
+
+def test_expand_weights_zero_fills_dropped_columns():
+    mask = np.ones(2002, dtype=bool)
+    mask[[0, 5, 2001]] = False
+    m = gblinear.GBLinearModel(np.arange(10 * 1999, dtype=np.float32), 0.1, 0.5)
+    W, off = expand_weights([m], mask)
+    assert W.shape == (1, 20020) and np.isclose(off[0], 0.6)
+    W3 = W.reshape(10, 2002)
+    assert np.all(W3[:, ~mask] == 0) and np.array_equal(W3[:, mask].ravel(), m.weights)
+    with pytest.raises(ValueError):
+        expand_weights([gblinear.GBLinearModel(np.zeros(20020, np.float32), 0, 0)], mask)
+
+
+def test_cli_defaults_match_reference():
+    a = build_parser().parse_args(["-o", "x"])
+    assert (a.nfeatures, a.fixeddist, a.maxshift, a.batchSize, a.threads) == (2002, 0, 800, 500, 16)
+    assert chromatin_shifts(800) == O.SHIFTS_CHROMATIN(800)
+    assert np.array_equal(fixed_pos_weights(), O.fixed_pos_weights())

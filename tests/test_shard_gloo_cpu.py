@@ -1,0 +1,84 @@
+"""The N>1 host path on CPU: world_size-2 gloo processes exercising the shard split, the strand-aware gather
+to rank 0 and the no-collective alternative (each rank pwrite()s its row slabs of one HDF5 file)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from expecto_b200 import hdf5, shard
+
+F = 2002
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _fake_rows(n):
+    """[2n, F] in chromatin.py's layout: value encodes (strand, variant, feature)."""
+    v = np.arange(n, dtype=np.float32)[:, None] * 10 + np.arange(F, dtype=np.float32)[None, :] / 4096
+    return np.concatenate([v, -v - 1], axis=0)
+
+
+def _worker(rank, world, port, n, tmp):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    r, w, _ = shard.init_distributed("gloo")
+    assert (r, w) == (rank, world)
+    full = _fake_rows(n)
+    lo, hi = shard.shard_range(n, rank, world)
+    local = torch.from_numpy(np.concatenate([full[lo:hi], full[n + lo:n + hi]], axis=0))
+    got = shard.gather_strand_rows(local, n)
+    if rank == 0:
+        assert got is not None and np.array_equal(got.numpy(), full)
+    else:
+        assert got is None
+    plain = shard.gather_rows(torch.from_numpy(full[lo:hi].copy()), n)
+    if rank == 0:
+        assert np.array_equal(plain.numpy(), full[:n])
+    assert shard.allreduce_sum_ints([rank + 1, 10, hi - lo]) == [sum(range(1, world + 1)), 10 * world, n]
+    # no-collective mode: rank 0 creates, the others attach and write their own slabs
+    path = os.path.join(tmp, "slabs.h5")
+    shapes = {"diff": (2 * n, F)}
+    if rank == 0:
+        wtr = hdf5.H5Writer(path, shapes)
+    shard.barrier()
+    if rank != 0:
+        wtr = hdf5.H5Writer(path, shapes, create=False)
+    wtr.write_rows("diff", lo, full[lo:hi])
+    wtr.write_rows("diff", n + lo, full[n + lo:n + hi])
+    wtr.close()
+    shard.barrier()
+    if rank == 0:
+        with hdf5.File(path) as f:
+            assert np.array_equal(np.asarray(f["diff"]), full)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [7, 8, 1])
+def test_two_rank_gather_and_slab_write(tmp_path, n):
+    mp.spawn(_worker, args=(2, _free_port(), n, str(tmp_path)), nprocs=2, join=True)
+
+
+def test_shard_bounds_cover_rows_in_order():
+    for n in (0, 1, 7, 8, 1000003):
+        for world in (1, 2, 4, 8):
+            b = shard.shard_bounds(n, world)
+            assert b[0] == 0 and b[-1] == n and np.all(np.diff(b) >= 0)
+            assert np.diff(b).max() - np.diff(b).min() <= 1
+            assert [shard.shard_range(n, r, world) for r in range(world)] == list(zip(b[:-1], b[1:]))
+
+
+def test_attach_rejects_mismatched_file(tmp_path):
+    p = str(tmp_path / "a.h5")
+    hdf5.H5Writer(p, {"diff": (4, F)}).close()
+    with pytest.raises(ValueError):
+        hdf5.H5Writer(p, {"diff": (6, F)}, create=False)
