@@ -48,7 +48,7 @@ def main():
     ok = True
     if rank == 0:
         # single-process run on this GPU: temporarily hide the process group from chromatin.run
-        env = {k: os.environ.pop(k) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+        env = {k: os.environ.pop(k) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK") if k in os.environ}
         import expecto_b200.shard as sh
         real = (sh.init_distributed, sh.barrier, sh.allreduce_sum_ints, sh.shard_range)
         sh.init_distributed = lambda backend=None: (0, 1, local)
