@@ -154,6 +154,8 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
   }
   p.m_tiles = (p.m_rows + 128 * CG - 1) / (128 * CG);
   p.n_chunks = p.n_total / BN;
+  static const int dbg = getenv("BX_DEBUG_FLAGS") ? atoi(getenv("BX_DEBUG_FLAGS")) : 0;  // timing diagnostics only
+  p.debug_flags = dbg;
   const int units = p.m_tiles * p.n_chunks * p.k_splits;
   int clusters = std::min(units, c->num_sms / CG);
   if (clusters < 1) clusters = 1;

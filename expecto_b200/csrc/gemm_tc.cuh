@@ -43,6 +43,7 @@ struct GemmParams {
   int ld_out;        // output leading dimension in elements
   int n_store;       // columns >= n_store are not stored
   long long split_stride;  // elements between split-K slices of the output (EPI_PARTIAL_F32)
+  int debug_flags;   // diagnostics only (BX_DEBUG_FLAGS): 1 = no B loads, 2 = no A loads, 4 = no epilogue work
   const float* bias; // [n_total] fp32 (unused for EPI_PARTIAL_F32)
   void* out;
 };
@@ -52,15 +53,20 @@ struct GemmCfg {
   static constexpr int A_ROWS = 128 + (TAPS > 1 ? 8 : 0);
   static constexpr int A_BYTES = A_ROWS * 128;
   static constexpr int B_ROWS = BLOCK_N / CG;
-  static constexpr int B_BYTES = B_ROWS * 128;
+  // taps per B stage: with one tap (4 MMAs) per barrier round trip the single issuing thread, not the tensor
+  // pipe, paced the N=160 layers (~95 cycles per MMA issued vs the 80-cycle MMA); two taps halve that overhead
+  static constexpr int TPS = (TAPS > 1) ? 2 : 1;
+  static constexpr int B_TAP_BYTES = B_ROWS * 128;
+  static constexpr int B_BYTES = TPS * B_TAP_BYTES;
   static constexpr int BIAS_BYTES = 8192;                // fp32 bias vector staged once per CTA
   static constexpr int SMEM_BUDGET = 227 * 1024 - 2048 - BIAS_BYTES;  // barriers + 1 KB alignment slack + bias
   static constexpr int SA = (TAPS > 1) ? 3 : 4;
   static constexpr int SB_MAX = (SMEM_BUDGET - SA * A_BYTES) / B_BYTES;
-  static constexpr int SB = (TAPS > 1) ? (SB_MAX > 16 ? 16 : SB_MAX) : (SB_MAX > SA ? SA : SB_MAX);
+  static constexpr int SB = (TAPS > 1) ? (SB_MAX > 8 ? 8 : SB_MAX) : (SB_MAX > SA ? SA : SB_MAX);
   static constexpr int NBUF = 512 / BLOCK_N;
   static constexpr int SMEM_BYTES = SA * A_BYTES + SB * B_BYTES + 1024 /*barriers*/ + BIAS_BYTES + 1024 /*align*/;
-  static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment (SWIZZLE_128B)");
+  static_assert(B_TAP_BYTES % 1024 == 0, "B tap tile must keep 1024-byte alignment (SWIZZLE_128B)");
+  static_assert(TAPS % TPS == 0, "taps per stage must divide the tap count");
   static_assert(A_BYTES % 1024 == 0, "A stage must keep 1024-byte alignment (SWIZZLE_128B)");
   static_assert(SB >= 2 && NBUF >= 1, "pipeline too shallow");
   static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "invalid UMMA N");
@@ -165,7 +171,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int ncol0 = nc * BLOCK_N + (int)rank * Cfg::B_ROWS;
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
-        if (elect_one()) {
+        if (p.debug_flags & 2) {
+          if (elect_one() && rank == 0) mbar_arrive_local(fullA(ra.idx));
+        } else if (elect_one()) {
           if constexpr (CG == 1) {
             mbar_arrive_expect_tx(fullA(ra.idx), Cfg::A_BYTES);
             tma_load_2d(sA + ra.idx * Cfg::A_BYTES, &tmA, fullA(ra.idx), kb * 64, row0);
@@ -177,16 +185,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         __syncwarp();
         ra.advance<SA>();
 #pragma unroll 1
-        for (int t = 0; t < TAPS; ++t) {
+        for (int t = 0; t < TAPS; t += Cfg::TPS) {
           mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
-          if (elect_one()) {
+          if (p.debug_flags & 1) {
+            if (elect_one() && rank == 0) mbar_arrive_local(fullB(rb.idx));
+          } else if (elect_one()) {
+            const uint32_t dst = sB + rb.idx * Cfg::B_BYTES;
             if constexpr (CG == 1) {
               mbar_arrive_expect_tx(fullB(rb.idx), Cfg::B_BYTES);
-              tma_load_2d(sB + rb.idx * Cfg::B_BYTES, &tmB, fullB(rb.idx), kb * 64, t * p.n_total + ncol0);
+#pragma unroll
+              for (int j = 0; j < Cfg::TPS; ++j)
+                tma_load_2d(dst + j * Cfg::B_TAP_BYTES, &tmB, fullB(rb.idx), kb * 64, (t + j) * p.n_total + ncol0);
             } else {
               if (rank == 0) mbar_arrive_expect_tx(fullB(rb.idx), 2 * Cfg::B_BYTES);
-              tma_load_2d_pair(sB + rb.idx * Cfg::B_BYTES, &tmB, mapa(fullB(rb.idx), 0), kb * 64,
-                               t * p.n_total + ncol0);
+              const uint32_t bar = mapa(fullB(rb.idx), 0);
+#pragma unroll
+              for (int j = 0; j < Cfg::TPS; ++j)
+                tma_load_2d_pair(dst + j * Cfg::B_TAP_BYTES, &tmB, bar, kb * 64, (t + j) * p.n_total + ncol0);
             }
           }
           __syncwarp();
@@ -211,21 +226,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_wait(fullA(ra.idx), ra.phase, 4);
           const uint32_t a_lo = sw128_desc_lo(sA + ra.idx * Cfg::A_BYTES);
 #pragma unroll 1
-          for (int t = 0; t < TAPS; ++t) {
+          for (int t = 0; t < TAPS; t += Cfg::TPS) {
             mbar_wait(fullB(rb.idx), rb.phase, 5);
             tc_fence_after();
             // tap t = the A slab viewed t rows (t*128 B) further down; K advances 32 B per UMMA_K=16
-            const uint32_t at_lo = a_lo + t * 8;
-            const uint32_t b_lo = sw128_desc_lo(sB + rb.idx * Cfg::B_BYTES);
+            const uint32_t b0_lo = sw128_desc_lo(sB + rb.idx * Cfg::B_BYTES);
             if (elect_one()) {
-              if (kcount == 4) {
-                umma_f16<CG>(d, sw128_desc(at_lo), sw128_desc(b_lo), IDESC, accum);
-                umma_f16<CG>(d, sw128_desc(at_lo + 2), sw128_desc(b_lo + 2), IDESC, 1u);
-                umma_f16<CG>(d, sw128_desc(at_lo + 4), sw128_desc(b_lo + 4), IDESC, 1u);
-                umma_f16<CG>(d, sw128_desc(at_lo + 6), sw128_desc(b_lo + 6), IDESC, 1u);
-              } else {
-                for (int k = 0; k < kcount; ++k)
-                  umma_f16<CG>(d, sw128_desc(at_lo + 2 * k), sw128_desc(b_lo + 2 * k), IDESC, k ? 1u : accum);
+#pragma unroll
+              for (int j = 0; j < Cfg::TPS; ++j) {
+                const uint32_t at_lo = a_lo + (t + j) * 8;
+                const uint32_t b_lo = b0_lo + j * (Cfg::B_TAP_BYTES >> 4);
+                if (kcount == 4) {
+                  umma_f16<CG>(d, sw128_desc(at_lo), sw128_desc(b_lo), IDESC, accum);
+                  umma_f16<CG>(d, sw128_desc(at_lo + 2), sw128_desc(b_lo + 2), IDESC, 1u);
+                  umma_f16<CG>(d, sw128_desc(at_lo + 4), sw128_desc(b_lo + 4), IDESC, 1u);
+                  umma_f16<CG>(d, sw128_desc(at_lo + 6), sw128_desc(b_lo + 6), IDESC, 1u);
+                } else if (kcount == 2) {
+                  umma_f16<CG>(d, sw128_desc(at_lo), sw128_desc(b_lo), IDESC, accum);
+                  umma_f16<CG>(d, sw128_desc(at_lo + 2), sw128_desc(b_lo + 2), IDESC, 1u);
+                } else {
+                  for (int k = 0; k < kcount; ++k)
+                    umma_f16<CG>(d, sw128_desc(at_lo + 2 * k), sw128_desc(b_lo + 2 * k), IDESC, k ? 1u : accum);
+                }
+                accum = 1;
               }
               umma_commit<CG>(emptyB(rb.idx));
             }
@@ -274,13 +297,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int j = lane & 3;
 
       // One 16-column chunk: registers -> bias/activation -> global.
-      auto process = [&](const uint32_t (&v)[16], int c) {
-        const float4* bp = reinterpret_cast<const float4*>(sbias + n0 + c * 16);
+      auto process = [&](const uint32_t (&v)[16], int c, const float4 (&bq)[4]) {
         if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU) {
           uint32_t pk[8];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const float4 b4 = bp[i];
+            const float4 b4 = bq[i];
             pk[2 * i] = pack2<T>(fmaxf(__uint_as_float(v[4 * i]) + b4.x, 0.f),
                                  fmaxf(__uint_as_float(v[4 * i + 1]) + b4.y, 0.f));
             pk[2 * i + 1] = pack2<T>(fmaxf(__uint_as_float(v[4 * i + 2]) + b4.z, 0.f),
@@ -288,11 +310,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           T* o = reinterpret_cast<T*>(p.out) + obase + c * 16;
           if constexpr (EPI == EPI_BIAS_RELU) {
-            if (valid) {
-              uint4* dst = reinterpret_cast<uint4*>(o);
-              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-            }
+            // one 256-bit store per lane (STG.256): each warp store touches 32 rows, so halving the instruction
+            // count halves the LSU transactions that bound the conv1 epilogue
+            if (valid) st_global_v8(o, pk);
           } else {
             // MaxPool over the 4 rows held by lanes 4g..4g+3 (rounding is monotonic, so max after
             // rounding equals rounding after max); lane j of the group stores columns 4j..4j+3.
@@ -333,14 +353,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // Software-pipelined TMEM reads: the load of chunk c+1 / c+2 is in flight while chunk c is processed.
       constexpr int NC = BLOCK_N / 16;
       uint32_t va[16], vb[16];
+      float4 qa[4], qb[4];
+      // bias of a chunk is read from shared memory BEFORE the TMEM wait so the two latencies overlap (ncu:
+      // short-scoreboard stalls on these loads were 52 % of the conv1 epilogue's cycles)
+      auto load_bias = [&](float4 (&q)[4], int c) {
+        if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU) {
+          const float4* bp = reinterpret_cast<const float4*>(sbias + n0 + c * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) q[i] = bp[i];
+        }
+      };
+      if (!(p.debug_flags & 4)) {
       tmem_ld16(t0, va);
 #pragma unroll 1
       for (int c = 0; c < NC; c += 2) {
         if (c + 1 < NC) tmem_ld16(t0 + (c + 1) * 16, vb);
+        load_bias(qa, c);
+        if (c + 1 < NC) load_bias(qb, c + 1);
         tmem_ld_wait();
-        process(va, c);
+        process(va, c, qa);
         if (c + 2 < NC) tmem_ld16(t0 + (c + 2) * 16, va);
-        if (c + 1 < NC) process(vb, c + 1);
+        if (c + 1 < NC) process(vb, c + 1, qb);
+      }
       }
       // Release the TMEM buffer to the MMA thread (leader CTA's barrier).
       tc_fence_before();

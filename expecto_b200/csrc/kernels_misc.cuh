@@ -71,26 +71,24 @@ template <> __device__ __forceinline__ uint32_t one_bits<__half>() { return 0x3C
 template <> __device__ __forceinline__ uint32_t one_bits<__nv_bfloat16>() { return 0x3F80u; }
 
 // Write the conv1 operand rows of one window from its codes: row l = [onehot(l), ..., onehot(l+7), 0 x32]
-// (k = tap*4 + channel), 128 bytes per row, one thread per row.
+// (k = tap*4 + channel), 128 bytes per row.  Eight lanes share a row (16 bytes each), so one warp store covers
+// four whole rows = 512 contiguous bytes.
 template <typename T>
 __device__ __forceinline__ void write_im2col_rows(const uint8_t* codes, uint4* __restrict__ dst_rows) {
   const uint32_t one = one_bits<T>();
-  for (int l = threadIdx.x; l < kP1; l += blockDim.x) {
-    uint32_t w[16];
-#pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      const int c = (l + t < kWin + 8) ? codes[l + t] : 4;
-      // channels 0,1 -> word 2t ; channels 2,3 -> word 2t+1
-      w[2 * t] = (c == 0) ? one : (c == 1) ? (one << 16) : 0u;
-      w[2 * t + 1] = (c == 2) ? one : (c == 3) ? (one << 16) : 0u;
+  const int q = threadIdx.x & 7;  // 16-byte piece of the row: pieces 0..3 hold taps 2q, 2q+1; 4..7 are zero
+  for (int l = threadIdx.x >> 3; l < kP1; l += blockDim.x >> 3) {
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (q < 4) {
+      const int c0 = (l + 2 * q < kWin + 8) ? codes[l + 2 * q] : 4;
+      const int c1 = (l + 2 * q + 1 < kWin + 8) ? codes[l + 2 * q + 1] : 4;
+      // channels 0,1 -> first word of the tap ; channels 2,3 -> second word
+      v.x = (c0 == 0) ? one : (c0 == 1) ? (one << 16) : 0u;
+      v.y = (c0 == 2) ? one : (c0 == 3) ? (one << 16) : 0u;
+      v.z = (c1 == 0) ? one : (c1 == 1) ? (one << 16) : 0u;
+      v.w = (c1 == 2) ? one : (c1 == 3) ? (one << 16) : 0u;
     }
-    uint4* o = dst_rows + (size_t)l * 8;
-    o[0] = make_uint4(w[0], w[1], w[2], w[3]);
-    o[1] = make_uint4(w[4], w[5], w[6], w[7]);
-    o[2] = make_uint4(w[8], w[9], w[10], w[11]);
-    o[3] = make_uint4(w[12], w[13], w[14], w[15]);
-    const uint4 z = make_uint4(0, 0, 0, 0);
-    o[4] = z; o[5] = z; o[6] = z; o[7] = z;
+    dst_rows[(size_t)l * 8 + q] = v;
   }
 }
 
