@@ -119,6 +119,50 @@ def cpu_forward_rate(batch: int, min_seconds: float, max_windows: int, seed: int
     return done / dt, cores, torch.get_num_threads(), done, dt
 
 
+def transform_rooflines(dev, peaks, iters: int = 10):
+    """Kernel 4 (decay-weighted shift reductions) as HBM GB/s over the algorithmic bytes of SURVEY §8(d); inputs
+    (1.6 GB / 1.2 GB) are larger than the 126 MB L2."""
+    import numpy as np
+    import torch
+
+    from expecto_b200.transform import decay_transform_fixed, decay_transform_variant, fixed_pos_weights
+
+    out = {}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(dev)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1) / iters * 1e-3
+
+    G = 512
+    probs = torch.rand((G, 200, 2, 2002), dtype=torch.float32, device=dev)
+    w = fixed_pos_weights()
+    res = torch.empty((G, 20020), dtype=torch.float32, device=dev)
+    t = timed(lambda: decay_transform_fixed(probs, w, out=res))
+    b = G * (200 * 2 * 2002 * 4 + 20020 * 4)
+    out["fixed"] = {"genes": G, "bytes_per_gene": b // G, "ms": t * 1e3, "achieved": b / t / 1e9, "unit": "GB/s",
+                    "peak": peaks["hbm_gbs"], "frac": b / t / 1e9 / peaks["hbm_gbs"], "genes_per_s": G / t}
+    del probs, res
+    n = 16384
+    x = torch.rand((9, n, 2002), dtype=torch.float32, device=dev)
+    dist = np.random.default_rng(0).integers(-40000, 40000, size=n).astype(np.float64)
+    strand = np.where(np.arange(n) % 2 == 0, 1, -1)
+    res = torch.empty((n, 20020), dtype=torch.float32, device=dev)
+    t = timed(lambda: decay_transform_variant(x, dist, strand, out=res))
+    b = n * (9 * 2002 * 4 + 20020 * 4 + 9)
+    out["variant"] = {"variants": n, "bytes_per_variant": b // n, "ms": t * 1e3, "achieved": b / t / 1e9,
+                      "unit": "GB/s", "peak": peaks["hbm_gbs"], "frac": b / t / 1e9 / peaks["hbm_gbs"],
+                      "variants_per_s": n / t, "note": "time includes the H2D of dist/strand (host wrapper)"}
+    return out
+
+
 def run_reference(args) -> int:
     """--impl reference: the reference's CPU implementation of the path (oracle port of Beluga.forward, torch
     fp32 on every host core), each step a bounded sample (--ref_batch windows, the reference's default batch of
@@ -292,6 +336,10 @@ def run_gpu(args) -> int:
         "clocks": sampler.summary(),
         "checksum": checksum,
     }
+    if world == 1 and not args.no_transform:
+        del x, out
+        torch.cuda.empty_cache()
+        line["transform_roofline"] = transform_rooflines(dev, peaks)
     if world == 1 and not args.no_cpu_baseline:
         rate, cores, threads, done, dt = cpu_forward_rate(32, args.cpu_seconds, 4096)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
@@ -316,6 +364,7 @@ def main() -> int:
     ap.add_argument("--ref_batch", type=int, default=32)
     ap.add_argument("--cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no_cpu_baseline", action="store_true")
+    ap.add_argument("--no_transform", action="store_true", help="skip the kernel-4 GB/s measurement")
     args = ap.parse_args()
     return run_reference(args) if args.impl == "reference" else run_gpu(args)
 
