@@ -47,7 +47,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--weights", default="./resources/deepsea.beluga.pth", help="state_dict (chromatin.py:103)")
     p.add_argument("--dtype", default="f16", choices=["f16", "bf16"], help="tensor-core operand type")
     p.add_argument("--device", type=int, default=0)
-    p.add_argument("--gpu_batch", type=int, default=8192, help="variants per GPU sub-batch (x4 windows)")
+    p.add_argument("--gpu_batch", type=int, default=4096, help="variants per GPU sub-batch (x4 windows)")
     p.add_argument("--gather", default="nccl", choices=["nccl", "file"],
                    help="multi-GPU (torchrun) only: gather rows to rank 0 over NCCL, or every rank writes its slabs")
     p.add_argument("--upstream_layout", action="store_true",
@@ -90,30 +90,110 @@ def variant_columns(vcf):
     return chroms, pos, refs, alts
 
 
-def predict_shift(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int, sink, pinned=None) -> None:
+class SlabWriter:
+    """Background file writer: the HDF5 row-slab writes of slab k run on a thread while the GPU pipeline
+    computes slab k+1 into the other set of pinned buffers (file output is as large as the GPU produces it —
+    48 KB per variant-shift — so the disk, not the GPU, bounds chromatin.py-style output; SURVEY §7 hard part 4)."""
+
+    def __init__(self, n_sets: int):
+        import queue
+        import threading
+        self._q = queue.Queue()
+        self._free = [threading.Event() for _ in range(n_sets)]
+        for e in self._free:
+            e.set()
+        self._err = None
+        self._next = 0
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def _run(self):
+        while True:
+            item = self._q.get()
+            if item is None:
+                return
+            set_idx, sink, tasks = item
+            try:
+                if set_idx is None:
+                    sink()  # ordered call (closing a finished shift's files)
+                elif self._err is None:
+                    for name, row0, arr in tasks:
+                        sink(name, row0, arr)
+            except BaseException as e:  # surfaced by wait_free / drain
+                self._err = e
+            finally:
+                if set_idx is not None:
+                    self._free[set_idx].set()
+
+    def next_set(self) -> int:
+        """Round-robin buffer set, continuing across shifts; blocks until its previous contents are on disk."""
+        i = self._next
+        self._next = (i + 1) % len(self._free)
+        self.wait_free(i)
+        return i
+
+    def wait_free(self, set_idx: int) -> None:
+        self._free[set_idx].wait()
+        if self._err is not None:
+            raise self._err
+
+    def submit(self, set_idx: int, sink, tasks) -> None:
+        self._free[set_idx].clear()
+        self._q.put((set_idx, sink, tasks))
+
+    def call(self, fn) -> None:
+        """Run ``fn()`` on the writer thread after everything submitted so far."""
+        self._q.put((None, fn, None))
+
+    def drain(self) -> None:
+        for i in range(len(self._free)):
+            self.wait_free(i)
+
+    def close(self) -> None:
+        self._q.put(None)
+        self._t.join()
+        if self._err is not None:
+            raise self._err
+
+
+def predict_shift(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int, sink, pinned=None,
+                  writer: SlabWriter | None = None) -> None:
     """One iteration of chromatin.py:243-286 for all variants.  ``sink(name, row0, array)`` receives
     float32 row slabs of the [2N,2002] datasets (forward rows at v, reverse-complement rows at N+v).
     Each slab of ``gpu_batch`` variants goes through the library's three-stream host pipeline
-    (bx_chromatin_shift_host): descriptors H2D, kernel 1 + forward + diff, ref/alt/diff D2H."""
+    (bx_chromatin_shift_host): descriptors H2D, kernel 1 + forward + diff, ref/alt/diff D2H.
+    ``pinned``: one set of three pinned [2*gpu_batch,2002] tensors, or a list of sets used round-robin with
+    ``writer`` so the file writes of one slab overlap the GPU work of the next."""
     import torch
 
     from .windows import check_valid_bases, chromatin_window_descs
 
     n = len(pos)
-    for v0 in range(0, n, gpu_batch):
+    sets = None
+    if pinned is not None:
+        sets = pinned if isinstance(pinned, list) else [pinned]
+    for k, v0 in enumerate(range(0, n, gpu_batch)):
         v1 = min(n, v0 + gpu_batch)
         m = v1 - v0
         descs, alleles = chromatin_window_descs(genome, chroms[v0:v1], pos[v0:v1], refs[v0:v1], alts[v0:v1], shift)
         check_valid_bases(genome, descs)
-        out = None
-        if pinned is not None:
-            out = tuple(t[:2 * m] for t in pinned)
+        out, si = None, 0
+        if sets is not None:
+            si = writer.next_set() if writer is not None else k % len(sets)
+            out = tuple(t[:2 * m] for t in sets[si])
         ref, alt, diff = engine.chromatin_shift_host(descs, alleles, m, average=False, out=out)
+        tasks = []
         for name, t in (("diff", diff), ("ref", ref), ("alt", alt)):
             h = t.numpy()
-            sink(name, v0, h[:m])
-            sink(name, n + v0, h[m:2 * m])
-    torch.cuda.synchronize(engine.device)
+            tasks.append((name, v0, h[:m]))
+            tasks.append((name, n + v0, h[m:2 * m]))
+        if writer is not None and sets is not None:
+            writer.submit(si, sink, tasks)
+        else:
+            for name, row0, arr in tasks:
+                sink(name, row0, arr)
+    if writer is None:
+        torch.cuda.synchronize(engine.device)
 
 
 def predict_shift_device(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int):
@@ -182,9 +262,12 @@ def run(args, engine=None, genome=None) -> dict:
     n_local = hi - lo
     files, counters = [], None
     gb = max(1, min(args.gpu_batch, max(n_local, 1)))
-    pinned = None
+    pinned, writer = None, None
     if world == 1 or args.gather == "file":
-        pinned = tuple(torch.empty((2 * gb, 2002), dtype=torch.float32, pin_memory=True) for _ in range(3))
+        n_sets = 2  # slab k's file writes overlap slab k+1's GPU work (also across shifts)
+        pinned = [tuple(torch.empty((2 * gb, 2002), dtype=torch.float32, pin_memory=True) for _ in range(3))
+                  for _ in range(n_sets)]
+        writer = SlabWriter(n_sets)
     shapes = {k: (2 * n, 2002) for k in ("diff", "ref", "alt")}
     for shift in shift_list(args.maxshift):
         if shift == 0:
@@ -224,12 +307,18 @@ def run(args, engine=None, genome=None) -> dict:
                 if up is not None and name == "diff":
                     up.write_rows("pred", g0, arr)
 
-            predict_shift(engine, genome, chroms, pos, refs, alts, shift, gb, sink, pinned)
-            w.close()
-            if up is not None:
-                up.close()
-            shard.barrier()
+            predict_shift(engine, genome, chroms, pos, refs, alts, shift, gb, sink, pinned, writer)
+
+            def finish(w=w, up=up):
+                w.close()
+                if up is not None:
+                    up.close()
+
+            writer.call(finish)  # files of this shift close once their slabs are on disk; the next shift starts now
         files.append(path)
+    if writer is not None:
+        writer.close()
+        shard.barrier()
     return {"n_variants": n, "counters": counters, "files": files, "rank": rank, "world": world}
 
 

@@ -711,8 +711,13 @@ int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, i
   if (n_genes < 0 || n_shifts < 1 || n_shifts > 1024) return fail(BX_E_ARG, "invalid arguments");
   if (n_genes == 0) return 0;
   if (!probs_dev || !weights_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
-  const size_t smem = (size_t)(10 * n_shifts + (kTfSlices - 1) * 10 * kTfF) * sizeof(float);
-  dim3 grid((kFeat + kTfF - 1) / kTfF, n_genes), block(kTfF, kTfSlices);
+  const size_t smem = (size_t)(10 * n_shifts + (kTfSlices - 1) * 20 * kTfF) * sizeof(float);
+  dim3 grid((kFeat2 + kTfF - 1) / kTfF, n_genes), block(kTfF, kTfSlices);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(decay_fixed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set = true;
+  }
   decay_fixed_kernel<<<grid, block, smem, (cudaStream_t)stream>>>(probs_dev, weights_dev, n_shifts, out_dev);
   g_launches++;
   CK(cudaGetLastError());
@@ -724,9 +729,12 @@ int bx_decay_transform_variant(const float* x_dev, const double* dist_dev, const
   if (n < 0 || n_shifts < 1 || n_shifts > 25) return fail(BX_E_ARG, "invalid arguments (n_shifts must be 1..25)");
   if (n == 0) return 0;
   if (!x_dev || !dist_dev || !strand_dev || !shifts_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
-  dim3 grid((kFeat + 255) / 256, n);
-  decay_variant_kernel<<<grid, 256, n_shifts * 10 * sizeof(float), (cudaStream_t)stream>>>(
-      x_dev, dist_dev, strand_dev, shifts_dev, n, n_shifts, out_dev);
+  if (n_shifts == 9)  // chromatin.py's 9 shifts: all loads of a column unrolled and in flight together
+    decay_variant_kernel<9><<<n, 256, 0, (cudaStream_t)stream>>>(x_dev, dist_dev, strand_dev, shifts_dev, n, n_shifts,
+                                                                 out_dev);
+  else
+    decay_variant_kernel<0><<<n, 256, 0, (cudaStream_t)stream>>>(x_dev, dist_dev, strand_dev, shifts_dev, n, n_shifts,
+                                                                 out_dev);
   g_launches++;
   CK(cudaGetLastError());
   return 0;

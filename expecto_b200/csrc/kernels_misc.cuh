@@ -217,76 +217,139 @@ __global__ void chromatin_outputs_avg_kernel(const float* __restrict__ probs, in
 }
 
 // ------------------------------------------------------------------ kernel 4: decay-weighted shift reductions
-// Fixed weights (compute_expecto_features.py:123-124).  Block = (gene, 128-feature tile) x 4 shift slices;
-// loads are coalesced along the feature axis, each thread keeps 10 partial sums, slices are combined
-// through shared memory.  probs [G, S, 2, 2002], w [10, S], out [G, 10, 2002].
-constexpr int kTfF = 128, kTfSlices = 4;
+// HBM-bound streaming reductions, coalesced along the 2002-feature axis.  Rows are 8008 bytes, so every row is
+// 8-byte aligned and each thread moves float2 (two features); loads of several shifts are issued back to back
+// so that enough bytes are in flight per SM to cover HBM latency.
+//
+// Fixed weights (compute_expecto_features.py:123-124).  Block = (gene, 256-feature tile) x 4 shift slices; each
+// thread keeps 2 x 10 partial sums, slices are combined through shared memory.
+// probs [G, S, 2, 2002], w [10, S], out [G, 10, 2002].
+constexpr int kTfF = 128, kTfSlices = 4;   // 128 float2 lanes = 256 features per block
+constexpr int kFeat2 = kFeat / 2;          // 1001 float2 per row
 __global__ void __launch_bounds__(kTfF * kTfSlices)
 decay_fixed_kernel(const float* __restrict__ probs, const float* __restrict__ w, int n_shifts,
                    float* __restrict__ out) {
-  extern __shared__ float sm[];                 // w[10*S] then partials [slices-1][10][128]
+  extern __shared__ float sm[];                 // w[10*S] then partials [slices-1][20][128]
   float* sw = sm;
   float* part = sm + 10 * n_shifts;
   const int g = blockIdx.y;
-  const int f = blockIdx.x * kTfF + threadIdx.x;
+  const int f2 = blockIdx.x * kTfF + threadIdx.x;  // float2 index within the row
   const int slice = threadIdx.y;
   for (int i = threadIdx.y * kTfF + threadIdx.x; i < 10 * n_shifts; i += kTfF * kTfSlices) sw[i] = w[i];
   __syncthreads();
-  float acc[10];
+  float2 acc[10];
 #pragma unroll
-  for (int k = 0; k < 10; ++k) acc[k] = 0.f;
-  if (f < kFeat) {
-    const float* p = probs + (size_t)g * n_shifts * 2 * kFeat + f;
-    for (int s = slice; s < n_shifts; s += kTfSlices) {
-      const float x = 0.5f * (__ldg(p + (size_t)(2 * s) * kFeat) + __ldg(p + (size_t)(2 * s + 1) * kFeat));
+  for (int k = 0; k < 10; ++k) acc[k] = make_float2(0.f, 0.f);
+  if (f2 < kFeat2) {
+    const float2* p = reinterpret_cast<const float2*>(probs + (size_t)g * n_shifts * 2 * kFeat) + f2;
+    int s = slice;
+    // two shifts (four rows) per iteration: 4 independent 8-byte loads in flight per thread
+    for (; s + kTfSlices < n_shifts; s += 2 * kTfSlices) {
+      const float2 a0 = __ldg(p + (size_t)(2 * s) * kFeat2), a1 = __ldg(p + (size_t)(2 * s + 1) * kFeat2);
+      const int s2 = s + kTfSlices;
+      const float2 b0 = __ldg(p + (size_t)(2 * s2) * kFeat2), b1 = __ldg(p + (size_t)(2 * s2 + 1) * kFeat2);
+      const float xa0 = 0.5f * (a0.x + a1.x), xa1 = 0.5f * (a0.y + a1.y);
+      const float xb0 = 0.5f * (b0.x + b1.x), xb1 = 0.5f * (b0.y + b1.y);
 #pragma unroll
-      for (int k = 0; k < 10; ++k) acc[k] = fmaf(sw[k * n_shifts + s], x, acc[k]);
+      for (int k = 0; k < 10; ++k) {
+        const float wa = sw[k * n_shifts + s], wb = sw[k * n_shifts + s2];
+        acc[k].x = fmaf(wa, xa0, acc[k].x);
+        acc[k].y = fmaf(wa, xa1, acc[k].y);
+        acc[k].x = fmaf(wb, xb0, acc[k].x);
+        acc[k].y = fmaf(wb, xb1, acc[k].y);
+      }
+    }
+    for (; s < n_shifts; s += kTfSlices) {
+      const float2 a0 = __ldg(p + (size_t)(2 * s) * kFeat2), a1 = __ldg(p + (size_t)(2 * s + 1) * kFeat2);
+      const float xa0 = 0.5f * (a0.x + a1.x), xa1 = 0.5f * (a0.y + a1.y);
+#pragma unroll
+      for (int k = 0; k < 10; ++k) {
+        const float wa = sw[k * n_shifts + s];
+        acc[k].x = fmaf(wa, xa0, acc[k].x);
+        acc[k].y = fmaf(wa, xa1, acc[k].y);
+      }
     }
   }
+  float2* part2 = reinterpret_cast<float2*>(part);
   if (slice > 0) {
 #pragma unroll
-    for (int k = 0; k < 10; ++k) part[((slice - 1) * 10 + k) * kTfF + threadIdx.x] = acc[k];
+    for (int k = 0; k < 10; ++k) part2[((slice - 1) * 10 + k) * kTfF + threadIdx.x] = acc[k];
   }
   __syncthreads();
-  if (slice == 0 && f < kFeat) {
+  if (slice == 0 && f2 < kFeat2) {
+    float2* o = reinterpret_cast<float2*>(out + (size_t)g * 10 * kFeat) + f2;
 #pragma unroll
     for (int k = 0; k < 10; ++k) {
-      float v = acc[k];
-      for (int sl = 0; sl < kTfSlices - 1; ++sl) v += part[(sl * 10 + k) * kTfF + threadIdx.x];
-      out[((size_t)g * 10 + k) * kFeat + f] = v;
+      float2 v = acc[k];
+      for (int sl = 0; sl < kTfSlices - 1; ++sl) {
+        const float2 q = part2[(sl * 10 + k) * kTfF + threadIdx.x];
+        v.x += q.x;
+        v.y += q.y;
+      }
+      o[(size_t)k * kFeat2] = v;
     }
   }
 }
 
-// Per-variant weights (predict.py:87-109) computed in-kernel in fp64, then the same reduction over S
-// shifts.  x [S, n, 2002], out [n, 10, 2002].  Block = (variant, 256-feature tile).
-__global__ void __launch_bounds__(256)
-decay_variant_kernel(const float* __restrict__ x, const double* __restrict__ dist, const int8_t* __restrict__ strand,
-                     const int32_t* __restrict__ shifts, int n, int n_shifts, float* __restrict__ out) {
-  extern __shared__ float sw[];  // [S][10]
-  const int v = blockIdx.y;
+// Weights of one variant for every (shift, basis): predict.py:87-109, evaluated in fp64 like numpy does.
+__device__ __forceinline__ void variant_weights_to_smem(float* sw, double dist, int strand,
+                                                        const int32_t* __restrict__ shifts, int n_shifts) {
   if (threadIdx.x < n_shifts * 10) {
     const int j = threadIdx.x / 10, k = threadIdx.x - j * 10;
-    const double sgn = strand[v] > 0 ? 1.0 : -1.0;
-    const double pos = dist[v] * sgn + (double)shifts[j] * sgn;
+    const double sgn = strand > 0 ? 1.0 : -1.0;
+    const double pos = dist * sgn + (double)shifts[j] * sgn;
     const double rate[5] = {0.01, 0.02, 0.05, 0.1, 0.2};
     const double e = exp(-rate[k % 5] * floor(fabs(pos / 200.0)));
     const bool on = (k < 5) ? (pos <= 0.0) : (pos >= 0.0);
     sw[j * 10 + k] = on ? (float)e : 0.f;
   }
+}
+
+// Per-variant weights, then the same reduction over S shifts.  x [S, n, 2002], out [n, 10, 2002].
+// One block per variant (the fp64 weight prologue is paid once per 152 KB of traffic); each thread streams
+// float2 columns tid, tid+256, ... with all S loads of a column issued before the FMAs.
+constexpr int kTvMaxShifts = 25;
+template <int S_STATIC>
+__global__ void __launch_bounds__(256)
+decay_variant_kernel(const float* __restrict__ x, const double* __restrict__ dist, const int8_t* __restrict__ strand,
+                     const int32_t* __restrict__ shifts, int n, int n_shifts_rt, float* __restrict__ out) {
+  __shared__ float sw[kTvMaxShifts * 10];  // [S][10]
+  const int n_shifts = S_STATIC > 0 ? S_STATIC : n_shifts_rt;
+  const int v = blockIdx.x;
+  variant_weights_to_smem(sw, dist[v], strand[v], shifts, n_shifts);
   __syncthreads();
-  const int f = blockIdx.x * 256 + threadIdx.x;
-  if (f >= kFeat) return;
-  float acc[10];
+  const float2* xp = reinterpret_cast<const float2*>(x + (size_t)v * kFeat);
+  float2* op = reinterpret_cast<float2*>(out + (size_t)v * 10 * kFeat);
+  const size_t shift_stride = (size_t)n * kFeat2;
+  for (int f2 = threadIdx.x; f2 < kFeat2; f2 += 256) {
+    float2 acc[10];
 #pragma unroll
-  for (int k = 0; k < 10; ++k) acc[k] = 0.f;
-  for (int j = 0; j < n_shifts; ++j) {
-    const float xv = __ldg(x + ((size_t)j * n + v) * kFeat + f);
+    for (int k = 0; k < 10; ++k) acc[k] = make_float2(0.f, 0.f);
+    if constexpr (S_STATIC > 0) {
+      float2 xv[S_STATIC];
 #pragma unroll
-    for (int k = 0; k < 10; ++k) acc[k] = fmaf(sw[j * 10 + k], xv, acc[k]);
+      for (int j = 0; j < S_STATIC; ++j) xv[j] = __ldg(xp + (size_t)j * shift_stride + f2);
+#pragma unroll
+      for (int j = 0; j < S_STATIC; ++j) {
+#pragma unroll
+        for (int k = 0; k < 10; ++k) {
+          acc[k].x = fmaf(sw[j * 10 + k], xv[j].x, acc[k].x);
+          acc[k].y = fmaf(sw[j * 10 + k], xv[j].y, acc[k].y);
+        }
+      }
+    } else {
+      for (int j = 0; j < n_shifts; ++j) {
+        const float2 xv = __ldg(xp + (size_t)j * shift_stride + f2);
+#pragma unroll
+        for (int k = 0; k < 10; ++k) {
+          acc[k].x = fmaf(sw[j * 10 + k], xv.x, acc[k].x);
+          acc[k].y = fmaf(sw[j * 10 + k], xv.y, acc[k].y);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 10; ++k) op[(size_t)k * kFeat2 + f2] = acc[k];
   }
-#pragma unroll
-  for (int k = 0; k < 10; ++k) out[((size_t)v * 10 + k) * kFeat + f] = acc[k];
 }
 
 // Per-variant transform fused with gblinear scoring (predict.py:123-160): the 20020 features of a variant are
@@ -304,15 +367,7 @@ decay_score_variant_kernel(const float* __restrict__ x, const double* __restrict
   float* red = sw + n_shifts * 10;
   const int v = blockIdx.x;
   const int m0 = blockIdx.y * kScoreModels;
-  if (threadIdx.x < n_shifts * 10) {
-    const int j = threadIdx.x / 10, k = threadIdx.x - j * 10;
-    const double sgn = strand[v] > 0 ? 1.0 : -1.0;
-    const double pos = dist[v] * sgn + (double)shifts[j] * sgn;
-    const double rate[5] = {0.01, 0.02, 0.05, 0.1, 0.2};
-    const double e = exp(-rate[k % 5] * floor(fabs(pos / 200.0)));
-    const bool on = (k < 5) ? (pos <= 0.0) : (pos >= 0.0);
-    sw[j * 10 + k] = on ? (float)e : 0.f;
-  }
+  variant_weights_to_smem(sw, dist[v], strand[v], shifts, n_shifts);
   __syncthreads();
   float acc[kScoreModels];
 #pragma unroll
