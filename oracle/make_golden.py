@@ -231,12 +231,61 @@ def stage_predict(work):
     print(f"[predict] sed.tsv rows {len(sed)}; oracle == reference (REF/ALT within 1e-4)")
 
 
+def closest_gene_inputs():
+    """A 700-gene slice of the reference's own resources/geneanno.csv (chr1, chr13 incl. two genes sharing one TSS,
+    chrX) and a VCF that exercises ties, exact-TSS hits, dense and gene-free neighbourhoods."""
+    import pandas as pd
+    g = pd.read_csv(os.path.join(REF, "resources", "geneanno.csv"), index_col=0)
+    sub = pd.concat([g[g["seqnames"] == "chr1"].iloc[:400], g[g["seqnames"] == "chr13"], g[g["seqnames"] == "chrX"].iloc[:60]])
+    rng = np.random.default_rng(12)
+    rows = [l.rstrip("\n").split("\t") for l in open(os.path.join(REF, "example", "example.vcf"))]
+    rows = [[r[0], int(r[1]), r[2], r[3], r[4]] for r in rows]
+    for chrom in ("chr1", "chr13", "chrX"):
+        t = np.sort(sub[sub["seqnames"] == chrom]["CAGE_representative_TSS"].values)
+        for k in range(12):
+            i = int(rng.integers(0, len(t) - 1))
+            rows.append([chrom, int((t[i] + t[i + 1]) // 2), f"mid{k}", "A", "C"])       # midpoints: ties when the gap is even
+            rows.append([chrom, int(t[i] + rng.integers(-30000, 30000)), f"rnd{k}", "G", "T"])
+        rows.append([chrom, int(t[5]), "on_tss", "A", "G"])
+        rows.append([chrom, int(t[-1] + 5_000_000), "far_right", "C", "T"])
+        rows.append([chrom, max(1, int(t[0] - 900_000)), "far_left", "C", "A"])
+    rows.append(["chr13", 57715052, "shared_tss", "A", "T"])      # PRR20A / PRR20C share this TSS: first annotation row wins
+    rows.append(["chr13", 57715052 + 20300, "rf_edge_plus", "A", "T"])
+    rows.append(["chr13", 57715052 - 20499, "rf_edge_minus", "A", "T"])
+    return sub, rows
+
+
+def stage_closest_genes(work):
+    sub, rows = closest_gene_inputs()
+    anno = os.path.join(work, "geneanno_sub.csv")
+    sub.to_csv(anno)
+    vcf = os.path.join(work, "closest_in.vcf")
+    with open(vcf, "w") as f:
+        for r in rows:
+            f.write("\t".join(str(x) for x in r) + "\n")
+    out = {}
+    for mode, flag in (("closest", []), ("rf", ["--all_in_receptive_field"])):
+        run_ref_script("make_closest_genes_file.py", ["closest_in.vcf", "--geneanno_file", "geneanno_sub.csv", "-o",
+                                                      f"out_closest_{mode}"] + flag, work)
+        out[f"{mode}_tsv"] = np.array(open(os.path.join(work, f"out_closest_{mode}", "closest_genes.tsv")).read())
+        out[f"{mode}_vcf"] = np.array(open(os.path.join(work, f"out_closest_{mode}", "snps_hg19.vcf")).read())
+    np.savez_compressed(os.path.join(GOLD, "closest_genes_golden.npz"), geneanno_csv=np.array(open(anno).read()),
+                        vcf=np.array(open(vcf).read()), **out)
+    print(f"[closest genes] {len(rows)} variants x {len(sub)} genes: reference outputs stored "
+          f"({str(out['closest_tsv']).count(chr(10))} / {str(out['rf_tsv']).count(chr(10))} rows)")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workdir", default="/tmp/bx_golden")
     ap.add_argument("--skip-scripts", action="store_true", help="only the import-level stages (fast)")
+    ap.add_argument("--only-closest", action="store_true", help="only the make_closest_genes_file.py stage")
     args = ap.parse_args()
     os.makedirs(GOLD, exist_ok=True)
+    if args.only_closest:
+        os.makedirs(args.workdir, exist_ok=True)
+        stage_closest_genes(args.workdir)
+        return
     stage_encode()
     sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
     stage_beluga(sd)
@@ -245,6 +294,7 @@ def main():
         stage_chromatin(args.workdir, sd, genome)
         stage_features(args.workdir, sd, genome)
         stage_predict(args.workdir)
+        stage_closest_genes(args.workdir)
     print("golden fixtures written to", GOLD)
 
 
