@@ -116,6 +116,9 @@ struct bx_ctx {
   size_t stage_out_bytes = 0;
   float* probs_scratch = nullptr;
   size_t probs_scratch_bytes = 0;
+  // segment mode: phase-B conv6 output and the dense FC1 operand gathered from the segment activations
+  void* act6b = nullptr;
+  void* fc_in = nullptr;
 };
 
 // RAII-ish stage timer: records an event pair around a stage when profiling is on.
@@ -289,6 +292,58 @@ static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st) {
   return run_fc2(c, n, probs, st);
 }
 
+// ------------------------------------------------------------------ segment mode
+// Row pitches of every activation for "windows" of L positions (L = 2000 reproduces kLayers).
+struct Geom {
+  int L, p1, p2, p3, p4, p5, p6, l4b;
+};
+static Geom make_geom(int L) {
+  Geom g;
+  g.L = L;
+  g.p1 = (L - 7 + 3) / 4 * 4;       // conv1 rows (L-7 valid), pooled by conv2's epilogue -> multiple of 4
+  g.p2 = (L - 14) / 4;               // conv2 + MaxPool4
+  g.p3 = (g.p2 - 7 + 3) / 4 * 4;     // conv3 rows, pooled by conv4's epilogue
+  g.p4 = (g.p2 - 14) / 4;            // conv4 + MaxPool4 (phase A: pooling groups start at row 0)
+  g.l4b = (g.p2 - 16) / 4;           // phase B: pooling groups start at row 2
+  g.p5 = g.p4 - 7;
+  g.p6 = g.p5 - 7;
+  return g;
+}
+
+// conv layer i over n_seg segments with explicit geometry; phase_b shifts conv4's input by two rows.
+static int run_conv_geom(bx_ctx* c, int i, int n_seg, const Geom& g, const void* in, void* out, bool phase_b,
+                         cudaStream_t st) {
+  const LayerDef& L = kLayers[i];
+  const int pin[6] = {g.p1, g.p1, g.p2, g.p3, g.p4, g.p5};
+  const int pout[6] = {g.p1, g.p2, g.p3, g.p4, g.p5, g.p6};
+  GemmParams p = {};
+  const int skip = phase_b ? 2 : 0;
+  p.m_rows = n_seg * pin[i] - skip;
+  p.k_valid = (i == 0) ? 32 : L.cin;
+  p.n_total = L.cout;
+  p.k_splits = 1;
+  p.k_blocks = (p.k_valid + 63) / 64;
+  p.kb_per_split = p.k_blocks;
+  p.pitch_in = pin[i];
+  p.pitch_out = pout[i];
+  p.l_store = (i == 3 && phase_b) ? g.l4b : pout[i];
+  p.ld_out = L.cout;
+  p.n_store = L.cout;
+  p.bias = c->bconv[i];
+  p.out = out;
+  const char* a = reinterpret_cast<const char*>(in) + (size_t)skip * L.cin * 2;
+  return launch_gemm(c, L.taps, L.block_n, L.epi, a, (uint64_t)p.m_rows, L.cin, c->wconv[i], (uint64_t)L.taps * L.cout,
+                     p, st);
+}
+
+// Largest number of L-position segments whose activations fit the scratch sized for `cap` 2000-bp windows.
+static int max_segments(const bx_ctx* c, const Geom& g) {
+  const int need[7] = {g.p1, g.p1, g.p2, g.p3, g.p4, g.p5, g.p6};
+  long long best = 1LL << 40;
+  for (int i = 0; i < 7; ++i) best = std::min(best, (long long)c->cap * (long long)act_rows(i) / need[i]);
+  return (int)std::max(0LL, best);
+}
+
 // ------------------------------------------------------------------ C ABI
 extern "C" {
 
@@ -352,6 +407,7 @@ int bx_ctx_destroy(bx_ctx* c) {
     if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
   }
   cudaFree(c->probs_scratch);
+  cudaFree(c->act6b); cudaFree(c->fc_in);
   if (c->s_comp) cudaStreamDestroy(c->s_comp);
   if (c->s_in) cudaStreamDestroy(c->s_in);
   if (c->s_out) cudaStreamDestroy(c->s_out);
@@ -754,6 +810,106 @@ int bx_decay_score_variant(const float* x_dev, const double* dist_dev, const int
                                                                         offset_dev, n, n_shifts, n_models, out_dev);
   g_launches++;
   CK(cudaGetLastError());
+  return 0;
+}
+
+int bx_segment_capacity(bx_ctx* c, int seg_len) {
+  if (!c || seg_len < 2000) return fail(BX_E_ARG, "invalid arguments");
+  return max_segments(c, make_geom(seg_len));
+}
+
+int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n_groups,
+                        int segs_per_group, int seg_len, int n_shifts, const int32_t* k_of_shift, int shift_major,
+                        float* probs_dev, void* stream) {
+  if (!c || n_groups < 0 || !k_of_shift) return fail(BX_E_ARG, "invalid arguments");
+  if (n_groups == 0) return 0;
+  if (!descs_dev || !alleles_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
+  if (segs_per_group < 1 || n_shifts < 1 || n_shifts > 200 || seg_len != 2000 + 200 * (n_shifts - 1))
+    return fail(BX_E_ARG, "segment mode needs seg_len == 2000 + 200*(n_shifts-1) and 1 <= n_shifts <= 200");
+  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  CK(cudaSetDevice(c->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const Geom g = make_geom(seg_len);
+  const int seg_cap = max_segments(c, g);
+  const int grp_cap = seg_cap / segs_per_group;
+  if (grp_cap < 1)
+    return fail(BX_E_ARG, "context capacity (%d windows) is too small for %d segments of %d positions", c->cap,
+                segs_per_group, seg_len);
+  if (!c->act6b) CK(cudaMalloc(&c->act6b, (size_t)c->cap * act_rows(6) * act_cols(6) * 2));
+  if (!c->fc_in) CK(cudaMalloc(&c->fc_in, (size_t)c->cap * 106 * 640 * 2));
+  SegGather sg = {};
+  sg.segs_per_group = segs_per_group;
+  sg.n_shifts = n_shifts;
+  sg.shift_major = shift_major ? 1 : 0;
+  sg.p6 = g.p6;
+  for (int i = 0; i < n_shifts; ++i) {
+    if (k_of_shift[i] < 0 || k_of_shift[i] >= n_shifts) return fail(BX_E_ARG, "k_of_shift[%d] out of range", i);
+    sg.k_of_shift[i] = k_of_shift[i];
+  }
+  const bool f16 = c->dtype == BX_DTYPE_F16;
+  // Groups are processed in chunks that fit the activation scratch; with shift-major output order a chunk's
+  // windows are not contiguous in probs_dev, so chunks are only allowed there when one chunk covers everything.
+  if (shift_major && n_groups > grp_cap)
+    return fail(BX_E_ARG, "shift-major output needs all %d groups in one chunk (capacity %d): split the call", n_groups,
+                grp_cap);
+  for (int g0 = 0; g0 < n_groups; g0 += grp_cap) {
+    const int ng = std::min(grp_cap, n_groups - g0);
+    const int ns = ng * segs_per_group;
+    const bx_window_desc* d = descs_dev + (size_t)g0 * segs_per_group;
+    {
+      StageTimer t(c, 0, st);
+      dim3 grid((g.p1 * 8 + 255) / 256, ns);
+      if (f16)
+        encode_im2col_seg_kernel<__half><<<grid, 256, 0, st>>>(d, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                               (__half*)c->act[0], seg_len, g.p1);
+      else
+        encode_im2col_seg_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(d, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                                      (__nv_bfloat16*)c->act[0], seg_len, g.p1);
+      g_launches++;
+      CK(cudaGetLastError());
+    }
+    for (int i = 0; i < 4; ++i) {  // conv1..conv4 (phase A pooling)
+      StageTimer t(c, 1 + i, st);
+      if (int r = run_conv_geom(c, i, ns, g, c->act[i], c->act[i + 1], false, st)) return r;
+    }
+    for (int phase = 0; phase < 2; ++phase) {
+      if (phase == 1) {
+        if (n_shifts < 2) break;
+        StageTimer t(c, 4, st);
+        if (int r = run_conv_geom(c, 3, ns, g, c->act[3], c->act[4], true, st)) return r;
+      }
+      { StageTimer t(c, 5, st); if (int r = run_conv_geom(c, 4, ns, g, c->act[4], c->act[5], false, st)) return r; }
+      { StageTimer t(c, 6, st);
+        if (int r = run_conv_geom(c, 5, ns, g, c->act[5], phase ? c->act6b : c->act[6], false, st)) return r; }
+    }
+    // dense layers per window, in final output order, `cap` windows at a time
+    sg.n_groups = ng;
+    const long long n_win = (long long)ns * n_shifts;
+    float* out = probs_dev + (size_t)g0 * segs_per_group * n_shifts * BX_FEATURES;  // group-major chunks are contiguous
+    void* saved = c->act[6];
+    for (long long w0 = 0; w0 < n_win; w0 += c->cap) {
+      const int m = (int)std::min<long long>(c->cap, n_win - w0);
+      {
+        StageTimer t(c, 7, st);
+        if (f16)
+          gather_fc1_kernel<__half><<<m, 256, 0, st>>>((const __half*)saved, (const __half*)c->act6b, d, sg, w0,
+                                                       (__half*)c->fc_in);
+        else
+          gather_fc1_kernel<__nv_bfloat16><<<m, 256, 0, st>>>((const __nv_bfloat16*)saved,
+                                                              (const __nv_bfloat16*)c->act6b, d, sg, w0,
+                                                              (__nv_bfloat16*)c->fc_in);
+        g_launches++;
+        CK(cudaGetLastError());
+        c->act[6] = c->fc_in;  // run_fc1 reads its operand from act[6]
+        const int r = run_fc1(c, m, st);
+        c->act[6] = saved;
+        if (r) return r;
+      }
+      StageTimer t(c, 8, st);
+      if (int r = run_fc2(c, m, out + (size_t)w0 * BX_FEATURES, st)) return r;
+    }
+  }
   return 0;
 }
 

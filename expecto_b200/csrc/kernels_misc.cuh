@@ -123,6 +123,84 @@ __global__ void onehot_im2col_kernel(const uint8_t* __restrict__ onehot, T* __re
   write_im2col_rows<T>(codes, reinterpret_cast<uint4*>(a0) + (size_t)blockIdx.x * kP1 * 8);
 }
 
+// ------------------------------------------------------------------ segment mode (shared activations)
+// The 9 (chromatin.py:243) or 200 (compute_expecto_features.py:88) shifted windows of one variant / gene overlap
+// almost entirely: they are 2000-bp substrings, 200 bp apart, of ONE strand-oriented sequence (the "segment":
+// 3600 or 41800 positions; for an alt allele the spliced sequence).  A valid convolution's output at a sequence
+// position does not depend on which window asked for it, and both MaxPool(1,4) stages keep their alignment for
+// offsets that are multiples of 16 (even multiples of the 200-bp step) — odd multiples fall on the second pool's
+// phase 2.  So the conv stack runs once per segment (twice from conv4's pooling on: phase A / phase B) and only
+// the dense layers run per window, on 106-row slices of the segment's conv6 output.  Every window's result is
+// bit-identical to the per-window path (same dot products, same order).
+//
+// Strand-oriented code of position i of a segment of length L described like a window (bx_window_desc).
+__device__ __forceinline__ int segment_code(const bx_window_desc& d, int i, int L, const uint32_t* __restrict__ bases2,
+                                            const uint32_t* __restrict__ nmask, const uint8_t* __restrict__ alleles,
+                                            int64_t n_bases) {
+  if (i < 0 || i >= L) return 4;
+  const bool rc = d.flags & 1;
+  int c = window_code(d, rc ? (L - 1 - i) : i, bases2, nmask, alleles, n_bases);
+  if (rc && c < 4) c = 3 - c;
+  return c;
+}
+
+// conv1 operand rows of segments: a0 [n_seg * pitch, 64]; grid (ceil(pitch*8/256), n_seg); one thread per
+// 16-byte piece of a row (two taps), codes fetched straight from the packed genome (L2-resident re-reads).
+template <typename T>
+__global__ void __launch_bounds__(256)
+encode_im2col_seg_kernel(const bx_window_desc* __restrict__ descs, const uint8_t* __restrict__ alleles,
+                         const uint32_t* __restrict__ bases2, const uint32_t* __restrict__ nmask, int64_t n_bases,
+                         T* __restrict__ a0, int L, int pitch) {
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  const int l = idx >> 3, q = idx & 7;
+  if (l >= pitch) return;
+  const bx_window_desc d = descs[blockIdx.y];
+  const uint32_t one = one_bits<T>();
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (q < 4) {
+    const int c0 = segment_code(d, l + 2 * q, L, bases2, nmask, alleles, n_bases);
+    const int c1 = segment_code(d, l + 2 * q + 1, L, bases2, nmask, alleles, n_bases);
+    v.x = (c0 == 0) ? one : (c0 == 1) ? (one << 16) : 0u;
+    v.y = (c0 == 2) ? one : (c0 == 3) ? (one << 16) : 0u;
+    v.z = (c1 == 0) ? one : (c1 == 1) ? (one << 16) : 0u;
+    v.w = (c1 == 2) ? one : (c1 == 3) ? (one << 16) : 0u;
+  }
+  reinterpret_cast<uint4*>(a0)[((size_t)blockIdx.y * pitch + l) * 8 + q] = v;
+}
+
+// Geometry of the window -> segment mapping handed to the gather kernel.
+struct SegGather {
+  int n_groups;       // variants / genes in this chunk
+  int segs_per_group; // 4 (ref fwd, ref rc, alt fwd, alt rc) or 2 (fwd, rc)
+  int n_shifts;       // windows per segment
+  int shift_major;    // 1: window index = (shift, group, seg) [chromatin]; 0: (group, shift, seg) [TSS]
+  int p6;             // rows per segment of the conv6 output
+  int k_of_shift[200]; // offset index (window start = 200*k positions into a non-reversed segment) per shift index
+};
+
+// FC1 operand rows: dense [n_windows, 106*640] gathered from the segment-level conv6 outputs (phase A / B).
+// One block per window; 135,680 contiguous bytes each.  Window w0 + blockIdx.x of the final output order.
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_fc1_kernel(const T* __restrict__ act6a, const T* __restrict__ act6b, const bx_window_desc* __restrict__ descs,
+                  const SegGather g, long long w0, T* __restrict__ dst) {
+  const long long w = w0 + blockIdx.x;
+  const int q = (int)(w % g.segs_per_group);
+  const long long r = w / g.segs_per_group;
+  int grp, si;
+  if (g.shift_major) { si = (int)(r / g.n_groups); grp = (int)(r % g.n_groups); }
+  else { grp = (int)(r / g.n_shifts); si = (int)(r % g.n_shifts); }
+  const long long seg = (long long)grp * g.segs_per_group + q;
+  int k = g.k_of_shift[si];
+  if (descs[seg].flags & 2) k = g.n_shifts - 1 - k;  // reversed offset order (rc segments, '-' strand genes)
+  const int j = k >> 1;
+  const T* src = ((k & 1) ? act6b : act6a) + ((size_t)seg * g.p6 + ((k & 1) ? 12 : 0) + 25 * j) * 640;
+  const uint4* s4 = reinterpret_cast<const uint4*>(src);
+  uint4* d4 = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * 106 * 640);
+  constexpr int N16 = 106 * 640 * 2 / 16;
+  for (int i = threadIdx.x; i < N16; i += 256) d4[i] = __ldg(s4 + i);
+}
+
 // ------------------------------------------------------------------ weight re-layout (run once)
 template <typename T> __device__ __forceinline__ T to_t(float v);
 template <> __device__ __forceinline__ __half to_t<__half>(float v) { return __float2half_rn(v); }

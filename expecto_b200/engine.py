@@ -120,6 +120,31 @@ class BelugaEngine:
                                        _stream_ptr(self.device)))
         return out
 
+    def segment_capacity(self, seg_len: int) -> int:
+        """Segments of ``seg_len`` positions per chunk of this engine's activation scratch."""
+        r = lib().bx_segment_capacity(self._ctx, int(seg_len))
+        if r < 0:
+            check(r)
+        return int(r)
+
+    def forward_segments(self, descs: np.ndarray, alleles: np.ndarray, n_groups: int, segs_per_group: int,
+                         seg_len: int, k_of_shift: np.ndarray, shift_major: bool,
+                         out: torch.Tensor | None = None) -> torch.Tensor:
+        """Segment mode (bx_forward_segments): all shifted windows of ``n_groups`` variants / genes with the conv
+        stack evaluated once per segment.  Returns fp32 [n_shifts, n_groups, segs, 2002] (``shift_major``) or
+        [n_groups, n_shifts, segs, 2002]; bit-identical to ``forward_windows`` on the same windows."""
+        k = np.ascontiguousarray(k_of_shift, dtype=np.int32)
+        S = int(k.size)
+        assert len(descs) == n_groups * segs_per_group
+        d, a = self._upload_descs(descs, alleles)
+        shape = (S, n_groups, segs_per_group, N_FEATURES) if shift_major else (n_groups, S, segs_per_group, N_FEATURES)
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float32, device=self.device)
+        check(lib().bx_forward_segments(self._ctx, d.data_ptr(), a.data_ptr(), n_groups, segs_per_group, int(seg_len), S,
+                                        k.ctypes.data_as(C.POINTER(C.c_int32)), 1 if shift_major else 0,
+                                        out.data_ptr(), _stream_ptr(self.device)))
+        return out
+
     def forward_onehot(self, onehot: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
         """``onehot``: uint8/bool [n,4,2000] (or [n,4,1,2000]) on this device -> fp32 [n,2002]."""
         x = onehot.reshape(-1, 4, WINDOW)

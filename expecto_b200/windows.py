@@ -125,3 +125,83 @@ def allele_match_counts(genome: PackedGenome, chroms, pos, refs: list[str], alts
         ref_ok += g == r.upper()
         alt_ok += g == a.upper()
     return ref_ok, alt_ok, len(refs)
+
+
+# ------------------------------------------------------------------ segment mode (shared activations)
+SHIFT_STEP = 200
+
+
+def chromatin_shift_list(maxshift: int) -> list[int]:
+    return [0] + list(range(-200, -maxshift - 1, -200)) + list(range(200, maxshift + 1, 200))  # chromatin.py:243
+
+
+def segment_eligible(ref_len: np.ndarray, alt_len: np.ndarray) -> np.ndarray:
+    """Variants whose 2*maxshift/200+1 shifted windows are all plain 2000-bp substrings of one spliced sequence:
+    the centre crop must start inside the left flank for both alleles (deletions of at most 100 bp, chromatin.py:164)
+    and the right flank must exist at every shift (len(ref) <= 250, chromatin.py:209).  The rest (rare, long
+    indels) go through the per-window path, which follows the reference's Python slice semantics literally."""
+    ref_len = np.asarray(ref_len, dtype=np.int64)
+    alt_len = np.asarray(alt_len, dtype=np.int64)
+    return (ref_len <= 250) & (alt_len - ref_len >= -100) & (alt_len <= 1000) & (ref_len >= 1) & (alt_len >= 0)
+
+
+def _allele_segment(genome, coff, pos, ref_len, la, aoff, maxshift, rc):
+    n = len(pos)
+    seg_len = INPUTSIZE + 2 * maxshift
+    a = np.floor_divide(100 + (la - ref_len), 2)             # crop start, chromatin.py:164
+    v = coff + pos - 1                                        # global index of the variant's first base
+    len1 = maxshift + 1049 - a                                # left flank inside the segment
+    d = np.zeros(n, dtype=DESC_DTYPE)
+    d["g1"] = v - len1
+    d["len1"] = len1
+    d["alen"] = la
+    d["aoff"] = aoff
+    d["g2"] = v + ref_len
+    d["len2"] = seg_len - len1 - la
+    d["flags"] = 3 if rc else 0                               # rc segments: reversed strand AND reversed offsets
+    return d
+
+
+def chromatin_segment_descs(genome: PackedGenome, chroms, pos, refs: list[str], alts: list[str], maxshift: int = 800):
+    """Four segments per variant, order {ref fwd, ref rc, alt fwd, alt rc}: the sequences every shifted window of
+    fetchSeqs + encodeSeqs (chromatin.py:175-209,164) is a substring of.  Window of shift s starts 200*k positions
+    into a forward segment, k = (s + maxshift)/200, and 200*(n_shifts-1-k) into a reverse-complement segment.
+    Returns (descs [4N], allele codes, k_of_shift int32 [n_shifts]); callers must pre-filter with segment_eligible."""
+    n = len(pos)
+    tab = AlleleTable(list(refs) + list(alts))
+    rl, al = tab.lengths[:n], tab.lengths[n:]
+    ro, ao = tab.offsets[:n], tab.offsets[n:]
+    if not np.all(segment_eligible(rl, al)):
+        raise ValueError("chromatin_segment_descs needs variants pre-filtered with segment_eligible")
+    pos = np.asarray(pos, dtype=np.int64)
+    coff = np.fromiter((genome.offsets[c] for c in chroms), dtype=np.int64, count=n)
+    out = np.zeros((n, 4), dtype=DESC_DTYPE)
+    out[:, 0] = _allele_segment(genome, coff, pos, rl, rl, ro, maxshift, False)
+    out[:, 1] = _allele_segment(genome, coff, pos, rl, rl, ro, maxshift, True)
+    out[:, 2] = _allele_segment(genome, coff, pos, rl, al, ao, maxshift, False)
+    out[:, 3] = _allele_segment(genome, coff, pos, rl, al, ao, maxshift, True)
+    k = np.array([(s + maxshift) // SHIFT_STEP for s in chromatin_shift_list(maxshift)], dtype=np.int32)
+    return out.reshape(-1), tab.codes, k
+
+
+def tss_segment_descs(genome: PackedGenome, chroms, tss, strand, shifts, windowsize: int = INPUTSIZE):
+    """Two segments per gene, order {fwd, rc}, covering the windows of compute_expecto_features.py:105-111
+    (``tss + shift*strand - 999 .. + 1000``).  ``shifts`` must be an arithmetic progression with step 200.
+    For '-' genes the windows run backwards along the forward segment (flags bit 1)."""
+    shifts = np.asarray(shifts, dtype=np.int64)
+    S = len(shifts)
+    if S > 1 and not np.all(np.diff(shifts) == SHIFT_STEP):
+        raise ValueError("segment mode needs shifts in steps of 200")
+    n = len(tss)
+    tss = np.asarray(tss, dtype=np.int64)
+    strand = np.asarray(strand, dtype=np.int64)
+    coff = np.fromiter((genome.offsets[c] for c in chroms), dtype=np.int64, count=n)
+    seg_len = windowsize + SHIFT_STEP * (S - 1)
+    first = np.where(strand > 0, shifts[0], -shifts[-1])       # smallest shift*strand
+    start0 = coff + tss + first - int(windowsize / 2 - 1) - 1
+    d = np.zeros((n, 2), dtype=DESC_DTYPE)
+    d["g1"] = start0[:, None]
+    d["len1"] = seg_len
+    d["flags"][:, 0] = np.where(strand > 0, 0, 2)
+    d["flags"][:, 1] = np.where(strand > 0, 3, 1)
+    return d.reshape(-1), np.arange(S, dtype=np.int32), seg_len

@@ -127,6 +127,20 @@ int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, i
 int bx_decay_transform_variant(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
                                const int32_t* shifts_dev, int n, int n_shifts, float* out_dev, void* stream);
 
+/* Segment mode — the whole shift loop of one variant / gene with shared activations.  The 9 windows of
+ * chromatin.py:243 (or the 200 of compute_expecto_features.py:88) are 2000-bp substrings, 200 bp apart, of one
+ * strand-oriented sequence of seg_len = 2000 + 200*(n_shifts-1) positions; the conv stack runs once per segment
+ * and only the dense layers run per window.  Results are bit-identical to bx_forward_windows on the same windows.
+ * descs_dev: n_groups*segs_per_group segment descriptors (same struct, len1+alen+len2 = seg_len; flags bit 0 =
+ * reverse complement, bit 1 = window offsets run backwards: window of shift index i starts at 200*(n_shifts-1-k)
+ * instead of 200*k, k = k_of_shift[i]).  probs_dev fp32 [n_windows, 2002] ordered (shift, group, seg) when
+ * shift_major != 0 (chromatin.py's per-shift files) or (group, shift, seg) (compute_expecto_features.py). */
+/* How many seg_len-position segments fit one chunk of the context's activation scratch (>= 0), or a negative code. */
+int bx_segment_capacity(bx_ctx* ctx, int seg_len);
+int bx_forward_segments(bx_ctx* ctx, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n_groups,
+                        int segs_per_group, int seg_len, int n_shifts, const int32_t* k_of_shift, int shift_major,
+                        float* probs_dev, void* stream);
+
 /* predict.py:123-160 fused: per-variant decay features contracted with n_models gblinear weight vectors
  * (xgboost Booster.predict = base_score + bias + w.x) without materialising the [n,20020] feature matrix.
  * w_dev fp32 [n_models, 10*2002] (columns removed by cluster_utils.get_keep_mask set to 0), offset_dev fp32

@@ -89,3 +89,46 @@ def test_invalid_genome_char_detected():
     d_bad = tss_descs(pg, ["chr1"], [5200], [1], [0])
     with pytest.raises(KeyError):
         check_valid_bases(pg, d_bad)
+
+
+def test_segment_descriptors_cover_every_shifted_window(small_genome):
+    """Segment mode: each window of every shift is the 2000-bp slice at offset 200*k of its segment."""
+    from expecto_b200.windows import chromatin_segment_descs, chromatin_shift_list, segment_eligible
+    rows = GI.edge_variants(small_genome)
+    ok = segment_eligible([len(r[3]) for r in rows], [len(r[4]) for r in rows])
+    assert 0 < ok.sum() < len(rows)            # the 120-bp deletion etc. are not eligible
+    assert not ok[[r[2] for r in rows].index("del120")] and ok[[r[2] for r in rows].index("ins150")]
+    rows = [r for r, e in zip(rows, ok) if e]
+    pg = PackedGenome.from_sequences(small_genome)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    sdescs, scodes, k_of = chromatin_segment_descs(pg, chroms, pos, refs, alts, 800)
+    seg = decode_descs(pg, sdescs, scodes, length=3600).reshape(len(rows), 4, 4, 3600)
+    for si, shift in enumerate(chromatin_shift_list(800)):
+        wdescs, wcodes = chromatin_window_descs(pg, chroms, pos, refs, alts, shift)
+        win = decode_descs(pg, wdescs, wcodes).reshape(len(rows), 4, 4, 2000)
+        k = int(k_of[si])
+        assert k == (shift + 800) // 200
+        for q in range(4):
+            off = 200 * (8 - k) if q % 2 else 200 * k
+            assert np.array_equal(win[:, q], seg[:, q, :, off:off + 2000]), (shift, q)
+
+
+def test_tss_segment_descriptors(small_genome):
+    from expecto_b200.windows import tss_segment_descs
+    pg = PackedGenome.from_sequences(small_genome)
+    shifts = list(range(-2000, 2000, 200))
+    genes = [("chr1", 30000, 1), ("chr2", 20000, -1)]
+    wd = tss_descs(pg, [g[0] for g in genes], [g[1] for g in genes], [g[2] for g in genes], shifts)
+    win = decode_descs(pg, wd, np.zeros(1, np.uint8)).reshape(2, len(shifts), 2, 4, 2000)
+    sd, k_of, seg_len = tss_segment_descs(pg, [g[0] for g in genes], [g[1] for g in genes], [g[2] for g in genes], shifts)
+    assert seg_len == 2000 + 200 * (len(shifts) - 1)
+    seg = decode_descs(pg, sd, np.zeros(1, np.uint8), length=seg_len).reshape(2, 2, 4, seg_len)
+    S = len(shifts)
+    for gi in range(2):
+        for i in range(S):
+            for q in range(2):
+                k = int(k_of[i])
+                if int(sd.reshape(2, 2)[gi, q]["flags"]) & 2:
+                    k = S - 1 - k
+                assert np.array_equal(win[gi, i, q], seg[gi, q, :, 200 * k:200 * k + 2000]), (gi, i, q)
