@@ -50,6 +50,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--gpu_batch", type=int, default=4096, help="variants per GPU sub-batch (x4 windows)")
     p.add_argument("--gather", default="nccl", choices=["nccl", "file"],
                    help="multi-GPU (torchrun) only: gather rows to rank 0 over NCCL, or every rank writes its slabs")
+    p.add_argument("--mode", default="segments", choices=["segments", "windows"],
+                   help="segments: conv stack once per variant segment (shared activations across shifts, "
+                        "bit-identical); windows: every window separately, as the reference does")
     p.add_argument("--upstream_layout", action="store_true",
                    help="also write upstream ExPecto's {inputfile}.shift_{s}.diff.h5 with one 'pred' dataset")
     return p
@@ -196,6 +199,89 @@ def predict_shift(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch
         torch.cuda.synchronize(engine.device)
 
 
+def _runs(idx: np.ndarray):
+    """(offset in idx, first value, length) of each run of consecutive integers in ``idx``."""
+    if len(idx) == 0:
+        return
+    cut = np.flatnonzero(np.diff(idx) != 1) + 1
+    starts = np.concatenate([[0], cut])
+    ends = np.concatenate([cut, [len(idx)]])
+    for a, b in zip(starts, ends):
+        yield int(a), int(idx[a]), int(b - a)
+
+
+def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshift: int, sinks: dict,
+                                writer: SlabWriter | None = None) -> dict:
+    """The whole shift loop (chromatin.py:243-286) in segment mode: the ref/alt x fwd/rc sequences of a variant are
+    encoded once as 2000+2*maxshift-bp segments, the conv stack runs once per segment and all shifts' ref/alt/diff
+    rows come out together (bit-identical to the per-shift path).  ``sinks[shift](name, row0, array)`` receives the
+    row slabs of that shift's datasets.  Variants whose windows are not plain substrings of one segment (long
+    indels, ``windows.segment_eligible``) go through the per-window path."""
+    import torch
+
+    from .engine import chromatin_outputs
+    from .windows import (AlleleTable, check_valid_bases, chromatin_segment_descs, chromatin_window_descs,
+                          segment_eligible)
+
+    n = len(pos)
+    shifts = shift_list(maxshift)
+    S = len(shifts)
+    seg_len = 2000 + 2 * maxshift
+    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts]) if n else np.zeros(0, bool)
+    elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)
+    cap = max(1, min(engine.segment_capacity(seg_len) // 4, max(1, len(elig))))
+    n_sets = 2
+    pinned = [torch.empty((S, 3, 2 * cap, 2002), dtype=torch.float32, pin_memory=True) for _ in range(n_sets)]
+    own_writer = writer is None
+    if own_writer:
+        writer = SlabWriter(n_sets)
+    for c0 in range(0, len(elig), cap):
+        idx = elig[c0:c0 + cap]
+        m = len(idx)
+        descs, codes, k_of = chromatin_segment_descs(genome, [chroms[i] for i in idx], pos[idx], [refs[i] for i in idx],
+                                                     [alts[i] for i in idx], maxshift)
+        check_valid_bases(genome, descs)
+        probs = engine.forward_segments(descs, codes, m, 4, seg_len, k_of, shift_major=True)  # [S, m, 4, 2002]
+        si_set = writer.next_set()
+        buf = pinned[si_set]
+        for si in range(S):
+            ref, alt, diff = chromatin_outputs(probs[si].reshape(4 * m, 2002), m)
+            for j, t in enumerate((diff, ref, alt)):
+                buf[si, j, :2 * m].copy_(t, non_blocking=True)
+        torch.cuda.synchronize(engine.device)
+        for si, shift in enumerate(shifts):
+            tasks = []
+            for j, name in enumerate(("diff", "ref", "alt")):
+                h = buf[si, j].numpy()
+                for off, g0, ln in _runs(idx):
+                    tasks.append((name, g0, h[off:off + ln]))
+                    tasks.append((name, n + g0, h[m + off:m + off + ln]))
+            # every shift's tasks read the same buffer set; the last submit of the chunk (FIFO) frees it
+            if si == S - 1:
+                writer.submit(si_set, sinks[shift], tasks)
+            else:
+                writer.call(lambda sink=sinks[shift], tasks=tasks: [sink(*t) for t in tasks])
+        del probs
+    # long indels etc.: per-window path, one variant-run at a time
+    for shift in shifts if len(rest) else []:
+        sub = [(chroms[i], pos[i], refs[i], alts[i]) for i in rest]
+        descs, codes = chromatin_window_descs(genome, [x[0] for x in sub], np.array([x[1] for x in sub]),
+                                              [x[2] for x in sub], [x[3] for x in sub], shift)
+        check_valid_bases(genome, descs)
+        m = len(rest)
+        ref, alt, diff = engine.chromatin_shift_host(descs, codes, m, average=False)
+        tasks = []
+        for name, t in (("diff", diff), ("ref", ref), ("alt", alt)):
+            h = t.numpy()
+            for off, g0, ln in _runs(rest):
+                tasks.append((name, g0, h[off:off + ln].copy()))
+                tasks.append((name, n + g0, h[m + off:m + off + ln].copy()))
+        writer.call(lambda sink=sinks[shift], tasks=tasks: [sink(*t) for t in tasks])
+    if own_writer:
+        writer.close()
+    return {"segment_variants": int(len(elig)), "window_variants": int(len(rest))}
+
+
 def predict_shift_device(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int):
     """Same computation with the results left in HBM: (ref, alt, diff) device tensors [2n,2002] in the strand-
     stacked row order — the operands of the end-of-shift NCCL gather when variants are sharded over GPUs."""
@@ -261,6 +347,8 @@ def run(args, engine=None, genome=None) -> dict:
     chroms, pos, refs, alts = chroms[lo:hi], pos[lo:hi], refs[lo:hi], alts[lo:hi]
     n_local = hi - lo
     files, counters = [], None
+    if args.mode == "segments" and args.maxshift % 200 == 0 and (world == 1 or args.gather == "file"):
+        return _run_segments(args, engine, genome, chroms, pos, refs, alts, n, lo, n_local, rank, world)
     gb = max(1, min(args.gpu_batch, max(n_local, 1)))
     pinned, writer = None, None
     if world == 1 or args.gather == "file":
@@ -320,6 +408,57 @@ def run(args, engine=None, genome=None) -> dict:
         writer.close()
         shard.barrier()
     return {"n_variants": n, "counters": counters, "files": files, "rank": rank, "world": world}
+
+
+def _run_segments(args, engine, genome, chroms, pos, refs, alts, n, lo, n_local, rank, world) -> dict:
+    """run() in segment mode: all shifts of a variant come out of one pass, so every shift's file is open at once."""
+    from . import shard
+    from .hdf5 import H5Writer
+    from .windows import allele_match_counts
+
+    mine = allele_match_counts(genome, chroms, pos, refs, alts)
+    counters = tuple(shard.allreduce_sum_ints(mine, device=engine.device if world > 1 else None))
+    if rank == 0:
+        print(f"Number of variants with reference allele matched with reference genome: {counters[0]}")
+        print(f"Number of variants with alternate allele matched with reference genome: {counters[1]}")
+        print(f"Number of input variants: {counters[2]}")
+    shapes = {k: (2 * n, 2002) for k in ("diff", "ref", "alt")}
+    shifts = shift_list(args.maxshift)
+    paths = {s: f"{args.output_dir}/snps.shift_{str(s)}.diff.h5" for s in shifts}
+    ups = {s: f"{args.inputfile}.shift_{str(s)}.diff.h5" for s in shifts}
+    ws, us = {}, {}
+    if rank == 0:
+        for s in shifts:
+            ws[s] = H5Writer(paths[s], shapes)
+            if args.upstream_layout:
+                us[s] = H5Writer(ups[s], {"pred": (2 * n, 2002)})
+    shard.barrier()
+    if rank != 0:
+        for s in shifts:
+            ws[s] = H5Writer(paths[s], shapes, create=False)
+            if args.upstream_layout:
+                us[s] = H5Writer(ups[s], {"pred": (2 * n, 2002)}, create=False)
+
+    def make_sink(s):
+        w, up = ws[s], us.get(s)
+
+        def sink(name, row0, arr):
+            # local strand-stacked row -> global row: forward rows at lo+v, reverse-complement rows at n+lo+v
+            g0 = lo + row0 if row0 < n_local else n + lo + (row0 - n_local)
+            w.write_rows(name, g0, arr)
+            if up is not None and name == "diff":
+                up.write_rows("pred", g0, arr)
+        return sink
+
+    info = predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, args.maxshift,
+                                       {s: make_sink(s) for s in shifts})
+    for s in shifts:
+        ws[s].close()
+        if s in us:
+            us[s].close()
+    shard.barrier()
+    return {"n_variants": n, "counters": counters, "files": [paths[s] for s in shifts], "rank": rank, "world": world,
+            "mode": "segments", **info}
 
 
 def main(argv=None) -> int:

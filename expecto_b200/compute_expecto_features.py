@@ -35,6 +35,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--dtype", default="f16", choices=["f16", "bf16"])
     p.add_argument("--device", type=int, default=0)
     p.add_argument("--genes_per_batch", type=int, default=32, help="genes per GPU batch (x400 windows)")
+    p.add_argument("--mode", default="segments", choices=["segments", "windows"],
+                   help="segments: conv stack once per gene and strand (shared activations, bit-identical)")
     p.add_argument("--tss_is_hg19", action="store_true", help="tss_file coordinates are already hg19 (no liftover)")
     return p
 
@@ -63,21 +65,31 @@ def read_genes(anno_file: str, tss_file: str, tss_is_hg19: bool = False):
     return genes
 
 
-def gene_features(engine, genome, genes, shifts, weights, genes_per_batch: int = 32) -> np.ndarray:
-    """float64 [len(genes), 20020] for (id, chrom, tss, strand) tuples — the loop at :105-124, batched."""
+def gene_features(engine, genome, genes, shifts, weights, genes_per_batch: int = 32, mode: str = "segments") -> np.ndarray:
+    """float64 [len(genes), 20020] for (id, chrom, tss, strand) tuples — the loop at :105-124, batched.
+    ``mode="segments"``: the 200 windows of a gene are 200-bp-apart substrings of one 41.8-kb sequence per strand,
+    so the conv stack runs once per gene and strand (bx_forward_segments; bit-identical to ``"windows"``)."""
     import torch
 
     from .transform import decay_transform_fixed
-    from .windows import check_valid_bases, tss_descs
+    from .windows import check_valid_bases, tss_descs, tss_segment_descs
 
     S = len(shifts)
     out = np.empty((len(genes), 10 * 2002), dtype=np.float64)
     no_alleles = np.zeros(1, dtype=np.uint8)
+    steps = np.diff(np.asarray(shifts))
+    use_segments = mode == "segments" and S > 1 and S <= 200 and bool(np.all(steps == 200))
     for g0 in range(0, len(genes), genes_per_batch):
         part = genes[g0:g0 + genes_per_batch]
-        descs = tss_descs(genome, [g[1] for g in part], [g[2] for g in part], [g[3] for g in part], shifts)
-        check_valid_bases(genome, descs)
-        probs = engine.forward_windows(descs, no_alleles).view(len(part), S, 2, 2002)
+        cols = ([g[1] for g in part], [g[2] for g in part], [g[3] for g in part])
+        if use_segments:
+            descs, k_of, seg_len = tss_segment_descs(genome, *cols, shifts)
+            check_valid_bases(genome, descs)
+            probs = engine.forward_segments(descs, no_alleles, len(part), 2, seg_len, k_of, shift_major=False)
+        else:
+            descs = tss_descs(genome, *cols, shifts)
+            check_valid_bases(genome, descs)
+            probs = engine.forward_windows(descs, no_alleles).view(len(part), S, 2, 2002)
         feats = decay_transform_fixed(probs, weights)
         out[g0:g0 + len(part)] = feats.cpu().numpy()
         del probs, feats
@@ -104,7 +116,8 @@ def run(args, engine=None, genome=None) -> str:
     missing = sorted({g[1] for g in genes if g[1] not in genome.offsets})
     if missing:
         raise KeyError(f"contig(s) {missing} are not in the genome")
-    feats = gene_features(engine, genome, genes, TSS_SHIFTS, fixed_pos_weights(TSS_SHIFTS), args.genes_per_batch)
+    feats = gene_features(engine, genome, genes, TSS_SHIFTS, fixed_pos_weights(TSS_SHIFTS), args.genes_per_batch,
+                          mode=args.mode)
     path = f"{args.out_dir}/Xreducedall.2002.representative_tss_top"
     np.save(path, feats)
     return path + ".npy"

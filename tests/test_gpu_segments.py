@@ -63,3 +63,42 @@ def test_segment_chunking_and_argument_errors(engine, small_genome):
         engine.forward_segments(sd, np.zeros(1, np.uint8), n, 2, seg_len, k_of, shift_major=True)
     with pytest.raises(BelugaError):   # seg_len must match the shift count
         engine.forward_segments(sd, np.zeros(1, np.uint8), n, 2, seg_len + 200, k_of, shift_major=False)
+
+
+def test_chromatin_cli_segments_and_windows_modes_write_identical_files(engine, cfg1_genome, golden, tmp_path):
+    """Edge VCF (one variant — the 120-bp deletion — falls back to the per-window path inside segment mode)."""
+    from expecto_b200 import chromatin, hdf5
+    g = golden("chromatin_edge_golden.npz")
+    vcf = tmp_path / "edge.vcf"
+    vcf.write_text("".join("\t".join(str(x) for x in r) + "\n" for r in g["rows"]))
+    pg = PackedGenome.from_sequences(cfg1_genome)
+    infos = {}
+    for mode in ("segments", "windows"):
+        args = chromatin.build_parser().parse_args([str(vcf), "--output_dir", str(tmp_path / mode), "--mode", mode,
+                                                    "--upstream_layout"])
+        infos[mode] = chromatin.run(args, engine=engine, genome=pg)
+        # --upstream_layout files land next to the input; keep each mode's copy
+        for s in chromatin.shift_list(800):
+            (tmp_path / f"edge.vcf.shift_{s}.diff.h5").rename(tmp_path / mode / f"pred_{s}.h5")
+    assert infos["segments"]["mode"] == "segments" and infos["segments"]["window_variants"] == 1
+    assert infos["segments"]["segment_variants"] == 5
+    assert list(infos["segments"]["counters"]) == list(infos["windows"]["counters"]) == list(g["counters"])
+    for s in chromatin.shift_list(800):
+        with hdf5.File(str(tmp_path / "segments" / f"snps.shift_{s}.diff.h5")) as a, \
+                hdf5.File(str(tmp_path / "windows" / f"snps.shift_{s}.diff.h5")) as b:
+            for k in ("diff", "ref", "alt"):
+                assert np.array_equal(np.asarray(a[k]), np.asarray(b[k])), (s, k)
+            d = np.asarray(a["diff"])
+        with hdf5.File(str(tmp_path / "segments" / f"pred_{s}.h5")) as p:
+            assert np.array_equal(np.asarray(p["pred"]), d)
+
+
+def test_features_cli_segments_equal_windows(engine, cfg1_genome):
+    from expecto_b200.compute_expecto_features import gene_features
+    from expecto_b200.transform import TSS_SHIFTS, fixed_pos_weights
+    pg = PackedGenome.from_sequences(cfg1_genome)
+    engine.set_genome(pg)
+    genes = [("g1", "chr1", 5_000_000, 1), ("g2", "chr1", 7_654_321, -1), ("g3", "chr1", 30_000, 1)]
+    a = gene_features(engine, pg, genes, TSS_SHIFTS, fixed_pos_weights(), 2, mode="segments")
+    b = gene_features(engine, pg, genes, TSS_SHIFTS, fixed_pos_weights(), 2, mode="windows")
+    assert np.array_equal(a, b)

@@ -78,14 +78,24 @@ def main():
     res["chromatin_no_file"] = {"variants": nv, "windows": nv * 36, "seconds": total, "host_descriptor_s": t_desc,
                                 "gpu_pipeline_s": t_gpu, "windows_per_s": nv * 36 / total,
                                 "variants_per_s": nv / total, "d2h_bytes": 9 * 3 * 2 * nv * 2002 * 4}
-    out_dir = os.path.join(tmp, "chromatin_out")
-    a = chromatin.build_parser().parse_args([vcf, "--output_dir", out_dir])
+    # segment mode (shared activations across the 9 shifts), no file: device results copied to pinned host memory
+    from expecto_b200.chromatin import predict_all_shifts_segments
+    sink = lambda name, row0, arr: None
+    predict_all_shifts_segments(eng, pg, chroms[:600], pos[:600], refs[:600], alts[:600], 800, {s: sink for s in shifts})
     t0 = time.perf_counter()
-    info = chromatin.run(a, engine=eng, genome=pg)
+    sinfo = predict_all_shifts_segments(eng, pg, chroms, pos, refs, alts, 800, {s: sink for s in shifts})
     total = time.perf_counter() - t0
-    res["chromatin_cli_with_files"] = {"variants": info["n_variants"], "seconds": total,
-                                       "windows_per_s": info["n_variants"] * 36 / total,
-                                       "bytes_written": 9 * 3 * 2 * info["n_variants"] * 2002 * 4, "dir": tmp}
+    res["chromatin_segments_no_file"] = {"variants": nv, "windows": nv * 36, "seconds": total,
+                                         "windows_per_s": nv * 36 / total, "variants_per_s": nv / total, **sinfo}
+    out_dir = os.path.join(tmp, "chromatin_out")
+    for mode in ("windows", "segments"):
+        a = chromatin.build_parser().parse_args([vcf, "--output_dir", out_dir, "--mode", mode])
+        t0 = time.perf_counter()
+        info = chromatin.run(a, engine=eng, genome=pg)
+        total = time.perf_counter() - t0
+        res[f"chromatin_cli_with_files_{mode}"] = {"variants": info["n_variants"], "seconds": total,
+                                                   "windows_per_s": info["n_variants"] * 36 / total,
+                                                   "bytes_written": 9 * 3 * 2 * info["n_variants"] * 2002 * 4}
 
     # CPU reference (oracle port of chromatin.py's loop) on a tiny sample, all host threads
     from oracle import beluga_oracle as O
@@ -140,12 +150,13 @@ def main():
         c = contigs[i % len(contigs)]
         genes.append((f"ENSG{i:05d}", c[0], int(rng.integers(30000, c[1] - 30000)), 1 if i % 2 else -1))
     from expecto_b200.transform import TSS_SHIFTS, fixed_pos_weights
-    cef.gene_features(eng, pg, genes[:8], TSS_SHIFTS, fixed_pos_weights(), 8)  # warm-up
-    t0 = time.perf_counter()
-    f = cef.gene_features(eng, pg, genes, TSS_SHIFTS, fixed_pos_weights(), 32)
-    dt = time.perf_counter() - t0
-    res["features"] = {"genes": g, "windows": g * 400, "seconds": dt, "windows_per_s": g * 400 / dt, "genes_per_s": g / dt,
-                       "checksum": float(f.sum())}
+    for mode in ("windows", "segments"):
+        cef.gene_features(eng, pg, genes[:8], TSS_SHIFTS, fixed_pos_weights(), 8, mode=mode)  # warm-up
+        t0 = time.perf_counter()
+        f = cef.gene_features(eng, pg, genes, TSS_SHIFTS, fixed_pos_weights(), 32, mode=mode)
+        dt = time.perf_counter() - t0
+        res[f"features_{mode}"] = {"genes": g, "windows": g * 400, "seconds": dt, "windows_per_s": g * 400 / dt,
+                                   "genes_per_s": g / dt, "checksum": float(f.sum())}
     print(json.dumps(res, indent=1))
     if args.out:
         json.dump(res, open(args.out, "w"), indent=1)
