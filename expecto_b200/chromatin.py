@@ -282,6 +282,50 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
     return {"segment_variants": int(len(elig)), "window_variants": int(len(rest))}
 
 
+def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, maxshift: int):
+    """Segment mode with the results left in HBM: {shift: (ref, alt, diff)} device tensors [2n,2002] in the strand-
+    stacked row order — the operands of the per-shift NCCL gather when variants are sharded over GPUs."""
+    import torch
+
+    from .engine import chromatin_outputs
+    from .windows import check_valid_bases, chromatin_segment_descs, chromatin_window_descs, segment_eligible
+
+    n = len(pos)
+    shifts = shift_list(maxshift)
+    seg_len = 2000 + 2 * maxshift
+    outs = {s: tuple(torch.empty((2 * n, 2002), dtype=torch.float32, device=engine.device) for _ in range(3))
+            for s in shifts}
+    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts]) if n else np.zeros(0, bool)
+    elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)
+    cap = max(1, engine.segment_capacity(seg_len) // 4)
+
+    def scatter(shift, idx, parts):
+        m = len(idx)
+        ii = torch.from_numpy(np.asarray(idx, dtype=np.int64)).to(engine.device)
+        for full, part in zip(outs[shift], parts):
+            full.index_copy_(0, ii, part[:m])
+            full.index_copy_(0, ii + n, part[m:2 * m])
+
+    for c0 in range(0, len(elig), cap):
+        idx = elig[c0:c0 + cap]
+        m = len(idx)
+        descs, codes, k_of = chromatin_segment_descs(genome, [chroms[i] for i in idx], pos[idx], [refs[i] for i in idx],
+                                                     [alts[i] for i in idx], maxshift)
+        check_valid_bases(genome, descs)
+        probs = engine.forward_segments(descs, codes, m, 4, seg_len, k_of, shift_major=True)
+        for si, shift in enumerate(shifts):
+            scatter(shift, idx, chromatin_outputs(probs[si].reshape(4 * m, 2002), m))
+        del probs
+    if len(rest):
+        for shift in shifts:
+            descs, codes = chromatin_window_descs(genome, [chroms[i] for i in rest], pos[rest], [refs[i] for i in rest],
+                                                  [alts[i] for i in rest], shift)
+            check_valid_bases(genome, descs)
+            probs = engine.forward_windows(descs, codes)
+            scatter(shift, rest, chromatin_outputs(probs, len(rest)))
+    return outs
+
+
 def predict_shift_device(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int):
     """Same computation with the results left in HBM: (ref, alt, diff) device tensors [2n,2002] in the strand-
     stacked row order — the operands of the end-of-shift NCCL gather when variants are sharded over GPUs."""
@@ -350,6 +394,9 @@ def run(args, engine=None, genome=None) -> dict:
     if args.mode == "segments" and args.maxshift % 200 == 0 and (world == 1 or args.gather == "file"):
         return _run_segments(args, engine, genome, chroms, pos, refs, alts, n, lo, n_local, rank, world)
     gb = max(1, min(args.gpu_batch, max(n_local, 1)))
+    seg_outs = None
+    if args.mode == "segments" and args.maxshift % 200 == 0 and world > 1 and args.gather == "nccl":
+        seg_outs = predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, args.maxshift)
     pinned, writer = None, None
     if world == 1 or args.gather == "file":
         n_sets = 2  # slab k's file writes overlap slab k+1's GPU work (also across shifts)
@@ -368,7 +415,8 @@ def run(args, engine=None, genome=None) -> dict:
         path = f"{args.output_dir}/snps.shift_{str(shift)}.diff.h5"
         up_path = f"{args.inputfile}.shift_{str(shift)}.diff.h5"
         if world > 1 and args.gather == "nccl":
-            local_out = predict_shift_device(engine, genome, chroms, pos, refs, alts, shift, gb)
+            local_out = seg_outs.pop(shift) if seg_outs is not None else \
+                predict_shift_device(engine, genome, chroms, pos, refs, alts, shift, gb)
             full = [shard.gather_strand_rows(t, n) for t in local_out]  # ref, alt, diff
             if rank == 0:
                 with H5Writer(path, shapes) as w:

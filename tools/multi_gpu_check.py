@@ -55,7 +55,7 @@ def main():
         sh.barrier = lambda: None
         sh.allreduce_sum_ints = lambda v, device=None: [int(x) for x in v]
         args = chromatin.build_parser().parse_args([vcf, "--output_dir", os.path.join(base, "single"), "--maxshift",
-                                                    "200", "--gpu_batch", "128"])
+                                                    "200", "--gpu_batch", "128", "--mode", "windows"])
         single = chromatin.run(args, engine=eng, genome=pg)
         sh.init_distributed, sh.barrier, sh.allreduce_sum_ints, sh.shard_range = real
         os.environ.update(env)
