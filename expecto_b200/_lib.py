@@ -49,7 +49,7 @@ EXPORTS = [
     "bx_ctx_set_genome", "bx_encode_windows", "bx_forward_windows", "bx_forward_onehot", "bx_debug_activation", "bx_debug_run_layer",
     "bx_chromatin_outputs", "bx_chromatin_outputs_avg", "bx_decay_transform_fixed", "bx_decay_transform_variant",
     "bx_forward_onehot_host", "bx_chromatin_shift_host", "bx_ctx_profile", "bx_ctx_profile_read",
-    "bx_decay_score_variant", "bx_forward_segments", "bx_segment_capacity",
+    "bx_decay_score_variant", "bx_forward_segments", "bx_segment_capacity", "bx_strand_average",
 ]
 NSTAGES = 10
 STAGE_NAMES = ["encode", "conv1", "conv2", "conv3", "conv4", "conv5", "conv6", "fc1", "fc2", "outputs"]
@@ -116,6 +116,7 @@ def lib() -> C.CDLL:
     L.bx_decay_score_variant.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
     L.bx_forward_segments.argtypes = [vp, vp, vp, i32, i32, i32, i32, C.POINTER(C.c_int32), i32, vp, vp]
     L.bx_segment_capacity.argtypes = [vp, i32]
+    L.bx_strand_average.argtypes = [vp, i32, vp, vp]
     L.bx_ctx_profile.argtypes = [vp, i32]
     L.bx_ctx_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), i32]
     for name in EXPORTS:

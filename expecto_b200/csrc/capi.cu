@@ -762,6 +762,18 @@ int bx_chromatin_outputs_avg(const float* probs_dev, int n_var, float* ref_dev, 
   return 0;
 }
 
+int bx_strand_average(const float* x_dev, int n, float* out_dev, void* stream) {
+  if (n < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n == 0) return 0;
+  if (!x_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
+  const size_t total2 = (size_t)n * (kFeat / 2);
+  const unsigned blocks = (unsigned)std::min<size_t>((total2 + 255) / 256, 148 * 16);
+  strand_average_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x_dev, n, out_dev);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
 int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, int n_genes, int n_shifts,
                              float* out_dev, void* stream) {
   if (n_genes < 0 || n_shifts < 1 || n_shifts > 1024) return fail(BX_E_ARG, "invalid arguments");

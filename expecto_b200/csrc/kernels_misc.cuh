@@ -294,6 +294,19 @@ __global__ void chromatin_outputs_avg_kernel(const float* __restrict__ probs, in
   }
 }
 
+// predict.py:183-190: (rows 0..n-1 + rows n..2n-1) / 2.0 of a strand-stacked [2n, 2002] matrix -> [n, 2002].
+__global__ void __launch_bounds__(256)
+strand_average_kernel(const float* __restrict__ x, int n, float* __restrict__ out) {
+  const size_t total2 = (size_t)n * (kFeat / 2);
+  const float2* f = reinterpret_cast<const float2*>(x);
+  const float2* r = f + total2;
+  float2* o = reinterpret_cast<float2*>(out);
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < total2; i += (size_t)gridDim.x * 256) {
+    const float2 a = __ldg(f + i), b = __ldg(r + i);
+    o[i] = make_float2((a.x + b.x) / 2.0f, (a.y + b.y) / 2.0f);
+  }
+}
+
 // ------------------------------------------------------------------ kernel 4: decay-weighted shift reductions
 // HBM-bound streaming reductions, coalesced along the 2002-feature axis.  Rows are 8008 bytes, so every row is
 // 8-byte aligned and each thread moves float2 (two features); loads of several shifts are issued back to back

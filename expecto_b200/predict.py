@@ -82,26 +82,38 @@ def keep_mask(features_tsv: str, args) -> np.ndarray:
 
 def num_repeats(gene_df) -> list[int]:
     """get_num_repeats, predict.py:202-213: run lengths of consecutive rows sharing columns 0-4."""
-    keys = gene_df.iloc[:, 0:5].astype(str).agg(":".join, axis=1).values
-    if len(keys) == 0:
+    if len(gene_df) == 0:
         return [0]
+    cols = [gene_df.iloc[:, i].astype(str) for i in range(5)]
+    keys = cols[0]
+    for c in cols[1:]:
+        keys = keys + ":" + c
+    keys = keys.values
     change = np.flatnonzero(keys[1:] != keys[:-1]) + 1
     edges = np.concatenate([[0], change, [len(keys)]])
     return [int(x) for x in np.diff(edges)]
 
 
-def load_strand_averaged(pattern: str, maxshift: int):
-    """predict.py:173-194 -> dict of float32 [S, N, 2002] for diff / ref / alt."""
-    from . import hdf5
+def load_strand_averaged(pattern: str, maxshift: int, keys=("diff", "ref", "alt"), device=None):
+    """predict.py:173-194 -> dict of float32 CUDA tensors [S, N, 2002]: each per-shift dataset is read straight
+    from the file mapping into HBM and its forward / reverse-complement halves averaged there."""
+    import torch
 
-    out = {"diff": [], "ref": [], "alt": []}
-    for s in shift_list(maxshift):
+    from . import hdf5
+    from .transform import strand_average
+
+    shifts = shift_list(maxshift)
+    out = {}
+    for si, s in enumerate(shifts):
         with hdf5.File(pattern.replace("SHIFT", str(s))) as f:
-            for k in out:
+            for k in keys:
                 d = f[k]
                 n = int(d.shape[0] / 2)
-                out[k].append((np.asarray(d[0:n, :]) + np.asarray(d[n:2 * n, :])) / 2.0)
-    return {k: np.array(v) for k, v in out.items()}
+                if k not in out:
+                    out[k] = torch.empty((len(shifts), n, 2002), dtype=torch.float32, device=device)
+                x = torch.from_numpy(np.array(d[0:2 * n, :], dtype=np.float32)).to(device, non_blocking=False)
+                strand_average(x, out=out[k][si])
+    return out
 
 
 def expand_weights(models, mask: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
@@ -133,7 +145,8 @@ def run(args) -> dict:
         raise ValueError("give --model_save_file or --modelList")
     W, offsets = expand_weights([load_model(p) for p in paths], mask)
 
-    data = load_strand_averaged(args.snpEffectFilePattern, int(args.maxshift))
+    dev = torch.device("cuda", args.device)
+    data = load_strand_averaged(args.snpEffectFilePattern, int(args.maxshift), keys=("ref", "alt"), device=dev)
     coor = pd.read_csv(args.coorFile_chromatin, sep="\t", header=None, comment="#")
     gene = pd.read_csv(args.geneFile, sep="\t", header=None, comment="#")
     gene = gene.drop_duplicates(keep="first")
@@ -150,11 +163,11 @@ def run(args) -> dict:
         dist = np.full(gene.shape[0], float(args.fixeddist))
     genename, strand = np.asarray(gene.iloc[:, -2]), np.asarray(gene.iloc[:, -3])
 
-    dev = torch.device("cuda", args.device)
     sel = torch.from_numpy(idx).to(dev)
+    identity = len(idx) == data["ref"].shape[1] and bool(np.array_equal(idx, np.arange(len(idx))))
     scores = {}
     for key in ("ref", "alt"):
-        x = torch.from_numpy(np.ascontiguousarray(data[key], dtype=np.float32)).to(dev).index_select(1, sel)
+        x = data[key] if identity else data[key].index_select(1, sel)
         scores[key] = decay_score_variant(x, dist, strand, W, offsets, shifts=shift_list(int(args.maxshift))).cpu().numpy()
     ref, alt = scores["ref"], scores["alt"]
 

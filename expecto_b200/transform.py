@@ -50,6 +50,18 @@ def decay_transform_fixed(probs: torch.Tensor, weights, out: torch.Tensor | None
     return out
 
 
+def strand_average(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """predict.py:183-190 on the device: strand-stacked fp32 [2n,2002] -> [n,2002] = (top half + bottom half) / 2."""
+    if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] != N_FEATURES or x.shape[0] % 2:
+        raise ValueError("x must be a CUDA float32 tensor [2n,2002]")
+    n = x.shape[0] // 2
+    x = x.contiguous()
+    if out is None:
+        out = torch.empty((n, N_FEATURES), dtype=torch.float32, device=x.device)
+    check(lib().bx_strand_average(x.data_ptr(), n, out.data_ptr(), _stream(x)))
+    return out
+
+
 def chromatin_shifts(maxshift: int = 800) -> list[int]:
     return [0] + list(range(-200, -maxshift - 1, -200)) + list(range(200, maxshift + 1, 200))  # predict.py:173
 

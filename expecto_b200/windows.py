@@ -118,13 +118,40 @@ def check_valid_bases(genome: PackedGenome, descs: np.ndarray) -> None:
 
 def allele_match_counts(genome: PackedGenome, chroms, pos, refs: list[str], alts: list[str]):
     """The three diagnostics chromatin.py:256-260 prints at shift 0: how many variants have
-    ``seq[mutpos:mutpos+len(ref)].upper() == ref.upper()`` / ``== alt.upper()``, and the count."""
+    ``seq[mutpos:mutpos+len(ref)].upper() == ref.upper()`` / ``== alt.upper()``, and the count.
+    Single-base ref alleles (the bulk of any VCF) are compared vectorised on the packed codes; longer ones
+    go through the string comparison."""
+    n = len(refs)
+    if n == 0:
+        return 0, 0, 0
+    pos = np.asarray(pos, dtype=np.int64)
+    coff = np.fromiter((genome.offsets[c] for c in chroms), dtype=np.int64, count=n)
+    rl = np.fromiter((len(r) for r in refs), dtype=np.int64, count=n)
+    al = np.fromiter((len(a) for a in alts), dtype=np.int64, count=n)
     ref_ok = alt_ok = 0
-    for c, p, r, a in zip(chroms, pos, refs, alts):
-        g = genome.upper_string(genome.offsets[c] + int(p) - 1, len(r))
-        ref_ok += g == r.upper()
-        alt_ok += g == a.upper()
-    return ref_ok, alt_ok, len(refs)
+    snv = rl == 1
+    if snv.any():
+        g = coff[snv] + pos[snv] - 1
+        inside = (g >= 0) & (g < genome.n_bases)
+        j = np.where(inside, g, 0)
+        two = (genome.bases2[j >> 4] >> ((j & 15) * 2).astype(np.uint32)) & 3
+        msk = (genome.nmask[j >> 5] >> (j & 31).astype(np.uint32)) & 1
+        gcode = np.where((msk == 1) | ~inside, 4, two).astype(np.int64)   # 4 = 'N' after .upper()
+        lut = np.full(256, -1, dtype=np.int64)                              # allele letter -> code, 'N' -> 4
+        for ch, code in (("A", 0), ("G", 1), ("C", 2), ("T", 3), ("N", 4)):
+            lut[ord(ch)] = lut[ord(ch.lower())] = code
+        idx = np.flatnonzero(snv)
+        rcode = lut[np.frombuffer("".join(refs[i] for i in idx).encode("latin-1", "replace"), dtype=np.uint8)]
+        ref_ok += int(np.sum(rcode == gcode))
+        a1 = al[snv] == 1   # a longer alt can never equal the one genome base
+        if a1.any():
+            acode = lut[np.frombuffer("".join(alts[i] for i in idx[a1]).encode("latin-1", "replace"), dtype=np.uint8)]
+            alt_ok += int(np.sum(acode == gcode[a1]))
+    for i in np.flatnonzero(~snv):
+        g = genome.upper_string(int(coff[i] + pos[i] - 1), int(rl[i]))
+        ref_ok += g == refs[i].upper()
+        alt_ok += g == alts[i].upper()
+    return int(ref_ok), int(alt_ok), n
 
 
 # ------------------------------------------------------------------ segment mode (shared activations)

@@ -118,6 +118,10 @@ int bx_chromatin_outputs(const float* probs_dev, int n_var, float* ref_dev, floa
 int bx_chromatin_outputs_avg(const float* probs_dev, int n_var, float* ref_dev, float* alt_dev, float* diff_dev,
                              void* stream);
 
+/* predict.py:183-190: x_dev fp32 [2n,2002] (forward rows then reverse-complement rows, as chromatin.py writes
+ * them) -> out_dev fp32 [n,2002] = (x[0:n] + x[n:2n]) / 2.0. */
+int bx_strand_average(const float* x_dev, int n, float* out_dev, void* stream);
+
 /* compute_expecto_features.py:123-124: probs_dev fp32 [n_genes, S, 2, 2002] (shift-major, fwd then rc),
  * weights_dev fp32 [10,S]; out_dev fp32 [n_genes, 10*2002] = sum_s w[k,s] * 0.5*(fwd+rc)[s,f]. */
 int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, int n_genes, int n_shifts,

@@ -132,3 +132,35 @@ def test_tss_segment_descriptors(small_genome):
                 if int(sd.reshape(2, 2)[gi, q]["flags"]) & 2:
                     k = S - 1 - k
                 assert np.array_equal(win[gi, i, q], seg[gi, q, :, 200 * k:200 * k + 2000]), (gi, i, q)
+
+
+def test_allele_match_counts_vectorised_vs_oracle(small_genome):
+    from expecto_b200 import synth
+    rows = synth.make_vcf_rows(small_genome, 400, seed=9, odd_names=False, margin=3000)
+    rows += [["chr1", 5000, "n_ref", "N", "A"], ["chr1", 5001, "lower", small_genome["chr1"][5000].lower(), "n"]]
+    # put the first two on genome N / lower-case positions if there are any
+    npos = [i for i, c in enumerate(small_genome["chr1"][3000:50000]) if c == "N"][:3]
+    rows += [["chr1", 3001 + i, "on_N", "N", "N"] for i in npos]
+    pg = PackedGenome.from_sequences(small_genome)
+    dg = O.DictGenome(small_genome)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    flags = [O.fetch_seqs(dg, c, int(p), r, a)[2:] for c, p, r, a in zip(chroms, pos, refs, alts)]
+    want = (sum(f[0] for f in flags), sum(f[1] for f in flags), len(rows))
+    assert allele_match_counts(pg, chroms, pos, refs, alts) == want
+    assert want[0] > 300 and len(npos) > 0
+
+
+def test_packed_genome_from_fasta_roundtrip(tmp_path, small_genome):
+    from expecto_b200 import synth
+    fa = tmp_path / "g.fa"
+    synth.write_fasta(str(fa), small_genome, width=60)
+    pg = PackedGenome.from_fasta(str(fa))
+    assert (tmp_path / "g.fa.bx2.npz").exists()
+    again = PackedGenome.from_fasta(str(fa))  # served from the cache
+    ref = PackedGenome.from_sequences(small_genome)
+    for g in (pg, again):
+        assert g.names == ref.names and g.offsets == ref.offsets and g.lengths == ref.lengths
+        assert np.array_equal(g.bases2, ref.bases2) and np.array_equal(g.nmask, ref.nmask)
+    s = small_genome["chr2"]
+    assert pg.upper_string(pg.offsets["chr2"] + 100, 50) == s[100:150].upper()
