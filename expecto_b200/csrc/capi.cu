@@ -142,14 +142,15 @@ static size_t act_rows(int i) { return i == 0 ? kLayers[0].pitch_in : kLayers[i 
 static size_t act_cols(int i) { return i == 0 ? 64 : kLayers[i - 1].cout; }
 
 // ------------------------------------------------------------------ GEMM launch
-template <typename T, int TAPS, int BN, int CG, int EPI>
+template <typename T, int TAPS, int BN, int CG, int EPI, int A_MODE = 0>
 static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64_t a_cols, const void* b,
-                         uint64_t b_rows, GemmParams p, cudaStream_t st) {
+                         uint64_t b_rows, GemmParams p, cudaStream_t st, const EncParams& enc = EncParams()) {
   using Cfg = GemmCfg<TAPS, BN, CG>;
   CUtensorMap tmA, tmB;
-  if (int r = make_tmap(&tmA, c->dtype, a, a_rows, a_cols, a_cols, Cfg::A_ROWS)) return r;
   if (int r = make_tmap(&tmB, c->dtype, b, b_rows, a_cols, a_cols, Cfg::B_ROWS)) return r;
-  auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI>;
+  if (A_MODE != 0) tmA = tmB;  // unused: the producer warp builds the A tile in shared memory
+  else if (int r = make_tmap(&tmA, c->dtype, a, a_rows, a_cols, a_cols, Cfg::A_ROWS)) return r;
+  auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI, A_MODE>;
   static bool attr_set = false;
   if (!attr_set) {
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -159,7 +160,7 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
   p.n_chunks = p.n_total / BN;
   static const int dbg = getenv("BX_DEBUG_FLAGS") ? atoi(getenv("BX_DEBUG_FLAGS")) : 0;  // timing diagnostics only
   p.debug_flags = dbg;
-  const int units = p.m_tiles * p.n_chunks * p.k_splits;
+  const int units = (A_MODE != 0) ? p.m_tiles : p.m_tiles * p.n_chunks * p.k_splits;
   int clusters = std::min(units, c->num_sms / CG);
   if (clusters < 1) clusters = 1;
   cudaLaunchConfig_t cfg = {};
@@ -174,7 +175,7 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  CK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
+  CK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p, enc));
   g_launches++;
   return 0;
 }
@@ -205,8 +206,33 @@ static int launch_gemm(const bx_ctx* c, int taps, int bn, int epi, const void* a
   return launch_gemm_tc<__nv_bfloat16, 2>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
 }
 
-// conv layer i (0..5) over n windows: act[i] -> act[i+1]
-static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st) {
+// conv1 with the operand generated inside the kernel (north-star item 1: extraction + one-hot + reverse
+// complement fused into conv1's staged input): amode 1 = descriptors over the packed genome, 2 = one-hot bytes.
+static int launch_conv1_gen(const bx_ctx* c, int amode, const EncParams& enc, const GemmParams& p, cudaStream_t st) {
+  const LayerDef& L = kLayers[0];
+  if (p.pitch_in < 136) return fail(BX_E_ARG, "conv1 row pitch %d too small for in-kernel encoding", p.pitch_in);
+#define BX_GEN(T, CG, M) \
+  return launch_gemm_t<T, 1, 160, CG, EPI_BIAS_RELU, M>(c, nullptr, 0, L.cin, c->wconv[0], L.cout, p, st, enc)
+  const bool f16 = c->dtype == BX_DTYPE_F16;
+  if (amode == 1) {
+    if (f16) { if (c->cg == 1) BX_GEN(__half, 1, 1); BX_GEN(__half, 2, 1); }
+    if (c->cg == 1) BX_GEN(__nv_bfloat16, 1, 1);
+    BX_GEN(__nv_bfloat16, 2, 1);
+  }
+  if (f16) { if (c->cg == 1) BX_GEN(__half, 1, 2); BX_GEN(__half, 2, 2); }
+  if (c->cg == 1) BX_GEN(__nv_bfloat16, 1, 2);
+  BX_GEN(__nv_bfloat16, 2, 2);
+#undef BX_GEN
+}
+
+// BX_CONV1_IM2COL=1 keeps the two-kernel form (encode -> im2col matrix in HBM -> TMA) for A/B comparisons.
+static bool conv1_gen_enabled() {
+  static const bool on = !(getenv("BX_CONV1_IM2COL") && atoi(getenv("BX_CONV1_IM2COL")) != 0);
+  return on;
+}
+
+// conv layer i (0..5) over n windows: act[i] -> act[i+1]; `enc` (conv1 only) selects in-kernel operand generation
+static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st, const EncParams* enc = nullptr, int amode = 0) {
   const LayerDef& L = kLayers[i];
   GemmParams p = {};
   p.m_rows = n * L.pitch_in;
@@ -222,6 +248,7 @@ static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st) {
   p.n_store = L.cout;
   p.bias = c->bconv[i];
   p.out = c->act[i + 1];
+  if (i == 0 && enc) return launch_conv1_gen(c, amode, *enc, p, st);
   return launch_gemm(c, L.taps, L.block_n, L.epi, c->act[i], (uint64_t)n * L.pitch_in, L.cin, c->wconv[i],
                      (uint64_t)L.taps * L.cout, p, st);
 }
@@ -278,11 +305,12 @@ static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
   return launch_gemm(c, 1, 256, EPI_BIAS_SIGMOID, c->hid, n, 2048, c->wfc2, 2048, p, st);
 }
 
-// conv1..conv6, fc1, fc2 over n windows whose conv1 operand is already in act[0].
-static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st) {
+// conv1..conv6, fc1, fc2 over n windows whose conv1 operand is already in act[0] or is generated from `enc`.
+static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st, const EncParams* enc = nullptr,
+                       int amode = 0) {
   for (int i = 0; i < 6; ++i) {
     StageTimer t(c, 1 + i, st);
-    if (int r = run_conv(c, i, n, st)) return r;
+    if (int r = run_conv(c, i, n, st, enc, amode)) return r;
   }
   {
     StageTimer t(c, 7, st);
@@ -312,7 +340,7 @@ static Geom make_geom(int L) {
 
 // conv layer i over n_seg segments with explicit geometry; phase_b shifts conv4's input by two rows.
 static int run_conv_geom(bx_ctx* c, int i, int n_seg, const Geom& g, const void* in, void* out, bool phase_b,
-                         cudaStream_t st) {
+                         cudaStream_t st, const EncParams* enc = nullptr) {
   const LayerDef& L = kLayers[i];
   const int pin[6] = {g.p1, g.p1, g.p2, g.p3, g.p4, g.p5};
   const int pout[6] = {g.p1, g.p2, g.p3, g.p4, g.p5, g.p6};
@@ -331,6 +359,7 @@ static int run_conv_geom(bx_ctx* c, int i, int n_seg, const Geom& g, const void*
   p.n_store = L.cout;
   p.bias = c->bconv[i];
   p.out = out;
+  if (i == 0 && enc) return launch_conv1_gen(c, 1, *enc, p, st);
   const char* a = reinterpret_cast<const char*>(in) + (size_t)skip * L.cin * 2;
   return launch_gemm(c, L.taps, L.block_n, L.epi, a, (uint64_t)p.m_rows, L.cin, c->wconv[i], (uint64_t)L.taps * L.cout,
                      p, st);
@@ -501,6 +530,12 @@ int bx_encode_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t*
 // One chunk (m <= cap windows): kernel 1 fused into the conv1 operand, then the network.
 static int forward_chunk_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int m,
                                  float* probs_dev, cudaStream_t st) {
+  if (conv1_gen_enabled()) {
+    EncParams e = {};
+    e.descs = descs_dev; e.alleles = alleles_dev; e.bases2 = c->bases2; e.nmask = c->nmask; e.n_bases = c->n_bases;
+    e.L = BX_WINDOW; e.n_seg = m;
+    return run_network(c, m, probs_dev, st, &e, 1);
+  }
   {
     StageTimer t(c, 0, st);
     if (c->dtype == BX_DTYPE_F16)
@@ -516,6 +551,11 @@ static int forward_chunk_windows(bx_ctx* c, const bx_window_desc* descs_dev, con
 }
 
 static int forward_chunk_onehot(bx_ctx* c, const uint8_t* x, int m, float* probs_dev, cudaStream_t st) {
+  if (conv1_gen_enabled()) {
+    EncParams e = {};
+    e.onehot = x; e.L = BX_WINDOW; e.n_seg = m;
+    return run_network(c, m, probs_dev, st, &e, 2);
+  }
   {
     StageTimer t(c, 0, st);
     if (c->dtype == BX_DTYPE_F16)
@@ -869,7 +909,11 @@ int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_
     const int ng = std::min(grp_cap, n_groups - g0);
     const int ns = ng * segs_per_group;
     const bx_window_desc* d = descs_dev + (size_t)g0 * segs_per_group;
-    {
+    EncParams e = {};
+    e.descs = d; e.alleles = alleles_dev; e.bases2 = c->bases2; e.nmask = c->nmask; e.n_bases = c->n_bases;
+    e.L = seg_len; e.n_seg = ns;
+    const bool gen = conv1_gen_enabled();
+    if (!gen) {
       StageTimer t(c, 0, st);
       dim3 grid((g.p1 * 8 + 255) / 256, ns);
       if (f16)
@@ -883,7 +927,7 @@ int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_
     }
     for (int i = 0; i < 4; ++i) {  // conv1..conv4 (phase A pooling)
       StageTimer t(c, 1 + i, st);
-      if (int r = run_conv_geom(c, i, ns, g, c->act[i], c->act[i + 1], false, st)) return r;
+      if (int r = run_conv_geom(c, i, ns, g, c->act[i], c->act[i + 1], false, st, gen ? &e : nullptr)) return r;
     }
     for (int phase = 0; phase < 2; ++phase) {
       if (phase == 1) {

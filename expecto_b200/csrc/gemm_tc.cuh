@@ -14,8 +14,15 @@
 // CTA_GROUP == 2 runs a CTA pair (cluster of 2): M = 256 per pair, each CTA stages its own 128 A
 // rows and half of the B rows, the leader CTA issues tcgen05.mma.cta_group::2.
 // Accumulators live in a TMEM ring of 512/BLOCK_N buffers so the epilogue overlaps the next tile.
+//
+// A_MODE != 0 (conv1 only; reference: fetchSeqs + encodeSeqs feeding model.forward, chromatin.py:138-209,270):
+// the A operand is never in HBM.  The producer warp reads the 2-bit packed genome through the window / segment
+// descriptors (A_MODE 1) or an explicit one-hot tensor (A_MODE 2), reverse-complements, and writes the
+// 128 x [8 taps x 4 channels] operand tile straight into the swizzled A stage in shared memory; the weights
+// still arrive by TMA.  The tile is built once per 128-row block and reused for every N chunk.
 #pragma once
 #include <type_traits>
+#include "encode.cuh"
 #include "ptx.cuh"
 
 namespace bx {
@@ -105,10 +112,11 @@ struct RingState {
   }
 };
 
-template <typename T, int TAPS, int BLOCK_N, int CG, int EPI>
+template <typename T, int TAPS, int BLOCK_N, int CG, int EPI, int A_MODE = 0>
 __global__ void __launch_bounds__(192, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const GemmParams p) {
+               const GemmParams p, const EncParams enc) {
+  static_assert(A_MODE == 0 || TAPS == 1, "in-kernel operand generation is the conv1 (im2col, one K block) form");
   using Cfg = GemmCfg<TAPS, BLOCK_N, CG>;
   constexpr int SA = Cfg::SA, SB = Cfg::SB, NBUF = Cfg::NBUF;
   constexpr int FMT = sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
@@ -128,6 +136,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   auto tempty = [&](uint32_t i) { return bars + 8u * (2 * SA + 2 * SB + NBUF + i); };
   const uint32_t tmem_slot = bars + 8u * (2 * SA + 2 * SB + 2 * NBUF);
   float* sbias = reinterpret_cast<float*>(smem_raw + (bars + 1024 - raw));  // [n_total] fp32, n_total <= 2048
+  // A_MODE scratch: 144 per-position operand patterns (upper half of the bias area; n_total <= 1024 there)
+  unsigned long long* s_pat = reinterpret_cast<unsigned long long*>(smem_raw + (bars + 1024 + 4096 - raw));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -138,7 +148,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmA);
     prefetch_tensormap(&tmB);
-    for (int i = 0; i < SA; ++i) { mbar_init(fullA(i), 1); mbar_init(emptyA(i), 1); }
+    // A_MODE: one arrival per CTA of the pair (each producer warp fills its own 128 rows) instead of TMA bytes
+    for (int i = 0; i < SA; ++i) { mbar_init(fullA(i), A_MODE ? CG : 1); mbar_init(emptyA(i), 1); }
     for (int i = 0; i < SB; ++i) { mbar_init(fullB(i), 1); mbar_init(emptyB(i), 1); }
     for (int i = 0; i < NBUF; ++i) { mbar_init(tfull(i), 1); mbar_init(tempty(i), 4 * CG); }
     fence_barrier_init();
@@ -153,6 +164,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int tiles_mn = p.m_tiles * p.n_chunks;
   const int total_units = tiles_mn * p.k_splits;
+  // Work unit `it` of this cluster.  Default: units strided over the clusters.  A_MODE: 128-row blocks strided
+  // over the clusters, all N chunks of a block back to back so the generated A tile is reused.
+  auto unit = [&](int it, int& ks, int& mt, int& nc) -> bool {
+    if constexpr (A_MODE != 0) {
+      const int g = it / p.n_chunks;
+      ks = 0;
+      mt = cluster_id + g * num_clusters;
+      nc = it - g * p.n_chunks;
+      return mt < p.m_tiles;
+    } else {
+      const int u = cluster_id + it * num_clusters;
+      if (u >= total_units) return false;
+      ks = u / tiles_mn;
+      const int rem = u - ks * tiles_mn;
+      mt = rem / p.n_chunks;
+      nc = rem - mt * p.n_chunks;
+      return true;
+    }
+  };
 
   // Producer and MMA warps run their loops warp-uniformly (all 32 lanes wait on the barriers) and only
   // the elected lane issues the async instruction: descriptors, coordinates and barrier addresses then
@@ -162,14 +192,61 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     RingState ra, rb;
-    for (int u = cluster_id; u < total_units; u += num_clusters) {
-      const int ks = u / tiles_mn, rem = u - ks * tiles_mn;
-      const int mt = rem / p.n_chunks, nc = rem - mt * p.n_chunks;
+    int ks, mt, nc;
+    // A_MODE: raw genome / one-hot words of the NEXT 128-row block, loaded one block ahead (encode.cuh)
+    EncRaw<A_MODE> enc_raw;
+    auto load_block = [&](int mtile) {
+      const int r0 = mtile * 128 * CG + (int)rank * 128;
+      const int w = r0 / p.pitch_in, l = r0 - w * p.pitch_in;
+      enc_tile_load<A_MODE>(enc, w, l, p.pitch_in - l, lane, enc_raw);
+    };
+    if constexpr (A_MODE != 0) {
+      if (cluster_id < p.m_tiles) load_block(cluster_id);
+    }
+    for (int it = 0; unit(it, ks, mt, nc); ++it) {
       const int kb0 = ks * p.kb_per_split;
       const int kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
       const int row0 = mt * 128 * CG + (int)rank * 128;
       const int ncol0 = nc * BLOCK_N + (int)rank * Cfg::B_ROWS;
       for (int kb = kb0; kb < kb1; ++kb) {
+        if constexpr (A_MODE != 0) {
+          if (nc == 0) {
+            mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
+            if (!(p.debug_flags & 2)) {
+              // Slots of s_pat: see enc_tile_load (pitch_in >= 136, so a tile touches at most two windows).
+              const int jB = p.pitch_in - row0 % p.pitch_in;
+              int codes[5];
+              enc_tile_codes<A_MODE>(enc_raw, codes);
+              if (mt + num_clusters < p.m_tiles) load_block(mt + num_clusters);  // in flight during the stores below
+#pragma unroll
+              for (int k = 0; k < 5; ++k)  // 64-bit operand pattern of one position: k = tap*4 + channel
+                if (lane + 32 * k < 144)
+                  s_pat[lane + 32 * k] =
+                      (codes[k] < 4) ? ((unsigned long long)one_bits<T>() << (16 * codes[k])) : 0ull;
+              __syncwarp();
+              uint8_t* stage = smem_raw + (sA - raw) + ra.idx * Cfg::A_BYTES;
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) {
+                const int j = jj * 32 + lane;
+                const int o = (j < jB) ? j : j + 8;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {  // 16-byte piece q = taps 2q, 2q+1; SWIZZLE_128B: piece ^ (row & 7)
+                  const unsigned long long lo = s_pat[o + 2 * q], hi = s_pat[o + 2 * q + 1];
+                  *reinterpret_cast<uint4*>(stage + j * 128 + ((q ^ (j & 7)) << 4)) =
+                      make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+                }
+              }
+              fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+            }
+            __syncwarp();
+            if (elect_one()) {
+              if constexpr (CG == 1) mbar_arrive_local(fullA(ra.idx));
+              else mbar_arrive_remote(mapa(fullA(ra.idx), 0));
+            }
+            __syncwarp();
+            ra.advance<SA>();
+          }
+        } else {
         mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
         if (p.debug_flags & 2) {
           if (elect_one() && rank == 0) mbar_arrive_local(fullA(ra.idx));
@@ -184,6 +261,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         __syncwarp();
         ra.advance<SA>();
+        }
 #pragma unroll 1
         for (int t = 0; t < TAPS; t += Cfg::TPS) {
           mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
@@ -213,8 +291,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------------------------------------------ MMA issuer (leader CTA, elected lane)
     if (rank == 0) {
       RingState ra, rb, rt;
-      for (int u = cluster_id; u < total_units; u += num_clusters) {
-        const int ks = u / tiles_mn;
+      int ks, mt, nc;
+      for (int it = 0; unit(it, ks, mt, nc); ++it) {
         const int kb0 = ks * p.kb_per_split;
         const int kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
         mbar_wait(tempty(rt.idx), rt.phase ^ 1, 3);
@@ -223,7 +301,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t accum = 0;
         for (int kb = kb0; kb < kb1; ++kb) {
           const int kcount = min(4, (p.k_valid - kb * 64 + 15) >> 4);
-          mbar_wait(fullA(ra.idx), ra.phase, 4);
+          if (A_MODE == 0 || nc == 0) mbar_wait(fullA(ra.idx), ra.phase, 4);
           const uint32_t a_lo = sw128_desc_lo(sA + ra.idx * Cfg::A_BYTES);
 #pragma unroll 1
           for (int t = 0; t < TAPS; t += Cfg::TPS) {
@@ -256,9 +334,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             accum = 1;
             rb.advance<SB>();
           }
-          if (elect_one()) umma_commit<CG>(emptyA(ra.idx));
-          __syncwarp();
-          ra.advance<SA>();
+          if (A_MODE == 0 || nc == p.n_chunks - 1) {  // A_MODE: the generated tile serves every N chunk
+            if (elect_one()) umma_commit<CG>(emptyA(ra.idx));
+            __syncwarp();
+            ra.advance<SA>();
+          }
         }
         if (elect_one()) umma_commit<CG>(tfull(rt.idx));
         __syncwarp();
@@ -269,9 +349,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------------------------------------------ epilogue warps 2..5
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     RingState rt;
-    for (int u = cluster_id; u < total_units; u += num_clusters) {
-      const int ks = u / tiles_mn, rem = u - ks * tiles_mn;
-      const int mt = rem / p.n_chunks, nc = rem - mt * p.n_chunks;
+    int ks, mt, nc;
+    for (int it = 0; unit(it, ks, mt, nc); ++it) {
       const int r = mt * 128 * CG + (int)rank * 128 + q * 32 + lane;
       const int wb = r / p.pitch_in;
       const int l = r - wb * p.pitch_in;

@@ -8,31 +8,13 @@
 #include <cuda_fp16.h>
 #include <cuda_bf16.h>
 #include "../../include/beluga_b200.h"
+#include "encode.cuh"
 
 namespace bx {
 
 constexpr int kWin = 2000;
 constexpr int kP1 = 1996;   // row pitch of the conv1 operand / conv1 output per window (1993 valid)
 constexpr int kFeat = 2002;
-
-// Channel code (A=0,G=1,C=2,T=3; 4 = all-zero column) of forward-strand position i of a window.
-__device__ __forceinline__ int window_code(const bx_window_desc& d, int i, const uint32_t* __restrict__ bases2,
-                                           const uint32_t* __restrict__ nmask, const uint8_t* __restrict__ alleles,
-                                           int64_t n_bases) {
-  int64_t g;
-  if (i < d.len1) {
-    g = d.g1 + i;
-  } else if (i < d.len1 + d.alen) {
-    return alleles[d.aoff + (i - d.len1)];
-  } else if (i < d.len1 + d.alen + d.len2) {
-    g = d.g2 + (i - d.len1 - d.alen);
-  } else {
-    return 4;
-  }
-  if (g < 0 || g >= n_bases) return 4;
-  if ((__ldg(nmask + (g >> 5)) >> (g & 31)) & 1u) return 4;
-  return (__ldg(bases2 + (g >> 4)) >> ((g & 15) * 2)) & 3u;
-}
 
 // Codes of one window in strand orientation into shared memory (2000 + 8 pad entries of 4).
 __device__ __forceinline__ void load_window_codes(uint8_t* codes, const bx_window_desc& d,
@@ -64,11 +46,6 @@ __global__ void encode_onehot_kernel(const bx_window_desc* __restrict__ descs, c
     o[idx] = codes[i] == ch ? 1 : 0;
   }
 }
-
-// 16-bit 1.0 in the operand format.
-template <typename T> __device__ __forceinline__ uint32_t one_bits();
-template <> __device__ __forceinline__ uint32_t one_bits<__half>() { return 0x3C00u; }
-template <> __device__ __forceinline__ uint32_t one_bits<__nv_bfloat16>() { return 0x3F80u; }
 
 // Write the conv1 operand rows of one window from its codes: row l = [onehot(l), ..., onehot(l+7), 0 x32]
 // (k = tap*4 + channel), 128 bytes per row.  Eight lanes share a row (16 bytes each), so one warp store covers
@@ -133,17 +110,6 @@ __global__ void onehot_im2col_kernel(const uint8_t* __restrict__ onehot, T* __re
 // the dense layers run per window, on 106-row slices of the segment's conv6 output.  Every window's result is
 // bit-identical to the per-window path (same dot products, same order).
 //
-// Strand-oriented code of position i of a segment of length L described like a window (bx_window_desc).
-__device__ __forceinline__ int segment_code(const bx_window_desc& d, int i, int L, const uint32_t* __restrict__ bases2,
-                                            const uint32_t* __restrict__ nmask, const uint8_t* __restrict__ alleles,
-                                            int64_t n_bases) {
-  if (i < 0 || i >= L) return 4;
-  const bool rc = d.flags & 1;
-  int c = window_code(d, rc ? (L - 1 - i) : i, bases2, nmask, alleles, n_bases);
-  if (rc && c < 4) c = 3 - c;
-  return c;
-}
-
 // conv1 operand rows of segments: a0 [n_seg * pitch, 64]; grid (ceil(pitch*8/256), n_seg); one thread per
 // 16-byte piece of a row (two taps), codes fetched straight from the packed genome (L2-resident re-reads).
 template <typename T>

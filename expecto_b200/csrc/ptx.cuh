@@ -52,6 +52,10 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_bar) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
+// Orders this thread's generic-proxy shared-memory writes before later async-proxy (TMA / tcgen05) accesses.
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
