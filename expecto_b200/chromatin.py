@@ -94,21 +94,46 @@ def variant_columns(vcf):
 
 
 class SlabWriter:
-    """Background file writer: the HDF5 row-slab writes of slab k run on a thread while the GPU pipeline
+    """Background file writer: the HDF5 row-slab writes of slab k run on threads while the GPU pipeline
     computes slab k+1 into the other set of pinned buffers (file output is as large as the GPU produces it —
-    48 KB per variant-shift — so the disk, not the GPU, bounds chromatin.py-style output; SURVEY §7 hard part 4)."""
+    48 KB per variant-shift — so the disk, not the GPU, bounds chromatin.py-style output; SURVEY §7 hard part 4).
+    Submissions are handled in order by one dispatcher; the slab writes inside one submission are independent
+    positional writes and go out on ``n_threads`` workers (one thread's page-cache copy tops out near 3.6 GB/s on
+    the B200 host, four reach ~5 GB/s: tools/disk_bench.py)."""
 
-    def __init__(self, n_sets: int):
+    def __init__(self, n_sets: int, n_threads: int = 4):
         import queue
         import threading
+        from concurrent.futures import ThreadPoolExecutor
         self._q = queue.Queue()
         self._free = [threading.Event() for _ in range(n_sets)]
         for e in self._free:
             e.set()
         self._err = None
         self._next = 0
+        self.busy_s = 0.0     # dispatcher time inside slab writes
+        self.blocked_s = 0.0  # producer time spent waiting for a free buffer set
+        self.bytes = 0
+        self._pool = ThreadPoolExecutor(max_workers=max(1, n_threads)) if n_threads > 1 else None
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
+
+    def _write(self, sink, tasks):
+        import time
+        t0 = time.perf_counter()
+        try:
+            self._write_tasks(sink, tasks)
+        finally:
+            self.busy_s += time.perf_counter() - t0
+            self.bytes += sum(int(getattr(t[-1], "nbytes", 0)) for t in tasks)
+
+    def _write_tasks(self, sink, tasks):
+        if self._pool is None or len(tasks) < 2:
+            for t in tasks:
+                sink(*t)
+        else:
+            for f in [self._pool.submit(sink, *t) for t in tasks]:
+                f.result()
 
     def _run(self):
         while True:
@@ -117,11 +142,10 @@ class SlabWriter:
                 return
             set_idx, sink, tasks = item
             try:
-                if set_idx is None:
+                if tasks is None:
                     sink()  # ordered call (closing a finished shift's files)
                 elif self._err is None:
-                    for name, row0, arr in tasks:
-                        sink(name, row0, arr)
+                    self._write(sink, tasks)
             except BaseException as e:  # surfaced by wait_free / drain
                 self._err = e
             finally:
@@ -136,7 +160,10 @@ class SlabWriter:
         return i
 
     def wait_free(self, set_idx: int) -> None:
+        import time
+        t0 = time.perf_counter()
         self._free[set_idx].wait()
+        self.blocked_s += time.perf_counter() - t0
         if self._err is not None:
             raise self._err
 
@@ -148,6 +175,10 @@ class SlabWriter:
         """Run ``fn()`` on the writer thread after everything submitted so far."""
         self._q.put((None, fn, None))
 
+    def write(self, sink, tasks) -> None:
+        """Ordered slab writes that do not release a buffer set (the set's last ``submit`` does)."""
+        self._q.put((None, sink, tasks))
+
     def drain(self) -> None:
         for i in range(len(self._free)):
             self.wait_free(i)
@@ -155,6 +186,8 @@ class SlabWriter:
     def close(self) -> None:
         self._q.put(None)
         self._t.join()
+        if self._pool is not None:
+            self._pool.shutdown()
         if self._err is not None:
             raise self._err
 
@@ -230,25 +263,24 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
     ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts]) if n else np.zeros(0, bool)
     elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)
     cap = max(1, min(engine.segment_capacity(seg_len) // 4, max(1, len(elig))))
-    n_sets = 2
+    n_sets = 3  # one being filled by the GPU, one waiting to be handed over, one being written
     pinned = [torch.empty((S, 3, 2 * cap, 2002), dtype=torch.float32, pin_memory=True) for _ in range(n_sets)]
     own_writer = writer is None
     if own_writer:
         writer = SlabWriter(n_sets)
-    for c0 in range(0, len(elig), cap):
-        idx = elig[c0:c0 + cap]
-        m = len(idx)
-        descs, codes, k_of = chromatin_segment_descs(genome, [chroms[i] for i in idx], pos[idx], [refs[i] for i in idx],
-                                                     [alts[i] for i in idx], maxshift)
-        check_valid_bases(genome, descs)
-        probs = engine.forward_segments(descs, codes, m, 4, seg_len, k_of, shift_major=True)  # [S, m, 4, 2002]
-        si_set = writer.next_set()
+    # Software pipeline over chunks: while the GPU runs chunk k (compute stream) and its results stream to pinned
+    # memory (copy stream), the host builds chunk k+1's descriptors and hands chunk k-1's slabs to the writer.
+    import time
+    copy_stream = torch.cuda.Stream(device=engine.device)
+    pending = None
+    t_host = {"descriptor_s": 0.0, "enqueue_s": 0.0, "gpu_wait_s": 0.0}
+
+    def flush(p):
+        done, si_set, idx, m = p
+        t0 = time.perf_counter()
+        done.synchronize()
+        t_host["gpu_wait_s"] += time.perf_counter() - t0
         buf = pinned[si_set]
-        for si in range(S):
-            ref, alt, diff = chromatin_outputs(probs[si].reshape(4 * m, 2002), m)
-            for j, t in enumerate((diff, ref, alt)):
-                buf[si, j, :2 * m].copy_(t, non_blocking=True)
-        torch.cuda.synchronize(engine.device)
         for si, shift in enumerate(shifts):
             tasks = []
             for j, name in enumerate(("diff", "ref", "alt")):
@@ -260,8 +292,39 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
             if si == S - 1:
                 writer.submit(si_set, sinks[shift], tasks)
             else:
-                writer.call(lambda sink=sinks[shift], tasks=tasks: [sink(*t) for t in tasks])
-        del probs
+                writer.write(sinks[shift], tasks)
+
+    with torch.cuda.device(engine.device):
+        for c0 in range(0, len(elig), cap):
+            idx = elig[c0:c0 + cap]
+            m = len(idx)
+            t0 = time.perf_counter()
+            descs, codes, k_of = chromatin_segment_descs(genome, [chroms[i] for i in idx], pos[idx],
+                                                         [refs[i] for i in idx], [alts[i] for i in idx], maxshift)
+            check_valid_bases(genome, descs)
+            t1 = time.perf_counter()
+            probs = engine.forward_segments(descs, codes, m, 4, seg_len, k_of, shift_major=True)  # [S, m, 4, 2002]
+            outs = [chromatin_outputs(probs[si].reshape(4 * m, 2002), m) for si in range(S)]
+            computed = torch.cuda.Event()
+            computed.record()
+            t_host["descriptor_s"] += t1 - t0
+            t_host["enqueue_s"] += time.perf_counter() - t1
+            si_set = writer.next_set()  # blocks until the set's previous contents are on disk
+            buf = pinned[si_set]
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(computed)
+                for si, (ref, alt, diff) in enumerate(outs):
+                    for j, t in enumerate((diff, ref, alt)):
+                        buf[si, j, :2 * m].copy_(t, non_blocking=True)
+                        t.record_stream(copy_stream)
+                done = torch.cuda.Event()
+                done.record(copy_stream)
+            del probs, outs
+            if pending is not None:
+                flush(pending)
+            pending = (done, si_set, idx, m)
+        if pending is not None:
+            flush(pending)
     # long indels etc.: per-window path, one variant-run at a time
     for shift in shifts if len(rest) else []:
         sub = [(chroms[i], pos[i], refs[i], alts[i]) for i in rest]
@@ -279,7 +342,9 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
         writer.call(lambda sink=sinks[shift], tasks=tasks: [sink(*t) for t in tasks])
     if own_writer:
         writer.close()
-    return {"segment_variants": int(len(elig)), "window_variants": int(len(rest))}
+    return {"segment_variants": int(len(elig)), "window_variants": int(len(rest)), "chunk_variants": int(cap),
+            "writer_busy_s": writer.busy_s, "writer_bytes": writer.bytes, "producer_blocked_s": writer.blocked_s,
+            **{"host_" + k: v for k, v in t_host.items()}}
 
 
 def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, maxshift: int):

@@ -68,11 +68,11 @@ class H5Writer:
             off += (-off) % 8
         self.eof = off
         if create:
-            self._f = open(path, "wb+")
+            self._f = open(path, "wb+", buffering=0)
             self._f.write(self._metadata())
             self._f.truncate(self.eof)
         else:
-            self._f = open(path, "rb+")
+            self._f = open(path, "rb+", buffering=0)
             if self._f.read(8) != _SIG or os.fstat(self._f.fileno()).st_size != self.eof:
                 raise ValueError(f"{path} was not created with these datasets")
 
@@ -133,8 +133,12 @@ class H5Writer:
             raise ValueError("slab does not fit the dataset")
         if arr.size == 0:
             return
-        self._f.seek(self.addr[name] + row0 * row_elems * 4)
-        self._f.write(memoryview(arr.reshape(-1)).cast("B"))
+        # positional writes: no shared file offset, so slabs can be written from several threads at once
+        mv = memoryview(arr.reshape(-1)).cast("B")
+        off, fd = self.addr[name] + row0 * row_elems * 4, self._f.fileno()
+        while len(mv):
+            k = os.pwrite(fd, mv[:1 << 30], off)
+            mv, off = mv[k:], off + k
 
     def write(self, name: str, arr: np.ndarray) -> None:
         if tuple(arr.shape) != self.shapes[name]:
