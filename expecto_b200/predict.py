@@ -136,6 +136,15 @@ def run(args) -> dict:
 
     if not torch.cuda.is_available():
         raise RuntimeError("predict needs a CUDA device (B200); there is no CPU fallback")
+    import time
+    timing, t_last = {}, time.perf_counter()
+
+    def lap(name):
+        nonlocal t_last
+        now = time.perf_counter()
+        timing[name] = timing.get(name, 0.0) + now - t_last
+        t_last = now
+
     os.makedirs(args.out_dir, exist_ok=True)
     mask = keep_mask(args.belugaFeatures, args)
     paths = [args.model_save_file.strip()] if args.model_save_file else []
@@ -144,9 +153,12 @@ def run(args) -> dict:
     if not paths:
         raise ValueError("give --model_save_file or --modelList")
     W, offsets = expand_weights([load_model(p) for p in paths], mask)
+    lap("models_s")
 
     dev = torch.device("cuda", args.device)
     data = load_strand_averaged(args.snpEffectFilePattern, int(args.maxshift), keys=("ref", "alt"), device=dev)
+    torch.cuda.synchronize(dev)
+    lap("load_h5_s")
     coor = pd.read_csv(args.coorFile_chromatin, sep="\t", header=None, comment="#")
     gene = pd.read_csv(args.geneFile, sep="\t", header=None, comment="#")
     gene = gene.drop_duplicates(keep="first")
@@ -163,6 +175,7 @@ def run(args) -> dict:
         dist = np.full(gene.shape[0], float(args.fixeddist))
     genename, strand = np.asarray(gene.iloc[:, -2]), np.asarray(gene.iloc[:, -3])
 
+    lap("tables_s")
     sel = torch.from_numpy(idx).to(dev)
     identity = len(idx) == data["ref"].shape[1] and bool(np.array_equal(idx, np.arange(len(idx))))
     scores = {}
@@ -170,6 +183,7 @@ def run(args) -> dict:
         x = data[key] if identity else data[key].index_select(1, sel)
         scores[key] = decay_score_variant(x, dist, strand, W, offsets, shifts=shift_list(int(args.maxshift))).cpu().numpy()
     ref, alt = scores["ref"], scores["alt"]
+    lap("score_s")
 
     df = coor
     df["dist"] = dist if args.fixeddist else -np.asarray(gene.iloc[:, -1])
@@ -189,7 +203,8 @@ def run(args) -> dict:
     s["SED_PROPORTION"] = np.abs(s["SED"] / ((s["REF"] + s["ALT"]) / 2))
     s.sort_values(by="SED_PROPORTION", axis=0, ascending=False).to_csv(
         f"{args.out_dir}/sed_sorted_by_proportion.tsv", header=True, sep="\t", index=False)
-    return {"n_rows": len(df), "ref": ref, "alt": alt, "models": paths}
+    lap("write_tsv_s")
+    return {"n_rows": len(df), "ref": ref, "alt": alt, "models": paths, "timing": timing}
 
 
 def main(argv=None) -> int:

@@ -150,7 +150,8 @@ def main():
     try:
         pinfo = predict.run(pa)
         res["predict_cli"] = {"rows": pinfo["n_rows"], "models": args.models, "seconds": time.perf_counter() - t0,
-                              "variants_per_s": pinfo["n_rows"] / (time.perf_counter() - t0)}
+                              "variants_per_s": pinfo["n_rows"] / (time.perf_counter() - t0),
+                              "timing": pinfo["timing"]}
     except Exception as e:  # the synthetic VCF has one filtered row: predict.py shares the reference's caveat
         res["predict_cli"] = {"error": repr(e)[:300]}
 
