@@ -53,3 +53,34 @@ def test_reads_reference_example_and_writer_is_byte_compatible(tmp_path):
     assert len(ours) == len(theirs)
     assert ours[0x800:] == theirs[0x800:]      # raw data region
     assert ours[:8] == theirs[:8]               # signature
+
+
+def test_slab_writer_threads_and_order(tmp_path):
+    """chromatin's background writer: slabs of one submission go out on several threads (positional writes),
+    submissions stay ordered, an ordered call closes the file after its slabs, errors surface to the producer."""
+    from expecto_b200.chromatin import SlabWriter
+
+    p = str(tmp_path / "bg.h5")
+    n = 64
+    a = np.random.default_rng(1).standard_normal((2 * n, 2002)).astype(np.float32)
+    w = hdf5.H5Writer(p, {"diff": (2 * n, 2002), "ref": (2 * n, 2002)})
+    sw = SlabWriter(2, n_threads=4)
+    sink = lambda name, row0, arr: w.write_rows(name, row0, arr)
+    for k in range(0, n, 16):  # forward rows at v, reverse-complement rows at n + v (chromatin.py:170-171 order)
+        s = sw.next_set()
+        tasks = [(name, r0, a[r0:r0 + 16]) for name in ("diff", "ref") for r0 in (k, n + k)]
+        sw.write(sink, tasks[:2])
+        sw.submit(s, sink, tasks[2:])
+    sw.call(w.close)
+    sw.close()
+    assert sw.bytes == 2 * a.nbytes and sw.busy_s > 0
+    with hdf5.File(p) as f:
+        assert np.array_equal(np.asarray(f["diff"]), a) and np.array_equal(np.asarray(f["ref"]), a)
+
+    sw = SlabWriter(1)
+    s = sw.next_set()
+    sw.submit(s, lambda *t: (_ for _ in ()).throw(OSError("disk full")), [("diff", 0, a[:1])])
+    with pytest.raises(OSError):
+        sw.wait_free(s)
+    with pytest.raises(OSError):
+        sw.close()
