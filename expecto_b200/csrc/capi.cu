@@ -119,6 +119,8 @@ struct bx_ctx {
   // segment mode: phase-B conv6 output and the dense FC1 operand gathered from the segment activations
   void* act6b = nullptr;
   void* fc_in = nullptr;
+  void* act4h = nullptr;  // conv4 half-pooled (row pairs), both pooling phases are finished from it
+  void* act4b = nullptr;  // phase-B pooled conv4 output
 };
 
 // RAII-ish stage timer: records an event pair around a stage when profiling is on.
@@ -189,6 +191,7 @@ static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void
   BX_CASE(8, 160, EPI_POOL4_BIAS_RELU);
   BX_CASE(8, 240, EPI_BIAS_RELU);
   BX_CASE(8, 240, EPI_POOL4_BIAS_RELU);
+  BX_CASE(8, 240, EPI_POOL2_BIAS_RELU);
   BX_CASE(8, 160, EPI_BIAS_RELU);
   BX_CASE(1, 256, EPI_PARTIAL_F32);
   BX_CASE(1, 256, EPI_BIAS_SIGMOID);
@@ -323,7 +326,7 @@ static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st, const En
 // ------------------------------------------------------------------ segment mode
 // Row pitches of every activation for "windows" of L positions (L = 2000 reproduces kLayers).
 struct Geom {
-  int L, p1, p2, p3, p4, p5, p6, l4b;
+  int L, p1, p2, p3, p4, p5, p6, l4b, ph;
 };
 static Geom make_geom(int L) {
   Geom g;
@@ -333,6 +336,7 @@ static Geom make_geom(int L) {
   g.p3 = (g.p2 - 7 + 3) / 4 * 4;     // conv3 rows, pooled by conv4's epilogue
   g.p4 = (g.p2 - 14) / 4;            // conv4 + MaxPool4 (phase A: pooling groups start at row 0)
   g.l4b = (g.p2 - 16) / 4;           // phase B: pooling groups start at row 2
+  g.ph = (g.p2 - 14) / 2;            // conv4 rows pooled in pairs (segment mode: both phases come from these)
   g.p5 = g.p4 - 7;
   g.p6 = g.p5 - 7;
   return g;
@@ -340,7 +344,7 @@ static Geom make_geom(int L) {
 
 // conv layer i over n_seg segments with explicit geometry; phase_b shifts conv4's input by two rows.
 static int run_conv_geom(bx_ctx* c, int i, int n_seg, const Geom& g, const void* in, void* out, bool phase_b,
-                         cudaStream_t st, const EncParams* enc = nullptr) {
+                         cudaStream_t st, const EncParams* enc = nullptr, bool half_pool = false) {
   const LayerDef& L = kLayers[i];
   const int pin[6] = {g.p1, g.p1, g.p2, g.p3, g.p4, g.p5};
   const int pout[6] = {g.p1, g.p2, g.p3, g.p4, g.p5, g.p6};
@@ -361,7 +365,12 @@ static int run_conv_geom(bx_ctx* c, int i, int n_seg, const Geom& g, const void*
   p.out = out;
   if (i == 0 && enc) return launch_conv1_gen(c, 1, *enc, p, st);
   const char* a = reinterpret_cast<const char*>(in) + (size_t)skip * L.cin * 2;
-  return launch_gemm(c, L.taps, L.block_n, L.epi, a, (uint64_t)p.m_rows, L.cin, c->wconv[i], (uint64_t)L.taps * L.cout,
+  int epi = L.epi;
+  if (half_pool) {  // conv4 in segment mode: MaxPool over row pairs only, [n_seg, ph, 480]
+    epi = EPI_POOL2_BIAS_RELU;
+    p.pitch_out = p.l_store = g.ph;
+  }
+  return launch_gemm(c, L.taps, L.block_n, epi, a, (uint64_t)p.m_rows, L.cin, c->wconv[i], (uint64_t)L.taps * L.cout,
                      p, st);
 }
 
@@ -436,7 +445,7 @@ int bx_ctx_destroy(bx_ctx* c) {
     if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
   }
   cudaFree(c->probs_scratch);
-  cudaFree(c->act6b); cudaFree(c->fc_in);
+  cudaFree(c->act6b); cudaFree(c->fc_in); cudaFree(c->act4h); cudaFree(c->act4b);
   if (c->s_comp) cudaStreamDestroy(c->s_comp);
   if (c->s_in) cudaStreamDestroy(c->s_in);
   if (c->s_out) cudaStreamDestroy(c->s_out);
@@ -890,6 +899,9 @@ int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_
                 segs_per_group, seg_len);
   if (!c->act6b) CK(cudaMalloc(&c->act6b, (size_t)c->cap * act_rows(6) * act_cols(6) * 2));
   if (!c->fc_in) CK(cudaMalloc(&c->fc_in, (size_t)c->cap * 106 * 640 * 2));
+  // ph <= 2*p4 + 1 and n_seg <= cap, n_seg*p4 <= cap*120 (max_segments): n_seg*ph <= cap*241 rows
+  if (!c->act4h) CK(cudaMalloc(&c->act4h, (size_t)c->cap * 241 * act_cols(4) * 2));
+  if (!c->act4b) CK(cudaMalloc(&c->act4b, (size_t)c->cap * act_rows(4) * act_cols(4) * 2));
   SegGather sg = {};
   sg.segs_per_group = segs_per_group;
   sg.n_shifts = n_shifts;
@@ -925,17 +937,31 @@ int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_
       g_launches++;
       CK(cudaGetLastError());
     }
-    for (int i = 0; i < 4; ++i) {  // conv1..conv4 (phase A pooling)
+    for (int i = 0; i < 3; ++i) {  // conv1..conv3
       StageTimer t(c, 1 + i, st);
       if (int r = run_conv_geom(c, i, ns, g, c->act[i], c->act[i + 1], false, st, gen ? &e : nullptr)) return r;
     }
+    {
+      // conv4 once, pooled over row pairs; both phases of the second MaxPool(1,4) are finished from that
+      // (phase A: groups from row 0 -> act[4]; phase B: groups from row 2 -> act4b)
+      StageTimer t(c, 4, st);
+      if (int r = run_conv_geom(c, 3, ns, g, c->act[3], c->act4h, false, st, nullptr, true)) return r;
+      const long long total = (long long)ns * g.p4 * (480 / 8);
+      const unsigned blocks = (unsigned)((total + 255) / 256);
+      if (f16)
+        pool_phases_kernel<__half><<<blocks, 256, 0, st>>>((const __half*)c->act4h, (__half*)c->act[4],
+                                                           (__half*)c->act4b, g.ph, g.p4, g.l4b, 480 / 8, total);
+      else
+        pool_phases_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)c->act4h,
+                                                                  (__nv_bfloat16*)c->act[4], (__nv_bfloat16*)c->act4b,
+                                                                  g.ph, g.p4, g.l4b, 480 / 8, total);
+      g_launches++;
+      CK(cudaGetLastError());
+    }
     for (int phase = 0; phase < 2; ++phase) {
-      if (phase == 1) {
-        if (n_shifts < 2) break;
-        StageTimer t(c, 4, st);
-        if (int r = run_conv_geom(c, 3, ns, g, c->act[3], c->act[4], true, st)) return r;
-      }
-      { StageTimer t(c, 5, st); if (int r = run_conv_geom(c, 4, ns, g, c->act[4], c->act[5], false, st)) return r; }
+      if (phase == 1 && n_shifts < 2) break;
+      { StageTimer t(c, 5, st);
+        if (int r = run_conv_geom(c, 4, ns, g, phase ? c->act4b : c->act[4], c->act[5], false, st)) return r; }
       { StageTimer t(c, 6, st);
         if (int r = run_conv_geom(c, 5, ns, g, c->act[5], phase ? c->act6b : c->act[6], false, st)) return r; }
     }

@@ -33,6 +33,8 @@ enum EpiKind : int {
   EPI_PARTIAL_F32 = 2,     // split-K partial sums: plain fp32 stores into slice ks of [k_splits, rows, ld_out]
                            // (summed in fixed order by the finaliser: deterministic, no atomics)
   EPI_BIAS_SIGMOID = 3,    // y = sigmoid(acc + b) -> fp32
+  EPI_POOL2_BIAS_RELU = 4, // y = max over 2 consecutive rows of relu(acc + b) -> 16-bit: half of a MaxPool(1,4), so
+                           // that segment mode can finish both pooling phases from one conv4 pass (pool_phases_kernel)
 };
 
 struct GemmParams {
@@ -368,6 +370,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       } else if constexpr (EPI == EPI_POOL4_BIAS_RELU) {
         valid = (r < p.m_rows) && ((l >> 2) < p.l_store);
         orow_idx = wb * p.pitch_out + (l >> 2);
+      } else if constexpr (EPI == EPI_POOL2_BIAS_RELU) {
+        valid = (r < p.m_rows) && ((l >> 1) < p.l_store);
+        orow_idx = wb * p.pitch_out + (l >> 1);
       } else {
         valid = r < p.m_rows;
         orow_idx = r;
@@ -377,7 +382,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
       // One 16-column chunk: registers -> bias/activation -> global.
       auto process = [&](const uint32_t (&v)[16], int c, const float4 (&bq)[4]) {
-        if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU) {
+        if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU || EPI == EPI_POOL2_BIAS_RELU) {
           uint32_t pk[8];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -392,6 +397,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // one 256-bit store per lane (STG.256): each warp store touches 32 rows, so halving the instruction
             // count halves the LSU transactions that bound the conv1 epilogue
             if (valid) st_global_v8(o, pk);
+          } else if constexpr (EPI == EPI_POOL2_BIAS_RELU) {
+            // max over the row pair held by lanes 2g, 2g+1; the even lane stores columns 0..7, the odd one 8..15
+#pragma unroll
+            for (int i = 0; i < 8; ++i) pk[i] = max2<T>(pk[i], __shfl_xor_sync(0xffffffffu, pk[i], 1));
+            const bool odd = lane & 1;
+            const uint4 w = odd ? make_uint4(pk[4], pk[5], pk[6], pk[7]) : make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            if (valid) *reinterpret_cast<uint4*>(o + (odd ? 8 : 0)) = w;
           } else {
             // MaxPool over the 4 rows held by lanes 4g..4g+3 (rounding is monotonic, so max after
             // rounding equals rounding after max); lane j of the group stores columns 4j..4j+3.
@@ -436,7 +448,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // bias of a chunk is read from shared memory BEFORE the TMEM wait so the two latencies overlap (ncu:
       // short-scoreboard stalls on these loads were 52 % of the conv1 epilogue's cycles)
       auto load_bias = [&](float4 (&q)[4], int c) {
-        if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU) {
+        if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU || EPI == EPI_POOL2_BIAS_RELU) {
           const float4* bp = reinterpret_cast<const float4*>(sbias + n0 + c * 16);
 #pragma unroll
           for (int i = 0; i < 4; ++i) q[i] = bp[i];

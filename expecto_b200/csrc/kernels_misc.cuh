@@ -134,6 +134,33 @@ encode_im2col_seg_kernel(const bx_window_desc* __restrict__ descs, const uint8_t
   reinterpret_cast<uint4*>(a0)[((size_t)blockIdx.y * pitch + l) * 8 + q] = v;
 }
 
+// Both phases of the second MaxPool(1,4) from conv4's half-pooled output h[n_seg, ph, C] (h[j] = max of conv4 rows
+// 2j, 2j+1): phase A pools rows 4g..4g+3 = max(h[2g], h[2g+1]); phase B (windows whose offset is an odd multiple
+// of 200 bp) pools rows 4g+2..4g+5 = max(h[2g+1], h[2g+2]).  max is exact, so both equal the fused MaxPool4
+// epilogue bit for bit.  One thread per 8 channels of one pooled row; rows >= l4b of phase B are zero-filled.
+template <typename T>
+__global__ void __launch_bounds__(256)
+pool_phases_kernel(const T* __restrict__ h, T* __restrict__ a, T* __restrict__ b, int ph, int p4, int l4b, int c8,
+                   long long total) {
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= total) return;
+  const int c = (int)(idx % c8);
+  const long long row = idx / c8;
+  const int g = (int)(row % p4);
+  const long long seg = row / p4;
+  const uint4* hp = reinterpret_cast<const uint4*>(h) + (seg * ph + 2 * g) * c8 + c;
+  auto mx = [](uint4 x, uint4 y) {
+    uint4 r;
+    r.x = max2<T>(x.x, y.x); r.y = max2<T>(x.y, y.y); r.z = max2<T>(x.z, y.z); r.w = max2<T>(x.w, y.w);
+    return r;
+  };
+  const uint4 h0 = hp[0], h1 = hp[c8];
+  reinterpret_cast<uint4*>(a)[idx] = mx(h0, h1);
+  uint4 vb = make_uint4(0, 0, 0, 0);
+  if (g < l4b) vb = mx(h1, hp[2 * (size_t)c8]);
+  reinterpret_cast<uint4*>(b)[idx] = vb;
+}
+
 // Geometry of the window -> segment mapping handed to the gather kernel.
 struct SegGather {
   int n_groups;       // variants / genes in this chunk
