@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libbeluga_b200.so")
 SRC = os.path.join(_HERE, "csrc", "capi.cu")
-SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh")] + [
+SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh", "encode.cuh")] + [
     os.path.join(ROOT, "include", "beluga_b200.h")
 ]
 
@@ -50,6 +50,7 @@ EXPORTS = [
     "bx_chromatin_outputs", "bx_chromatin_outputs_avg", "bx_decay_transform_fixed", "bx_decay_transform_variant",
     "bx_forward_onehot_host", "bx_chromatin_shift_host", "bx_ctx_profile", "bx_ctx_profile_read",
     "bx_decay_score_variant", "bx_forward_segments", "bx_segment_capacity", "bx_strand_average",
+    "bx_forward_segments_delta",
 ]
 NSTAGES = 10
 STAGE_NAMES = ["encode", "conv1", "conv2", "conv3", "conv4", "conv5", "conv6", "fc1", "fc2", "outputs"]
@@ -115,6 +116,7 @@ def lib() -> C.CDLL:
     L.bx_chromatin_shift_host.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp]
     L.bx_decay_score_variant.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
     L.bx_forward_segments.argtypes = [vp, vp, vp, i32, i32, i32, i32, C.POINTER(C.c_int32), i32, vp, vp]
+    L.bx_forward_segments_delta.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, C.POINTER(C.c_int32), i32, vp, vp]
     L.bx_segment_capacity.argtypes = [vp, i32]
     L.bx_strand_average.argtypes = [vp, i32, vp, vp]
     L.bx_ctx_profile.argtypes = [vp, i32]

@@ -53,6 +53,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--mode", default="segments", choices=["segments", "windows"],
                    help="segments: conv stack once per variant segment (shared activations across shifts, "
                         "bit-identical); windows: every window separately, as the reference does")
+    p.add_argument("--no_delta", action="store_true",
+                   help="segment mode: run the alt segments of substitutions in full instead of as patches around the "
+                        "variant (same results bit for bit; for comparisons)")
     p.add_argument("--upstream_layout", action="store_true",
                    help="also write upstream ExPecto's {inputfile}.shift_{s}.diff.h5 with one 'pred' dataset")
     return p
@@ -243,8 +246,52 @@ def _runs(idx: np.ndarray):
         yield int(a), int(idx[a]), int(b - a)
 
 
+def _segment_chunks(engine, genome, chroms, pos, refs, alts, maxshift: int, ids, cap: int, delta: bool, stats=None):
+    """Enqueue segment-mode forwards for the variants ``ids`` in chunks of at most ``cap`` and yield
+    (variant indices, probs [S, m, 4, 2002] on the device).  Substitutions (SNVs / MNVs, ``windows.delta_eligible``)
+    go through ``forward_segments_delta`` — ref segments in full, alt alleles as short patches — when ``delta``."""
+    from .windows import (check_valid_bases, chromatin_delta_descs, chromatin_segment_descs, delta_eligible)
+
+    seg_len = 2000 + 2 * maxshift
+    ids = np.asarray(ids, dtype=np.int64)
+    sub = delta_eligible([len(refs[i]) for i in ids], [len(alts[i]) for i in ids]) if (delta and len(ids)) else \
+        np.zeros(len(ids), bool)
+    if stats is not None:
+        stats["delta_variants"] = int(sub.sum())
+    import torch
+
+    for c0 in range(0, len(ids), cap):
+        # chunks stay contiguous in variant order (one row run per dataset and strand when they are written): the
+        # chunk's substitutions and its other variants are run separately and merged on the device
+        idx, is_sub = ids[c0:c0 + cap], sub[c0:c0 + cap]
+        parts = []
+        for kind, sel in (("delta", np.flatnonzero(is_sub)), ("full", np.flatnonzero(~is_sub))):
+            if len(sel) == 0:
+                continue
+            part = idx[sel]
+            m = len(part)
+            args = (genome, [chroms[i] for i in part], pos[part], [refs[i] for i in part], [alts[i] for i in part],
+                    maxshift)
+            if kind == "delta":
+                rd, pd, codes, k_of, row0, plen = chromatin_delta_descs(*args)
+                check_valid_bases(genome, rd)
+                probs = engine.forward_segments_delta(rd, pd, codes, m, seg_len, plen, row0, k_of, shift_major=True)
+            else:
+                descs, codes, k_of = chromatin_segment_descs(*args)
+                check_valid_bases(genome, descs)
+                probs = engine.forward_segments(descs, codes, m, 4, seg_len, k_of, shift_major=True)
+            parts.append((sel, probs))
+        if len(parts) == 1:
+            yield idx, parts[0][1]
+        else:
+            merged = torch.empty((parts[0][1].shape[0], len(idx), 4, 2002), dtype=torch.float32, device=engine.device)
+            for sel, probs in parts:
+                merged.index_copy_(1, torch.from_numpy(sel).to(engine.device), probs)
+            yield idx, merged
+
+
 def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshift: int, sinks: dict,
-                                writer: SlabWriter | None = None) -> dict:
+                                writer: SlabWriter | None = None, delta: bool = True) -> dict:
     """The whole shift loop (chromatin.py:243-286) in segment mode: the ref/alt x fwd/rc sequences of a variant are
     encoded once as 2000+2*maxshift-bp segments, the conv stack runs once per segment and all shifts' ref/alt/diff
     rows come out together (bit-identical to the per-shift path).  ``sinks[shift](name, row0, array)`` receives the
@@ -253,8 +300,7 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
     import torch
 
     from .engine import chromatin_outputs
-    from .windows import (AlleleTable, check_valid_bases, chromatin_segment_descs, chromatin_window_descs,
-                          segment_eligible)
+    from .windows import check_valid_bases, chromatin_window_descs, segment_eligible
 
     n = len(pos)
     shifts = shift_list(maxshift)
@@ -273,7 +319,8 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
     import time
     copy_stream = torch.cuda.Stream(device=engine.device)
     pending = None
-    t_host = {"descriptor_s": 0.0, "enqueue_s": 0.0, "gpu_wait_s": 0.0}
+    t_host = {"enqueue_s": 0.0, "gpu_wait_s": 0.0}
+    stats = {}
 
     def flush(p):
         done, si_set, idx, m = p
@@ -295,20 +342,13 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
                 writer.write(sinks[shift], tasks)
 
     with torch.cuda.device(engine.device):
-        for c0 in range(0, len(elig), cap):
-            idx = elig[c0:c0 + cap]
+        t1 = time.perf_counter()
+        for idx, probs in _segment_chunks(engine, genome, chroms, pos, refs, alts, maxshift, elig, cap, delta, stats):
             m = len(idx)
-            t0 = time.perf_counter()
-            descs, codes, k_of = chromatin_segment_descs(genome, [chroms[i] for i in idx], pos[idx],
-                                                         [refs[i] for i in idx], [alts[i] for i in idx], maxshift)
-            check_valid_bases(genome, descs)
-            t1 = time.perf_counter()
-            probs = engine.forward_segments(descs, codes, m, 4, seg_len, k_of, shift_major=True)  # [S, m, 4, 2002]
             outs = [chromatin_outputs(probs[si].reshape(4 * m, 2002), m) for si in range(S)]
             computed = torch.cuda.Event()
             computed.record()
-            t_host["descriptor_s"] += t1 - t0
-            t_host["enqueue_s"] += time.perf_counter() - t1
+            t_host["enqueue_s"] += time.perf_counter() - t1   # descriptors + launches of this chunk
             si_set = writer.next_set()  # blocks until the set's previous contents are on disk
             buf = pinned[si_set]
             with torch.cuda.stream(copy_stream):
@@ -323,6 +363,7 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
             if pending is not None:
                 flush(pending)
             pending = (done, si_set, idx, m)
+            t1 = time.perf_counter()
         if pending is not None:
             flush(pending)
     # long indels etc.: per-window path, one variant-run at a time
@@ -343,17 +384,18 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
     if own_writer:
         writer.close()
     return {"segment_variants": int(len(elig)), "window_variants": int(len(rest)), "chunk_variants": int(cap),
+            "delta_variants": int(stats.get("delta_variants", 0)),
             "writer_busy_s": writer.busy_s, "writer_bytes": writer.bytes, "producer_blocked_s": writer.blocked_s,
             **{"host_" + k: v for k, v in t_host.items()}}
 
 
-def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, maxshift: int):
+def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, maxshift: int, delta: bool = True):
     """Segment mode with the results left in HBM: {shift: (ref, alt, diff)} device tensors [2n,2002] in the strand-
     stacked row order — the operands of the per-shift NCCL gather when variants are sharded over GPUs."""
     import torch
 
     from .engine import chromatin_outputs
-    from .windows import check_valid_bases, chromatin_segment_descs, chromatin_window_descs, segment_eligible
+    from .windows import check_valid_bases, chromatin_window_descs, segment_eligible
 
     n = len(pos)
     shifts = shift_list(maxshift)
@@ -371,13 +413,8 @@ def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, 
             full.index_copy_(0, ii, part[:m])
             full.index_copy_(0, ii + n, part[m:2 * m])
 
-    for c0 in range(0, len(elig), cap):
-        idx = elig[c0:c0 + cap]
+    for idx, probs in _segment_chunks(engine, genome, chroms, pos, refs, alts, maxshift, elig, cap, delta):
         m = len(idx)
-        descs, codes, k_of = chromatin_segment_descs(genome, [chroms[i] for i in idx], pos[idx], [refs[i] for i in idx],
-                                                     [alts[i] for i in idx], maxshift)
-        check_valid_bases(genome, descs)
-        probs = engine.forward_segments(descs, codes, m, 4, seg_len, k_of, shift_major=True)
         for si, shift in enumerate(shifts):
             scatter(shift, idx, chromatin_outputs(probs[si].reshape(4 * m, 2002), m))
         del probs
@@ -461,7 +498,8 @@ def run(args, engine=None, genome=None) -> dict:
     gb = max(1, min(args.gpu_batch, max(n_local, 1)))
     seg_outs = None
     if args.mode == "segments" and args.maxshift % 200 == 0 and world > 1 and args.gather == "nccl":
-        seg_outs = predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, args.maxshift)
+        seg_outs = predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, args.maxshift,
+                                                      delta=not args.no_delta)
     pinned, writer = None, None
     if world == 1 or args.gather == "file":
         n_sets = 2  # slab k's file writes overlap slab k+1's GPU work (also across shifts)
@@ -564,7 +602,7 @@ def _run_segments(args, engine, genome, chroms, pos, refs, alts, n, lo, n_local,
         return sink
 
     info = predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, args.maxshift,
-                                       {s: make_sink(s) for s in shifts})
+                                       {s: make_sink(s) for s in shifts}, delta=not args.no_delta)
     for s in shifts:
         ws[s].close()
         if s in us:

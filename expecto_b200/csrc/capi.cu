@@ -121,6 +121,9 @@ struct bx_ctx {
   void* fc_in = nullptr;
   void* act4h = nullptr;  // conv4 half-pooled (row pairs), both pooling phases are finished from it
   void* act4b = nullptr;  // phase-B pooled conv4 output
+  void* patch6a = nullptr;  // delta mode: conv6 outputs of the alt patches (phase A / B)
+  void* patch6b = nullptr;
+  size_t patch6_bytes = 0;
 };
 
 // RAII-ish stage timer: records an event pair around a stage when profiling is on.
@@ -446,6 +449,7 @@ int bx_ctx_destroy(bx_ctx* c) {
   }
   cudaFree(c->probs_scratch);
   cudaFree(c->act6b); cudaFree(c->fc_in); cudaFree(c->act4h); cudaFree(c->act4b);
+  cudaFree(c->patch6a); cudaFree(c->patch6b);
   if (c->s_comp) cudaStreamDestroy(c->s_comp);
   if (c->s_in) cudaStreamDestroy(c->s_in);
   if (c->s_out) cudaStreamDestroy(c->s_out);
@@ -879,34 +883,107 @@ int bx_segment_capacity(bx_ctx* c, int seg_len) {
   return max_segments(c, make_geom(seg_len));
 }
 
-int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n_groups,
-                        int segs_per_group, int seg_len, int n_shifts, const int32_t* k_of_shift, int shift_major,
-                        float* probs_dev, void* stream) {
-  if (!c || n_groups < 0 || !k_of_shift) return fail(BX_E_ARG, "invalid arguments");
-  if (n_groups == 0) return 0;
-  if (!descs_dev || !alleles_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
-  if (segs_per_group < 1 || n_shifts < 1 || n_shifts > 200 || seg_len != 2000 + 200 * (n_shifts - 1))
-    return fail(BX_E_ARG, "segment mode needs seg_len == 2000 + 200*(n_shifts-1) and 1 <= n_shifts <= 200");
-  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
-  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
-  CK(cudaSetDevice(c->device));
-  cudaStream_t st = (cudaStream_t)stream;
+}  // extern "C"
+
+// conv1..conv6 over ns segments of L positions described by d: conv6 output of pooling phase A -> out6a and
+// (two_phases) of phase B -> out6b, [ns, g.p6, 640] each.  Uses the context's activation scratch act[0..5].
+static int run_segment_convs(bx_ctx* c, const bx_window_desc* d, const uint8_t* alleles_dev, int ns, int L,
+                             const Geom& g, void* out6a, void* out6b, bool two_phases, cudaStream_t st) {
+  const bool f16 = c->dtype == BX_DTYPE_F16;
+  EncParams e = {};
+  e.descs = d; e.alleles = alleles_dev; e.bases2 = c->bases2; e.nmask = c->nmask; e.n_bases = c->n_bases;
+  e.L = L; e.n_seg = ns;
+  const bool gen = conv1_gen_enabled();
+  if (!gen) {
+    StageTimer t(c, 0, st);
+    dim3 grid((g.p1 * 8 + 255) / 256, ns);
+    if (f16)
+      encode_im2col_seg_kernel<__half><<<grid, 256, 0, st>>>(d, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                             (__half*)c->act[0], L, g.p1);
+    else
+      encode_im2col_seg_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(d, alleles_dev, c->bases2, c->nmask, c->n_bases,
+                                                                    (__nv_bfloat16*)c->act[0], L, g.p1);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
+  for (int i = 0; i < 3; ++i) {  // conv1..conv3
+    StageTimer t(c, 1 + i, st);
+    if (int r = run_conv_geom(c, i, ns, g, c->act[i], c->act[i + 1], false, st, gen ? &e : nullptr)) return r;
+  }
+  {
+    // conv4 once, pooled over row pairs; both phases of the second MaxPool(1,4) are finished from that
+    // (phase A: groups from row 0 -> act[4]; phase B: groups from row 2 -> act4b)
+    StageTimer t(c, 4, st);
+    if (int r = run_conv_geom(c, 3, ns, g, c->act[3], c->act4h, false, st, nullptr, true)) return r;
+    const long long total = (long long)ns * g.p4 * (480 / 8);
+    const unsigned blocks = (unsigned)((total + 255) / 256);
+    if (f16)
+      pool_phases_kernel<__half><<<blocks, 256, 0, st>>>((const __half*)c->act4h, (__half*)c->act[4],
+                                                         (__half*)c->act4b, g.ph, g.p4, g.l4b, 480 / 8, total);
+    else
+      pool_phases_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)c->act4h,
+                                                                (__nv_bfloat16*)c->act[4], (__nv_bfloat16*)c->act4b,
+                                                                g.ph, g.p4, g.l4b, 480 / 8, total);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
+  for (int phase = 0; phase < 2; ++phase) {
+    if (phase == 1 && !two_phases) break;
+    { StageTimer t(c, 5, st);
+      if (int r = run_conv_geom(c, 4, ns, g, phase ? c->act4b : c->act[4], c->act[5], false, st)) return r; }
+    { StageTimer t(c, 6, st);
+      if (int r = run_conv_geom(c, 5, ns, g, c->act[5], phase ? out6b : out6a, false, st)) return r; }
+  }
+  return 0;
+}
+
+// Segment mode proper.  patch_descs_dev == nullptr: descs_dev holds segs_out segments per group.  Delta mode
+// (patch_descs_dev != nullptr, segs_out == 4): descs_dev holds the group's two REF segments (fwd, rc) and
+// patch_descs_dev two short ALT patches (fwd, rc) of patch_len positions that start 16*patch_row0 positions into
+// the alt segments; alt windows read the conv6 rows the substitution can reach from the patch and all others from
+// the ref segment (identical there).
+static int forward_segments_impl(bx_ctx* c, const bx_window_desc* descs_dev, const bx_window_desc* patch_descs_dev,
+                                 const uint8_t* alleles_dev, int n_groups, int segs_out, int seg_len, int patch_len,
+                                 int patch_row0, int n_shifts, const int32_t* k_of_shift, int shift_major,
+                                 float* probs_dev, cudaStream_t st) {
+  const bool delta = patch_descs_dev != nullptr;
+  const int segs_in = delta ? 2 : segs_out;
   const Geom g = make_geom(seg_len);
   const int seg_cap = max_segments(c, g);
-  const int grp_cap = seg_cap / segs_per_group;
+  const int grp_cap = seg_cap / segs_in;
   if (grp_cap < 1)
     return fail(BX_E_ARG, "context capacity (%d windows) is too small for %d segments of %d positions", c->cap,
-                segs_per_group, seg_len);
+                segs_in, seg_len);
   if (!c->act6b) CK(cudaMalloc(&c->act6b, (size_t)c->cap * act_rows(6) * act_cols(6) * 2));
   if (!c->fc_in) CK(cudaMalloc(&c->fc_in, (size_t)c->cap * 106 * 640 * 2));
   // ph <= 2*p4 + 1 and n_seg <= cap, n_seg*p4 <= cap*120 (max_segments): n_seg*ph <= cap*241 rows
   if (!c->act4h) CK(cudaMalloc(&c->act4h, (size_t)c->cap * 241 * act_cols(4) * 2));
   if (!c->act4b) CK(cudaMalloc(&c->act4b, (size_t)c->cap * act_rows(4) * act_cols(4) * 2));
   SegGather sg = {};
-  sg.segs_per_group = segs_per_group;
+  sg.segs_per_group = segs_out;
   sg.n_shifts = n_shifts;
   sg.shift_major = shift_major ? 1 : 0;
   sg.p6 = g.p6;
+  Geom gp = {};
+  if (delta) {
+    gp = make_geom(patch_len);
+    sg.delta = 1;
+    sg.p6p = gp.p6;
+    sg.row0 = patch_row0;
+    sg.valid_a = gp.p6;             // patch conv6 rows computed from complete receptive fields, phase A / phase B
+    sg.valid_b = gp.l4b - 14;
+    if (sg.valid_b < 1 || gp.p6 < 1) return fail(BX_E_ARG, "patch_len %d is too short", patch_len);
+    const size_t need = (size_t)std::min(grp_cap, n_groups) * 2 * gp.p6 * 640 * 2;
+    if (need > c->patch6_bytes) {
+      CK(cudaStreamSynchronize(st));
+      cudaFree(c->patch6a); cudaFree(c->patch6b);
+      c->patch6a = c->patch6b = nullptr;
+      c->patch6_bytes = 0;
+      CK(cudaMalloc(&c->patch6a, need));
+      CK(cudaMalloc(&c->patch6b, need));
+      c->patch6_bytes = need;
+    }
+  }
   for (int i = 0; i < n_shifts; ++i) {
     if (k_of_shift[i] < 0 || k_of_shift[i] >= n_shifts) return fail(BX_E_ARG, "k_of_shift[%d] out of range", i);
     sg.k_of_shift[i] = k_of_shift[i];
@@ -919,68 +996,30 @@ int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_
                 grp_cap);
   for (int g0 = 0; g0 < n_groups; g0 += grp_cap) {
     const int ng = std::min(grp_cap, n_groups - g0);
-    const int ns = ng * segs_per_group;
-    const bx_window_desc* d = descs_dev + (size_t)g0 * segs_per_group;
-    EncParams e = {};
-    e.descs = d; e.alleles = alleles_dev; e.bases2 = c->bases2; e.nmask = c->nmask; e.n_bases = c->n_bases;
-    e.L = seg_len; e.n_seg = ns;
-    const bool gen = conv1_gen_enabled();
-    if (!gen) {
-      StageTimer t(c, 0, st);
-      dim3 grid((g.p1 * 8 + 255) / 256, ns);
-      if (f16)
-        encode_im2col_seg_kernel<__half><<<grid, 256, 0, st>>>(d, alleles_dev, c->bases2, c->nmask, c->n_bases,
-                                                               (__half*)c->act[0], seg_len, g.p1);
-      else
-        encode_im2col_seg_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(d, alleles_dev, c->bases2, c->nmask, c->n_bases,
-                                                                      (__nv_bfloat16*)c->act[0], seg_len, g.p1);
-      g_launches++;
-      CK(cudaGetLastError());
-    }
-    for (int i = 0; i < 3; ++i) {  // conv1..conv3
-      StageTimer t(c, 1 + i, st);
-      if (int r = run_conv_geom(c, i, ns, g, c->act[i], c->act[i + 1], false, st, gen ? &e : nullptr)) return r;
-    }
-    {
-      // conv4 once, pooled over row pairs; both phases of the second MaxPool(1,4) are finished from that
-      // (phase A: groups from row 0 -> act[4]; phase B: groups from row 2 -> act4b)
-      StageTimer t(c, 4, st);
-      if (int r = run_conv_geom(c, 3, ns, g, c->act[3], c->act4h, false, st, nullptr, true)) return r;
-      const long long total = (long long)ns * g.p4 * (480 / 8);
-      const unsigned blocks = (unsigned)((total + 255) / 256);
-      if (f16)
-        pool_phases_kernel<__half><<<blocks, 256, 0, st>>>((const __half*)c->act4h, (__half*)c->act[4],
-                                                           (__half*)c->act4b, g.ph, g.p4, g.l4b, 480 / 8, total);
-      else
-        pool_phases_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)c->act4h,
-                                                                  (__nv_bfloat16*)c->act[4], (__nv_bfloat16*)c->act4b,
-                                                                  g.ph, g.p4, g.l4b, 480 / 8, total);
-      g_launches++;
-      CK(cudaGetLastError());
-    }
-    for (int phase = 0; phase < 2; ++phase) {
-      if (phase == 1 && n_shifts < 2) break;
-      { StageTimer t(c, 5, st);
-        if (int r = run_conv_geom(c, 4, ns, g, phase ? c->act4b : c->act[4], c->act[5], false, st)) return r; }
-      { StageTimer t(c, 6, st);
-        if (int r = run_conv_geom(c, 5, ns, g, c->act[5], phase ? c->act6b : c->act[6], false, st)) return r; }
-    }
+    const bx_window_desc* d = descs_dev + (size_t)g0 * segs_in;
+    if (int r = run_segment_convs(c, d, alleles_dev, ng * segs_in, seg_len, g, c->act[6], c->act6b, n_shifts > 1, st))
+      return r;
+    if (delta)
+      if (int r = run_segment_convs(c, patch_descs_dev + (size_t)g0 * 2, alleles_dev, ng * 2, patch_len, gp,
+                                    c->patch6a, c->patch6b, n_shifts > 1, st))
+        return r;
     // dense layers per window, in final output order, `cap` windows at a time
     sg.n_groups = ng;
-    const long long n_win = (long long)ns * n_shifts;
-    float* out = probs_dev + (size_t)g0 * segs_per_group * n_shifts * BX_FEATURES;  // group-major chunks are contiguous
+    const long long n_win = (long long)ng * segs_out * n_shifts;
+    float* out = probs_dev + (size_t)g0 * segs_out * n_shifts * BX_FEATURES;  // group-major chunks are contiguous
     void* saved = c->act[6];
     for (long long w0 = 0; w0 < n_win; w0 += c->cap) {
       const int m = (int)std::min<long long>(c->cap, n_win - w0);
       {
         StageTimer t(c, 7, st);
         if (f16)
-          gather_fc1_kernel<__half><<<m, 256, 0, st>>>((const __half*)saved, (const __half*)c->act6b, d, sg, w0,
+          gather_fc1_kernel<__half><<<m, 256, 0, st>>>((const __half*)saved, (const __half*)c->act6b,
+                                                       (const __half*)c->patch6a, (const __half*)c->patch6b, d, sg, w0,
                                                        (__half*)c->fc_in);
         else
-          gather_fc1_kernel<__nv_bfloat16><<<m, 256, 0, st>>>((const __nv_bfloat16*)saved,
-                                                              (const __nv_bfloat16*)c->act6b, d, sg, w0,
-                                                              (__nv_bfloat16*)c->fc_in);
+          gather_fc1_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(
+              (const __nv_bfloat16*)saved, (const __nv_bfloat16*)c->act6b, (const __nv_bfloat16*)c->patch6a,
+              (const __nv_bfloat16*)c->patch6b, d, sg, w0, (__nv_bfloat16*)c->fc_in);
         g_launches++;
         CK(cudaGetLastError());
         c->act[6] = c->fc_in;  // run_fc1 reads its operand from act[6]
@@ -993,6 +1032,42 @@ int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_
     }
   }
   return 0;
+}
+
+extern "C" {
+
+int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int n_groups,
+                        int segs_per_group, int seg_len, int n_shifts, const int32_t* k_of_shift, int shift_major,
+                        float* probs_dev, void* stream) {
+  if (!c || n_groups < 0 || !k_of_shift) return fail(BX_E_ARG, "invalid arguments");
+  if (n_groups == 0) return 0;
+  if (!descs_dev || !alleles_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
+  if (segs_per_group < 1 || n_shifts < 1 || n_shifts > 200 || seg_len != 2000 + 200 * (n_shifts - 1))
+    return fail(BX_E_ARG, "segment mode needs seg_len == 2000 + 200*(n_shifts-1) and 1 <= n_shifts <= 200");
+  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  CK(cudaSetDevice(c->device));
+  return forward_segments_impl(c, descs_dev, nullptr, alleles_dev, n_groups, segs_per_group, seg_len, 0, 0, n_shifts,
+                               k_of_shift, shift_major, probs_dev, (cudaStream_t)stream);
+}
+
+int bx_forward_segments_delta(bx_ctx* c, const bx_window_desc* ref_descs_dev, const bx_window_desc* patch_descs_dev,
+                              const uint8_t* alleles_dev, int n_groups, int seg_len, int patch_len, int patch_row0,
+                              int n_shifts, const int32_t* k_of_shift, int shift_major, float* probs_dev,
+                              void* stream) {
+  if (!c || n_groups < 0 || !k_of_shift) return fail(BX_E_ARG, "invalid arguments");
+  if (n_groups == 0) return 0;
+  if (!ref_descs_dev || !patch_descs_dev || !alleles_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
+  if (n_shifts < 1 || n_shifts > 200 || seg_len != 2000 + 200 * (n_shifts - 1))
+    return fail(BX_E_ARG, "segment mode needs seg_len == 2000 + 200*(n_shifts-1) and 1 <= n_shifts <= 200");
+  if (patch_len < 336 || patch_len % 16 || patch_row0 < 0 || 16 * patch_row0 + patch_len > seg_len)
+    return fail(BX_E_ARG, "patch must be a multiple of 16 positions (>= 336) inside the segment, starting at a multiple "
+                          "of 16 (patch_len=%d patch_row0=%d seg_len=%d)", patch_len, patch_row0, seg_len);
+  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  CK(cudaSetDevice(c->device));
+  return forward_segments_impl(c, ref_descs_dev, patch_descs_dev, alleles_dev, n_groups, 4, seg_len, patch_len,
+                               patch_row0, n_shifts, k_of_shift, shift_major, probs_dev, (cudaStream_t)stream);
 }
 
 }  // extern "C"

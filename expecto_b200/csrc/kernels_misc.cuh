@@ -164,10 +164,13 @@ pool_phases_kernel(const T* __restrict__ h, T* __restrict__ a, T* __restrict__ b
 // Geometry of the window -> segment mapping handed to the gather kernel.
 struct SegGather {
   int n_groups;       // variants / genes in this chunk
-  int segs_per_group; // 4 (ref fwd, ref rc, alt fwd, alt rc) or 2 (fwd, rc)
+  int segs_per_group; // windows' segments per group: 4 (ref fwd, ref rc, alt fwd, alt rc) or 2 (fwd, rc)
   int n_shifts;       // windows per segment
   int shift_major;    // 1: window index = (shift, group, seg) [chromatin]; 0: (group, shift, seg) [TSS]
   int p6;             // rows per segment of the conv6 output
+  // delta mode: only the two ref segments of a group were run in full; alt windows take conv6 rows
+  // [row0, row0 + valid) from the group's alt patch and every other row from the ref segment of the same strand
+  int delta, p6p, row0, valid_a, valid_b;
   int k_of_shift[200]; // offset index (window start = 200*k positions into a non-reversed segment) per shift index
 };
 
@@ -175,23 +178,37 @@ struct SegGather {
 // One block per window; 135,680 contiguous bytes each.  Window w0 + blockIdx.x of the final output order.
 template <typename T>
 __global__ void __launch_bounds__(256)
-gather_fc1_kernel(const T* __restrict__ act6a, const T* __restrict__ act6b, const bx_window_desc* __restrict__ descs,
-                  const SegGather g, long long w0, T* __restrict__ dst) {
+gather_fc1_kernel(const T* __restrict__ act6a, const T* __restrict__ act6b, const T* __restrict__ patch6a,
+                  const T* __restrict__ patch6b, const bx_window_desc* __restrict__ descs, const SegGather g,
+                  long long w0, T* __restrict__ dst) {
   const long long w = w0 + blockIdx.x;
   const int q = (int)(w % g.segs_per_group);
   const long long r = w / g.segs_per_group;
   int grp, si;
   if (g.shift_major) { si = (int)(r / g.n_groups); grp = (int)(r % g.n_groups); }
   else { grp = (int)(r / g.n_shifts); si = (int)(r % g.n_shifts); }
-  const long long seg = (long long)grp * g.segs_per_group + q;
+  // segment that was run in full for this window (delta mode: the ref segment of the same strand)
+  const long long seg = g.delta ? (long long)grp * 2 + (q & 1) : (long long)grp * g.segs_per_group + q;
   int k = g.k_of_shift[si];
   if (descs[seg].flags & 2) k = g.n_shifts - 1 - k;  // reversed offset order (rc segments, '-' strand genes)
   const int j = k >> 1;
-  const T* src = ((k & 1) ? act6b : act6a) + ((size_t)seg * g.p6 + ((k & 1) ? 12 : 0) + 25 * j) * 640;
+  const int off = ((k & 1) ? 12 : 0) + 25 * j;       // first conv6 row of the window within its phase
+  const T* src = ((k & 1) ? act6b : act6a) + ((size_t)seg * g.p6 + off) * 640;
   const uint4* s4 = reinterpret_cast<const uint4*>(src);
   uint4* d4 = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * 106 * 640);
   constexpr int N16 = 106 * 640 * 2 / 16;
-  for (int i = threadIdx.x; i < N16; i += 256) d4[i] = __ldg(s4 + i);
+  if (g.delta && q >= 2) {
+    const int valid = (k & 1) ? g.valid_b : g.valid_a;
+    const int lo = g.row0 - off;                      // window rows [lo, lo + valid) come from the patch
+    const uint4* p4 = reinterpret_cast<const uint4*>(((k & 1) ? patch6b : patch6a) + (size_t)seg * g.p6p * 640);
+    for (int i = threadIdx.x; i < N16; i += 256) {
+      const int l = i / 80;                           // 80 x 16 bytes per 640-channel row
+      const int pr = l - lo;
+      d4[i] = (pr >= 0 && pr < valid) ? __ldg(p4 + (size_t)pr * 80 + (i - l * 80)) : __ldg(s4 + i);
+    }
+  } else {
+    for (int i = threadIdx.x; i < N16; i += 256) d4[i] = __ldg(s4 + i);
+  }
 }
 
 // ------------------------------------------------------------------ weight re-layout (run once)

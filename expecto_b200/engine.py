@@ -145,6 +145,27 @@ class BelugaEngine:
                                         out.data_ptr(), _stream_ptr(self.device)))
         return out
 
+    def forward_segments_delta(self, ref_descs: np.ndarray, patch_descs: np.ndarray, alleles: np.ndarray,
+                               n_groups: int, seg_len: int, patch_len: int, patch_row0: int, k_of_shift: np.ndarray,
+                               shift_major: bool, out: torch.Tensor | None = None) -> torch.Tensor:
+        """Segment mode for substitutions (bx_forward_segments_delta): the two ref segments of each variant run in
+        full, the alt alleles only as ``patch_len``-position patches around the variant.  Returns fp32
+        [n_shifts, n_groups, 4, 2002] (``shift_major``) or [n_groups, n_shifts, 4, 2002] in the order ref fwd, ref rc,
+        alt fwd, alt rc — bit-identical to ``forward_segments`` on the four full segments."""
+        k = np.ascontiguousarray(k_of_shift, dtype=np.int32)
+        S = int(k.size)
+        assert len(ref_descs) == 2 * n_groups and len(patch_descs) == 2 * n_groups
+        both = np.concatenate([np.ascontiguousarray(ref_descs), np.ascontiguousarray(patch_descs)])
+        d, a = self._upload_descs(both, alleles)
+        shape = (S, n_groups, 4, N_FEATURES) if shift_major else (n_groups, S, 4, N_FEATURES)
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float32, device=self.device)
+        check(lib().bx_forward_segments_delta(self._ctx, d.data_ptr(), d.data_ptr() + 2 * n_groups * both.dtype.itemsize,
+                                              a.data_ptr(), n_groups, int(seg_len), int(patch_len), int(patch_row0), S,
+                                              k.ctypes.data_as(C.POINTER(C.c_int32)), 1 if shift_major else 0,
+                                              out.data_ptr(), _stream_ptr(self.device)))
+        return out
+
     def forward_onehot(self, onehot: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
         """``onehot``: uint8/bool [n,4,2000] (or [n,4,1,2000]) on this device -> fp32 [n,2002]."""
         x = onehot.reshape(-1, 4, WINDOW)

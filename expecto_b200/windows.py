@@ -211,6 +211,80 @@ def chromatin_segment_descs(genome: PackedGenome, chroms, pos, refs: list[str], 
     return out.reshape(-1), tab.codes, k
 
 
+RECEPTIVE_FIELD = 310  # input positions one conv6 row depends on (8,8,pool4,8,8,pool4,8,8 with strides 1,1,4,4,4,16,16,16)
+DELTA_MAX_ALLELE = 16  # longest substitution handled by the patch path
+
+
+def segment_geometry(L: int) -> dict:
+    """Row counts of every activation for a segment of L positions (mirror of capi.cu: make_geom)."""
+    p2 = (L - 14) // 4
+    p4 = (p2 - 14) // 4
+    l4b = (p2 - 16) // 4
+    return {"p1": (L - 7 + 3) // 4 * 4, "p2": p2, "p3": (p2 - 7 + 3) // 4 * 4, "p4": p4, "l4b": l4b, "p5": p4 - 7,
+            "p6": p4 - 14, "valid_a": p4 - 14, "valid_b": l4b - 14}
+
+
+def delta_eligible(ref_len: np.ndarray, alt_len: np.ndarray) -> np.ndarray:
+    """Substitutions (SNVs / MNVs): the alt segment equals the ref segment outside the allele, position for position."""
+    ref_len = np.asarray(ref_len, dtype=np.int64)
+    alt_len = np.asarray(alt_len, dtype=np.int64)
+    return (ref_len == alt_len) & (ref_len >= 1) & (ref_len <= DELTA_MAX_ALLELE)
+
+
+def sub_descs(d: np.ndarray, start: int, length: int, seg_len: int) -> np.ndarray:
+    """Descriptors of the strand-oriented positions [start, start+length) of segments described by ``d``
+    (``seg_len`` positions each).  Reverse-complement segments are stored forward, so their range is mirrored."""
+    rc = (d["flags"] & 1).astype(bool)
+    f0 = np.where(rc, seg_len - start - length, start).astype(np.int64)   # first forward-strand position kept
+    a0, a1 = d["len1"].astype(np.int64), d["len1"].astype(np.int64) + d["alen"]
+    out = d.copy()
+    len1 = np.clip(a0 - f0, 0, length)
+    alen = np.clip(np.minimum(a1, f0 + length) - np.maximum(a0, f0), 0, None)
+    out["g1"] = d["g1"] + f0
+    out["len1"] = len1
+    out["alen"] = alen
+    out["aoff"] = d["aoff"] + np.maximum(0, f0 - a0)
+    out["g2"] = d["g2"] + np.maximum(0, f0 - a1)
+    out["len2"] = length - len1 - alen
+    return out
+
+
+def delta_patch_geometry(maxshift: int, max_allele: int = DELTA_MAX_ALLELE) -> tuple[int, int]:
+    """(patch_row0, patch_len) for substitutions of up to ``max_allele`` bases: the patch starts 16*patch_row0
+    positions into the alt segment and its valid conv6 rows cover every row whose receptive field reaches the allele,
+    in both pooling phases (phase B rows sit 8 positions later), on both strands."""
+    seg_len = INPUTSIZE + 2 * maxshift
+    v0_f = maxshift + 999                       # allele start in the forward segment (_allele_segment, la == ref_len)
+    starts = [v0_f, seg_len - v0_f - max_allele, seg_len - v0_f - 1]
+    ends = [v0_f + max_allele, seg_len - v0_f]
+    row0 = (min(starts) - (RECEPTIVE_FIELD + 7)) // 16           # first row of either phase that can see the allele
+    last = (max(ends) - 1) // 16
+    rows = last - row0 + 1
+    L = 16 * ((16 * (rows - 1) + RECEPTIVE_FIELD + 8 + 15) // 16)
+    while min(segment_geometry(L)["valid_a"], segment_geometry(L)["valid_b"]) < rows:
+        L += 16
+    if row0 < 0 or 16 * row0 + L > seg_len:
+        raise ValueError("segment too short for a delta patch")
+    return int(row0), int(L)
+
+
+def chromatin_delta_descs(genome: PackedGenome, chroms, pos, refs: list[str], alts: list[str], maxshift: int = 800):
+    """Segment mode for substitutions: per variant the two full ref segments {ref fwd, ref rc} and two short alt
+    patches {alt fwd, alt rc}.  Returns (ref_descs [2N], patch_descs [2N], allele codes, k_of_shift, patch_row0,
+    patch_len); callers must pre-filter with delta_eligible."""
+    n = len(pos)
+    rl = np.fromiter((len(r) for r in refs), dtype=np.int64, count=n)
+    al = np.fromiter((len(a) for a in alts), dtype=np.int64, count=n)
+    if not np.all(delta_eligible(rl, al)):
+        raise ValueError("chromatin_delta_descs needs variants pre-filtered with delta_eligible")
+    descs, codes, k = chromatin_segment_descs(genome, chroms, pos, refs, alts, maxshift)
+    d = descs.reshape(n, 4)
+    row0, plen = delta_patch_geometry(maxshift)
+    seg_len = INPUTSIZE + 2 * maxshift
+    patches = sub_descs(d[:, 2:4].reshape(-1), 16 * row0, plen, seg_len)
+    return np.ascontiguousarray(d[:, 0:2]).reshape(-1), patches, codes, k, row0, plen
+
+
 def tss_segment_descs(genome: PackedGenome, chroms, tss, strand, shifts, windowsize: int = INPUTSIZE):
     """Two segments per gene, order {fwd, rc}, covering the windows of compute_expecto_features.py:105-111
     (``tss + shift*strand - 999 .. + 1000``).  ``shifts`` must be an arithmetic progression with step 200.

@@ -145,6 +145,18 @@ int bx_forward_segments(bx_ctx* ctx, const bx_window_desc* descs_dev, const uint
                         int segs_per_group, int seg_len, int n_shifts, const int32_t* k_of_shift, int shift_major,
                         float* probs_dev, void* stream);
 
+/* Segment mode for substitutions (len(ref) == len(alt)): the alt sequence differs from the ref sequence in a few
+ * positions at the segment centre, so only the conv6 rows whose 310-position receptive field reaches them can
+ * differ.  ref_descs_dev: 2 segments per group (ref fwd, ref rc), run in full; patch_descs_dev: 2 per group (alt
+ * fwd, alt rc), patch_len positions (multiple of 16) that start 16*patch_row0 positions into the alt segments and
+ * must cover every affected row's receptive field in both pooling phases.  Alt windows take those rows from the
+ * patch and all others from the ref segment.  Output as bx_forward_segments with segs_per_group = 4 (ref fwd, ref
+ * rc, alt fwd, alt rc), bit-identical to it (reference: the ref/alt loop bodies of chromatin.py:262-279). */
+int bx_forward_segments_delta(bx_ctx* ctx, const bx_window_desc* ref_descs_dev, const bx_window_desc* patch_descs_dev,
+                              const uint8_t* alleles_dev, int n_groups, int seg_len, int patch_len, int patch_row0,
+                              int n_shifts, const int32_t* k_of_shift, int shift_major, float* probs_dev,
+                              void* stream);
+
 /* predict.py:123-160 fused: per-variant decay features contracted with n_models gblinear weight vectors
  * (xgboost Booster.predict = base_score + bias + w.x) without materialising the [n,20020] feature matrix.
  * w_dev fp32 [n_models, 10*2002] (columns removed by cluster_utils.get_keep_mask set to 0), offset_dev fp32

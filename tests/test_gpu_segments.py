@@ -65,6 +65,87 @@ def test_segment_chunking_and_argument_errors(engine, small_genome):
         engine.forward_segments(sd, np.zeros(1, np.uint8), n, 2, seg_len + 200, k_of, shift_major=False)
 
 
+def _substitutions(small_genome, n_random=40):
+    """SNVs / MNVs incl. ref-mismatch, lower case, N alleles and the longest handled MNV, on both ends of contigs."""
+    from expecto_b200.windows import delta_eligible
+    rows = [r for r in GI.edge_variants(small_genome) if delta_eligible([len(r[3])], [len(r[4])])[0]]
+    rng = np.random.default_rng(11)
+    names = sorted(small_genome)
+    for i in range(n_random):
+        c = names[i % len(names)]
+        p = int(rng.integers(3000, len(small_genome[c]) - 3000))
+        ln = int(rng.choice([1, 1, 1, 2, 3, 8, 16]))
+        ref = small_genome[c][p - 1:p - 1 + ln].upper()
+        if i % 7 == 0:
+            ref = "".join("ACGT"[(("ACGT".find(b) + 1) % 4)] if b in "ACGT" else "A" for b in ref)  # ref mismatch
+        alt = "".join("ACGTN"[int(rng.integers(0, 5))] for _ in range(ln))
+        rows.append((c, p, f"sub{i}", ref, alt.lower() if i % 5 == 0 else alt))
+    return rows
+
+
+def test_delta_patches_equal_full_segments_and_windows_bitwise(engine, small_genome):
+    """Substitutions: ref segments in full + alt patches (bx_forward_segments_delta) == four full segments ==
+    per-window path, bit for bit, for every shift, strand and allele."""
+    from expecto_b200.windows import chromatin_delta_descs
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    rows = _substitutions(small_genome)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    n = len(rows)
+    rd, pd, codes, k_of, row0, plen = chromatin_delta_descs(pg, chroms, pos, refs, alts, 800)
+    delta = engine.forward_segments_delta(rd, pd, codes, n, 3600, plen, row0, k_of, shift_major=True)
+    sd, scodes, k2 = chromatin_segment_descs(pg, chroms, pos, refs, alts, 800)
+    full = engine.forward_segments(sd, scodes, n, 4, 3600, k2, shift_major=True)
+    assert delta.shape == full.shape == (9, n, 4, 2002)
+    assert torch.equal(delta, full)
+    assert not torch.equal(full[:, :, 0], full[:, :, 2])          # the alleles do change the predictions
+    for si, shift in enumerate(chromatin_shift_list(800)):
+        wd, wcodes = chromatin_window_descs(pg, chroms, pos, refs, alts, shift)
+        assert torch.equal(delta[si], engine.forward_windows(wd, wcodes).reshape(n, 4, 2002)), shift
+    # group-major order and a single shift (maxshift 0: one window per segment, phase A only)
+    gm = engine.forward_segments_delta(rd, pd, codes, n, 3600, plen, row0, k_of, shift_major=False)
+    assert torch.equal(gm, full.permute(1, 0, 2, 3))
+    rd0, pd0, codes0, k0, row00, plen0 = chromatin_delta_descs(pg, chroms, pos, refs, alts, 0)
+    one = engine.forward_segments_delta(rd0, pd0, codes0, n, 2000, plen0, row00, k0, shift_major=True)
+    wd, wcodes = chromatin_window_descs(pg, chroms, pos, refs, alts, 0)
+    assert torch.equal(one[0], engine.forward_windows(wd, wcodes).reshape(n, 4, 2002))
+    from expecto_b200._lib import BelugaError
+    with pytest.raises(BelugaError):
+        engine.forward_segments_delta(rd, pd, codes, n, 3600, plen + 8, row0, k_of, shift_major=True)
+    with pytest.raises(BelugaError):
+        engine.forward_segments_delta(rd, pd, codes, n, 3600, plen, 3600 // 16, k_of, shift_major=True)
+
+
+def test_segment_loop_with_and_without_delta_is_identical(engine, small_genome):
+    """The pipelined chromatin loop: a mix of substitutions, indels and window-path variants gives the same slabs
+    whether substitutions take the patch path or not."""
+    from expecto_b200.chromatin import predict_all_shifts_segments
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    rows = GI.edge_variants(small_genome) + _substitutions(small_genome, 12)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    n = len(rows)
+    got = {}
+    for delta in (True, False):
+        store = {s: {k: np.full((2 * n, 2002), np.nan, np.float32) for k in ("diff", "ref", "alt")}
+                 for s in chromatin_shift_list(800)}
+
+        def make(s):
+            def sink(name, row0, arr):
+                store[s][name][row0:row0 + len(arr)] = arr
+            return sink
+        info = predict_all_shifts_segments(engine, pg, chroms, pos, refs, alts, 800,
+                                           {s: make(s) for s in store}, delta=delta)
+        assert (info["delta_variants"] > 0) == delta
+        got[delta] = store
+    for s in got[True]:
+        for k in ("diff", "ref", "alt"):
+            assert not np.isnan(got[True][s][k]).any()
+            assert np.array_equal(got[True][s][k], got[False][s][k]), (s, k)
+
+
 def test_chromatin_cli_segments_and_windows_modes_write_identical_files(engine, cfg1_genome, golden, tmp_path):
     """Edge VCF (one variant — the 120-bp deletion — falls back to the per-window path inside segment mode)."""
     from expecto_b200 import chromatin, hdf5

@@ -114,6 +114,48 @@ def test_segment_descriptors_cover_every_shifted_window(small_genome):
             assert np.array_equal(win[:, q], seg[:, q, :, off:off + 2000]), (shift, q)
 
 
+def test_delta_patches_are_slices_of_the_alt_segments(small_genome):
+    """Substitution patches: the alt patch descriptors decode to positions [16*row0, 16*row0 + patch_len) of the
+    alt segments on both strands, the ref descriptors are the plain ref segments, and outside the patch's valid
+    receptive-field rows ref and alt segments agree (what the gather relies on)."""
+    from expecto_b200.windows import (RECEPTIVE_FIELD, chromatin_delta_descs, chromatin_segment_descs, delta_eligible,
+                                      delta_patch_geometry, segment_geometry, sub_descs)
+    rows = GI.edge_variants(small_genome)
+    ok = delta_eligible([len(r[3]) for r in rows], [len(r[4]) for r in rows])
+    assert 0 < ok.sum() < len(rows)
+    rows = [r for r, e in zip(rows, ok) if e]
+    # an MNV of the longest handled length on top of the fixture's substitutions
+    c, p = rows[0][0], rows[0][1]
+    rows.append((c, p, "mnv16", small_genome[c][p - 1:p + 15].upper(), "ACGTTGCAACGTTGCA"))
+    pg = PackedGenome.from_sequences(small_genome)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    n = len(rows)
+    rd, pd, codes, k_of, row0, plen = chromatin_delta_descs(pg, chroms, pos, refs, alts, 800)
+    assert (row0, plen) == delta_patch_geometry(800) and plen % 16 == 0
+    sd, scodes, k2 = chromatin_segment_descs(pg, chroms, pos, refs, alts, 800)
+    assert np.array_equal(k_of, k2) and np.array_equal(codes, scodes)
+    seg = decode_descs(pg, sd, scodes, length=3600).reshape(n, 4, 4, 3600)
+    assert np.array_equal(decode_descs(pg, rd, codes, length=3600).reshape(n, 2, 4, 3600), seg[:, 0:2])
+    patch = decode_descs(pg, pd, codes, length=plen).reshape(n, 2, 4, plen)
+    assert np.array_equal(patch, seg[:, 2:4, :, 16 * row0:16 * row0 + plen])
+    # every position where alt differs from ref lies inside the receptive field of valid patch rows only
+    g = segment_geometry(plen)
+    for strand in range(2):
+        diff = np.flatnonzero((seg[:, strand] != seg[:, 2 + strand]).any(axis=(0, 1)))
+        if diff.size == 0:
+            continue
+        for phase_off, valid in ((0, g["valid_a"]), (8, g["valid_b"])):
+            first = (diff.min() - phase_off - (RECEPTIVE_FIELD - 1) + 15) // 16      # first row that sees a change
+            last = (diff.max() - phase_off) // 16
+            assert row0 <= first and last < row0 + valid, (strand, phase_off, first, last)
+    # general sub-ranges, including ones that start inside the allele or the right flank
+    for start, length in ((0, 3600), (1790, 64), (1800, 32), (1805, 200), (3000, 600)):
+        sub = sub_descs(sd, start, length, 3600)
+        got = decode_descs(pg, sub, scodes, length=length).reshape(n, 4, 4, length)
+        assert np.array_equal(got, seg[..., start:start + length]), (start, length)
+
+
 def test_tss_segment_descriptors(small_genome):
     from expecto_b200.windows import tss_segment_descs
     pg = PackedGenome.from_sequences(small_genome)
