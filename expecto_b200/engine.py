@@ -89,12 +89,32 @@ class BelugaEngine:
         check(lib().bx_ctx_set_genome(self._ctx, self._bases2.data_ptr(), self._nmask.data_ptr(), packed.n_bases))
 
     # ------------------------------------------------------------------ compute
+    def _stage(self, host: np.ndarray) -> torch.Tensor:
+        """Bytes of ``host`` -> device through a ring of reusable pinned buffers, so the H2D copy is truly
+        asynchronous (a pageable source makes cudaMemcpyAsync wait for the stream's earlier work once it exceeds the
+        driver's 64 KB staging chunk, which serialised the host with the GPU in the chunked segment loops)."""
+        raw = np.ascontiguousarray(host).view(np.uint8).reshape(-1)
+        ring = self.__dict__.setdefault("_pin_ring", [])
+        slot = self.__dict__.get("_pin_next", 0)
+        self._pin_next = (slot + 1) % 8
+        if len(ring) <= slot:
+            ring.append([None, None])
+        buf, ev = ring[slot]
+        if ev is not None:
+            ev.synchronize()           # the copy that last used this buffer has finished
+        if buf is None or buf.numel() < raw.size:
+            buf = torch.empty(max(raw.size, 1 << 16), dtype=torch.uint8, pin_memory=True)
+        buf[:raw.size].numpy()[:] = raw
+        dev = buf[:raw.size].to(self.device, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        ring[slot] = [buf, ev]
+        return dev
+
     def _upload_descs(self, descs: np.ndarray, alleles: np.ndarray):
-        d = torch.from_numpy(np.ascontiguousarray(descs).view(np.uint8)).to(self.device, non_blocking=True)
         if alleles.size == 0:
             alleles = np.zeros(1, dtype=np.uint8)
-        a = torch.from_numpy(np.ascontiguousarray(alleles, dtype=np.uint8)).to(self.device, non_blocking=True)
-        return d, a
+        return self._stage(descs), self._stage(np.ascontiguousarray(alleles, dtype=np.uint8))
 
     def encode_windows(self, descs: np.ndarray, alleles: np.ndarray) -> torch.Tensor:
         """encodeSeqs materialised on the GPU: uint8 [n,4,2000] (bit-exact test hook)."""

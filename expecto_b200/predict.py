@@ -127,6 +127,36 @@ def expand_weights(models, mask: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
     return W.reshape(len(models), -1), np.array([m.offset for m in models], dtype=np.float32)
 
 
+def write_sed_tables(df, out_dir: str) -> None:
+    """sed.tsv, sed_sorted_by_magnitude.tsv, sed_sorted_by_proportion.tsv (predict.py:255-280).  The three files hold
+    the same rows, so every row is formatted once (with a --modelList of 218 models the float formatting is the
+    longest phase of the whole script) and the sorted files re-emit those lines in the order pandas' own
+    sort_values gives, with the extra column appended; any surprise in the text falls back to three to_csv calls."""
+    text = df.to_csv(None, header=True, sep="\t", index=False)
+    with open(f"{out_dir}/sed.tsv", "w", newline="") as f:
+        f.write(text)
+    lines = text.split("\n")
+    header, body = lines[0], lines[1:-1]
+    extras = (("SED_MAGNITUDES", np.abs(df["SED"]), "magnitude"),
+              ("SED_PROPORTION", np.abs(df["SED"] / ((df["REF"] + df["ALT"]) / 2)), "proportion"))
+    for col, values, name in extras:
+        path = f"{out_dir}/sed_sorted_by_{name}.tsv"
+        if len(body) != len(df) or lines[-1] != "":
+            s = df.copy()
+            s[col] = values
+            s.sort_values(by=col, axis=0, ascending=False).to_csv(path, header=True, sep="\t", index=False)
+            continue
+        values = values.reset_index(drop=True)
+        order = values.sort_values(ascending=False).index.to_numpy()
+        # pandas' own cell text for this dtype (a lone empty cell comes back quoted)
+        cells = ["" if c == '""' else c for c in values.to_csv(None, header=False, index=False).split("\n")]
+        if len(cells) != len(df) + 1:
+            raise RuntimeError("unexpected text for the sort column")
+        with open(path, "w", newline="") as f:
+            f.write(header + "\t" + col + "\n")
+            f.write("".join(body[i] + "\t" + cells[i] + "\n" for i in order))
+
+
 def run(args) -> dict:
     import pandas as pd
     import torch
@@ -194,15 +224,7 @@ def run(args) -> dict:
         cols[f"SED_{os.path.basename(p)}"] = alt[:, i] - ref[:, i]
     df = pd.concat([df.reset_index()] + [pd.DataFrame(v, columns=[k]) for k, v in cols.items()], axis=1,
                    ignore_index=False)
-    df.to_csv(f"{args.out_dir}/sed.tsv", header=True, sep="\t", index=False)
-    s = df.copy()
-    s["SED_MAGNITUDES"] = np.abs(s["SED"])
-    s.sort_values(by="SED_MAGNITUDES", axis=0, ascending=False).to_csv(
-        f"{args.out_dir}/sed_sorted_by_magnitude.tsv", header=True, sep="\t", index=False)
-    s = df.copy()
-    s["SED_PROPORTION"] = np.abs(s["SED"] / ((s["REF"] + s["ALT"]) / 2))
-    s.sort_values(by="SED_PROPORTION", axis=0, ascending=False).to_csv(
-        f"{args.out_dir}/sed_sorted_by_proportion.tsv", header=True, sep="\t", index=False)
+    write_sed_tables(df, args.out_dir)
     lap("write_tsv_s")
     return {"n_rows": len(df), "ref": ref, "alt": alt, "models": paths, "timing": timing}
 

@@ -62,3 +62,35 @@ def test_cli_defaults_match_reference():
     assert (a.nfeatures, a.fixeddist, a.maxshift, a.batchSize, a.threads) == (2002, 0, 800, 500, 16)
     assert chromatin_shifts(800) == O.SHIFTS_CHROMATIN(800)
     assert np.array_equal(fixed_pos_weights(), O.fixed_pos_weights())
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_sed_tables_byte_identical_to_three_pandas_passes(tmp_path, dt):
+    """write_sed_tables formats every row once; the three files must equal predict.py:255-280's three to_csv calls
+    byte for byte, including NaN / inf proportions, zero effects and repeated magnitudes."""
+    import pandas as pd
+    from expecto_b200.predict import write_sed_tables
+    rng = np.random.default_rng(0)
+    n = 400
+    ref = rng.standard_normal(n).astype(dt)
+    alt = ref + rng.standard_normal(n).astype(dt) * dt(1e-3)
+    alt[5] = ref[5]; ref[7] = 0; alt[7] = 0; alt[9] = -ref[9]; alt[20:30] = ref[20:30] + dt(0.5); ref[40] = np.nan
+    df = pd.DataFrame({"index": np.arange(n), 0: ["chr1"] * n, 1: rng.integers(1, 10 ** 6, n),
+                       2: [f"rs{i}" for i in range(n)], "dist": rng.integers(-20000, 20000, n),
+                       "gene": [f"G{i % 7}" for i in range(n)], "strand": ["+"] * n})
+    df = pd.concat([df] + [pd.DataFrame(v, columns=[k]) for k, v in
+                           (("REF", ref), ("ALT", alt), ("SED", alt - ref), ("SED_model2", (alt - ref) * 2))], axis=1)
+    ours, theirs = tmp_path / "ours", tmp_path / "theirs"
+    ours.mkdir(); theirs.mkdir()
+    write_sed_tables(df, str(ours))
+    df.to_csv(f"{theirs}/sed.tsv", header=True, sep="\t", index=False)
+    s = df.copy()
+    s["SED_MAGNITUDES"] = np.abs(s["SED"])
+    s.sort_values(by="SED_MAGNITUDES", axis=0, ascending=False).to_csv(
+        f"{theirs}/sed_sorted_by_magnitude.tsv", header=True, sep="\t", index=False)
+    s = df.copy()
+    s["SED_PROPORTION"] = np.abs(s["SED"] / ((s["REF"] + s["ALT"]) / 2))
+    s.sort_values(by="SED_PROPORTION", axis=0, ascending=False).to_csv(
+        f"{theirs}/sed_sorted_by_proportion.tsv", header=True, sep="\t", index=False)
+    for name in ("sed.tsv", "sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
+        assert (ours / name).read_bytes() == (theirs / name).read_bytes(), name
