@@ -286,7 +286,9 @@ def _segment_chunks(engine, genome, chroms, pos, refs, alts, maxshift: int, ids,
         else:
             merged = torch.empty((parts[0][1].shape[0], len(idx), 4, 2002), dtype=torch.float32, device=engine.device)
             for sel, probs in parts:
-                merged.index_copy_(1, torch.from_numpy(sel).to(engine.device), probs)
+                # indices go up through the engine's pinned staging ring: a pageable source would make the copy wait
+                # for the stream's earlier work and serialise this thread with the GPU
+                merged.index_copy_(1, engine._stage(sel.astype(np.int64)).view(torch.int64), probs)
             yield idx, merged
 
 

@@ -96,7 +96,7 @@ class BelugaEngine:
         raw = np.ascontiguousarray(host).view(np.uint8).reshape(-1)
         ring = self.__dict__.setdefault("_pin_ring", [])
         slot = self.__dict__.get("_pin_next", 0)
-        self._pin_next = (slot + 1) % 8
+        self._pin_next = (slot + 1) % 32
         if len(ring) <= slot:
             ring.append([None, None])
         buf, ev = ring[slot]
