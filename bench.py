@@ -119,6 +119,38 @@ def cpu_forward_rate(batch: int, min_seconds: float, max_windows: int, seed: int
     return done / dt, cores, torch.get_num_threads(), done, dt
 
 
+def variant_workflow(eng, n_variants: int):
+    """BASELINE configs[2] shape at a stated reduced size, outside the timed region: a synthetic VCF (90 % SNV, 5 %
+    ref-mismatch, 5 % indel) on a synthetic genome -> ref/alt x fwd/rc x 9 shifts -> pinned host ref/alt/diff, through
+    the drop-in's segment + delta mode (host descriptors in, host arrays out, no file).  Reported in the headline
+    metric's unit: windows/s = 36 windows per variant, every one bit-identical to the per-window forward."""
+    import numpy as np
+    import torch
+
+    from expecto_b200 import chromatin, synth
+    from expecto_b200.genome import PackedGenome
+
+    genome = synth.make_genome([("chr1", 6_000_000), ("chr2", 4_000_000)], seed=3)
+    pg = PackedGenome.from_sequences(genome)
+    eng.set_genome(pg)
+    rows = synth.make_vcf_rows(genome, n_variants, seed=3, odd_names=False)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    sinks = {s: (lambda *a: None) for s in chromatin.shift_list(800)}
+    k = min(1200, n_variants)
+    chromatin.predict_all_shifts_segments(eng, pg, chroms[:k], pos[:k], refs[:k], alts[:k], 800, sinks)  # warm-up
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    info = chromatin.predict_all_shifts_segments(eng, pg, chroms, pos, refs, alts, 800, sinks)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    return {"workload": f"{n_variants} synthetic variants x (ref, alt) x (fwd, rc) x 9 shifts, segment + delta mode, "
+                        "host descriptors -> pinned host ref/alt/diff, no file",
+            "variants": n_variants, "windows": 36 * n_variants, "seconds": dt, "windows_per_s": 36 * n_variants / dt,
+            "variants_per_s": n_variants / dt, "d2h_bytes": 9 * 3 * 2 * n_variants * 2002 * 4,
+            "delta_variants": info["delta_variants"], "window_path_variants": info["window_variants"]}
+
+
 def transform_rooflines(dev, peaks, iters: int = 10):
     """Kernel 4 (decay-weighted shift reductions) as HBM GB/s over the algorithmic bytes of SURVEY §8(d); inputs
     (1.6 GB / 1.2 GB) are larger than the 126 MB L2."""
@@ -341,6 +373,8 @@ def run_gpu(args) -> int:
         del x, out
         torch.cuda.empty_cache()
         line["transform_roofline"] = transform_rooflines(dev, peaks)
+    if world == 1 and not args.no_workflow:
+        line["variant_workflow"] = variant_workflow(eng, args.workflow_variants)
     if world == 1 and not args.no_cpu_baseline:
         rate, cores, threads, done, dt = cpu_forward_rate(32, args.cpu_seconds, 4096)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
@@ -366,6 +400,8 @@ def main() -> int:
     ap.add_argument("--cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no_cpu_baseline", action="store_true")
     ap.add_argument("--no_transform", action="store_true", help="skip the kernel-4 GB/s measurement")
+    ap.add_argument("--no_workflow", action="store_true", help="skip the variant-workflow (segment mode) measurement")
+    ap.add_argument("--workflow_variants", type=int, default=8192)
     args = ap.parse_args()
     return run_reference(args) if args.impl == "reference" else run_gpu(args)
 
