@@ -141,3 +141,87 @@ def random_onehot(n: int, seed: int = 2) -> np.ndarray:
     x = np.zeros((n, 4, 2000), dtype=np.uint8)
     np.put_along_axis(x, codes[:, None, :], 1, axis=1)
     return x
+
+
+HG19_CONTIGS = [("chr1", 249250621), ("chr2", 243199373), ("chr3", 198022430), ("chr4", 191154276),
+                ("chr5", 180915260), ("chr6", 171115067), ("chr7", 159138663), ("chr8", 146364022),
+                ("chr9", 141213431), ("chr10", 135534747), ("chr11", 135006516), ("chr12", 133851895),
+                ("chr13", 115169878), ("chr14", 107349540), ("chr15", 102531392), ("chr16", 90354753),
+                ("chr17", 81195210), ("chr18", 78077248), ("chr19", 59128983), ("chr20", 63025520),
+                ("chr21", 48129895), ("chr22", 51304566), ("chrX", 155270560), ("chrY", 59373566)]
+
+
+def make_packed_genome(contigs=HG19_CONTIGS, seed: int = 3, n_frac: float = 0.002):
+    """hg19-shaped synthetic genome built directly in the packed form (3.1 Gb would be a 3 GB
+    Python string otherwise): uniformly random bases, N in runs of 64 bases covering ``n_frac`` of every contig."""
+    from .genome import PAD, PackedGenome
+
+    rng = np.random.default_rng(seed)
+    g = PackedGenome()
+    total = PAD
+    for name, ln in contigs:
+        total = (total + 31) // 32 * 32
+        g.names.append(name)
+        g.offsets[name] = total
+        g.lengths[name] = int(ln)
+        total += int(ln) + PAD
+    total = (total + 31) // 32 * 32
+    g.n_bases = total
+    g.bases2 = rng.integers(0, 1 << 32, size=total // 16, dtype=np.uint32)
+    g.nmask = np.full(total // 32, 0xFFFFFFFF, dtype=np.uint32)   # padding between contigs is N
+    for name, ln in contigs:
+        off = g.offsets[name]
+        w0, w1 = off // 32, (off + ln) // 32
+        g.nmask[w0:w1] = 0
+        tail = (off + ln) % 32
+        if tail:
+            g.nmask[w1] = np.uint32((0xFFFFFFFF << tail) & 0xFFFFFFFF)
+        n_runs = int(ln * n_frac / 64)
+        if n_runs:
+            at = rng.integers(w0, max(w0 + 1, w1 - 2), size=n_runs)
+            g.nmask[at] = 0xFFFFFFFF
+            g.nmask[at + 1] = 0xFFFFFFFF
+    return g
+
+
+def make_vcf_rows_packed(pg, n: int, seed: int = 3, margin: int = 3000, frac_mismatch: float = 0.05,
+                         frac_indel: float = 0.05, max_indel: int = 10):
+    """make_vcf_rows for a packed genome, vectorised over variants (1 M rows in seconds): returns
+    (chroms list, pos int64 array, refs list, alts list) sorted by contig order and position."""
+    rng = np.random.default_rng(seed)
+    names = [k for k in pg.names if pg.lengths[k] > 2 * margin + 10]
+    w = np.array([pg.lengths[k] for k in names], dtype=np.float64)
+    ci = np.sort(rng.choice(len(names), size=n, p=w / w.sum()))
+    lens = np.array([pg.lengths[k] for k in names], dtype=np.int64)[ci]
+    pos = (margin + rng.random(n) * (lens - 2 * margin)).astype(np.int64)
+    order = np.lexsort((pos, ci))
+    ci, pos = ci[order], pos[order]
+    offs = np.array([pg.offsets[k] for k in names], dtype=np.int64)[ci]
+    gidx = offs + pos - 1
+    span = max_indel + 1
+    j = gidx[:, None] + np.arange(span, dtype=np.int64)[None, :]
+    two = (pg.bases2[j >> 4] >> ((j & 15) * 2).astype(np.uint32)) & 3
+    msk = (pg.nmask[j >> 5] >> (j & 31).astype(np.uint32)) & 1
+    codes = np.where(msk == 1, 0, two).astype(np.int64)        # N -> "A", as make_vcf_rows does
+    letters = np.frombuffer(b"AGCT", dtype=np.uint8)             # channel order of the packed codes
+    u = rng.random(n)
+    kind = np.where(u < frac_indel, np.where(rng.random(n) < 0.5, 1, 2), np.where(u < frac_indel + frac_mismatch, 3, 0))
+    d = rng.integers(1, max_indel + 1, size=n)
+    step = rng.integers(1, 4, size=n)
+    ins = rng.integers(0, 4, size=(n, max_indel))
+    chroms, refs, alts = [names[i] for i in ci], [], []
+    txt = letters[codes]                                          # [n, span] ASCII
+    for i in range(n):
+        k = kind[i]
+        g0 = int(codes[i, 0])
+        if k == 1:      # deletion
+            r = txt[i, :d[i] + 1].tobytes().decode()
+            refs.append(r); alts.append(r[0])
+        elif k == 2:    # insertion
+            r = chr(letters[g0])
+            refs.append(r); alts.append(r + letters[ins[i, :d[i]]].tobytes().decode())
+        elif k == 3:    # ref allele disagrees with the genome
+            refs.append(chr(letters[(g0 + 1) % 4])); alts.append(chr(letters[(g0 + 2) % 4]))
+        else:
+            refs.append(chr(letters[g0])); alts.append(chr(letters[(g0 + int(step[i])) % 4]))
+    return chroms, pos, refs, alts
