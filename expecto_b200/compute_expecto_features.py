@@ -79,7 +79,17 @@ def gene_features(engine, genome, genes, shifts, weights, genes_per_batch: int =
     no_alleles = np.zeros(1, dtype=np.uint8)
     steps = np.diff(np.asarray(shifts))
     use_segments = mode == "segments" and S > 1 and S <= 200 and bool(np.all(steps == 200))
-    for g0 in range(0, len(genes), genes_per_batch):
+    # two pinned result buffers: batch k's features are fetched after batch k+1 has been enqueued, so the GPU never
+    # waits for the host's descriptor building or the float64 widening
+    pinned = [torch.empty((genes_per_batch, 10 * 2002), dtype=torch.float32, pin_memory=True) for _ in range(2)]
+    pending = None
+
+    def collect(p):
+        ev, hb, at, m = p
+        ev.synchronize()
+        out[at:at + m] = hb[:m].numpy()
+
+    for bi, g0 in enumerate(range(0, len(genes), genes_per_batch)):
         part = genes[g0:g0 + genes_per_batch]
         cols = ([g[1] for g in part], [g[2] for g in part], [g[3] for g in part])
         if use_segments:
@@ -91,8 +101,16 @@ def gene_features(engine, genome, genes, shifts, weights, genes_per_batch: int =
             check_valid_bases(genome, descs)
             probs = engine.forward_windows(descs, no_alleles).view(len(part), S, 2, 2002)
         feats = decay_transform_fixed(probs, weights)
-        out[g0:g0 + len(part)] = feats.cpu().numpy()
+        hb = pinned[bi % 2]
+        hb[:len(part)].copy_(feats, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(engine.device))
+        if pending is not None:
+            collect(pending)
+        pending = (ev, hb, g0, len(part))
         del probs, feats
+    if pending is not None:
+        collect(pending)
     torch.cuda.synchronize(engine.device)
     return out
 
