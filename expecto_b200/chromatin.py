@@ -430,6 +430,52 @@ def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, 
     return outs
 
 
+def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, maxshift: int, delta: bool = True):
+    """The chromatin step as ``predict.py`` consumes it, left in HBM: {"ref", "alt", "diff"} -> float32 [S, n, 2002],
+    already averaged over the forward / reverse-complement rows (predict.py:186-190).  This is what reading the nine
+    ``.diff.h5`` files back and averaging gives, without the 432 KB per variant of file traffic in between."""
+    import torch
+
+    from .engine import chromatin_outputs
+    from .windows import check_valid_bases, chromatin_window_descs, segment_eligible
+
+    n = len(pos)
+    shifts = shift_list(maxshift)
+    S = len(shifts)
+    seg_len = 2000 + 2 * maxshift
+    out = {k: torch.empty((S, n, 2002), dtype=torch.float32, device=engine.device) for k in ("ref", "alt", "diff")}
+    use_segments = maxshift % 200 == 0
+    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts]) if (n and use_segments) else np.zeros(n, bool)
+    elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)
+    if len(elig):
+        cap = max(1, engine.segment_capacity(seg_len) // 4)
+        for idx, probs in _segment_chunks(engine, genome, chroms, pos, refs, alts, maxshift, elig, cap, delta):
+            m = len(idx)
+            contiguous = m == int(idx[-1] - idx[0] + 1)
+            ii = None if contiguous else engine._stage(idx.astype(np.int64)).view(torch.int64)
+            for si in range(S):
+                parts = chromatin_outputs(probs[si].reshape(4 * m, 2002), m, average=True)
+                for k, t in zip(("ref", "alt", "diff"), parts):
+                    if contiguous:
+                        out[k][si, int(idx[0]):int(idx[0]) + m] = t
+                    else:
+                        out[k][si].index_copy_(0, ii, t)
+            del probs
+    gb = 1024
+    for v0 in range(0, len(rest), gb):
+        part = rest[v0:v0 + gb]
+        m = len(part)
+        ii = engine._stage(part.astype(np.int64)).view(torch.int64)
+        for si, shift in enumerate(shifts):
+            descs, codes = chromatin_window_descs(genome, [chroms[i] for i in part], pos[part], [refs[i] for i in part],
+                                                  [alts[i] for i in part], shift)
+            check_valid_bases(genome, descs)
+            parts = chromatin_outputs(engine.forward_windows(descs, codes), m, average=True)
+            for k, t in zip(("ref", "alt", "diff"), parts):
+                out[k][si].index_copy_(0, ii, t)
+    return out
+
+
 def predict_shift_device(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int):
     """Same computation with the results left in HBM: (ref, alt, diff) device tensors [2n,2002] in the strand-
     stacked row order — the operands of the end-of-shift NCCL gather when variants are sharded over GPUs."""

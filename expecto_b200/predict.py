@@ -52,6 +52,14 @@ def build_parser() -> argparse.ArgumentParser:
     # extensions
     p.add_argument("--modelList", default=None, help="file with one model path per line (upstream interface)")
     p.add_argument("--device", type=int, default=0)
+    p.add_argument("--vcf", default=None,
+                   help="compute the chromatin effects of this VCF in-process (segment + delta mode) instead of reading "
+                        "--snpEffectFilePattern files: chromatin.py and predict.py in one pass, no .diff.h5 in between; "
+                        "snps_hg19.vcf is written to -o and used as --coorFile_chromatin unless that is given")
+    p.add_argument("--genome", default="./resources/hg19.fa", help="--vcf: FASTA (chromatin.py:44)")
+    p.add_argument("--weights", default="./resources/deepsea.beluga.pth", help="--vcf: Beluga state_dict (chromatin.py:103)")
+    p.add_argument("--dtype", default="f16", choices=["f16", "bf16"], help="--vcf: tensor-core operand type")
+    p.add_argument("--vcf_block", type=int, default=131072, help="--vcf: variants resident in HBM at a time")
     return p
 
 
@@ -127,12 +135,40 @@ def expand_weights(models, mask: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
     return W.reshape(len(models), -1), np.array([m.offset for m in models], dtype=np.float32)
 
 
+def _table_text(df) -> str:
+    """``df.to_csv(sep='\\t', index=False)``.  The reference's columns (everything up to ``SED``) are formatted by
+    pandas itself, so they are byte-identical to predict.py's files.  The extra per-model ``SED_<model>`` columns of
+    ``--modelList`` (an extension: 217 float columns per row for the 218-model list) go through Arrow's CSV writer —
+    shortest round-trip float32 text as well, ten times faster, different exponent style (``1e-5``/``0.00001``)."""
+    cols = list(df.columns)
+    n_ref = cols.index("SED") + 1 if "SED" in cols else len(cols)
+    extra = cols[n_ref:]
+    if not extra or len(df) == 0 or not all(str(df[c].dtype).startswith("float") for c in extra):
+        return df.to_csv(None, header=True, sep="\t", index=False)
+    try:
+        import io
+
+        import pyarrow as pa
+        import pyarrow.csv as pc
+    except ImportError:
+        return df.to_csv(None, header=True, sep="\t", index=False)
+    base = df[cols[:n_ref]].to_csv(None, header=True, sep="\t", index=False).split("\n")
+    buf = io.BytesIO()
+    pc.write_csv(pa.Table.from_pandas(df[extra], preserve_index=False), buf,
+                 pc.WriteOptions(include_header=False, delimiter="\t"))
+    more = buf.getvalue().decode("ascii").split("\n")
+    if len(base) != len(df) + 2 or len(more) != len(df) + 1:
+        return df.to_csv(None, header=True, sep="\t", index=False)
+    head = base[0] + "\t" + "\t".join(str(c) for c in extra)
+    return "\n".join([head] + [b + "\t" + m for b, m in zip(base[1:-1], more[:-1])]) + "\n"
+
+
 def write_sed_tables(df, out_dir: str) -> None:
     """sed.tsv, sed_sorted_by_magnitude.tsv, sed_sorted_by_proportion.tsv (predict.py:255-280).  The three files hold
     the same rows, so every row is formatted once (with a --modelList of 218 models the float formatting is the
     longest phase of the whole script) and the sorted files re-emit those lines in the order pandas' own
     sort_values gives, with the extra column appended; any surprise in the text falls back to three to_csv calls."""
-    text = df.to_csv(None, header=True, sep="\t", index=False)
+    text = _table_text(df)
     with open(f"{out_dir}/sed.tsv", "w", newline="") as f:
         f.write(text)
     lines = text.split("\n")
@@ -157,7 +193,38 @@ def write_sed_tables(df, out_dir: str) -> None:
             f.write("".join(body[i] + "\t" + cells[i] + "\n" for i in order))
 
 
-def run(args) -> dict:
+def _chromatin_blocks(args, dev, engine=None, genome=None):
+    """--vcf: yield (v0, v1, {"ref","alt"} -> [S, v1-v0, 2002] strand-averaged device tensors) for blocks of the
+    filtered variants, straight from the CUDA forward (chromatin.py:211-281 + predict.py:173-194 without the files)."""
+    from . import chromatin
+    from .genome import PackedGenome
+
+    if genome is None:
+        genome = PackedGenome.from_fasta(args.genome)
+    if engine is None:
+        from .engine import BelugaEngine
+        engine = BelugaEngine(dev.index or 0, dtype=args.dtype, capacity=4096)
+        engine.load_weights_file(args.weights)
+    if engine._genome is not genome:
+        engine.set_genome(genome)
+    vcf = chromatin.read_vcf(args.vcf)
+    chromatin.write_snps_vcf(vcf, args.out_dir)
+    chroms, pos, refs, alts = chromatin.variant_columns(chromatin.normalise_and_filter(vcf))
+    missing = sorted({c for c in chroms if c not in genome.offsets})
+    if missing:
+        raise KeyError(f"contig(s) {missing} are not in the genome")
+    n = len(pos)
+    yield n
+    for v0 in range(0, n, args.vcf_block):
+        v1 = min(n, v0 + args.vcf_block)
+        data = chromatin.predict_all_shifts_averaged_device(engine, genome, chroms[v0:v1], pos[v0:v1], refs[v0:v1],
+                                                            alts[v0:v1], int(args.maxshift))
+        data.pop("diff")
+        yield v0, v1, data
+        del data
+
+
+def run(args, engine=None, genome=None) -> dict:
     import pandas as pd
     import torch
 
@@ -186,8 +253,17 @@ def run(args) -> dict:
     lap("models_s")
 
     dev = torch.device("cuda", args.device)
-    data = load_strand_averaged(args.snpEffectFilePattern, int(args.maxshift), keys=("ref", "alt"), device=dev)
-    torch.cuda.synchronize(dev)
+    if args.vcf:
+        blocks = _chromatin_blocks(args, dev, engine, genome)
+        n_pred = next(blocks)
+        if not args.coorFile_chromatin:
+            args.coorFile_chromatin = f"{args.out_dir}/snps_hg19.vcf"
+    else:
+        data = load_strand_averaged(args.snpEffectFilePattern, int(args.maxshift), keys=("ref", "alt"), device=dev)
+        torch.cuda.synchronize(dev)
+        n_pred = int(data["ref"].shape[1])
+        blocks = iter([(0, n_pred, data)])
+        del data
     lap("load_h5_s")
     coor = pd.read_csv(args.coorFile_chromatin, sep="\t", header=None, comment="#")
     gene = pd.read_csv(args.geneFile, sep="\t", header=None, comment="#")
@@ -206,12 +282,22 @@ def run(args) -> dict:
     genename, strand = np.asarray(gene.iloc[:, -2]), np.asarray(gene.iloc[:, -3])
 
     lap("tables_s")
-    sel = torch.from_numpy(idx).to(dev)
-    identity = len(idx) == data["ref"].shape[1] and bool(np.array_equal(idx, np.arange(len(idx))))
-    scores = {}
-    for key in ("ref", "alt"):
-        x = data[key] if identity else data[key].index_select(1, sel)
-        scores[key] = decay_score_variant(x, dist, strand, W, offsets, shifts=shift_list(int(args.maxshift))).cpu().numpy()
+    if len(idx) and (int(idx.max()) >= n_pred or int(idx.min()) < 0):
+        raise IndexError(f"gene rows point at variant {int(idx.max())} but only {n_pred} were predicted "
+                         "(rows filtered by chromatin.py:241 shift the two tables apart, predict.py:217)")
+    shifts = shift_list(int(args.maxshift))
+    scores = {k: np.empty((len(idx), len(paths)), dtype=np.float32) for k in ("ref", "alt")}
+    for v0, v1, data in blocks:  # one block when reading files; --vcf computes --vcf_block variants at a time
+        rows = np.flatnonzero((idx >= v0) & (idx < v1))   # idx is non-decreasing: a contiguous run of gene rows
+        if rows.size:
+            local = idx[rows] - v0
+            identity = len(local) == v1 - v0 and bool(np.array_equal(local, np.arange(v1 - v0)))
+            sel = None if identity else torch.from_numpy(local).to(dev)
+            for key in ("ref", "alt"):
+                x = data[key] if identity else data[key].index_select(1, sel)
+                scores[key][rows] = decay_score_variant(x, dist[rows], strand[rows], W, offsets, shifts=shifts).cpu().numpy()
+        del data
+        lap("chromatin_and_score_s" if args.vcf else "score_s")
     ref, alt = scores["ref"], scores["alt"]
     lap("score_s")
 

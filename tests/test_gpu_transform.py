@@ -230,3 +230,12 @@ def test_predict_cli_matches_predict_script(engine, cfg1_genome, golden, tmp_pat
     assert np.abs(ours["SED"].values - want["SED"].values).max() <= 5e-3
     for name in ("sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
         assert (tmp_path / "pred" / name).exists()
+    # one pass, no .diff.h5 in between (--vcf): byte-identical tables, with the variants in two HBM blocks
+    args = predict.build_parser().parse_args([
+        "--model_save_file", str(tmp_path / "model.npz"), "--belugaFeatures", str(feats_tsv), "--geneFile",
+        str(genefile), "--vcf", str(vcf), "--vcf_block", "6", "-o", str(tmp_path / "pred_fused")])
+    info = predict.run(args, engine=engine, genome=PackedGenome.from_sequences(cfg1_genome))
+    assert info["n_rows"] == len(ours)
+    assert (tmp_path / "pred_fused" / "snps_hg19.vcf").read_bytes() == (out / "snps_hg19.vcf").read_bytes()
+    for name in ("sed.tsv", "sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
+        assert (tmp_path / "pred_fused" / name).read_bytes() == (tmp_path / "pred" / name).read_bytes(), name

@@ -79,7 +79,7 @@ def test_sed_tables_byte_identical_to_three_pandas_passes(tmp_path, dt):
                        2: [f"rs{i}" for i in range(n)], "dist": rng.integers(-20000, 20000, n),
                        "gene": [f"G{i % 7}" for i in range(n)], "strand": ["+"] * n})
     df = pd.concat([df] + [pd.DataFrame(v, columns=[k]) for k, v in
-                           (("REF", ref), ("ALT", alt), ("SED", alt - ref), ("SED_model2", (alt - ref) * 2))], axis=1)
+                           (("REF", ref), ("ALT", alt), ("SED", alt - ref))], axis=1)   # the reference's columns
     ours, theirs = tmp_path / "ours", tmp_path / "theirs"
     ours.mkdir(); theirs.mkdir()
     write_sed_tables(df, str(ours))
@@ -94,3 +94,30 @@ def test_sed_tables_byte_identical_to_three_pandas_passes(tmp_path, dt):
         f"{theirs}/sed_sorted_by_proportion.tsv", header=True, sep="\t", index=False)
     for name in ("sed.tsv", "sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
         assert (ours / name).read_bytes() == (theirs / name).read_bytes(), name
+
+
+def test_model_list_columns_round_trip(tmp_path):
+    """--modelList extension: the reference's columns keep pandas' text, the extra SED_<model> columns are written by
+    the fast path and must read back to the same float32 values (incl. NaN as empty)."""
+    import pandas as pd
+    from expecto_b200.predict import write_sed_tables
+    rng = np.random.default_rng(1)
+    n = 300
+    ref = rng.standard_normal(n).astype(np.float32)
+    alt = ref + (rng.standard_normal(n) * 1e-3).astype(np.float32)
+    extra = (rng.standard_normal((n, 5)) * np.float32(10.0) ** rng.integers(-8, 8, (n, 5))).astype(np.float32)
+    extra[3, 2] = np.nan; extra[4, 1] = 0.0; extra[5, 0] = 1e-5; extra[6, 0] = 123456789.0
+    df = pd.DataFrame({"index": np.arange(n), 0: ["chr1"] * n, "gene": [f"G{i}" for i in range(n)]})
+    cols = [("REF", ref), ("ALT", alt), ("SED", alt - ref)] + [(f"SED_model{i}.save", extra[:, i]) for i in range(5)]
+    df = pd.concat([df] + [pd.DataFrame(v, columns=[k]) for k, v in cols], axis=1)
+    write_sed_tables(df, str(tmp_path))
+    base = df[list(df.columns)[:6]]
+    got_text = (tmp_path / "sed.tsv").read_text().split("\n")
+    want_text = base.to_csv(None, header=True, sep="\t", index=False).split("\n")
+    assert all(g.startswith(w + "\t") for g, w in zip(got_text[:-1], want_text[:-1]))
+    for name in ("sed.tsv", "sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
+        back = pd.read_csv(tmp_path / name, sep="\t")
+        assert list(back.columns)[:11] == [str(c) for c in df.columns]
+        back = back.sort_values("index").reset_index(drop=True)
+        for i in range(5):
+            assert np.array_equal(back[f"SED_model{i}.save"].values.astype(np.float32), extra[:, i], equal_nan=True)
