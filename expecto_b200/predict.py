@@ -102,9 +102,13 @@ def num_repeats(gene_df) -> list[int]:
     return [int(x) for x in np.diff(edges)]
 
 
-def load_strand_averaged(pattern: str, maxshift: int, keys=("diff", "ref", "alt"), device=None):
-    """predict.py:173-194 -> dict of float32 CUDA tensors [S, N, 2002]: each per-shift dataset is read straight
-    from the file mapping into HBM and its forward / reverse-complement halves averaged there."""
+def load_strand_averaged(pattern: str, maxshift: int, keys=("diff", "ref", "alt"), device=None, n_threads: int = 4,
+                         slab_rows: int = 8192):
+    """predict.py:173-194 -> dict of float32 CUDA tensors [S, N, 2002]: every per-shift dataset is read by
+    ``n_threads`` positional readers straight into pinned slabs, copied to HBM asynchronously and its forward /
+    reverse-complement halves averaged there (``strand_average``)."""
+    from concurrent.futures import ThreadPoolExecutor
+
     import torch
 
     from . import hdf5
@@ -112,15 +116,39 @@ def load_strand_averaged(pattern: str, maxshift: int, keys=("diff", "ref", "alt"
 
     shifts = shift_list(maxshift)
     out = {}
-    for si, s in enumerate(shifts):
-        with hdf5.File(pattern.replace("SHIFT", str(s))) as f:
-            for k in keys:
-                d = f[k]
-                n = int(d.shape[0] / 2)
-                if k not in out:
-                    out[k] = torch.empty((len(shifts), n, 2002), dtype=torch.float32, device=device)
-                x = torch.from_numpy(np.array(d[0:2 * n, :], dtype=np.float32)).to(device, non_blocking=False)
-                strand_average(x, out=out[k][si])
+    ring = [[torch.empty((slab_rows, 2002), dtype=torch.float32, pin_memory=True), None] for _ in range(2 * n_threads)]
+    slot = 0
+    with ThreadPoolExecutor(max_workers=n_threads) as pool:
+        for si, s in enumerate(shifts):
+            with hdf5.File(pattern.replace("SHIFT", str(s))) as f:
+                for k in keys:
+                    d = f[k]
+                    n = int(d.shape[0] / 2)
+                    if k not in out:
+                        out[k] = torch.empty((len(shifts), n, 2002), dtype=torch.float32, device=device)
+                    x = torch.empty((2 * n, 2002), dtype=torch.float32, device=device)
+                    jobs = []
+                    for r0 in range(0, 2 * n, slab_rows):
+                        r1 = min(2 * n, r0 + slab_rows)
+                        buf, ev = ring[slot]
+                        if ev is not None:
+                            ev.synchronize()     # the H2D copy that last used this slab has finished
+                        jobs.append((pool.submit(d.read_rows_into, buf.numpy(), r0, r1), slot, r0, r1))
+                        slot = (slot + 1) % len(ring)
+                        if len(jobs) >= n_threads:           # keep n_threads reads in flight, copy in order
+                            fut, sl, a0, a1 = jobs.pop(0)
+                            fut.result()
+                            x[a0:a1].copy_(ring[sl][0][:a1 - a0], non_blocking=True)
+                            ring[sl][1] = torch.cuda.Event()
+                            ring[sl][1].record(torch.cuda.current_stream(device))
+                    for fut, sl, a0, a1 in jobs:
+                        fut.result()
+                        x[a0:a1].copy_(ring[sl][0][:a1 - a0], non_blocking=True)
+                        ring[sl][1] = torch.cuda.Event()
+                        ring[sl][1].record(torch.cuda.current_stream(device))
+                    strand_average(x, out=out[k][si])
+                    del x
+    torch.cuda.synchronize(device)
     return out
 
 

@@ -84,3 +84,16 @@ def test_slab_writer_threads_and_order(tmp_path):
         sw.wait_free(s)
     with pytest.raises(OSError):
         sw.close()
+
+
+def test_positional_row_reads(tmp_path):
+    """predict's loader reads row ranges of a dataset straight into (pinned) buffers from several threads."""
+    p = str(tmp_path / "r.h5")
+    a = np.random.default_rng(2).standard_normal((50, 2002)).astype(np.float32)
+    hdf5.write_datasets(p, {"ref": a, "alt": a * 2})
+    with hdf5.File(p) as f:
+        buf = np.zeros((20, 2002), np.float32)
+        f["alt"].read_rows_into(buf, 7, 19)
+        assert np.array_equal(buf[:12], a[7:19] * 2) and not buf[12:].any()
+        f["ref"].read_rows_into(buf, 30, 50)
+        assert np.array_equal(buf, a[30:50])
