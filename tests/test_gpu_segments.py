@@ -146,6 +146,32 @@ def test_segment_loop_with_and_without_delta_is_identical(engine, small_genome):
             assert np.array_equal(got[True][s][k], got[False][s][k]), (s, k)
 
 
+def test_averaged_device_effects_equal_strand_average_of_the_file_rows(engine, small_genome):
+    """predict --vcf's source (predict_all_shifts_averaged_device) == (fwd + rc) / 2 of the rows the chromatin step
+    writes, for substitutions, indels and window-path variants alike (predict.py:186-190)."""
+    from expecto_b200.chromatin import predict_all_shifts_averaged_device, predict_all_shifts_segments
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    rows = GI.edge_variants(small_genome) + _substitutions(small_genome, 10)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    n = len(rows)
+    shifts = chromatin_shift_list(800)
+    store = {s: {k: np.zeros((2 * n, 2002), np.float32) for k in ("diff", "ref", "alt")} for s in shifts}
+
+    def make(s):
+        def sink(name, row0, arr):
+            store[s][name][row0:row0 + len(arr)] = arr
+        return sink
+    info = predict_all_shifts_segments(engine, pg, chroms, pos, refs, alts, 800, {s: make(s) for s in shifts})
+    assert info["window_variants"] > 0 and info["delta_variants"] > 0
+    dev = predict_all_shifts_averaged_device(engine, pg, chroms, pos, refs, alts, 800)
+    for si, s in enumerate(shifts):
+        for k in ("ref", "alt", "diff"):
+            want = (torch.from_numpy(store[s][k][:n]) + torch.from_numpy(store[s][k][n:])) / 2.0
+            assert torch.equal(dev[k][si].cpu(), want), (s, k)
+
+
 def test_chromatin_cli_segments_and_windows_modes_write_identical_files(engine, cfg1_genome, golden, tmp_path):
     """Edge VCF (one variant — the 120-bp deletion — falls back to the per-window path inside segment mode)."""
     from expecto_b200 import chromatin, hdf5
