@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Timing diagnostics: per-layer times with parts of the GEMM pipeline switched off (BX_DEBUG_FLAGS:
 1 = no B TMA loads, 2 = no A TMA loads, 4 = no epilogue work).  Results are WRONG by construction; only the
-times matter.  Usage: python tools/diag_flags.py [n]"""
+times matter — and only as CYCLES: with flag 4 no layer writes its output, so the next layer multiplies zeros, the
+tensor pipe draws far less power and the clock rises by ~20 % (tools/diag_epilogue_cycles.sh: conv2 5.78 M vs
+5.69 M cycles, 1.44 vs 1.76 GHz).  Operand data, not the epilogue, moves the clock.  Usage: python tools/diag_flags.py [n]"""
 import json, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
