@@ -249,20 +249,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             ra.advance<SA>();
           }
         } else {
-        mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
-        if (p.debug_flags & 2) {
-          if (elect_one() && rank == 0) mbar_arrive_local(fullA(ra.idx));
-        } else if (elect_one()) {
-          if constexpr (CG == 1) {
-            mbar_arrive_expect_tx(fullA(ra.idx), Cfg::A_BYTES);
-            tma_load_2d(sA + ra.idx * Cfg::A_BYTES, &tmA, fullA(ra.idx), kb * 64, row0);
-          } else {
-            if (rank == 0) mbar_arrive_expect_tx(fullA(ra.idx), 2 * Cfg::A_BYTES);
-            tma_load_2d_pair(sA + ra.idx * Cfg::A_BYTES, &tmA, mapa(fullA(ra.idx), 0), kb * 64, row0);
+          mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
+          if (p.debug_flags & 2) {
+            if (elect_one() && rank == 0) mbar_arrive_local(fullA(ra.idx));
+          } else if (elect_one()) {
+            if constexpr (CG == 1) {
+              mbar_arrive_expect_tx(fullA(ra.idx), Cfg::A_BYTES);
+              tma_load_2d(sA + ra.idx * Cfg::A_BYTES, &tmA, fullA(ra.idx), kb * 64, row0);
+            } else {
+              if (rank == 0) mbar_arrive_expect_tx(fullA(ra.idx), 2 * Cfg::A_BYTES);
+              tma_load_2d_pair(sA + ra.idx * Cfg::A_BYTES, &tmA, mapa(fullA(ra.idx), 0), kb * 64, row0);
+            }
           }
-        }
-        __syncwarp();
-        ra.advance<SA>();
+          __syncwarp();
+          ra.advance<SA>();
         }
 #pragma unroll 1
         for (int t = 0; t < TAPS; t += Cfg::TPS) {
