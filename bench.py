@@ -119,7 +119,7 @@ def cpu_forward_rate(batch: int, min_seconds: float, max_windows: int, seed: int
     return done / dt, cores, torch.get_num_threads(), done, dt
 
 
-def variant_workflow(eng, n_variants: int):
+def variant_workflow(eng, n_variants: int, rank: int = 0, world: int = 1, sync=None):
     """BASELINE configs[2] shape at a stated reduced size, outside the timed region: a synthetic VCF (90 % SNV, 5 %
     ref-mismatch, 5 % indel) on a synthetic genome -> ref/alt x fwd/rc x 9 shifts -> pinned host ref/alt/diff, through
     the drop-in's segment + delta mode (host descriptors in, host arrays out, no file).  Reported in the headline
@@ -133,21 +133,27 @@ def variant_workflow(eng, n_variants: int):
     genome = synth.make_genome([("chr1", 6_000_000), ("chr2", 4_000_000)], seed=3)
     pg = PackedGenome.from_sequences(genome)
     eng.set_genome(pg)
-    rows = synth.make_vcf_rows(genome, n_variants, seed=3, odd_names=False)
+    rows = synth.make_vcf_rows(genome, n_variants, seed=3 + rank, odd_names=False)  # every rank: its own shard
     chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
     refs, alts = [r[3] for r in rows], [r[4] for r in rows]
     sinks = {s: (lambda *a: None) for s in chromatin.shift_list(800)}
     k = min(1200, n_variants)
     chromatin.predict_all_shifts_segments(eng, pg, chroms[:k], pos[:k], refs[:k], alts[:k], 800, sinks)  # warm-up
     torch.cuda.synchronize()
+    if sync is not None:
+        sync(0.0)                      # barrier: all ranks start together
     t0 = time.perf_counter()
     info = chromatin.predict_all_shifts_segments(eng, pg, chroms, pos, refs, alts, 800, sinks)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    return {"workload": f"{n_variants} synthetic variants x (ref, alt) x (fwd, rc) x 9 shifts, segment + delta mode, "
-                        "host descriptors -> pinned host ref/alt/diff, no file",
-            "variants": n_variants, "windows": 36 * n_variants, "seconds": dt, "windows_per_s": 36 * n_variants / dt,
-            "variants_per_s": n_variants / dt, "d2h_bytes": 9 * 3 * 2 * n_variants * 2002 * 4,
+    if sync is not None:
+        dt = sync(dt)                  # slowest rank
+    n_all = n_variants * world
+    return {"workload": f"{n_variants} synthetic variants per GPU x (ref, alt) x (fwd, rc) x 9 shifts, segment + delta "
+                        "mode, host descriptors -> pinned host ref/alt/diff, no file; variants sharded over the GPUs, "
+                        "no collective",
+            "variants": n_all, "windows": 36 * n_all, "seconds": dt, "windows_per_s": 36 * n_all / dt,
+            "variants_per_s": n_all / dt, "d2h_bytes": 9 * 3 * 2 * n_all * 2002 * 4,
             "delta_variants": info["delta_variants"], "window_path_variants": info["window_variants"]}
 
 
@@ -319,6 +325,10 @@ def run_gpu(args) -> int:
     e2e_value = world * B * K / e2e_s
     e2e_ok = bool(torch.equal(out_host, out.cpu()))
 
+    wf = None
+    if world > 1 and not args.no_workflow:   # all ranks take part (N = 1 runs it after the transform measurement)
+        wf = variant_workflow(eng, args.workflow_variants, rank, world, max_over_ranks)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -373,8 +383,8 @@ def run_gpu(args) -> int:
         del x, out
         torch.cuda.empty_cache()
         line["transform_roofline"] = transform_rooflines(dev, peaks)
-    if world == 1 and not args.no_workflow:
-        line["variant_workflow"] = variant_workflow(eng, args.workflow_variants)
+    if not args.no_workflow:
+        line["variant_workflow"] = wf if world > 1 else variant_workflow(eng, args.workflow_variants)
     if world == 1 and not args.no_cpu_baseline:
         rate, cores, threads, done, dt = cpu_forward_rate(32, args.cpu_seconds, 4096)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
