@@ -96,6 +96,7 @@ struct bx_ctx {
   float* bfc2 = nullptr; // [2048]
   void* act[7] = {};     // act[0] = im2col one-hot [cap*1996,64]; act[i] = output of conv i
   float* acc1 = nullptr; // fp32 [cap, 2048]
+  float* acc1_view = nullptr;  // partial sums the next finaliser reads (acc1, or a slab of acc_ref in delta mode)
   void* hid = nullptr;   // 16-bit [cap, 2048]
   const uint32_t* bases2 = nullptr;
   const uint32_t* nmask = nullptr;
@@ -121,6 +122,9 @@ struct bx_ctx {
   void* fc_in = nullptr;
   void* act4h = nullptr;  // conv4 half-pooled (row pairs), both pooling phases are finished from it
   void* act4b = nullptr;  // phase-B pooled conv4 output
+  float* acc_ref = nullptr;     // delta mode: FC1 partial sums of a chunk's ref windows [8][n_ref][2048]
+  size_t acc_ref_bytes = 0;
+  float* probs_dense = nullptr; // delta mode: FC2 output of one piece in dense order, before the scatter
   void* patch6a = nullptr;  // delta mode: conv6 outputs of the alt patches (phase A / B)
   void* patch6b = nullptr;
   size_t patch6_bytes = 0;
@@ -165,7 +169,12 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
   p.n_chunks = p.n_total / BN;
   static const int dbg = getenv("BX_DEBUG_FLAGS") ? atoi(getenv("BX_DEBUG_FLAGS")) : 0;  // timing diagnostics only
   p.debug_flags = dbg;
-  const int units = (A_MODE != 0) ? p.m_tiles : p.m_tiles * p.n_chunks * p.k_splits;
+  int units = (A_MODE != 0) ? p.m_tiles : p.m_tiles * p.n_chunks * p.k_splits;
+  if (p.n_tile_ranges > 0) {
+    if (p.n_tile_ranges != p.m_tiles) return fail(BX_E_ARG, "tile ranges (%d) != M tiles (%d)", p.n_tile_ranges, p.m_tiles);
+    units = 0;
+    for (int t = 0; t < p.n_tile_ranges; ++t) units += p.tile_n[t] * p.n_chunks;
+  }
   int clusters = std::min(units, c->num_sms / CG);
   if (clusters < 1) clusters = 1;
   cudaLaunchConfig_t cfg = {};
@@ -262,7 +271,7 @@ static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st, const EncParams* e
 template <typename T>
 static int run_fc1_finalize(bx_ctx* c, int n, int k_splits, size_t split_stride, cudaStream_t st) {
   const size_t total = (size_t)n * 2048;
-  fc1_finalize_kernel<T><<<(unsigned)((total / 4 + 255) / 256), 256, 0, st>>>(c->acc1, k_splits, split_stride, c->bfc1,
+  fc1_finalize_kernel<T><<<(unsigned)((total / 4 + 255) / 256), 256, 0, st>>>(c->acc1_view, k_splits, split_stride, c->bfc1,
                                                                              (T*)c->hid, total);
   g_launches++;
   CK(cudaGetLastError());
@@ -274,9 +283,9 @@ static int run_fc1_finalize(bx_ctx* c, int n, int k_splits, size_t split_stride,
 constexpr int kFc1Splits = 8;
 static size_t fc1_scratch_rows(int cap) { return (size_t)cap * kFc1Splits; }
 
-static int run_fc1(bx_ctx* c, int n, cudaStream_t st) {
-  // fc1: [n, 67840] x [2048, 67840]^T; each K slice writes its own fp32 partial and the finaliser adds the
-  // slices in index order (deterministic, no atomics).
+// fc1 GEMM: [n, 67840] x [2048, 67840]^T; each K slice writes its own fp32 partial into out[ks][row][2048]
+// (slices split_stride elements apart).  ranges: optional per-M-tile slice ranges (GemmParams::tile_lo/tile_n).
+static int launch_fc1_gemm(bx_ctx* c, int n, float* out, size_t split_stride, const GemmParams* ranges, cudaStream_t st) {
   GemmParams p = {};
   p.m_rows = n;
   p.k_valid = 67840;
@@ -284,15 +293,31 @@ static int run_fc1(bx_ctx* c, int n, cudaStream_t st) {
   p.k_blocks = 67840 / 64;
   p.kb_per_split = (p.k_blocks + kFc1Splits - 1) / kFc1Splits;
   p.k_splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
-  p.split_stride = (long long)n * 2048;
+  p.split_stride = (long long)split_stride;
   p.pitch_in = p.pitch_out = p.l_store = 1 << 30;
   p.ld_out = 2048;
   p.n_store = 2048;
   p.bias = nullptr;
-  p.out = c->acc1;
-  if (int r = launch_gemm(c, 1, 256, EPI_PARTIAL_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st)) return r;
-  return (c->dtype == BX_DTYPE_F16) ? run_fc1_finalize<__half>(c, n, p.k_splits, (size_t)p.split_stride, st)
-                                    : run_fc1_finalize<__nv_bfloat16>(c, n, p.k_splits, (size_t)p.split_stride, st);
+  p.out = out;
+  if (ranges) {
+    p.n_tile_ranges = ranges->n_tile_ranges;
+    memcpy(p.tile_lo, ranges->tile_lo, sizeof(p.tile_lo));
+    memcpy(p.tile_n, ranges->tile_n, sizeof(p.tile_n));
+  }
+  return launch_gemm(c, 1, 256, EPI_PARTIAL_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st);
+}
+constexpr int kFc1KbPerSplit = (67840 / 64 + kFc1Splits - 1) / kFc1Splits;
+
+static int run_fc1(bx_ctx* c, int n, cudaStream_t st, float* part = nullptr, size_t split_stride = 0) {
+  // the finaliser adds the slices in index order (deterministic, no atomics)
+  if (!part) { part = c->acc1; split_stride = (size_t)n * 2048; }
+  if (int r = launch_fc1_gemm(c, n, part, split_stride, nullptr, st)) return r;
+  if (c->dtype == BX_DTYPE_F16) {
+    c->acc1_view = part;
+    return run_fc1_finalize<__half>(c, n, kFc1Splits, split_stride, st);
+  }
+  c->acc1_view = part;
+  return run_fc1_finalize<__nv_bfloat16>(c, n, kFc1Splits, split_stride, st);
 }
 
 static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
@@ -449,7 +474,7 @@ int bx_ctx_destroy(bx_ctx* c) {
   }
   cudaFree(c->probs_scratch);
   cudaFree(c->act6b); cudaFree(c->fc_in); cudaFree(c->act4h); cudaFree(c->act4b);
-  cudaFree(c->patch6a); cudaFree(c->patch6b);
+  cudaFree(c->patch6a); cudaFree(c->patch6b); cudaFree(c->acc_ref); cudaFree(c->probs_dense);
   if (c->s_comp) cudaStreamDestroy(c->s_comp);
   if (c->s_in) cudaStreamDestroy(c->s_in);
   if (c->s_out) cudaStreamDestroy(c->s_out);
@@ -937,6 +962,118 @@ static int run_segment_convs(bx_ctx* c, const bx_window_desc* d, const uint8_t* 
   return 0;
 }
 
+// BX_DELTA_DENSE=0: alt windows go through FC1 in full (comparisons).
+static bool delta_dense_enabled() {
+  static const bool on = !(getenv("BX_DELTA_DENSE") && atoi(getenv("BX_DELTA_DENSE")) == 0);
+  return on;
+}
+
+// Dense layers of one delta-mode chunk (kernels_misc.cuh, "delta mode, dense layers"): FC1 over all slices for the
+// ref windows, over the slices that hold patched rows for the alt windows, then FC2 and the scatter to the final order.
+static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int ng, int n_shifts, int patch_row0,
+                             int shift_major, float* out, cudaStream_t st) {
+  (void)gp;
+  const bool f16 = c->dtype == BX_DTYPE_F16;
+  DeltaDense dd = {};
+  dd.ng = ng; dd.S = n_shifts; dd.shift_major = shift_major ? 1 : 0;
+  dd.p6 = sg.p6; dd.p6p = sg.p6p; dd.row0 = patch_row0; dd.valid_a = sg.valid_a; dd.valid_b = sg.valid_b;
+  dd.kb_per_split = kFc1KbPerSplit;
+  for (int i = 0; i < n_shifts; ++i) { dd.k_of_shift[i] = sg.k_of_shift[i]; dd.si_of_k[i] = -1; }
+  for (int i = 0; i < n_shifts; ++i) dd.si_of_k[sg.k_of_shift[i]] = i;
+  for (int k = 0; k < n_shifts; ++k) {
+    if (dd.si_of_k[k] < 0) return fail(BX_E_ARG, "k_of_shift is not a permutation (offset %d missing)", k);
+    const DeltaClass cl = delta_class(dd, k);
+    if (cl.lo >= cl.hi) return fail(BX_E_ARG, "the patch does not reach the window at offset %d", k);
+  }
+  const size_t n_half = (size_t)ng * n_shifts * 2;   // ref windows of the chunk = alt windows of the chunk
+  const size_t ref_bytes = (size_t)kFc1Splits * n_half * 2048 * sizeof(float);
+  if (ref_bytes > c->acc_ref_bytes) {
+    CK(cudaStreamSynchronize(st));
+    cudaFree(c->acc_ref);
+    c->acc_ref = nullptr; c->acc_ref_bytes = 0;
+    CK(cudaMalloc(&c->acc_ref, ref_bytes));
+    c->acc_ref_bytes = ref_bytes;
+  }
+  if (!c->probs_dense) CK(cudaMalloc(&c->probs_dense, (size_t)c->cap * BX_FEATURES * sizeof(float)));
+  const size_t ref_stride = n_half * 2048;
+  void* saved = c->act[6];
+  auto gather = [&](int alt, long long d0, int m) {
+    if (f16)
+      gather_fc1_delta_kernel<__half><<<m, 256, 0, st>>>((const __half*)saved, (const __half*)c->act6b,
+                                                         (const __half*)c->patch6a, (const __half*)c->patch6b, dd, alt,
+                                                         d0, (__half*)c->fc_in);
+    else
+      gather_fc1_delta_kernel<__nv_bfloat16><<<m, 256, 0, st>>>(
+          (const __nv_bfloat16*)saved, (const __nv_bfloat16*)c->act6b, (const __nv_bfloat16*)c->patch6a,
+          (const __nv_bfloat16*)c->patch6b, dd, alt, d0, (__nv_bfloat16*)c->fc_in);
+    g_launches++;
+  };
+  auto finish = [&](int alt, long long d0, int m) -> int {   // FC2 + scatter of a piece whose hidden layer is ready
+    StageTimer t(c, 8, st);
+    if (int r = run_fc2(c, m, c->probs_dense, st)) return r;
+    scatter_delta_rows_kernel<<<m, 256, 0, st>>>(c->probs_dense, dd, alt, d0, out);
+    g_launches++;
+    CK(cudaGetLastError());
+    return 0;
+  };
+  // ref windows: all slices, partials kept in acc_ref for the alt windows of the same chunk
+  for (size_t d0 = 0; d0 < n_half; d0 += c->cap) {
+    const int m = (int)std::min<size_t>(c->cap, n_half - d0);
+    {
+      StageTimer t(c, 7, st);
+      gather(0, (long long)d0, m);
+      CK(cudaGetLastError());
+      c->act[6] = c->fc_in;
+      const int r = run_fc1(c, m, st, c->acc_ref + d0 * 2048, ref_stride);
+      c->act[6] = saved;
+      if (r) return r;
+    }
+    if (int r = finish(0, (long long)d0, m)) return r;
+  }
+  // alt windows: per M tile only the slices its rows' classes need
+  const int tile_rows = 128 * c->cg;
+  for (size_t d0 = 0; d0 < n_half; d0 += c->cap) {
+    const int m = (int)std::min<size_t>(c->cap, n_half - d0);
+    GemmParams ranges = {};
+    ranges.n_tile_ranges = (m + tile_rows - 1) / tile_rows;
+    if (ranges.n_tile_ranges > 32) return fail(BX_E_STATE, "delta dense phase: %d M tiles per piece", ranges.n_tile_ranges);
+    for (int t = 0; t < ranges.n_tile_ranges; ++t) {
+      const size_t first = d0 + (size_t)t * tile_rows, last = std::min(d0 + m, first + tile_rows) - 1;
+      int lo = kFc1Splits, hi = -1;
+      for (int cls = (int)(first / (2 * (size_t)ng)); cls <= (int)(last / (2 * (size_t)ng)); ++cls) {
+        const DeltaClass cl = delta_class(dd, cls);
+        lo = std::min(lo, cl.ks_lo); hi = std::max(hi, cl.ks_hi);
+      }
+      ranges.tile_lo[t] = (unsigned char)lo;
+      ranges.tile_n[t] = (unsigned char)(hi - lo + 1);
+    }
+    {
+      StageTimer t(c, 7, st);
+      gather(1, (long long)d0, m);
+      CK(cudaGetLastError());
+      c->act[6] = c->fc_in;
+      const size_t stride = (size_t)m * 2048;
+      const int r = launch_fc1_gemm(c, m, c->acc1, stride, &ranges, st);
+      c->act[6] = saved;
+      if (r) return r;
+      const size_t total = (size_t)m * 2048;
+      const unsigned blocks = (unsigned)((total / 4 + 255) / 256);
+      if (f16)
+        fc1_finalize_delta_kernel<__half><<<blocks, 256, 0, st>>>(c->acc1, stride, c->acc_ref, ref_stride, dd,
+                                                                  (long long)d0, kFc1Splits, c->bfc1, (__half*)c->hid,
+                                                                  total);
+      else
+        fc1_finalize_delta_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(c->acc1, stride, c->acc_ref, ref_stride, dd,
+                                                                         (long long)d0, kFc1Splits, c->bfc1,
+                                                                         (__nv_bfloat16*)c->hid, total);
+      g_launches++;
+      CK(cudaGetLastError());
+    }
+    if (int r = finish(1, (long long)d0, m)) return r;
+  }
+  return 0;
+}
+
 // Segment mode proper.  patch_descs_dev == nullptr: descs_dev holds segs_out segments per group.  Delta mode
 // (patch_descs_dev != nullptr, segs_out == 4): descs_dev holds the group's two REF segments (fwd, rc) and
 // patch_descs_dev two short ALT patches (fwd, rc) of patch_len positions that start 16*patch_row0 positions into
@@ -1003,6 +1140,12 @@ static int forward_segments_impl(bx_ctx* c, const bx_window_desc* descs_dev, con
       if (int r = run_segment_convs(c, patch_descs_dev + (size_t)g0 * 2, alleles_dev, ng * 2, patch_len, gp,
                                     c->patch6a, c->patch6b, n_shifts > 1, st))
         return r;
+    if (delta && delta_dense_enabled()) {
+      if (int r = delta_dense_phase(c, sg, gp, ng, n_shifts, patch_row0, shift_major,
+                                    probs_dev + (size_t)g0 * segs_out * n_shifts * BX_FEATURES, st))
+        return r;
+      continue;
+    }
     // dense layers per window, in final output order, `cap` windows at a time
     sg.n_groups = ng;
     const long long n_win = (long long)ng * segs_out * n_shifts;

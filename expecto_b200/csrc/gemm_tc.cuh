@@ -55,6 +55,10 @@ struct GemmParams {
   int debug_flags;   // diagnostics only (BX_DEBUG_FLAGS): 1 = no B loads, 2 = no A loads, 4 = no epilogue work
   const float* bias; // [n_total] fp32 (unused for EPI_PARTIAL_F32)
   void* out;
+  // Optional per-M-tile split-K ranges (EPI_PARTIAL_F32): tile mt computes slices tile_lo[mt] .. tile_lo[mt] +
+  // tile_n[mt] - 1 only (delta mode's alt windows need just the slices whose K range holds changed rows).
+  int n_tile_ranges;  // 0 = every tile computes all k_splits slices
+  unsigned char tile_lo[32], tile_n[32];
 };
 
 template <int TAPS, int BLOCK_N, int CG>
@@ -177,6 +181,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       return mt < p.m_tiles;
     } else {
       const int u = cluster_id + it * num_clusters;
+      if (p.n_tile_ranges > 0) {  // units ordered (tile, slice, N chunk)
+        int first = 0;
+        for (int t = 0; t < p.n_tile_ranges; ++t) {
+          const int cnt = (int)p.tile_n[t] * p.n_chunks;
+          if (u < first + cnt) {
+            const int l = u - first;
+            mt = t;
+            ks = (int)p.tile_lo[t] + l / p.n_chunks;
+            nc = l % p.n_chunks;
+            return true;
+          }
+          first += cnt;
+        }
+        return false;
+      }
       if (u >= total_units) return false;
       ks = u / tiles_mn;
       const int rem = u - ks * tiles_mn;

@@ -275,6 +275,134 @@ __global__ void fc1_finalize_kernel(const float* __restrict__ part, int k_splits
   o[3] = to_t<T>(fminf(fmaxf(a.w + b4.w, 0.f), 65504.f));
 }
 
+// ------------------------------------------------------------------ delta mode, dense layers
+// In delta mode an alt window's FC1 operand equals the ref window's (same shift, same strand) outside the conv6
+// rows the patch supplies.  FC1's split-K slices are fixed K ranges (8 slices of 133 K-blocks = 13.3 rows), and the
+// finaliser adds the slices in index order, so every slice whose K range holds no patched row has, for the alt
+// window, bit for bit the partial sum the ref window already produced.  The dense phase therefore runs FC1 over
+// all slices for the ref windows only (partials kept for the whole chunk) and, for the alt windows, only over the
+// 1-3 slices their patched rows fall into; the finaliser takes the remaining slices from the ref window's partials.
+// Dense row orders: ref row rr = (si*ng + grp)*2 + t; alt row ar = c*2*ng + grp*2 + t with t = strand (0 fwd, 1 rc)
+// and class c = the window's offset index k (fwd) or S-1-k (rc), so that all rows of a class share one offset.
+struct DeltaDense {
+  int ng, S, shift_major;
+  int p6, p6p, row0, valid_a, valid_b;   // as SegGather
+  int kb_per_split;                       // K-blocks (64 elements, a tenth of a 640-channel row) per FC1 slice
+  int k_of_shift[200], si_of_k[200];
+};
+
+struct DeltaClass { int off, lo, hi, ks_lo, ks_hi; };  // conv6 row offset, patched window rows [lo, hi), slice range
+
+__host__ __device__ inline DeltaClass delta_class(const DeltaDense& g, int c) {
+  DeltaClass r;
+  r.off = ((c & 1) ? 12 : 0) + 25 * (c >> 1);
+  const int valid = (c & 1) ? g.valid_b : g.valid_a;
+  r.lo = g.row0 - r.off < 0 ? 0 : g.row0 - r.off;
+  r.hi = g.row0 - r.off + valid > 106 ? 106 : g.row0 - r.off + valid;
+  r.ks_lo = r.lo * 10 / g.kb_per_split;
+  r.ks_hi = (r.hi * 10 - 1) / g.kb_per_split;
+  return r;
+}
+
+// FC1 operand rows of a piece of the ref (alt == 0) or alt (alt == 1) dense order starting at dense row d0.
+// Alt rows copy only the conv6 rows their FC1 slices read: patched rows from the patch, the others from the ref
+// segment.  One block per dense row.
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_fc1_delta_kernel(const T* __restrict__ act6a, const T* __restrict__ act6b, const T* __restrict__ patch6a,
+                        const T* __restrict__ patch6b, const DeltaDense g, int alt, long long d0, T* __restrict__ dst) {
+  const long long d = d0 + blockIdx.x;
+  int c, grp, t;
+  if (alt) {
+    c = (int)(d / (2 * g.ng));
+    const int x = (int)(d % (2 * g.ng));
+    grp = x >> 1; t = x & 1;
+  } else {
+    t = (int)(d & 1);
+    const long long x = d >> 1;
+    const int si = (int)(x / g.ng);
+    grp = (int)(x % g.ng);
+    const int k = g.k_of_shift[si];
+    c = t ? g.S - 1 - k : k;
+  }
+  const DeltaClass cl = delta_class(g, c);
+  const long long seg = (long long)grp * 2 + t;
+  const bool pb = c & 1;
+  const uint4* s4 = reinterpret_cast<const uint4*>((pb ? act6b : act6a) + ((size_t)seg * g.p6 + cl.off) * 640);
+  uint4* d4 = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * 106 * 640);
+  if (!alt) {
+    constexpr int N16 = 106 * 640 * 2 / 16;
+    for (int i = threadIdx.x; i < N16; i += 256) d4[i] = __ldg(s4 + i);
+    return;
+  }
+  const uint4* p4 = reinterpret_cast<const uint4*>((pb ? patch6b : patch6a) + (size_t)seg * g.p6p * 640);
+  const int plo = g.row0 - cl.off;                               // window row of patch row 0
+  const int r_lo = cl.ks_lo * g.kb_per_split / 10;               // conv6 rows the computed slices read
+  int r_hi = ((cl.ks_hi + 1) * g.kb_per_split + 9) / 10;
+  if (r_hi > 106) r_hi = 106;
+  for (int i = r_lo * 80 + threadIdx.x; i < r_hi * 80; i += 256) {
+    const int l = i / 80;                                         // 80 x 16 bytes per 640-channel row
+    d4[i] = (l >= cl.lo && l < cl.hi) ? __ldg(p4 + (size_t)(l - plo) * 80 + (i - l * 80)) : __ldg(s4 + i);
+  }
+}
+
+// fc1 finaliser for a piece of alt rows: slices inside the row's class range come from this piece's partials,
+// the others from the ref window's; same summation order as fc1_finalize_kernel.
+template <typename T>
+__global__ void fc1_finalize_delta_kernel(const float* __restrict__ part, size_t split_stride,
+                                          const float* __restrict__ ref_part, size_t ref_stride, const DeltaDense g,
+                                          long long a0, int k_splits, const float* __restrict__ bias,
+                                          T* __restrict__ h, size_t total) {
+  const size_t idx = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (idx >= total) return;
+  const long long ar = a0 + (long long)(idx >> 11);
+  const int c = (int)(ar / (2 * g.ng));
+  const int x = (int)(ar % (2 * g.ng));
+  const int grp = x >> 1, t = x & 1;
+  const int k = t ? g.S - 1 - c : c;
+  const size_t ref_idx = ((size_t)((size_t)g.si_of_k[k] * g.ng + grp) * 2 + t) * 2048 + (idx & 2047);
+  const DeltaClass cl = delta_class(g, c);
+  auto slice = [&](int s) {
+    return (s >= cl.ks_lo && s <= cl.ks_hi) ? *reinterpret_cast<const float4*>(part + (size_t)s * split_stride + idx)
+                                            : *reinterpret_cast<const float4*>(ref_part + (size_t)s * ref_stride + ref_idx);
+  };
+  float4 a = slice(0);
+  for (int s = 1; s < k_splits; ++s) {
+    const float4 b = slice(s);
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+  }
+  const float4 b4 = *reinterpret_cast<const float4*>(bias + (idx & 2047));
+  T* o = h + idx;
+  o[0] = to_t<T>(fminf(fmaxf(a.x + b4.x, 0.f), 65504.f));
+  o[1] = to_t<T>(fminf(fmaxf(a.y + b4.y, 0.f), 65504.f));
+  o[2] = to_t<T>(fminf(fmaxf(a.z + b4.z, 0.f), 65504.f));
+  o[3] = to_t<T>(fminf(fmaxf(a.w + b4.w, 0.f), 65504.f));
+}
+
+// Probabilities of a piece of dense rows -> their windows' rows of the final output (shift-major or group-major).
+__global__ void __launch_bounds__(256)
+scatter_delta_rows_kernel(const float* __restrict__ src, const DeltaDense g, int alt, long long d0,
+                          float* __restrict__ out) {
+  const long long d = d0 + blockIdx.x;
+  int si, grp, t;
+  if (alt) {
+    const int c = (int)(d / (2 * g.ng));
+    const int x = (int)(d % (2 * g.ng));
+    grp = x >> 1; t = x & 1;
+    si = g.si_of_k[t ? g.S - 1 - c : c];
+  } else {
+    t = (int)(d & 1);
+    const long long x = d >> 1;
+    si = (int)(x / g.ng);
+    grp = (int)(x % g.ng);
+  }
+  const int q = alt ? 2 + t : t;
+  const size_t w = g.shift_major ? ((size_t)si * g.ng + grp) * 4 + q : ((size_t)grp * g.S + si) * 4 + q;
+  const float* s = src + (size_t)blockIdx.x * kFeat;
+  float* o = out + w * kFeat;
+  for (int f = threadIdx.x; f < kFeat; f += 256) o[f] = s[f];
+}
+
 // ------------------------------------------------------------------ chromatin.py:281-286 outputs
 // probs [4N, 2002] in (variant, {ref fwd, ref rc, alt fwd, alt rc}) order.
 __global__ void chromatin_outputs_kernel(const float* __restrict__ probs, int n_var, float* __restrict__ ref,
