@@ -1030,10 +1030,11 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
     }
     if (int r = finish(0, (long long)d0, m)) return r;
   }
-  // alt windows: per M tile only the slices its rows' classes need
+  // alt windows: per M tile only the slices its rows' classes need (at most 32 tiles per launch: GemmParams)
   const int tile_rows = 128 * c->cg;
-  for (size_t d0 = 0; d0 < n_half; d0 += c->cap) {
-    const int m = (int)std::min<size_t>(c->cap, n_half - d0);
+  const size_t piece = std::min<size_t>(c->cap, (size_t)32 * tile_rows);
+  for (size_t d0 = 0; d0 < n_half; d0 += piece) {
+    const int m = (int)std::min<size_t>(piece, n_half - d0);
     GemmParams ranges = {};
     ranges.n_tile_ranges = (m + tile_rows - 1) / tile_rows;
     if (ranges.n_tile_ranges > 32) return fail(BX_E_STATE, "delta dense phase: %d M tiles per piece", ranges.n_tile_ranges);

@@ -117,6 +117,32 @@ def test_delta_patches_equal_full_segments_and_windows_bitwise(engine, small_gen
         engine.forward_segments_delta(rd, pd, codes, n, 3600, plen, 3600 // 16, k_of, shift_major=True)
 
 
+@pytest.mark.parametrize("dtype,cta_group,maxshift", [("f16", 2, 400), ("f16", 1, 1000), ("bf16", 2, 800)])
+def test_delta_mode_other_shift_ranges_and_engines(small_genome, dtype, cta_group, maxshift):
+    """Delta mode (conv patches + FC1 slice reuse) for 5 / 11 shifts, single-CTA tiles and bf16 operands."""
+    from expecto_b200 import synth
+    from expecto_b200.engine import BelugaEngine
+    from expecto_b200.windows import chromatin_delta_descs
+    eng = BelugaEngine(0, dtype=dtype, cta_group=cta_group, capacity=512)
+    eng.load_state_dict(synth.make_beluga_weights(0, round_dtype=dtype))
+    pg = PackedGenome.from_sequences(small_genome)
+    eng.set_genome(pg)
+    rows = _substitutions(small_genome, 30)
+    chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    n = len(rows)
+    seg_len = 2000 + 2 * maxshift
+    rd, pd, codes, k_of, row0, plen = chromatin_delta_descs(pg, chroms, pos, refs, alts, maxshift)
+    cap = eng.segment_capacity(seg_len) // 2
+    assert cap >= 8
+    m = min(n, cap)
+    delta = eng.forward_segments_delta(rd[:2 * m], pd[:2 * m], codes, m, seg_len, plen, row0, k_of, shift_major=True)
+    for si, shift in enumerate(chromatin_shift_list(maxshift)):
+        wd, wcodes = chromatin_window_descs(pg, chroms[:m], pos[:m], refs[:m], alts[:m], shift)
+        assert torch.equal(delta[si], eng.forward_windows(wd, wcodes).reshape(m, 4, 2002)), shift
+    eng.close()
+
+
 def test_segment_loop_with_and_without_delta_is_identical(engine, small_genome):
     """The pipelined chromatin loop: a mix of substitutions, indels and window-path variants gives the same slabs
     whether substitutions take the patch path or not."""
