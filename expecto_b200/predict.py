@@ -181,10 +181,21 @@ def _table_text(df) -> str:
     except ImportError:
         return df.to_csv(None, header=True, sep="\t", index=False)
     base = df[cols[:n_ref]].to_csv(None, header=True, sep="\t", index=False).split("\n")
-    buf = io.BytesIO()
-    pc.write_csv(pa.Table.from_pandas(df[extra], preserve_index=False), buf,
-                 pc.WriteOptions(include_header=False, delimiter="\t"))
-    more = buf.getvalue().decode("ascii").split("\n")
+    values = [df[c].to_numpy() for c in extra]
+
+    def block(ab):  # Arrow releases the GIL: row blocks are formatted on several threads
+        a, b = ab
+        tb = pa.Table.from_arrays([pa.array(v[a:b], from_pandas=True) for v in values], names=[str(c) for c in extra])
+        buf = io.BytesIO()
+        pc.write_csv(tb, buf, pc.WriteOptions(include_header=False, delimiter="\t"))
+        return buf.getvalue()
+
+    n_threads = max(1, min(8, os.cpu_count() or 1))
+    edges = np.linspace(0, len(df), 2 * n_threads + 1).astype(np.int64)
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(n_threads) as ex:
+        parts = list(ex.map(block, [(int(a), int(b)) for a, b in zip(edges[:-1], edges[1:]) if b > a]))
+    more = b"".join(parts).decode("ascii").split("\n")
     if len(base) != len(df) + 2 or len(more) != len(df) + 1:
         return df.to_csv(None, header=True, sep="\t", index=False)
     head = base[0] + "\t" + "\t".join(str(c) for c in extra)
