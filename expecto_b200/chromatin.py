@@ -308,7 +308,7 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
     shifts = shift_list(maxshift)
     S = len(shifts)
     seg_len = 2000 + 2 * maxshift
-    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts]) if n else np.zeros(0, bool)
+    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts], maxshift) if n else np.zeros(0, bool)
     elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)
     cap = max(1, min(engine.segment_capacity(seg_len) // 4, max(1, len(elig))))
     n_sets = 3  # one being filled by the GPU, one waiting to be handed over, one being written
@@ -404,7 +404,7 @@ def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, 
     seg_len = 2000 + 2 * maxshift
     outs = {s: tuple(torch.empty((2 * n, 2002), dtype=torch.float32, device=engine.device) for _ in range(3))
             for s in shifts}
-    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts]) if n else np.zeros(0, bool)
+    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts], maxshift) if n else np.zeros(0, bool)
     elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)
     cap = max(1, engine.segment_capacity(seg_len) // 4)
 
@@ -445,7 +445,7 @@ def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, 
     seg_len = 2000 + 2 * maxshift
     out = {k: torch.empty((S, n, 2002), dtype=torch.float32, device=engine.device) for k in ("ref", "alt", "diff")}
     use_segments = maxshift % 200 == 0
-    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts]) if (n and use_segments) else np.zeros(n, bool)
+    ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts], maxshift) if (n and use_segments) else np.zeros(n, bool)
     elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)
     if len(elig):
         cap = max(1, engine.segment_capacity(seg_len) // 4)

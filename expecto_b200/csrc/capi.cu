@@ -982,8 +982,6 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
   for (int i = 0; i < n_shifts; ++i) dd.si_of_k[sg.k_of_shift[i]] = i;
   for (int k = 0; k < n_shifts; ++k) {
     if (dd.si_of_k[k] < 0) return fail(BX_E_ARG, "k_of_shift is not a permutation (offset %d missing)", k);
-    const DeltaClass cl = delta_class(dd, k);
-    if (cl.lo >= cl.hi) return fail(BX_E_ARG, "the patch does not reach the window at offset %d", k);
   }
   const size_t n_half = (size_t)ng * n_shifts * 2;   // ref windows of the chunk = alt windows of the chunk
   const size_t ref_bytes = (size_t)kFc1Splits * n_half * 2048 * sizeof(float);
@@ -1043,10 +1041,11 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
       int lo = kFc1Splits, hi = -1;
       for (int cls = (int)(first / (2 * (size_t)ng)); cls <= (int)(last / (2 * (size_t)ng)); ++cls) {
         const DeltaClass cl = delta_class(dd, cls);
+        if (cl.lo >= cl.hi) continue;  // the patch does not reach this window: every slice comes from the ref window
         lo = std::min(lo, cl.ks_lo); hi = std::max(hi, cl.ks_hi);
       }
-      ranges.tile_lo[t] = (unsigned char)lo;
-      ranges.tile_n[t] = (unsigned char)(hi - lo + 1);
+      ranges.tile_lo[t] = (unsigned char)(hi < lo ? 0 : lo);
+      ranges.tile_n[t] = (unsigned char)(hi < lo ? 0 : hi - lo + 1);
     }
     {
       StageTimer t(c, 7, st);

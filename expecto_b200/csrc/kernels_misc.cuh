@@ -299,6 +299,10 @@ __host__ __device__ inline DeltaClass delta_class(const DeltaDense& g, int c) {
   const int valid = (c & 1) ? g.valid_b : g.valid_a;
   r.lo = g.row0 - r.off < 0 ? 0 : g.row0 - r.off;
   r.hi = g.row0 - r.off + valid > 106 ? 106 : g.row0 - r.off + valid;
+  if (r.lo >= r.hi) {  // the patch does not reach this window: no slice of its own
+    r.lo = r.hi = 0; r.ks_lo = 1; r.ks_hi = 0;
+    return r;
+  }
   r.ks_lo = r.lo * 10 / g.kb_per_split;
   r.ks_hi = (r.hi * 10 - 1) / g.kb_per_split;
   return r;
@@ -336,6 +340,7 @@ gather_fc1_delta_kernel(const T* __restrict__ act6a, const T* __restrict__ act6b
     return;
   }
   const uint4* p4 = reinterpret_cast<const uint4*>((pb ? patch6b : patch6a) + (size_t)seg * g.p6p * 640);
+  if (cl.ks_lo > cl.ks_hi) return;                               // nothing of this window is recomputed
   const int plo = g.row0 - cl.off;                               // window row of patch row 0
   const int r_lo = cl.ks_lo * g.kb_per_split / 10;               // conv6 rows the computed slices read
   int r_hi = ((cl.ks_hi + 1) * g.kb_per_split + 9) / 10;

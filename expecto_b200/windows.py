@@ -57,8 +57,15 @@ def variant_descs(genome: PackedGenome, chroms, pos, ref_len: np.ndarray, allele
     half = int(windowsize / 2 - 1)                       # 1049
     mutpos = int(windowsize / 2 - 1 - shift)             # chromatin.py:203
     s0 = coff + pos + shift - half - 1                   # global index of seq[0] (1-based start -> 0-based)
-    len_p = np.full(n, mutpos, dtype=np.int64)           # seq[:mutpos]
-    len_s = np.maximum(0, windowsize - mutpos - ref_len)  # seq[mutpos+len(ref):]
+    # Python slice semantics of seq[:mutpos] and seq[mutpos+len(ref):] on the 2100-character fetch, chromatin.py:209:
+    # beyond |shift| = 1049 the variant lies outside the fetch, mutpos goes negative (counts from the end) or past the
+    # end, and the reference still splices the alleles in at that accidental place
+    def norm(x):
+        x = np.asarray(x, dtype=np.int64)
+        return np.where(x < 0, np.maximum(0, windowsize + x), np.minimum(x, windowsize))
+    len_p = np.full(n, int(norm(mutpos)), dtype=np.int64)  # seq[:mutpos]
+    suffix0 = norm(mutpos + ref_len)                         # first character of seq[mutpos+len(ref):]
+    len_s = windowsize - suffix0
     total = len_p + la + len_s
     a, b = crop_bounds(total, inputsize)
     d = np.zeros(n, dtype=DESC_DTYPE)
@@ -70,7 +77,7 @@ def variant_descs(genome: PackedGenome, chroms, pos, ref_len: np.ndarray, allele
     d["aoff"] = np.asarray(allele_off, dtype=np.int64) + al_lo
     s_lo, s_hi = np.clip(a - len_p - la, 0, len_s), np.clip(b - len_p - la, 0, len_s)
     d["len2"] = np.maximum(0, s_hi - s_lo)
-    d["g2"] = s0 + mutpos + ref_len + s_lo
+    d["g2"] = s0 + suffix0 + s_lo
     d["flags"] = 1 if rc else 0
     return d
 
@@ -162,14 +169,19 @@ def chromatin_shift_list(maxshift: int) -> list[int]:
     return [0] + list(range(-200, -maxshift - 1, -200)) + list(range(200, maxshift + 1, 200))  # chromatin.py:243
 
 
-def segment_eligible(ref_len: np.ndarray, alt_len: np.ndarray) -> np.ndarray:
+def segment_eligible(ref_len: np.ndarray, alt_len: np.ndarray, maxshift: int = 800) -> np.ndarray:
     """Variants whose 2*maxshift/200+1 shifted windows are all plain 2000-bp substrings of one spliced sequence:
-    the centre crop must start inside the left flank for both alleles (deletions of at most 100 bp, chromatin.py:164)
-    and the right flank must exist at every shift (len(ref) <= 250, chromatin.py:209).  The rest (rare, long
-    indels) go through the per-window path, which follows the reference's Python slice semantics literally."""
+    the centre crop must start inside the left flank for both alleles (deletions of at most 100 bp, chromatin.py:164),
+    the variant must lie inside the 2100-bp fetch at every shift (maxshift <= 1000: mutpos = 1049 - shift >= 0,
+    chromatin.py:203) and the right flank must exist at every shift (len(ref) <= 1050 - maxshift, i.e. 250 for the
+    default range, chromatin.py:209).  The rest (rare long indels, exotic shift ranges) go through the per-window
+    path, which follows the reference's Python slice semantics literally."""
     ref_len = np.asarray(ref_len, dtype=np.int64)
     alt_len = np.asarray(alt_len, dtype=np.int64)
-    return (ref_len <= 250) & (alt_len - ref_len >= -100) & (alt_len <= 1000) & (ref_len >= 1) & (alt_len >= 0)
+    if maxshift > 1000:
+        return np.zeros(ref_len.shape, dtype=bool)
+    return (ref_len <= 1050 - maxshift) & (alt_len - ref_len >= -100) & (alt_len <= 1000) & (ref_len >= 1) & \
+        (alt_len >= 0)
 
 
 def _allele_segment(genome, coff, pos, ref_len, la, aoff, maxshift, rc):
@@ -198,7 +210,7 @@ def chromatin_segment_descs(genome: PackedGenome, chroms, pos, refs: list[str], 
     tab = AlleleTable(list(refs) + list(alts))
     rl, al = tab.lengths[:n], tab.lengths[n:]
     ro, ao = tab.offsets[:n], tab.offsets[n:]
-    if not np.all(segment_eligible(rl, al)):
+    if not np.all(segment_eligible(rl, al, maxshift)):
         raise ValueError("chromatin_segment_descs needs variants pre-filtered with segment_eligible")
     pos = np.asarray(pos, dtype=np.int64)
     coff = np.fromiter((genome.offsets[c] for c in chroms), dtype=np.int64, count=n)

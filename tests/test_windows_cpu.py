@@ -46,7 +46,10 @@ def test_descriptors_match_oracle_all_shifts(small_genome):
     chroms = [r[0] for r in rows]
     pos = np.array([r[1] for r in rows])
     refs, alts = [r[3] for r in rows], [r[4] for r in rows]
-    for shift in O.SHIFTS_CHROMATIN(800):
+    # the default range, then shifts around and beyond +-1049, where the variant leaves the 2100-bp fetch and the
+    # reference's splice follows Python's negative / past-the-end slice semantics (chromatin.py:203-209)
+    for shift in list(O.SHIFTS_CHROMATIN(800)) + [1000, -1000, 1040, 1049, 1050, 1051, 1200, 2000, -1049, -1050, -1051,
+                                                   -1100, -1200, -2000, 3000, -3000]:
         descs, codes = chromatin_window_descs(pg, chroms, pos, refs, alts, shift)
         ours = decode_descs(pg, descs, codes).reshape(len(rows), 4, 4, 2000)
         seqs = [O.fetch_seqs(dg, c, int(p), r, a, shift=shift) for c, p, r, a in zip(chroms, pos, refs, alts)]
@@ -91,26 +94,31 @@ def test_invalid_genome_char_detected():
         check_valid_bases(pg, d_bad)
 
 
-def test_segment_descriptors_cover_every_shifted_window(small_genome):
+@pytest.mark.parametrize("maxshift", [800, 1000, 400])
+def test_segment_descriptors_cover_every_shifted_window(small_genome, maxshift):
     """Segment mode: each window of every shift is the 2000-bp slice at offset 200*k of its segment."""
     from expecto_b200.windows import chromatin_segment_descs, chromatin_shift_list, segment_eligible
     rows = GI.edge_variants(small_genome)
-    ok = segment_eligible([len(r[3]) for r in rows], [len(r[4]) for r in rows])
+    ok = segment_eligible([len(r[3]) for r in rows], [len(r[4]) for r in rows], maxshift)
     assert 0 < ok.sum() < len(rows)            # the 120-bp deletion etc. are not eligible
     assert not ok[[r[2] for r in rows].index("del120")] and ok[[r[2] for r in rows].index("ins150")]
+    assert not segment_eligible([1, 60], [1, 1], 1200).any()          # variant outside the fetch at +-1200
+    assert list(segment_eligible([1, 50, 51], [1, 1, 1], 1000)) == [True, True, False]   # right flank at shift -1000
     rows = [r for r, e in zip(rows, ok) if e]
     pg = PackedGenome.from_sequences(small_genome)
     chroms, pos = [r[0] for r in rows], np.array([r[1] for r in rows])
     refs, alts = [r[3] for r in rows], [r[4] for r in rows]
-    sdescs, scodes, k_of = chromatin_segment_descs(pg, chroms, pos, refs, alts, 800)
-    seg = decode_descs(pg, sdescs, scodes, length=3600).reshape(len(rows), 4, 4, 3600)
-    for si, shift in enumerate(chromatin_shift_list(800)):
+    S = 2 * maxshift // 200 + 1
+    L = 2000 + 2 * maxshift
+    sdescs, scodes, k_of = chromatin_segment_descs(pg, chroms, pos, refs, alts, maxshift)
+    seg = decode_descs(pg, sdescs, scodes, length=L).reshape(len(rows), 4, 4, L)
+    for si, shift in enumerate(chromatin_shift_list(maxshift)):
         wdescs, wcodes = chromatin_window_descs(pg, chroms, pos, refs, alts, shift)
         win = decode_descs(pg, wdescs, wcodes).reshape(len(rows), 4, 4, 2000)
         k = int(k_of[si])
-        assert k == (shift + 800) // 200
+        assert k == (shift + maxshift) // 200
         for q in range(4):
-            off = 200 * (8 - k) if q % 2 else 200 * k
+            off = 200 * (S - 1 - k) if q % 2 else 200 * k
             assert np.array_equal(win[:, q], seg[:, q, :, off:off + 2000]), (shift, q)
 
 
