@@ -12,6 +12,7 @@ GBLINEAR_SEED = 5
 SMALL_CONTIGS = [("chr1", 60000), ("chr2", 40000), ("chrX", 30000)]
 SMALL_GENOME_SEED = 11
 ENCODE_SHIFTS = [0, -800, 800, 200]
+EXTREME_SHIFTS = [1000, -1000, 1040, 1049, 1050, 1051, 1200, 2000, -1049, -1050, -1051, -1100, -1200, -2000, 3000, -3000]
 CFG1_KEEP_SHIFTS = [0, 800]
 CFG1_CONTIGS = [("chr1", 11_200_000), ("chr2", 50_000), ("chrX", 50_000)]
 

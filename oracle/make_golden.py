@@ -68,6 +68,14 @@ def stage_encode():
             assert r.dtype == np.bool_ and np.array_equal(r, o), "encodeSeqs restatement differs"
             packed.append(np.packbits(r.reshape(r.shape[0], -1), axis=1))
             meta.append((shift, name))
+    # shifts at and beyond +-1049, where the variant leaves the 2100-bp fetch and fetchSeqs' splice index goes negative
+    # or past the end (Python slice semantics): the restatement must follow the reference there too (no fixture;
+    # tests/test_windows_cpu.py checks the descriptors against the oracle at the same shifts)
+    for shift in GI.EXTREME_SHIFTS:
+        for chrom, pos, _id, ref, alt in rows:
+            a = ref_fetch(chrom, pos, ref, alt, shift=shift)
+            assert a == O.fetch_seqs(g, chrom, pos, ref, alt, shift=shift), ("fetchSeqs restatement differs", shift)
+            assert np.array_equal(ref_encode([a[0], a[1]]), O.encode_seqs([a[0], a[1]]))
     # odd-length / short strings straight into the encoder (crop arithmetic, chromatin.py:164)
     rng = np.random.default_rng(5)
     odd = [synth.random_sequence(rng, n) for n in (2000, 2001, 2099, 2100, 2101, 2103, 2110, 1990, 1999)]
