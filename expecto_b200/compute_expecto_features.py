@@ -115,18 +115,38 @@ def gene_features(engine, genome, genes, shifts, weights, genes_per_batch: int =
     return out
 
 
+def gather_features(local: np.ndarray, n_total: int, device=None):
+    """Per-rank float64 [n_local, 20020] blocks (contiguous gene shards in rank order) -> the full matrix on rank 0,
+    None elsewhere.  The values are float32 results widened to float64 (as the reference's ``np.sum`` over float64
+    weights stores them), so they travel as float32 — half the bytes over NVLink — and are widened again on rank 0."""
+    import torch
+
+    from . import shard
+
+    t = torch.from_numpy(np.ascontiguousarray(local, dtype=np.float32))
+    if device is not None:
+        t = t.to(device)
+    full = shard.gather_rows(t, n_total)
+    return None if full is None else full.cpu().numpy().astype(np.float64)
+
+
 def run(args, engine=None, genome=None) -> str:
+    """The whole script.  Under torchrun (one process per GPU) the genes are split into contiguous per-rank shards
+    (expecto_b200/shard.py: no collective on the forward path), the feature rows are gathered on rank 0 over NCCL and
+    rank 0 writes the ``.npy``."""
+    from . import shard
     from .genome import PackedGenome
     from .transform import TSS_SHIFTS, fixed_pos_weights
 
     if args.windowsize != 2000:
         raise ValueError("Beluga's architecture fixes --windowsize at 2000 (Beluga.py:43)")
+    rank, world, local = shard.init_distributed()
     os.makedirs(args.out_dir, exist_ok=True)
     if genome is None:
         genome = PackedGenome.from_fasta(args.genome)
     if engine is None:
         from .engine import BelugaEngine
-        engine = BelugaEngine(args.device, dtype=args.dtype, capacity=4096)
+        engine = BelugaEngine(local if world > 1 else args.device, dtype=args.dtype, capacity=4096)
         engine.load_weights_file(args.weights)
     if engine._genome is not genome:
         engine.set_genome(genome)
@@ -134,10 +154,15 @@ def run(args, engine=None, genome=None) -> str:
     missing = sorted({g[1] for g in genes if g[1] not in genome.offsets})
     if missing:
         raise KeyError(f"contig(s) {missing} are not in the genome")
-    feats = gene_features(engine, genome, genes, TSS_SHIFTS, fixed_pos_weights(TSS_SHIFTS), args.genes_per_batch,
+    lo, hi = shard.shard_range(len(genes), rank, world)
+    feats = gene_features(engine, genome, genes[lo:hi], TSS_SHIFTS, fixed_pos_weights(TSS_SHIFTS), args.genes_per_batch,
                           mode=args.mode)
+    if world > 1:
+        feats = gather_features(feats, len(genes), getattr(engine, "device", None))
     path = f"{args.out_dir}/Xreducedall.2002.representative_tss_top"
-    np.save(path, feats)
+    if rank == 0:
+        np.save(path, feats)
+    shard.barrier()
     return path + ".npy"
 
 

@@ -82,3 +82,41 @@ def test_attach_rejects_mismatched_file(tmp_path):
     hdf5.H5Writer(p, {"diff": (4, F)}).close()
     with pytest.raises(ValueError):
         hdf5.H5Writer(p, {"diff": (6, F)}, create=False)
+
+
+def _features_worker(rank, world, port, n_genes, tmp):
+    """compute_expecto_features.run under two gloo ranks with the GPU part stubbed: gene shards, gather, one .npy."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from expecto_b200 import compute_expecto_features as cef
+
+    genes = [(f"ENSG{i:05d}", "chr1", 1000 + 37 * i, 1 if i % 2 else -1) for i in range(n_genes)]
+
+    def fake_features(engine, genome, part, shifts, weights, genes_per_batch, mode="segments"):
+        tss = np.array([g[2] for g in part], dtype=np.float64)
+        return (tss[:, None] + np.arange(20020, dtype=np.float64)[None, :] / 32).astype(np.float32).astype(np.float64)
+
+    class Genome:
+        offsets = {"chr1": 0}
+
+    class Engine:
+        device = None
+        _genome = None
+
+    g, e = Genome(), Engine()
+    e._genome = g
+    cef.gene_features = fake_features
+    cef.read_genes = lambda a, t, h=False: genes
+    shard.init_distributed("gloo")
+    args = cef.build_parser().parse_args(["anno.csv", "tss.tsv", "-o", tmp])
+    path = cef.run(args, engine=e, genome=g)
+    if rank == 0:
+        got = np.load(path)
+        assert got.dtype == np.float64 and got.shape == (n_genes, 20020)
+        assert np.array_equal(got, fake_features(None, None, genes, None, None, 0))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_genes", [5, 1])
+def test_two_rank_feature_shards_gather_to_one_file(tmp_path, n_genes):
+    mp.spawn(_features_worker, args=(2, _free_port(), n_genes, str(tmp_path)), nprocs=2, join=True)
