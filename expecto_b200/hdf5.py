@@ -30,12 +30,26 @@ def _msg(mtype: int, data: bytes, flags: int = 0) -> bytes:
     return struct.pack("<HHB3x", mtype, len(data), flags) + data
 
 
-def _dataset_header(shape, data_addr: int, nbytes: int, mtime: int) -> bytes:
+def _datatype_message(dtype: np.dtype) -> bytes:
+    """Datatype message body for the three element types the pipeline stores: float32 (chromatin.py:282-286),
+    float64 (``chromatin_preds``, geuvadis_predict_consensus.py:128) and fixed-length byte strings (numpy ``S<n>``,
+    ``record_ids`` :129 — h5py maps them to null-padded ASCII strings)."""
+    if dtype == np.dtype("<f4"):
+        # IEEE little-endian float32: class 1 version 1; bit fields 0x20,0x1f,0x00; size 4;
+        # bit offset 0, precision 32, exp loc 23, exp size 8, mantissa loc 0, mantissa size 23, bias 127
+        return struct.pack("<BBBBI", 0x11, 0x20, 0x1F, 0x00, 4) + struct.pack("<HHBBBBI", 0, 32, 23, 8, 0, 23, 127)
+    if dtype == np.dtype("<f8"):
+        return struct.pack("<BBBBI", 0x11, 0x20, 0x3F, 0x00, 8) + struct.pack("<HHBBBBI", 0, 64, 52, 11, 0, 52, 1023)
+    if dtype.kind == "S" and dtype.itemsize > 0:
+        # class 3 (string) version 1; bit field 0: padding = 1 (null pad), character set = 0 (ASCII); no properties
+        return struct.pack("<BBBBI", 0x13, 0x01, 0x00, 0x00, dtype.itemsize)
+    raise ValueError(f"unsupported HDF5 element type {dtype}")
+
+
+def _dataset_header(shape, data_addr: int, nbytes: int, mtime: int, dtype=np.dtype("<f4")) -> bytes:
     rank = len(shape)
     dataspace = struct.pack("<BBB5x", 1, rank, 1) + b"".join(struct.pack("<Q", d) for d in shape) * 2
-    # IEEE little-endian float32: class 1 version 1; bit fields 0x20,0x1f,0x00; size 4;
-    # bit offset 0, precision 32, exp loc 23, exp size 8, mantissa loc 0, mantissa size 23, bias 127
-    datatype = struct.pack("<BBBBI", 0x11, 0x20, 0x1F, 0x00, 4) + struct.pack("<HHBBBBI", 0, 32, 23, 8, 0, 23, 127)
+    datatype = _datatype_message(np.dtype(dtype))
     fill = struct.pack("<BBBBI", 2, 2, 2, 1, 0)
     layout = struct.pack("<BBQQ", 3, 1, data_addr, nbytes)
     mt = struct.pack("<B3xI", 1, mtime & 0xFFFFFFFF)
@@ -48,12 +62,13 @@ def _dataset_header(shape, data_addr: int, nbytes: int, mtime: int) -> bytes:
 
 
 class H5Writer:
-    """Write float32 datasets (<= 8, names sorted as HDF5 requires) into one v0-superblock file.
+    """Write datasets (<= 8, names sorted as HDF5 requires; float32 unless ``dtypes`` says float64 or ``S<n>``) into
+    one v0-superblock file.
 
     ``create(name, shape)`` reserves space; ``write_rows(name, row0, array)`` pwrite()s row slabs, so several
     producers (GPU ranks, pipeline stages) can fill one contiguous dataset without an in-memory copy."""
 
-    def __init__(self, path: str, datasets: dict[str, tuple[int, ...]], create: bool = True):
+    def __init__(self, path: str, datasets: dict[str, tuple[int, ...]], create: bool = True, dtypes=None):
         """``create=False`` attaches to a file another process already created with the same datasets (a GPU
         rank writing its own row slab; the layout is a pure function of the dataset shapes)."""
         if not 1 <= len(datasets) <= 2 * _LEAF_K:
@@ -61,10 +76,13 @@ class H5Writer:
         self.path = path
         self.names = sorted(datasets)
         self.shapes = {n: tuple(int(x) for x in datasets[n]) for n in self.names}
+        self.dtypes = {n: np.dtype((dtypes or {}).get(n, "<f4")) for n in self.names}
+        for n in self.names:
+            _datatype_message(self.dtypes[n])
         self.addr, off = {}, _DATA_START
         for n in self.names:
             self.addr[n] = off
-            off += int(np.prod(self.shapes[n])) * 4
+            off += int(np.prod(self.shapes[n])) * self.dtypes[n].itemsize
             off += (-off) % 8
         self.eof = off
         if create:
@@ -120,22 +138,23 @@ class H5Writer:
             sn += struct.pack("<QQII16x", name_off[n], hdr_addr[n], 0, 0)
         out[snod_addr:snod_addr + len(sn)] = sn
         for n in self.names:
-            nbytes = int(np.prod(self.shapes[n])) * 4
-            h = _dataset_header(self.shapes[n], self.addr[n], nbytes, mtime)
+            nbytes = int(np.prod(self.shapes[n])) * self.dtypes[n].itemsize
+            h = _dataset_header(self.shapes[n], self.addr[n], nbytes, mtime, self.dtypes[n])
             out[hdr_addr[n]:hdr_addr[n] + len(h)] = h
         return bytes(out)
 
     def write_rows(self, name: str, row0: int, arr: np.ndarray) -> None:
         shape = self.shapes[name]
-        arr = np.ascontiguousarray(arr, dtype="<f4")
+        dt = self.dtypes[name]
+        arr = np.ascontiguousarray(arr, dtype=dt)
         row_elems = int(np.prod(shape[1:])) if len(shape) > 1 else 1
         if arr.size % row_elems or row0 * row_elems + arr.size > int(np.prod(shape)):
             raise ValueError("slab does not fit the dataset")
         if arr.size == 0:
             return
         # positional writes: no shared file offset, so slabs can be written from several threads at once
-        mv = memoryview(arr.reshape(-1)).cast("B")
-        off, fd = self.addr[name] + row0 * row_elems * 4, self._f.fileno()
+        mv = memoryview(arr.reshape(-1).view(np.uint8))
+        off, fd = self.addr[name] + row0 * row_elems * dt.itemsize, self._f.fileno()
         while len(mv):
             k = os.pwrite(fd, mv[:1 << 30], off)
             mv, off = mv[k:], off + k
@@ -158,8 +177,12 @@ class H5Writer:
 
 
 def write_datasets(path: str, arrays: dict[str, np.ndarray]) -> None:
-    """``h5py.File(path,'w'); create_dataset(name, data=...)`` for float32 arrays (chromatin.py:282-286)."""
-    with H5Writer(path, {k: v.shape for k, v in arrays.items()}) as w:
+    """``h5py.File(path,'w'); create_dataset(name, data=...)`` (chromatin.py:282-286; geuvadis_predict_consensus.py:
+    127-133).  float64 and ``S<n>`` arrays keep their type; everything else is stored as float32."""
+    arrays = {k: np.asarray(v) for k, v in arrays.items()}
+    dtypes = {k: (v.dtype if v.dtype == np.float64 or (v.dtype.kind == "S" and v.dtype.itemsize) else np.dtype("<f4"))
+              for k, v in arrays.items()}
+    with H5Writer(path, {k: v.shape for k, v in arrays.items()}, dtypes=dtypes) as w:
         for k, v in arrays.items():
             w.write(k, v)
 
@@ -198,7 +221,9 @@ class H5Dataset:
 
     def __array__(self, dtype=None, copy=None):
         a = np.asarray(self._map())
-        return a.astype(dtype) if dtype is not None else a
+        if dtype is not None and np.dtype(dtype) != a.dtype:
+            return a.astype(dtype)
+        return a.copy() if copy else a
 
 
 class H5File:
@@ -296,6 +321,8 @@ class H5File:
                 elif cls == 0:
                     signed = (data[1] >> 3) & 1
                     dtype = (">" if big else "<") + ("i" if signed else "u") + str(size)
+                elif cls == 3:
+                    dtype = "S%d" % size
             elif mtype == 8:
                 if data[0] != 3 or data[1] != 1:
                     raise ValueError("only contiguous (layout v3 class 1) datasets are supported")

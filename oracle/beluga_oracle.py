@@ -171,3 +171,67 @@ def gblinear_predict(features, weights, bias, base_score=0.0):
     """xgboost 0.7 gblinear Booster.predict (predict.py:150-160; dump layout predict_by_cluster.py:73-75):
     base_score + bias + w . x  (xgboost==0.7.post4 is a pinned third-party dependency, requirements.txt:38)."""
     return base_score + bias + np.asarray(features) @ np.asarray(weights)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# SURVEY §8f rank 4: consensus-sequence front end (geuvadis_predict_consensus.py) and per-gene prediction dumps
+# (replicate_expecto_features.py).  Pinned by oracle/make_golden.py stage_consensus / stage_replicate.
+ENFORMER_SEQ_LENGTH = 393216  # geuvadis_predict_consensus.py:23
+
+
+def consensus_pad(record_id, seq):
+    """gen_sample_seqs_and_id_for_gene, geuvadis_predict_consensus.py:143-167: upper-case; a record whose interval
+    starts with ``-`` is missing its beginning (N-padded in front), otherwise a short record is N-padded at the end."""
+    seq = seq.upper()
+    interval = record_id.split(":")[1]
+    if interval.startswith("-"):
+        bp_start = -int(interval.split("-")[-2])
+        bp_end = int(interval.split("-")[-1])
+        assert bp_end - bp_start + 1 == ENFORMER_SEQ_LENGTH
+        seq = "N" * (ENFORMER_SEQ_LENGTH - len(seq)) + seq
+    else:
+        bp_start, bp_end = map(int, interval.split("-"))
+        assert bp_end - bp_start + 1 == ENFORMER_SEQ_LENGTH
+        if len(seq) < ENFORMER_SEQ_LENGTH:
+            seq = seq + "N" * (ENFORMER_SEQ_LENGTH - len(seq))
+    assert len(seq) == ENFORMER_SEQ_LENGTH
+    return seq
+
+
+def consensus_seq_shifts(sample_seq, strand, shifts, windowsize=INPUTSIZE):
+    """get_seq_shifts_for_sample_seq, geuvadis_predict_consensus.py:210-243: TSS at ``len // 2``; ``strand`` '+'/'-'."""
+    tss_i = len(sample_seq) // 2
+    sgn = {"+": 1, "-": -1}[strand]
+    out = []
+    for shift in shifts:
+        seq = sample_seq[tss_i + (shift * sgn) - int(windowsize / 2 - 1): tss_i + (shift * sgn) + int(windowsize / 2) + 1]
+        assert len(seq) == windowsize
+        out.append(seq)
+    return out
+
+
+def consensus_chromatin(sample_seq, strand, sd, shifts, chunk=50):
+    """geuvadis_predict_consensus.py:91-103 for one record: encodeSeqs (forward windows then their reverse
+    complements), Beluga, the two halves averaged in float64 -> [len(shifts), 2002]."""
+    enc = encode_seqs(consensus_seq_shifts(sample_seq, strand, shifts)).astype(np.float32)
+    p = np.zeros((enc.shape[0], 2002))
+    for i in range(0, enc.shape[0], chunk):
+        p[i:i + chunk] = beluga_forward(enc[i:i + chunk], sd)
+    return (p[:p.shape[0] // 2] + p[p.shape[0] // 2:]) / 2
+
+
+def consensus_features(preds, shifts=None):
+    """geuvadis_predict_consensus.py:108-124: float64 [n, 20030] (zero column in front of each basis function)."""
+    pw = fixed_pos_weights(shifts)
+    features = np.sum(pw[None, :, :, None] * np.asarray(preds)[:, None, :, :], axis=2)
+    return np.concatenate([np.zeros((features.shape[0], 10, 1)), features], axis=2).reshape((-1, 20030))
+
+
+def replicate_prediction(genome, chrom, tss, strand, sd, shifts=None, chunk=50):
+    """replicate_expecto_features.py:65-83: float32 [S,2002] = 0.5 * (prediction + rc prediction)."""
+    enc = encode_seqs(tss_windows(genome, chrom, tss, strand, shifts), concat_rc=False)
+    fwd_in = enc.astype(np.float32)
+    rc_in = np.ascontiguousarray(enc[:, ::-1, ::-1]).astype(np.float32)
+    fwd = np.vstack([beluga_forward(fwd_in[i:i + chunk], sd) for i in range(0, len(fwd_in), chunk)])
+    rc = np.vstack([beluga_forward(rc_in[i:i + chunk], sd) for i in range(0, len(rc_in), chunk)])
+    return 0.5 * (fwd + rc)

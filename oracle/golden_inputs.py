@@ -83,3 +83,68 @@ def cfg1_edge_variants(genome):
 def cfg4_genes():
     """[gene id, chrom, strand, CAGE_representative_TSS] for the compute_expecto_features run (>= 21 kb from ends)."""
     return [["ENSG_T1", "chr1", "+", 5_000_000], ["ENSG_T2", "chr1", "-", 7_654_321]]
+
+
+# --- consensus front end (geuvadis_predict_consensus.py) -------------------------------------------------------
+CONSENSUS_LEN = 393216
+CONSENSUS_KEEP_SHIFTS = [0, 37, 66, 99, 100, 101, 133, 170, 199]   # shift indices stored in the fixture
+CONSENSUS_FEATURE_STEP = 7                                          # every 7th chromatin feature stored
+CONSENSUS_MODEL_SEED = 9
+# genes file rows (ens_id, chrom, bp, gene_symbol, strand); the second gene has no symbol -> its directory is
+# the lower-cased ens_id (geuvadis_predict_consensus.py:62)
+CONSENSUS_GENES = [["ENSG00000000011", "chr1", 1_200_000, "Abc1", "+"], ["ENSG00000000002", "chr2", 900_000, "", "-"]]
+
+
+def consensus_records(gene_index: int):
+    """{file stem: [(record id, sequence as stored in the FASTA)]} for one gene: a full-length record, one missing its
+    end (N-padded at the end by the reference), one missing its beginning (interval starting with '-', N-padded in
+    front) — the truncations reach into the +-21 kb the windows read.  Individuals differ from the gene's base
+    sequence by 60 substitutions near the TSS."""
+    rng = np.random.default_rng(100 + gene_index)
+    base = np.frombuffer(synth.random_sequence(rng, CONSENSUS_LEN).encode(), dtype=np.uint8)
+    chrom = CONSENSUS_GENES[gene_index][1]
+
+    def individual(k):
+        r = np.random.default_rng(1000 * gene_index + k)
+        s = base.copy()
+        at = CONSENSUS_LEN // 2 + r.integers(-21000, 21000, size=60)
+        s[at] = np.frombuffer(b"ACGT", dtype=np.uint8)[r.integers(0, 4, size=60)]
+        return s.tobytes().decode()
+
+    start = 500_000 + 1000 * gene_index
+    full_id = f"{chrom}:{start}-{start + CONSENSUS_LEN - 1}"
+    out = {"HG001": [(full_id, individual(0))]}
+    if gene_index == 0:
+        out["HG002"] = [(full_id, individual(1)[:210_000])]
+        out["NA003"] = [(f"{chrom}:-5000-{CONSENSUS_LEN - 5001}", individual(2)[190_000:]), (full_id, individual(3))]
+    else:
+        out["HG010"] = [(full_id, individual(1)[:CONSENSUS_LEN - 7])]
+    return out
+
+
+def write_consensus_dir(root: str):
+    """{root}/consensus/{gene}/samples/{stem}.fa + {root}/genes.csv; returns (consensus_dir, genes_file, gene names)."""
+    import os
+    names = []
+    for gi, row in enumerate(CONSENSUS_GENES):
+        gene = (row[3] or row[0]).lower()
+        names.append(gene)
+        d = os.path.join(root, "consensus", gene, "samples")
+        os.makedirs(d, exist_ok=True)
+        for stem, recs in consensus_records(gi).items():
+            with open(os.path.join(d, stem + ".fa"), "w") as f:
+                for rid, seq in recs:
+                    f.write(f">{rid} sample={stem}\n")
+                    for i in range(0, len(seq), 80):
+                        f.write(seq[i:i + 80] + "\n")
+    genes_file = os.path.join(root, "genes.csv")
+    with open(genes_file, "w") as f:
+        for row in CONSENSUS_GENES:
+            f.write(",".join(str(x) for x in row) + "\n")
+    return os.path.join(root, "consensus"), genes_file, names
+
+
+def consensus_model():
+    """Seeded gblinear model over the 20030-wide legacy layout: (weights float32 [20030], bias, base_score)."""
+    rng = np.random.default_rng(CONSENSUS_MODEL_SEED)
+    return (rng.standard_normal(20030) * 0.01).astype(np.float32), np.float32(-0.125), np.float32(0.5)

@@ -9,7 +9,8 @@ reference computes here is computed by the reference's own, unmodified code:
   and cannot be imported) — executed, not copied: no reference source enters this repository;
 * ``chromatin.py``, ``compute_expecto_features.py`` and ``predict.py`` run as subprocesses in a scratch
   directory holding synthetic ``resources/hg19.fa`` + ``resources/deepsea.beluga.pth``, behind the import shims in
-  oracle/shims (pyfasta, h5py, liftover, xgboost, matplotlib — third-party packages absent from this image).
+  oracle/shims (pyfasta, h5py, liftover, xgboost, matplotlib, natsort, Bio, seaborn — third-party packages absent
+  from this image); ``geuvadis_predict_consensus.py`` and ``replicate_expecto_features.py`` run the same way.
 
 Every stage asserts that oracle/beluga_oracle.py reproduces the reference output, then stores a small slice
 as a fixture.  Usage:  python oracle/make_golden.py [--workdir /tmp/bx_golden] [--skip-scripts]
@@ -283,16 +284,106 @@ def stage_closest_genes(work):
           f"({str(out['closest_tsv']).count(chr(10))} / {str(out['rf_tsv']).count(chr(10))} rows)")
 
 
+def stage_consensus(work, sd):
+    """geuvadis_predict_consensus.py as a subprocess on seeded consensus FASTAs (2 genes, 6 records, truncated at
+    either end), then again with --exp_only; the restatements in beluga_oracle.py must reproduce both."""
+    import torch
+    pth = os.path.join(work, "resources", "deepsea.beluga.pth")
+    if not os.path.exists(pth):
+        os.makedirs(os.path.dirname(pth), exist_ok=True)
+        torch.save({k: torch.from_numpy(v) for k, v in sd.items()}, pth)
+    root = os.path.join(work, "consensus_in")
+    shutil.rmtree(root, ignore_errors=True)
+    shutil.rmtree(os.path.join(work, "out_consensus"), ignore_errors=True)
+    cdir, genes_file, names = GI.write_consensus_dir(root)
+    w, bias, base = GI.consensus_model()
+    np.savez(os.path.join(work, "consensus_model.npz"), weights=w, bias=bias, base_score=base)
+    run_ref_script("geuvadis_predict_consensus.py", ["consensus_model.npz ", cdir, genes_file, "-o", "out_consensus"], work)
+    shifts = list(range(-20000, 20000, 200))
+    keep = {}
+    for gi, gene in enumerate(names):
+        z = np.load(os.path.join(work, "out_consensus", gene, f"{gene}_chromatin.h5.npz"))
+        e = np.load(os.path.join(work, "out_consensus", gene, f"{gene}.h5.npz"))
+        preds, ids = z["chromatin_preds"], [x.decode() for x in z["record_ids"]]
+        assert preds.dtype == np.float64 and preds.shape == (len(ids), 200, 2002)
+        assert e["expecto_preds"].dtype == np.float32 and list(e["record_ids"]) == list(z["record_ids"])
+        # restatement: records in the reference's own (glob) order, identified by "{record.id}|{stem}"
+        recs = {f"{rid}|{stem}": (rid, seq) for stem, rs in GI.consensus_records(gi).items() for rid, seq in rs}
+        assert sorted(ids) == sorted(recs), (ids, list(recs))
+        strand = GI.CONSENSUS_GENES[gi][4]
+        for k, rec in enumerate(ids):
+            ours = O.consensus_chromatin(O.consensus_pad(*recs[rec]), strand, sd, shifts)
+            err = np.abs(ours - preds[k]).max()
+            assert err < 2e-6, f"consensus restatement differs for {rec}: {err}"
+        feats = O.consensus_features(preds)
+        score = O.gblinear_predict(feats, w, float(bias), float(base))
+        assert np.abs(score - e["expecto_preds"]).max() < 1e-5
+        order = np.argsort(ids)
+        keep[f"ids_{gi}"] = np.array(ids)[order]
+        keep[f"preds_{gi}"] = preds[order][:, GI.CONSENSUS_KEEP_SHIFTS][:, :, ::GI.CONSENSUS_FEATURE_STEP]
+        keep[f"expecto_{gi}"] = e["expecto_preds"][order]
+    # --exp_only re-scores the stored chromatin predictions: same numbers
+    for gene in names:
+        os.rename(os.path.join(work, "out_consensus", gene, f"{gene}.h5.npz"),
+                  os.path.join(work, "out_consensus", gene, f"{gene}.first.npz"))
+    run_ref_script("geuvadis_predict_consensus.py", ["consensus_model.npz", cdir, genes_file, "-o", "out_consensus",
+                                                     "--exp_only"], work)
+    for gene in names:
+        a = np.load(os.path.join(work, "out_consensus", gene, f"{gene}.first.npz"))["expecto_preds"]
+        b = np.load(os.path.join(work, "out_consensus", gene, f"{gene}.h5.npz"))["expecto_preds"]
+        assert np.array_equal(a, b)
+    np.savez_compressed(os.path.join(GOLD, "consensus_golden.npz"), genes=np.array(names), **keep)
+    print(f"[consensus] {len(names)} genes, {sum(len(keep[f'ids_{i}']) for i in range(len(names)))} records: "
+          f"oracle == reference (chromatin within 2e-6, scores within 1e-5); fixture written")
+
+
+def stage_replicate(work, sd, genome):
+    """replicate_expecto_features.py as a subprocess on the two compute_expecto_features genes."""
+    genes = GI.cfg4_genes()
+    anno = os.path.join(work, "geneanno_small.csv")
+    if not os.path.exists(anno):
+        with open(anno, "w") as f:
+            f.write("id,symbol,seqnames,strand,TSS,CAGE_representative_TSS,type\n")
+            for gid, chrom, strand, tss in genes:
+                f.write(f"{gid},SYM,{chrom},{strand},{tss},{tss},protein_coding\n")
+    run_ref_script("replicate_expecto_features.py", ["geneanno_small.csv", "-o", "out_replicate"], work)
+    g = O.DictGenome(genome)
+    keep = {}
+    for i, (gid, chrom, strand, tss) in enumerate(genes):
+        ref = np.load(os.path.join(work, "out_replicate", f"{gid}.npy"))
+        assert ref.dtype == np.float32 and ref.shape == (200, 2002)
+        ours = O.replicate_prediction(g, chrom, tss, 1 if strand == "+" else -1, sd)
+        err = np.abs(ours - ref).max()
+        assert err < 2e-6, f"replicate restatement differs for {gid}: {err}"
+        keep[f"pred_{i}"] = ref[GI.CONSENSUS_KEEP_SHIFTS]
+    # the features file of compute_expecto_features is the pos_weights reduction of these dumps
+    feats = np.load(os.path.join(GOLD, "features_golden.npz"))["features"]
+    full = np.load(os.path.join(work, "out_replicate", f"{genes[0][0]}.npy"))
+    red = np.sum(O.fixed_pos_weights()[:, :, None] * full[None, :, :], axis=1).flatten()
+    assert np.abs(red - feats[0]).max() / np.abs(feats[0]).max() < 1e-6
+    np.savez_compressed(os.path.join(GOLD, "replicate_golden.npz"),
+                        genes=np.array([[str(x) for x in gg] for gg in genes]), **keep)
+    print(f"[replicate] {len(genes)} genes: oracle == reference, dumps reduce to the features fixture")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workdir", default="/tmp/bx_golden")
     ap.add_argument("--skip-scripts", action="store_true", help="only the import-level stages (fast)")
     ap.add_argument("--only-closest", action="store_true", help="only the make_closest_genes_file.py stage")
+    ap.add_argument("--only-consensus", action="store_true",
+                    help="only the geuvadis_predict_consensus.py / replicate_expecto_features.py stages")
     args = ap.parse_args()
     os.makedirs(GOLD, exist_ok=True)
     if args.only_closest:
         os.makedirs(args.workdir, exist_ok=True)
         stage_closest_genes(args.workdir)
+        return
+    if args.only_consensus:
+        sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
+        genome = prepare_workdir(args.workdir, sd)
+        stage_consensus(args.workdir, sd)
+        stage_replicate(args.workdir, sd, genome)
         return
     stage_encode()
     sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
@@ -303,6 +394,8 @@ def main():
         stage_features(args.workdir, sd, genome)
         stage_predict(args.workdir)
         stage_closest_genes(args.workdir)
+        stage_consensus(args.workdir, sd)
+        stage_replicate(args.workdir, sd, genome)
     print("golden fixtures written to", GOLD)
 
 

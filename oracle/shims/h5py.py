@@ -29,3 +29,9 @@ class File:
     def close(self):
         if self.mode != "r":
             np.savez(self.path + ".npz", **self._w)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
