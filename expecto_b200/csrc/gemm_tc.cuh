@@ -52,7 +52,8 @@ struct GemmParams {
   int ld_out;        // output leading dimension in elements
   int n_store;       // columns >= n_store are not stored
   long long split_stride;  // elements between split-K slices of the output (EPI_PARTIAL_F32)
-  int debug_flags;   // diagnostics only (BX_DEBUG_FLAGS): 1 = no B loads, 2 = no A loads, 4 = no epilogue work
+  int debug_flags;   // diagnostics only (BX_DEBUG_FLAGS): 1 = no B loads, 2 = no A loads, 4 = no epilogue work,
+                     // 8 = B ring filled once and then reused (real weight values, no further L2->SMEM weight traffic)
   const float* bias; // [n_total] fp32 (unused for EPI_PARTIAL_F32)
   void* out;
   // Optional per-M-tile split-K ranges (EPI_PARTIAL_F32): tile mt computes slices tile_lo[mt] .. tile_lo[mt] +
@@ -214,6 +215,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------------------------------------------ TMA producer
     RingState ra, rb;
     int ks, mt, nc;
+    int b_fills = 0;  // debug flag 8
     // A_MODE: raw genome / one-hot words of the NEXT 128-row block, loaded one block ahead (encode.cuh)
     EncRaw<A_MODE> enc_raw;
     auto load_block = [&](int mtile) {
@@ -286,7 +288,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll 1
         for (int t = 0; t < TAPS; t += Cfg::TPS) {
           mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
-          if (p.debug_flags & 1) {
+          if ((p.debug_flags & 1) || ((p.debug_flags & 8) && b_fills >= SB)) {
             if (elect_one() && rank == 0) mbar_arrive_local(fullB(rb.idx));
           } else if (elect_one()) {
             const uint32_t dst = sB + rb.idx * Cfg::B_BYTES;
@@ -305,6 +307,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           __syncwarp();
           rb.advance<SB>();
+          ++b_fills;
         }
       }
     }

@@ -40,7 +40,10 @@ def decay_transform_fixed(probs: torch.Tensor, weights, out: torch.Tensor | None
     if not probs.is_cuda or probs.dtype != torch.float32 or probs.dim() != 4 or probs.shape[2:] != (2, N_FEATURES):
         raise ValueError("probs must be a CUDA float32 tensor [G,S,2,2002]")
     G, S = probs.shape[:2]
-    w = torch.as_tensor(np.ascontiguousarray(np.asarray(weights, dtype=np.float32))).to(probs.device)
+    if isinstance(weights, torch.Tensor) and weights.is_cuda:  # already staged by the caller (no copy per call)
+        w = weights.to(dtype=torch.float32).contiguous()
+    else:
+        w = torch.as_tensor(np.ascontiguousarray(np.asarray(weights, dtype=np.float32))).to(probs.device)
     if tuple(w.shape) != (N_BASIS, S):
         raise ValueError(f"weights must be [10,{S}]")
     probs = probs.contiguous()
@@ -70,9 +73,19 @@ def _variant_args(x: torch.Tensor, dist, strand, shifts):
     if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 3 or x.shape[2] != N_FEATURES:
         raise ValueError("x must be a CUDA float32 tensor [S,n,2002]")
     S, n = x.shape[:2]
-    shifts = chromatin_shifts((S - 1) // 2 * 200) if shifts is None else list(shifts)
+    shifts_dev = shifts if isinstance(shifts, torch.Tensor) and shifts.is_cuda else None
+    if shifts_dev is None:
+        shifts = chromatin_shifts((S - 1) // 2 * 200) if shifts is None else list(shifts)
+    elif shifts_dev.dtype != torch.int32:
+        raise ValueError("device-resident shifts must be int32")
     if len(shifts) != S:
         raise ValueError("len(shifts) must equal x.shape[0]")
+    if isinstance(dist, torch.Tensor) and dist.is_cuda and isinstance(strand, torch.Tensor) and strand.is_cuda:
+        # already staged by the caller: float64 distances and int8 signs on the device (no copy per call)
+        if dist.dtype != torch.float64 or strand.dtype != torch.int8 or dist.numel() != n or strand.numel() != n:
+            raise ValueError("device-resident dist/strand must be float64 / int8 (+1, -1) with one entry per variant")
+        sh = shifts_dev if shifts_dev is not None else torch.tensor(shifts, dtype=torch.int32, device=x.device)
+        return x.contiguous(), dist.contiguous(), strand.contiguous(), sh.contiguous(), n, S
     st = np.asarray(strand)
     if st.dtype.kind in "USO":  # '+' / '-' as predict.py:90 compares them (pandas 3 hands back object arrays)
         sgn = np.where(np.asarray([str(v) for v in st.ravel()]) == "+", 1, -1).astype(np.int8)
@@ -80,7 +93,7 @@ def _variant_args(x: torch.Tensor, dist, strand, shifts):
         sgn = np.where(st > 0, 1, -1).astype(np.int8)
     d = torch.from_numpy(np.ascontiguousarray(np.asarray(dist, dtype=np.float64))).to(x.device)
     sg = torch.from_numpy(np.ascontiguousarray(sgn)).to(x.device)
-    sh = torch.tensor(shifts, dtype=torch.int32, device=x.device)
+    sh = shifts_dev if shifts_dev is not None else torch.tensor(shifts, dtype=torch.int32, device=x.device)
     if d.numel() != n or sg.numel() != n:
         raise ValueError("dist/strand must have one entry per variant")
     return x.contiguous(), d, sg, sh, n, S
