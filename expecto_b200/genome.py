@@ -51,50 +51,63 @@ class PackedGenome:
     # ------------------------------------------------------------------ construction
     @classmethod
     def from_sequences(cls, seqs: dict[str, str | bytes]) -> "PackedGenome":
-        g = cls()
-        total = PAD
-        for name, s in seqs.items():
-            total = (total + 31) // 32 * 32
-            g.names.append(name)
-            g.offsets[name] = total
-            g.lengths[name] = len(s)
-            total += len(s) + PAD
-        total = (total + 31) // 32 * 32
-        g.n_bases = total
-        g.bases2 = np.zeros(total // 16, dtype=np.uint32)
-        g.nmask = np.full(total // 32, 0xFFFFFFFF, dtype=np.uint32)  # padding is N
+        raws = {name: np.frombuffer(s.encode("ascii", "replace") if isinstance(s, str) else s, dtype=np.uint8)
+                for name, s in seqs.items()}
+        g = cls._allocate({name: r.size for name, r in raws.items()})
         invalid = []
-        for name, s in seqs.items():
-            raw = np.frombuffer(s.encode("ascii", "replace") if isinstance(s, str) else s, dtype=np.uint8)
+        for name, raw in raws.items():
             g._pack_contig(g.offsets[name], raw, invalid)
         g.invalid = np.sort(np.concatenate(invalid)) if invalid else np.zeros(0, dtype=np.int64)
         return g
 
+    @classmethod
+    def _allocate(cls, lengths: dict[str, int]) -> "PackedGenome":
+        """Offsets (PAD bases of N before/after every contig, contigs on 32-base boundaries) and all-N arrays."""
+        g = cls()
+        total = PAD
+        for name, n in lengths.items():
+            total = (total + 31) // 32 * 32
+            g.names.append(name)
+            g.offsets[name] = total
+            g.lengths[name] = int(n)
+            total += int(n) + PAD
+        total = (total + 31) // 32 * 32
+        g.n_bases = total
+        g.bases2 = np.zeros(total // 16, dtype=np.uint32)
+        g.nmask = np.full(total // 32, 0xFFFFFFFF, dtype=np.uint32)  # padding is N
+        return g
+
+    _CHUNK = 1 << 26  # bases packed per pass (multiple of 32): bounds the temporaries at a few hundred MB
+
     def _pack_contig(self, off: int, raw: np.ndarray, invalid: list) -> None:
-        n = raw.size
-        if n == 0:
-            return
-        codes = _CODE[raw]
-        bad = np.flatnonzero(codes == 255)
-        if bad.size:
-            invalid.append(bad.astype(np.int64) + off)
-            codes = codes.copy()
-            codes[bad] = 4
-        # off is a multiple of 32: pack whole words, tail padded with N
-        n32 = (n + 31) // 32 * 32
-        full = np.full(n32, 4, dtype=np.uint8)
-        full[:n] = codes
-        two = (full & 3).astype(np.uint32).reshape(-1, 16)
-        two[full.reshape(-1, 16) == 4] = 0
-        sh = (np.arange(16, dtype=np.uint32) * 2)[None, :]
-        self.bases2[off // 16: off // 16 + n32 // 16] = np.bitwise_or.reduce(two << sh, axis=1)
-        m = (full == 4).astype(np.uint32).reshape(-1, 32)
-        sh1 = np.arange(32, dtype=np.uint32)[None, :]
-        self.nmask[off // 32: off // 32 + n32 // 32] = np.bitwise_or.reduce(m << sh1, axis=1)
+        """Pack one contig's characters at global index ``off`` (a multiple of 32).  Byte-wise bit packing: four
+        2-bit codes per byte and eight mask bits per byte, both little-endian, so the byte stream viewed as
+        little-endian uint32 is the word layout of the module docstring (base i of a word at bits 2*(i%16))."""
+        for c0 in range(0, raw.size, self._CHUNK):
+            piece = raw[c0:c0 + self._CHUNK]
+            n = piece.size
+            codes = _CODE[piece]
+            bad = np.flatnonzero(codes == 255)
+            if bad.size:
+                invalid.append(bad.astype(np.int64) + (off + c0))
+                codes[bad] = 4
+            n32 = (n + 31) // 32 * 32
+            if n32 != n:  # only the last piece of a contig: tail padded with N
+                full = np.full(n32, 4, dtype=np.uint8)
+                full[:n] = codes
+            else:
+                full = codes
+            q = (full & 3).reshape(-1, 4)          # code 4 (zero column) packs as 0
+            packed = q[:, 0] | (q[:, 1] << 2) | (q[:, 2] << 4) | (q[:, 3] << 6)
+            w0 = (off + c0) // 16
+            self.bases2[w0: w0 + n32 // 16] = np.ascontiguousarray(packed).view("<u4")
+            m0 = (off + c0) // 32
+            self.nmask[m0: m0 + n32 // 32] = np.packbits(full == 4, bitorder="little").view("<u4")
 
     @classmethod
     def from_fasta(cls, path: str, cache: bool = True) -> "PackedGenome":
-        """Parse a (multi-)FASTA; a ``<path>.bx2.npz`` cache is written next to it when possible."""
+        """Parse a (multi-)FASTA; a ``<path>.bx2.npz`` cache is written next to it when possible (atomically: a
+        temporary file renamed into place, so concurrent readers never see a partial cache)."""
         cpath = path + ".bx2.npz"
         if cache and os.path.exists(cpath) and os.path.getmtime(cpath) >= os.path.getmtime(path):
             return cls.load(cpath)
@@ -102,21 +115,34 @@ class PackedGenome:
         starts = np.flatnonzero(buf == ord(">"))
         # keep only '>' at line starts
         starts = starts[(starts == 0) | (buf[np.maximum(starts - 1, 0)] == 10)]
-        seqs: dict[str, bytes] = {}
+        bodies: dict[str, tuple[int, int]] = {}
+        lengths: dict[str, int] = {}
         for i, s in enumerate(starts):
             e = int(starts[i + 1]) if i + 1 < len(starts) else buf.size
             nl = int(s) + int(np.argmax(buf[s:e] == 10)) if np.any(buf[s:min(e, s + 4096)] == 10) else e
             header = buf[s + 1:nl].tobytes().decode("ascii", "replace").strip()
             name = header.split()[0] if header else f"contig{i}"
-            body = buf[nl + 1:e]
-            body = body[(body != 10) & (body != 13)]
-            seqs[name] = body.tobytes()
-        g = cls.from_sequences(seqs)
+            b0 = min(nl + 1, e)
+            body = buf[b0:e]
+            bodies[name] = (b0, e)
+            lengths[name] = int(body.size - np.count_nonzero(body == 10) - np.count_nonzero(body == 13))
+        g = cls._allocate(lengths)
+        invalid = []
+        for name, (b0, e) in bodies.items():  # one contig at a time: the stripped copy is the only large temporary
+            body = buf[b0:e]
+            g._pack_contig(g.offsets[name], body[(body != 10) & (body != 13)], invalid)
+        g.invalid = np.sort(np.concatenate(invalid)) if invalid else np.zeros(0, dtype=np.int64)
+        del buf
         if cache:
+            tmp = f"{cpath}.{os.getpid()}.tmp.npz"
             try:
-                g.save(cpath)
+                g.save(tmp)
+                os.replace(tmp, cpath)
             except OSError:
-                pass
+                try:
+                    os.unlink(tmp)
+                except OSError:
+                    pass
         return g
 
     def save(self, path: str) -> None:

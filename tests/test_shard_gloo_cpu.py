@@ -120,3 +120,22 @@ def _features_worker(rank, world, port, n_genes, tmp):
 @pytest.mark.parametrize("n_genes", [5, 1])
 def test_two_rank_feature_shards_gather_to_one_file(tmp_path, n_genes):
     mp.spawn(_features_worker, args=(2, _free_port(), n_genes, str(tmp_path)), nprocs=2, join=True)
+
+
+def _genome_worker(rank, world, port, fa):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    shard.init_distributed("gloo")
+    g = shard.load_genome(fa)
+    # every rank ends up with the same packed arrays; only rank 0 parsed the FASTA (the others found the cache)
+    sums = shard.allreduce_sum_ints([int(g.bases2.sum() % (1 << 31)), int(g.nmask.sum() % (1 << 31)), g.n_bases])
+    assert sums == [world * int(g.bases2.sum() % (1 << 31)), world * int(g.nmask.sum() % (1 << 31)), world * g.n_bases]
+    assert os.path.exists(fa + ".bx2.npz")
+    dist.destroy_process_group()
+
+
+def test_genome_is_packed_once_and_shared_through_the_cache(tmp_path):
+    from expecto_b200 import synth
+    fa = str(tmp_path / "g.fa")
+    synth.write_fasta(fa, synth.make_genome([("chr1", 50000), ("chr2", 30000)], seed=4), width=60)
+    mp.spawn(_genome_worker, args=(2, _free_port(), fa), nprocs=2, join=True)

@@ -214,3 +214,58 @@ def test_packed_genome_from_fasta_roundtrip(tmp_path, small_genome):
         assert np.array_equal(g.bases2, ref.bases2) and np.array_equal(g.nmask, ref.nmask)
     s = small_genome["chr2"]
     assert pg.upper_string(pg.offsets["chr2"] + 100, 50) == s[100:150].upper()
+
+
+def test_packed_layout_against_a_per_base_loop(tmp_path, monkeypatch):
+    """The word layout of genome.py's docstring, checked base by base with plain Python (independent of the packer's
+    byte tricks): CRLF line ends, ragged line widths, lower case, every zero-column character, characters outside
+    ``mydict`` (recorded as invalid, chromatin.py:155-160 would raise KeyError), contigs that end inside a word, and
+    contigs longer than one packing pass."""
+    from expecto_b200 import genome as G
+    monkeypatch.setattr(G.PackedGenome, "_CHUNK", 64)   # several passes per contig
+    rng = np.random.default_rng(11)
+    alphabet = np.frombuffer(b"ACGTacgtNnH-RY", dtype=np.uint8)
+    seqs = {"chrA": alphabet[rng.integers(0, len(alphabet), size=333)].tobytes().decode(),
+            "chrB": "ACGT" * 16 + "N",
+            "chrC": alphabet[rng.integers(0, 8, size=64 * 3)].tobytes().decode()}
+    fa = tmp_path / "ragged.fa"
+    with open(fa, "wb") as f:
+        for name, s in seqs.items():
+            f.write(f">{name} some description\r\n".encode())
+            i, widths = 0, [7, 60, 1, 33]
+            while i < len(s):
+                w = widths[(i + len(name)) % len(widths)]
+                f.write(s[i:i + w].encode() + (b"\r\n" if name != "chrB" else b"\n"))
+                i += w
+    g = G.PackedGenome.from_fasta(str(fa), cache=False)
+    assert g.names == list(seqs) and g.lengths == {k: len(v) for k, v in seqs.items()}
+    row = {"A": 0, "G": 1, "C": 2, "T": 3}
+    want_invalid = []
+    for name, s in seqs.items():
+        off = g.offsets[name]
+        assert off % 32 == 0
+        for i, ch in enumerate(s):
+            j = off + i
+            two = (int(g.bases2[j >> 4]) >> (2 * (j & 15))) & 3
+            msk = (int(g.nmask[j >> 5]) >> (j & 31)) & 1
+            if ch.upper() in row:
+                assert (two, msk) == (row[ch.upper()], 0), (name, i, ch)
+            else:
+                assert msk == 1, (name, i, ch)
+                if ch not in "NnH-":
+                    want_invalid.append(j)
+        # padding after the contig reads as zero columns
+        assert all((int(g.nmask[j >> 5]) >> (j & 31)) & 1 for j in range(off + len(s), off + len(s) + 64))
+    assert g.invalid.tolist() == want_invalid
+    same = G.PackedGenome.from_sequences(seqs)
+    assert np.array_equal(same.bases2, g.bases2) and np.array_equal(same.nmask, g.nmask)
+    assert np.array_equal(same.invalid, g.invalid)
+
+
+def test_fasta_cache_is_written_atomically(tmp_path, small_genome):
+    from expecto_b200 import synth
+    fa = tmp_path / "g.fa"
+    synth.write_fasta(str(fa), small_genome, width=50)
+    PackedGenome.from_fasta(str(fa))
+    left = sorted(p.name for p in tmp_path.iterdir())
+    assert left == ["g.fa", "g.fa.bx2.npz"]   # no temporary file left behind
