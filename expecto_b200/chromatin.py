@@ -661,8 +661,10 @@ def _run_segments(args, engine, genome, chroms, pos, refs, alts, n, lo, n_local,
 
 
 def main(argv=None) -> int:
+    from . import shard
     args = build_parser().parse_args(argv)
     run(args)
+    shard.finalize()
     return 0
 
 

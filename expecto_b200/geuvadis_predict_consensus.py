@@ -278,7 +278,9 @@ def run(args, engine=None) -> list[str]:
 
 
 def main(argv=None) -> int:
+    from . import shard
     run(build_parser().parse_args(argv))
+    shard.finalize()
     return 0
 
 

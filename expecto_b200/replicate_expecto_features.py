@@ -125,7 +125,9 @@ def run(args, engine=None, genome=None) -> int:
 
 
 def main(argv=None) -> int:
+    from . import shard
     run(build_parser().parse_args(argv))
+    shard.finalize()
     return 0
 
 

@@ -115,3 +115,9 @@ def load_genome(path: str):
     genome = PackedGenome.from_fasta(path) if dist.get_rank() == 0 else None
     barrier()
     return genome if genome is not None else PackedGenome.from_fasta(path)
+
+
+def finalize() -> None:
+    """End of a script's ``main()``: leave the process group cleanly (NCCL warns about leaked resources otherwise)."""
+    if dist.is_initialized():
+        dist.destroy_process_group()
