@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libbeluga_b200.so")
 SRC = os.path.join(_HERE, "csrc", "capi.cu")
-SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh", "encode.cuh")] + [
+SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh", "encode.cuh", "genome_pack.cuh")] + [
     os.path.join(ROOT, "include", "beluga_b200.h")
 ]
 
@@ -50,7 +50,7 @@ EXPORTS = [
     "bx_chromatin_outputs", "bx_chromatin_outputs_avg", "bx_decay_transform_fixed", "bx_decay_transform_variant",
     "bx_forward_onehot_host", "bx_chromatin_shift_host", "bx_ctx_profile", "bx_ctx_profile_read",
     "bx_decay_score_variant", "bx_forward_segments", "bx_segment_capacity", "bx_strand_average",
-    "bx_forward_segments_delta",
+    "bx_forward_segments_delta", "bx_fasta_blocks", "bx_fasta_find_headers", "bx_fasta_count", "bx_fasta_pack",
 ]
 NSTAGES = 10
 STAGE_NAMES = ["encode", "conv1", "conv2", "conv3", "conv4", "conv5", "conv6", "fc1", "fc2", "outputs"]
@@ -119,10 +119,15 @@ def lib() -> C.CDLL:
     L.bx_forward_segments_delta.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, C.POINTER(C.c_int32), i32, vp, vp]
     L.bx_segment_capacity.argtypes = [vp, i32]
     L.bx_strand_average.argtypes = [vp, i32, vp, vp]
+    L.bx_fasta_blocks.argtypes = [i64, i64]
+    L.bx_fasta_blocks.restype = i64
+    L.bx_fasta_find_headers.argtypes = [vp, i64, vp, i64, vp, vp]
+    L.bx_fasta_count.argtypes = [vp, i64, i64, vp, C.POINTER(i64), vp]
+    L.bx_fasta_pack.argtypes = [vp, i64, i64, vp, i64, vp, vp, vp, i64, vp, vp]
     L.bx_ctx_profile.argtypes = [vp, i32]
     L.bx_ctx_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), i32]
     for name in EXPORTS:
-        if name not in ("bx_last_error", "bx_launch_count"):
+        if name not in ("bx_last_error", "bx_launch_count", "bx_fasta_blocks"):
             getattr(L, name).restype = i32
     _lib = L
     return L

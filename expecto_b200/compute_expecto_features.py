@@ -143,7 +143,8 @@ def run(args, engine=None, genome=None) -> str:
     rank, world, local = shard.init_distributed()
     os.makedirs(args.out_dir, exist_ok=True)
     if genome is None:
-        genome = shard.load_genome(args.genome)
+        genome = shard.load_genome(args.genome, device=engine.device if engine is not None else
+                                   (local if world > 1 else args.device))
     if engine is None:
         from .engine import BelugaEngine
         engine = BelugaEngine(local if world > 1 else args.device, dtype=args.dtype, capacity=4096)

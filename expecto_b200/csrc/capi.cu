@@ -15,6 +15,8 @@
 #include "../../include/beluga_b200.h"
 #include "gemm_tc.cuh"
 #include "kernels_misc.cuh"
+#include "genome_pack.cuh"
+#include <cub/device/device_scan.cuh>
 
 using namespace bx;
 
@@ -1211,6 +1213,93 @@ int bx_forward_segments_delta(bx_ctx* c, const bx_window_desc* ref_descs_dev, co
   CK(cudaSetDevice(c->device));
   return forward_segments_impl(c, ref_descs_dev, patch_descs_dev, alleles_dev, n_groups, 4, seg_len, patch_len,
                                patch_row0, n_shifts, k_of_shift, shift_major, probs_dev, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ FASTA text in HBM -> packed genome
+static int check_device() {
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(BX_E_CUDA, "no CUDA device (%s): this library has no CPU fallback", cudaGetErrorString(e));
+  return 0;
+}
+static unsigned grid_for(long long n_items, int per_block) {
+  return (unsigned)std::max<long long>(1, std::min<long long>((n_items + per_block - 1) / per_block, 148LL * 16));
+}
+
+int64_t bx_fasta_blocks(int64_t body_start, int64_t body_end) {
+  if (body_start < 0 || body_end <= body_start) return 0;
+  const long long a0 = body_start & ~15LL;
+  return (body_end - a0 + kFaBlockBytes - 1) / kFaBlockBytes;
+}
+
+int bx_fasta_find_headers(const uint8_t* text_dev, int64_t n_text, int64_t* pos_dev, int64_t cap, int64_t* count_dev,
+                          void* stream) {
+  if (n_text < 0 || cap < 0 || !count_dev || (cap > 0 && !pos_dev)) return fail(BX_E_ARG, "invalid arguments");
+  if (int r = check_device()) return r;
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaMemsetAsync(count_dev, 0, sizeof(int64_t), st));
+  if (n_text == 0) return 0;
+  if (!text_dev || (reinterpret_cast<uintptr_t>(text_dev) & 15)) return fail(BX_E_ARG, "text_dev must be 16-byte aligned");
+  fasta_headers_kernel<<<grid_for((n_text + 15) / 16, 256), 256, 0, st>>>(
+      text_dev, n_text, reinterpret_cast<long long*>(pos_dev), cap, reinterpret_cast<unsigned long long*>(count_dev));
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int bx_fasta_count(const uint8_t* text_dev, int64_t body_start, int64_t body_end, int64_t* block_offsets_dev,
+                   int64_t* n_bases_host, void* stream) {
+  if (body_start < 0 || body_end < body_start || !block_offsets_dev || !n_bases_host)
+    return fail(BX_E_ARG, "invalid arguments");
+  if (int r = check_device()) return r;
+  if (!text_dev || (reinterpret_cast<uintptr_t>(text_dev) & 15)) return fail(BX_E_ARG, "text_dev must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n_blocks = bx_fasta_blocks(body_start, body_end);
+  long long* off = reinterpret_cast<long long*>(block_offsets_dev);
+  CK(cudaMemsetAsync(off + n_blocks, 0, sizeof(long long), st));  // the scan turns this extra entry into the total
+  if (n_blocks > 0) {
+    fasta_count_kernel<<<grid_for(n_blocks, kFaThreads / 32), kFaThreads, 0, st>>>(text_dev, body_start & ~15LL, body_start, body_end,
+                                                                      n_blocks, off);
+    g_launches++;
+    CK(cudaGetLastError());
+    if (n_blocks + 1 > 0x7fffffffLL) return fail(BX_E_ARG, "contig body too large");
+    size_t tmp_bytes = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, off, off, (int)(n_blocks + 1), st));
+    void* tmp = nullptr;
+    CK(cudaMallocAsync(&tmp, tmp_bytes ? tmp_bytes : 1, st));
+    cudaError_t e = cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, off, off, (int)(n_blocks + 1), st);
+    g_launches++;
+    cudaFreeAsync(tmp, st);
+    CK(e);
+  }
+  long long total = 0;
+  CK(cudaMemcpyAsync(&total, off + n_blocks, sizeof(long long), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  *n_bases_host = total;
+  return 0;
+}
+
+int bx_fasta_pack(const uint8_t* text_dev, int64_t body_start, int64_t body_end, const int64_t* block_offsets_dev,
+                  int64_t base_offset, uint32_t* bases2_dev, uint32_t* nmask_dev, int64_t* invalid_dev,
+                  int64_t invalid_cap, int64_t* invalid_count_dev, void* stream) {
+  if (body_start < 0 || body_end < body_start || base_offset < 0 || (base_offset & 31) || invalid_cap < 0)
+    return fail(BX_E_ARG, "invalid arguments (base_offset must be a multiple of 32)");
+  const long long n_blocks = bx_fasta_blocks(body_start, body_end);
+  if (n_blocks == 0) return 0;
+  if (!text_dev || !block_offsets_dev || !bases2_dev || !nmask_dev || !invalid_count_dev ||
+      (invalid_cap > 0 && !invalid_dev))
+    return fail(BX_E_ARG, "invalid arguments");
+  if (reinterpret_cast<uintptr_t>(text_dev) & 15) return fail(BX_E_ARG, "text_dev must be 16-byte aligned");
+  if (int r = check_device()) return r;
+  cudaStream_t st = (cudaStream_t)stream;
+  fasta_pack_kernel<<<grid_for(n_blocks, 1), kFaThreads, 0, st>>>(
+      text_dev, body_start & ~15LL, body_start, body_end, n_blocks, reinterpret_cast<const long long*>(block_offsets_dev),
+      base_offset, bases2_dev, nmask_dev, reinterpret_cast<long long*>(invalid_dev), invalid_cap,
+      reinterpret_cast<unsigned long long*>(invalid_count_dev));
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
 }
 
 }  // extern "C"

@@ -84,8 +84,12 @@ class BelugaEngine:
     def set_genome(self, packed) -> None:
         """``packed``: expecto_b200.genome.PackedGenome; uploads the 2-bit planes once."""
         self._genome = packed
-        self._bases2 = torch.from_numpy(packed.bases2.view(np.int32)).to(self.device)
-        self._nmask = torch.from_numpy(packed.nmask.view(np.int32)).to(self.device)
+        planes = getattr(packed, "_device_planes", None)
+        if planes is not None and planes[0] == self.device:  # packed on this device (PackedGenome.from_fasta)
+            self._bases2, self._nmask = planes[1], planes[2]
+        else:
+            self._bases2 = torch.from_numpy(packed.bases2.view(np.int32)).to(self.device)
+            self._nmask = torch.from_numpy(packed.nmask.view(np.int32)).to(self.device)
         check(lib().bx_ctx_set_genome(self._ctx, self._bases2.data_ptr(), self._nmask.data_ptr(), packed.n_bases))
 
     # ------------------------------------------------------------------ compute

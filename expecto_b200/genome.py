@@ -61,7 +61,7 @@ class PackedGenome:
         return g
 
     @classmethod
-    def _allocate(cls, lengths: dict[str, int]) -> "PackedGenome":
+    def _allocate(cls, lengths: dict[str, int], host_arrays: bool = True) -> "PackedGenome":
         """Offsets (PAD bases of N before/after every contig, contigs on 32-base boundaries) and all-N arrays."""
         g = cls()
         total = PAD
@@ -73,8 +73,9 @@ class PackedGenome:
             total += int(n) + PAD
         total = (total + 31) // 32 * 32
         g.n_bases = total
-        g.bases2 = np.zeros(total // 16, dtype=np.uint32)
-        g.nmask = np.full(total // 32, 0xFFFFFFFF, dtype=np.uint32)  # padding is N
+        if host_arrays:
+            g.bases2 = np.zeros(total // 16, dtype=np.uint32)
+            g.nmask = np.full(total // 32, 0xFFFFFFFF, dtype=np.uint32)  # padding is N
         return g
 
     _CHUNK = 1 << 26  # bases packed per pass (multiple of 32): bounds the temporaries at a few hundred MB
@@ -105,12 +106,22 @@ class PackedGenome:
             self.nmask[m0: m0 + n32 // 32] = np.packbits(full == 4, bitorder="little").view("<u4")
 
     @classmethod
-    def from_fasta(cls, path: str, cache: bool = True) -> "PackedGenome":
+    def from_fasta(cls, path: str, cache: bool = True, device=None) -> "PackedGenome":
         """Parse a (multi-)FASTA; a ``<path>.bx2.npz`` cache is written next to it when possible (atomically: a
-        temporary file renamed into place, so concurrent readers never see a partial cache)."""
+        temporary file renamed into place, so concurrent readers never see a partial cache).
+
+        ``device`` (a CUDA device): the file is copied to HBM and packed there by the ``bx_fasta_*`` kernels
+        (csrc/genome_pack.cuh) — what the drop-in CLIs do; the packed planes stay on that device for
+        ``BelugaEngine.set_genome``.  ``device=None`` packs with numpy on the host (tests, tools without a GPU); the
+        two produce identical arrays (tests/test_gpu_parity.py)."""
         cpath = path + ".bx2.npz"
         if cache and os.path.exists(cpath) and os.path.getmtime(cpath) >= os.path.getmtime(path):
             return cls.load(cpath)
+        if device is not None:
+            g = cls._from_fasta_device(path, device)
+            if cache:
+                g._save_cache(cpath)
+            return g
         buf = np.fromfile(path, dtype=np.uint8)
         starts = np.flatnonzero(buf == ord(">"))
         # keep only '>' at line starts
@@ -134,15 +145,92 @@ class PackedGenome:
         g.invalid = np.sort(np.concatenate(invalid)) if invalid else np.zeros(0, dtype=np.int64)
         del buf
         if cache:
-            tmp = f"{cpath}.{os.getpid()}.tmp.npz"
+            g._save_cache(cpath)
+        return g
+
+    def _save_cache(self, cpath: str) -> None:
+        tmp = f"{cpath}.{os.getpid()}.tmp.npz"
+        try:
+            self.save(tmp)
+            os.replace(tmp, cpath)
+        except OSError:
             try:
-                g.save(tmp)
-                os.replace(tmp, cpath)
+                os.unlink(tmp)
             except OSError:
-                try:
-                    os.unlink(tmp)
-                except OSError:
-                    pass
+                pass
+
+    # ------------------------------------------------------------------ device-side packing
+    @classmethod
+    def _from_fasta_device(cls, path: str, device, chunk_bytes: int = 1 << 26, header_cap: int = 1 << 20,
+                           invalid_cap: int = 1 << 22) -> "PackedGenome":
+        """FASTA -> packed planes on ``device`` (include/beluga_b200.h: bx_fasta_find_headers / _count / _pack).
+        The host only streams the file into HBM through two pinned buffers and reads the header lines."""
+        import ctypes as C
+
+        import torch
+
+        from ._lib import check, lib
+
+        L = lib()
+        dev = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        if dev.type != "cuda":
+            raise ValueError("device must be a CUDA device")
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        size = os.path.getsize(path)
+        st = torch.cuda.current_stream(dev)
+        with torch.cuda.device(dev):
+            text = torch.empty((size + 15) // 16 * 16 + 16, dtype=torch.uint8, device=dev)
+            text[size:] = 10  # the kernels load whole 16-byte vectors
+            pinned = [torch.empty(chunk_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+            done = [torch.cuda.Event(), torch.cuda.Event()]
+            with open(path, "rb", buffering=0) as f:
+                off, i = 0, 0
+                while off < size:
+                    done[i].synchronize()  # the copy that last used this buffer
+                    n = f.readinto(memoryview(pinned[i].numpy())[:min(chunk_bytes, size - off)])
+                    if not n:
+                        raise IOError(f"{path}: short read at byte {off}")
+                    text[off:off + n].copy_(pinned[i][:n], non_blocking=True)
+                    done[i].record(st)
+                    off, i = off + n, i ^ 1
+            pos = torch.empty(header_cap, dtype=torch.int64, device=dev)
+            cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+            check(L.bx_fasta_find_headers(text.data_ptr(), size, pos.data_ptr(), header_cap, cnt.data_ptr(), st.cuda_stream))
+            n_hdr = int(cnt.item())
+            if n_hdr > header_cap:
+                raise ValueError(f"{path}: {n_hdr} contigs exceed the header buffer ({header_cap})")
+            starts = np.sort(pos[:n_hdr].cpu().numpy())
+            bodies, lengths = [], {}
+            with open(path, "rb") as f:
+                for k, s0 in enumerate(starts):
+                    e = int(starts[k + 1]) if k + 1 < n_hdr else size
+                    f.seek(int(s0))
+                    line = f.readline()
+                    header = line[1:].decode("ascii", "replace").strip()
+                    name = header.split()[0] if header else f"contig{k}"
+                    bodies.append((name, min(int(s0) + len(line), e), e))
+            offs = [torch.empty(int(L.bx_fasta_blocks(b0, e)) + 1, dtype=torch.int64, device=dev) for _, b0, e in bodies]
+            n_out = C.c_int64(0)
+            for (name, b0, e), o in zip(bodies, offs):
+                check(L.bx_fasta_count(text.data_ptr(), b0, e, o.data_ptr(), C.byref(n_out), st.cuda_stream))
+                lengths[name] = int(n_out.value)
+            g = cls._allocate(lengths, host_arrays=False)
+            bases2 = torch.zeros(g.n_bases // 16, dtype=torch.int32, device=dev)
+            nmask = torch.full((g.n_bases // 32,), -1, dtype=torch.int32, device=dev)  # padding is N
+            invalid = torch.empty(invalid_cap, dtype=torch.int64, device=dev)
+            n_invalid = torch.zeros(1, dtype=torch.int64, device=dev)
+            for (name, b0, e), o in zip(bodies, offs):
+                check(L.bx_fasta_pack(text.data_ptr(), b0, e, o.data_ptr(), g.offsets[name], bases2.data_ptr(),
+                                      nmask.data_ptr(), invalid.data_ptr(), invalid_cap, n_invalid.data_ptr(),
+                                      st.cuda_stream))
+            n_bad = int(n_invalid.item())
+            if n_bad > invalid_cap:
+                raise ValueError(f"{path}: {n_bad} characters outside ACGTacgtNnH- exceed the list of {invalid_cap}")
+            g.invalid = np.sort(invalid[:n_bad].cpu().numpy()).astype(np.int64)
+            g.bases2 = bases2.cpu().numpy().view(np.uint32)
+            g.nmask = nmask.cpu().numpy().view(np.uint32)
+            g._device_planes = (dev, bases2, nmask)  # BelugaEngine.set_genome reuses them on the same device
         return g
 
     def save(self, path: str) -> None:

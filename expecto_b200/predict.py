@@ -239,7 +239,7 @@ def _chromatin_blocks(args, dev, engine=None, genome=None):
     from .genome import PackedGenome
 
     if genome is None:
-        genome = PackedGenome.from_fasta(args.genome)
+        genome = PackedGenome.from_fasta(args.genome, device=engine.device if engine is not None else dev)
     if engine is None:
         from .engine import BelugaEngine
         engine = BelugaEngine(dev.index or 0, dtype=args.dtype, capacity=4096)

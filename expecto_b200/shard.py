@@ -104,17 +104,18 @@ def barrier() -> None:
         dist.barrier()
 
 
-def load_genome(path: str):
-    """``PackedGenome.from_fasta`` for every rank without packing the FASTA ``world`` times: rank 0 parses it first
-    (and writes the ``.bx2.npz`` cache next to it, atomically), the other ranks wait at a barrier and then read the
-    cache — or, where the cache could not be written (read-only directory), parse the FASTA themselves."""
+def load_genome(path: str, device=None):
+    """``PackedGenome.from_fasta`` for every rank without packing the FASTA ``world`` times: rank 0 packs it first
+    (on its GPU when ``device`` is given) and writes the ``.bx2.npz`` cache next to it, atomically; the other ranks
+    wait at a barrier and then read the cache — or, where the cache could not be written (read-only directory), pack
+    the FASTA themselves."""
     from .genome import PackedGenome
 
     if not dist.is_initialized() or dist.get_world_size() == 1:
-        return PackedGenome.from_fasta(path)
-    genome = PackedGenome.from_fasta(path) if dist.get_rank() == 0 else None
+        return PackedGenome.from_fasta(path, device=device)
+    genome = PackedGenome.from_fasta(path, device=device) if dist.get_rank() == 0 else None
     barrier()
-    return genome if genome is not None else PackedGenome.from_fasta(path)
+    return genome if genome is not None else PackedGenome.from_fasta(path, device=device)
 
 
 def finalize() -> None:

@@ -165,6 +165,33 @@ int bx_decay_score_variant(const float* x_dev, const double* dist_dev, const int
                             const int32_t* shifts_dev, const float* w_dev, const float* offset_dev, int n,
                             int n_shifts, int n_models, float* out_dev, void* stream);
 
+/* ---- FASTA text resident in HBM -> packed genome (the arrays of bx_ctx_set_genome) --------------------------------
+ * Replaces the genome side of the reference's input handling: pyfasta.Fasta('./resources/hg19.fa') builds a flat
+ * index and serves string slices (chromatin.py:44,205; compute_expecto_features.py:31,108), and encodeSeqs maps each
+ * character through `mydict` (chromatin.py:155-160).  Here the whole file is copied to the device once and packed
+ * there.  text_dev: the file's bytes, 16-byte aligned, readable up to the next multiple of 16 past n_text.
+ *
+ * 1. bx_fasta_find_headers: file offsets of every '>' that starts a line -> pos_dev[0..min(count,cap)) (unordered),
+ *    *count_dev = how many there are (device int64; the caller reads it back and sorts).
+ * 2. per contig body [body_start, body_end) = the bytes after its header line up to the next header (line ends may
+ *    sit anywhere: ragged widths, CRLF): bx_fasta_count fills block_offsets_dev[0 .. bx_fasta_blocks()] with the
+ *    exclusive prefix of the bases per 4096-byte block and returns the contig length in *n_bases_host (synchronises
+ *    the stream).
+ * 3. bx_fasta_pack writes the contig at global base index base_offset (a multiple of 32).  The caller lays the
+ *    contigs out and PRE-FILLS bases2 with 0 and nmask with ones (the padding between contigs reads as zero columns;
+ *    32-base groups shared by two 4096-byte blocks are merged into the planes with atomic OR / AND).  Characters
+ *    outside mydict (the reference raises KeyError when a window touches one) are packed as zero columns and their
+ *    global indices appended to invalid_dev[0..invalid_cap) (unordered); *invalid_count_dev (device int64, zeroed by
+ *    the caller) counts all of them. */
+int64_t bx_fasta_blocks(int64_t body_start, int64_t body_end);
+int bx_fasta_find_headers(const uint8_t* text_dev, int64_t n_text, int64_t* pos_dev, int64_t cap, int64_t* count_dev,
+                          void* stream);
+int bx_fasta_count(const uint8_t* text_dev, int64_t body_start, int64_t body_end, int64_t* block_offsets_dev,
+                   int64_t* n_bases_host, void* stream);
+int bx_fasta_pack(const uint8_t* text_dev, int64_t body_start, int64_t body_end, const int64_t* block_offsets_dev,
+                  int64_t base_offset, uint32_t* bases2_dev, uint32_t* nmask_dev, int64_t* invalid_dev,
+                  int64_t invalid_cap, int64_t* invalid_count_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
