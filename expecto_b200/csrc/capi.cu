@@ -1259,11 +1259,11 @@ int bx_fasta_count(const uint8_t* text_dev, int64_t body_start, int64_t body_end
   long long* off = reinterpret_cast<long long*>(block_offsets_dev);
   CK(cudaMemsetAsync(off + n_blocks, 0, sizeof(long long), st));  // the scan turns this extra entry into the total
   if (n_blocks > 0) {
+    if (n_blocks + 1 > 0x7fffffffLL) return fail(BX_E_ARG, "contig body too large");
     fasta_count_kernel<<<grid_for(n_blocks, kFaThreads / 32), kFaThreads, 0, st>>>(text_dev, body_start & ~15LL, body_start, body_end,
                                                                       n_blocks, off);
     g_launches++;
     CK(cudaGetLastError());
-    if (n_blocks + 1 > 0x7fffffffLL) return fail(BX_E_ARG, "contig body too large");
     size_t tmp_bytes = 0;
     CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, off, off, (int)(n_blocks + 1), st));
     void* tmp = nullptr;

@@ -8,7 +8,7 @@
 //   pass 1  fasta_count_kernel   bases per 4096-byte block            (text read once, 8 B written per block)
 //           cub::DeviceScan      exclusive sum over the blocks; the last entry is the contig length
 //   pass 2  fasta_pack_kernel    block-local scan, the block's bases compacted in shared memory at their position
-//                                modulo 32, then one thread per 32-base group: two bases2 words + one mask word.
+//                                modulo 32, then one thread per 16 bases: one bases2 word + half a mask word.
 //                                Groups a block covers completely are plain stores; the (at most two) groups it
 //                                shares with its neighbours are merged with atomicOr / atomicAnd into the planes the
 //                                caller pre-filled (bases2 = 0, nmask = ones).  Characters outside mydict (the
@@ -47,6 +47,11 @@ __device__ __forceinline__ void fasta_load16(const uint8_t* __restrict__ text, l
   uint4 v = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
   if (at + 16 > b0 && at < b1) v = __ldg(reinterpret_cast<const uint4*>(text + at));
   const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  if (at >= b0 && at + 16 <= b1) {  // the common case: no per-byte bounds
+#pragma unroll
+    for (int i = 0; i < 16; ++i) c[i] = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
     const long long p = at + i;
@@ -162,34 +167,50 @@ fasta_pack_kernel(const uint8_t* __restrict__ text, long long a0, long long b0, 
     for (int i = 0; i < 16; ++i)
       if (k[i] != kFaEol) s_codes[at++] = k[i];
     __syncthreads();
-    if ((int)threadIdx.x < n_groups) {
-      const uint4* p = reinterpret_cast<const uint4*>(s_codes + 32 * threadIdx.x);
-      const uint4 lo = p[0], hi = p[1];
-      const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-      const long long g = (G >> 5) + threadIdx.x;
-      uint32_t two[2] = {0u, 0u}, base_bits = 0u, covered = 0u;
+    // One thread per HALF group (16 bases -> one bases2 word and 16 mask bits); the two halves of a group sit in
+    // neighbouring lanes and combine their mask bits with one shuffle.
+    // (lead + total can reach 129 groups = 258 halves: the loop runs twice for such a block, uniformly.)
+    for (int t0 = 0; t0 < 2 * n_groups; t0 += kFaThreads) {
+    const int t = t0 + (int)threadIdx.x;
+    const int half = t & 1;
+    const long long g = (G >> 5) + (t >> 1);
+    uint32_t two = 0u, base_bits = 0u, covered = 0u;
+    const bool active = (t >> 1) < n_groups;
+    if (active) {
+      const uint4 q = *reinterpret_cast<const uint4*>(s_codes + 16 * t);
+      const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+      if (((w[0] | w[1] | w[2] | w[3]) & 0xfcfcfcfcu) == 0u) {  // sixteen plain bases: pack four codes per step
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const uint32_t code = (w[i >> 2] >> (8 * (i & 3))) & 0xffu;
-        if (code == kFaUncovered) continue;
-        covered |= 1u << i;
-        if (code < 4) {
-          base_bits |= 1u << i;
-          two[i >> 4] |= code << (2 * (i & 15));
-        } else if (code == kFaInvalid) {
-          const unsigned long long slot = atomicAdd(invalid_count, 1ull);
-          if ((long long)slot < invalid_cap) invalid[slot] = g * 32 + i;
+        for (int j = 0; j < 4; ++j) two |= ((w[j] | (w[j] >> 6) | (w[j] >> 12) | (w[j] >> 18)) & 0xffu) << (8 * j);
+        base_bits = covered = 0xffffu;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const uint32_t code = (w[i >> 2] >> (8 * (i & 3))) & 0xffu;
+          if (code == kFaUncovered) continue;
+          covered |= 1u << i;
+          if (code < 4) {
+            base_bits |= 1u << i;
+            two |= code << (2 * i);
+          } else if (code == kFaInvalid) {
+            const unsigned long long slot = atomicAdd(invalid_count, 1ull);
+            if ((long long)slot < invalid_cap) invalid[slot] = g * 32 + half * 16 + i;
+          }
         }
       }
-      if (covered == 0xffffffffu) {
-        bases2[2 * g] = two[0];
-        bases2[2 * g + 1] = two[1];
-        nmask[g] = ~base_bits;
-      } else {  // shared with a neighbouring block (or the contig's last, partly filled group)
-        if (two[0]) atomicOr(bases2 + 2 * g, two[0]);
-        if (two[1]) atomicOr(bases2 + 2 * g + 1, two[1]);
-        if (base_bits) atomicAnd(nmask + g, ~base_bits);
+      if (covered == 0xffffu) bases2[2 * g + half] = two;
+      else if (two) atomicOr(bases2 + 2 * g + half, two);  // shared with a neighbouring block / the contig's tail
+    }
+    const uint32_t my_bits = base_bits << (16 * half), my_cov = covered << (16 * half);
+    const uint32_t other_bits = __shfl_xor_sync(0xffffffffu, my_bits, 1);
+    const uint32_t other_cov = __shfl_xor_sync(0xffffffffu, my_cov, 1);
+    if (active) {
+      if ((my_cov | other_cov) == 0xffffffffu) {
+        if (half == 0) nmask[g] = ~(my_bits | other_bits);
+      } else if (my_bits) {
+        atomicAnd(nmask + g, ~my_bits);
       }
+    }
     }
     __syncthreads();
   }

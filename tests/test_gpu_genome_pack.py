@@ -20,7 +20,7 @@ def _same(a: PackedGenome, b: PackedGenome):
     assert np.array_equal(a.invalid, b.invalid)
 
 
-def _write_ragged(path, seqs, eol=b"\r\n", widths=(7, 60, 1, 33, 4096, 5000)):
+def _write_ragged(path, seqs, eol=b"\r\n", widths=(7, 60, 1, 33, 4096, 9000)):
     with open(path, "wb") as f:
         for name, s in seqs.items():
             f.write(f">{name} description text\n".encode())
@@ -32,6 +32,8 @@ def _write_ragged(path, seqs, eol=b"\r\n", widths=(7, 60, 1, 33, 4096, 5000)):
 
 
 def test_device_packer_equals_host_packer_on_ragged_crlf_fasta(tmp_path):
+    """Line widths from 1 to 9000 characters: 32-base groups shared by two 4096-byte blocks (atomic merge), blocks
+    without any line end whose first base is not group-aligned (129 groups in one block), CRLF line ends."""
     rng = np.random.default_rng(5)
     alphabet = np.frombuffer(b"ACGTacgtNnH-RYhx", dtype=np.uint8)   # incl. characters outside mydict
     chr1 = alphabet[rng.integers(0, len(alphabet), size=70_001)].tobytes().decode()
