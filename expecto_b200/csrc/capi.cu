@@ -22,6 +22,7 @@ using namespace bx;
 
 namespace {
 
+constexpr int kMaxDevices = 64;
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
 
@@ -162,10 +163,12 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
   if (A_MODE != 0) tmA = tmB;  // unused: the producer warp builds the A tile in shared memory
   else if (int r = make_tmap(&tmA, c->dtype, a, a_rows, a_cols, a_cols, Cfg::A_ROWS)) return r;
   auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI, A_MODE>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  // function attributes are per device: one flag per device, so contexts on several GPUs of one process all get it
+  static std::atomic<bool> attr_set[kMaxDevices];
+  if (c->device < 0 || c->device >= kMaxDevices) return fail(BX_E_ARG, "device index %d out of range", c->device);
+  if (!attr_set[c->device].load(std::memory_order_acquire)) {
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set = true;
+    attr_set[c->device].store(true, std::memory_order_release);
   }
   p.m_tiles = (p.m_rows + 128 * CG - 1) / (128 * CG);
   p.n_chunks = p.n_total / BN;
@@ -861,10 +864,13 @@ int bx_decay_transform_fixed(const float* probs_dev, const float* weights_dev, i
   if (!probs_dev || !weights_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
   const size_t smem = (size_t)(10 * n_shifts + (kTfSlices - 1) * 20 * kTfF) * sizeof(float);
   dim3 grid((kFeat2 + kTfF - 1) / kTfF, n_genes), block(kTfF, kTfSlices);
-  static bool attr_set = false;
-  if (!attr_set) {
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  static std::atomic<bool> attr_set[kMaxDevices];  // per device, like the GEMM launcher's
+  if (dev < 0 || dev >= kMaxDevices) return fail(BX_E_ARG, "device index %d out of range", dev);
+  if (!attr_set[dev].load(std::memory_order_acquire)) {
     CK(cudaFuncSetAttribute(decay_fixed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-    attr_set = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   decay_fixed_kernel<<<grid, block, smem, (cudaStream_t)stream>>>(probs_dev, weights_dev, n_shifts, out_dev);
   g_launches++;

@@ -271,5 +271,6 @@ def chromatin_outputs(probs: torch.Tensor, n_var: int, average: bool = False):
     alt = torch.empty_like(ref)
     diff = torch.empty_like(ref)
     fn = lib().bx_chromatin_outputs_avg if average else lib().bx_chromatin_outputs
-    check(fn(probs.data_ptr(), n_var, ref.data_ptr(), alt.data_ptr(), diff.data_ptr(), _stream_ptr(probs.device)))
+    with torch.cuda.device(probs.device):  # context-free entry point: launches on the current device
+        check(fn(probs.data_ptr(), n_var, ref.data_ptr(), alt.data_ptr(), diff.data_ptr(), _stream_ptr(probs.device)))
     return ref, alt, diff

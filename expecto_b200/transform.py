@@ -49,7 +49,8 @@ def decay_transform_fixed(probs: torch.Tensor, weights, out: torch.Tensor | None
     probs = probs.contiguous()
     if out is None:
         out = torch.empty((G, N_BASIS * N_FEATURES), dtype=torch.float32, device=probs.device)
-    check(lib().bx_decay_transform_fixed(probs.data_ptr(), w.data_ptr(), G, S, out.data_ptr(), _stream(probs)))
+    with torch.cuda.device(probs.device):  # the context-free entry points launch on the current device
+        check(lib().bx_decay_transform_fixed(probs.data_ptr(), w.data_ptr(), G, S, out.data_ptr(), _stream(probs)))
     return out
 
 
@@ -61,7 +62,8 @@ def strand_average(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Te
     x = x.contiguous()
     if out is None:
         out = torch.empty((n, N_FEATURES), dtype=torch.float32, device=x.device)
-    check(lib().bx_strand_average(x.data_ptr(), n, out.data_ptr(), _stream(x)))
+    with torch.cuda.device(x.device):
+        check(lib().bx_strand_average(x.data_ptr(), n, out.data_ptr(), _stream(x)))
     return out
 
 
@@ -105,8 +107,9 @@ def decay_transform_variant(x: torch.Tensor, dist, strand, shifts=None, out: tor
     x, d, sg, sh, n, S = _variant_args(x, dist, strand, shifts)
     if out is None:
         out = torch.empty((n, N_BASIS * N_FEATURES), dtype=torch.float32, device=x.device)
-    check(lib().bx_decay_transform_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), n, S,
-                                           out.data_ptr(), _stream(x)))
+    with torch.cuda.device(x.device):
+        check(lib().bx_decay_transform_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), n, S,
+                                               out.data_ptr(), _stream(x)))
     return out
 
 
@@ -120,6 +123,7 @@ def decay_score_variant(x: torch.Tensor, dist, strand, weights, offsets, shifts=
     if off.numel() != m:
         raise ValueError("one offset per model")
     out = torch.empty((n, m), dtype=torch.float32, device=x.device)
-    check(lib().bx_decay_score_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), w.data_ptr(),
-                                       off.data_ptr(), n, S, m, out.data_ptr(), _stream(x)))
+    with torch.cuda.device(x.device):
+        check(lib().bx_decay_score_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), w.data_ptr(),
+                                           off.data_ptr(), n, S, m, out.data_ptr(), _stream(x)))
     return out

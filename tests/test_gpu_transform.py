@@ -239,3 +239,26 @@ def test_predict_cli_matches_predict_script(engine, cfg1_genome, golden, tmp_pat
     assert (tmp_path / "pred_fused" / "snps_hg19.vcf").read_bytes() == (out / "snps_hg19.vcf").read_bytes()
     for name in ("sed.tsv", "sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
         assert (tmp_path / "pred_fused" / name).read_bytes() == (tmp_path / "pred" / name).read_bytes(), name
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_devices_in_one_process(weights_f16):
+    """Contexts on two GPUs of ONE process (the C ABI allows one context per GPU): kernel attributes are set per
+    device, context-free entry points follow the tensors' device; both GPUs give bit-identical results."""
+    from expecto_b200 import synth
+    from expecto_b200.engine import BelugaEngine, chromatin_outputs
+    from expecto_b200.transform import decay_transform_fixed, fixed_pos_weights
+    x = torch.from_numpy(synth.random_onehot(8, seed=9))
+    outs = []
+    for d in (0, 1):
+        eng = BelugaEngine(d, dtype="f16", cta_group=2, capacity=64)
+        eng.load_state_dict(weights_f16)
+        probs = eng.forward_onehot(x.to(f"cuda:{d}"))
+        ref, alt, diff = chromatin_outputs(probs, 2)
+        feats = decay_transform_fixed(torch.rand((3, 200, 2, 2002), generator=torch.Generator().manual_seed(1)).to(f"cuda:{d}"),
+                                      fixed_pos_weights())
+        torch.cuda.synchronize(d)
+        outs.append((probs.cpu(), diff.cpu(), feats.cpu()))
+        eng.close()
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
