@@ -41,6 +41,22 @@ int fail(int code, const char* fmt, ...) {
       return fail(BX_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
   } while (0)
 
+// Entry points run on their context's device and put the caller's current device back on return.
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    err = cudaSetDevice(device);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+#define ON_DEVICE(dev)          \
+  DeviceGuard _guard(dev);      \
+  CK(_guard.err)
+
 PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 
 int load_driver_entry() {
@@ -438,7 +454,7 @@ int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx
   if (prop.major != 10)
     return fail(BX_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major,
                 prop.minor);
-  CK(cudaSetDevice(device));
+  ON_DEVICE(device);
   if (int r = load_driver_entry()) return r;
   bx_ctx* c = new bx_ctx();
   c->device = device;
@@ -466,7 +482,7 @@ int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx
 
 int bx_ctx_destroy(bx_ctx* c) {
   if (!c) return 0;
-  cudaSetDevice(c->device);
+  DeviceGuard guard(c->device);
   for (int i = 0; i < 6; ++i) { cudaFree(c->wconv[i]); cudaFree(c->bconv[i]); }
   cudaFree(c->wfc1); cudaFree(c->bfc1); cudaFree(c->wfc2); cudaFree(c->bfc2);
   for (int i = 0; i < 7; ++i) cudaFree(c->act[i]);
@@ -542,7 +558,7 @@ int bx_ctx_load_weights(bx_ctx* c, const float* const w[8], const float* const b
   if (!c || !w || !b) return fail(BX_E_ARG, "null argument");
   for (int i = 0; i < 8; ++i)
     if (!w[i] || !b[i]) return fail(BX_E_ARG, "weight/bias %d is null", i);
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   return c->dtype == BX_DTYPE_F16 ? load_weights_t<__half>(c, w, b) : load_weights_t<__nv_bfloat16>(c, w, b);
 }
 
@@ -560,7 +576,7 @@ int bx_encode_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t*
   if (n == 0) return 0;  // empty input: nothing to do, buffers may be null
   if (!descs_dev || !alleles_dev || !out_dev) return fail(BX_E_ARG, "invalid arguments");
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   encode_onehot_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(descs_dev, alleles_dev, c->bases2, c->nmask, c->n_bases,
                                                              out_dev);
   g_launches++;
@@ -648,7 +664,7 @@ int bx_forward_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t
   if (!descs_dev || !alleles_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   cudaStream_t st = (cudaStream_t)stream;
   for (int off = 0; off < n; off += c->cap) {
     const int m = std::min(c->cap, n - off);
@@ -663,7 +679,7 @@ int bx_forward_onehot(bx_ctx* c, const uint8_t* onehot_dev, int n, float* probs_
   if (n == 0) return 0;
   if (!onehot_dev || !probs_dev) return fail(BX_E_ARG, "invalid arguments");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   cudaStream_t st = (cudaStream_t)stream;
   for (int off = 0; off < n; off += c->cap) {
     const int m = std::min(c->cap, n - off);
@@ -679,7 +695,7 @@ int bx_forward_onehot_host(bx_ctx* c, const uint8_t* onehot_host, int n, float* 
   if (n == 0) return 0;
   if (!onehot_host || !probs_host) return fail(BX_E_ARG, "invalid arguments");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   const size_t in_chunk = (size_t)c->cap * 4 * BX_WINDOW, out_chunk = (size_t)c->cap * BX_FEATURES * sizeof(float);
   if (int r = ensure_pipe(c, in_chunk, out_chunk, 0)) return r;
   int i = 0;
@@ -714,7 +730,7 @@ int bx_chromatin_shift_host(bx_ctx* c, const bx_window_desc* descs_host, const u
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
   if (c->cap < 4) return fail(BX_E_ARG, "context capacity must be >= 4 windows");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   const int vcap = c->cap / 4;  // variants per chunk (4 windows each)
   const size_t rows_chunk = (size_t)(average ? 1 : 2) * vcap;
   const size_t out_chunk = 3 * rows_chunk * BX_FEATURES * sizeof(float);
@@ -785,7 +801,7 @@ int bx_ctx_profile(bx_ctx* c, int enable) {
 
 int bx_ctx_profile_read(bx_ctx* c, double* ms_out, int64_t* count_out, int reset) {
   if (!c || !ms_out || !count_out) return fail(BX_E_ARG, "null argument");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   for (auto& r : c->prof_recs) {
     CK(cudaEventSynchronize(r.e1));
     float ms = 0.f;
@@ -814,7 +830,7 @@ int bx_debug_activation(bx_ctx* c, int layer, int n, void* dst_dev, int64_t* cou
 int bx_debug_run_layer(bx_ctx* c, int layer, int n, float* probs_dev, void* stream) {
   if (!c || layer < 0 || layer > 7 || n < 1 || n > c->cap) return fail(BX_E_ARG, "invalid arguments");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (layer < 6) return run_conv(c, layer, n, st);
   if (layer == 6) return run_fc1(c, n, st);
@@ -1197,7 +1213,7 @@ int bx_forward_segments(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_
     return fail(BX_E_ARG, "segment mode needs seg_len == 2000 + 200*(n_shifts-1) and 1 <= n_shifts <= 200");
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   return forward_segments_impl(c, descs_dev, nullptr, alleles_dev, n_groups, segs_per_group, seg_len, 0, 0, n_shifts,
                                k_of_shift, shift_major, probs_dev, (cudaStream_t)stream);
 }
@@ -1216,7 +1232,7 @@ int bx_forward_segments_delta(bx_ctx* c, const bx_window_desc* ref_descs_dev, co
                           "of 16 (patch_len=%d patch_row0=%d seg_len=%d)", patch_len, patch_row0, seg_len);
   if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
   if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
-  CK(cudaSetDevice(c->device));
+  ON_DEVICE(c->device);
   return forward_segments_impl(c, ref_descs_dev, patch_descs_dev, alleles_dev, n_groups, 4, seg_len, patch_len,
                                patch_row0, n_shifts, k_of_shift, shift_major, probs_dev, (cudaStream_t)stream);
 }

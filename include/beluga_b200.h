@@ -5,6 +5,9 @@
  * replaces.  All functions return 0 on success or a negative code (see BX_E_*); bx_last_error()
  * gives the message.  No exceptions cross the boundary, the caller owns every buffer, device
  * pointers are plain `void*` (e.g. torch.Tensor.data_ptr()), streams are cudaStream_t as `void*`.
+ * Entry points that take a context run on that context's device and restore the caller's current device before
+ * returning; the context-free ones (bx_chromatin_outputs*, bx_strand_average, bx_decay_*, bx_fasta_*) launch on the
+ * caller's current device, which must own the buffers.
  * There is NO CPU fallback: every compute entry point fails with BX_E_CUDA when no sm_100 device
  * is present.
  */
