@@ -74,7 +74,10 @@ struct GemmCfg {
   static constexpr int B_BYTES = TPS * B_TAP_BYTES;
   static constexpr int BIAS_BYTES = 8192;                // fp32 bias vector staged once per CTA
   static constexpr int SMEM_BUDGET = 227 * 1024 - 2048 - BIAS_BYTES;  // barriers + 1 KB alignment slack + bias
-  static constexpr int SA = (TAPS > 1) ? 3 : 4;
+  // Stages of the A ring.  The dense layers (one tap, N = 256: 16 KB + 16 KB per stage and CTA) stream every operand
+  // byte exactly once, so their rate is bytes in flight / L2 latency: six stages instead of four took FC1 from 0.96
+  // to 0.83 ms per 4096 windows (tools/dense_sweep.py); conv1 (one tap, N = 160) gains nothing from more than four.
+  static constexpr int SA = (TAPS > 1) ? 3 : (BLOCK_N == 256 ? 6 : 4);
   static constexpr int SB_MAX = (SMEM_BUDGET - SA * A_BYTES) / B_BYTES;
   static constexpr int SB = (TAPS > 1) ? (SB_MAX > 8 ? 8 : SB_MAX) : (SB_MAX > SA ? SA : SB_MAX);
   static constexpr int NBUF = 512 / BLOCK_N;
