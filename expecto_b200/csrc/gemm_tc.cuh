@@ -165,8 +165,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<CG>(tmem_slot, 512);
-  if (p.bias != nullptr)
-    for (int i = threadIdx.x; i < p.n_total; i += blockDim.x) sbias[i] = p.bias[i];
+  if (p.bias != nullptr) {  // n_total is a multiple of 16 and the bias vectors are cudaMalloc'd: 16-byte loads
+    const float4* b4 = reinterpret_cast<const float4*>(p.bias);
+    float4* s4 = reinterpret_cast<float4*>(sbias);
+    for (int i = threadIdx.x; i < (p.n_total >> 2); i += blockDim.x) s4[i] = __ldg(b4 + i);
+  }
   tc_fence_before();
   if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
   tc_fence_after();
@@ -453,13 +456,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                  __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
           }
         } else {  // EPI_BIAS_SIGMOID
-          float* o = reinterpret_cast<float*>(p.out) + obase + c * 16;
+          // rows are ld_out = 2002 floats apart (8-byte aligned) and n_store is even: float2 stores, half the
+          // store instructions of the scalar form (each one touches 32 rows, so the LSU sees 32 sectors either way)
+          float2* o = reinterpret_cast<float2*>(reinterpret_cast<float*>(p.out) + obase + c * 16);
           if (valid) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
+            for (int i = 0; i < 16; i += 2) {
               if (n0 + c * 16 + i < p.n_store) {
-                const float z = __uint_as_float(v[i]) + sbias[n0 + c * 16 + i];
-                o[i] = 1.f / (1.f + __expf(-z));
+                const float z0 = __uint_as_float(v[i]) + sbias[n0 + c * 16 + i];
+                const float z1 = __uint_as_float(v[i + 1]) + sbias[n0 + c * 16 + i + 1];
+                o[i >> 1] = make_float2(1.f / (1.f + __expf(-z0)), 1.f / (1.f + __expf(-z1)));
               }
             }
           }
