@@ -227,6 +227,19 @@ def consensus_features(preds, shifts=None):
     return np.concatenate([np.zeros((features.shape[0], 10, 1)), features], axis=2).reshape((-1, 20030))
 
 
+def ref_all_genes_scores(records, strands, sd, weights, bias, base_score, shifts=None):
+    """geuvadis_predict_ref_all_genes.py:61-102: one reference record per gene -> padded, 200 shifted windows, Beluga
+    on the forward windows and their reverse complements, the halves averaged (:77), the legacy 20030-wide features
+    (:80-96) and the gblinear score (:98); float32 [n_genes] as ``np.array(list).squeeze()`` leaves them (:100)."""
+    shifts = list(range(-20000, 20000, 200)) if shifts is None else shifts
+    out = []
+    for (rid, seq), strand in zip(records, strands):
+        preds = consensus_chromatin(consensus_pad(rid, seq), strand, sd, shifts)
+        feats = consensus_features(preds[None], shifts)
+        out.append(np.asarray(gblinear_predict(feats, weights, bias, base_score), dtype=np.float32))
+    return np.array(out).squeeze()
+
+
 def replicate_prediction(genome, chrom, tss, strand, sd, shifts=None, chunk=50):
     """replicate_expecto_features.py:65-83: float32 [S,2002] = 0.5 * (prediction + rc prediction)."""
     enc = encode_seqs(tss_windows(genome, chrom, tss, strand, shifts), concat_rc=False)

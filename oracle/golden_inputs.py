@@ -144,6 +144,31 @@ def write_consensus_dir(root: str):
     return os.path.join(root, "consensus"), genes_file, names
 
 
+def consensus_ref_record(gene_index: int):
+    """(record id, sequence as stored in ``{gene}/ref.fa``) — the one reference-genome record per gene that
+    geuvadis_predict_ref_all_genes.py reads; the second gene's record misses its last 12,345 bases (N-padded by the
+    reference, the padding reaching no window) and is lower case in part (the reference upper-cases)."""
+    rng = np.random.default_rng(100 + gene_index)
+    base = synth.random_sequence(rng, CONSENSUS_LEN)      # same base sequence as consensus_records()
+    chrom = CONSENSUS_GENES[gene_index][1]
+    start = 500_000 + 1000 * gene_index
+    rid = f"{chrom}:{start}-{start + CONSENSUS_LEN - 1}"
+    return (rid, base) if gene_index == 0 else (rid, base[:CONSENSUS_LEN - 12_345])
+
+
+def write_ref_fastas(consensus_dir: str):
+    """{consensus_dir}/{gene}/ref.fa for every gene of CONSENSUS_GENES (the directory may already hold samples/)."""
+    import os
+    for gi, row in enumerate(CONSENSUS_GENES):
+        gene = (row[3] or row[0]).lower()
+        os.makedirs(os.path.join(consensus_dir, gene), exist_ok=True)
+        rid, seq = consensus_ref_record(gi)
+        with open(os.path.join(consensus_dir, gene, "ref.fa"), "w") as f:
+            f.write(f">{rid} reference\n")
+            for i in range(0, len(seq), 70):
+                f.write(seq[i:i + 70] + "\n")
+
+
 def consensus_model():
     """Seeded gblinear model over the 20030-wide legacy layout: (weights float32 [20030], bias, base_score)."""
     rng = np.random.default_rng(CONSENSUS_MODEL_SEED)

@@ -10,7 +10,8 @@ reference computes here is computed by the reference's own, unmodified code:
 * ``chromatin.py``, ``compute_expecto_features.py`` and ``predict.py`` run as subprocesses in a scratch
   directory holding synthetic ``resources/hg19.fa`` + ``resources/deepsea.beluga.pth``, behind the import shims in
   oracle/shims (pyfasta, h5py, liftover, xgboost, matplotlib, natsort, Bio, seaborn — third-party packages absent
-  from this image); ``geuvadis_predict_consensus.py`` and ``replicate_expecto_features.py`` run the same way.
+  from this image); ``geuvadis_predict_consensus.py``, ``geuvadis_predict_ref_all_genes.py`` and
+  ``replicate_expecto_features.py`` run the same way.
 
 Every stage asserts that oracle/beluga_oracle.py reproduces the reference output, then stores a small slice
 as a fixture.  Usage:  python oracle/make_golden.py [--workdir /tmp/bx_golden] [--skip-scripts]
@@ -337,6 +338,31 @@ def stage_consensus(work, sd):
           f"oracle == reference (chromatin within 2e-6, scores within 1e-5); fixture written")
 
 
+def stage_ref_all_genes(work, sd):
+    """geuvadis_predict_ref_all_genes.py as a subprocess on one ref.fa per gene (stage_consensus's directory)."""
+    import io
+    import pandas as pd
+    root = os.path.join(work, "consensus_in")
+    cdir, genes_file = os.path.join(root, "consensus"), os.path.join(root, "genes.csv")
+    if not os.path.exists(genes_file):
+        cdir, genes_file, _ = GI.write_consensus_dir(root)
+    GI.write_ref_fastas(cdir)
+    w, bias, base = GI.consensus_model()
+    np.savez(os.path.join(work, "consensus_model.npz"), weights=w, bias=bias, base_score=base)
+    shutil.rmtree(os.path.join(work, "out_ref_all"), ignore_errors=True)
+    run_ref_script("geuvadis_predict_ref_all_genes.py", ["consensus_model.npz", cdir, genes_file, "-o", "out_ref_all"], work)
+    text = open(os.path.join(work, "out_ref_all", "ref_preds.csv")).read()
+    df = pd.read_csv(io.StringIO(text))
+    assert list(df.columns) == ["genes", "ref_preds"]
+    assert list(df["genes"]) == [row[3] or row[0] for row in GI.CONSENSUS_GENES]      # original case, ens_id filled in
+    ours = O.ref_all_genes_scores([GI.consensus_ref_record(i) for i in range(len(GI.CONSENSUS_GENES))],
+                                  [row[4] for row in GI.CONSENSUS_GENES], sd, w, float(bias), float(base))
+    err = np.abs(ours - df["ref_preds"].to_numpy()).max()
+    assert err < 1e-5, f"ref_all_genes restatement differs: {err}"
+    np.savez_compressed(os.path.join(GOLD, "ref_all_genes_golden.npz"), csv=np.array(text))
+    print(f"[ref all genes] {len(df)} genes: oracle == reference (scores within 1e-5); fixture written")
+
+
 def stage_replicate(work, sd, genome):
     """replicate_expecto_features.py as a subprocess on the two compute_expecto_features genes."""
     genes = GI.cfg4_genes()
@@ -371,6 +397,7 @@ def main():
     ap.add_argument("--workdir", default="/tmp/bx_golden")
     ap.add_argument("--skip-scripts", action="store_true", help="only the import-level stages (fast)")
     ap.add_argument("--only-closest", action="store_true", help="only the make_closest_genes_file.py stage")
+    ap.add_argument("--only-ref-all-genes", action="store_true", help="only the geuvadis_predict_ref_all_genes.py stage")
     ap.add_argument("--only-consensus", action="store_true",
                     help="only the geuvadis_predict_consensus.py / replicate_expecto_features.py stages")
     args = ap.parse_args()
@@ -379,10 +406,16 @@ def main():
         os.makedirs(args.workdir, exist_ok=True)
         stage_closest_genes(args.workdir)
         return
+    if args.only_ref_all_genes:
+        sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
+        prepare_workdir(args.workdir, sd)
+        stage_ref_all_genes(args.workdir, sd)
+        return
     if args.only_consensus:
         sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
         genome = prepare_workdir(args.workdir, sd)
         stage_consensus(args.workdir, sd)
+        stage_ref_all_genes(args.workdir, sd)
         stage_replicate(args.workdir, sd, genome)
         return
     stage_encode()
@@ -395,6 +428,7 @@ def main():
         stage_predict(args.workdir)
         stage_closest_genes(args.workdir)
         stage_consensus(args.workdir, sd)
+        stage_ref_all_genes(args.workdir, sd)
         stage_replicate(args.workdir, sd, genome)
     print("golden fixtures written to", GOLD)
 

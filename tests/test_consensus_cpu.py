@@ -164,3 +164,39 @@ def test_replicate_reads_seven_columns(tmp_path):
     p.write_text("id,symbol\nG1,S\n")
     with pytest.raises(ValueError):
         ref.read_genes(str(p))
+
+
+# ---- geuvadis_predict_ref_all_genes.py -----------------------------------------------------------------------------
+def _golden_ref_csv(golden):
+    import io
+    import pandas as pd
+    return pd.read_csv(io.StringIO(str(golden("ref_all_genes_golden.npz")["csv"])))
+
+
+def test_ref_all_genes_host_side(tmp_path, consensus_dir):
+    from expecto_b200 import geuvadis_predict_ref_all_genes as rag
+    cdir, genes_file, names = consensus_dir
+    GI.write_ref_fastas(cdir)
+    df = rag.read_genes(genes_file)
+    # the symbol falls back to the ens_id and keeps its case (geuvadis_predict_ref_all_genes.py:57-59)
+    assert list(df.index) == ["Abc1", "ENSG00000000002"] and list(df["strand"]) == ["+", "-"]
+    assert [g.lower() for g in df.index] == names
+    for gi, gene in enumerate(names):
+        seq = rag.read_ref_sequence(f"{cdir}/{gene}/ref.fa")
+        assert seq == O.consensus_pad(*GI.consensus_ref_record(gi)) and len(seq) == O.ENFORMER_SEQ_LENGTH
+        assert seq == seq.upper()
+    two = tmp_path / "two.fa"
+    two.write_text(">chr1:1-393216\nACGT\n>chr1:1-393216\nACGT\n")
+    with pytest.raises(AssertionError):
+        rag.read_ref_sequence(str(two))                                 # :117-118 exactly one record
+
+
+def test_ref_all_genes_oracle_matches_reference_csv(golden):
+    """One gene (400 windows through the CPU Beluga): the restatement reproduces the reference script's score."""
+    from expecto_b200 import synth
+    want = _golden_ref_csv(golden)
+    assert list(want.columns) == ["genes", "ref_preds"] and list(want["genes"]) == ["Abc1", "ENSG00000000002"]
+    sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
+    w, bias, base = GI.consensus_model()
+    got = O.ref_all_genes_scores([GI.consensus_ref_record(0)], [GI.CONSENSUS_GENES[0][4]], sd, w, float(bias), float(base))
+    assert got.shape == () and abs(float(got) - float(want["ref_preds"][0])) < 1e-5

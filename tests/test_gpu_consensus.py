@@ -102,3 +102,31 @@ def test_replicate_cli_matches_reference_script(engine, cfg1_genome, golden, tmp
     for i in range(len(genes)):
         red = np.sum(O.fixed_pos_weights()[:, :, None] * outs["segments"][i][None].astype(np.float64), axis=1).flatten()
         assert np.abs(red - feats[i]).max() <= 1e-4 * np.abs(red).max()
+
+
+def test_ref_all_genes_cli_matches_reference_script(engine, golden, tmp_path):
+    """geuvadis_predict_ref_all_genes.py drop-in: same ref_preds.csv (genes, order, case), scores within the bound the
+    2e-3 probability tolerance implies; segment mode == per-window mode bit for bit."""
+    import io
+    import pandas as pd
+    from expecto_b200 import geuvadis_predict_ref_all_genes as rag
+    want = pd.read_csv(io.StringIO(str(golden("ref_all_genes_golden.npz")["csv"])))
+    cdir, genes_file, names = GI.write_consensus_dir(str(tmp_path / "in"))
+    GI.write_ref_fastas(cdir)
+    w, bias, base = GI.consensus_model()
+    model = str(tmp_path / "model.npz")
+    np.savez(model, weights=w, bias=bias, base_score=base)
+    outs = {}
+    for mode in ("segments", "windows"):
+        args = rag.build_parser().parse_args([model, cdir, genes_file, "-o", str(tmp_path / mode), "--mode", mode,
+                                              "--genes_per_batch", "1" if mode == "windows" else "64"])
+        df = rag.run(args, engine=engine)
+        text = open(tmp_path / mode / "ref_preds.csv").read()
+        got = pd.read_csv(io.StringIO(text))
+        assert list(got.columns) == ["genes", "ref_preds"] and list(got["genes"]) == list(want["genes"])
+        assert df["ref_preds"].dtype == np.float32
+        outs[mode] = text
+        w_abs = np.abs(O.fixed_pos_weights()).sum(axis=1)
+        bound = float((np.abs(w.reshape(10, 2003)[:, 1:]) * w_abs[:, None]).sum()) * PROB_TOL
+        assert np.abs(got["ref_preds"].to_numpy() - want["ref_preds"].to_numpy()).max() <= bound
+    assert outs["segments"] == outs["windows"]
