@@ -78,6 +78,23 @@ def stage_encode():
             a = ref_fetch(chrom, pos, ref, alt, shift=shift)
             assert a == O.fetch_seqs(g, chrom, pos, ref, alt, shift=shift), ("fetchSeqs restatement differs", shift)
             assert np.array_equal(ref_encode([a[0], a[1]]), O.encode_seqs([a[0], a[1]]))
+    # random variants of every kind at random shifts (the generator of tools/fuzz_segments.py and of
+    # tests/test_windows_cpu.py::test_random_variants_descriptors_match_oracle): oracle == the reference's own functions
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("fuzz_segments", os.path.join(ROOT, "tools", "fuzz_segments.py"))
+    fuzz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fuzz)
+    n_random = 0
+    for seed in (0, 1, 2):
+        rng = np.random.default_rng(100 + seed)
+        rrows = fuzz.random_variants(rng, genome, 40, margin=3200)
+        for shift in [0] + [int(x) for x in rng.choice(np.arange(-2200, 2201, 50), size=4, replace=False)]:
+            for chrom, pos, _id, ref, alt in rrows:
+                a = ref_fetch(chrom, pos, ref, alt, shift=shift)
+                assert a == O.fetch_seqs(g, chrom, pos, ref, alt, shift=shift), ("fetchSeqs restatement differs", ref, alt, shift)
+                assert np.array_equal(ref_encode([a[0], a[1]]), O.encode_seqs([a[0], a[1]]))
+                n_random += 1
+    print(f"[encode] {n_random} random variant-shifts: oracle == reference fetchSeqs / encodeSeqs")
     # odd-length / short strings straight into the encoder (crop arithmetic, chromatin.py:164)
     rng = np.random.default_rng(5)
     odd = [synth.random_sequence(rng, n) for n in (2000, 2001, 2099, 2100, 2101, 2103, 2110, 1990, 1999)]

@@ -1,4 +1,6 @@
 """Host logic of kernel 1 against the oracle and the reference-generated fixture (bit-exact)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -269,3 +271,32 @@ def test_fasta_cache_is_written_atomically(tmp_path, small_genome):
     PackedGenome.from_fasta(str(fa))
     left = sorted(p.name for p in tmp_path.iterdir())
     assert left == ["g.fa", "g.fa.bx2.npz"]   # no temporary file left behind
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_random_variants_descriptors_match_oracle(small_genome, seed):
+    """Randomised host-side version of tools/fuzz_segments.py: SNVs, MNVs, insertions up to 300 bp, deletions up to
+    120 bp, long ref alleles, ref mismatches, N / lower-case alleles at random shifts (incl. beyond +-1049): the window
+    descriptors decode to exactly what fetchSeqs + encodeSeqs (chromatin.py:138-209, restated in the oracle) produce."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "fuzz_segments", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "fuzz_segments.py"))
+    fuzz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fuzz)
+    rng = np.random.default_rng(100 + seed)
+    rows = fuzz.random_variants(rng, small_genome, 40, margin=3200)
+    pg = PackedGenome.from_sequences(small_genome)
+    dg = O.DictGenome(small_genome)
+    chroms = [r[0] for r in rows]
+    pos = np.array([r[1] for r in rows])
+    refs, alts = [r[3] for r in rows], [r[4] for r in rows]
+    shifts = [0] + [int(s) for s in rng.choice(np.arange(-2200, 2201, 50), size=4, replace=False)]
+    n = len(rows)
+    for shift in shifts:
+        descs, codes = chromatin_window_descs(pg, chroms, pos, refs, alts, shift)
+        ours = decode_descs(pg, descs, codes).reshape(n, 4, 4, 2000)
+        seqs = [O.fetch_seqs(dg, c, int(p), r, a, shift=shift) for c, p, r, a in zip(chroms, pos, refs, alts)]
+        ref_enc = O.encode_seqs([s[0] for s in seqs])
+        alt_enc = O.encode_seqs([s[1] for s in seqs])
+        assert np.array_equal(ours[:, 0], ref_enc[:n]) and np.array_equal(ours[:, 1], ref_enc[n:]), shift
+        assert np.array_equal(ours[:, 2], alt_enc[:n]) and np.array_equal(ours[:, 3], alt_enc[n:]), shift
