@@ -507,7 +507,6 @@ def run(args, engine=None, genome=None) -> dict:
     import torch
 
     from . import shard
-    from .genome import PackedGenome
     from .hdf5 import H5Writer
     from .windows import allele_match_counts
 

@@ -135,7 +135,6 @@ def run(args, engine=None, genome=None) -> str:
     (expecto_b200/shard.py: no collective on the forward path), the feature rows are gathered on rank 0 over NCCL and
     rank 0 writes the ``.npy``."""
     from . import shard
-    from .genome import PackedGenome
     from .transform import TSS_SHIFTS, fixed_pos_weights
 
     if args.windowsize != 2000:

@@ -95,7 +95,6 @@ def gene_predictions(engine, genome, genes, shifts, genes_per_batch: int = 32, m
 def run(args, engine=None, genome=None) -> int:
     """The whole script; returns the number of files this process wrote."""
     from . import shard
-    from .genome import PackedGenome
     from .transform import TSS_SHIFTS
 
     if args.windowsize != 2000:
