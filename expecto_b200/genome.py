@@ -210,6 +210,7 @@ class PackedGenome:
                     header = line[1:].decode("ascii", "replace").strip()
                     name = header.split()[0] if header else f"contig{k}"
                     bodies.append((name, min(int(s0) + len(line), e), e))
+            bodies = list({name: (name, b0, e) for name, b0, e in bodies}.values())  # a repeated name: the last record wins
             offs = [torch.empty(int(L.bx_fasta_blocks(b0, e)) + 1, dtype=torch.int64, device=dev) for _, b0, e in bodies]
             n_out = C.c_int64(0)
             for (name, b0, e), o in zip(bodies, offs):
