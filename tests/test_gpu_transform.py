@@ -262,3 +262,39 @@ def test_two_devices_in_one_process(weights_f16):
         eng.close()
     for a, b in zip(*outs):
         assert torch.equal(a, b)
+
+
+def test_output_buffers_are_written_inside_their_bounds(engine):
+    """Guard rows around the caller's output buffers (compute-sanitizer is closed on this pool): the FC2 epilogue
+    (float2 stores, 2002-column rows), the per-window / segment forwards and both decay transforms must leave the rows
+    before and after their output untouched, for batch sizes that do not fill a tile."""
+    from expecto_b200 import synth
+    from expecto_b200.transform import decay_transform_fixed, decay_transform_variant, fixed_pos_weights
+    G, SENT = 3, -123.25
+
+    def guarded(rows, cols):
+        buf = torch.full((rows + 2 * G, cols), SENT, dtype=torch.float32, device="cuda")
+        return buf, buf[G:G + rows]
+
+    def intact(buf, rows):
+        return bool((buf[:G] == SENT).all() and (buf[G + rows:] == SENT).all())
+
+    for n in (1, 37, 129):
+        x = torch.from_numpy(synth.random_onehot(n, seed=n)).cuda()
+        buf, out = guarded(n, 2002)
+        engine.forward_onehot(x, out)
+        torch.cuda.synchronize()
+        assert intact(buf, n) and bool(((out > 0) & (out < 1)).all())
+        assert torch.equal(out, engine.forward_onehot(x))
+    probs = torch.rand((5, 200, 2, 2002), dtype=torch.float32, device="cuda")
+    buf, out = guarded(5, 20020)
+    decay_transform_fixed(probs, fixed_pos_weights(), out=out)
+    torch.cuda.synchronize()
+    assert intact(buf, 5) and torch.equal(out, decay_transform_fixed(probs, fixed_pos_weights()))
+    xs = torch.rand((9, 7, 2002), dtype=torch.float32, device="cuda")
+    dist = np.array([-900.0, -1.0, 0.0, 1.0, 350.0, 12345.0, -40000.0])
+    strand = np.array(["+", "-", "+", "-", "+", "-", "+"])
+    buf, out = guarded(7, 20020)
+    decay_transform_variant(xs, dist, strand, out=out)
+    torch.cuda.synchronize()
+    assert intact(buf, 7) and torch.equal(out, decay_transform_variant(xs, dist, strand))
