@@ -121,3 +121,27 @@ def test_model_list_columns_round_trip(tmp_path):
         back = back.sort_values("index").reset_index(drop=True)
         for i in range(5):
             assert np.array_equal(back[f"SED_model{i}.save"].values.astype(np.float32), extra[:, i], equal_nan=True)
+
+
+def test_merge_predict_batched_natural_order_and_index(tmp_path):
+    """merge_predict_batched.py:22-26: chunk directories in natural order (chunk_2 before chunk_10), the chunk count
+    asserted, pandas' default index (restarting in every chunk) written as the first column."""
+    import pandas as pd
+    from expecto_b200 import merge_predict_batched as mpb
+    frames = {}
+    for k in (10, 2, 0, 1):
+        d = tmp_path / "batches" / f"chunk_{k}"
+        d.mkdir(parents=True)
+        frames[k] = pd.DataFrame({"index": [0, 1], 0: ["chr1", "chr2"], 1: [100 + k, 200 + k], "SED": [0.125 * k, -1.5e-7]})
+        frames[k].to_csv(d / "sed.tsv", sep="\t", index=False)
+    args = mpb.build_parser().parse_args(["--batch_dir", str(tmp_path / "batches"), "--n_chunks", "4", "-o", str(tmp_path / "out")])
+    out = mpb.run(args)
+    want = pd.concat([pd.read_csv(tmp_path / "batches" / f"chunk_{k}" / "sed.tsv", sep="\t") for k in (0, 1, 2, 10)])
+    import io
+    buf = io.StringIO()
+    want.to_csv(buf, sep="\t")
+    assert open(out).read() == buf.getvalue()
+    assert open(out).read().split("\n")[1].startswith("0\t0\tchr1\t100")
+    args.n_chunks = 5
+    with pytest.raises(AssertionError):
+        mpb.run(args)
