@@ -35,6 +35,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--dtype", default="f16", choices=["f16", "bf16"])
     p.add_argument("--device", type=int, default=0)
     p.add_argument("--genes_per_batch", type=int, default=32, help="genes per GPU batch (x400 windows)")
+    p.add_argument("--gather", default="nccl", choices=["nccl", "file"],
+                   help="multi-GPU (torchrun) only: gather the feature rows on rank 0 over NCCL, or every rank writes "
+                        "its own rows of the .npy (no collective; the widening to float64 and the write run in parallel)")
     p.add_argument("--mode", default="segments", choices=["segments", "windows"],
                    help="segments: conv stack once per gene and strand (shared activations, bit-identical)")
     p.add_argument("--tss_is_hg19", action="store_true", help="tss_file coordinates are already hg19 (no liftover)")
@@ -130,10 +133,28 @@ def gather_features(local: np.ndarray, n_total: int, device=None):
     return None if full is None else full.cpu().numpy().astype(np.float64)
 
 
+def write_feature_slabs(npy_path: str, local: np.ndarray, row0: int, n_total: int, rank: int) -> None:
+    """``--gather file``: rank 0 creates the ``.npy`` (the header ``np.save`` writes for a float64 [n_total, 20020]
+    C-order array, compute_expecto_features.py:128), every rank then writes its own contiguous row range in place."""
+    from . import shard
+
+    shape = (int(n_total), local.shape[1])
+    if rank == 0:
+        mm = np.lib.format.open_memmap(npy_path, mode="w+", dtype=np.float64, shape=shape)
+        del mm
+    shard.barrier()
+    mm = np.lib.format.open_memmap(npy_path, mode="r+")
+    if mm.shape != shape or mm.dtype != np.float64:
+        raise ValueError(f"{npy_path}: found {mm.dtype}{mm.shape}, expected float64{shape}")
+    mm[row0:row0 + local.shape[0]] = local
+    mm.flush()
+    del mm
+
+
 def run(args, engine=None, genome=None) -> str:
     """The whole script.  Under torchrun (one process per GPU) the genes are split into contiguous per-rank shards
-    (expecto_b200/shard.py: no collective on the forward path), the feature rows are gathered on rank 0 over NCCL and
-    rank 0 writes the ``.npy``."""
+    (expecto_b200/shard.py: no collective on the forward path); ``--gather nccl`` collects the feature rows on rank 0
+    over NCCL and rank 0 writes the ``.npy``, ``--gather file`` has every rank write its own rows of it."""
     from . import shard
     from .transform import TSS_SHIFTS, fixed_pos_weights
 
@@ -157,11 +178,14 @@ def run(args, engine=None, genome=None) -> str:
     lo, hi = shard.shard_range(len(genes), rank, world)
     feats = gene_features(engine, genome, genes[lo:hi], TSS_SHIFTS, fixed_pos_weights(TSS_SHIFTS), args.genes_per_batch,
                           mode=args.mode)
-    if world > 1:
-        feats = gather_features(feats, len(genes), getattr(engine, "device", None))
     path = f"{args.out_dir}/Xreducedall.2002.representative_tss_top"
-    if rank == 0:
-        np.save(path, feats)
+    if world > 1 and args.gather == "file":
+        write_feature_slabs(path + ".npy", feats, lo, len(genes), rank)
+    else:
+        if world > 1:
+            feats = gather_features(feats, len(genes), getattr(engine, "device", None))
+        if rank == 0:
+            np.save(path, feats)
     shard.barrier()
     return path + ".npy"
 

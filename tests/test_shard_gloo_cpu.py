@@ -84,7 +84,7 @@ def test_attach_rejects_mismatched_file(tmp_path):
         hdf5.H5Writer(p, {"diff": (6, F)}, create=False)
 
 
-def _features_worker(rank, world, port, n_genes, tmp):
+def _features_worker(rank, world, port, n_genes, tmp, gather="nccl"):
     """compute_expecto_features.run under two gloo ranks with the GPU part stubbed: gene shards, gather, one .npy."""
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
                       LOCAL_RANK=str(rank))
@@ -108,18 +108,23 @@ def _features_worker(rank, world, port, n_genes, tmp):
     cef.gene_features = fake_features
     cef.read_genes = lambda a, t, h=False: genes
     shard.init_distributed("gloo")
-    args = cef.build_parser().parse_args(["anno.csv", "tss.tsv", "-o", tmp])
+    args = cef.build_parser().parse_args(["anno.csv", "tss.tsv", "-o", tmp, "--gather", gather])
     path = cef.run(args, engine=e, genome=g)
     if rank == 0:
         got = np.load(path)
+        want = fake_features(None, None, genes, None, None, 0)
         assert got.dtype == np.float64 and got.shape == (n_genes, 20020)
-        assert np.array_equal(got, fake_features(None, None, genes, None, None, 0))
+        assert np.array_equal(got, want)
+        ref = os.path.join(tmp, "np_save.npy")          # the bytes np.save gives for the same matrix
+        np.save(ref, want)
+        assert open(path, "rb").read() == open(ref, "rb").read()
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("gather", ["nccl", "file"])
 @pytest.mark.parametrize("n_genes", [5, 1])
-def test_two_rank_feature_shards_gather_to_one_file(tmp_path, n_genes):
-    mp.spawn(_features_worker, args=(2, _free_port(), n_genes, str(tmp_path)), nprocs=2, join=True)
+def test_two_rank_feature_shards_gather_to_one_file(tmp_path, n_genes, gather):
+    mp.spawn(_features_worker, args=(2, _free_port(), n_genes, str(tmp_path), gather), nprocs=2, join=True)
 
 
 def _genome_worker(rank, world, port, fa):

@@ -77,6 +77,21 @@ def main():
                             "npy_bytes": os.path.getsize(path),
                             "note": "wall clock of the whole CLI run(): read genes, forward + transform on N GPUs, "
                                     "NCCL gather, np.save of the float64 matrix"}
+    # the same job with --gather file: every rank writes its own rows of the .npy (no collective)
+    shard.barrier()
+    args = cef.build_parser().parse_args([os.path.join(base, f"geneanno_{n_full}.csv"), tss_file, "-o",
+                                          os.path.join(base, "full_file"), "--gather", "file"])
+    torch.cuda.synchronize()
+    shard.barrier()
+    t0 = time.perf_counter()
+    path_f = cef.run(args, engine=eng, genome=pg)
+    dt_f = time.perf_counter() - t0
+    if rank == 0:
+        same = open(path, "rb").read() == open(path_f, "rb").read() if world > 1 else True
+        ok = ok and same
+        res["cfg4_full_gather_file"] = {"seconds": round(dt_f, 2), "windows_per_s": round(400 * n_full / dt_f),
+                                        "genes_per_s": round(n_full / dt_f, 1),
+                                        "npy_byte_identical_to_nccl_gather": bool(same)}
         print(json.dumps(res), flush=True)
     if world > 1:
         flag = torch.tensor([1 if ok else 0], device=eng.device)
