@@ -143,3 +143,22 @@ def test_chromatin_cli_edge_vcf_matches_reference_script(engine, cfg1_genome, go
         assert r.shape == (12, 2002)
         assert np.abs(r - g[f"ref_{s}"]).max() <= PROB_TOL and np.abs(a - g[f"alt_{s}"]).max() <= PROB_TOL
         assert pearson(d, g[f"alt_{s}"] - g[f"ref_{s}"]) >= 0.999
+
+
+@pytest.mark.parametrize("mode", ["segments", "windows"])
+def test_chromatin_cli_all_rows_filtered(engine, small_genome, tmp_path, mode, capsys):
+    """A VCF whose rows are all dropped by the CHRS filter (chromatin.py:241).  The reference dies there
+    (``np.vstack([])`` at :271 raises ValueError); the drop-in writes the nine files with empty ``[0,2002]`` datasets,
+    the unfiltered ``snps_hg19.vcf`` and zero counters."""
+    from expecto_b200 import chromatin, hdf5
+    pg = PackedGenome.from_sequences(small_genome)
+    vcf = tmp_path / "f.vcf"
+    vcf.write_text("chrUn_gl000220\t1234\tx\tA\tC\nchrM\t5\ty\tG\tT\n")
+    args = chromatin.build_parser().parse_args([str(vcf), "--output_dir", str(tmp_path / "out"), "--mode", mode])
+    res = chromatin.run(args, engine=engine, genome=pg)
+    assert res["n_variants"] == 0
+    assert "Number of input variants: 0" in capsys.readouterr().out
+    for s in chromatin.shift_list(800):
+        with hdf5.File(str(tmp_path / "out" / f"snps.shift_{s}.diff.h5")) as f:
+            assert {k: tuple(f[k].shape) for k in f} == {"diff": (0, 2002), "ref": (0, 2002), "alt": (0, 2002)}
+    assert (tmp_path / "out" / "snps_hg19.vcf").read_text().count("\n") == 4   # two header lines + both rows
