@@ -380,6 +380,29 @@ def stage_ref_all_genes(work, sd):
     print(f"[ref all genes] {len(df)} genes: oracle == reference (scores within 1e-5); fixture written")
 
 
+def stage_keep_mask():
+    """cluster_utils.get_keep_mask (imported from /root/reference) on the reference's own 2002-feature table, for the
+    16 combinations of --no_tf_features / --no_dnase_features / --no_histone_features / --no_pol2 (predict.py:139-147
+    uses the mask to subset the model's columns).  The fixture keeps the two columns the masks depend on."""
+    import contextlib
+    import io
+    import itertools
+    import pandas as pd
+    sys.path.insert(0, REF)
+    import cluster_utils
+    df = pd.read_csv(os.path.join(REF, "resources", "deepsea_beluga_2002_features.tsv"), sep="\t", index_col=0)
+    combos, masks = [], []
+    for tf, dn, hi, po in itertools.product([False, True], repeat=4):
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = cluster_utils.get_keep_mask(df, tf, dn, hi, False, po, return_hgnc_df=True)[0]
+        combos.append([tf, dn, hi, po])
+        masks.append(np.packbits(np.asarray(m, dtype=bool)))
+    np.savez_compressed(os.path.join(GOLD, "keep_mask_golden.npz"), assay=np.array([str(x) for x in df["Assay"]], dtype=str),
+                        assay_type=np.array([str(x) for x in df["Assay type"]], dtype=str), combos=np.array(combos),
+                        masks=np.stack(masks))
+    print(f"[keep mask] {len(combos)} flag combinations on {len(df)} features: reference masks stored")
+
+
 def stage_replicate(work, sd, genome):
     """replicate_expecto_features.py as a subprocess on the two compute_expecto_features genes."""
     genes = GI.cfg4_genes()
@@ -436,6 +459,7 @@ def main():
         stage_replicate(args.workdir, sd, genome)
         return
     stage_encode()
+    stage_keep_mask()
     sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
     stage_beluga(sd)
     if not args.skip_scripts:

@@ -3,7 +3,7 @@ import numpy as np
 import pandas as pd
 import pytest
 
-from expecto_b200 import gblinear
+from expecto_b200 import gblinear, predict
 from expecto_b200.predict import build_parser, expand_weights, num_repeats
 from expecto_b200.transform import chromatin_shifts, fixed_pos_weights
 from oracle import beluga_oracle as O
@@ -145,3 +145,25 @@ def test_merge_predict_batched_natural_order_and_index(tmp_path):
     args.n_chunks = 5
     with pytest.raises(AssertionError):
         mpb.run(args)
+
+
+def test_keep_mask_matches_reference_cluster_utils(golden, tmp_path):
+    """predict.keep_mask against cluster_utils.get_keep_mask run by oracle/make_golden.py on the reference's own
+    2002-feature table: all 16 combinations of the four feature-class flags (cluster_utils.py:8-49)."""
+    import pandas as pd
+    g = golden("keep_mask_golden.npz")
+    tsv = tmp_path / "features.tsv"
+    pd.DataFrame({"Cell type": "x", "Assay": g["assay"], "Treatment": "", "Assay type": g["assay_type"]},
+                 index=np.arange(1, len(g["assay"]) + 1)).to_csv(tsv, sep="\t")
+
+    class Flags:
+        intersect_with_lambert = False
+
+    for (tf, dn, hi, po), packed in zip(g["combos"], g["masks"]):
+        a = Flags()
+        a.no_tf_features, a.no_dnase_features, a.no_histone_features, a.no_pol2 = bool(tf), bool(dn), bool(hi), bool(po)
+        want = np.unpackbits(packed)[:len(g["assay"])].astype(bool)
+        assert np.array_equal(predict.keep_mask(str(tsv), a), want), (tf, dn, hi, po)
+    a.intersect_with_lambert = True
+    with pytest.raises(NotImplementedError):
+        predict.keep_mask(str(tsv), a)
