@@ -225,6 +225,36 @@ def stage_features(work, sd, genome):
     print(f"[features] {len(genes)} genes: oracle == reference, shape {ref.shape} {ref.dtype}")
 
 
+def stage_features_override(work, sd, genome):
+    """compute_expecto_features.py with a TSS table that matches both genes (:54-69; liftover = identity shim): gene 1
+    has a non-default TSS -> chrom, TSS and strand come from the table; gene 2 is marked default -> only its strand is
+    taken from the table (the reference overwrites ``strand`` at :56 before it looks at ``is_default_tss``).  The
+    output must be what the oracle computes at exactly those coordinates; they are stored for the host-logic test."""
+    genes = GI.cfg4_genes()
+    (g1, c1, s1, t1), (g2, c2, s2, t2) = genes
+    with open(os.path.join(work, "tss_override.tsv"), "w") as f:
+        f.write("\tens_id\tchrom\ttss\tstrand\tx\tis_default_tss\n")
+        f.write(f"0\t{g1}\t{c1}\t{t1 + 400}\t-\t0\tFalse\n")
+        f.write(f"1\t{g2}\tchr2\t123\t+\t0\tTrue\n")
+    run_ref_script("compute_expecto_features.py", ["geneanno_small.csv", "tss_override.tsv", "-o", "out_features_override"], work)
+    ref = np.load(os.path.join(work, "out_features_override", "Xreducedall.2002.representative_tss_top.npy"))
+    expected = [(g1, c1, t1 + 400, -1), (g2, c2, t2, 1)]
+    g = O.DictGenome(genome)
+    pw = O.fixed_pos_weights()
+    for i, (gid, chrom, tss, sgn) in enumerate(expected):
+        enc = O.encode_seqs(O.tss_windows(g, chrom, tss, sgn), concat_rc=False)
+        fwd = O.beluga_forward(enc.astype(np.float32), sd)
+        rc = O.beluga_forward(np.ascontiguousarray(enc[:, ::-1, ::-1]).astype(np.float32), sd)
+        rel = np.abs(O.fixed_transform(fwd, rc, pw) - ref[i]).max() / np.abs(ref[i]).max()
+        assert rel < 1e-6, f"TSS override: the reference did not use {expected[i]} (rel {rel})"
+    np.savez_compressed(os.path.join(GOLD, "features_override_golden.npz"),
+                        anno=np.array(open(os.path.join(work, "geneanno_small.csv")).read()),
+                        tss=np.array(open(os.path.join(work, "tss_override.tsv")).read()),
+                        expected=np.array([[str(x) for x in e] for e in expected]),
+                        feature_sums=ref.sum(axis=1))
+    print(f"[features override] reference used {expected}: fixture written")
+
+
 def stage_predict(work):
     rng = np.random.default_rng(GI.GBLINEAR_SEED)
     w = (rng.standard_normal(20020) * 0.01).astype(np.float32)
@@ -437,6 +467,8 @@ def main():
     ap.add_argument("--workdir", default="/tmp/bx_golden")
     ap.add_argument("--skip-scripts", action="store_true", help="only the import-level stages (fast)")
     ap.add_argument("--only-closest", action="store_true", help="only the make_closest_genes_file.py stage")
+    ap.add_argument("--only-features-override", action="store_true",
+                    help="only the compute_expecto_features.py TSS-override stage")
     ap.add_argument("--only-ref-all-genes", action="store_true", help="only the geuvadis_predict_ref_all_genes.py stage")
     ap.add_argument("--only-consensus", action="store_true",
                     help="only the geuvadis_predict_consensus.py / replicate_expecto_features.py stages")
@@ -445,6 +477,13 @@ def main():
     if args.only_closest:
         os.makedirs(args.workdir, exist_ok=True)
         stage_closest_genes(args.workdir)
+        return
+    if args.only_features_override:
+        sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
+        genome = prepare_workdir(args.workdir, sd)
+        if not os.path.exists(os.path.join(args.workdir, "geneanno_small.csv")):
+            stage_features(args.workdir, sd, genome)
+        stage_features_override(args.workdir, sd, genome)
         return
     if args.only_ref_all_genes:
         sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
@@ -466,6 +505,7 @@ def main():
         genome = prepare_workdir(args.workdir, sd)
         stage_chromatin(args.workdir, sd, genome)
         stage_features(args.workdir, sd, genome)
+        stage_features_override(args.workdir, sd, genome)
         stage_predict(args.workdir)
         stage_closest_genes(args.workdir)
         stage_consensus(args.workdir, sd)

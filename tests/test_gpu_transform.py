@@ -85,6 +85,23 @@ def test_feature_pipeline_matches_compute_expecto_features_script(engine, cfg1_g
     assert _rel_err(ours, want) <= 2e-3
 
 
+def test_feature_pipeline_tss_override_matches_reference_script(engine, cfg1_genome, golden, tmp_path):
+    """The TSS-override rows of compute_expecto_features.py:54-69 through the drop-in (--tss_is_hg19 = the identity
+    liftover the reference ran behind): per-gene feature sums of the reference's .npy, within the summed tolerance."""
+    from expecto_b200 import compute_expecto_features as cef
+    g = golden("features_override_golden.npz")
+    (tmp_path / "anno.csv").write_text(str(g["anno"]))
+    (tmp_path / "tss.tsv").write_text(str(g["tss"]))
+    args = cef.build_parser().parse_args([str(tmp_path / "anno.csv"), str(tmp_path / "tss.tsv"), "-o",
+                                          str(tmp_path / "out"), "--tss_is_hg19"])
+    cef.run(args, engine=engine, genome=PackedGenome.from_sequences(cfg1_genome))
+    ours = np.load(tmp_path / "out" / "Xreducedall.2002.representative_tss_top.npy")
+    assert ours.shape == (2, 20020)
+    bound = float(np.abs(O.fixed_pos_weights()).sum() * 2002 * 2e-3)     # every probability within 2e-3
+    assert np.all(np.abs(ours.sum(axis=1) - g["feature_sums"]) <= bound)
+    assert np.all(np.abs(ours.sum(axis=1) - g["feature_sums"]) <= 2e-3 * np.abs(g["feature_sums"]))
+
+
 def test_predict_pipeline_matches_predict_script(engine, cfg1_genome, golden, tmp_path):
     """chromatin -> strand average -> per-variant transform -> gblinear scores, vs predict.py's sed.tsv."""
     import pandas as pd

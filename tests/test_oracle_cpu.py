@@ -105,3 +105,18 @@ def test_variant_weights_edge_cases():
     assert np.allclose(w0[1, :5], 0) and np.allclose(w0[1, 5:], 1.0)           # p = 199 -> floor 0, upstream half off
     assert np.allclose(w0[2, :5], np.exp(-np.array([0.01, 0.02, 0.05, 0.1, 0.2])))  # '-' strand: p = -200
     assert np.allclose(w0[3, 5:], 1.0) and np.allclose(w0[3, :5], 0)           # '-' strand: p = +1
+
+
+def test_tss_override_rules_match_reference_script(golden, tmp_path):
+    """compute_expecto_features.py:54-69 with a TSS table that matches both genes (oracle/make_golden.py
+    stage_features_override ran the reference behind the identity liftover shim and checked which coordinates it
+    used): a non-default row replaces chrom, TSS and strand; a default row still replaces the strand."""
+    from expecto_b200 import compute_expecto_features as cef
+    g = golden("features_override_golden.npz")
+    (tmp_path / "anno.csv").write_text(str(g["anno"]))
+    (tmp_path / "tss.tsv").write_text(str(g["tss"]))
+    got = cef.read_genes(str(tmp_path / "anno.csv"), str(tmp_path / "tss.tsv"), tss_is_hg19=True)
+    want = [(a, b, int(c), int(d)) for a, b, c, d in g["expected"]]
+    assert got == want
+    with pytest.raises(NotImplementedError):      # without --tss_is_hg19 the override would need the liftover package
+        cef.read_genes(str(tmp_path / "anno.csv"), str(tmp_path / "tss.tsv"))
