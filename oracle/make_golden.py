@@ -410,6 +410,39 @@ def stage_ref_all_genes(work, sd):
     print(f"[ref all genes] {len(df)} genes: oracle == reference (scores within 1e-5); fixture written")
 
 
+def stage_num_repeats():
+    """predict.py's get_num_repeats (:202-213), lifted out of the script with ``ast`` and exec'd (predict.py is
+    module-level code), on seeded gene tables: runs of rows sharing columns 0-4, incl. a group that reappears later
+    (counted again, the reference compares neighbours only) and numeric columns that pandas parses as floats."""
+    import io
+    import pandas as pd
+    src = open(os.path.join(REF, "predict.py")).read()
+    fn = [n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "get_num_repeats"][0]
+    ns = {}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), "predict.py", "exec"), ns)
+    rng = np.random.default_rng(17)
+    tables, expected = [], []
+    for t in range(6):
+        rows = []
+        n_groups = int(rng.integers(1, 12))
+        keys = [(f"chr{int(rng.integers(1, 4))}", int(rng.integers(1, 50)), "ACGT"[int(rng.integers(4))],
+                 "ACGT"[int(rng.integers(4))]) for _ in range(n_groups)]
+        if t == 3 and n_groups > 2:
+            keys.append(keys[0])                       # the same variant again, not adjacent
+        for c, p, r, a in keys:
+            for k in range(int(rng.integers(1, 5))):
+                pos = float(p) if t == 4 else p        # a float position column ("12.0" in the joined key)
+                rows.append([c, pos, pos + 1, r, a, "+-"[int(rng.integers(2))], f"ENSG{int(rng.integers(1000))}",
+                             int(rng.integers(-5000, 5000))])
+        text = pd.DataFrame(rows).to_csv(sep="\t", header=False, index=False)
+        df = pd.read_csv(io.StringIO(text), sep="\t", header=None, comment="#")
+        tables.append(text)
+        expected.append(",".join(str(x) for x in ns["get_num_repeats"](df)))
+    np.savez_compressed(os.path.join(GOLD, "num_repeats_golden.npz"), tables=np.array(tables, dtype=str),
+                        expected=np.array(expected, dtype=str))
+    print(f"[num repeats] {len(tables)} gene tables: the reference's get_num_repeats outputs stored")
+
+
 def stage_keep_mask():
     """cluster_utils.get_keep_mask (imported from /root/reference) on the reference's own 2002-feature table, for the
     16 combinations of --no_tf_features / --no_dnase_features / --no_histone_features / --no_pol2 (predict.py:139-147
@@ -499,6 +532,7 @@ def main():
         return
     stage_encode()
     stage_keep_mask()
+    stage_num_repeats()
     sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
     stage_beluga(sd)
     if not args.skip_scripts:

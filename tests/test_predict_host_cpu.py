@@ -167,3 +167,13 @@ def test_keep_mask_matches_reference_cluster_utils(golden, tmp_path):
     a.intersect_with_lambert = True
     with pytest.raises(NotImplementedError):
         predict.keep_mask(str(tsv), a)
+
+
+def test_num_repeats_matches_reference_function(golden):
+    """predict.num_repeats against predict.py's own get_num_repeats (:202-213, exec'd by oracle/make_golden.py) on
+    seeded gene tables: singleton groups, a variant that reappears later, float-typed position columns."""
+    import io
+    g = golden("num_repeats_golden.npz")
+    for text, want in zip(g["tables"], g["expected"]):
+        df = pd.read_csv(io.StringIO(str(text)), sep="\t", header=None, comment="#")
+        assert num_repeats(df) == [int(x) for x in str(want).split(",")]
