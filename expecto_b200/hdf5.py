@@ -62,27 +62,61 @@ def _dataset_header(shape, data_addr: int, nbytes: int, mtime: int, dtype=np.dty
 
 
 class H5Writer:
-    """Write datasets (<= 8, names sorted as HDF5 requires; float32 unless ``dtypes`` says float64 or ``S<n>``) into
-    one v0-superblock file.
+    """Write datasets (<= 8; float32 unless ``dtypes`` says float64 or ``S<n>``) into one v0-superblock file, laid out
+    the way libhdf5 1.8/1.10 lays out ``h5py.File(path, 'w')`` + ``create_dataset(name, data=...)`` calls in the order
+    of ``datasets`` (chromatin.py:283-285: diff, ref, alt): metadata is carved out of the first 2048-byte aggregator
+    block in allocation order — root header, B-tree node, local heap, the first dataset's object header, the group's
+    symbol node, then the remaining dataset headers — names enter the local heap in creation order, the symbol node
+    lists them sorted, and each dataset's raw data follows the previous one's from 0x800.  For a single ``pred``
+    dataset the first 2048 bytes are identical to example/example.vcf.shift_0.diff.h5 (written by h5py) except the
+    4-byte modification time (tests/test_hdf5_cpu.py).
 
-    ``create(name, shape)`` reserves space; ``write_rows(name, row0, array)`` pwrite()s row slabs, so several
-    producers (GPU ranks, pipeline stages) can fill one contiguous dataset without an in-memory copy."""
+    ``write_rows(name, row0, array)`` pwrite()s row slabs, so several producers (GPU ranks, pipeline stages) can
+    fill one contiguous dataset without an in-memory copy."""
+
+    _HDR_SIZE = 0x110   # v1 object header: 16-byte prefix + 0x100 bytes of messages
+    _SNOD_SIZE = 8 + 2 * _LEAF_K * 40
 
     def __init__(self, path: str, datasets: dict[str, tuple[int, ...]], create: bool = True, dtypes=None):
         """``create=False`` attaches to a file another process already created with the same datasets (a GPU
-        rank writing its own row slab; the layout is a pure function of the dataset shapes)."""
+        rank writing its own row slab; the layout is a pure function of the dataset names, order and shapes)."""
         if not 1 <= len(datasets) <= 2 * _LEAF_K:
             raise ValueError("1..8 datasets per file")
         self.path = path
-        self.names = sorted(datasets)
-        self.shapes = {n: tuple(int(x) for x in datasets[n]) for n in self.names}
-        self.dtypes = {n: np.dtype((dtypes or {}).get(n, "<f4")) for n in self.names}
-        for n in self.names:
+        self.order = list(datasets)            # creation order (heap offsets, header addresses, data addresses)
+        self.names = sorted(datasets)          # symbol-node order
+        self.shapes = {n: tuple(int(x) for x in datasets[n]) for n in self.order}
+        self.dtypes = {n: np.dtype((dtypes or {}).get(n, "<f4")) for n in self.order}
+        for n in self.order:
             _datatype_message(self.dtypes[n])
-        self.addr, off = {}, _DATA_START
-        for n in self.names:
-            self.addr[n] = off
-            off += int(np.prod(self.shapes[n])) * self.dtypes[n].itemsize
+        # local heap data: "" at 0, then each name (creation order) NUL-terminated and padded to 8, then the free
+        # block; libhdf5 starts a group's heap at 88 bytes (longer name lists get a larger segment here)
+        heap = bytearray(8)
+        self._name_off = {}
+        for n in self.order:
+            self._name_off[n] = len(heap)
+            heap += _pad8(n.encode("ascii") + b"\x00")
+        self._heap_free = len(heap)
+        self._heap_size = max(88, (self._heap_free + 16 + 7) // 8 * 8)
+        heap += struct.pack("<QQ", 1, self._heap_size - self._heap_free)
+        self._heap = bytes(heap) + b"\x00" * (self._heap_size - len(heap))
+        # metadata addresses: the first object header follows the heap data segment (0x320 for an 88-byte heap)
+        self._hdr_addr, a = {}, 0x2A8 + 32 + self._heap_size
+        for i, n in enumerate(self.order):
+            self._hdr_addr[n] = a
+            a += self._HDR_SIZE
+            if i == 0:
+                self._snod_addr = a
+                a += self._SNOD_SIZE
+        # three headers fit libhdf5's first 2048-byte metadata block; with more, libhdf5 would open a second block
+        # after the raw data written so far — this writer keeps one (larger) leading block instead, equally valid
+        self.data_start = _DATA_START if a <= _DATA_START else (a + 0x7FF) // 0x800 * 0x800
+        self.addr, self.nbytes, off = {}, {}, self.data_start
+        for n in self.order:
+            nb = int(np.prod(self.shapes[n])) * self.dtypes[n].itemsize
+            self.nbytes[n] = nb
+            self.addr[n] = off            # empty datasets own no storage (layout address UNDEF, as libhdf5 leaves it)
+            off += nb
             off += (-off) % 8
         self.eof = off
         if create:
@@ -97,30 +131,10 @@ class H5Writer:
     def _metadata(self) -> bytes:
         btree_addr, heap_addr = 0x88, 0x2A8
         heap_data_addr = heap_addr + 32
-        # local heap: "" at 0, then each name NUL-terminated padded to 8
-        heap = bytearray(8)
-        name_off = {}
-        for n in self.names:
-            name_off[n] = len(heap)
-            heap += _pad8(n.encode("ascii") + b"\x00")
-        free_off = len(heap)
-        heap_size = max(88, free_off + 16)
-        heap_size += (-heap_size) % 8
-        heap += struct.pack("<QQ", 1, heap_size - free_off)
-        heap += b"\x00" * (heap_size - len(heap))
-        snod_addr = heap_data_addr + heap_size
-        snod_size = 8 + 2 * _LEAF_K * 40
-        hdr_addr = {}
-        a = snod_addr + snod_size
-        a += (-a) % 8
-        for n in self.names:
-            hdr_addr[n] = a
-            a += 0x110
-        if a > _DATA_START:
-            raise ValueError("metadata block overflow")
+        heap, name_off, free_off, heap_size = self._heap, self._name_off, self._heap_free, self._heap_size
         mtime = int(time.time())
 
-        out = bytearray(_DATA_START)
+        out = bytearray(self.data_start)
         sb = _SIG + struct.pack("<BBBBBBBBHHI", 0, 0, 0, 0, 0, 8, 8, 0, _LEAF_K, _INTERNAL_K, 0)
         sb += struct.pack("<QQQQ", 0, _UNDEF, self.eof, _UNDEF)
         sb += struct.pack("<QQII", 0, 0x60, 1, 0) + struct.pack("<QQ", btree_addr, heap_addr)  # root symbol entry
@@ -128,19 +142,19 @@ class H5Writer:
         root = struct.pack("<BBHII4x", 1, 0, 1, 1, 0x18) + _msg(0x11, struct.pack("<QQ", btree_addr, heap_addr))
         out[0x60:0x60 + len(root)] = root
         bt = b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, _UNDEF, _UNDEF)
-        bt += struct.pack("<QQQ", 0, snod_addr, name_off[self.names[-1]])
+        bt += struct.pack("<QQQ", 0, self._snod_addr, name_off[self.names[-1]])
         out[btree_addr:btree_addr + len(bt)] = bt
         hp = b"HEAP" + struct.pack("<B3xQQQ", 0, heap_size, free_off, heap_data_addr)
         out[heap_addr:heap_addr + len(hp)] = hp
         out[heap_data_addr:heap_data_addr + heap_size] = heap
         sn = b"SNOD" + struct.pack("<BBH", 1, 0, len(self.names))
         for n in self.names:
-            sn += struct.pack("<QQII16x", name_off[n], hdr_addr[n], 0, 0)
-        out[snod_addr:snod_addr + len(sn)] = sn
-        for n in self.names:
-            nbytes = int(np.prod(self.shapes[n])) * self.dtypes[n].itemsize
-            h = _dataset_header(self.shapes[n], self.addr[n], nbytes, mtime, self.dtypes[n])
-            out[hdr_addr[n]:hdr_addr[n] + len(h)] = h
+            sn += struct.pack("<QQII16x", name_off[n], self._hdr_addr[n], 0, 0)
+        out[self._snod_addr:self._snod_addr + len(sn)] = sn
+        for n in self.order:
+            nb = self.nbytes[n]
+            h = _dataset_header(self.shapes[n], self.addr[n] if nb else _UNDEF, nb, mtime, self.dtypes[n])
+            out[self._hdr_addr[n]:self._hdr_addr[n] + len(h)] = h
         return bytes(out)
 
     def write_rows(self, name: str, row0: int, arr: np.ndarray) -> None:
@@ -195,6 +209,8 @@ class H5Dataset:
         self._mm = None
 
     def _map(self):
+        if self._mm is None and (self.addr is None or 0 in self.shape):
+            self._mm = np.zeros(self.shape, dtype=self.dtype)   # HDF5 fill value of unallocated storage
         if self._mm is None:
             self._mm = np.memmap(self.path, dtype=self.dtype, mode="r", offset=self.addr, shape=self.shape)
         return self._mm
@@ -205,6 +221,9 @@ class H5Dataset:
         row_bytes = int(np.prod(self.shape[1:])) * np.dtype(self.dtype).itemsize if len(self.shape) > 1 else \
             np.dtype(self.dtype).itemsize
         mv = memoryview(dst.reshape(-1)).cast("B")[:(row1 - row0) * row_bytes]
+        if self.addr is None:          # unallocated storage reads as the fill value
+            mv[:] = bytes(len(mv))
+            return
         off = self.addr + row0 * row_bytes
         fd = os.open(self.path, os.O_RDONLY)
         try:
@@ -329,7 +348,9 @@ class H5File:
                 data_addr = struct.unpack_from("<Q", data, 2)[0]
         if shape is None or dtype is None or data_addr is None:
             return None
-        return H5Dataset(self.path, shape, dtype, self._base + data_addr)
+        if data_addr == _UNDEF:  # no storage allocated (empty dataset, or never written): reads as zeros / empty
+            data_addr = None
+        return H5Dataset(self.path, shape, dtype, None if data_addr is None else self._base + data_addr)
 
     def __getitem__(self, name: str) -> H5Dataset:
         return self._datasets[name]
