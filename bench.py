@@ -291,7 +291,7 @@ def run_gpu(args) -> int:
     _lib.build()
     B, K, W = args.batch, args.steps, max(3, args.warmup)
     eng = BelugaEngine(local, dtype=args.dtype, cta_group=args.cta_group, capacity=min(B, args.capacity))
-    eng.load_state_dict(synth.make_beluga_weights(0, round_dtype=args.dtype))
+    eng.load_state_dict(synth.make_beluga_weights(0, round_dtype=None if args.dtype == "f16x3" else args.dtype))
     x_host = torch.from_numpy(synth.random_onehot(B, seed=2 + rank)).pin_memory()
     x = x_host.to(dev)
     out = torch.empty((B, 2002), dtype=torch.float32, device=dev)
@@ -367,7 +367,10 @@ def run_gpu(args) -> int:
         "config": {"workload": f"Beluga forward over {B} synthetic 2000-bp one-hot windows per GPU per step "
                                f"(BASELINE configs[1] batch sweep point B={B}), calibrated random-init weights",
                    "batch_per_gpu": B, "chunk_windows": chunk, "cta_group": args.cta_group,
-                   "operands": f"{args.dtype} x {args.dtype} -> fp32 accumulate (tcgen05.mma kind::f16)",
+                   "operands": ("fp16 (hi, lo) pairs, Ah*Wh + Ah*Wl + Al*Wh -> fp32 accumulate: three tcgen05.mma "
+                                "kind::f16 per product, FLOP figures count the algorithmic product once"
+                                if args.dtype == "f16x3" else
+                                f"{args.dtype} x {args.dtype} -> fp32 accumulate (tcgen05.mma kind::f16)"),
                    "l2": "per-step activation traffic (2.7 MB/window) far exceeds the 126 MB L2; no explicit flush",
                    "parallelism": f"dp{world} (windows sharded, no collective on the path)"},
         "tflops_per_gpu": fwd_tf,
@@ -414,7 +417,8 @@ def main() -> int:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=8192, help="windows per GPU per step (BASELINE configs[1]: 64..8192)")
     ap.add_argument("--capacity", type=int, default=4096, help="windows per forward chunk (activation scratch)")
-    ap.add_argument("--dtype", default="f16", choices=["f16", "bf16"])
+    ap.add_argument("--dtype", default="f16", choices=["f16", "bf16", "f16x3"],
+                    help="tensor-core operand mode; f16x3 = split fp16 operands (3 MMAs per product, ~1e-4 of fp32)")
     ap.add_argument("--cta_group", type=int, default=2, choices=[1, 2])
     ap.add_argument("--ref_batch", type=int, default=32)
     ap.add_argument("--cpu_seconds", type=float, default=12.0)

@@ -20,7 +20,7 @@ SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "
 ]
 
 BX_OK, BX_E_ARG, BX_E_CUDA, BX_E_STATE, BX_E_BASE = 0, -1, -2, -3, -4
-DTYPE_F16, DTYPE_BF16 = 0, 1
+DTYPE_F16, DTYPE_BF16, DTYPE_F16X3 = 0, 1, 2
 
 
 class WindowDesc(C.Structure):

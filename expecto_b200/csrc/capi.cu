@@ -106,6 +106,11 @@ static const LayerDef kLayers[6] = {
 
 struct bx_ctx {
   int device = 0, dtype = 0, cg = 2, cap = 0, num_sms = 0;
+  // Split-operand mode (BX_DTYPE_F16X3): layer i (0..5 = conv1..6, 6 = fc1, 7 = fc2) reads its activation and its
+  // weights as fp16 (hi, lo) pairs and issues Ah*Wh + Ah*Wl + Al*Wh; entry 8 (the probabilities) is never split.
+  // conv1's activation is the exact one-hot, so only its weights are split (K = 32 -> 64).
+  bool split_in[9] = {};
+  bool split_any = false;
   bool weights_ready = false;
   void* wconv[6] = {};   // 16-bit [taps*cout, cin]
   float* bconv[6] = {};
@@ -168,17 +173,24 @@ struct StageTimer {
 
 static size_t act_rows(int i) { return i == 0 ? kLayers[0].pitch_in : kLayers[i - 1].pitch_out; }
 static size_t act_cols(int i) { return i == 0 ? 64 : kLayers[i - 1].cout; }
+// physical row width of activation i (the input of layer i): [hi | lo] when layer i runs on split operands
+static int act_mul(const bx_ctx* c, int i) { return (i >= 1 && c->split_in[i]) ? 2 : 1; }
+static size_t act_width(const bx_ctx* c, int i) { return act_cols(i) * act_mul(c, i); }
 
 // ------------------------------------------------------------------ GEMM launch
-template <typename T, int TAPS, int BN, int CG, int EPI, int A_MODE = 0>
+// a_cols / b_cols: physical row widths (elements) of the A and B matrices ([hi | lo] pairs in split-operand mode).
+template <typename T, int TAPS, int BN, int CG, int EPI, int A_MODE = 0, int SPLIT_OUT = 0>
 static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64_t a_cols, const void* b,
-                         uint64_t b_rows, GemmParams p, cudaStream_t st, const EncParams& enc = EncParams()) {
+                         uint64_t b_rows, uint64_t b_cols, GemmParams p, cudaStream_t st,
+                         const EncParams& enc = EncParams()) {
   using Cfg = GemmCfg<TAPS, BN, CG>;
   CUtensorMap tmA, tmB;
-  if (int r = make_tmap(&tmB, c->dtype, b, b_rows, a_cols, a_cols, Cfg::B_ROWS)) return r;
+  if (int r = make_tmap(&tmB, c->dtype, b, b_rows, b_cols, b_cols, Cfg::B_ROWS)) return r;
   if (A_MODE != 0) tmA = tmB;  // unused: the producer warp builds the A tile in shared memory
   else if (int r = make_tmap(&tmA, c->dtype, a, a_rows, a_cols, a_cols, Cfg::A_ROWS)) return r;
-  auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI, A_MODE>;
+  if (p.parts < 1) { p.parts = 1; }
+  if (p.a_grp < 1) { p.a_grp = 1 << 30; p.a_grp_stride = 0; }
+  auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI, A_MODE, SPLIT_OUT>;
   // function attributes are per device: one flag per device, so contexts on several GPUs of one process all get it
   static std::atomic<bool> attr_set[kMaxDevices];
   if (c->device < 0 || c->device >= kMaxDevices) return fail(BX_E_ARG, "device index %d out of range", c->device);
@@ -217,9 +229,11 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
 
 template <typename T, int CG>
 static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void* a, uint64_t a_rows,
-                          uint64_t a_cols, const void* b, uint64_t b_rows, const GemmParams& p, cudaStream_t st) {
+                          uint64_t a_cols, const void* b, uint64_t b_rows, uint64_t b_cols, const GemmParams& p,
+                          bool split_out, cudaStream_t st) {
 #define BX_CASE(TP, N, E) \
-  if (taps == TP && bn == N && epi == E) return launch_gemm_t<T, TP, N, CG, E>(c, a, a_rows, a_cols, b, b_rows, p, st)
+  if (taps == TP && bn == N && epi == E && !split_out) \
+    return launch_gemm_t<T, TP, N, CG, E>(c, a, a_rows, a_cols, b, b_rows, b_cols, p, st)
   BX_CASE(1, 160, EPI_BIAS_RELU);
   BX_CASE(8, 160, EPI_POOL4_BIAS_RELU);
   BX_CASE(8, 240, EPI_BIAS_RELU);
@@ -229,17 +243,44 @@ static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void
   BX_CASE(1, 256, EPI_PARTIAL_F32);
   BX_CASE(1, 256, EPI_BIAS_SIGMOID);
 #undef BX_CASE
-  return fail(BX_E_ARG, "no kernel instance for taps=%d block_n=%d epi=%d", taps, bn, epi);
+  if constexpr (std::is_same<T, __half>::value) {  // split-operand mode exists for fp16 operands only
+#define BX_CASE(TP, N, E) \
+  if (taps == TP && bn == N && epi == E && split_out) \
+    return launch_gemm_t<T, TP, N, CG, E, 0, 1>(c, a, a_rows, a_cols, b, b_rows, b_cols, p, st)
+    BX_CASE(1, 160, EPI_BIAS_RELU);
+    BX_CASE(8, 160, EPI_POOL4_BIAS_RELU);
+    BX_CASE(8, 240, EPI_BIAS_RELU);
+    BX_CASE(8, 240, EPI_POOL4_BIAS_RELU);
+    BX_CASE(8, 240, EPI_POOL2_BIAS_RELU);
+    BX_CASE(8, 160, EPI_BIAS_RELU);
+#undef BX_CASE
+  }
+  return fail(BX_E_ARG, "no kernel instance for taps=%d block_n=%d epi=%d split_out=%d", taps, bn, epi, (int)split_out);
 }
 
 static int launch_gemm(const bx_ctx* c, int taps, int bn, int epi, const void* a, uint64_t a_rows, uint64_t a_cols,
-                       const void* b, uint64_t b_rows, const GemmParams& p, cudaStream_t st) {
+                       const void* b, uint64_t b_rows, uint64_t b_cols, const GemmParams& p, bool split_out,
+                       cudaStream_t st) {
   if (c->dtype == BX_DTYPE_F16) {
-    if (c->cg == 1) return launch_gemm_tc<__half, 1>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
-    return launch_gemm_tc<__half, 2>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
+    if (c->cg == 1)
+      return launch_gemm_tc<__half, 1>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, b_cols, p, split_out, st);
+    return launch_gemm_tc<__half, 2>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, b_cols, p, split_out, st);
   }
-  if (c->cg == 1) return launch_gemm_tc<__nv_bfloat16, 1>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
-  return launch_gemm_tc<__nv_bfloat16, 2>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, p, st);
+  if (c->cg == 1)
+    return launch_gemm_tc<__nv_bfloat16, 1>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, b_cols, p, split_out, st);
+  return launch_gemm_tc<__nv_bfloat16, 2>(c, taps, bn, epi, a, a_rows, a_cols, b, b_rows, b_cols, p, split_out, st);
+}
+
+// Split-operand fields of conv layer i (1..5): A = act[i] [rows, cin * mul], B = wconv[i] [8*cout, cin * mul].
+static void conv_split_params(const bx_ctx* c, int i, GemmParams& p) {
+  const LayerDef& L = kLayers[i];
+  p.parts = (i >= 1 && c->split_in[i]) ? 3 : 1;
+  p.a_grp = 1 << 30;
+  p.a_grp_stride = 0;
+  p.a_lo_off = L.cin;
+  p.b_lo_off = L.cin;
+  p.ld_out = L.cout * (c->split_in[i + 1] ? 2 : 1);
+  p.out_lo_off = L.cout;
 }
 
 // conv1 with the operand generated inside the kernel (north-star item 1: extraction + one-hot + reverse
@@ -248,8 +289,15 @@ static int launch_conv1_gen(const bx_ctx* c, int amode, const EncParams& enc, co
   const LayerDef& L = kLayers[0];
   if (p.pitch_in < 136) return fail(BX_E_ARG, "conv1 row pitch %d too small for in-kernel encoding", p.pitch_in);
 #define BX_GEN(T, CG, M) \
-  return launch_gemm_t<T, 1, 160, CG, EPI_BIAS_RELU, M>(c, nullptr, 0, L.cin, c->wconv[0], L.cout, p, st, enc)
+  return launch_gemm_t<T, 1, 160, CG, EPI_BIAS_RELU, M>(c, nullptr, 0, L.cin, c->wconv[0], L.cout, L.cin, p, st, enc)
+#define BX_GEN_S(CG, M) \
+  return launch_gemm_t<__half, 1, 160, CG, EPI_BIAS_RELU, M, 1>(c, nullptr, 0, L.cin, c->wconv[0], L.cout, L.cin, p, st, enc)
   const bool f16 = c->dtype == BX_DTYPE_F16;
+  if (c->split_in[1]) {  // conv2 reads conv1's output as (hi, lo) pairs
+    if (amode == 1) { if (c->cg == 1) BX_GEN_S(1, 1); BX_GEN_S(2, 1); }
+    if (c->cg == 1) BX_GEN_S(1, 2);
+    BX_GEN_S(2, 2);
+  }
   if (amode == 1) {
     if (f16) { if (c->cg == 1) BX_GEN(__half, 1, 1); BX_GEN(__half, 2, 1); }
     if (c->cg == 1) BX_GEN(__nv_bfloat16, 1, 1);
@@ -259,12 +307,13 @@ static int launch_conv1_gen(const bx_ctx* c, int amode, const EncParams& enc, co
   if (c->cg == 1) BX_GEN(__nv_bfloat16, 1, 2);
   BX_GEN(__nv_bfloat16, 2, 2);
 #undef BX_GEN
+#undef BX_GEN_S
 }
 
 // BX_CONV1_IM2COL=1 keeps the two-kernel form (encode -> im2col matrix in HBM -> TMA) for A/B comparisons.
-static bool conv1_gen_enabled() {
+static bool conv1_gen_enabled(const bx_ctx* c) {
   static const bool on = !(getenv("BX_CONV1_IM2COL") && atoi(getenv("BX_CONV1_IM2COL")) != 0);
-  return on;
+  return on || c->split_any;  // the two-kernel form has no split-operand variant
 }
 
 // conv layer i (0..5) over n windows: act[i] -> act[i+1]; `enc` (conv1 only) selects in-kernel operand generation
@@ -272,7 +321,7 @@ static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st, const EncParams* e
   const LayerDef& L = kLayers[i];
   GemmParams p = {};
   p.m_rows = n * L.pitch_in;
-  p.k_valid = (i == 0) ? 32 : L.cin;
+  p.k_valid = (i == 0) ? (c->split_in[0] ? 64 : 32) : L.cin;
   p.n_total = L.cout;
   p.k_splits = 1;
   p.k_blocks = (p.k_valid + 63) / 64;
@@ -280,20 +329,21 @@ static int run_conv(bx_ctx* c, int i, int n, cudaStream_t st, const EncParams* e
   p.pitch_in = L.pitch_in;
   p.pitch_out = L.pitch_out;
   p.l_store = L.l_store;
-  p.ld_out = L.cout;
   p.n_store = L.cout;
   p.bias = c->bconv[i];
   p.out = c->act[i + 1];
+  conv_split_params(c, i, p);
   if (i == 0 && enc) return launch_conv1_gen(c, amode, *enc, p, st);
-  return launch_gemm(c, L.taps, L.block_n, L.epi, c->act[i], (uint64_t)n * L.pitch_in, L.cin, c->wconv[i],
-                     (uint64_t)L.taps * L.cout, p, st);
+  const uint64_t width = (uint64_t)L.cin * act_mul(c, i);
+  return launch_gemm(c, L.taps, L.block_n, L.epi, c->act[i], (uint64_t)n * L.pitch_in, width, c->wconv[i],
+                     (uint64_t)L.taps * L.cout, width, p, c->split_in[i + 1], st);
 }
 
 template <typename T>
 static int run_fc1_finalize(bx_ctx* c, int n, int k_splits, size_t split_stride, cudaStream_t st) {
   const size_t total = (size_t)n * 2048;
   fc1_finalize_kernel<T><<<(unsigned)((total / 4 + 255) / 256), 256, 0, st>>>(c->acc1_view, k_splits, split_stride, c->bfc1,
-                                                                             (T*)c->hid, total);
+                                                                             (T*)c->hid, total, c->split_in[7] ? 1 : 0);
   g_launches++;
   CK(cudaGetLastError());
   return 0;
@@ -325,7 +375,15 @@ static int launch_fc1_gemm(bx_ctx* c, int n, float* out, size_t split_stride, co
     memcpy(p.tile_lo, ranges->tile_lo, sizeof(p.tile_lo));
     memcpy(p.tile_n, ranges->tile_n, sizeof(p.tile_n));
   }
-  return launch_gemm(c, 1, 256, EPI_PARTIAL_F32, c->act[6], n, 67840, c->wfc1, 2048, p, st);
+  // operand rows are 106 conv6 rows of [hi(640) | lo(640)] in split mode: ten K-blocks per conv6 row
+  const int mul = c->split_in[6] ? 2 : 1;
+  p.parts = c->split_in[6] ? 3 : 1;
+  p.a_grp = 10;
+  p.a_grp_stride = 640 * mul;
+  p.a_lo_off = 640;
+  p.b_lo_off = 67840;
+  return launch_gemm(c, 1, 256, EPI_PARTIAL_F32, c->act[6], n, (uint64_t)67840 * mul, c->wfc1, 2048,
+                     (uint64_t)67840 * mul, p, false, st);
 }
 constexpr int kFc1KbPerSplit = (67840 / 64 + kFc1Splits - 1) / kFc1Splits;
 
@@ -354,7 +412,13 @@ static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
   p.n_store = BX_FEATURES;
   p.bias = c->bfc2;
   p.out = probs;
-  return launch_gemm(c, 1, 256, EPI_BIAS_SIGMOID, c->hid, n, 2048, c->wfc2, 2048, p, st);
+  const int mul = c->split_in[7] ? 2 : 1;
+  p.parts = c->split_in[7] ? 3 : 1;
+  p.a_grp = 1 << 30;
+  p.a_lo_off = 2048;
+  p.b_lo_off = 2048;
+  return launch_gemm(c, 1, 256, EPI_BIAS_SIGMOID, c->hid, n, (uint64_t)2048 * mul, c->wfc2, 2048, (uint64_t)2048 * mul,
+                     p, false, st);
 }
 
 // conv1..conv6, fc1, fc2 over n windows whose conv1 operand is already in act[0] or is generated from `enc`.
@@ -400,7 +464,7 @@ static int run_conv_geom(bx_ctx* c, int i, int n_seg, const Geom& g, const void*
   GemmParams p = {};
   const int skip = phase_b ? 2 : 0;
   p.m_rows = n_seg * pin[i] - skip;
-  p.k_valid = (i == 0) ? 32 : L.cin;
+  p.k_valid = (i == 0) ? (c->split_in[0] ? 64 : 32) : L.cin;
   p.n_total = L.cout;
   p.k_splits = 1;
   p.k_blocks = (p.k_valid + 63) / 64;
@@ -408,19 +472,20 @@ static int run_conv_geom(bx_ctx* c, int i, int n_seg, const Geom& g, const void*
   p.pitch_in = pin[i];
   p.pitch_out = pout[i];
   p.l_store = (i == 3 && phase_b) ? g.l4b : pout[i];
-  p.ld_out = L.cout;
   p.n_store = L.cout;
   p.bias = c->bconv[i];
   p.out = out;
+  conv_split_params(c, i, p);
   if (i == 0 && enc) return launch_conv1_gen(c, 1, *enc, p, st);
-  const char* a = reinterpret_cast<const char*>(in) + (size_t)skip * L.cin * 2;
+  const uint64_t width = (uint64_t)L.cin * act_mul(c, i);
+  const char* a = reinterpret_cast<const char*>(in) + (size_t)skip * width * 2;
   int epi = L.epi;
   if (half_pool) {  // conv4 in segment mode: MaxPool over row pairs only, [n_seg, ph, 480]
     epi = EPI_POOL2_BIAS_RELU;
     p.pitch_out = p.l_store = g.ph;
   }
-  return launch_gemm(c, L.taps, L.block_n, epi, a, (uint64_t)p.m_rows, L.cin, c->wconv[i], (uint64_t)L.taps * L.cout,
-                     p, st);
+  return launch_gemm(c, L.taps, L.block_n, epi, a, (uint64_t)p.m_rows, width, c->wconv[i], (uint64_t)L.taps * L.cout,
+                     width, p, c->split_in[i + 1], st);
 }
 
 // Largest number of L-position segments whose activations fit the scratch sized for `cap` 2000-bp windows.
@@ -441,7 +506,8 @@ int64_t bx_launch_count(void) { return g_launches.load(); }
 int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx_ctx** out) {
   if (!out) return fail(BX_E_ARG, "out is null");
   *out = nullptr;
-  if (dtype != BX_DTYPE_F16 && dtype != BX_DTYPE_BF16) return fail(BX_E_ARG, "dtype must be 0 (f16) or 1 (bf16)");
+  if (dtype != BX_DTYPE_F16 && dtype != BX_DTYPE_BF16 && dtype != BX_DTYPE_F16X3)
+    return fail(BX_E_ARG, "dtype must be 0 (f16), 1 (bf16) or 2 (f16x3: split fp16 operands)");
   if (cta_group != 1 && cta_group != 2) return fail(BX_E_ARG, "cta_group must be 1 or 2");
   if (capacity_windows < 1) return fail(BX_E_ARG, "capacity_windows must be >= 1");
   int ndev = 0;
@@ -458,21 +524,27 @@ int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx
   if (int r = load_driver_entry()) return r;
   bx_ctx* c = new bx_ctx();
   c->device = device;
-  c->dtype = dtype;
+  c->dtype = dtype == BX_DTYPE_F16X3 ? BX_DTYPE_F16 : dtype;
+  if (dtype == BX_DTYPE_F16X3) {
+    // BX_SPLIT_MASK (experiments): bit i = layer i on split operands; default every layer
+    const unsigned mask = getenv("BX_SPLIT_MASK") ? (unsigned)strtoul(getenv("BX_SPLIT_MASK"), nullptr, 0) : 0xFFu;
+    for (int i = 0; i < 8; ++i) c->split_in[i] = (mask >> i) & 1u;
+    c->split_any = true;
+  }
   c->cg = cta_group;
   c->cap = capacity_windows;
   c->num_sms = prop.multiProcessorCount;
   const size_t cap = capacity_windows;
   for (int i = 0; i < 7; ++i) {
     // +256 rows of slack is not needed: TMA zero-fills rows past the tensor end.
-    const size_t bytes = cap * act_rows(i) * act_cols(i) * 2;
+    const size_t bytes = cap * act_rows(i) * act_width(c, i) * 2;
     if (cudaMalloc(&c->act[i], bytes) != cudaSuccess) {
       bx_ctx_destroy(c);
       return fail(BX_E_CUDA, "cudaMalloc of activation %d (%zu bytes) failed", i, bytes);
     }
     cudaMemset(c->act[i], 0, bytes);
   }
-  if (cudaMalloc(&c->acc1, fc1_scratch_rows(capacity_windows) * 2048 * 4) != cudaSuccess || cudaMalloc(&c->hid, cap * 2048 * 2) != cudaSuccess) {
+  if (cudaMalloc(&c->acc1, fc1_scratch_rows(capacity_windows) * 2048 * 4) != cudaSuccess || cudaMalloc(&c->hid, cap * 2048 * 2 * (c->split_in[7] ? 2 : 1)) != cudaSuccess) {
     bx_ctx_destroy(c);
     return fail(BX_E_CUDA, "cudaMalloc of fc scratch failed");
   }
@@ -519,27 +591,29 @@ static int load_weights_t(bx_ctx* c, const float* const w[8], const float* const
     const int cin_real = (i == 0) ? 4 : L.cin;
     const size_t src_elems = (size_t)L.cout * cin_real * 8;
     const size_t dst_elems = (size_t)L.taps * L.cout * L.cin;
-    if (!c->wconv[i]) CK(cudaMalloc(&c->wconv[i], dst_elems * 2));
+    const int split = c->split_in[i] ? 1 : 0;
+    if (!c->wconv[i]) CK(cudaMalloc(&c->wconv[i], dst_elems * 2 * ((split && i > 0) ? 2 : 1)));
     if (!c->bconv[i]) CK(cudaMalloc(&c->bconv[i], L.cout * sizeof(float)));
     CK(cudaMemcpy(tmp, w[i], src_elems * sizeof(float), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(c->bconv[i], b[i], L.cout * sizeof(float), cudaMemcpyHostToDevice));
     if (i == 0)
-      prep_conv1_kernel<T><<<(L.cout * 64 + 255) / 256, 256, 0, st>>>(tmp, (T*)c->wconv[i], L.cout);
+      prep_conv1_kernel<T><<<(L.cout * 64 + 255) / 256, 256, 0, st>>>(tmp, (T*)c->wconv[i], L.cout, split);
     else
-      prep_conv_kernel<T><<<(unsigned)((dst_elems + 255) / 256), 256, 0, st>>>(tmp, (T*)c->wconv[i], L.cout, L.cin);
+      prep_conv_kernel<T><<<(unsigned)((dst_elems + 255) / 256), 256, 0, st>>>(tmp, (T*)c->wconv[i], L.cout, L.cin, split);
     g_launches++;
     CK(cudaStreamSynchronize(st));
   }
-  if (!c->wfc1) CK(cudaMalloc(&c->wfc1, (size_t)2048 * 67840 * 2));
+  if (!c->wfc1) CK(cudaMalloc(&c->wfc1, (size_t)2048 * 67840 * 2 * (c->split_in[6] ? 2 : 1)));
   if (!c->bfc1) CK(cudaMalloc(&c->bfc1, 2048 * sizeof(float)));
-  if (!c->wfc2) CK(cudaMalloc(&c->wfc2, (size_t)2048 * 2048 * 2));
+  if (!c->wfc2) CK(cudaMalloc(&c->wfc2, (size_t)2048 * 2048 * 2 * (c->split_in[7] ? 2 : 1)));
   if (!c->bfc2) CK(cudaMalloc(&c->bfc2, 2048 * sizeof(float)));
   CK(cudaMemcpy(tmp, w[6], fc1_elems * sizeof(float), cudaMemcpyHostToDevice));
-  prep_fc1_kernel<T><<<(unsigned)(((size_t)2048 * 67840 + 255) / 256), 256, 0, st>>>(tmp, (T*)c->wfc1);
+  prep_fc1_kernel<T><<<(unsigned)(((size_t)2048 * 67840 + 255) / 256), 256, 0, st>>>(tmp, (T*)c->wfc1,
+                                                                                     c->split_in[6] ? 1 : 0);
   g_launches++;
   CK(cudaStreamSynchronize(st));
   CK(cudaMemcpy(tmp, w[7], (size_t)2002 * 2003 * sizeof(float), cudaMemcpyHostToDevice));
-  prep_fc2_kernel<T><<<(2048 * 2048 + 255) / 256, 256, 0, st>>>(tmp, (T*)c->wfc2);
+  prep_fc2_kernel<T><<<(2048 * 2048 + 255) / 256, 256, 0, st>>>(tmp, (T*)c->wfc2, c->split_in[7] ? 1 : 0);
   g_launches++;
   CK(cudaMemset(c->bfc1, 0, 2048 * sizeof(float)));
   CK(cudaMemset(c->bfc2, 0, 2048 * sizeof(float)));
@@ -589,7 +663,7 @@ int bx_encode_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t*
 // One chunk (m <= cap windows): kernel 1 fused into the conv1 operand, then the network.
 static int forward_chunk_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int m,
                                  float* probs_dev, cudaStream_t st) {
-  if (conv1_gen_enabled()) {
+  if (conv1_gen_enabled(c)) {
     EncParams e = {};
     e.descs = descs_dev; e.alleles = alleles_dev; e.bases2 = c->bases2; e.nmask = c->nmask; e.n_bases = c->n_bases;
     e.L = BX_WINDOW; e.n_seg = m;
@@ -610,7 +684,7 @@ static int forward_chunk_windows(bx_ctx* c, const bx_window_desc* descs_dev, con
 }
 
 static int forward_chunk_onehot(bx_ctx* c, const uint8_t* x, int m, float* probs_dev, cudaStream_t st) {
-  if (conv1_gen_enabled()) {
+  if (conv1_gen_enabled(c)) {
     EncParams e = {};
     e.onehot = x; e.L = BX_WINDOW; e.n_seg = m;
     return run_network(c, m, probs_dev, st, &e, 2);
@@ -820,6 +894,7 @@ int bx_ctx_profile_read(bx_ctx* c, double* ms_out, int64_t* count_out, int reset
 
 int bx_debug_activation(bx_ctx* c, int layer, int n, void* dst_dev, int64_t* count, void* stream) {
   if (!c || layer < 0 || layer > 7 || n < 1 || n > c->cap || !dst_dev) return fail(BX_E_ARG, "invalid arguments");
+  if (c->split_any) return fail(BX_E_STATE, "activation dumps are not available in split-operand mode");
   const void* src = layer == 7 ? c->hid : c->act[layer];
   const size_t elems = layer == 7 ? (size_t)n * 2048 : (size_t)n * act_rows(layer) * act_cols(layer);
   CK(cudaMemcpyAsync(dst_dev, src, elems * 2, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
@@ -942,7 +1017,7 @@ static int run_segment_convs(bx_ctx* c, const bx_window_desc* d, const uint8_t* 
   EncParams e = {};
   e.descs = d; e.alleles = alleles_dev; e.bases2 = c->bases2; e.nmask = c->nmask; e.n_bases = c->n_bases;
   e.L = L; e.n_seg = ns;
-  const bool gen = conv1_gen_enabled();
+  const bool gen = conv1_gen_enabled(c);
   if (!gen) {
     StageTimer t(c, 0, st);
     dim3 grid((g.p1 * 8 + 255) / 256, ns);
@@ -966,13 +1041,16 @@ static int run_segment_convs(bx_ctx* c, const bx_window_desc* d, const uint8_t* 
     if (int r = run_conv_geom(c, 3, ns, g, c->act[3], c->act4h, false, st, nullptr, true)) return r;
     const long long total = (long long)ns * g.p4 * (480 / 8);
     const unsigned blocks = (unsigned)((total + 255) / 256);
-    if (f16)
-      pool_phases_kernel<__half><<<blocks, 256, 0, st>>>((const __half*)c->act4h, (__half*)c->act[4],
-                                                         (__half*)c->act4b, g.ph, g.p4, g.l4b, 480 / 8, total);
+    if (f16 && c->split_in[4])
+      pool_phases_kernel<__half, true><<<blocks, 256, 0, st>>>((const __half*)c->act4h, (__half*)c->act[4],
+                                                               (__half*)c->act4b, g.ph, g.p4, g.l4b, 480 / 8, total);
+    else if (f16)
+      pool_phases_kernel<__half, false><<<blocks, 256, 0, st>>>((const __half*)c->act4h, (__half*)c->act[4],
+                                                                (__half*)c->act4b, g.ph, g.p4, g.l4b, 480 / 8, total);
     else
-      pool_phases_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)c->act4h,
-                                                                (__nv_bfloat16*)c->act[4], (__nv_bfloat16*)c->act4b,
-                                                                g.ph, g.p4, g.l4b, 480 / 8, total);
+      pool_phases_kernel<__nv_bfloat16, false><<<blocks, 256, 0, st>>>(
+          (const __nv_bfloat16*)c->act4h, (__nv_bfloat16*)c->act[4], (__nv_bfloat16*)c->act4b, g.ph, g.p4, g.l4b,
+          480 / 8, total);
     g_launches++;
     CK(cudaGetLastError());
   }
@@ -1002,6 +1080,7 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
   dd.ng = ng; dd.S = n_shifts; dd.shift_major = shift_major ? 1 : 0;
   dd.p6 = sg.p6; dd.p6p = sg.p6p; dd.row0 = patch_row0; dd.valid_a = sg.valid_a; dd.valid_b = sg.valid_b;
   dd.kb_per_split = kFc1KbPerSplit;
+  dd.rw = sg.rw;
   for (int i = 0; i < n_shifts; ++i) { dd.k_of_shift[i] = sg.k_of_shift[i]; dd.si_of_k[i] = -1; }
   for (int i = 0; i < n_shifts; ++i) dd.si_of_k[sg.k_of_shift[i]] = i;
   for (int k = 0; k < n_shifts; ++k) {
@@ -1085,11 +1164,11 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
       if (f16)
         fc1_finalize_delta_kernel<__half><<<blocks, 256, 0, st>>>(c->acc1, stride, c->acc_ref, ref_stride, dd,
                                                                   (long long)d0, kFc1Splits, c->bfc1, (__half*)c->hid,
-                                                                  total);
+                                                                  total, c->split_in[7] ? 1 : 0);
       else
         fc1_finalize_delta_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(c->acc1, stride, c->acc_ref, ref_stride, dd,
                                                                          (long long)d0, kFc1Splits, c->bfc1,
-                                                                         (__nv_bfloat16*)c->hid, total);
+                                                                         (__nv_bfloat16*)c->hid, total, 0);
       g_launches++;
       CK(cudaGetLastError());
     }
@@ -1115,16 +1194,17 @@ static int forward_segments_impl(bx_ctx* c, const bx_window_desc* descs_dev, con
   if (grp_cap < 1)
     return fail(BX_E_ARG, "context capacity (%d windows) is too small for %d segments of %d positions", c->cap,
                 segs_in, seg_len);
-  if (!c->act6b) CK(cudaMalloc(&c->act6b, (size_t)c->cap * act_rows(6) * act_cols(6) * 2));
-  if (!c->fc_in) CK(cudaMalloc(&c->fc_in, (size_t)c->cap * 106 * 640 * 2));
+  if (!c->act6b) CK(cudaMalloc(&c->act6b, (size_t)c->cap * act_rows(6) * act_width(c, 6) * 2));
+  if (!c->fc_in) CK(cudaMalloc(&c->fc_in, (size_t)c->cap * 106 * act_width(c, 6) * 2));
   // ph <= 2*p4 + 1 and n_seg <= cap, n_seg*p4 <= cap*120 (max_segments): n_seg*ph <= cap*241 rows
-  if (!c->act4h) CK(cudaMalloc(&c->act4h, (size_t)c->cap * 241 * act_cols(4) * 2));
-  if (!c->act4b) CK(cudaMalloc(&c->act4b, (size_t)c->cap * act_rows(4) * act_cols(4) * 2));
+  if (!c->act4h) CK(cudaMalloc(&c->act4h, (size_t)c->cap * 241 * act_width(c, 4) * 2));
+  if (!c->act4b) CK(cudaMalloc(&c->act4b, (size_t)c->cap * act_rows(4) * act_width(c, 4) * 2));
   SegGather sg = {};
   sg.segs_per_group = segs_out;
   sg.n_shifts = n_shifts;
   sg.shift_major = shift_major ? 1 : 0;
   sg.p6 = g.p6;
+  sg.rw = (int)act_width(c, 6);
   Geom gp = {};
   if (delta) {
     gp = make_geom(patch_len);
@@ -1134,7 +1214,7 @@ static int forward_segments_impl(bx_ctx* c, const bx_window_desc* descs_dev, con
     sg.valid_a = gp.p6;             // patch conv6 rows computed from complete receptive fields, phase A / phase B
     sg.valid_b = gp.l4b - 14;
     if (sg.valid_b < 1 || gp.p6 < 1) return fail(BX_E_ARG, "patch_len %d is too short", patch_len);
-    const size_t need = (size_t)std::min(grp_cap, n_groups) * 2 * gp.p6 * 640 * 2;
+    const size_t need = (size_t)std::min(grp_cap, n_groups) * 2 * gp.p6 * act_width(c, 6) * 2;
     if (need > c->patch6_bytes) {
       CK(cudaStreamSynchronize(st));
       cudaFree(c->patch6a); cudaFree(c->patch6b);

@@ -60,6 +60,14 @@ struct GemmParams {
   // tile_n[mt] - 1 only (delta mode's alt windows need just the slices whose K range holds changed rows).
   int n_tile_ranges;  // 0 = every tile computes all k_splits slices
   unsigned char tile_lo[32], tile_n[32];
+  // Split-operand mode (BX_DTYPE_F16X3): A = Ah + Al and W = Wh + Wl as fp16 pairs, product = Ah*Wh + Ah*Wl + Al*Wh
+  // accumulated in fp32 (the Al*Wl term is below fp32 resolution).  parts = 3 runs every logical K-block three times:
+  // part 0 (Ah, Wh), part 1 (Ah, Wl: the A stage of part 0 is reused), part 2 (Al, Wh).  parts = 1: plain operands.
+  // Column (K element) of logical K-block kb in the A / B tensor maps:
+  //   A: (kb / a_grp) * a_grp_stride + (kb % a_grp) * 64 + (part == 2 ? a_lo_off : 0)
+  //   B: kb * 64 + (part == 1 ? b_lo_off : 0)
+  int parts, a_grp, a_grp_stride, a_lo_off, b_lo_off;
+  int out_lo_off;    // SPLIT_OUT epilogues: the low half of an output goes out_lo_off elements after the high half
 };
 
 template <int TAPS, int BLOCK_N, int CG>
@@ -101,6 +109,26 @@ __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
+// Two fp32 values -> packed 16-bit high parts (round to nearest) and packed 16-bit residuals (value - high part).
+template <typename T>
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo);
+template <>
+__device__ __forceinline__ void split2<__half>(float a, float b, uint32_t& hi, uint32_t& lo) {
+  a = fminf(a, 65504.f); b = fminf(b, 65504.f);
+  const __half2 h = __floats2half2_rn(a, b);
+  const float2 f = __half22float2(h);
+  const __half2 l = __floats2half2_rn(a - f.x, b - f.y);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+template <>
+__device__ __forceinline__ void split2<__nv_bfloat16>(float a, float b, uint32_t& hi, uint32_t& lo) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  const float2 f = __bfloat1622float2(h);
+  const __nv_bfloat162 l = __floats2bfloat162_rn(a - f.x, b - f.y);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = *reinterpret_cast<const uint32_t*>(&l);
+}
 template <typename T>
 __device__ __forceinline__ uint32_t max2(uint32_t a, uint32_t b);
 template <>
@@ -122,7 +150,7 @@ struct RingState {
   }
 };
 
-template <typename T, int TAPS, int BLOCK_N, int CG, int EPI, int A_MODE = 0>
+template <typename T, int TAPS, int BLOCK_N, int CG, int EPI, int A_MODE = 0, int SPLIT_OUT = 0>
 __global__ void __launch_bounds__(192, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const GemmParams p, const EncParams enc) {
@@ -261,8 +289,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {  // 16-byte piece q = taps 2q, 2q+1; SWIZZLE_128B: piece ^ (row & 7)
                   const unsigned long long lo = s_pat[o + 2 * q], hi = s_pat[o + 2 * q + 1];
-                  *reinterpret_cast<uint4*>(stage + j * 128 + ((q ^ (j & 7)) << 4)) =
-                      make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+                  const uint4 piece = make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+                  *reinterpret_cast<uint4*>(stage + j * 128 + ((q ^ (j & 7)) << 4)) = piece;
+                  // split weights (k_valid = 64): K elements 32..63 multiply the low halves of the weights by the
+                  // same one-hot pattern
+                  if (p.k_valid > 32) *reinterpret_cast<uint4*>(stage + j * 128 + (((q + 4) ^ (j & 7)) << 4)) = piece;
                 }
               }
               fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
@@ -275,22 +306,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             __syncwarp();
             ra.advance<SA>();
           }
-        } else {
+        }
+        const int a_col0 = (kb / p.a_grp) * p.a_grp_stride + (kb % p.a_grp) * 64;
+#pragma unroll 1
+        for (int part = 0; part < p.parts; ++part) {
+        if constexpr (A_MODE == 0) {
+          if (part != 1) {  // part 1 (Ah x Wl) reuses the A stage of part 0
           mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
+          const int a_col = a_col0 + (part == 2 ? p.a_lo_off : 0);
           if (p.debug_flags & 2) {
             if (elect_one() && rank == 0) mbar_arrive_local(fullA(ra.idx));
           } else if (elect_one()) {
             if constexpr (CG == 1) {
               mbar_arrive_expect_tx(fullA(ra.idx), Cfg::A_BYTES);
-              tma_load_2d(sA + ra.idx * Cfg::A_BYTES, &tmA, fullA(ra.idx), kb * 64, row0);
+              tma_load_2d(sA + ra.idx * Cfg::A_BYTES, &tmA, fullA(ra.idx), a_col, row0);
             } else {
               if (rank == 0) mbar_arrive_expect_tx(fullA(ra.idx), 2 * Cfg::A_BYTES);
-              tma_load_2d_pair(sA + ra.idx * Cfg::A_BYTES, &tmA, mapa(fullA(ra.idx), 0), kb * 64, row0);
+              tma_load_2d_pair(sA + ra.idx * Cfg::A_BYTES, &tmA, mapa(fullA(ra.idx), 0), a_col, row0);
             }
           }
           __syncwarp();
           ra.advance<SA>();
+          }
         }
+        const int b_col = kb * 64 + (part == 1 ? p.b_lo_off : 0);
 #pragma unroll 1
         for (int t = 0; t < TAPS; t += Cfg::TPS) {
           mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
@@ -302,19 +341,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               mbar_arrive_expect_tx(fullB(rb.idx), Cfg::B_BYTES);
 #pragma unroll
               for (int j = 0; j < Cfg::TPS; ++j)
-                tma_load_2d(dst + j * Cfg::B_TAP_BYTES, &tmB, fullB(rb.idx), kb * 64, (t + j) * p.n_total + ncol0);
+                tma_load_2d(dst + j * Cfg::B_TAP_BYTES, &tmB, fullB(rb.idx), b_col, (t + j) * p.n_total + ncol0);
             } else {
               if (rank == 0) mbar_arrive_expect_tx(fullB(rb.idx), 2 * Cfg::B_BYTES);
               const uint32_t bar = mapa(fullB(rb.idx), 0);
 #pragma unroll
               for (int j = 0; j < Cfg::TPS; ++j)
-                tma_load_2d_pair(dst + j * Cfg::B_TAP_BYTES, &tmB, bar, kb * 64, (t + j) * p.n_total + ncol0);
+                tma_load_2d_pair(dst + j * Cfg::B_TAP_BYTES, &tmB, bar, b_col, (t + j) * p.n_total + ncol0);
             }
           }
           __syncwarp();
           rb.advance<SB>();
           ++b_fills;
         }
+        }  // part
       }
     }
   } else if (warp == 1) {
@@ -331,7 +371,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t accum = 0;
         for (int kb = kb0; kb < kb1; ++kb) {
           const int kcount = min(4, (p.k_valid - kb * 64 + 15) >> 4);
-          if (A_MODE == 0 || nc == 0) mbar_wait(fullA(ra.idx), ra.phase, 4);
+#pragma unroll 1
+          for (int part = 0; part < p.parts; ++part) {
+          if ((A_MODE == 0 && part != 1) || (A_MODE != 0 && nc == 0)) mbar_wait(fullA(ra.idx), ra.phase, 4);
           const uint32_t a_lo = sw128_desc_lo(sA + ra.idx * Cfg::A_BYTES);
 #pragma unroll 1
           for (int t = 0; t < TAPS; t += Cfg::TPS) {
@@ -364,11 +406,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             accum = 1;
             rb.advance<SB>();
           }
-          if (A_MODE == 0 || nc == p.n_chunks - 1) {  // A_MODE: the generated tile serves every N chunk
+          // release the A stage after its last use: split mode keeps Ah for parts 0 and 1; A_MODE: the generated
+          // tile serves every N chunk
+          if ((A_MODE == 0 && (p.parts == 1 || part >= 1)) || (A_MODE != 0 && nc == p.n_chunks - 1)) {
             if (elect_one()) umma_commit<CG>(emptyA(ra.idx));
             __syncwarp();
             ra.advance<SA>();
           }
+          }  // part
         }
         if (elect_one()) umma_commit<CG>(tfull(rt.idx));
         __syncwarp();
@@ -410,7 +455,51 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
       // One 16-column chunk: registers -> bias/activation -> global.
       auto process = [&](const uint32_t (&v)[16], int c, const float4 (&bq)[4]) {
-        if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU || EPI == EPI_POOL2_BIAS_RELU) {
+        if constexpr (SPLIT_OUT && (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU || EPI == EPI_POOL2_BIAS_RELU)) {
+          // split-operand mode: the next layer reads this activation as an fp16 pair (hi = rounded value, lo = the
+          // rounding residual, out_lo_off elements further along the row); pooling runs on the fp32 values
+          float y[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 b4 = bq[i];
+            y[4 * i] = fmaxf(__uint_as_float(v[4 * i]) + b4.x, 0.f);
+            y[4 * i + 1] = fmaxf(__uint_as_float(v[4 * i + 1]) + b4.y, 0.f);
+            y[4 * i + 2] = fmaxf(__uint_as_float(v[4 * i + 2]) + b4.z, 0.f);
+            y[4 * i + 3] = fmaxf(__uint_as_float(v[4 * i + 3]) + b4.w, 0.f);
+          }
+          if constexpr (EPI != EPI_BIAS_RELU) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              y[i] = fmaxf(y[i], __shfl_xor_sync(0xffffffffu, y[i], 1));
+              if constexpr (EPI == EPI_POOL4_BIAS_RELU) y[i] = fmaxf(y[i], __shfl_xor_sync(0xffffffffu, y[i], 2));
+            }
+          }
+          uint32_t hi[8], lo[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) split2<T>(y[2 * i], y[2 * i + 1], hi[i], lo[i]);
+          T* o = reinterpret_cast<T*>(p.out) + obase + c * 16;
+          T* ol = o + p.out_lo_off;
+          if constexpr (EPI == EPI_BIAS_RELU) {
+            if (valid) { st_global_v8(o, hi); st_global_v8(ol, lo); }
+          } else if constexpr (EPI == EPI_POOL2_BIAS_RELU) {
+            const bool odd = lane & 1;
+            if (valid) {
+              *reinterpret_cast<uint4*>(o + (odd ? 8 : 0)) =
+                  odd ? make_uint4(hi[4], hi[5], hi[6], hi[7]) : make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              *reinterpret_cast<uint4*>(ol + (odd ? 8 : 0)) =
+                  odd ? make_uint4(lo[4], lo[5], lo[6], lo[7]) : make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+          } else {
+            uint32_t h0 = hi[0], h1 = hi[1], l0 = lo[0], l1 = lo[1];
+            if (j == 1) { h0 = hi[2]; h1 = hi[3]; l0 = lo[2]; l1 = lo[3]; }
+            if (j == 2) { h0 = hi[4]; h1 = hi[5]; l0 = lo[4]; l1 = lo[5]; }
+            if (j == 3) { h0 = hi[6]; h1 = hi[7]; l0 = lo[6]; l1 = lo[7]; }
+            if (valid) {
+              *reinterpret_cast<uint2*>(o + 4 * j) = make_uint2(h0, h1);
+              *reinterpret_cast<uint2*>(ol + 4 * j) = make_uint2(l0, l1);
+            }
+          }
+        } else if constexpr (EPI == EPI_BIAS_RELU || EPI == EPI_POOL4_BIAS_RELU || EPI == EPI_POOL2_BIAS_RELU) {
           uint32_t pk[8];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {

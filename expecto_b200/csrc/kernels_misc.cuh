@@ -138,7 +138,26 @@ encode_im2col_seg_kernel(const bx_window_desc* __restrict__ descs, const uint8_t
 // 2j, 2j+1): phase A pools rows 4g..4g+3 = max(h[2g], h[2g+1]); phase B (windows whose offset is an odd multiple
 // of 200 bp) pools rows 4g+2..4g+5 = max(h[2g+1], h[2g+2]).  max is exact, so both equal the fused MaxPool4
 // epilogue bit for bit.  One thread per 8 channels of one pooled row; rows >= l4b of phase B are zero-filled.
+//
+// SPLIT (split-operand mode): rows hold [hi(C) | lo(C)] fp16 pairs (value = hi + lo, |lo| <= ulp(hi)/2); the larger
+// value is the pair that is larger lexicographically, and because the hi/lo split is monotonic this equals the split
+// of the fp32 maximum the fused epilogue forms — still bit-identical to the per-window path.
 template <typename T>
+__device__ __forceinline__ void pair_max8(const uint4& ah, const uint4& al, const uint4& bh, const uint4& bl, uint4& oh,
+                                          uint4& ol) {
+  const T* xh = reinterpret_cast<const T*>(&ah); const T* xl = reinterpret_cast<const T*>(&al);
+  const T* yh = reinterpret_cast<const T*>(&bh); const T* yl = reinterpret_cast<const T*>(&bl);
+  T* rh = reinterpret_cast<T*>(&oh); T* rl = reinterpret_cast<T*>(&ol);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float a1 = (float)xh[i], b1 = (float)yh[i];
+    const bool first = a1 > b1 || (a1 == b1 && (float)xl[i] >= (float)yl[i]);
+    rh[i] = first ? xh[i] : yh[i];
+    rl[i] = first ? xl[i] : yl[i];
+  }
+}
+
+template <typename T, bool SPLIT>
 __global__ void __launch_bounds__(256)
 pool_phases_kernel(const T* __restrict__ h, T* __restrict__ a, T* __restrict__ b, int ph, int p4, int l4b, int c8,
                    long long total) {
@@ -148,6 +167,21 @@ pool_phases_kernel(const T* __restrict__ h, T* __restrict__ a, T* __restrict__ b
   const long long row = idx / c8;
   const int g = (int)(row % p4);
   const long long seg = row / p4;
+  if constexpr (SPLIT) {
+    // c8 = C/8 uint4 of high parts per row, followed by as many of low parts (row width 2*c8 uint4)
+    const int rw = 2 * c8;
+    const uint4* hp = reinterpret_cast<const uint4*>(h) + (seg * ph + 2 * g) * rw + c;
+    const uint4 h0 = hp[0], l0 = hp[c8], h1 = hp[rw], l1 = hp[rw + c8];
+    uint4 oh, ol;
+    pair_max8<T>(h0, l0, h1, l1, oh, ol);
+    uint4* ap = reinterpret_cast<uint4*>(a) + row * rw + c;
+    ap[0] = oh; ap[c8] = ol;
+    oh = ol = make_uint4(0, 0, 0, 0);
+    if (g < l4b) pair_max8<T>(h1, l1, hp[2 * (size_t)rw], hp[2 * (size_t)rw + c8], oh, ol);
+    uint4* bp = reinterpret_cast<uint4*>(b) + row * rw + c;
+    bp[0] = oh; bp[c8] = ol;
+    return;
+  }
   const uint4* hp = reinterpret_cast<const uint4*>(h) + (seg * ph + 2 * g) * c8 + c;
   auto mx = [](uint4 x, uint4 y) {
     uint4 r;
@@ -171,6 +205,7 @@ struct SegGather {
   // delta mode: only the two ref segments of a group were run in full; alt windows take conv6 rows
   // [row0, row0 + valid) from the group's alt patch and every other row from the ref segment of the same strand
   int delta, p6p, row0, valid_a, valid_b;
+  int rw;             // elements per conv6 row: 640, or 1280 in split-operand mode ([hi | lo])
   int k_of_shift[200]; // offset index (window start = 200*k positions into a non-reversed segment) per shift index
 };
 
@@ -193,18 +228,19 @@ gather_fc1_kernel(const T* __restrict__ act6a, const T* __restrict__ act6b, cons
   if (descs[seg].flags & 2) k = g.n_shifts - 1 - k;  // reversed offset order (rc segments, '-' strand genes)
   const int j = k >> 1;
   const int off = ((k & 1) ? 12 : 0) + 25 * j;       // first conv6 row of the window within its phase
-  const T* src = ((k & 1) ? act6b : act6a) + ((size_t)seg * g.p6 + off) * 640;
+  const T* src = ((k & 1) ? act6b : act6a) + ((size_t)seg * g.p6 + off) * g.rw;
   const uint4* s4 = reinterpret_cast<const uint4*>(src);
-  uint4* d4 = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * 106 * 640);
-  constexpr int N16 = 106 * 640 * 2 / 16;
+  uint4* d4 = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * 106 * g.rw);
+  const int r16 = g.rw / 8;                           // 16-byte pieces per conv6 row (80, or 160 in split mode)
+  const int N16 = 106 * r16;
   if (g.delta && q >= 2) {
     const int valid = (k & 1) ? g.valid_b : g.valid_a;
     const int lo = g.row0 - off;                      // window rows [lo, lo + valid) come from the patch
-    const uint4* p4 = reinterpret_cast<const uint4*>(((k & 1) ? patch6b : patch6a) + (size_t)seg * g.p6p * 640);
+    const uint4* p4 = reinterpret_cast<const uint4*>(((k & 1) ? patch6b : patch6a) + (size_t)seg * g.p6p * g.rw);
     for (int i = threadIdx.x; i < N16; i += 256) {
-      const int l = i / 80;                           // 80 x 16 bytes per 640-channel row
+      const int l = i / r16;
       const int pr = l - lo;
-      d4[i] = (pr >= 0 && pr < valid) ? __ldg(p4 + (size_t)pr * 80 + (i - l * 80)) : __ldg(s4 + i);
+      d4[i] = (pr >= 0 && pr < valid) ? __ldg(p4 + (size_t)pr * r16 + (i - l * r16)) : __ldg(s4 + i);
     }
   } else {
     for (int i = threadIdx.x; i < N16; i += 256) d4[i] = __ldg(s4 + i);
@@ -216,50 +252,84 @@ template <typename T> __device__ __forceinline__ T to_t(float v);
 template <> __device__ __forceinline__ __half to_t<__half>(float v) { return __float2half_rn(v); }
 template <> __device__ __forceinline__ __nv_bfloat16 to_t<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
 
-// conv1: src [320,4,1,8] -> dst [320,64], k = t*4 + c, k >= 32 zero.
+// Split-operand mode stores every weight as an fp16 pair: the rounded value and, `lo_off` columns further along the
+// row, the rounding residual (value - rounded value, itself rounded to 16 bits).
 template <typename T>
-__global__ void prep_conv1_kernel(const float* __restrict__ src, T* __restrict__ dst, int cout) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= cout * 64) return;
-  const int co = idx >> 6, k = idx & 63;
-  float v = 0.f;
-  if (k < 32) { const int t = k >> 2, c = k & 3; v = src[(co * 4 + c) * 8 + t]; }
-  dst[idx] = to_t<T>(v);
+__device__ __forceinline__ void store_weight(T* __restrict__ row, size_t col, float v, int lo_off) {
+  const T h = to_t<T>(v);
+  row[col] = h;
+  if (lo_off > 0) row[col + lo_off] = to_t<T>(v - (float)h);
 }
-// conv2..6: src [Cout,Cin,1,8] -> dst [8*Cout, Cin] (tap-major, K-major rows).
+// conv1: src [320,4,1,8] -> dst [320,64], k = t*4 + c; k >= 32 zero, or (split) the low halves.
 template <typename T>
-__global__ void prep_conv_kernel(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin) {
+__global__ void prep_conv1_kernel(const float* __restrict__ src, T* __restrict__ dst, int cout, int split) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= cout * 32) return;
+  const int co = idx >> 5, k = idx & 31;
+  const int t = k >> 2, c = k & 3;
+  const float v = src[(co * 4 + c) * 8 + t];
+  T* row = dst + (size_t)co * 64;
+  row[k + 32] = to_t<T>(0.f);
+  store_weight<T>(row, k, v, split ? 32 : 0);
+}
+// conv2..6: src [Cout,Cin,1,8] -> dst [8*Cout, ld] (tap-major, K-major rows; ld = Cin, or 2*Cin in split mode).
+template <typename T>
+__global__ void prep_conv_kernel(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin, int split) {
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (size_t)8 * cout * cin) return;
   const int ci = idx % cin;
   const int co = (idx / cin) % cout;
   const int t = idx / ((size_t)cin * cout);
-  dst[idx] = to_t<T>(src[((size_t)co * cin + ci) * 8 + t]);
+  const size_t ld = split ? 2 * (size_t)cin : (size_t)cin;
+  store_weight<T>(dst + ((size_t)t * cout + co) * ld, ci, src[((size_t)co * cin + ci) * 8 + t], split ? cin : 0);
 }
-// fc1: src [2003, 67840] with column c*106+l -> dst [2048, 67840] with column l*640+c, rows >= 2003 zero.
+// fc1: src [2003, 67840] with column c*106+l -> dst [2048, ld] with column l*640+c, rows >= 2003 zero.
 template <typename T>
-__global__ void prep_fc1_kernel(const float* __restrict__ src, T* __restrict__ dst) {
+__global__ void prep_fc1_kernel(const float* __restrict__ src, T* __restrict__ dst, int split) {
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (size_t)2048 * 67840) return;
   const int col = idx % 67840;
   const int n = idx / 67840;
   const int l = col / 640, c = col - l * 640;
-  dst[idx] = to_t<T>(n < 2003 ? src[(size_t)n * 67840 + c * 106 + l] : 0.f);
+  const size_t ld = split ? 2 * (size_t)67840 : (size_t)67840;
+  store_weight<T>(dst + (size_t)n * ld, col, n < 2003 ? src[(size_t)n * 67840 + c * 106 + l] : 0.f, split ? 67840 : 0);
 }
-// fc2: src [2002, 2003] -> dst [2048, 2048] zero padded.
+// fc2: src [2002, 2003] -> dst [2048, ld] zero padded (ld = 2048, or 4096 in split mode).
 template <typename T>
-__global__ void prep_fc2_kernel(const float* __restrict__ src, T* __restrict__ dst) {
+__global__ void prep_fc2_kernel(const float* __restrict__ src, T* __restrict__ dst, int split) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= 2048 * 2048) return;
   const int k = idx & 2047, n = idx >> 11;
-  dst[idx] = to_t<T>((n < 2002 && k < 2003) ? src[(size_t)n * 2003 + k] : 0.f);
+  const size_t ld = split ? 4096 : 2048;
+  store_weight<T>(dst + (size_t)n * ld, k, (n < 2002 && k < 2003) ? src[(size_t)n * 2003 + k] : 0.f, split ? 2048 : 0);
+}
+
+// relu + round of four consecutive hidden units starting at flat index idx of [n, 2048]; split-operand mode writes
+// rows of 4096 = [hi(2048) | lo(2048)].
+template <typename T>
+__device__ __forceinline__ void store_hidden(T* __restrict__ h, size_t idx, int split, float x0, float x1, float x2,
+                                             float x3) {
+  const float v[4] = {fminf(fmaxf(x0, 0.f), 65504.f), fminf(fmaxf(x1, 0.f), 65504.f), fminf(fmaxf(x2, 0.f), 65504.f),
+                      fminf(fmaxf(x3, 0.f), 65504.f)};
+  if (!split) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[idx + i] = to_t<T>(v[i]);
+    return;
+  }
+  T* row = h + (idx >> 11) * 4096 + (idx & 2047);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const T hi = to_t<T>(v[i]);
+    row[i] = hi;
+    row[2048 + i] = to_t<T>(v[i] - (float)hi);
+  }
 }
 
 // fc1 finaliser: h = relu(sum_ks part[ks] + b1) -> 16-bit [n, 2048]; slices are summed in a fixed order so
 // the result does not depend on scheduling (the split-K GEMM writes plain stores, no atomics).
 template <typename T>
 __global__ void fc1_finalize_kernel(const float* __restrict__ part, int k_splits, size_t split_stride,
-                                    const float* __restrict__ bias, T* __restrict__ h, size_t total) {
+                                    const float* __restrict__ bias, T* __restrict__ h, size_t total, int split) {
   const size_t idx = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (idx >= total) return;
   float4 a = *reinterpret_cast<const float4*>(part + idx);
@@ -268,11 +338,7 @@ __global__ void fc1_finalize_kernel(const float* __restrict__ part, int k_splits
     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
   }
   const float4 b4 = *reinterpret_cast<const float4*>(bias + (idx & 2047));
-  T* o = h + idx;
-  o[0] = to_t<T>(fminf(fmaxf(a.x + b4.x, 0.f), 65504.f));
-  o[1] = to_t<T>(fminf(fmaxf(a.y + b4.y, 0.f), 65504.f));
-  o[2] = to_t<T>(fminf(fmaxf(a.z + b4.z, 0.f), 65504.f));
-  o[3] = to_t<T>(fminf(fmaxf(a.w + b4.w, 0.f), 65504.f));
+  store_hidden<T>(h, idx, split, a.x + b4.x, a.y + b4.y, a.z + b4.z, a.w + b4.w);
 }
 
 // ------------------------------------------------------------------ delta mode, dense layers
@@ -288,6 +354,7 @@ struct DeltaDense {
   int ng, S, shift_major;
   int p6, p6p, row0, valid_a, valid_b;   // as SegGather
   int kb_per_split;                       // K-blocks (64 elements, a tenth of a 640-channel row) per FC1 slice
+  int rw;                                 // elements per conv6 row: 640, or 1280 in split-operand mode ([hi | lo])
   int k_of_shift[200], si_of_k[200];
 };
 
@@ -332,22 +399,23 @@ gather_fc1_delta_kernel(const T* __restrict__ act6a, const T* __restrict__ act6b
   const DeltaClass cl = delta_class(g, c);
   const long long seg = (long long)grp * 2 + t;
   const bool pb = c & 1;
-  const uint4* s4 = reinterpret_cast<const uint4*>((pb ? act6b : act6a) + ((size_t)seg * g.p6 + cl.off) * 640);
-  uint4* d4 = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * 106 * 640);
+  const uint4* s4 = reinterpret_cast<const uint4*>((pb ? act6b : act6a) + ((size_t)seg * g.p6 + cl.off) * g.rw);
+  uint4* d4 = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * 106 * g.rw);
+  const int r16 = g.rw / 8;                                       // 16-byte pieces per conv6 row
   if (!alt) {
-    constexpr int N16 = 106 * 640 * 2 / 16;
+    const int N16 = 106 * r16;
     for (int i = threadIdx.x; i < N16; i += 256) d4[i] = __ldg(s4 + i);
     return;
   }
-  const uint4* p4 = reinterpret_cast<const uint4*>((pb ? patch6b : patch6a) + (size_t)seg * g.p6p * 640);
+  const uint4* p4 = reinterpret_cast<const uint4*>((pb ? patch6b : patch6a) + (size_t)seg * g.p6p * g.rw);
   if (cl.ks_lo > cl.ks_hi) return;                               // nothing of this window is recomputed
   const int plo = g.row0 - cl.off;                               // window row of patch row 0
   const int r_lo = cl.ks_lo * g.kb_per_split / 10;               // conv6 rows the computed slices read
   int r_hi = ((cl.ks_hi + 1) * g.kb_per_split + 9) / 10;
   if (r_hi > 106) r_hi = 106;
-  for (int i = r_lo * 80 + threadIdx.x; i < r_hi * 80; i += 256) {
-    const int l = i / 80;                                         // 80 x 16 bytes per 640-channel row
-    d4[i] = (l >= cl.lo && l < cl.hi) ? __ldg(p4 + (size_t)(l - plo) * 80 + (i - l * 80)) : __ldg(s4 + i);
+  for (int i = r_lo * r16 + threadIdx.x; i < r_hi * r16; i += 256) {
+    const int l = i / r16;
+    d4[i] = (l >= cl.lo && l < cl.hi) ? __ldg(p4 + (size_t)(l - plo) * r16 + (i - l * r16)) : __ldg(s4 + i);
   }
 }
 
@@ -357,7 +425,7 @@ template <typename T>
 __global__ void fc1_finalize_delta_kernel(const float* __restrict__ part, size_t split_stride,
                                           const float* __restrict__ ref_part, size_t ref_stride, const DeltaDense g,
                                           long long a0, int k_splits, const float* __restrict__ bias,
-                                          T* __restrict__ h, size_t total) {
+                                          T* __restrict__ h, size_t total, int split) {
   const size_t idx = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (idx >= total) return;
   const long long ar = a0 + (long long)(idx >> 11);
@@ -377,11 +445,7 @@ __global__ void fc1_finalize_delta_kernel(const float* __restrict__ part, size_t
     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
   }
   const float4 b4 = *reinterpret_cast<const float4*>(bias + (idx & 2047));
-  T* o = h + idx;
-  o[0] = to_t<T>(fminf(fmaxf(a.x + b4.x, 0.f), 65504.f));
-  o[1] = to_t<T>(fminf(fmaxf(a.y + b4.y, 0.f), 65504.f));
-  o[2] = to_t<T>(fminf(fmaxf(a.z + b4.z, 0.f), 65504.f));
-  o[3] = to_t<T>(fminf(fmaxf(a.w + b4.w, 0.f), 65504.f));
+  store_hidden<T>(h, idx, split, a.x + b4.x, a.y + b4.y, a.z + b4.z, a.w + b4.w);
 }
 
 // Probabilities of a piece of dense rows -> their windows' rows of the final output (shift-major or group-major).

@@ -27,8 +27,9 @@ def _stream_ptr(device: torch.device) -> int:
 
 
 class BelugaEngine:
-    """Beluga forward on one B200.  ``dtype`` is the tensor-core operand type ("f16" or "bf16");
-    accumulation, bias, ReLU/MaxPool inputs, sigmoid and all outputs are fp32."""
+    """Beluga forward on one B200.  ``dtype`` is the tensor-core operand type: "f16" (default), "bf16", or "f16x3" —
+    fp16 operands split into (hi, lo) pairs, three MMAs per product, ~1e-5 from the fp32 reference at a third of
+    the throughput; accumulation, bias, ReLU/MaxPool inputs, sigmoid and all outputs are fp32."""
 
     def __init__(self, device: int | str | torch.device = 0, dtype: str = "f16", cta_group: int = 2,
                  capacity: int = 1024):
@@ -38,7 +39,7 @@ class BelugaEngine:
         self.dtype = dtype
         self.capacity = int(capacity)
         self._ctx = C.c_void_p()
-        code = {"f16": _lib.DTYPE_F16, "bf16": _lib.DTYPE_BF16}[dtype]
+        code = {"f16": _lib.DTYPE_F16, "bf16": _lib.DTYPE_BF16, "f16x3": _lib.DTYPE_F16X3}[dtype]
         check(lib().bx_ctx_create(self.device.index or 0, code, cta_group, self.capacity, C.byref(self._ctx)))
         self._genome = None
         self._keep = []
@@ -255,7 +256,7 @@ class BelugaEngine:
     def debug_activation(self, layer: int, n: int) -> torch.Tensor:
         """Internal activation after the last forward: [n, pitch, C] in the operand dtype (test hook)."""
         rows, cols = _ACT_SHAPES[layer]
-        tdt = torch.float16 if self.dtype == "f16" else torch.bfloat16
+        tdt = torch.bfloat16 if self.dtype == "bf16" else torch.float16
         dst = torch.empty((n, rows, cols), dtype=tdt, device=self.device)
         cnt = C.c_int64()
         check(lib().bx_debug_activation(self._ctx, layer, n, dst.data_ptr(), C.byref(cnt), _stream_ptr(self.device)))

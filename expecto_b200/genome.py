@@ -7,9 +7,11 @@ Layout handed to the kernels (include/beluga_b200.h, bx_ctx_set_genome):
 * ``nmask``   uint32, 1 bit per base; 1 = all-zero column (``N n H -`` in ``mydict``).
 
 Contigs are concatenated in file order, each starting on a 32-base boundary after ``PAD`` bases of
-N, so a window that runs off a contig reads zero columns.  (The reference's behaviour there is
-accidental — negative Python slice indices / short strings from pyfasta — and is not reproduced;
-SURVEY §7 hard part 2.)  Characters outside ``mydict`` make the reference raise ``KeyError`` when a
+N, so a window that runs off a contig reads zero columns.  ``PAD`` exceeds the farthest any window of the
+path reaches from a coordinate inside its contig: compute_expecto_features.py:105-111 goes 20,000 + 1,000 bp
+either side of a TSS, chromatin.py:202-206 at most maxshift + 1,050 bp plus the allele.  (The reference's
+behaviour off a contig end is accidental — negative Python slice indices / short strings from pyfasta — and is not
+reproduced; SURVEY §7 hard part 2.)  Characters outside ``mydict`` make the reference raise ``KeyError`` when a
 window touches them; they are recorded in ``invalid`` and checked on the host before any launch.
 """
 from __future__ import annotations
@@ -18,7 +20,7 @@ import os
 
 import numpy as np
 
-PAD = 4096
+PAD = 24576  # >= 21,000 (TSS windows: +-20,000 shift +-1,000 half window) + slack, a multiple of 32
 _CODE = np.full(256, 255, dtype=np.uint8)
 for _i, _c in enumerate("AGCT"):
     _CODE[ord(_c)] = _i
@@ -46,6 +48,7 @@ class PackedGenome:
         self.bases2 = np.zeros(0, dtype=np.uint32)
         self.nmask = np.zeros(0, dtype=np.uint32)
         self.n_bases = 0
+        self.pad = PAD                               # N bases before / after every contig in this layout
         self.invalid = np.zeros(0, dtype=np.int64)  # sorted global indices of characters outside mydict
 
     # ------------------------------------------------------------------ construction
@@ -116,7 +119,9 @@ class PackedGenome:
         two produce identical arrays (tests/test_gpu_parity.py)."""
         cpath = path + ".bx2.npz"
         if cache and os.path.exists(cpath) and os.path.getmtime(cpath) >= os.path.getmtime(path):
-            return cls.load(cpath)
+            g = cls.load(cpath)
+            if g.pad >= PAD:   # caches written with a narrower inter-contig padding are rebuilt
+                return g
         if device is not None:
             g = cls._from_fasta_device(path, device)
             if cache:
@@ -235,7 +240,7 @@ class PackedGenome:
         return g
 
     def save(self, path: str) -> None:
-        np.savez(path, bases2=self.bases2, nmask=self.nmask, invalid=self.invalid,
+        np.savez(path, bases2=self.bases2, nmask=self.nmask, invalid=self.invalid, pad=np.int64(self.pad),
                  names=np.array(self.names), offsets=np.array([self.offsets[n] for n in self.names], dtype=np.int64),
                  lengths=np.array([self.lengths[n] for n in self.names], dtype=np.int64))
 
@@ -247,6 +252,7 @@ class PackedGenome:
         g.offsets = {n: int(o) for n, o in zip(g.names, z["offsets"])}
         g.lengths = {n: int(o) for n, o in zip(g.names, z["lengths"])}
         g.bases2, g.nmask, g.invalid = z["bases2"], z["nmask"], z["invalid"]
+        g.pad = int(z["pad"]) if "pad" in z.files else 4096  # the padding of caches that predate the field
         g.n_bases = int(g.nmask.size) * 32
         return g
 

@@ -51,6 +51,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("-o", action="store", dest="out_dir")
     # extensions
     p.add_argument("--modelList", default=None, help="file with one model path per line (upstream interface)")
+    p.add_argument("--lambert_csv", default="./resources/Lambert-hgnc-symbol-check.csv",
+                   help="--intersect_with_lambert: table with an 'Approved symbol' column (cluster_utils.py:5)")
+    p.add_argument("--hgnc_mapping_csv", default="./resources/beluga_hgnc_mapping.csv",
+                   help="--intersect_with_lambert: Beluga assay -> HGNC symbol table (cluster_utils.py:6)")
     p.add_argument("--device", type=int, default=0)
     p.add_argument("--vcf", default=None,
                    help="compute the chromatin effects of this VCF in-process (segment + delta mode) instead of reading "
@@ -63,8 +67,34 @@ def build_parser() -> argparse.ArgumentParser:
     return p
 
 
+def lambert_mask(assays, lambert_csv: str, mapping_csv: str) -> np.ndarray:
+    """The --intersect_with_lambert clause of cluster_utils.get_keep_mask (cluster_utils.py:26-42): every Beluga assay
+    name found in the index of the HGNC mapping table (rows without an approved symbol dropped) is replaced by that
+    row's approved symbol in upper case — when the name has several rows, by the first one whose ``Match type`` is
+    "Approved symbol" — and a feature is kept when the resulting name is one of the Lambert table's approved symbols."""
+    import pandas as pd
+
+    lambert = pd.read_csv(lambert_csv, index_col=0)
+    mapping = pd.read_csv(mapping_csv, index_col=0).dropna(subset=["Approved symbol"])
+    symbol_of, n_rows = {}, {}
+    for name, mtype, sym in zip(mapping.index, mapping["Match type"], mapping["Approved symbol"]):
+        n_rows[name] = n_rows.get(name, 0) + 1
+        if name not in symbol_of or (symbol_of[name][0] != "Approved symbol" and mtype == "Approved symbol"):
+            symbol_of[name] = (mtype, str(sym).upper())
+    for name, k in n_rows.items():
+        if k > 1 and symbol_of[name][0] != "Approved symbol":
+            # the reference indexes .iloc[0] of an empty selection here
+            raise IndexError(f"{mapping_csv}: {name!r} has {k} rows, none with Match type 'Approved symbol'")
+    approved = set(lambert["Approved symbol"].values)
+    out = np.zeros(len(assays), dtype=bool)
+    for i, a in enumerate(assays):
+        a = symbol_of[a][1] if a in symbol_of else a
+        out[i] = (a in approved) and not (isinstance(a, float) and np.isnan(a))
+    return out
+
+
 def keep_mask(features_tsv: str, args) -> np.ndarray:
-    """cluster_utils.get_keep_mask (cluster_utils.py:8-49) for the flags that need no extra resource files."""
+    """cluster_utils.get_keep_mask (cluster_utils.py:8-49)."""
     import pandas as pd
 
     df = pd.read_csv(features_tsv, sep="\t", index_col=0)
@@ -79,8 +109,10 @@ def keep_mask(features_tsv: str, args) -> np.ndarray:
         print("not including histone features")
         mask &= (df["Assay type"] != "Histone").values
     if args.intersect_with_lambert:
-        raise NotImplementedError("--intersect_with_lambert needs resources/Lambert-hgnc-symbol-check.csv and "
-                                  "beluga_hgnc_mapping.csv, which are not part of the reference repository")
+        print("intersecting with Lambert data")
+        mask &= lambert_mask(list(df["Assay"].values),
+                             getattr(args, "lambert_csv", "./resources/Lambert-hgnc-symbol-check.csv"),
+                             getattr(args, "hgnc_mapping_csv", "./resources/beluga_hgnc_mapping.csv"))
     if args.no_pol2:
         print("taking out Pol2*")
         mask &= ~df["Assay"].astype(str).str.startswith("Pol").values
@@ -341,10 +373,14 @@ def run(args, engine=None, genome=None) -> dict:
     lap("score_s")
 
     df = coor
-    df["dist"] = dist if args.fixeddist else -np.asarray(gene.iloc[:, -1])
+    # predict.py:240: with --fixeddist the column holds the int scalar itself ("500", not "500.0")
+    df["dist"] = int(args.fixeddist) if args.fixeddist else -np.asarray(gene.iloc[:, -1])
     df["gene"] = genename
     df["strand"] = strand
-    cols = {"REF": ref[:, 0], "ALT": alt[:, 0], "SED": alt[:, 0] - ref[:, 0]}
+    # the reference keeps xgboost's float32 predictions in float64 arrays (compute_effects' np.zeros), so REF / ALT
+    # print as widened float32 values and SED = alt - ref is a float64 difference (predict.py:158-161,264)
+    ref64, alt64 = ref[:, 0].astype(np.float64), alt[:, 0].astype(np.float64)
+    cols = {"REF": ref64, "ALT": alt64, "SED": alt64 - ref64}
     for i, p in enumerate(paths[1:], start=1):  # --modelList: one SED column per extra model
         cols[f"SED_{os.path.basename(p)}"] = alt[:, i] - ref[:, i]
     df = pd.concat([df.reset_index()] + [pd.DataFrame(v, columns=[k]) for k, v in cols.items()], axis=1,

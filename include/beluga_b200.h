@@ -26,6 +26,11 @@ extern "C" {
 
 #define BX_DTYPE_F16 0
 #define BX_DTYPE_BF16 1
+/* fp16 operands split into (hi, lo) pairs: every product is Ah*Wh + Ah*Wl + Al*Wh with fp32 accumulation (three
+ * tcgen05.mma per K step), which carries ~21 significant bits of both operands through all eight layers.  Three
+ * times the tensor work of BX_DTYPE_F16; for callers that need the reference's fp32 results to ~1e-5 on the
+ * probabilities rather than the 2e-3 bar. */
+#define BX_DTYPE_F16X3 2
 
 #define BX_WINDOW 2000     /* Beluga input length, chromatin.py:35-36 */
 #define BX_FEATURES 2002   /* Beluga outputs, Beluga.py:45 */

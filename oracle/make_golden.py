@@ -466,6 +466,69 @@ def stage_keep_mask():
     print(f"[keep mask] {len(combos)} flag combinations on {len(df)} features: reference masks stored")
 
 
+def lambert_tables(assays, seed=9):
+    """Seeded stand-ins for resources/Lambert-hgnc-symbol-check.csv and resources/beluga_hgnc_mapping.csv (neither is
+    in the reference repository): a mapping table whose index holds a third of the Beluga assay names — some twice with
+    different ``Match type`` values, some without an approved symbol, some mapped to a differently-cased or different
+    symbol — and a Lambert table listing about half of the resulting symbols plus unrelated ones."""
+    import pandas as pd
+    rng = np.random.default_rng(seed)
+    uniq = sorted(set(assays))
+    picked = [a for a in uniq if rng.random() < 0.35]
+    rows = []
+    for a in picked:
+        u = rng.random()
+        sym = a.upper() if u < 0.5 else (a.lower() + "x" if u < 0.7 else "SYM" + str(int(rng.integers(1000))))
+        if u > 0.9:
+            rows.append((a, "Unmatched", np.nan))
+        elif rng.random() < 0.25:   # two rows: the "Approved symbol" one wins, wherever it stands
+            other = (a, "Previous symbol", "OLD" + str(int(rng.integers(1000))))
+            good = (a, "Approved symbol", sym)
+            rows += [other, good] if rng.random() < 0.5 else [good, other]
+        else:
+            rows.append((a, "Approved symbol" if rng.random() < 0.8 else "Alias symbol", sym))
+    mapping = pd.DataFrame(rows, columns=["Input", "Match type", "Approved symbol"]).set_index("Input")
+    symbols = sorted({str(s).upper() for s in mapping["Approved symbol"].dropna()} | {a for a in uniq if a not in picked})
+    keep = [s for s in symbols if rng.random() < 0.5] + ["ZNF9999", "NOTABELUGAASSAY"]
+    lambert = pd.DataFrame({"Input": keep, "Approved symbol": keep})
+    return lambert, mapping
+
+
+def stage_keep_mask_lambert(work):
+    """cluster_utils.get_keep_mask with intersect_with_lambert=True (cluster_utils.py:26-42), run from a scratch cwd
+    holding the two seeded resource tables, alone and combined with --no_dnase_features / --no_pol2."""
+    import contextlib
+    import io
+    import pandas as pd
+    sys.path.insert(0, REF)
+    import cluster_utils
+    df = pd.read_csv(os.path.join(REF, "resources", "deepsea_beluga_2002_features.tsv"), sep="\t", index_col=0)
+    lambert, mapping = lambert_tables([str(x) for x in df["Assay"]])
+    os.makedirs(os.path.join(work, "resources"), exist_ok=True)
+    lp, mp = (os.path.join(work, "resources", n) for n in ("Lambert-hgnc-symbol-check.csv", "beluga_hgnc_mapping.csv"))
+    lambert.to_csv(lp)
+    mapping.to_csv(mp)
+    combos, masks = [], []
+    cwd = os.getcwd()
+    os.chdir(work)
+    try:
+        for dn, po in ((False, False), (True, False), (False, True), (True, True)):
+            with contextlib.redirect_stdout(io.StringIO()):
+                m = cluster_utils.get_keep_mask(df, False, dn, False, True, po, return_hgnc_df=True)[0]
+            combos.append([dn, po])
+            masks.append(np.packbits(np.asarray(m, dtype=bool)))
+    finally:
+        os.chdir(cwd)
+    np.savez_compressed(os.path.join(GOLD, "keep_mask_lambert_golden.npz"),
+                        assay=np.array([str(x) for x in df["Assay"]], dtype=str),
+                        assay_type=np.array([str(x) for x in df["Assay type"]], dtype=str),
+                        lambert_csv=np.array(open(lp).read()), mapping_csv=np.array(open(mp).read()),
+                        combos=np.array(combos), masks=np.stack(masks))
+    kept = int(np.unpackbits(masks[0])[:len(df)].sum())
+    print(f"[keep mask / lambert] {len(mapping)} mapping rows, {len(lambert)} Lambert symbols: {kept} of {len(df)} "
+          "features kept; reference masks stored")
+
+
 def stage_replicate(work, sd, genome):
     """replicate_expecto_features.py as a subprocess on the two compute_expecto_features genes."""
     genes = GI.cfg4_genes()
@@ -500,6 +563,7 @@ def main():
     ap.add_argument("--workdir", default="/tmp/bx_golden")
     ap.add_argument("--skip-scripts", action="store_true", help="only the import-level stages (fast)")
     ap.add_argument("--only-closest", action="store_true", help="only the make_closest_genes_file.py stage")
+    ap.add_argument("--only-keep-mask", action="store_true", help="only the cluster_utils.get_keep_mask stages")
     ap.add_argument("--only-features-override", action="store_true",
                     help="only the compute_expecto_features.py TSS-override stage")
     ap.add_argument("--only-ref-all-genes", action="store_true", help="only the geuvadis_predict_ref_all_genes.py stage")
@@ -510,6 +574,11 @@ def main():
     if args.only_closest:
         os.makedirs(args.workdir, exist_ok=True)
         stage_closest_genes(args.workdir)
+        return
+    if args.only_keep_mask:
+        os.makedirs(args.workdir, exist_ok=True)
+        stage_keep_mask()
+        stage_keep_mask_lambert(args.workdir)
         return
     if args.only_features_override:
         sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
@@ -532,6 +601,8 @@ def main():
         return
     stage_encode()
     stage_keep_mask()
+    os.makedirs(args.workdir, exist_ok=True)
+    stage_keep_mask_lambert(args.workdir)
     stage_num_repeats()
     sd = synth.make_beluga_weights(GI.WEIGHT_SEED, round_dtype="f16")
     stage_beluga(sd)

@@ -164,9 +164,33 @@ def test_keep_mask_matches_reference_cluster_utils(golden, tmp_path):
         a.no_tf_features, a.no_dnase_features, a.no_histone_features, a.no_pol2 = bool(tf), bool(dn), bool(hi), bool(po)
         want = np.unpackbits(packed)[:len(g["assay"])].astype(bool)
         assert np.array_equal(predict.keep_mask(str(tsv), a), want), (tf, dn, hi, po)
-    a.intersect_with_lambert = True
-    with pytest.raises(NotImplementedError):
-        predict.keep_mask(str(tsv), a)
+
+
+def test_lambert_intersection_matches_reference_cluster_utils(golden, tmp_path):
+    """--intersect_with_lambert against cluster_utils.get_keep_mask(…, intersect_with_lambert=True) run by
+    oracle/make_golden.py on seeded stand-ins for the two resource tables (cluster_utils.py:26-42): duplicated mapping
+    rows, rows without an approved symbol, case changes, alone and combined with --no_dnase_features / --no_pol2."""
+    import pandas as pd
+    g = golden("keep_mask_lambert_golden.npz")
+    tsv = tmp_path / "features.tsv"
+    pd.DataFrame({"Cell type": "x", "Assay": g["assay"], "Treatment": "", "Assay type": g["assay_type"]},
+                 index=np.arange(1, len(g["assay"]) + 1)).to_csv(tsv, sep="\t")
+    (tmp_path / "lambert.csv").write_text(str(g["lambert_csv"]))
+    (tmp_path / "mapping.csv").write_text(str(g["mapping_csv"]))
+
+    class Flags:
+        no_tf_features = no_histone_features = False
+        intersect_with_lambert = True
+        lambert_csv, hgnc_mapping_csv = str(tmp_path / "lambert.csv"), str(tmp_path / "mapping.csv")
+
+    kept = []
+    for (dn, po), packed in zip(g["combos"], g["masks"]):
+        a = Flags()
+        a.no_dnase_features, a.no_pol2 = bool(dn), bool(po)
+        want = np.unpackbits(packed)[:len(g["assay"])].astype(bool)
+        assert np.array_equal(predict.keep_mask(str(tsv), a), want), (dn, po)
+        kept.append(int(want.sum()))
+    assert 50 < kept[0] < len(g["assay"]) - 50 and kept[3] < kept[0]      # the fixture exercises both outcomes
 
 
 def test_num_repeats_matches_reference_function(golden):

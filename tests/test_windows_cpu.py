@@ -4,6 +4,7 @@ import os
 import numpy as np
 import pytest
 
+from expecto_b200 import synth
 from expecto_b200.genome import PackedGenome, encode_bases
 from expecto_b200.windows import (AlleleTable, allele_match_counts, chromatin_window_descs, crop_bounds, tss_descs,
                                   variant_descs)
@@ -300,3 +301,55 @@ def test_random_variants_descriptors_match_oracle(small_genome, seed):
         alt_enc = O.encode_seqs([s[1] for s in seqs])
         assert np.array_equal(ours[:, 0], ref_enc[:n]) and np.array_equal(ours[:, 1], ref_enc[n:]), shift
         assert np.array_equal(ours[:, 2], alt_enc[:n]) and np.array_equal(ours[:, 3], alt_enc[n:]), shift
+
+
+def test_windows_running_off_a_contig_read_zero_columns_not_the_neighbour():
+    """with 4096 bases of padding between contigs, a compute_expecto_features window near a contig edge
+    (TSS +-20,000 shift +-1,000 bp, compute_expecto_features.py:105-111) landed inside the neighbouring contig.  The
+    padding now exceeds that reach: every off-contig position must decode as code 4 (an all-zero column), for plain TSS
+    windows, TSS segments and variant windows at the largest chromatin shift."""
+    from expecto_b200.genome import PAD
+    from expecto_b200.windows import tss_descs, tss_segment_descs, variant_descs
+    assert PAD >= 21000 + 32 and PAD % 32 == 0
+    genome = {"chrA": "ACGT" * 10000, "chrB": "ACGT" * 15000, "chrC": "TTGA" * 2000}
+    pg = PackedGenome.from_sequences(genome)
+    shifts = np.arange(-20000, 20000, 200)
+    for chrom, tss, strand in (("chrB", 5000, 1), ("chrB", 5000, -1), ("chrB", 59000, 1), ("chrA", 1, -1),
+                               ("chrC", 7999, 1)):
+        d = tss_descs(pg, [chrom], [tss], [strand], shifts).reshape(len(shifts), 2)
+        off, ln = pg.offsets[chrom], pg.lengths[chrom]
+        for si, s in enumerate(shifts):
+            codes = pg.codes(int(d[si, 0]["g1"]), 2000)
+            start0 = tss + int(s) * strand - 999 - 1           # 0-based contig coordinate of the window's first base
+            inside = (np.arange(start0, start0 + 2000) >= 0) & (np.arange(start0, start0 + 2000) < ln)
+            assert np.all(codes[~inside] == 4), (chrom, tss, strand, int(s))
+            want = pg.codes(off + max(start0, 0), 1)[0] if inside.any() else None
+            assert np.all(codes[inside] < 4) and (want is None or want < 4)
+        sd, _, seg_len = tss_segment_descs(pg, [chrom], [tss], [strand], shifts)
+        codes = pg.codes(int(sd[0]["g1"]), seg_len)
+        g0 = int(sd[0]["g1"]) - off
+        inside = (np.arange(g0, g0 + seg_len) >= 0) & (np.arange(g0, g0 + seg_len) < ln)
+        assert np.all(codes[~inside] == 4) and np.all(codes[inside] < 4)
+    for shift in (800, -800):     # a variant two bases from a contig start / end
+        for chrom, pos in (("chrB", 2), ("chrA", 39999)):
+            d = variant_descs(pg, [chrom], [pos], np.array([1]), np.array([1]), np.array([0]), shift, rc=False)[0]
+            off, ln = pg.offsets[chrom], pg.lengths[chrom]
+            for g, n in ((int(d["g1"]), int(d["len1"])), (int(d["g2"]), int(d["len2"]))):
+                idx = np.arange(g, g + n) - off
+                codes = pg.codes(g, n)
+                assert np.all(codes[(idx < 0) | (idx >= ln)] == 4)
+
+
+def test_cache_with_narrow_padding_is_rebuilt(tmp_path, small_genome):
+    """A .bx2.npz written before the padding was widened (no ``pad`` field, 4096 bases) must not be reused."""
+    import expecto_b200.genome as G
+    fa = str(tmp_path / "g.fa")
+    synth.write_fasta(fa, {k: v[:5000] for k, v in small_genome.items()})
+    g = PackedGenome.from_fasta(fa)
+    z = dict(np.load(fa + ".bx2.npz"))
+    assert int(z["pad"]) == G.PAD
+    z.pop("pad")
+    z["offsets"] = z["offsets"] - 1                       # a stale layout: would be wrong if it were loaded
+    np.savez(fa + ".bx2.npz", **z)
+    g2 = PackedGenome.from_fasta(fa)
+    assert g2.offsets == g.offsets and g2.pad == G.PAD

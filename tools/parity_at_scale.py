@@ -14,7 +14,7 @@ Runs on a GPU box (the oracle runs on its host cores at ~230-340 windows/s, so t
               (compute_expecto_features.py:105-124).
 
 Writes max / p99.99 / p99 / mean |dp|, Pearson on the diffs and the end-to-end feature error per config as JSON.
-``--precision`` selects the engine's operand mode ("f16", "bf16", or "f16x3": hi/lo-split operands).
+``--dtype`` selects the engine's operand mode ("f16", "bf16", or "f16x3": hi/lo-split fp16 operands).
 """
 from __future__ import annotations
 
@@ -91,7 +91,10 @@ def run_cfg2(args, make_engine) -> dict:
     out = {}
     x = cfg2_windows(args.windows)
     xd = torch.from_numpy(x).cuda()
-    for tag, rd in (("same_inputs_prerounded_weights", args.dtype), ("oracle_fp32_weights_engine_rounds", None)):
+    cases = (("same_inputs_prerounded_weights", args.dtype), ("oracle_fp32_weights_engine_rounds", None))
+    if args.dtype == "f16x3":   # split operands carry the fp32 weights to ~21 bits: there is nothing to pre-round
+        cases = cases[1:]
+    for tag, rd in cases:
         sd = synth.make_beluga_weights(0, round_dtype=rd)
         eng = make_engine(sd)
         got = eng.forward_onehot(xd).cpu().numpy()
@@ -130,7 +133,7 @@ def run_cfg3(args, make_engine) -> dict:
     kinds["ref_mismatch"] = int(sum(gs.sequence({"chr": c, "start": int(p), "stop": int(p) + len(r) - 1}) != r
                                     for c, p, r in zip(chroms, pos, refs)))
     print(f"cfg3: genome + {args.vcf_rows}-row VCF in {time.perf_counter() - t0:.1f} s; sample {n}: {kinds}", flush=True)
-    sd = synth.make_beluga_weights(0, round_dtype=args.dtype)
+    sd = synth.make_beluga_weights(0, round_dtype=None if args.dtype == "f16x3" else args.dtype)
     eng = make_engine(sd)
     eng.set_genome(pg)
     outs = chromatin.predict_all_shifts_segments_device(eng, pg, chroms, pos, refs, alts, 800)
@@ -182,7 +185,7 @@ def run_cfg4(args, make_engine) -> dict:
         c = names[int(rng.integers(0, len(names)))]
         tss = int(rng.integers(21_100, pg.lengths[c] - 21_100))
         genes.append((f"ENSG{g:011d}", c, tss, 1 if g % 2 == 0 else -1))
-    sd = synth.make_beluga_weights(0, round_dtype=args.dtype)
+    sd = synth.make_beluga_weights(0, round_dtype=None if args.dtype == "f16x3" else args.dtype)
     eng = make_engine(sd)
     eng.set_genome(pg)
     pw = fixed_pos_weights(TSS_SHIFTS)
@@ -221,8 +224,8 @@ def main() -> int:
     ap.add_argument("--vcf_rows", type=int, default=1_000_000)
     ap.add_argument("--genes", type=int, default=16)
     ap.add_argument("--shifts", default="0,-800,800,-200,-400,-600,200,400,600")
-    ap.add_argument("--dtype", default="f16")
-    ap.add_argument("--precision", default=None, help="engine precision mode (default: the engine's default)")
+    ap.add_argument("--dtype", default="f16", choices=["f16", "bf16", "f16x3"])
+    ap.add_argument("--capacity", type=int, default=4096)
     ap.add_argument("--skip", default="", help="comma list of cfg2,cfg3,cfg4")
     args = ap.parse_args()
     args.shifts = [int(s) for s in args.shifts.split(",") if s]
@@ -235,12 +238,11 @@ def main() -> int:
     torch.set_num_threads(os.cpu_count() or 1)
 
     def make_engine(sd):
-        kw = {"precision": args.precision} if args.precision else {}
-        eng = BelugaEngine(0, dtype=args.dtype, capacity=4096, **kw)
+        eng = BelugaEngine(0, dtype=args.dtype, capacity=args.capacity)
         eng.load_state_dict(sd)
         return eng
 
-    res = {"dtype": args.dtype, "precision": args.precision or "default", "host_cores": os.cpu_count(),
+    res = {"dtype": args.dtype, "host_cores": os.cpu_count(),
            "bars": {"probabilities_abs": 2e-3, "diff_pearson": 0.999}}
     skip = set(args.skip.split(","))
     t0 = time.perf_counter()
