@@ -119,7 +119,7 @@ def cpu_forward_rate(batch: int, min_seconds: float, max_windows: int, seed: int
     return done / dt, cores, torch.get_num_threads(), done, dt
 
 
-def variant_workflow(eng, n_variants: int, rank: int = 0, world: int = 1, sync=None):
+def variant_workflow(eng, n_variants: int, rank: int = 0, world: int = 1, sync=None, cpu: bool = False):
     """BASELINE configs[2] shape at a stated reduced size, outside the timed region: a synthetic VCF (90 % SNV, 5 %
     ref-mismatch, 5 % indel) on a synthetic genome -> ref/alt x fwd/rc x 9 shifts -> pinned host ref/alt/diff, through
     the drop-in's segment + delta mode (host descriptors in, host arrays out, no file).  Reported in the headline
@@ -149,15 +149,18 @@ def variant_workflow(eng, n_variants: int, rank: int = 0, world: int = 1, sync=N
     if sync is not None:
         dt = sync(dt)                  # slowest rank
     n_all = n_variants * world
-    return {"workload": f"{n_variants} synthetic variants per GPU x (ref, alt) x (fwd, rc) x 9 shifts, segment + delta "
-                        "mode, host descriptors -> pinned host ref/alt/diff, no file; variants sharded over the GPUs, "
-                        "no collective",
-            "variants": n_all, "windows": 36 * n_all, "seconds": dt, "windows_per_s": 36 * n_all / dt,
-            "variants_per_s": n_all / dt, "d2h_bytes": 9 * 3 * 2 * n_all * 2002 * 4,
-            "delta_variants": info["delta_variants"], "window_path_variants": info["window_variants"]}
+    out = {"workload": f"{n_variants} synthetic variants per GPU x (ref, alt) x (fwd, rc) x 9 shifts, segment + delta "
+                       "mode, host descriptors -> pinned host ref/alt/diff, no file; variants sharded over the GPUs, "
+                       "no collective",
+           "variants": n_all, "windows": 36 * n_all, "seconds": dt, "windows_per_s": 36 * n_all / dt,
+           "variants_per_s": n_all / dt, "d2h_bytes": 9 * 3 * 2 * n_all * 2002 * 4,
+           "delta_variants": info["delta_variants"], "window_path_variants": info["window_variants"]}
+    if cpu and rank == 0:
+        out["cpu_baseline"] = chromatin_cpu_baseline(genome, rows)
+    return out
 
 
-def transform_rooflines(dev, peaks, iters: int = 10):
+def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
     """Kernel 4 (decay-weighted shift reductions) as HBM GB/s over the algorithmic bytes of SURVEY §8(d); inputs
     (1.6 GB / 1.2 GB) are larger than the 126 MB L2."""
     import numpy as np
@@ -206,9 +209,78 @@ def transform_rooflines(dev, peaks, iters: int = 10):
         tr = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))["transform"]
         out["fixed"]["traffic"] = int(tr["fixed_per_gene_bytes"] * G)
         out["variant"]["traffic"] = int(tr["variant_per_variant_bytes"] * n)
+        out["fixed"]["traffic_source"] = out["variant"]["traffic_source"] = \
+            "ncu capture r01 (profiles/r01_ncu_transform_launches.csv), static: not measured in this run"
     except Exception:
         out["fixed"]["traffic"] = out["variant"]["traffic"] = None
+    del x, res
+    if cpu:
+        out["fixed"]["cpu_baseline"], out["variant"]["cpu_baseline"] = transform_cpu_baselines()
     return out
+
+
+def transform_cpu_baselines(genes: int = 64, variants: int = 5000):
+    """The reference's numpy expressions for kernel 4 on this box's host (oracle restatements, bounded samples):
+    compute_expecto_features.py:123-124 on ``genes`` genes and predict.py:120-136 (``compute_effects``' reduce over
+    np.tile / np.repeat temporaries, 500-row batches) on ``variants`` variants, as GB/s over the same algorithmic
+    bytes the GPU figures use."""
+    import numpy as np
+
+    from oracle import beluga_oracle as O
+
+    rng = np.random.default_rng(0)
+    cores = os.cpu_count() or 1
+    pw = O.fixed_pos_weights()
+    fwd = rng.random((200, 2002), dtype=np.float32)
+    rc = rng.random((200, 2002), dtype=np.float32)
+    O.fixed_transform(fwd, rc, pw)
+    t0 = time.perf_counter()
+    for _ in range(genes):
+        O.fixed_transform(fwd, rc, pw)
+    dt = time.perf_counter() - t0
+    b = genes * (200 * 2 * 2002 * 4 + 20020 * 4)
+    fixed = {"value": b / dt / 1e9, "unit": "GB/s", "genes_per_s": genes / dt, "cores": cores, "kind": "port",
+             "sample": f"{genes} genes, numpy float64 expression of compute_expecto_features.py:123-124 "
+                       "(numpy's own threading; the expression is a broadcast multiply + sum, single-threaded)"}
+    x = [rng.random((500, 2002), dtype=np.float32) for _ in range(9)]
+    done, t0 = 0, time.perf_counter()
+    while done < variants:
+        dist = rng.integers(-40000, 40000, size=500).astype(np.float64)
+        strand = np.where(np.arange(500) % 2 == 0, "+", "-")
+        O.variant_transform(x, O.variant_weights(dist, strand, 800))
+        done += 500
+    dt = time.perf_counter() - t0
+    b = done * (9 * 2002 * 4 + 20020 * 4 + 9)
+    variant = {"value": b / dt / 1e9, "unit": "GB/s", "variants_per_s": done / dt, "cores": cores, "kind": "port",
+               "sample": f"{done} variants in 500-row batches (predict.py's --batchSize), one of diff/ref/alt: numpy "
+                         "float64 np.tile / np.repeat reduce of predict.py:87-124"}
+    return fixed, variant
+
+
+def chromatin_cpu_baseline(genome: dict, rows, n_variants: int = 8):
+    """The reference's chromatin.py shift loop on the host (oracle.chromatin_shift restating chromatin.py:243-281:
+    fetchSeqs + encodeSeqs + fp32 forward for ref and alt, all 9 shifts) on the first ``n_variants`` rows of the same
+    VCF the GPU workflow runs; windows/s with 4 windows per variant-shift."""
+    import torch
+
+    from expecto_b200 import synth
+    from oracle import beluga_oracle as O
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = {k: torch.from_numpy(v) for k, v in synth.make_beluga_weights(0, round_dtype="f16").items()}
+    dg = O.DictGenome(genome)
+    part = [list(r) for r in rows[:n_variants]]
+    O.chromatin_shift(dg, part[:1], sd, 0)   # warm-up
+    t0 = time.perf_counter()
+    for shift in O.SHIFTS_CHROMATIN(800):
+        O.chromatin_shift(dg, part, sd, shift)
+    dt = time.perf_counter() - t0
+    w = 36 * len(part)
+    return {"value": w / dt, "unit": UNIT, "variants_per_s": len(part) / dt, "cores": cores, "kind": "port",
+            "sample": f"{len(part)} variants x 9 shifts x (ref, alt) x (fwd, rc) = {w} windows in {dt:.1f} s: fetchSeqs + "
+                      f"encodeSeqs + fp32 torch CPU forward at the reference's batch of 32, {torch.get_num_threads()} "
+                      "threads"}
 
 
 def run_reference(args) -> int:
@@ -376,7 +448,9 @@ def run_gpu(args) -> int:
         "tflops_per_gpu": fwd_tf,
         "roofline": {"bound": "tensor", "kernel": f"gemm_tc_kernel ({top})", "achieved": top_tf,
                      "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": top_tf / peaks["bf16_tflops"],
-                     "traffic": traffic, "peak_source": peaks["source"] + ", burst",
+                     "traffic": traffic,
+                     "traffic_source": "ncu capture r01 (profiles/dram_traffic.json), static: not measured in this run",
+                     "peak_source": peaks["source"] + ", burst",
                      "peak_sustained": peaks["bf16_tflops_sustained"],
                      "frac_sustained": top_tf / peaks["bf16_tflops_sustained"],
                      "flop_per_launch": chunk * STAGE_FLOP[top], "ms_per_launch": per[top],
@@ -395,14 +469,19 @@ def run_gpu(args) -> int:
     if world == 1 and not args.no_transform:
         del x, out
         torch.cuda.empty_cache()
-        line["transform_roofline"] = transform_rooflines(dev, peaks)
+        line["transform_roofline"] = transform_rooflines(dev, peaks, cpu=not args.no_cpu_baseline)
     if not args.no_workflow:
-        line["variant_workflow"] = wf if world > 1 else variant_workflow(eng, args.workflow_variants)
+        line["variant_workflow"] = wf if world > 1 else variant_workflow(eng, args.workflow_variants,
+                                                                         cpu=not args.no_cpu_baseline)
     if world == 1 and not args.no_cpu_baseline:
         rate, cores, threads, done, dt = cpu_forward_rate(32, args.cpu_seconds, 4096)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{done} windows in {dt:.1f} s, batch 32 (reference default), fp32 torch CPU "
                                           f"forward restating Beluga.py:21-51, {threads} threads"}
+        # the batch the reference's authors run with (scripts/sed_immune_atlas/chromatin_immune_atlas.sh:12)
+        rate, cores, threads, done, dt = cpu_forward_rate(512, 4.0, 1024)
+        line["cpu_baseline"]["batch_512"] = {"value": rate, "unit": UNIT, "cores": cores,
+                                             "sample": f"{done} windows in {dt:.1f} s, batch 512, {threads} threads"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

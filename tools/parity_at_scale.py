@@ -108,6 +108,15 @@ def run_cfg2(args, make_engine) -> dict:
         s["n_rich_windows"] = int(len(range(0, len(x), 8)))
         nr = np.arange(0, len(x), 8)
         s["max_n_rich"] = float(np.abs(got[nr] - want[nr]).max())
+        # systematic part of the error, in the logit domain: dz regressed on (z - b2) estimates a multiplicative
+        # shrink (< 0) of the last layer's pre-activations, the signature of truncating fp32 accumulation
+        g64, w64 = np.clip(got.astype(np.float64), 1e-12, 1 - 1e-12), np.clip(want.astype(np.float64), 1e-12, 1 - 1e-12)
+        zg, zw = np.log(g64 / (1 - g64)), np.log(w64 / (1 - w64))
+        zc = zw - sd["model.1.4.1.bias"].astype(np.float64)[None, :]
+        sel = np.abs(zw) < 8
+        s["logit_err_mean_signed"] = float((zg - zw)[sel].mean())
+        s["logit_err_rms"] = float(np.sqrt(((zg - zw)[sel] ** 2).mean()))
+        s["logit_shrink_slope"] = float(((zg - zw)[sel] * zc[sel]).sum() / (zc[sel] ** 2).sum())
         out[tag] = s
         print(tag, json.dumps(s), flush=True)
     return out
