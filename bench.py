@@ -160,6 +160,65 @@ def variant_workflow(eng, n_variants: int, rank: int = 0, world: int = 1, sync=N
     return out
 
 
+def sharded_chromatin(eng, total_variants: int, rank: int, world: int, barrier, max_over_ranks):
+    """The multi-GPU design of the variant path in front of the driver (strong scaling: ONE synthetic VCF of
+    ``total_variants`` rows split into contiguous per-rank shards), both ways the drop-in offers:
+
+    * ``gather_nccl``  — every chunk's ref / alt / diff rows are gathered to rank 0 over NCCL on a side stream while the
+      next chunk computes, and rank 0 copies them to pinned host memory (``chromatin --gather nccl`` minus the file);
+    * ``local_copy``   — every rank copies its own rows to its own pinned host memory, no collective
+      (``chromatin --gather file`` minus the file).
+
+    Timed barrier to barrier, slowest rank; windows/s = 36 windows per variant of the whole job."""
+    import numpy as np
+    import torch
+
+    from expecto_b200 import chromatin, shard, synth
+    from expecto_b200.genome import PackedGenome
+    from expecto_b200.windows import variant_columns
+
+    genome = synth.make_genome([("chr1", 6_000_000), ("chr2", 4_000_000)], seed=3)
+    pg = PackedGenome.from_sequences(genome)
+    eng.set_genome(pg)
+    rows = synth.make_vcf_rows(genome, total_variants, seed=17, odd_names=False)     # the same table on every rank
+    lo, hi = shard.shard_range(total_variants, rank, world)
+    part = rows[lo:hi]
+    chroms, pos = [r[0] for r in part], np.array([r[1] for r in part])
+    refs, alts = [r[3] for r in part], [r[4] for r in part]
+    cols = variant_columns(pg, chroms, pos, refs, alts)
+    shifts = chromatin.shift_list(800)
+    noop = {s: (lambda *a: None) for s in shifts}
+    out = {"workload": f"one synthetic VCF of {total_variants} variants (90 % SNV, 5 % ref-mismatch, 5 % indel) split "
+                       f"over {world} GPU(s) in contiguous shards x (ref, alt) x (fwd, rc) x 9 shifts, segment + delta "
+                       "mode with device-built descriptors; results delivered to pinned host memory",
+           "scaling": "strong", "total_variants": total_variants, "windows": 36 * total_variants}
+    k = min(1200, len(pos))
+    chromatin.predict_all_shifts_segments(eng, pg, chroms[:k], pos[:k], refs[:k], alts[:k], 800, noop)  # warm-up
+    for mode in ("gather_nccl", "local_copy"):
+        barrier()
+        t0 = time.perf_counter()
+        if mode == "gather_nccl":
+            info = chromatin.predict_all_shifts_gathered(eng, cols, 800, total_variants, noop if rank == 0 else None)
+        else:
+            info = chromatin.predict_all_shifts_segments(eng, pg, chroms, pos, refs, alts, 800, noop)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        res = {"seconds": dt, "windows_per_s": 36 * total_variants / dt, "variants_per_s": total_variants / dt}
+        if mode == "gather_nccl":
+            gb = info["gathered_bytes"] / 1e9
+            res.update({"gathered_GB_to_rank0": gb, "rank0_gather_ms": info["gather_ms"], "rank0_d2h_ms": info["d2h_ms"],
+                        "rank0_host_wait_s": info["wait_s"],
+                        "gather_GBps": (gb / (info["gather_ms"] * 1e-3)) if info["gather_ms"] > 0 and gb > 0 else None,
+                        "frac_of_wall_in_gather": info["gather_ms"] * 1e-3 / dt,
+                        "frac_of_wall_in_rank0_d2h": info["d2h_ms"] * 1e-3 / dt,
+                        "rank0_d2h_GBps": (36 * total_variants / 4 * 3 * 2002 * 4 / 1e9) / (info["d2h_ms"] * 1e-3)
+                        if info["d2h_ms"] > 0 else None,
+                        "note": "gather / d2h times are CUDA-event sums on rank 0's side stream; they overlap compute"})
+        out[mode] = res
+    return out
+
+
 def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
     """Kernel 4 (decay-weighted shift reductions) as HBM GB/s over the algorithmic bytes of SURVEY §8(d); inputs
     (1.6 GB / 1.2 GB) are larger than the 126 MB L2."""
@@ -407,9 +466,11 @@ def run_gpu(args) -> int:
     e2e_value = world * B * K / e2e_s
     e2e_ok = bool(torch.equal(out_host, out.cpu()))
 
-    wf = None
+    wf = sc = None
     if world > 1 and not args.no_workflow:   # all ranks take part (N = 1 runs it after the transform measurement)
         wf = variant_workflow(eng, args.workflow_variants, rank, world, max_over_ranks)
+    if world > 1 and not args.no_sharded:
+        sc = sharded_chromatin(eng, args.sharded_variants, rank, world, barrier, max_over_ranks)
 
     if rank != 0:
         if world > 1:
@@ -473,6 +534,9 @@ def run_gpu(args) -> int:
     if not args.no_workflow:
         line["variant_workflow"] = wf if world > 1 else variant_workflow(eng, args.workflow_variants,
                                                                          cpu=not args.no_cpu_baseline)
+    if not args.no_sharded:
+        line["sharded_chromatin"] = sc if world > 1 else sharded_chromatin(eng, args.sharded_variants, 0, 1, barrier,
+                                                                           max_over_ranks)
     if world == 1 and not args.no_cpu_baseline:
         rate, cores, threads, done, dt = cpu_forward_rate(32, args.cpu_seconds, 4096)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
@@ -505,6 +569,9 @@ def main() -> int:
     ap.add_argument("--no_transform", action="store_true", help="skip the kernel-4 GB/s measurement")
     ap.add_argument("--no_workflow", action="store_true", help="skip the variant-workflow (segment mode) measurement")
     ap.add_argument("--workflow_variants", type=int, default=8192)
+    ap.add_argument("--no_sharded", action="store_true", help="skip the sharded-pipeline (strong scaling) measurement")
+    ap.add_argument("--sharded_variants", type=int, default=65536,
+                    help="variants of the one VCF that the sharded-pipeline measurement splits over the GPUs")
     args = ap.parse_args()
     return run_reference(args) if args.impl == "reference" else run_gpu(args)
 

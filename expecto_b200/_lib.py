@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libbeluga_b200.so")
 SRC = os.path.join(_HERE, "csrc", "capi.cu")
-SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh", "encode.cuh", "genome_pack.cuh")] + [
+SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh", "encode.cuh", "genome_pack.cuh", "variants.cuh")] + [
     os.path.join(ROOT, "include", "beluga_b200.h")
 ]
 
@@ -51,7 +51,10 @@ EXPORTS = [
     "bx_forward_onehot_host", "bx_chromatin_shift_host", "bx_ctx_profile", "bx_ctx_profile_read",
     "bx_decay_score_variant", "bx_forward_segments", "bx_segment_capacity", "bx_strand_average",
     "bx_forward_segments_delta", "bx_fasta_blocks", "bx_fasta_find_headers", "bx_fasta_count", "bx_fasta_pack",
+    "bx_chromatin_open", "bx_chromatin_chunk_info", "bx_chromatin_submit", "bx_chromatin_wait",
+    "bx_chromatin_submit_device", "bx_chromatin_close", "bx_variant_descs_host",
 ]
+CHROM_NO_DELTA, CHROM_AVERAGE, CHROM_WINDOWS = 1, 2, 4
 NSTAGES = 10
 STAGE_NAMES = ["encode", "conv1", "conv2", "conv3", "conv4", "conv5", "conv6", "fc1", "fc2", "outputs"]
 
@@ -124,6 +127,14 @@ def lib() -> C.CDLL:
     L.bx_fasta_find_headers.argtypes = [vp, i64, vp, i64, vp, vp]
     L.bx_fasta_count.argtypes = [vp, i64, i64, vp, C.POINTER(i64), vp]
     L.bx_fasta_pack.argtypes = [vp, i64, i64, vp, i64, vp, vp, vp, i64, vp, vp]
+    ip = C.POINTER(i32)
+    L.bx_chromatin_open.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, ip, ip]
+    L.bx_chromatin_chunk_info.argtypes = [vp, i32, C.POINTER(i64), ip, ip, ip, ip]
+    L.bx_chromatin_submit.argtypes = [vp, i32, vp, vp, vp]
+    L.bx_chromatin_wait.argtypes = [vp, i32]
+    L.bx_chromatin_submit_device.argtypes = [vp, i32, vp, vp, vp, i64, i64, i64, vp]
+    L.bx_chromatin_close.argtypes = [vp]
+    L.bx_variant_descs_host.argtypes = [i32, i64, vp, vp, vp, vp, vp, i32, i32, ip, ip, vp]
     L.bx_ctx_profile.argtypes = [vp, i32]
     L.bx_ctx_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), i32]
     for name in EXPORTS:

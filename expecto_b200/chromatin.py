@@ -45,7 +45,9 @@ def build_parser() -> argparse.ArgumentParser:
     # extensions
     p.add_argument("--genome", default="./resources/hg19.fa", help="FASTA (chromatin.py:44 hard-codes this path)")
     p.add_argument("--weights", default="./resources/deepsea.beluga.pth", help="state_dict (chromatin.py:103)")
-    p.add_argument("--dtype", default="f16", choices=["f16", "bf16"], help="tensor-core operand type")
+    p.add_argument("--dtype", default="f16", choices=["f16", "bf16", "f16x3"],
+                   help="tensor-core operand type; f16x3 = fp16 (hi, lo) pairs, ~1e-4 of the fp32 reference at a third "
+                        "of the throughput")
     p.add_argument("--device", type=int, default=0)
     p.add_argument("--gpu_batch", type=int, default=4096, help="variants per GPU sub-batch (x4 windows)")
     p.add_argument("--gather", default="nccl", choices=["nccl", "file"],
@@ -56,6 +58,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--no_delta", action="store_true",
                    help="segment mode: run the alt segments of substitutions in full instead of as patches around the "
                         "variant (same results bit for bit; for comparisons)")
+    p.add_argument("--host_descs", action="store_true",
+                   help="build the window / segment descriptors on the host (windows.py) and loop over chunks in Python "
+                        "instead of inside the library (same results bit for bit; for comparisons)")
     p.add_argument("--upstream_layout", action="store_true",
                    help="also write upstream ExPecto's {inputfile}.shift_{s}.diff.h5 with one 'pred' dataset")
     return p
@@ -293,8 +298,89 @@ def _segment_chunks(engine, genome, chroms, pos, refs, alts, maxshift: int, ids,
 
 
 def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshift: int, sinks: dict,
-                                writer: SlabWriter | None = None, delta: bool = True) -> dict:
-    """The whole shift loop (chromatin.py:243-286) in segment mode: the ref/alt x fwd/rc sequences of a variant are
+                                writer: SlabWriter | None = None, delta: bool = True, host_descs: bool = False) -> dict:
+    """The whole shift loop (chromatin.py:243-286) for all variants: ``sinks[shift](name, row0, array)`` receives the
+    float32 row slabs of that shift's ``diff`` / ``ref`` / ``alt`` datasets (forward rows at v, reverse-complement rows
+    at n + v).
+
+    The loop itself runs inside the library (include/beluga_b200.h: bx_chromatin_open / _submit / _wait): this function
+    hands over the VCF columns once, then only moves finished chunks from pinned buffers to the writer.  Descriptors
+    are built on the device, substitutions go through delta mode, other variants through four full segments or — long
+    indels — window by window, and FC2's epilogue writes ref / alt / diff = alt - ref in their final row order; chunk
+    k + 1 computes while chunk k travels to the host and chunk k - 1 is written.
+
+    ``host_descs`` (and genomes holding characters outside encodeSeqs' dictionary, whose windows must raise KeyError
+    as chromatin.py:166 does) use the host-side descriptor builder of windows.py instead — same bits."""
+    import time
+
+    import torch
+
+    from .windows import variant_columns, variant_extent_invalid
+
+    cols = variant_columns(genome, chroms, pos, refs, alts)
+    if host_descs or variant_extent_invalid(genome, cols, maxshift) >= 0:
+        return _predict_all_shifts_segments_host(engine, genome, chroms, pos, refs, alts, maxshift, sinks, writer, delta)
+    n = cols["n"]
+    shifts = shift_list(maxshift)
+    S = len(shifts)
+    n_chunks, chunk = engine.chromatin_open(cols, maxshift, delta=delta)
+    n_sets = 3  # one being filled by the GPU, one waiting to be handed over, one being written
+    own_writer = writer is None
+    if own_writer:
+        writer = SlabWriter(n_sets)
+    rows_cap = max(1, min(chunk, n))
+    pinned = [tuple(torch.empty(S * 2 * rows_cap * 2002, dtype=torch.float32, pin_memory=True) for _ in range(3))
+              for _ in range(n_sets)]
+    t_host = {"gpu_wait_s": 0.0}
+    counts = {"delta": 0, "full": 0, "window": 0}
+
+    def flush(p):
+        k, si_set, v0, m, bufs = p
+        t0 = time.perf_counter()
+        engine.chromatin_wait(k)
+        t_host["gpu_wait_s"] += time.perf_counter() - t0
+        hs = [b.numpy() for b in bufs]           # (ref, alt, diff), each [S, 2, m, 2002]
+        for si, shift in enumerate(shifts):
+            tasks = []
+            for name, h in (("diff", hs[2]), ("ref", hs[0]), ("alt", hs[1])):
+                tasks.append((name, v0, h[si, 0]))
+                tasks.append((name, n + v0, h[si, 1]))
+            # every shift's tasks read the same buffer set; the last submit of the chunk (FIFO) frees it
+            if si == S - 1:
+                writer.submit(si_set, sinks[shift], tasks)
+            else:
+                writer.write(sinks[shift], tasks)
+
+    pending = None
+    try:
+        for k in range(n_chunks):
+            info = engine.chromatin_chunk_info(k)
+            m = info["m"]
+            for key in counts:
+                counts[key] += info[key]
+            si_set = writer.next_set()  # blocks until the set's previous contents are on disk
+            bufs = tuple(t[:S * 2 * m * 2002].view(S, 2, m, 2002) for t in pinned[si_set])
+            engine.chromatin_submit(k, *bufs)
+            if pending is not None:
+                flush(pending)
+            pending = (k, si_set, info["v0"], m, bufs)
+        if pending is not None:
+            flush(pending)
+        if own_writer:
+            writer.close()
+        else:
+            writer.drain()
+    finally:
+        engine.chromatin_close()
+    return {"segment_variants": counts["delta"] + counts["full"], "window_variants": counts["window"],
+            "chunk_variants": int(chunk), "delta_variants": counts["delta"], "writer_busy_s": writer.busy_s,
+            "writer_bytes": writer.bytes, "producer_blocked_s": writer.blocked_s, "descriptors": "device",
+            **{"host_" + k: v for k, v in t_host.items()}}
+
+
+def _predict_all_shifts_segments_host(engine, genome, chroms, pos, refs, alts, maxshift: int, sinks: dict,
+                                      writer: SlabWriter | None = None, delta: bool = True) -> dict:
+    """predict_all_shifts_segments with the descriptors built on the host (windows.py) and the chunk loop in Python: the ref/alt x fwd/rc sequences of a variant are
     encoded once as 2000+2*maxshift-bp segments, the conv stack runs once per segment and all shifts' ref/alt/diff
     rows come out together (bit-identical to the per-shift path).  ``sinks[shift](name, row0, array)`` receives the
     row slabs of that shift's datasets.  Variants whose windows are not plain substrings of one segment (long
@@ -391,10 +477,29 @@ def predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, maxshif
             **{"host_" + k: v for k, v in t_host.items()}}
 
 
-def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, maxshift: int, delta: bool = True):
-    """Segment mode with the results left in HBM: {shift: (ref, alt, diff)} device tensors [2n,2002] in the strand-
-    stacked row order — the operands of the per-shift NCCL gather when variants are sharded over GPUs."""
+def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, maxshift: int, delta: bool = True,
+                                       host_descs: bool = False):
+    """The shift loop with the results left in HBM: {shift: (ref, alt, diff)} device tensors [2n,2002] in the strand-
+    stacked row order (bx_chromatin_submit_device; ``host_descs``: the windows.py builder + Python chunk loop)."""
     import torch
+
+    from .windows import variant_columns, variant_extent_invalid
+
+    cols = variant_columns(genome, chroms, pos, refs, alts)
+    if not host_descs and variant_extent_invalid(genome, cols, maxshift) < 0:
+        n = cols["n"]
+        shifts = shift_list(maxshift)
+        S = len(shifts)
+        full = [torch.empty((S, 2 * n, 2002), dtype=torch.float32, device=engine.device) for _ in range(3)]
+        n_chunks, _ = engine.chromatin_open(cols, maxshift, delta=delta)
+        try:
+            with torch.cuda.device(engine.device):
+                for k in range(n_chunks):
+                    engine.chromatin_submit_device(k, *[t.view(-1, 2002) for t in full], 2 * n, n,
+                                                   engine.chromatin_chunk_info(k)["v0"])
+        finally:
+            engine.chromatin_close()
+        return {s: tuple(t[si] for t in full) for si, s in enumerate(shifts)}
 
     from .engine import chromatin_outputs
     from .windows import check_valid_bases, chromatin_window_descs, segment_eligible
@@ -430,11 +535,30 @@ def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, 
     return outs
 
 
-def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, maxshift: int, delta: bool = True):
+def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, maxshift: int, delta: bool = True,
+                                       host_descs: bool = False):
     """The chromatin step as ``predict.py`` consumes it, left in HBM: {"ref", "alt", "diff"} -> float32 [S, n, 2002],
     already averaged over the forward / reverse-complement rows (predict.py:186-190).  This is what reading the nine
-    ``.diff.h5`` files back and averaging gives, without the 432 KB per variant of file traffic in between."""
+    ``.diff.h5`` files back and averaging gives, without the 432 KB per variant of file traffic in between.  The
+    averaging happens in FC2's epilogue (BX_CHROM_AVERAGE)."""
     import torch
+
+    from .windows import variant_columns, variant_extent_invalid
+
+    cols = variant_columns(genome, chroms, pos, refs, alts)
+    if not host_descs and variant_extent_invalid(genome, cols, maxshift) < 0:
+        n = cols["n"]
+        S = len(shift_list(maxshift))
+        res = {k: torch.empty((S, n, 2002), dtype=torch.float32, device=engine.device) for k in ("ref", "alt", "diff")}
+        n_chunks, _ = engine.chromatin_open(cols, maxshift, delta=delta, average=True, windows_only=maxshift % 200 != 0)
+        try:
+            with torch.cuda.device(engine.device):
+                for k in range(n_chunks):
+                    engine.chromatin_submit_device(k, *[res[key].view(-1, 2002) for key in ("ref", "alt", "diff")], n, 0,
+                                                   engine.chromatin_chunk_info(k)["v0"])
+        finally:
+            engine.chromatin_close()
+        return res
 
     from .engine import chromatin_outputs
     from .windows import check_valid_bases, chromatin_window_descs, segment_eligible
@@ -474,6 +598,161 @@ def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, 
             for k, t in zip(("ref", "alt", "diff"), parts):
                 out[k][si].index_copy_(0, ii, t)
     return out
+
+
+def predict_all_shifts_gathered(engine, cols: dict, maxshift: int, n_total: int, sinks: dict | None,
+                                writer: SlabWriter | None = None, delta: bool = True) -> dict:
+    """The shift loop for variants sharded over ranks with the results gathered on rank 0 (north_star:
+    "a final NCCL gather of the diff tensors over NVLink"), streamed chunk by chunk instead of holding every shift's
+    [2 n_local, 2002] tensors until the end:
+
+      round k, every rank:  chunk k of its shard -> device buffer [3, S, 2, chunk, 2002] (bx_chromatin_submit_device)
+                            -> ``dist.gather`` to rank 0 on a side stream, overlapping chunk k + 1's compute;
+      rank 0:               the gathered buffers -> pinned host memory on that side stream, then row slabs to
+                            ``sinks[shift](name, global_row0, array)`` (rank order == row order inside each strand
+                            half of chromatin.py:281-286's layout) through ``writer``.
+
+    ``cols``: this rank's columns (windows.variant_columns of its contiguous shard, shard.shard_range order).  Rank 0
+    receives 3 x S x 2 x 2002 x 4 bytes = 432 KB per variant of the WHOLE job and must move them over its one PCIe
+    link, which is what bounds this mode at 8 GPUs (the timings returned say so); ``--gather file`` has every rank
+    copy and write its own rows instead."""
+    import time
+
+    import torch
+    import torch.distributed as dist
+
+    from . import shard
+
+    world, rank = (dist.get_world_size(), dist.get_rank()) if dist.is_initialized() else (1, 0)
+    dev = engine.device
+    cuda = dev.type == "cuda"
+    shifts = shift_list(maxshift)
+    S = len(shifts)
+    bounds = shard.shard_bounds(n_total, world)
+    if cols["n"] != int(bounds[rank + 1] - bounds[rank]):
+        raise ValueError(f"rank {rank} holds {cols['n']} variants, expected {int(bounds[rank + 1] - bounds[rank])}")
+    n_chunks, chunk = engine.chromatin_open(cols, maxshift, delta=delta)
+    # every rank takes part in every round, so all agree on the chunk size and the number of rounds
+    if world > 1:
+        t = torch.tensor([n_chunks, -chunk], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        chunk_all = int(-t[1].item())
+        if chunk_all != chunk:
+            engine.chromatin_close()
+            n_chunks, chunk = engine.chromatin_open(cols, maxshift, delta=delta, chunk_variants=chunk_all)
+        t = torch.tensor([n_chunks], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        rounds = int(t.item())
+    else:
+        rounds = n_chunks
+    chunk = max(chunk, 1)
+    shape = (3, S, 2, chunk, 2002)
+    send = [torch.zeros(shape, dtype=torch.float32, device=dev) for _ in range(2)]
+    recv = [[torch.empty(shape, dtype=torch.float32, device=dev) for _ in range(world)] for _ in range(2)] \
+        if (rank == 0 and world > 1) else None
+    n_sets = 2
+    host = [torch.empty((world,) + shape, dtype=torch.float32, pin_memory=cuda) for _ in range(n_sets)] if rank == 0 else None
+    own_writer = writer is None and rank == 0
+    if own_writer:
+        writer = SlabWriter(n_sets)
+    side = torch.cuda.Stream(device=dev) if cuda else None
+    works = [None, None]
+    timing = {"gather_ms": 0.0, "d2h_ms": 0.0, "wait_s": 0.0, "rounds": rounds, "chunk_variants": chunk}
+    ev_pairs = []
+    # chunk sizes of every rank in every round (shards differ by at most one variant)
+    sizes = [[max(0, min(chunk, int(bounds[r + 1] - bounds[r]) - k * chunk)) for r in range(world)] for k in range(rounds)]
+
+    def flush(p):
+        k, b, done = p
+        t0 = time.perf_counter()
+        if done is not None:
+            done.synchronize()
+        timing["wait_s"] += time.perf_counter() - t0
+        h = host[b].numpy()
+        for si, shift in enumerate(shifts):
+            tasks = []
+            for r in range(world):
+                m = sizes[k][r]
+                if m == 0:
+                    continue
+                g0 = int(bounds[r]) + k * chunk
+                for j, name in ((2, "diff"), (0, "ref"), (1, "alt")):
+                    tasks.append((name, g0, h[r, j, si, 0, :m]))
+                    tasks.append((name, n_total + g0, h[r, j, si, 1, :m]))
+            if si == S - 1:
+                writer.submit(b, sinks[shift], tasks)
+            else:
+                writer.write(sinks[shift], tasks)
+
+    pending = None
+    try:
+        for k in range(rounds):
+            b = k & 1
+            if works[b] is not None:       # the gather that last read send[b] / wrote recv[b]
+                works[b].wait()
+            if k < n_chunks:
+                flat = send[b].view(3, -1, 2002)
+                engine.chromatin_submit_device(k, flat[0], flat[1], flat[2], 2 * chunk, chunk, 0)
+            if rank == 0:
+                hb = writer.next_set()     # == b: the pinned set's previous contents are on disk
+                assert hb == b
+            if cuda:
+                computed = torch.cuda.Event()
+                computed.record()
+                side.wait_event(computed)
+            done = None
+            with (torch.cuda.stream(side) if cuda else _nullcontext()):
+                e = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if (cuda and rank == 0) else None
+                if e:
+                    e[0].record()
+                if world > 1:
+                    works[b] = dist.gather(send[b], recv[b] if rank == 0 else None, dst=0, async_op=True)
+                if rank == 0:
+                    if world > 1:
+                        works[b].wait()    # the side stream waits for the collective
+                    if e:
+                        e[1].record()
+                    src = recv[b] if world > 1 else [send[b]]
+                    for r in range(world):
+                        if sizes[k][r]:
+                            host[b][r].copy_(src[r], non_blocking=True)
+                    if cuda:
+                        e[2].record()
+                        done = e[2]
+                        ev_pairs.append(e)
+                        for t_ in src:
+                            t_.record_stream(side)
+            if rank == 0:
+                if pending is not None:
+                    flush(pending)
+                pending = (k, b, done)
+        if rank == 0 and pending is not None:
+            flush(pending)
+        for w in works:
+            if w is not None:
+                w.wait()
+        if cuda:
+            torch.cuda.synchronize(dev)
+        if rank == 0:
+            if own_writer:
+                writer.close()
+            else:
+                writer.drain()
+            for e in ev_pairs:
+                timing["gather_ms"] += e[0].elapsed_time(e[1])
+                timing["d2h_ms"] += e[1].elapsed_time(e[2])
+    finally:
+        engine.chromatin_close()
+    timing["gathered_bytes"] = int(3 * S * 2 * 2002 * 4) * (n_total - int(bounds[1] - bounds[0])) if world > 1 else 0
+    return timing
+
+
+class _nullcontext:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
 
 
 def predict_shift_device(engine, genome, chroms, pos, refs, alts, shift: int, gpu_batch: int):
@@ -546,8 +825,13 @@ def run(args, engine=None, genome=None) -> dict:
     gb = max(1, min(args.gpu_batch, max(n_local, 1)))
     seg_outs = None
     if args.mode == "segments" and args.maxshift % 200 == 0 and world > 1 and args.gather == "nccl":
+        from .windows import variant_columns as vcols, variant_extent_invalid
+        cols = vcols(genome, chroms, pos, refs, alts)
+        bad = shard.allreduce_sum_ints([int(variant_extent_invalid(genome, cols, args.maxshift) >= 0)], device=engine.device)[0]
+        if not bad and not getattr(args, "host_descs", False):
+            return _run_gathered(args, engine, genome, cols, chroms, pos, refs, alts, n, rank, world)
         seg_outs = predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, args.maxshift,
-                                                      delta=not args.no_delta)
+                                                      delta=not args.no_delta, host_descs=True)
     pinned, writer = None, None
     if world == 1 or args.gather == "file":
         n_sets = 2  # slab k's file writes overlap slab k+1's GPU work (also across shifts)
@@ -609,6 +893,46 @@ def run(args, engine=None, genome=None) -> dict:
     return {"n_variants": n, "counters": counters, "files": files, "rank": rank, "world": world}
 
 
+def _run_gathered(args, engine, genome, cols, chroms, pos, refs, alts, n, rank, world) -> dict:
+    """run() under torchrun with ``--gather nccl``: per-chunk NCCL gather to rank 0, which writes every file."""
+    from . import shard
+    from .hdf5 import H5Writer
+    from .windows import allele_match_counts
+
+    mine = allele_match_counts(genome, chroms, pos, refs, alts)
+    counters = tuple(shard.allreduce_sum_ints(mine, device=engine.device))
+    shifts = shift_list(args.maxshift)
+    paths = {s: f"{args.output_dir}/snps.shift_{str(s)}.diff.h5" for s in shifts}
+    ws, us, sinks = {}, {}, None
+    if rank == 0:
+        print(f"Number of variants with reference allele matched with reference genome: {counters[0]}")
+        print(f"Number of variants with alternate allele matched with reference genome: {counters[1]}")
+        print(f"Number of input variants: {counters[2]}")
+        shapes = {k: (2 * n, 2002) for k in ("diff", "ref", "alt")}
+        for s in shifts:
+            ws[s] = H5Writer(paths[s], shapes)
+            if args.upstream_layout:
+                us[s] = H5Writer(f"{args.inputfile}.shift_{str(s)}.diff.h5", {"pred": (2 * n, 2002)})
+
+        def make_sink(s):
+            w, up = ws[s], us.get(s)
+
+            def sink(name, row0, arr):
+                w.write_rows(name, row0, arr)
+                if up is not None and name == "diff":
+                    up.write_rows("pred", row0, arr)
+            return sink
+        sinks = {s: make_sink(s) for s in shifts}
+    info = predict_all_shifts_gathered(engine, cols, args.maxshift, n, sinks, delta=not args.no_delta)
+    for s in ws:
+        ws[s].close()
+        if s in us:
+            us[s].close()
+    shard.barrier()
+    return {"n_variants": n, "counters": counters, "files": [paths[s] for s in shifts], "rank": rank, "world": world,
+            "mode": "segments", "gather": "nccl", **info}
+
+
 def _run_segments(args, engine, genome, chroms, pos, refs, alts, n, lo, n_local, rank, world) -> dict:
     """run() in segment mode: all shifts of a variant come out of one pass, so every shift's file is open at once."""
     from . import shard
@@ -650,7 +974,8 @@ def _run_segments(args, engine, genome, chroms, pos, refs, alts, n, lo, n_local,
         return sink
 
     info = predict_all_shifts_segments(engine, genome, chroms, pos, refs, alts, args.maxshift,
-                                       {s: make_sink(s) for s in shifts}, delta=not args.no_delta)
+                                       {s: make_sink(s) for s in shifts}, delta=not args.no_delta,
+                                       host_descs=getattr(args, "host_descs", False))
     for s in shifts:
         ws[s].close()
         if s in us:

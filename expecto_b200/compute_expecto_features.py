@@ -32,7 +32,7 @@ def build_parser() -> argparse.ArgumentParser:
     # extensions
     p.add_argument("--genome", default="./resources/hg19.fa")
     p.add_argument("--weights", default="./resources/deepsea.beluga.pth")
-    p.add_argument("--dtype", default="f16", choices=["f16", "bf16"])
+    p.add_argument("--dtype", default="f16", choices=["f16", "bf16", "f16x3"])
     p.add_argument("--device", type=int, default=0)
     p.add_argument("--genes_per_batch", type=int, default=32, help="genes per GPU batch (x400 windows)")
     p.add_argument("--gather", default="nccl", choices=["nccl", "file"],

@@ -16,6 +16,7 @@
 #include "gemm_tc.cuh"
 #include "kernels_misc.cuh"
 #include "genome_pack.cuh"
+#include "variants.cuh"
 #include <cub/device/device_scan.cuh>
 
 using namespace bx;
@@ -152,6 +153,18 @@ struct bx_ctx {
   void* patch6a = nullptr;  // delta mode: conv6 outputs of the alt patches (phase A / B)
   void* patch6b = nullptr;
   size_t patch6_bytes = 0;
+  int* si_of_k_dev = nullptr;   // [200] shift index of each window offset (EPI_CHROMATIN, delta mode's alt rows)
+  float* ref_scratch = nullptr; // averaged outputs in delta mode: per-strand ref probabilities of a chunk
+  size_t ref_scratch_bytes = 0;
+  struct ChromPlan* plan = nullptr;  // bx_chromatin_open .. bx_chromatin_close
+};
+
+// Where the variant path's FC2 epilogue puts ref / alt / diff (see ChromEpi): device arrays, rows of 2002 floats.
+struct ChromSink {
+  float* ref; float* alt; float* diff;
+  const int* dst;                                  // device [group size]: output row of each group member (or null)
+  long long shift_stride, strand_stride, row0;
+  int average;
 };
 
 // RAII-ish stage timer: records an event pair around a stage when profiling is on.
@@ -242,6 +255,7 @@ static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void
   BX_CASE(8, 160, EPI_BIAS_RELU);
   BX_CASE(1, 256, EPI_PARTIAL_F32);
   BX_CASE(1, 256, EPI_BIAS_SIGMOID);
+  BX_CASE(1, 256, EPI_CHROMATIN);
 #undef BX_CASE
   if constexpr (std::is_same<T, __half>::value) {  // split-operand mode exists for fp16 operands only
 #define BX_CASE(TP, N, E) \
@@ -399,7 +413,7 @@ static int run_fc1(bx_ctx* c, int n, cudaStream_t st, float* part = nullptr, siz
   return run_fc1_finalize<__nv_bfloat16>(c, n, kFc1Splits, split_stride, st);
 }
 
-static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
+static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st, const ChromEpi* chrom = nullptr) {
   GemmParams p = {};
   p.m_rows = n;
   p.k_valid = 2048;
@@ -417,13 +431,28 @@ static int run_fc2(bx_ctx* c, int n, float* probs, cudaStream_t st) {
   p.a_grp = 1 << 30;
   p.a_lo_off = 2048;
   p.b_lo_off = 2048;
-  return launch_gemm(c, 1, 256, EPI_BIAS_SIGMOID, c->hid, n, (uint64_t)2048 * mul, c->wfc2, 2048, (uint64_t)2048 * mul,
-                     p, false, st);
+  if (chrom) p.chrom = *chrom;
+  return launch_gemm(c, 1, 256, chrom ? EPI_CHROMATIN : EPI_BIAS_SIGMOID, c->hid, n, (uint64_t)2048 * mul, c->wfc2, 2048,
+                     (uint64_t)2048 * mul, p, false, st);
+}
+
+// FC2 epilogue parameters of a launch whose rows start at index `first` of row order `mode` (ChromEpi).
+static ChromEpi make_chrom(const bx_ctx* c, const ChromSink& s, int mode, int ng, int n_shifts, long long first,
+                           int si_fixed = 0) {
+  ChromEpi e = {};
+  e.ref = s.ref; e.alt = s.alt; e.diff = s.diff;
+  e.ref_scratch = c->ref_scratch;
+  e.dst = s.dst;
+  e.si_of_k = c->si_of_k_dev;
+  e.shift_stride = s.shift_stride; e.strand_stride = s.strand_stride; e.row0 = s.row0;
+  e.first = first;
+  e.mode = mode; e.ng = ng; e.S = n_shifts; e.si_fixed = si_fixed; e.average = s.average;
+  return e;
 }
 
 // conv1..conv6, fc1, fc2 over n windows whose conv1 operand is already in act[0] or is generated from `enc`.
 static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st, const EncParams* enc = nullptr,
-                       int amode = 0) {
+                       int amode = 0, const ChromEpi* chrom = nullptr) {
   for (int i = 0; i < 6; ++i) {
     StageTimer t(c, 1 + i, st);
     if (int r = run_conv(c, i, n, st, enc, amode)) return r;
@@ -433,7 +462,7 @@ static int run_network(bx_ctx* c, int n, float* probs, cudaStream_t st, const En
     if (int r = run_fc1(c, n, st)) return r;
   }
   StageTimer t(c, 8, st);
-  return run_fc2(c, n, probs, st);
+  return run_fc2(c, n, probs, st, chrom);
 }
 
 // ------------------------------------------------------------------ segment mode
@@ -568,6 +597,8 @@ int bx_ctx_destroy(bx_ctx* c) {
   cudaFree(c->probs_scratch);
   cudaFree(c->act6b); cudaFree(c->fc_in); cudaFree(c->act4h); cudaFree(c->act4b);
   cudaFree(c->patch6a); cudaFree(c->patch6b); cudaFree(c->acc_ref); cudaFree(c->probs_dense);
+  cudaFree(c->si_of_k_dev); cudaFree(c->ref_scratch);
+  bx_chromatin_close(c);
   if (c->s_comp) cudaStreamDestroy(c->s_comp);
   if (c->s_in) cudaStreamDestroy(c->s_in);
   if (c->s_out) cudaStreamDestroy(c->s_out);
@@ -662,12 +693,12 @@ int bx_encode_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t*
 
 // One chunk (m <= cap windows): kernel 1 fused into the conv1 operand, then the network.
 static int forward_chunk_windows(bx_ctx* c, const bx_window_desc* descs_dev, const uint8_t* alleles_dev, int m,
-                                 float* probs_dev, cudaStream_t st) {
+                                 float* probs_dev, cudaStream_t st, const ChromEpi* chrom = nullptr) {
   if (conv1_gen_enabled(c)) {
     EncParams e = {};
     e.descs = descs_dev; e.alleles = alleles_dev; e.bases2 = c->bases2; e.nmask = c->nmask; e.n_bases = c->n_bases;
     e.L = BX_WINDOW; e.n_seg = m;
-    return run_network(c, m, probs_dev, st, &e, 1);
+    return run_network(c, m, probs_dev, st, &e, 1, chrom);
   }
   {
     StageTimer t(c, 0, st);
@@ -680,7 +711,7 @@ static int forward_chunk_windows(bx_ctx* c, const bx_window_desc* descs_dev, con
     g_launches++;
     CK(cudaGetLastError());
   }
-  return run_network(c, m, probs_dev, st);
+  return run_network(c, m, probs_dev, st, nullptr, 0, chrom);
 }
 
 static int forward_chunk_onehot(bx_ctx* c, const uint8_t* x, int m, float* probs_dev, cudaStream_t st) {
@@ -1073,7 +1104,7 @@ static bool delta_dense_enabled() {
 // Dense layers of one delta-mode chunk (kernels_misc.cuh, "delta mode, dense layers"): FC1 over all slices for the
 // ref windows, over the slices that hold patched rows for the alt windows, then FC2 and the scatter to the final order.
 static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int ng, int n_shifts, int patch_row0,
-                             int shift_major, float* out, cudaStream_t st) {
+                             int shift_major, float* out, cudaStream_t st, const ChromSink* sink = nullptr) {
   (void)gp;
   const bool f16 = c->dtype == BX_DTYPE_F16;
   DeltaDense dd = {};
@@ -1109,8 +1140,22 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
           (const __nv_bfloat16*)c->patch6b, dd, alt, d0, (__nv_bfloat16*)c->fc_in);
     g_launches++;
   };
+  if (sink && sink->average) {   // per-strand ref probabilities for the alt launches' alt - ref
+    const size_t need = (size_t)n_shifts * 2 * ng * BX_FEATURES * sizeof(float);
+    if (need > c->ref_scratch_bytes) {
+      CK(cudaStreamSynchronize(st));
+      cudaFree(c->ref_scratch);
+      c->ref_scratch = nullptr; c->ref_scratch_bytes = 0;
+      CK(cudaMalloc(&c->ref_scratch, need));
+      c->ref_scratch_bytes = need;
+    }
+  }
   auto finish = [&](int alt, long long d0, int m) -> int {   // FC2 + scatter of a piece whose hidden layer is ready
     StageTimer t(c, 8, st);
+    if (sink) {   // FC2's epilogue writes ref / alt / diff in their final layout: no dense copy, no scatter
+      const ChromEpi ce = make_chrom(c, *sink, alt ? 2 : 1, ng, n_shifts, d0);
+      return run_fc2(c, m, nullptr, st, &ce);
+    }
     if (int r = run_fc2(c, m, c->probs_dense, st)) return r;
     scatter_delta_rows_kernel<<<m, 256, 0, st>>>(c->probs_dense, dd, alt, d0, out);
     g_launches++;
@@ -1118,8 +1163,9 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
     return 0;
   };
   // ref windows: all slices, partials kept in acc_ref for the alt windows of the same chunk
-  for (size_t d0 = 0; d0 < n_half; d0 += c->cap) {
-    const int m = (int)std::min<size_t>(c->cap, n_half - d0);
+  const size_t ref_piece = (size_t)(c->cap & ~3);   // pieces start at multiples of 4 rows (strand pairs / quads stay in a warp)
+  for (size_t d0 = 0; d0 < n_half; d0 += ref_piece) {
+    const int m = (int)std::min<size_t>(ref_piece, n_half - d0);
     {
       StageTimer t(c, 7, st);
       gather(0, (long long)d0, m);
@@ -1133,7 +1179,7 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
   }
   // alt windows: per M tile only the slices its rows' classes need (at most 32 tiles per launch: GemmParams)
   const int tile_rows = 128 * c->cg;
-  const size_t piece = std::min<size_t>(c->cap, (size_t)32 * tile_rows);
+  const size_t piece = std::min<size_t>(ref_piece, (size_t)32 * tile_rows);
   for (size_t d0 = 0; d0 < n_half; d0 += piece) {
     const int m = (int)std::min<size_t>(piece, n_half - d0);
     GemmParams ranges = {};
@@ -1185,8 +1231,9 @@ static int delta_dense_phase(bx_ctx* c, const SegGather& sg, const Geom& gp, int
 static int forward_segments_impl(bx_ctx* c, const bx_window_desc* descs_dev, const bx_window_desc* patch_descs_dev,
                                  const uint8_t* alleles_dev, int n_groups, int segs_out, int seg_len, int patch_len,
                                  int patch_row0, int n_shifts, const int32_t* k_of_shift, int shift_major,
-                                 float* probs_dev, cudaStream_t st) {
+                                 float* probs_dev, cudaStream_t st, const ChromSink* sink = nullptr) {
   const bool delta = patch_descs_dev != nullptr;
+  if (c->cap < 4) return fail(BX_E_ARG, "context capacity must be >= 4 windows");
   const int segs_in = delta ? 2 : segs_out;
   const Geom g = make_geom(seg_len);
   const int seg_cap = max_segments(c, g);
@@ -1246,17 +1293,21 @@ static int forward_segments_impl(bx_ctx* c, const bx_window_desc* descs_dev, con
         return r;
     if (delta && delta_dense_enabled()) {
       if (int r = delta_dense_phase(c, sg, gp, ng, n_shifts, patch_row0, shift_major,
-                                    probs_dev + (size_t)g0 * segs_out * n_shifts * BX_FEATURES, st))
+                                    sink ? nullptr : probs_dev + (size_t)g0 * segs_out * n_shifts * BX_FEATURES, st,
+                                    sink))
         return r;
       continue;
     }
+    if (sink && (delta || segs_out != 4 || !shift_major))
+      return fail(BX_E_STATE, "the fused ref/alt/diff epilogue needs shift-major quads (or the delta dense phase)");
     // dense layers per window, in final output order, `cap` windows at a time
     sg.n_groups = ng;
     const long long n_win = (long long)ng * segs_out * n_shifts;
-    float* out = probs_dev + (size_t)g0 * segs_out * n_shifts * BX_FEATURES;  // group-major chunks are contiguous
+    float* out = sink ? nullptr : probs_dev + (size_t)g0 * segs_out * n_shifts * BX_FEATURES;  // group-major chunks are contiguous
     void* saved = c->act[6];
-    for (long long w0 = 0; w0 < n_win; w0 += c->cap) {
-      const int m = (int)std::min<long long>(c->cap, n_win - w0);
+    const long long step = sink ? (long long)(c->cap & ~3) : (long long)c->cap;   // quads stay inside one launch
+    for (long long w0 = 0; w0 < n_win; w0 += step) {
+      const int m = (int)std::min<long long>(step, n_win - w0);
       {
         StageTimer t(c, 7, st);
         if (f16)
@@ -1275,7 +1326,10 @@ static int forward_segments_impl(bx_ctx* c, const bx_window_desc* descs_dev, con
         if (r) return r;
       }
       StageTimer t(c, 8, st);
-      if (int r = run_fc2(c, m, out + (size_t)w0 * BX_FEATURES, st)) return r;
+      if (sink) {
+        const ChromEpi ce = make_chrom(c, *sink, 0, ng, n_shifts, w0);
+        if (int r = run_fc2(c, m, nullptr, st, &ce)) return r;
+      } else if (int r = run_fc2(c, m, out + (size_t)w0 * BX_FEATURES, st)) return r;
     }
   }
   return 0;
@@ -1402,6 +1456,333 @@ int bx_fasta_pack(const uint8_t* text_dev, int64_t body_start, int64_t body_end,
   g_launches++;
   CK(cudaGetLastError());
   return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ variant pipeline (chromatin.py:243-286 in the library)
+// bx_chromatin_open takes whole-VCF column arrays once; the library classifies the variants (delta / full-segment /
+// per-window path), builds every descriptor on the device (variants.cuh) and runs the chunk loop with its own
+// streams: compute of chunk k+1 overlaps the device -> host copy of chunk k.  FC2's epilogue writes ref / alt /
+// diff = alt - ref straight into the strand-stacked layout of chromatin.py:281-286 (EPI_CHROMATIN).
+struct ChromPlan {
+  int64_t n = 0;
+  int maxshift = 0, S = 0, seg_len = 0, flags = 0, chunk = 0, n_chunks = 0;
+  bool segments = false;           // segment mode usable (maxshift a multiple of 200, <= 1000)
+  int patch_row0 = 0, patch_len = 0;
+  int shifts[200] = {}, k_of_shift[200] = {};
+  // device copies of the columns, the allele table and the per-chunk group lists
+  long long* gpos = nullptr;
+  int *ref_len = nullptr, *alt_len = nullptr, *ref_aoff = nullptr, *alt_aoff = nullptr, *idx = nullptr;
+  uint8_t* alleles = nullptr;
+  std::vector<int> n_delta, n_full, n_win;   // per chunk; idx holds [delta | full | window] local indices per chunk
+  bx_window_desc* descs = nullptr;           // 4 * chunk descriptors of scratch
+  float* stage[2][3] = {};                   // ref / alt / diff staging, [S][2][chunk][2002] each
+  cudaEvent_t ev_done[2] = {}, ev_copied[2] = {};
+  int set_chunk[2] = {-1, -1};
+  VariantCols cols() const { return VariantCols{gpos, ref_len, alt_len, ref_aoff, alt_aoff}; }
+};
+
+namespace {
+
+// windows.py: delta_patch_geometry for substitutions of up to 16 bases.
+bool delta_patch_geometry(int maxshift, int* row0_out, int* len_out) {
+  const int seg_len = 2000 + 2 * maxshift, v0 = maxshift + 999, ma = 16, rf = 310;
+  const int smin = std::min(v0, std::min(seg_len - v0 - ma, seg_len - v0 - 1));
+  const int emax = std::max(v0 + ma, seg_len - v0);
+  if (smin - (rf + 7) < 0) return false;
+  const int row0 = (smin - (rf + 7)) / 16;
+  const int rows = (emax - 1) / 16 - row0 + 1;
+  int L = 16 * ((16 * (rows - 1) + rf + 8 + 15) / 16);
+  auto valid = [](int len) {
+    const int p2 = (len - 14) / 4;
+    return std::min((p2 - 14) / 4 - 14, (p2 - 16) / 4 - 14);
+  };
+  while (valid(L) < rows) L += 16;
+  if (16 * row0 + L > seg_len) return false;
+  *row0_out = row0; *len_out = L;
+  return true;
+}
+
+template <typename T>
+int upload(T** dst, const T* src, size_t n, cudaStream_t st) {
+  CK(cudaMalloc(dst, std::max<size_t>(n, 1) * sizeof(T)));
+  if (n) CK(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+  return 0;
+}
+
+void free_plan(ChromPlan* p) {
+  if (!p) return;
+  cudaFree(p->gpos); cudaFree(p->ref_len); cudaFree(p->alt_len); cudaFree(p->ref_aoff); cudaFree(p->alt_aoff);
+  cudaFree(p->idx); cudaFree(p->alleles); cudaFree(p->descs);
+  for (int i = 0; i < 2; ++i) {
+    for (int j = 0; j < 3; ++j) cudaFree(p->stage[i][j]);
+    if (p->ev_done[i]) cudaEventDestroy(p->ev_done[i]);
+    if (p->ev_copied[i]) cudaEventDestroy(p->ev_copied[i]);
+  }
+  delete p;
+}
+
+// One chunk of the plan through the forward; results go to `sink` (rows relative to sink.row0).
+int run_plan_chunk(bx_ctx* c, int k, ChromSink sink, cudaStream_t st) {
+  ChromPlan* p = c->plan;
+  const long long v0 = (long long)k * p->chunk;
+  const int nd = p->n_delta[k], nf = p->n_full[k], nw = p->n_win[k];
+  const int* idx = p->idx + v0;
+  const VariantCols cols = p->cols();
+  if (nd > 0) {
+    bx_window_desc* rd = p->descs;
+    bx_window_desc* pd = p->descs + 2 * (size_t)nd;
+    build_delta_descs_kernel<<<(nd + 127) / 128, 128, 0, st>>>(cols, idx, v0, nd, p->maxshift, p->patch_row0,
+                                                               p->patch_len, rd, pd);
+    g_launches++;
+    CK(cudaGetLastError());
+    sink.dst = idx;
+    if (sink.average) {
+      // delta mode's alt rows add their halves into zeroed outputs (ChromEpi); the chunk's other groups overwrite
+      // their own rows afterwards
+      const int64_t v0m = std::min<int64_t>(p->chunk, p->n - v0);
+      for (float* t : {sink.alt, sink.diff})
+        for (int si = 0; si < p->S; ++si)
+          CK(cudaMemsetAsync(t + (size_t)(si * sink.shift_stride + sink.row0) * BX_FEATURES, 0,
+                             (size_t)v0m * BX_FEATURES * sizeof(float), st));
+    }
+    if (int r = forward_segments_impl(c, rd, pd, p->alleles, nd, 4, p->seg_len, p->patch_len, p->patch_row0, p->S,
+                                      p->k_of_shift, 1, nullptr, st, &sink))
+      return r;
+  }
+  if (nf > 0) {
+    build_segment_descs_kernel<<<(nf + 127) / 128, 128, 0, st>>>(cols, idx + nd, v0, nf, p->maxshift, p->descs);
+    g_launches++;
+    CK(cudaGetLastError());
+    sink.dst = idx + nd;
+    if (int r = forward_segments_impl(c, p->descs, nullptr, p->alleles, nf, 4, p->seg_len, 0, 0, p->S, p->k_of_shift,
+                                      1, nullptr, st, &sink))
+      return r;
+  }
+  if (nw > 0) {   // long indels, exotic shift ranges: every window separately, with the reference's slice semantics
+    const int* widx = idx + nd + nf;
+    const int step = (c->cap & ~3) / 4;   // variants per forward (4 windows each)
+    for (int si = 0; si < p->S; ++si) {
+      for (int g0 = 0; g0 < nw; g0 += step) {
+        const int m = std::min(step, nw - g0);
+        build_window_descs_kernel<<<(m + 127) / 128, 128, 0, st>>>(cols, widx + g0, v0, m, p->shifts[si], p->descs);
+        g_launches++;
+        CK(cudaGetLastError());
+        sink.dst = widx + g0;
+        const ChromEpi ce = make_chrom(c, sink, 3, m, p->S, 0, si);
+        if (int r = forward_chunk_windows(c, p->descs, p->alleles, 4 * m, nullptr, st, &ce)) return r;
+      }
+    }
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bx_chromatin_close(bx_ctx* c) {
+  if (!c) return fail(BX_E_ARG, "ctx is null");
+  if (c->plan) {
+    DeviceGuard guard(c->device);
+    if (c->s_comp) cudaStreamSynchronize(c->s_comp);
+    if (c->s_out) cudaStreamSynchronize(c->s_out);
+    free_plan(c->plan);
+    c->plan = nullptr;
+  }
+  return 0;
+}
+
+int bx_chromatin_open(bx_ctx* c, int64_t n, const int64_t* gpos, const int32_t* ref_len, const int32_t* alt_len,
+                      const int32_t* ref_aoff, const int32_t* alt_aoff, const uint8_t* alleles, int64_t n_alleles,
+                      int maxshift, int flags, int chunk_variants, int* n_chunks_out, int* chunk_variants_out) {
+  if (!c || n < 0 || n_alleles < 0 || maxshift < 0) return fail(BX_E_ARG, "invalid arguments");
+  if (n > 0 && (!gpos || !ref_len || !alt_len || !ref_aoff || !alt_aoff)) return fail(BX_E_ARG, "null column");
+  if (n_alleles > 0 && !alleles) return fail(BX_E_ARG, "null allele table");
+  if (!c->bases2) return fail(BX_E_STATE, "genome not set (bx_ctx_set_genome)");
+  if (!c->weights_ready) return fail(BX_E_STATE, "weights not loaded (bx_ctx_load_weights)");
+  if (c->cap < 4) return fail(BX_E_ARG, "context capacity must be >= 4 windows");
+  if (maxshift % 200 != 0 && !(flags & BX_CHROM_WINDOWS))
+    flags |= BX_CHROM_WINDOWS;   // chromatin.py:243's range() then has no +-maxshift entry; windows one by one
+  const int S = 1 + 2 * (maxshift / 200);
+  if (S > 200) return fail(BX_E_ARG, "maxshift %d gives %d shifts (limit 200)", maxshift, S);
+  ON_DEVICE(c->device);
+  bx_chromatin_close(c);
+  if (int r = ensure_pipe(c, 0, 0, 0)) return r;
+  ChromPlan* p = new ChromPlan();
+  c->plan = p;
+  auto bail = [&](int rc) { free_plan(p); c->plan = nullptr; return rc; };
+  p->n = n; p->maxshift = maxshift; p->S = S; p->seg_len = 2000 + 2 * maxshift; p->flags = flags;
+  {  // chromatin.py:243: [0, -200 .. -maxshift, 200 .. maxshift]; window offset index k = (shift + maxshift) / 200
+    int i = 0;
+    p->shifts[i++] = 0;
+    for (int s = -200; s >= -maxshift; s -= 200) p->shifts[i++] = s;
+    for (int s = 200; s <= maxshift; s += 200) p->shifts[i++] = s;
+    int si_of_k[200];
+    for (int j = 0; j < S; ++j) { p->k_of_shift[j] = (p->shifts[j] + maxshift) / 200; si_of_k[p->k_of_shift[j]] = j; }
+    if (!c->si_of_k_dev) { if (cudaMalloc(&c->si_of_k_dev, 200 * sizeof(int)) != cudaSuccess) return bail(fail(BX_E_CUDA, "cudaMalloc failed")); }
+    if (cudaMemcpy(c->si_of_k_dev, si_of_k, S * sizeof(int), cudaMemcpyHostToDevice) != cudaSuccess)
+      return bail(fail(BX_E_CUDA, "cudaMemcpy of the shift table failed"));
+  }
+  p->segments = !(flags & BX_CHROM_WINDOWS) && maxshift <= 1000;
+  bool delta = p->segments && !(flags & BX_CHROM_NO_DELTA) && S > 1 &&
+               delta_patch_geometry(maxshift, &p->patch_row0, &p->patch_len);
+  int chunk = p->segments ? max_segments(c, make_geom(p->seg_len)) / 4 : (c->cap & ~3) / 4;
+  if (chunk < 1) return bail(fail(BX_E_ARG, "context capacity (%d windows) is too small for %d-position segments", c->cap, p->seg_len));
+  if (chunk_variants > 0) chunk = std::min(chunk, chunk_variants);
+  p->chunk = chunk;
+  p->n_chunks = (int)((n + chunk - 1) / chunk);
+  // classification (windows.py: segment_eligible, delta_eligible) and per-chunk group lists
+  std::vector<int> idx((size_t)n);
+  p->n_delta.assign(p->n_chunks, 0); p->n_full.assign(p->n_chunks, 0); p->n_win.assign(p->n_chunks, 0);
+  for (int k = 0; k < p->n_chunks; ++k) {
+    const int64_t v0 = (int64_t)k * chunk, m = std::min<int64_t>(chunk, n - v0);
+    std::vector<int> full, win;
+    int nd = 0;
+    for (int64_t j = 0; j < m; ++j) {
+      const int64_t rl = ref_len[v0 + j], al = alt_len[v0 + j];
+      if (rl < 0 || al < 0 || ref_aoff[v0 + j] < 0 || alt_aoff[v0 + j] < 0 || ref_aoff[v0 + j] + rl > n_alleles ||
+          alt_aoff[v0 + j] + al > n_alleles)
+        return bail(fail(BX_E_ARG, "variant %lld: allele offsets outside the allele table", (long long)(v0 + j)));
+      const bool seg_ok = p->segments && rl <= 1050 - maxshift && al - rl >= -100 && al <= 1000 && rl >= 1;
+      if (seg_ok && delta && rl == al && rl <= 16) idx[v0 + nd++] = (int)j;
+      else if (seg_ok) full.push_back((int)j);
+      else win.push_back((int)j);
+    }
+    std::copy(full.begin(), full.end(), idx.begin() + v0 + nd);
+    std::copy(win.begin(), win.end(), idx.begin() + v0 + nd + full.size());
+    p->n_delta[k] = nd; p->n_full[k] = (int)full.size(); p->n_win[k] = (int)win.size();
+  }
+  cudaStream_t st = c->s_in;
+  if (upload(&p->gpos, reinterpret_cast<const long long*>(gpos), (size_t)n, st) || upload(&p->ref_len, ref_len, (size_t)n, st) ||
+      upload(&p->alt_len, alt_len, (size_t)n, st) || upload(&p->ref_aoff, ref_aoff, (size_t)n, st) ||
+      upload(&p->alt_aoff, alt_aoff, (size_t)n, st) || upload(&p->idx, idx.data(), (size_t)n, st) ||
+      upload(&p->alleles, alleles, (size_t)n_alleles, st))
+    return bail(BX_E_CUDA);
+  if (cudaMalloc(&p->descs, (size_t)4 * chunk * sizeof(bx_window_desc)) != cudaSuccess)
+    return bail(fail(BX_E_CUDA, "cudaMalloc of the descriptor scratch failed"));
+  for (int i = 0; i < 2; ++i) {
+    if (cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&p->ev_copied[i], cudaEventDisableTiming) != cudaSuccess)
+      return bail(fail(BX_E_CUDA, "cudaEventCreate failed"));
+  }
+  if (cudaStreamSynchronize(st) != cudaSuccess) return bail(fail(BX_E_CUDA, "column upload failed"));
+  if (n_chunks_out) *n_chunks_out = p->n_chunks;
+  if (chunk_variants_out) *chunk_variants_out = chunk;
+  return 0;
+}
+
+int bx_chromatin_chunk_info(bx_ctx* c, int chunk, int64_t* v0, int* m, int* n_delta, int* n_full, int* n_window) {
+  if (!c || !c->plan) return fail(BX_E_STATE, "no open variant plan (bx_chromatin_open)");
+  ChromPlan* p = c->plan;
+  if (chunk < 0 || chunk >= p->n_chunks) return fail(BX_E_ARG, "chunk %d out of range (%d chunks)", chunk, p->n_chunks);
+  const int64_t first = (int64_t)chunk * p->chunk;
+  if (v0) *v0 = first;
+  if (m) *m = (int)std::min<int64_t>(p->chunk, p->n - first);
+  if (n_delta) *n_delta = p->n_delta[chunk];
+  if (n_full) *n_full = p->n_full[chunk];
+  if (n_window) *n_window = p->n_win[chunk];
+  return 0;
+}
+
+int bx_chromatin_submit(bx_ctx* c, int chunk, float* ref_host, float* alt_host, float* diff_host) {
+  if (!c || !c->plan) return fail(BX_E_STATE, "no open variant plan (bx_chromatin_open)");
+  ChromPlan* p = c->plan;
+  if (chunk < 0 || chunk >= p->n_chunks || !ref_host || !alt_host || !diff_host) return fail(BX_E_ARG, "invalid arguments");
+  ON_DEVICE(c->device);
+  const int set = chunk & 1;
+  const int m = (int)std::min<int64_t>(p->chunk, p->n - (int64_t)chunk * p->chunk);
+  const bool avg = p->flags & BX_CHROM_AVERAGE;
+  const size_t rows = (size_t)p->S * (avg ? 1 : 2) * m;
+  for (int j = 0; j < 3; ++j)
+    if (!p->stage[set][j])
+      CK(cudaMalloc(&p->stage[set][j], (size_t)p->S * 2 * p->chunk * BX_FEATURES * sizeof(float)));
+  // the staging set's previous contents (chunk - 2) must have left for the host
+  CK(cudaStreamWaitEvent(c->s_comp, p->ev_copied[set], 0));
+  ChromSink sink = {};
+  sink.ref = p->stage[set][0]; sink.alt = p->stage[set][1]; sink.diff = p->stage[set][2];
+  sink.shift_stride = avg ? m : 2 * (long long)m;
+  sink.strand_stride = m;
+  sink.row0 = 0;
+  sink.average = avg ? 1 : 0;
+  {
+    StageTimer t(c, 9, c->s_comp);   // the whole chunk (the per-layer stages nest inside when profiling is on)
+    if (int r = run_plan_chunk(c, chunk, sink, c->s_comp)) return r;
+  }
+  CK(cudaEventRecord(p->ev_done[set], c->s_comp));
+  CK(cudaStreamWaitEvent(c->s_out, p->ev_done[set], 0));
+  float* dst[3] = {ref_host, alt_host, diff_host};
+  for (int j = 0; j < 3; ++j)
+    CK(cudaMemcpyAsync(dst[j], p->stage[set][j], rows * BX_FEATURES * sizeof(float), cudaMemcpyDeviceToHost, c->s_out));
+  CK(cudaEventRecord(p->ev_copied[set], c->s_out));
+  p->set_chunk[set] = chunk;
+  return 0;
+}
+
+int bx_chromatin_wait(bx_ctx* c, int chunk) {
+  if (!c || !c->plan) return fail(BX_E_STATE, "no open variant plan (bx_chromatin_open)");
+  ChromPlan* p = c->plan;
+  const int set = chunk & 1;
+  if (chunk < 0 || p->set_chunk[set] != chunk)
+    return fail(BX_E_STATE, "chunk %d is not in flight (wait for a chunk before submitting chunk + 2)", chunk);
+  ON_DEVICE(c->device);
+  CK(cudaEventSynchronize(p->ev_copied[set]));
+  return 0;
+}
+
+int bx_chromatin_submit_device(bx_ctx* c, int chunk, float* ref_dev, float* alt_dev, float* diff_dev,
+                               int64_t shift_stride_rows, int64_t strand_stride_rows, int64_t row0, void* stream) {
+  if (!c || !c->plan) return fail(BX_E_STATE, "no open variant plan (bx_chromatin_open)");
+  ChromPlan* p = c->plan;
+  if (chunk < 0 || chunk >= p->n_chunks || !ref_dev || !alt_dev || !diff_dev) return fail(BX_E_ARG, "invalid arguments");
+  ON_DEVICE(c->device);
+  ChromSink sink = {};
+  sink.ref = ref_dev; sink.alt = alt_dev; sink.diff = diff_dev;
+  sink.shift_stride = shift_stride_rows;
+  sink.strand_stride = strand_stride_rows;
+  sink.row0 = row0;
+  sink.average = (p->flags & BX_CHROM_AVERAGE) ? 1 : 0;
+  return run_plan_chunk(c, chunk, sink, (cudaStream_t)stream);
+}
+
+int bx_variant_descs_host(int kind, int64_t n, const int64_t* gpos, const int32_t* ref_len, const int32_t* alt_len,
+                          const int32_t* ref_aoff, const int32_t* alt_aoff, int maxshift, int shift,
+                          int* patch_row0, int* patch_len, bx_window_desc* out_host) {
+  if (n < 0 || kind < 0 || kind > 2) return fail(BX_E_ARG, "invalid arguments");
+  int row0 = 0, plen = 0;
+  if (kind == 1) {
+    if (!delta_patch_geometry(maxshift, &row0, &plen)) return fail(BX_E_ARG, "no delta patch for maxshift %d", maxshift);
+    if (patch_row0) *patch_row0 = row0;
+    if (patch_len) *patch_len = plen;
+  }
+  if (n == 0) return 0;
+  if (!gpos || !ref_len || !alt_len || !ref_aoff || !alt_aoff || !out_host) return fail(BX_E_ARG, "null argument");
+  if (int r = check_device()) return r;
+  if (n > (1 << 26)) return fail(BX_E_ARG, "too many variants for the test entry point");
+  ChromPlan p;
+  std::vector<int> idx((size_t)n);
+  for (int64_t i = 0; i < n; ++i) idx[i] = (int)i;
+  bx_window_desc* out = nullptr;
+  cudaStream_t st = 0;
+  int rc = 0;
+  if (upload(&p.gpos, reinterpret_cast<const long long*>(gpos), (size_t)n, st) || upload(&p.ref_len, ref_len, (size_t)n, st) ||
+      upload(&p.alt_len, alt_len, (size_t)n, st) || upload(&p.ref_aoff, ref_aoff, (size_t)n, st) ||
+      upload(&p.alt_aoff, alt_aoff, (size_t)n, st) || upload(&p.idx, idx.data(), (size_t)n, st) ||
+      cudaMalloc(&out, (size_t)4 * n * sizeof(bx_window_desc)) != cudaSuccess)
+    rc = fail(BX_E_CUDA, "device allocation failed");
+  if (!rc) {
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    if (kind == 0) build_segment_descs_kernel<<<blocks, 128, 0, st>>>(p.cols(), p.idx, 0, (int)n, maxshift, out);
+    else if (kind == 1) build_delta_descs_kernel<<<blocks, 128, 0, st>>>(p.cols(), p.idx, 0, (int)n, maxshift, row0, plen, out, out + 2 * n);
+    else build_window_descs_kernel<<<blocks, 128, 0, st>>>(p.cols(), p.idx, 0, (int)n, shift, out);
+    g_launches++;
+    if (cudaMemcpy(out_host, out, (size_t)4 * n * sizeof(bx_window_desc), cudaMemcpyDeviceToHost) != cudaSuccess)
+      rc = fail(BX_E_CUDA, "descriptor kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  cudaFree(p.gpos); cudaFree(p.ref_len); cudaFree(p.alt_len); cudaFree(p.ref_aoff); cudaFree(p.alt_aoff); cudaFree(p.idx);
+  cudaFree(out);
+  return rc;
 }
 
 }  // extern "C"

@@ -35,6 +35,36 @@ enum EpiKind : int {
   EPI_BIAS_SIGMOID = 3,    // y = sigmoid(acc + b) -> fp32
   EPI_POOL2_BIAS_RELU = 4, // y = max over 2 consecutive rows of relu(acc + b) -> 16-bit: half of a MaxPool(1,4), so
                            // that segment mode can finish both pooling phases from one conv4 pass (pool_phases_kernel)
+  EPI_CHROMATIN = 5,       // FC2 of the variant path: p = sigmoid(acc + b) written straight into chromatin.py's
+                           // ref / alt / diff = alt - ref row layout (chromatin.py:281-286), optionally averaged over
+                           // the forward / reverse-complement rows as predict.py:186-190 reads them (ChromEpi)
+};
+
+// Where the rows of an FC2 launch go in the variant path (EPI_CHROMATIN).  Every GEMM row is one window
+// (variant, shift, q) with q = 0 ref fwd, 1 ref rc, 2 alt fwd, 3 alt rc; its probabilities land in
+//   X[(si * shift_stride + (q & 1) * strand_stride + row0 + dst(grp)) * 2002 + feature],  X = ref (q < 2) or alt,
+// and alt rows also produce diff = alt - ref of the same strand.  Row order of the launch:
+//   mode 0: (si, grp, q) shift-major quads [segment mode, four full segments per variant]
+//   mode 1: delta mode's ref rows  d = (si * ng + grp) * 2 + t
+//   mode 2: delta mode's alt rows  d = c * 2 * ng + grp * 2 + t, si = si_of_k[t ? S - 1 - c : c]
+//   mode 3: (grp, q) quads of one shift si_fixed [per-window path]
+// Quads sit in four adjacent lanes of one warp (row offsets are multiples of 4), so alt - ref is a shfl.xor 2 away;
+// delta mode's alt launch reads the ref probabilities its ref launch stored (same stream, earlier kernel).
+// average: outputs are [.., row, 2002] without the strand axis: ref = (fwd + rc) / 2, alt likewise,
+// diff = ((alt_f - ref_f) + (alt_r - ref_r)) / 2 — the exact expressions of predict.py:186-190 on chromatin.py:281's
+// per-strand differences; per-strand ref probabilities of mode 1 go to ref_scratch for the mode-2 launch.  The two
+// strands of one shift are neighbouring lanes in modes 0, 1 and 3.  In mode 2 they are not (a forward window of
+// offset class c and the reverse-complement window of the same class belong to different shifts), so each alt row
+// adds its half, x / 2, to outputs the caller zeroed: x / 2 is exact and a two-term sum does not depend on the
+// order of its terms, so fl(a/2 + b/2) = fl(a + b) / 2 whichever row arrives first — deterministic and bit-identical.
+struct ChromEpi {
+  float* ref; float* alt; float* diff;
+  float* ref_scratch;            // average && delta mode: per-strand ref rows [S][2][ng] (dense, dst ignored)
+  const int* dst;                // [ng] local output row of each group member, or nullptr = identity
+  const int* si_of_k;            // [S] device table (mode 2)
+  long long shift_stride, strand_stride, row0;   // in rows of 2002 floats
+  long long first;               // index of the launch's first row in its mode's row order
+  int mode, ng, S, si_fixed, average;
 };
 
 struct GemmParams {
@@ -68,6 +98,7 @@ struct GemmParams {
   //   B: kb * 64 + (part == 1 ? b_lo_off : 0)
   int parts, a_grp, a_grp_stride, a_lo_off, b_lo_off;
   int out_lo_off;    // SPLIT_OUT epilogues: the low half of an output goes out_lo_off elements after the high half
+  ChromEpi chrom;    // EPI_CHROMATIN only
 };
 
 template <int TAPS, int BLOCK_N, int CG>
@@ -452,6 +483,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       const size_t obase = (size_t)orow_idx * p.ld_out + n0;
       const int j = lane & 3;
+      // EPI_CHROMATIN: this thread's window -> (shift, group member, q) -> output rows
+      int cq = 0;
+      size_t crow = 0, cscr = 0;
+      if constexpr (EPI == EPI_CHROMATIN) {
+        const ChromEpi& ce = p.chrom;
+        const long long d = ce.first + r;
+        int si, grp;
+        if (ce.mode == 0) { cq = (int)(d & 3); const long long x = d >> 2; si = (int)(x / ce.ng); grp = (int)(x % ce.ng); }
+        else if (ce.mode == 1) { cq = (int)(d & 1); const long long x = d >> 1; si = (int)(x / ce.ng); grp = (int)(x % ce.ng); }
+        else if (ce.mode == 2) {
+          const int cls = (int)(d / (2 * ce.ng)), x = (int)(d % (2 * ce.ng));
+          grp = x >> 1; cq = 2 + (x & 1);
+          si = valid ? ce.si_of_k[(x & 1) ? ce.S - 1 - cls : cls] : 0;
+        } else { cq = (int)(d & 3); grp = (int)(d >> 2); si = ce.si_fixed; }
+        const int t = cq & 1;
+        const long long v = ce.row0 + ((ce.dst != nullptr && valid) ? ce.dst[grp] : grp);
+        crow = (size_t)(si * ce.shift_stride + (ce.average ? 0 : t * ce.strand_stride) + v) * 2002;
+        cscr = ((size_t)((size_t)si * 2 + t) * ce.ng + grp) * 2002;
+      }
 
       // One 16-column chunk: registers -> bias/activation -> global.
       auto process = [&](const uint32_t (&v)[16], int c, const float4 (&bq)[4]) {
@@ -543,6 +593,61 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int i = 0; i < 4; ++i)
               o[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
                                  __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+          }
+        } else if constexpr (EPI == EPI_CHROMATIN) {
+          const ChromEpi& ce = p.chrom;
+          const int col0 = n0 + c * 16;
+#pragma unroll
+          for (int i = 0; i < 16; i += 2) {
+            const bool in = col0 + i < p.n_store;   // warp-uniform (n_store is even)
+            float2 pr = make_float2(0.f, 0.f);
+            if (in) {
+              const float z0 = __uint_as_float(v[i]) + sbias[col0 + i];
+              const float z1 = __uint_as_float(v[i + 1]) + sbias[col0 + i + 1];
+              pr = make_float2(1.f / (1.f + __expf(-z0)), 1.f / (1.f + __expf(-z1)));
+            }
+            const size_t o = crow + col0 + i;
+            // the same strand's ref probability: two lanes down in a quad, or what the ref launch stored
+            float2 rf;
+            if (ce.mode == 2) {
+              rf = make_float2(0.f, 0.f);
+              if (in && valid) rf = *reinterpret_cast<const float2*>((ce.average ? ce.ref_scratch + cscr : ce.ref + crow) + col0 + i);
+            } else {
+              rf.x = __shfl_xor_sync(0xffffffffu, pr.x, 2);
+              rf.y = __shfl_xor_sync(0xffffffffu, pr.y, 2);
+            }
+            const float2 df = make_float2(pr.x - rf.x, pr.y - rf.y);   // meaningful on alt rows
+            if (!ce.average) {
+              if (in && valid) {
+                if (cq < 2) *reinterpret_cast<float2*>(ce.ref + o) = pr;
+                else {
+                  *reinterpret_cast<float2*>(ce.alt + o) = pr;
+                  *reinterpret_cast<float2*>(ce.diff + o) = df;
+                }
+              }
+            } else if (ce.mode == 2) {
+              if (in && valid) {
+                atomicAdd(ce.alt + o, pr.x / 2.0f);
+                atomicAdd(ce.alt + o + 1, pr.y / 2.0f);
+                atomicAdd(ce.diff + o, df.x / 2.0f);
+                atomicAdd(ce.diff + o + 1, df.y / 2.0f);
+              }
+            } else {
+              // forward / reverse-complement rows of one shift are neighbouring lanes
+              const float2 po = make_float2(__shfl_xor_sync(0xffffffffu, pr.x, 1), __shfl_xor_sync(0xffffffffu, pr.y, 1));
+              const float2 dn = make_float2(__shfl_xor_sync(0xffffffffu, df.x, 1), __shfl_xor_sync(0xffffffffu, df.y, 1));
+              if (in && valid) {
+                if (ce.mode == 1) *reinterpret_cast<float2*>(ce.ref_scratch + cscr + col0 + i) = pr;
+                if ((cq & 1) == 0) {   // the forward lane writes the averages: (fwd + rc) / 2.0
+                  const float2 avg = make_float2((pr.x + po.x) / 2.0f, (pr.y + po.y) / 2.0f);
+                  if (cq < 2) *reinterpret_cast<float2*>(ce.ref + o) = avg;
+                  else {
+                    *reinterpret_cast<float2*>(ce.alt + o) = avg;
+                    *reinterpret_cast<float2*>(ce.diff + o) = make_float2((df.x + dn.x) / 2.0f, (df.y + dn.y) / 2.0f);
+                  }
+                }
+              }
+            }
           }
         } else {  // EPI_BIAS_SIGMOID
           // rows are ld_out = 2002 floats apart (8-byte aligned) and n_store is even: float2 stores, half the

@@ -191,6 +191,51 @@ class BelugaEngine:
                                               out.data_ptr(), _stream_ptr(self.device)))
         return out
 
+    # ------------------------------------------------------------------ the variant loop inside the library
+    def chromatin_open(self, cols: dict, maxshift: int = 800, delta: bool = True, average: bool = False,
+                       windows_only: bool = False, chunk_variants: int = 0) -> tuple[int, int]:
+        """bx_chromatin_open: hand the whole-VCF columns (``windows.variant_columns``) to the library.  Returns
+        (number of chunks, variants per chunk)."""
+        flags = (0 if delta else _lib.CHROM_NO_DELTA) | (_lib.CHROM_AVERAGE if average else 0) | \
+            (_lib.CHROM_WINDOWS if windows_only else 0)
+        nch, chunk = C.c_int(0), C.c_int(0)
+        p = lambda a: a.ctypes.data if a.size else None  # noqa: E731
+        check(lib().bx_chromatin_open(self._ctx, int(cols["n"]), p(cols["gpos"]), p(cols["ref_len"]), p(cols["alt_len"]),
+                                      p(cols["ref_aoff"]), p(cols["alt_aoff"]), p(cols["alleles"]),
+                                      int(cols["alleles"].size), int(maxshift), flags, int(chunk_variants),
+                                      C.byref(nch), C.byref(chunk)))
+        self._plan = {"S": 1 + 2 * (int(maxshift) // 200), "average": average, "n": int(cols["n"]), "chunk": chunk.value}
+        return nch.value, chunk.value
+
+    def chromatin_chunk_info(self, k: int) -> dict:
+        v0, m, nd, nf, nw = C.c_int64(0), C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+        check(lib().bx_chromatin_chunk_info(self._ctx, k, C.byref(v0), C.byref(m), C.byref(nd), C.byref(nf), C.byref(nw)))
+        return {"v0": v0.value, "m": m.value, "delta": nd.value, "full": nf.value, "window": nw.value}
+
+    def chromatin_submit(self, k: int, ref: torch.Tensor, alt: torch.Tensor, diff: torch.Tensor) -> None:
+        """Enqueue chunk ``k``; its ref / alt / diff arrive in the given pinned host tensors as dense
+        [S, 2, m, 2002] (``average``: [S, m, 2002]).  ``chromatin_wait(k)`` before touching them."""
+        for t in (ref, alt, diff):
+            if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+                raise ValueError("chromatin_submit takes contiguous float32 host tensors")
+        check(lib().bx_chromatin_submit(self._ctx, k, ref.data_ptr(), alt.data_ptr(), diff.data_ptr()))
+
+    def chromatin_wait(self, k: int) -> None:
+        check(lib().bx_chromatin_wait(self._ctx, k))
+
+    def chromatin_submit_device(self, k: int, ref: torch.Tensor, alt: torch.Tensor, diff: torch.Tensor,
+                                shift_stride: int, strand_stride: int, row0: int) -> None:
+        """Chunk ``k`` with the results left in HBM on the current stream: row (shift si, strand t, variant v of the
+        chunk) goes to row ``si * shift_stride + t * strand_stride + row0 + v`` of each [rows, 2002] device tensor."""
+        for t in (ref, alt, diff):
+            if not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+                raise ValueError("chromatin_submit_device takes contiguous float32 CUDA tensors")
+        check(lib().bx_chromatin_submit_device(self._ctx, k, ref.data_ptr(), alt.data_ptr(), diff.data_ptr(),
+                                               int(shift_stride), int(strand_stride), int(row0), _stream_ptr(self.device)))
+
+    def chromatin_close(self) -> None:
+        check(lib().bx_chromatin_close(self._ctx))
+
     def forward_onehot(self, onehot: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
         """``onehot``: uint8/bool [n,4,2000] (or [n,4,1,2000]) on this device -> fp32 [n,2002]."""
         x = onehot.reshape(-1, 4, WINDOW)
@@ -262,6 +307,22 @@ class BelugaEngine:
         check(lib().bx_debug_activation(self._ctx, layer, n, dst.data_ptr(), C.byref(cnt), _stream_ptr(self.device)))
         assert cnt.value == dst.numel()
         return dst
+
+
+def variant_descs_host(kind: int, cols: dict, maxshift: int = 800, shift: int = 0):
+    """The device descriptor builders (csrc/variants.cuh) on host columns — test hook (bx_variant_descs_host).
+    kind 0: [n, 4] full segments; 1: ([n, 2] ref segments, [n, 2] alt patches, patch_row0, patch_len);
+    2: [n, 4] windows at ``shift``."""
+    n = int(cols["n"])
+    out = np.zeros(4 * n, dtype=_lib.DESC_DTYPE)
+    row0, plen = C.c_int(0), C.c_int(0)
+    p = lambda a: a.ctypes.data if a.size else None  # noqa: E731
+    check(lib().bx_variant_descs_host(kind, n, p(cols["gpos"]), p(cols["ref_len"]), p(cols["alt_len"]),
+                                      p(cols["ref_aoff"]), p(cols["alt_aoff"]), int(maxshift), int(shift),
+                                      C.byref(row0), C.byref(plen), out.ctypes.data if n else None))
+    if kind == 1:
+        return out[:2 * n].reshape(n, 2), out[2 * n:].reshape(n, 2), row0.value, plen.value
+    return out.reshape(n, 4)
 
 
 def chromatin_outputs(probs: torch.Tensor, n_var: int, average: bool = False):

@@ -62,7 +62,7 @@ def build_parser() -> argparse.ArgumentParser:
                         "snps_hg19.vcf is written to -o and used as --coorFile_chromatin unless that is given")
     p.add_argument("--genome", default="./resources/hg19.fa", help="--vcf: FASTA (chromatin.py:44)")
     p.add_argument("--weights", default="./resources/deepsea.beluga.pth", help="--vcf: Beluga state_dict (chromatin.py:103)")
-    p.add_argument("--dtype", default="f16", choices=["f16", "bf16"], help="--vcf: tensor-core operand type")
+    p.add_argument("--dtype", default="f16", choices=["f16", "bf16", "f16x3"], help="--vcf: tensor-core operand type")
     p.add_argument("--vcf_block", type=int, default=131072, help="--vcf: variants resident in HBM at a time")
     return p
 

@@ -99,6 +99,34 @@ def tss_descs(genome: PackedGenome, chroms, tss, strand, shifts, windowsize: int
     return d.reshape(-1)
 
 
+def variant_columns(genome: PackedGenome, chroms, pos, refs: list[str], alts: list[str]) -> dict:
+    """Whole-VCF column arrays for the in-library variant loop (include/beluga_b200.h: bx_chromatin_open): the global
+    packed-genome index of every variant's first base, allele lengths, and the allele codes with their offsets.
+    One vectorised pass; the descriptors themselves are built on the device (csrc/variants.cuh)."""
+    n = len(pos)
+    tab = AlleleTable(list(refs) + list(alts))
+    if tab.codes.size >= 2 ** 31:
+        raise ValueError("allele table exceeds 2 GiB")
+    coff = np.fromiter((genome.offsets[c] for c in chroms), dtype=np.int64, count=n)
+    return {"n": n,
+            "gpos": np.ascontiguousarray(coff + np.asarray(pos, dtype=np.int64) - 1),
+            "ref_len": np.ascontiguousarray(tab.lengths[:n], dtype=np.int32),
+            "alt_len": np.ascontiguousarray(tab.lengths[n:], dtype=np.int32),
+            "ref_aoff": np.ascontiguousarray(tab.offsets[:n], dtype=np.int32),
+            "alt_aoff": np.ascontiguousarray(tab.offsets[n:], dtype=np.int32),
+            "alleles": np.ascontiguousarray(tab.codes, dtype=np.uint8)}
+
+
+def variant_extent_invalid(genome: PackedGenome, cols: dict, maxshift: int) -> int:
+    """Index of the first variant whose fetches (chromatin.py:202-206: 2100 bp around pos + shift for every shift)
+    touch a genome character outside encodeSeqs' dictionary, or -1.  Conservative by at most the 50-bp crop margin:
+    callers fall back to the per-chunk host check, which follows the cropped windows exactly."""
+    if genome.invalid.size == 0 or cols["n"] == 0:
+        return -1
+    reach = maxshift + 1050
+    return genome.any_invalid(cols["gpos"] - reach, np.full(cols["n"], 2 * reach + 1, dtype=np.int64) + cols["ref_len"])
+
+
 def chromatin_window_descs(genome: PackedGenome, chroms, pos, refs: list[str], alts: list[str], shift: int):
     """All four windows per variant in the order the fused output kernels expect:
     (variant, {ref fwd, ref rc, alt fwd, alt rc}).  Returns (descs [4N], allele codes)."""

@@ -173,6 +173,55 @@ int bx_decay_score_variant(const float* x_dev, const double* dist_dev, const int
                             const int32_t* shifts_dev, const float* w_dev, const float* offset_dev, int n,
                             int n_shifts, int n_models, float* out_dev, void* stream);
 
+/* ---- The variant loop of chromatin.py:243-286 inside the library -------------------------------------------------
+ * The reference walks the VCF row by row in Python (chromatin.py:248-254: fetchSeqs per variant and shift, then
+ * encodeSeqs, two batched forwards, diff = alt - ref, one HDF5 file per shift).  Here the caller hands over whole-VCF
+ * column arrays once (HOST memory, one entry per variant after chromatin.py:240-241's filter):
+ *   gpos      global index, in the packed genome of bx_ctx_set_genome, of the variant's first base
+ *             (contig offset + POS - 1);
+ *   ref_len / alt_len    len(REF), len(ALT);  ref_aoff / alt_aoff   offsets of their codes in `alleles`
+ *             (0..3 = A,G,C,T, 4 = zero column: the values of chromatin.py:155-160's mydict).
+ * The library classifies every variant (substitutions of up to 16 bases -> delta mode; other variants whose shifted
+ * windows are substrings of one spliced sequence -> four full segments; the rest -> window by window with the
+ * reference's literal slice semantics), builds all descriptors on the device, and runs chunks of *chunk_variants_out
+ * consecutive variants.  FC2's epilogue writes each chunk's ref / alt / diff = alt - ref in chromatin.py:281-286's
+ * strand-stacked order: [S][2][m][2002] floats per tensor, S shifts in chromatin.py:243's order
+ * (0, -200 .. -maxshift, 200 .. maxshift), forward rows then reverse-complement rows, m variants of the chunk.
+ * Results are bit-identical to bx_forward_windows + bx_chromatin_outputs on the same variants.
+ * flags: BX_CHROM_NO_DELTA  substitutions run four full segments (same bits; for comparisons);
+ *        BX_CHROM_AVERAGE   outputs are [S][m][2002], averaged over the two strands as predict.py:186-190 reads them:
+ *                           ref = (fwd + rc) / 2, alt likewise, diff = ((alt_f - ref_f) + (alt_r - ref_r)) / 2;
+ *        BX_CHROM_WINDOWS   every variant window by window (the reference's schedule).
+ * One plan per context; bx_chromatin_open replaces an open plan. */
+#define BX_CHROM_NO_DELTA 1
+#define BX_CHROM_AVERAGE 2
+#define BX_CHROM_WINDOWS 4
+int bx_chromatin_open(bx_ctx* ctx, int64_t n, const int64_t* gpos, const int32_t* ref_len, const int32_t* alt_len,
+                      const int32_t* ref_aoff, const int32_t* alt_aoff, const uint8_t* alleles, int64_t n_alleles,
+                      int maxshift, int flags, int chunk_variants, int* n_chunks_out, int* chunk_variants_out);
+/* First variant, size and path counts of a chunk (any output pointer may be null). */
+int bx_chromatin_chunk_info(bx_ctx* ctx, int chunk, int64_t* v0, int* m, int* n_delta, int* n_full, int* n_window);
+/* Enqueue chunk `chunk`: compute on the library's stream, then copy the three tensors into the caller's HOST buffers
+ * (pinned for overlap) in the layout above.  Returns at once; chunks must be submitted in any order but at most two
+ * may be in flight: call bx_chromatin_wait(chunk) before submitting chunk + 2.  While chunk k's results travel to
+ * the host, chunk k + 1 computes. */
+int bx_chromatin_submit(bx_ctx* ctx, int chunk, float* ref_host, float* alt_host, float* diff_host);
+int bx_chromatin_wait(bx_ctx* ctx, int chunk);
+/* Same computation with the results left in HBM, enqueued on `stream`: row (si, strand t, variant v of the chunk) of
+ * each tensor goes to row  si * shift_stride_rows + t * strand_stride_rows + row0 + v  of the caller's device array
+ * (rows of 2002 floats; t = 0 with BX_CHROM_AVERAGE) — e.g. the operands of an NCCL gather, or the [S, n, 2002]
+ * tensors the decay transform reads. */
+int bx_chromatin_submit_device(bx_ctx* ctx, int chunk, float* ref_dev, float* alt_dev, float* diff_dev,
+                               int64_t shift_stride_rows, int64_t strand_stride_rows, int64_t row0, void* stream);
+int bx_chromatin_close(bx_ctx* ctx);
+/* Test hook: the device descriptor builders on HOST columns.  kind 0: four full segments per variant (ref fwd, ref
+ * rc, alt fwd, alt rc); kind 1: delta mode, out_host[0 .. 2n) the ref segments and out_host[2n .. 4n) the alt patches,
+ * *patch_row0 / *patch_len the patch geometry; kind 2: the four windows of each variant at `shift`.  out_host holds
+ * 4 n descriptors.  The host restatement in expecto_b200/windows.py is their oracle. */
+int bx_variant_descs_host(int kind, int64_t n, const int64_t* gpos, const int32_t* ref_len, const int32_t* alt_len,
+                          const int32_t* ref_aoff, const int32_t* alt_aoff, int maxshift, int shift, int* patch_row0,
+                          int* patch_len, bx_window_desc* out_host);
+
 /* ---- FASTA text resident in HBM -> packed genome (the arrays of bx_ctx_set_genome) --------------------------------
  * Replaces the genome side of the reference's input handling: pyfasta.Fasta('./resources/hg19.fa') builds a flat
  * index and serves string slices (chromatin.py:44,205; compute_expecto_features.py:31,108), and encodeSeqs maps each

@@ -144,3 +144,70 @@ def test_genome_is_packed_once_and_shared_through_the_cache(tmp_path):
     fa = str(tmp_path / "g.fa")
     synth.write_fasta(fa, synth.make_genome([("chr1", 50000), ("chr2", 30000)], seed=4), width=60)
     mp.spawn(_genome_worker, args=(2, _free_port(), fa), nprocs=2, join=True)
+
+
+class _FakeEngine:
+    """Stands in for BelugaEngine's variant-plan calls on CPU tensors: value = f(tensor, shift, strand, global variant)."""
+
+    def __init__(self, lo, chunk=5):
+        self.device, self.lo, self.chunk = torch.device("cpu"), lo, chunk
+
+    def chromatin_open(self, cols, maxshift, delta=True, chunk_variants=0):
+        self.n = cols["n"]
+        if chunk_variants:
+            self.chunk = min(self.chunk, chunk_variants)
+        return (self.n + self.chunk - 1) // self.chunk, self.chunk
+
+    def chromatin_chunk_info(self, k):
+        return {"v0": k * self.chunk, "m": min(self.chunk, self.n - k * self.chunk), "delta": 0, "full": 0, "window": 0}
+
+    def chromatin_submit_device(self, k, ref, alt, diff, shift_stride, strand_stride, row0):
+        info = self.chromatin_chunk_info(k)
+        for j, t in enumerate((ref, alt, diff)):
+            for si in range(3):
+                for strand in range(2):
+                    for v in range(info["m"]):
+                        t[si * shift_stride + strand * strand_stride + row0 + v] = _fake_value(j, si, strand, self.lo + info["v0"] + v)
+
+    def chromatin_close(self):
+        pass
+
+
+def _fake_value(j, si, strand, g):
+    return float(1000 * j + 100 * si + 10 * strand) + g / 64.0
+
+
+def _gather_worker(rank, world, port, n, tmp):
+    from expecto_b200 import chromatin
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    shard.init_distributed("gloo")
+    lo, hi = shard.shard_range(n, rank, world)
+    eng = _FakeEngine(lo, chunk=5 if rank == 0 else 4)      # ranks must settle on the smaller chunk size
+    got = {s: {k: np.full((2 * n, F), np.nan, np.float32) for k in ("ref", "alt", "diff")} for s in (0, -200, 200)}
+    sinks = None
+    if rank == 0:
+        def make(s):
+            def sink(name, row0, arr):
+                got[s][name][row0:row0 + len(arr)] = arr
+            return sink
+        sinks = {s: make(s) for s in got}
+    info = chromatin.predict_all_shifts_gathered(eng, {"n": hi - lo}, 200, n, sinks)
+    assert info["chunk_variants"] == 4
+    if rank == 0:
+        for si, s in enumerate((0, -200, 200)):
+            for j, name in enumerate(("ref", "alt", "diff")):
+                for strand in range(2):
+                    want = np.array([_fake_value(j, si, strand, g) for g in range(n)], np.float32)
+                    assert np.array_equal(got[s][name][strand * n:(strand + 1) * n, 0], want), (s, name, strand)
+                    assert np.array_equal(got[s][name][strand * n:(strand + 1) * n, F - 1], want)
+    shard.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [23, 8, 1])
+def test_streaming_gather_places_every_rank_chunk_in_global_row_order(tmp_path, n):
+    """predict_all_shifts_gathered's host logic with world_size 2 over gloo: uneven shards (one rank may even be
+    empty), different chunk sizes on the ranks, partial last chunks, forward rows at g and reverse-complement rows at
+    n + g of the whole job (chromatin.py:281-286's layout)."""
+    mp.spawn(_gather_worker, args=(2, _free_port(), n, str(tmp_path)), nprocs=2, join=True)
