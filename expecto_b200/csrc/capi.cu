@@ -192,7 +192,7 @@ static size_t act_width(const bx_ctx* c, int i) { return act_cols(i) * act_mul(c
 
 // ------------------------------------------------------------------ GEMM launch
 // a_cols / b_cols: physical row widths (elements) of the A and B matrices ([hi | lo] pairs in split-operand mode).
-template <typename T, int TAPS, int BN, int CG, int EPI, int A_MODE = 0, int SPLIT_OUT = 0>
+template <typename T, int TAPS, int BN, int CG, int EPI, int A_MODE = 0, int SPLIT_OUT = 0, int PARTS = 1>
 static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64_t a_cols, const void* b,
                          uint64_t b_rows, uint64_t b_cols, GemmParams p, cudaStream_t st,
                          const EncParams& enc = EncParams()) {
@@ -201,9 +201,10 @@ static int launch_gemm_t(const bx_ctx* c, const void* a, uint64_t a_rows, uint64
   if (int r = make_tmap(&tmB, c->dtype, b, b_rows, b_cols, b_cols, Cfg::B_ROWS)) return r;
   if (A_MODE != 0) tmA = tmB;  // unused: the producer warp builds the A tile in shared memory
   else if (int r = make_tmap(&tmA, c->dtype, a, a_rows, a_cols, a_cols, Cfg::A_ROWS)) return r;
-  if (p.parts < 1) { p.parts = 1; }
+  if (p.parts < 1) p.parts = 1;
+  if (p.parts != PARTS) return fail(BX_E_STATE, "kernel instance with %d operand parts launched for %d", PARTS, p.parts);
   if (p.a_grp < 1) { p.a_grp = 1 << 30; p.a_grp_stride = 0; }
-  auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI, A_MODE, SPLIT_OUT>;
+  auto kern = gemm_tc_kernel<T, TAPS, BN, CG, EPI, A_MODE, SPLIT_OUT, PARTS>;
   // function attributes are per device: one flag per device, so contexts on several GPUs of one process all get it
   static std::atomic<bool> attr_set[kMaxDevices];
   if (c->device < 0 || c->device >= kMaxDevices) return fail(BX_E_ARG, "device index %d out of range", c->device);
@@ -245,7 +246,7 @@ static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void
                           uint64_t a_cols, const void* b, uint64_t b_rows, uint64_t b_cols, const GemmParams& p,
                           bool split_out, cudaStream_t st) {
 #define BX_CASE(TP, N, E) \
-  if (taps == TP && bn == N && epi == E && !split_out) \
+  if (taps == TP && bn == N && epi == E && !split_out && p.parts <= 1) \
     return launch_gemm_t<T, TP, N, CG, E>(c, a, a_rows, a_cols, b, b_rows, b_cols, p, st)
   BX_CASE(1, 160, EPI_BIAS_RELU);
   BX_CASE(8, 160, EPI_POOL4_BIAS_RELU);
@@ -258,10 +259,17 @@ static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void
   BX_CASE(1, 256, EPI_CHROMATIN);
 #undef BX_CASE
   if constexpr (std::is_same<T, __half>::value) {  // split-operand mode exists for fp16 operands only
+    // split-operand instances: conv layers read and write (hi, lo) pairs, the dense layers read them
 #define BX_CASE(TP, N, E) \
-  if (taps == TP && bn == N && epi == E && split_out) \
-    return launch_gemm_t<T, TP, N, CG, E, 0, 1>(c, a, a_rows, a_cols, b, b_rows, b_cols, p, st)
-    BX_CASE(1, 160, EPI_BIAS_RELU);
+  if (taps == TP && bn == N && epi == E && split_out && p.parts == 3) \
+    return launch_gemm_t<T, TP, N, CG, E, 0, 1, 3>(c, a, a_rows, a_cols, b, b_rows, b_cols, p, st)
+#define BX_CASE_FC(E) \
+  if (taps == 1 && bn == 256 && epi == E && !split_out && p.parts == 3) \
+    return launch_gemm_t<T, 1, 256, CG, E, 0, 0, 3>(c, a, a_rows, a_cols, b, b_rows, b_cols, p, st)
+    BX_CASE_FC(EPI_PARTIAL_F32);
+    BX_CASE_FC(EPI_BIAS_SIGMOID);
+    BX_CASE_FC(EPI_CHROMATIN);
+#undef BX_CASE_FC
     BX_CASE(8, 160, EPI_POOL4_BIAS_RELU);
     BX_CASE(8, 240, EPI_BIAS_RELU);
     BX_CASE(8, 240, EPI_POOL4_BIAS_RELU);
@@ -269,7 +277,8 @@ static int launch_gemm_tc(const bx_ctx* c, int taps, int bn, int epi, const void
     BX_CASE(8, 160, EPI_BIAS_RELU);
 #undef BX_CASE
   }
-  return fail(BX_E_ARG, "no kernel instance for taps=%d block_n=%d epi=%d split_out=%d", taps, bn, epi, (int)split_out);
+  return fail(BX_E_ARG, "no kernel instance for taps=%d block_n=%d epi=%d split_out=%d parts=%d", taps, bn, epi,
+              (int)split_out, p.parts);
 }
 
 static int launch_gemm(const bx_ctx* c, int taps, int bn, int epi, const void* a, uint64_t a_rows, uint64_t a_cols,
@@ -555,9 +564,7 @@ int bx_ctx_create(int device, int dtype, int cta_group, int capacity_windows, bx
   c->device = device;
   c->dtype = dtype == BX_DTYPE_F16X3 ? BX_DTYPE_F16 : dtype;
   if (dtype == BX_DTYPE_F16X3) {
-    // BX_SPLIT_MASK (experiments): bit i = layer i on split operands; default every layer
-    const unsigned mask = getenv("BX_SPLIT_MASK") ? (unsigned)strtoul(getenv("BX_SPLIT_MASK"), nullptr, 0) : 0xFFu;
-    for (int i = 0; i < 8; ++i) c->split_in[i] = (mask >> i) & 1u;
+    for (int i = 0; i < 8; ++i) c->split_in[i] = true;   // every layer (the kernel instances exist for all-or-nothing)
     c->split_any = true;
   }
   c->cg = cta_group;

@@ -181,11 +181,14 @@ struct RingState {
   }
 };
 
-template <typename T, int TAPS, int BLOCK_N, int CG, int EPI, int A_MODE = 0, int SPLIT_OUT = 0>
+// PARTS: 1 = plain operands; 3 = split operands (compile-time so that the plain instances keep the exact loop
+// structure they were tuned with: FC1's producer / issuer loops are sensitive to a few instructions per K-block).
+template <typename T, int TAPS, int BLOCK_N, int CG, int EPI, int A_MODE = 0, int SPLIT_OUT = 0, int PARTS = 1>
 __global__ void __launch_bounds__(192, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const GemmParams p, const EncParams enc) {
   static_assert(A_MODE == 0 || TAPS == 1, "in-kernel operand generation is the conv1 (im2col, one K block) form");
+  static_assert(PARTS == 1 || (PARTS == 3 && A_MODE == 0), "split operands: three parts, TMA-loaded A");
   using Cfg = GemmCfg<TAPS, BLOCK_N, CG>;
   constexpr int SA = Cfg::SA, SB = Cfg::SB, NBUF = Cfg::NBUF;
   constexpr int FMT = sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
@@ -296,6 +299,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
       const int row0 = mt * 128 * CG + (int)rank * 128;
       const int ncol0 = nc * BLOCK_N + (int)rank * Cfg::B_ROWS;
+      // A column of logical K-block kb, kept incrementally (no division in the loop): groups of a_grp K-blocks are
+      // a_grp_stride elements apart
+      int a_in_grp = 0, a_col0 = 0;
+      if constexpr (PARTS > 1) {
+        a_in_grp = kb0 % p.a_grp;
+        a_col0 = (kb0 / p.a_grp) * p.a_grp_stride + a_in_grp * 64;
+      }
       for (int kb = kb0; kb < kb1; ++kb) {
         if constexpr (A_MODE != 0) {
           if (nc == 0) {
@@ -338,13 +348,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             ra.advance<SA>();
           }
         }
-        const int a_col0 = (kb / p.a_grp) * p.a_grp_stride + (kb % p.a_grp) * 64;
-#pragma unroll 1
-        for (int part = 0; part < p.parts; ++part) {
+#pragma unroll
+        for (int part = 0; part < PARTS; ++part) {
         if constexpr (A_MODE == 0) {
           if (part != 1) {  // part 1 (Ah x Wl) reuses the A stage of part 0
           mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 1);
-          const int a_col = a_col0 + (part == 2 ? p.a_lo_off : 0);
+          const int a_col = (PARTS == 1) ? kb * 64 : a_col0 + (part == 2 ? p.a_lo_off : 0);
           if (p.debug_flags & 2) {
             if (elect_one() && rank == 0) mbar_arrive_local(fullA(ra.idx));
           } else if (elect_one()) {
@@ -360,7 +369,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           ra.advance<SA>();
           }
         }
-        const int b_col = kb * 64 + (part == 1 ? p.b_lo_off : 0);
+        const int b_col = kb * 64 + ((PARTS > 1 && part == 1) ? p.b_lo_off : 0);
 #pragma unroll 1
         for (int t = 0; t < TAPS; t += Cfg::TPS) {
           mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 2);
@@ -386,6 +395,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           ++b_fills;
         }
         }  // part
+        if constexpr (PARTS > 1) {
+          if (++a_in_grp == p.a_grp) { a_in_grp = 0; a_col0 += p.a_grp_stride - (p.a_grp - 1) * 64; }
+          else a_col0 += 64;
+        }
       }
     }
   } else if (warp == 1) {
@@ -402,8 +415,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t accum = 0;
         for (int kb = kb0; kb < kb1; ++kb) {
           const int kcount = min(4, (p.k_valid - kb * 64 + 15) >> 4);
-#pragma unroll 1
-          for (int part = 0; part < p.parts; ++part) {
+#pragma unroll
+          for (int part = 0; part < PARTS; ++part) {
           if ((A_MODE == 0 && part != 1) || (A_MODE != 0 && nc == 0)) mbar_wait(fullA(ra.idx), ra.phase, 4);
           const uint32_t a_lo = sw128_desc_lo(sA + ra.idx * Cfg::A_BYTES);
 #pragma unroll 1
@@ -439,7 +452,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           // release the A stage after its last use: split mode keeps Ah for parts 0 and 1; A_MODE: the generated
           // tile serves every N chunk
-          if ((A_MODE == 0 && (p.parts == 1 || part >= 1)) || (A_MODE != 0 && nc == p.n_chunks - 1)) {
+          if ((A_MODE == 0 && (PARTS == 1 || part >= 1)) || (A_MODE != 0 && nc == p.n_chunks - 1)) {
             if (elect_one()) umma_commit<CG>(emptyA(ra.idx));
             __syncwarp();
             ra.advance<SA>();
