@@ -272,7 +272,32 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
             "ncu capture r01 (profiles/r01_ncu_transform_launches.csv), static: not measured in this run"
     except Exception:
         out["fixed"]["traffic"] = out["variant"]["traffic"] = None
-    del x, res
+    del res
+    # ---- transform fused with gblinear scoring (predict.py:120-160) as one tcgen05 GEMM: HBM-bound on the x read
+    from expecto_b200.transform import ScoreModels, decay_score_variant
+    m = 218                                    # resources/modellist
+    rng = np.random.default_rng(5)
+    models = ScoreModels((rng.standard_normal((m, 20020)) * 0.01).astype(np.float32), rng.standard_normal(m).astype(np.float32), dev)
+    models.prepared()
+    # four full waves of 74 CTA pairs x 256 variants
+    del x
+    n = 74 * 256 * 4
+    x = torch.rand((9, n, 2002), dtype=torch.float32, device=dev)
+    dist_d = torch.from_numpy(np.random.default_rng(1).integers(-40000, 40000, size=n).astype(np.float64)).to(dev)
+    strand_d = torch.from_numpy(np.where(np.arange(n) % 2 == 0, 1, -1).astype(np.int8)).to(dev)
+    t = timed(lambda: decay_score_variant(x, dist_d, strand_d, models, shifts=shifts_d))
+    b = n * (9 * 2002 * 4 + m * 4 + 9)
+    flop = 2.0 * n * 20020 * m
+    out["score"] = {"variants": n, "models": m, "bytes_per_variant": b // n, "ms": t * 1e3, "achieved": b / t / 1e9,
+                    "unit": "GB/s", "peak": peaks["hbm_gbs"], "frac": b / t / 1e9 / peaks["hbm_gbs"],
+                    "variants_per_s": n / t, "kernel": "score_tc_kernel",
+                    "algorithmic_tflops": flop / t / 1e12, "executed_tflops": 3 * flop * (20160 / 20020) * (224 / m) / t / 1e12,
+                    "note": "features never leave shared memory; every product is three fp16 MMAs (hi/lo split operands)"}
+    t_simt = timed(lambda: decay_score_variant(x[:, :2048].contiguous(), dist_d[:2048], strand_d[:2048], models,
+                                               shifts=shifts_d, tensor_cores=False))
+    out["score"]["simt_kernel_ms_per_variant"] = t_simt * 1e3 / 2048
+    out["score"]["speedup_vs_simt_kernel"] = (t_simt / 2048) / (t / n)
+    del x
     if cpu:
         out["fixed"]["cpu_baseline"], out["variant"]["cpu_baseline"] = transform_cpu_baselines()
     return out

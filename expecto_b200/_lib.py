@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libbeluga_b200.so")
 SRC = os.path.join(_HERE, "csrc", "capi.cu")
-SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh", "encode.cuh", "genome_pack.cuh", "variants.cuh")] + [
+SRC_DEPS = [os.path.join(_HERE, "csrc", f) for f in ("capi.cu", "gemm_tc.cuh", "ptx.cuh", "kernels_misc.cuh", "encode.cuh", "genome_pack.cuh", "variants.cuh", "score_tc.cuh")] + [
     os.path.join(ROOT, "include", "beluga_b200.h")
 ]
 
@@ -53,6 +53,7 @@ EXPORTS = [
     "bx_forward_segments_delta", "bx_fasta_blocks", "bx_fasta_find_headers", "bx_fasta_count", "bx_fasta_pack",
     "bx_chromatin_open", "bx_chromatin_chunk_info", "bx_chromatin_submit", "bx_chromatin_wait",
     "bx_chromatin_submit_device", "bx_chromatin_close", "bx_variant_descs_host",
+    "bx_score_weights_bytes", "bx_score_prepare_weights", "bx_decay_score_variant_tc",
 ]
 CHROM_NO_DELTA, CHROM_AVERAGE, CHROM_WINDOWS = 1, 2, 4
 NSTAGES = 10
@@ -135,10 +136,14 @@ def lib() -> C.CDLL:
     L.bx_chromatin_submit_device.argtypes = [vp, i32, vp, vp, vp, i64, i64, i64, vp]
     L.bx_chromatin_close.argtypes = [vp]
     L.bx_variant_descs_host.argtypes = [i32, i64, vp, vp, vp, vp, vp, i32, i32, ip, ip, vp]
+    L.bx_score_weights_bytes.argtypes = [i32]
+    L.bx_score_weights_bytes.restype = i64
+    L.bx_score_prepare_weights.argtypes = [vp, i32, vp, vp]
+    L.bx_decay_score_variant_tc.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
     L.bx_ctx_profile.argtypes = [vp, i32]
     L.bx_ctx_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), i32]
     for name in EXPORTS:
-        if name not in ("bx_last_error", "bx_launch_count", "bx_fasta_blocks"):
+        if name not in ("bx_last_error", "bx_launch_count", "bx_fasta_blocks", "bx_score_weights_bytes"):
             getattr(L, name).restype = i32
     _lib = L
     return L

@@ -17,6 +17,7 @@
 #include "kernels_misc.cuh"
 #include "genome_pack.cuh"
 #include "variants.cuh"
+#include "score_tc.cuh"
 #include <cub/device/device_scan.cuh>
 
 using namespace bx;
@@ -1037,6 +1038,88 @@ int bx_decay_score_variant(const float* x_dev, const double* dist_dev, const int
                                                                         offset_dev, n, n_shifts, n_models, out_dev);
   g_launches++;
   CK(cudaGetLastError());
+  return 0;
+}
+
+// ---- transform + scoring as one tcgen05 GEMM (score_tc.cuh)
+static int check_device();
+static int score_group_pad(int m) { return (std::min(m, 256) + 15) / 16 * 16; }
+
+int64_t bx_score_weights_bytes(int n_models) {
+  if (n_models < 1) return 0;
+  int64_t rows = 0;
+  for (int m0 = 0; m0 < n_models; m0 += 256) rows += score_group_pad(n_models - m0);
+  return rows * 2 * (int64_t)kScK * (int64_t)sizeof(__half);
+}
+
+int bx_score_prepare_weights(const float* w_dev, int n_models, void* wp_dev, void* stream) {
+  if (n_models < 1 || !w_dev || !wp_dev) return fail(BX_E_ARG, "invalid arguments");
+  if (int r = check_device()) return r;
+  __half* out = reinterpret_cast<__half*>(wp_dev);
+  for (int m0 = 0; m0 < n_models; m0 += 256) {
+    const int m = std::min(256, n_models - m0), n_pad = score_group_pad(m);
+    const size_t total = (size_t)n_pad * kScK;
+    score_prep_weights_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        w_dev + (size_t)m0 * 20020, m, n_pad, out);
+    g_launches++;
+    CK(cudaGetLastError());
+    out += (size_t)n_pad * 2 * kScK;
+  }
+  return 0;
+}
+
+int bx_decay_score_variant_tc(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+                              const int32_t* shifts_dev, const void* wp_dev, const float* offset_dev, int n,
+                              int n_shifts, int n_models, float* out_dev, void* stream) {
+  if (n < 0 || n_models < 1) return fail(BX_E_ARG, "invalid arguments");
+  if (n_shifts != kScShifts)
+    return fail(BX_E_ARG, "the tensor-core scoring kernel is built for %d shifts (--maxshift 800); got %d", kScShifts, n_shifts);
+  if (n == 0) return 0;
+  if (!x_dev || !dist_dev || !strand_dev || !shifts_dev || !wp_dev || !offset_dev || !out_dev)
+    return fail(BX_E_ARG, "invalid arguments");
+  if (int r = check_device()) return r;
+  if (int r = load_driver_entry()) return r;
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(BX_E_ARG, "device index %d out of range", dev);
+  int sms = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const __half* wp = reinterpret_cast<const __half*>(wp_dev);
+  for (int m0 = 0; m0 < n_models; m0 += 256) {
+    const int m = std::min(256, n_models - m0), n_pad = score_group_pad(m);
+    ScoreParams p = {};
+    p.x = x_dev; p.dist = dist_dev; p.strand = strand_dev; p.shifts = shifts_dev;
+    p.offset = offset_dev + m0;
+    p.out = out_dev + m0;
+    p.ld_out = n_models;
+    p.n = n; p.m = m; p.n_pad = n_pad;
+    p.tiles = (n + 255) / 256;
+    p.idesc = make_idesc_f16(0, 256, n_pad);
+    p.sb_stages = 3;
+    const size_t smem = (size_t)(2 + 2) * 2 * kScATile + (size_t)p.sb_stages * 2 * (n_pad / 2) * 128 + 256 + 1024;
+    CUtensorMap tmW;
+    if (int r = make_tmap(&tmW, BX_DTYPE_F16, wp, (uint64_t)n_pad, (uint64_t)2 * kScK, (uint64_t)2 * kScK, (uint32_t)(n_pad / 2)))
+      return r;
+    static std::atomic<size_t> attr_smem[kMaxDevices];
+    if (attr_smem[dev].load(std::memory_order_acquire) < smem) {
+      CK(cudaFuncSetAttribute(score_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_smem[dev].store(smem, std::memory_order_release);
+    }
+    const int clusters = std::max(1, std::min(p.tiles, sms / 2));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(clusters * 2);
+    cfg.blockDim = dim3(kScThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, score_tc_kernel, tmW, p));
+    g_launches++;
+    wp += (size_t)n_pad * 2 * kScK;
+  }
   return 0;
 }
 

@@ -1,0 +1,329 @@
+// Per-variant decay transform fused with gblinear scoring as ONE tcgen05 GEMM (reference:
+// compute_effects, predict.py:87-160 — float64 [n, 20020] feature matrices built from np.tile / np.repeat temporaries,
+// then xgboost Booster.predict = base_score + bias + w . x per model).
+//
+//   out[n, m] = offset[m] + sum_{k<10} sum_{f<2002} feat[n, k, f] * W[m, k*2002 + f],
+//   feat[n, k, f] = sum_{j<9} w[n, j, k] * x[j, n, f]          (w from the variant's distance and strand)
+//
+// The [256 variants x 64] feature tiles are generated in shared memory straight from the nine shift rows of x and
+// never exist in HBM: x is read once (72 KB per variant and tensor — the kernel's HBM roofline), the weight matrix
+// streams from L2 (18 MB for 224 models).  The GEMM's K axis is a permutation of (k, f) chosen so that what one
+// thread computes from one 32-byte piece of each shift row is one swizzled row of one operand stage: per
+// "super-block" of 32 features there are five K-blocks of 64 columns,
+//   K-block c < 4 :  column k*8 + i          = feature 32*sb + 8*c + i,  basis k < 8
+//   K-block 4     :  column (k-8)*32 + 8*c+i = feature 32*sb + 8*c + i,  basis k = 8, 9
+// and the model weights are permuted the same way once (score_prep_weights_kernel).  Features and weights are fp16
+// (hi, lo) pairs and every product is Ah*Wh + Ah*Wl + Al*Wh in fp32 (three MMAs per K step): REF and ALT scores keep
+// fp32-level accuracy, which SED = ALT - REF (predict.py:264) needs because the two scores differ in their 4th digit.
+// The tensor core's fp32 accumulation truncates, so a chain of n MMAs into one accumulator loses ~n * 2^-24 of its
+// magnitude, always towards zero (measured: 7.9e-5 relative with all 3780 MMAs of a tile in one accumulator).  The two
+// correction products therefore go to a second TMEM accumulator — 2^-11 the magnitude, so their truncation is
+// negligible — and the epilogue adds the two in fp32: the main chain is 1260 MMAs long instead of 3780.
+//
+// CTA pair (cta_group::2): M = 256 variants (128 per CTA), N = models padded to a multiple of 16 (each CTA stages half
+// of the weight rows).  Warps 0-7: feature generators (four lanes per variant row, each lane one feature pair of every
+// 8-feature chunk and all ten bases: coalesced 32-byte row pieces in, 4-byte swizzled stores out; a first version with
+// one thread per row was bound by L1 wavefronts — 32 sectors per load instruction — at 5.9 us per K-block) and, at
+// the end of a tile, the epilogue; warp 8: TMA producer of the weight tiles; warp 9: MMA issuer (leader CTA) and TMEM
+// allocator.
+#pragma once
+#include "gemm_tc.cuh"
+
+namespace bx {
+
+constexpr int kScSuper = 63;                 // ceil(2002 / 32) feature super-blocks
+constexpr int kScKBlocks = kScSuper * 5;     // 315 K-blocks of 64 columns
+constexpr int kScK = kScKBlocks * 64;        // 20160 permuted K columns (2016 features x 10 bases)
+constexpr int kScShifts = 9;                 // chromatin.py:243 with the default --maxshift 800
+constexpr int kScATile = 128 * 128;          // one [128 x 64] fp16 operand tile
+constexpr int kScThreads = 320;
+
+struct ScoreParams {
+  const float* x;          // [9, n, 2002]
+  const double* dist;      // [n] variant - TSS (predict.py:241)
+  const int8_t* strand;    // [n] +1 / -1
+  const int32_t* shifts;   // [9]
+  const float* offset;     // [m] base_score + bias
+  float* out;              // [n, ld_out]: this launch writes columns [0, m)
+  int n, m, n_pad, tiles;  // m models in this launch, n_pad: padded to a multiple of 16 (<= 256); tiles = ceil(n / 256)
+  int ld_out;
+  uint32_t idesc;
+  int sb_stages;           // weight-ring depth (2 or 3, by shared-memory budget)
+};
+
+// Permuted K column -> (basis k, feature f); f >= 2002 is padding.
+__host__ __device__ inline void score_col_to_kf(int col, int& k, int& f) {
+  const int kb = col >> 6, c = kb % 5, sb = kb / 5, w = col & 63;
+  if (c < 4) { k = w >> 3; f = 32 * sb + 8 * c + (w & 7); }
+  else { k = 8 + (w >> 5); f = 32 * sb + (w & 31); }
+}
+
+// Model weights fp32 [m, 20020] -> fp16 pairs [n_pad, 2 * kScK]: high parts in columns [0, kScK), residuals after.
+__global__ void score_prep_weights_kernel(const float* __restrict__ w, int m, int n_pad, __half* __restrict__ out) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (size_t)n_pad * kScK) return;
+  const int row = (int)(idx / kScK), col = (int)(idx % kScK);
+  int k, f;
+  score_col_to_kf(col, k, f);
+  const float v = (row < m && f < 2002) ? w[(size_t)row * 20020 + (size_t)k * 2002 + f] : 0.f;
+  const __half h = __float2half_rn(v);
+  out[(size_t)row * 2 * kScK + col] = h;
+  out[(size_t)row * 2 * kScK + kScK + col] = __float2half_rn(v - __half2float(h));
+}
+
+// Memory behaviour (profiles/r02_ncu_score_tc.txt): a tile walks 256 variants x 9 shift rows in parallel, 32 bytes of
+// each per chunk, and the rows are 8008 bytes apart — not a multiple of the 32-byte sector — so DRAM sees scattered
+// sector reads (1.5 TB/s, long-scoreboard stalls) and most pieces straddle two sectors.  L2::128B / L2::256B fill hints
+// on the loads made it slower (4.6 / 5.2 ms against 3.9 ms per 75,776 variants); an L2 prefetch of each row's next
+// 128 bytes one super-block ahead plus a one-chunk register double buffer is the best of what was tried.  The remedy
+// is a tile-major layout of x written by the producing epilogue (what comes next).
+__global__ void __launch_bounds__(kScThreads, 1)
+score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
+  constexpr int SA = 2, SK = 2;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t b_half = (uint32_t)(p.n_pad / 2) * 128u;          // one weight tile (hi or lo) of this CTA
+  const uint32_t sA = base;                                        // SA x (hi, lo)
+  const uint32_t sK = sA + SA * 2 * kScATile;                      // SK x (hi, lo): the k = 8, 9 K-blocks
+  const uint32_t sB = sK + SK * 2 * kScATile;                      // sb_stages x (hi, lo)
+  const uint32_t bars = sB + (uint32_t)p.sb_stages * 2 * b_half;
+  auto fullA = [&](uint32_t i) { return bars + 8u * i; };
+  auto emptyA = [&](uint32_t i) { return bars + 8u * (2 + i); };
+  auto fullK = [&](uint32_t i) { return bars + 8u * (4 + i); };
+  auto emptyK = [&](uint32_t i) { return bars + 8u * (6 + i); };
+  auto fullB = [&](uint32_t i) { return bars + 8u * (8 + i); };
+  auto emptyB = [&](uint32_t i) { return bars + 8u * (12 + i); };
+  const uint32_t tfull = bars + 8u * 16, tempty = bars + 8u * 17, tmem_slot = bars + 8u * 18;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int num_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
+
+  if (warp == 8 && lane == 0) {
+    prefetch_tensormap(&tmW);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(fullA(i), 16); mbar_init(emptyA(i), 1);     // 8 generator warps in each CTA of the pair
+      mbar_init(fullK(i), 16); mbar_init(emptyK(i), 1);
+    }
+    for (int i = 0; i < 4; ++i) { mbar_init(fullB(i), 1); mbar_init(emptyB(i), 1); }
+    mbar_init(tfull, 1);
+    mbar_init(tempty, 16);
+    fence_barrier_init();
+  }
+  if (warp == 9) tmem_alloc<2>(tmem_slot, 512);   // columns [0, n_pad): Ah*Wh; [256, 256 + n_pad): Ah*Wl + Al*Wh
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  if (warp < 8) {
+    // ------------------------------------------------------------------ feature generators + epilogue
+    // Four lanes share a variant row: lane (rw, sub) of warp w handles rows w*16 + {0, 8} + rw and, in every chunk of
+    // eight features, the feature pair 2*sub, 2*sub + 1 — so a warp's loads cover eight rows x 32 contiguous bytes
+    // (full sectors), and the four lanes' 4-byte stores assemble each 16-byte swizzled piece of the operand row.
+    const int sub = lane & 3, rw = lane >> 2;
+    RingState ra, rk;
+    uint32_t tphase = 0;
+    for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      // y = exp(-0.01 * floor(|pos| / 200)) per shift (fp64 like numpy, predict.py:87-109) and which side of the TSS
+      // each shift falls on, for this lane's two rows.  The five decay rates 0.01, 0.02, 0.05, 0.1, 0.2 are the powers
+      // y, y^2, y^5, y^10, y^20, formed by five multiplications where they are used: keeping all 90 weights of the two
+      // rows in registers left no room to hold the next chunk's loads, and the kernel then ran at the load latency.
+      float y[2][kScShifts];
+      uint32_t negm[2], posm[2];
+      const float* xrow[2];
+      bool valid[2];
+#pragma unroll
+      for (int ps = 0; ps < 2; ++ps) {
+        const long long row = (long long)t * 256 + rank * 128 + warp * 16 + ps * 8 + rw;
+        valid[ps] = row < p.n;
+        xrow[ps] = p.x + (size_t)(valid[ps] ? row : 0) * 2002;
+        const double d = valid[ps] ? p.dist[row] : 0.0;
+        const double sgn = (valid[ps] && p.strand[row] > 0) ? 1.0 : -1.0;
+        negm[ps] = posm[ps] = 0;
+#pragma unroll
+        for (int j = 0; j < kScShifts; ++j) {
+          const double pos = d * sgn + (double)p.shifts[j] * sgn;
+          const double b = floor(fabs(pos / 200.0));
+          if (valid[ps] && pos <= 0.0) negm[ps] |= 1u << j;
+          if (valid[ps] && pos >= 0.0) posm[ps] |= 1u << j;
+          y[ps][j] = (float)exp(-0.01 * b);
+        }
+      }
+      const size_t shift_stride = (size_t)p.n * 2002;
+      auto load_chunk = [&](int f0, float2 (&xv)[2][kScShifts]) {
+#pragma unroll
+        for (int ps = 0; ps < 2; ++ps)
+#pragma unroll
+          for (int j = 0; j < kScShifts; ++j)
+            xv[ps][j] = (valid[ps] && f0 + 2 * sub < 2002)
+                            ? __ldg(reinterpret_cast<const float2*>(xrow[ps] + j * shift_stride + f0) + sub)
+                            : make_float2(0.f, 0.f);
+      };
+      auto prefetch_super = [&](int sb) {
+        if (32 * sb >= 2002) return;
+#pragma unroll
+        for (int ps = 0; ps < 2; ++ps)
+#pragma unroll
+          for (int j = 0; j < kScShifts; ++j)
+            if ((j & 3) == sub && valid[ps])
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(xrow[ps] + j * shift_stride + 32 * sb));
+      };
+      prefetch_super(0);
+      prefetch_super(1);
+      float2 xn[2][kScShifts];
+      load_chunk(0, xn);
+      for (int sb = 0; sb < kScSuper; ++sb) {
+        prefetch_super(sb + 2);
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          float2 xv[2][kScShifts];
+#pragma unroll
+          for (int ps = 0; ps < 2; ++ps)
+#pragma unroll
+            for (int j = 0; j < kScShifts; ++j) xv[ps][j] = xn[ps][j];
+          const int fnext = 32 * sb + 8 * c + 8;        // the next chunk's loads fly during this chunk's arithmetic
+          if (fnext < 32 * kScSuper) load_chunk(fnext, xn);
+          mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
+          if (c == 0) mbar_wait(emptyK(rk.idx), rk.phase ^ 1, 12);
+#pragma unroll
+          for (int ps = 0; ps < 2; ++ps) {
+            float2 acc[10];
+#pragma unroll
+            for (int k = 0; k < 10; ++k) acc[k] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < kScShifts; ++j) {
+              const bool ng = (negm[ps] >> j) & 1u, ps_ = (posm[ps] >> j) & 1u;
+              const float2 xm = ng ? xv[ps][j] : make_float2(0.f, 0.f);
+              const float2 xp = ps_ ? xv[ps][j] : make_float2(0.f, 0.f);
+              const float y1 = y[ps][j], y2 = y1 * y1, y4 = y2 * y2, y5 = y4 * y1, y10 = y5 * y5, y20 = y10 * y10;
+              const float e[5] = {y1, y2, y5, y10, y20};
+#pragma unroll
+              for (int q = 0; q < 5; ++q) {
+                acc[q].x = fmaf(e[q], xm.x, acc[q].x);
+                acc[q].y = fmaf(e[q], xm.y, acc[q].y);
+                acc[5 + q].x = fmaf(e[q], xp.x, acc[5 + q].x);
+                acc[5 + q].y = fmaf(e[q], xp.y, acc[5 + q].y);
+              }
+            }
+            const int r = warp * 16 + ps * 8 + rw;
+            const uint32_t swz = (uint32_t)(r & 7);
+            uint8_t* st = smem_raw + (sA - raw) + ra.idx * 2 * kScATile + r * 128 + sub * 4;
+            uint8_t* sk = smem_raw + (sK - raw) + rk.idx * 2 * kScATile + r * 128 + sub * 4;
+#pragma unroll
+            for (int k = 0; k < 10; ++k) {
+              uint32_t hi, lo;
+              split2<__half>(acc[k].x, acc[k].y, hi, lo);
+              // K-block 5*sb + c holds bases 0..7 (piece k); K-block 5*sb + 4 bases 8, 9 (piece (k - 8) * 4 + c)
+              uint8_t* dst = k < 8 ? st + (((uint32_t)k ^ swz) << 4) : sk + (((uint32_t)((k - 8) * 4 + c) ^ swz) << 4);
+              *reinterpret_cast<uint32_t*>(dst) = hi;
+              *reinterpret_cast<uint32_t*>(dst + kScATile) = lo;
+            }
+          }
+          fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive_remote(mapa(fullA(ra.idx), 0));
+            if (c == 3) mbar_arrive_remote(mapa(fullK(rk.idx), 0));
+          }
+          __syncwarp();
+          ra.advance<SA>();
+        }
+        rk.advance<SK>();
+      }
+      // ---- epilogue: TMEM -> + offset -> out[row, model]; warp handles its lane quarter and every other 16-column chunk
+      mbar_wait(tfull, tphase, 13);
+      tphase ^= 1;
+      tc_fence_after();
+      {
+        const int q = warp & 3;
+        const long long orow = (long long)t * 256 + rank * 128 + q * 32 + lane;
+        const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16);
+        for (int c16 = warp >> 2; c16 < p.n_pad / 16; c16 += 2) {
+          uint32_t v[16], u[16];
+          tmem_ld16(t0 + c16 * 16, v);
+          tmem_ld16(t0 + 256 + c16 * 16, u);
+          tmem_ld_wait();
+          if (orow < p.n) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int col = c16 * 16 + i;
+              if (col < p.m)
+                p.out[(size_t)orow * p.ld_out + col] = (__uint_as_float(v[i]) + __uint_as_float(u[i])) + __ldg(p.offset + col);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(mapa(tempty, 0));
+    }
+  } else if (warp == 8) {
+    // ------------------------------------------------------------------ weight tiles by TMA (both CTAs, own half of N)
+    RingState rb;
+    const int row0 = (int)rank * (p.n_pad / 2);
+    for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      for (int kb = 0; kb < kScKBlocks; ++kb) {
+        mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 14);
+        if (elect_one()) {
+          if (rank == 0) mbar_arrive_expect_tx(fullB(rb.idx), 4 * b_half);
+          const uint32_t bar = mapa(fullB(rb.idx), 0);
+          const uint32_t dst = sB + rb.idx * 2 * b_half;
+          tma_load_2d_pair(dst, &tmW, bar, kb * 64, row0);
+          tma_load_2d_pair(dst + b_half, &tmW, bar, kScK + kb * 64, row0);
+        }
+        __syncwarp();
+        if (++rb.idx == (uint32_t)p.sb_stages) { rb.idx = 0; rb.phase ^= 1; }
+      }
+    }
+  } else if (rank == 0) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA)
+    RingState ra, rk, rb;
+    uint32_t tphase = 0;
+    for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      mbar_wait(tempty, tphase ^ 1, 15);   // the previous tile's epilogue has read the accumulator
+      tphase ^= 1;
+      tc_fence_after();
+      uint32_t accum = 0;
+      for (int kb = 0; kb < kScKBlocks; ++kb) {
+        const bool k89 = (kb % 5) == 4;
+        uint32_t a_hi;
+        if (k89) { mbar_wait(fullK(rk.idx), rk.phase, 16); a_hi = sK + rk.idx * 2 * kScATile; }
+        else { mbar_wait(fullA(ra.idx), ra.phase, 17); a_hi = sA + ra.idx * 2 * kScATile; }
+        mbar_wait(fullB(rb.idx), rb.phase, 18);
+        tc_fence_after();
+        const uint32_t b_hi = sB + rb.idx * 2 * b_half;
+        if (elect_one()) {
+          const uint32_t ah = sw128_desc_lo(a_hi), al = sw128_desc_lo(a_hi + kScATile);
+          const uint32_t bh = sw128_desc_lo(b_hi), bl = sw128_desc_lo(b_hi + b_half);
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            umma_f16<2>(tmem_base, sw128_desc(ah + 2 * ks), sw128_desc(bh + 2 * ks), p.idesc, accum);
+            umma_f16<2>(tmem_base + 256, sw128_desc(ah + 2 * ks), sw128_desc(bl + 2 * ks), p.idesc, accum);
+            umma_f16<2>(tmem_base + 256, sw128_desc(al + 2 * ks), sw128_desc(bh + 2 * ks), p.idesc, 1u);
+            accum = 1;
+          }
+          umma_commit<2>(emptyB(rb.idx));
+          umma_commit<2>(k89 ? emptyK(rk.idx) : emptyA(ra.idx));
+        }
+        __syncwarp();
+        accum = 1;
+        if (++rb.idx == (uint32_t)p.sb_stages) { rb.idx = 0; rb.phase ^= 1; }
+        if (k89) rk.advance<SK>(); else ra.advance<SA>();
+      }
+      if (elect_one()) umma_commit<2>(tfull);
+      __syncwarp();
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc<2>(tmem_base, 512);
+  }
+}
+
+}  // namespace bx

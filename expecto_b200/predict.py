@@ -300,7 +300,7 @@ def run(args, engine=None, genome=None) -> dict:
     import torch
 
     from .gblinear import load_model
-    from .transform import decay_score_variant
+    from .transform import ScoreModels, decay_score_variant
 
     if not torch.cuda.is_available():
         raise RuntimeError("predict needs a CUDA device (B200); there is no CPU fallback")
@@ -357,6 +357,7 @@ def run(args, engine=None, genome=None) -> dict:
         raise IndexError(f"gene rows point at variant {int(idx.max())} but only {n_pred} were predicted "
                          "(rows filtered by chromatin.py:241 shift the two tables apart, predict.py:217)")
     shifts = shift_list(int(args.maxshift))
+    models = ScoreModels(W, offsets, dev)   # staged (and laid out for the tensor-core kernel) once
     scores = {k: np.empty((len(idx), len(paths)), dtype=np.float32) for k in ("ref", "alt")}
     for v0, v1, data in blocks:  # one block when reading files; --vcf computes --vcf_block variants at a time
         rows = np.flatnonzero((idx >= v0) & (idx < v1))   # idx is non-decreasing: a contiguous run of gene rows
@@ -366,7 +367,7 @@ def run(args, engine=None, genome=None) -> dict:
             sel = None if identity else torch.from_numpy(local).to(dev)
             for key in ("ref", "alt"):
                 x = data[key] if identity else data[key].index_select(1, sel)
-                scores[key][rows] = decay_score_variant(x, dist[rows], strand[rows], W, offsets, shifts=shifts).cpu().numpy()
+                scores[key][rows] = decay_score_variant(x, dist[rows], strand[rows], models, shifts=shifts).cpu().numpy()
         del data
         lap("chromatin_and_score_s" if args.vcf else "score_s")
     ref, alt = scores["ref"], scores["alt"]

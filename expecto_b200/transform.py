@@ -113,17 +113,53 @@ def decay_transform_variant(x: torch.Tensor, dist, strand, shifts=None, out: tor
     return out
 
 
-def decay_score_variant(x: torch.Tensor, dist, strand, weights, offsets, shifts=None) -> torch.Tensor:
-    """predict.py:123-160 fused (transform + gblinear scoring): ``weights`` [m,20020] (dropped columns = 0),
-    ``offsets`` [m] = base_score + bias -> fp32 [n,m] scores; the feature matrix is never materialised."""
+class ScoreModels:
+    """gblinear models staged once on the device for ``decay_score_variant``: fp32 weights [m, 20020] (columns dropped
+    by the keep mask = 0) for the SIMT kernel, and — prepared lazily — the tensor-core kernel's operand layout (fp16
+    (hi, lo) pairs, K axis permuted to the order the feature tiles are generated in; bx_score_prepare_weights)."""
+
+    def __init__(self, weights, offsets, device):
+        w = np.ascontiguousarray(np.asarray(weights, dtype=np.float32)).reshape(-1, N_BASIS * N_FEATURES)
+        off = np.ascontiguousarray(np.asarray(offsets, dtype=np.float32)).reshape(-1)
+        if off.size != w.shape[0]:
+            raise ValueError("one offset per model")
+        self.m = int(w.shape[0])
+        self.device = torch.device(device)
+        self.w = torch.from_numpy(w).to(self.device)
+        self.off = torch.from_numpy(off).to(self.device)
+        self._wp = None
+
+    def prepared(self) -> torch.Tensor:
+        if self._wp is None:
+            nbytes = int(lib().bx_score_weights_bytes(self.m))
+            self._wp = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            with torch.cuda.device(self.device):
+                check(lib().bx_score_prepare_weights(self.w.data_ptr(), self.m, self._wp.data_ptr(),
+                                                     torch.cuda.current_stream(self.device).cuda_stream))
+        return self._wp
+
+
+def decay_score_variant(x: torch.Tensor, dist, strand, weights, offsets=None, shifts=None,
+                        tensor_cores: bool | None = None) -> torch.Tensor:
+    """predict.py:123-160 fused (transform + gblinear scoring): ``weights`` [m,20020] (dropped columns = 0) with
+    ``offsets`` [m] = base_score + bias, or a ``ScoreModels`` staged once -> fp32 [n,m] scores; the feature matrix is
+    never materialised.  With the nine shifts of --maxshift 800 the contraction runs as one tcgen05 GEMM whose feature
+    tiles are generated in shared memory (bx_decay_score_variant_tc); other shift counts, or ``tensor_cores=False``,
+    use the SIMT kernel (bx_decay_score_variant)."""
     x, d, sg, sh, n, S = _variant_args(x, dist, strand, shifts)
-    w = torch.as_tensor(np.ascontiguousarray(np.asarray(weights, dtype=np.float32))).to(x.device).reshape(-1, N_BASIS * N_FEATURES)
-    m = w.shape[0]
-    off = torch.as_tensor(np.ascontiguousarray(np.asarray(offsets, dtype=np.float32)).reshape(-1)).to(x.device)
-    if off.numel() != m:
-        raise ValueError("one offset per model")
+    models = weights if isinstance(weights, ScoreModels) else ScoreModels(weights, offsets, x.device)
+    if models.device != x.device:
+        raise ValueError("models are staged on another device")
+    m = models.m
     out = torch.empty((n, m), dtype=torch.float32, device=x.device)
+    use_tc = (S == 9) if tensor_cores is None else bool(tensor_cores)
     with torch.cuda.device(x.device):
-        check(lib().bx_decay_score_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(), w.data_ptr(),
-                                           off.data_ptr(), n, S, m, out.data_ptr(), _stream(x)))
+        if use_tc:
+            check(lib().bx_decay_score_variant_tc(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(),
+                                                  models.prepared().data_ptr(), models.off.data_ptr(), n, S, m,
+                                                  out.data_ptr(), _stream(x)))
+        else:
+            check(lib().bx_decay_score_variant(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(),
+                                               models.w.data_ptr(), models.off.data_ptr(), n, S, m, out.data_ptr(),
+                                               _stream(x)))
     return out

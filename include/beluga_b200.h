@@ -222,6 +222,18 @@ int bx_variant_descs_host(int kind, int64_t n, const int64_t* gpos, const int32_
                           const int32_t* ref_aoff, const int32_t* alt_aoff, int maxshift, int shift, int* patch_row0,
                           int* patch_len, bx_window_desc* out_host);
 
+/* The same computation as bx_decay_score_variant as ONE tcgen05 GEMM ("[N', 20020] x [20020, 218]"
+ * with the features never leaving shared memory; reference predict.py:120-160).  The model weights are converted once
+ * to the kernel's operand layout — fp16 (hi, lo) pairs, K axis permuted to the order the feature tiles are generated
+ * in — with bx_score_prepare_weights into a caller-owned device buffer of bx_score_weights_bytes(n_models) bytes;
+ * bx_decay_score_variant_tc then takes that buffer.  n_shifts must be 9 (--maxshift 800); every product is
+ * Ah*Wh + Ah*Wl + Al*Wh with fp32 accumulation, so scores agree with the float64 reference to ~1e-6 relative. */
+int64_t bx_score_weights_bytes(int n_models);
+int bx_score_prepare_weights(const float* w_dev, int n_models, void* wp_dev, void* stream);
+int bx_decay_score_variant_tc(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+                              const int32_t* shifts_dev, const void* wp_dev, const float* offset_dev, int n,
+                              int n_shifts, int n_models, float* out_dev, void* stream);
+
 /* ---- FASTA text resident in HBM -> packed genome (the arrays of bx_ctx_set_genome) --------------------------------
  * Replaces the genome side of the reference's input handling: pyfasta.Fasta('./resources/hg19.fa') builds a flat
  * index and serves string slices (chromatin.py:44,205; compute_expecto_features.py:31,108), and encodeSeqs maps each

@@ -211,6 +211,36 @@ def test_fused_transform_scoring_kernel_vs_oracle():
     assert np.abs(ours - want).max() <= 1e-4 * max(1.0, np.abs(want).max())
 
 
+@pytest.mark.parametrize("n,m", [(131, 11), (700, 218), (256, 1), (1, 300)])
+def test_tensor_core_scoring_kernel_vs_float64_oracle(n, m):
+    """bx_decay_score_variant_tc (features generated in shared memory, one tcgen05 GEMM with split fp16 operands) vs
+    gblinear(variant_transform(x)) in float64 (predict.py:87-160): partial tiles, one model, more than 256 models
+    (two launches), variants at distance 0 / on shift boundaries, a keep-mask-style zero block; and vs the SIMT
+    kernel.  The bar is fp32-level agreement: SED = ALT - REF is a difference of scores that agree in 3-4 digits."""
+    from expecto_b200.transform import ScoreModels, decay_score_variant
+    rng = np.random.default_rng(3 + n)
+    x = rng.random((9, n, 2002)).astype(np.float32)           # probabilities, as ref / alt rows are
+    dist = rng.integers(-30000, 30000, size=n).astype(np.float64)
+    dist[:min(n, 6)] = [0, 200, -200, 199, -800, 800][:min(n, 6)]
+    strand = np.where(rng.random(n) < 0.5, "+", "-")
+    W = (rng.standard_normal((m, 20020)) * 0.01).astype(np.float32)
+    W[m // 3].reshape(10, 2002)[:, 100:700] = 0
+    off = rng.standard_normal(m).astype(np.float32)
+    models = ScoreModels(W, off, "cuda:0")
+    xd = torch.from_numpy(x).cuda()
+    tc = decay_score_variant(xd, dist, strand, models).cpu().numpy()
+    simt = decay_score_variant(xd, dist, strand, models, tensor_cores=False).cpu().numpy()
+    feats = O.variant_transform(list(x), O.variant_weights(dist, strand))
+    want = feats @ W.astype(np.float64).T + off[None, :]
+    scale = max(1.0, np.abs(want).max())
+    assert tc.shape == (n, m)
+    # what remains is the tensor core's truncating accumulation over the 1260-MMA main chain (score_tc.cuh)
+    assert np.abs(tc - want).max() <= 5e-5 * scale, np.abs(tc - want).max() / scale
+    assert np.abs(simt - want).max() <= 1e-4 * scale
+    # a second call reuses the prepared weights and is deterministic
+    assert np.array_equal(decay_score_variant(xd, dist, strand, models).cpu().numpy(), tc)
+
+
 def test_predict_cli_matches_predict_script(engine, cfg1_genome, golden, tmp_path):
     """chromatin CLI -> predict CLI (fused transform + scoring) vs the reference predict.py's sed.tsv."""
     import pandas as pd
