@@ -2,10 +2,22 @@
 
 xgboost==0.7.post4 is a pinned third-party dependency of the reference (requirements.txt:38) that is not in
 this image, and the reference's ``models/*.save`` files are not in its repository, so nothing here can be
-checked against a real model file: the binary layout below restates xgboost 0.7's published serialisation
-(learner.cc ``LearnerModelParam`` + gblinear ``GBLinearModelParam`` + weight vector) and is UNPINNED.  The
-text-dump and ``.npz`` forms are pinned by the tests (the ``.npz`` form is what the oracle's xgboost shim
-reads, oracle/shims/xgboost.py).
+checked against a real model file: the binary layout below restates xgboost 0.7's published serialisation and is
+pinned only as far as that goes offline — tests/test_predict_host_cpu.py builds a file byte by byte from the
+struct definitions, written down there with their source locations:
+
+    src/learner.cc   LearnerImpl::Save   = LearnerModelParam (136 bytes: float base_score, unsigned num_feature,
+                                           int num_class, int contain_extra_attrs, int contain_eval_metrics,
+                                           int reserved[29]) + dmlc string name_obj_ + dmlc string name_gbm_ +
+                                           gbm_->Save + optional attribute / metric vectors
+                     LearnerImpl::Load     accepts an optional 4-byte "binf" prefix
+    src/gbm/gblinear.cc  GBLinearModel::Save = GBLinearModelParam (136 bytes: unsigned num_feature,
+                                           int num_output_group, int reserved[32]) + dmlc vector<float> weight,
+                                           weight[i * num_output_group + gid], biases after the num_feature rows
+    dmlc-core serializer: string / vector = uint64 length + raw little-endian elements
+
+The text-dump form (``bst.dump_model``, train.py:158) is pinned against the reference's own parser of it
+(predict_by_cluster.py:73-75); the ``.npz`` form is what the oracle's xgboost shim reads (oracle/shims/xgboost.py).
 
 A gblinear model scores ``base_score + bias + w . x`` (dump layout: predict_by_cluster.py:73-75).
 """
@@ -52,8 +64,19 @@ def load_text_dump(path: str, base_score: float = 0.5) -> GBLinearModel:
     return GBLinearModel(np.asarray(weights, dtype=np.float32), bias[0], base_score)
 
 
+def save_text_dump(path: str, model: GBLinearModel) -> None:
+    """``bst.dump_model(path)`` of a gblinear booster (train.py:158): ``booster[0]:`` then what ``get_dump()[0]``
+    returns — ``bias:`` / value / ``weight:`` / one value per line (the layout predict_by_cluster.py:73-75 parses:
+    ``dump[1]`` is the bias, ``dump[3:]`` the weights).  Values are written with 9 significant digits, enough to
+    round-trip float32."""
+    with open(path, "w") as f:
+        f.write("booster[0]:\nbias:\n%.9g\nweight:\n" % float(np.float32(model.bias)))
+        f.write("\n".join("%.9g" % float(w) for w in np.asarray(model.weights, dtype=np.float32)))
+        f.write("\n")
+
+
 def load_binary(path: str) -> GBLinearModel:
-    """xgboost 0.7 binary model (UNPINNED restatement, see module docstring)."""
+    """xgboost 0.7 binary model (layout: module docstring; no real model file exists offline to pin it against)."""
     b = open(path, "rb").read()
     off = 4 if b[:4] == b"binf" else 0
     base_score, num_feature, num_class, extra_attrs, eval_metrics = struct.unpack_from("<fIiii", b, off)

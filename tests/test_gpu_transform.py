@@ -102,6 +102,24 @@ def test_feature_pipeline_tss_override_matches_reference_script(engine, cfg1_gen
     assert np.all(np.abs(ours.sum(axis=1) - g["feature_sums"]) <= 2e-3 * np.abs(g["feature_sums"]))
 
 
+def _check_sed(ref, alt, sed, want, tag, pearson_min=0.999, rel_max=0.05):
+    """absolute bars of 2e-2 / 5e-3 cannot fail on this fixture (median |SED| 4.1e-3, max 1.4e-2: an
+    all-zero SED column would pass).  SED is the scientific output, so it is held to a correlation and a relative
+    bar; the measured figures are printed (pytest -s) and quoted in DESIGN.md section 3."""
+    from helpers import pearson
+    w_ref, w_alt, w_sed = want["REF"].values, want["ALT"].values, want["SED"].values
+    scale = float(np.abs(w_sed).max())
+    err = float(np.abs(sed - w_sed).max())
+    r = pearson(sed, w_sed)
+    print(f"[sed {tag}] max|SED| {scale:.3e}  max err {err:.3e} ({err / scale:.2%})  pearson {r:.6f}  "
+          f"REF err {np.abs(ref - w_ref).max():.2e}  ALT err {np.abs(alt - w_alt).max():.2e}")
+    assert np.abs(ref - w_ref).max() <= 2e-3 * np.abs(w_ref).max() + 1e-3
+    assert np.abs(alt - w_alt).max() <= 2e-3 * np.abs(w_alt).max() + 1e-3
+    assert r >= pearson_min, r
+    assert err <= rel_max * scale, (err, scale)
+    assert np.all(np.sign(sed[np.abs(w_sed) > 0.2 * scale]) == np.sign(w_sed[np.abs(w_sed) > 0.2 * scale]))
+
+
 def test_predict_pipeline_matches_predict_script(engine, cfg1_genome, golden, tmp_path):
     """chromatin -> strand average -> per-variant transform -> gblinear scores, vs predict.py's sed.tsv."""
     import pandas as pd
@@ -124,11 +142,8 @@ def test_predict_pipeline_matches_predict_script(engine, cfg1_genome, golden, tm
              for k, v in stacks.items()}
     assert np.abs(feats["diff"][0] - g["diff_features_row0"]).max() <= 9 * 4e-3
     w = g["model_w"].astype(np.float64)
-    for key, col in (("ref", "REF"), ("alt", "ALT")):
-        score = O.gblinear_predict(feats[key], w, 0.25, 0.5)
-        assert np.abs(score - sed[col].values).max() <= 2e-2, key
-    sed_ours = O.gblinear_predict(feats["alt"], w, 0.25, 0.5) - O.gblinear_predict(feats["ref"], w, 0.25, 0.5)
-    assert np.abs(sed_ours - sed["SED"].values).max() <= 5e-3
+    s_ref, s_alt = (O.gblinear_predict(feats[key], w, 0.25, 0.5) for key in ("ref", "alt"))
+    _check_sed(s_ref, s_alt, s_alt - s_ref, sed, "transform kernels + float64 scoring, f16 forward")
 
 
 # ---------------------------------------------------------------- properties at BASELINE sizes
@@ -272,9 +287,10 @@ def test_predict_cli_matches_predict_script(engine, cfg1_genome, golden, tmp_pat
     assert list(ours.columns) == list(want.columns)
     for c in ("index", "0", "1", "2", "3", "4", "dist", "gene", "strand"):
         assert [str(v) for v in ours[c]] == [str(v) for v in want[c]], c
-    assert np.abs(ours["REF"].values - want["REF"].values).max() <= 2e-2
-    assert np.abs(ours["ALT"].values - want["ALT"].values).max() <= 2e-2
-    assert np.abs(ours["SED"].values - want["SED"].values).max() <= 5e-3
+    _check_sed(ours["REF"].values, ours["ALT"].values, ours["SED"].values, want, "predict CLI, f16 forward")
+    # SED is the float64 difference of the float32 scores (predict.py:264), printed like the reference prints it
+    assert np.abs(ours["SED"].values - (ours["ALT"].values - ours["REF"].values)).max() <= 1e-12
+    assert len(repr(float(ours["REF"].values[0]))) > 12          # widened float32, e.g. 3.9250710010528564
     for name in ("sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
         assert (tmp_path / "pred" / name).exists()
     # one pass, no .diff.h5 in between (--vcf): byte-identical tables, with the variants in two HBM blocks
@@ -286,6 +302,39 @@ def test_predict_cli_matches_predict_script(engine, cfg1_genome, golden, tmp_pat
     assert (tmp_path / "pred_fused" / "snps_hg19.vcf").read_bytes() == (out / "snps_hg19.vcf").read_bytes()
     for name in ("sed.tsv", "sed_sorted_by_magnitude.tsv", "sed_sorted_by_proportion.tsv"):
         assert (tmp_path / "pred_fused" / name).read_bytes() == (tmp_path / "pred" / name).read_bytes(), name
+
+
+def test_predict_one_pass_with_split_operands_reproduces_sed(weights_f16, cfg1_genome, golden, tmp_path):
+    """The same predict.py fixture with --dtype f16x3 (one pass, --vcf): the fp32 reference's SED to within 1 %% of its
+    largest value and Pearson >= 0.9999 — what the split-operand forward buys for the pipeline's scientific output."""
+    import pandas as pd
+    from expecto_b200 import predict
+    from expecto_b200.engine import BelugaEngine
+    g = golden("predict_golden.npz")
+    want = pd.read_csv(io.StringIO(str(g["sed_tsv"])), sep="\t")
+    rows = [l.split("\t") for l in str(golden("chromatin_cfg1_golden.npz")["snps_hg19_vcf"]).splitlines()[2:]]
+    vcf = tmp_path / "example.vcf"
+    vcf.write_text("".join("\t".join(r) + "\n" for r in rows))
+    genefile = tmp_path / "closestgene"
+    with open(genefile, "w") as f:
+        for r, (_, w) in zip(rows, want.iterrows()):
+            f.write("\t".join([r[0], str(int(r[1]) - 1), r[1], r[3], r[4], w["strand"], w["gene"], str(-int(w["dist"]))]) + "\n")
+    np.savez(tmp_path / "model.npz", weights=g["model_w"], bias=np.float32(0.25), base_score=np.float32(0.5))
+    feats_tsv = tmp_path / "features.tsv"
+    with open(feats_tsv, "w") as f:
+        f.write("\tCell type\tAssay\tTreatment\tAssay type\tSource\n")
+        for i in range(2002):
+            f.write(f"{i}\tcell{i}\tassay{i}\tNone\t{'DNase' if i % 3 == 0 else 'TF'}\tsrc\n")
+    eng = BelugaEngine(0, dtype="f16x3", capacity=256)
+    eng.load_state_dict(weights_f16)
+    args = predict.build_parser().parse_args([
+        "--model_save_file", str(tmp_path / "model.npz"), "--belugaFeatures", str(feats_tsv), "--geneFile",
+        str(genefile), "--vcf", str(vcf), "-o", str(tmp_path / "pred")])
+    predict.run(args, engine=eng, genome=PackedGenome.from_sequences(cfg1_genome))
+    eng.close()
+    ours = pd.read_csv(tmp_path / "pred" / "sed.tsv", sep="\t")
+    _check_sed(ours["REF"].values, ours["ALT"].values, ours["SED"].values, want, "predict CLI, f16x3 forward",
+               pearson_min=0.9999, rel_max=0.01)
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs in one process")

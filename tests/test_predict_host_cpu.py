@@ -1,4 +1,6 @@
 """Host logic of the predict.py drop-in: model loaders, gene-row run lengths, keep-mask expansion."""
+import os
+
 import numpy as np
 import pandas as pd
 import pytest
@@ -145,6 +147,78 @@ def test_merge_predict_batched_natural_order_and_index(tmp_path):
     args.n_chunks = 5
     with pytest.raises(AssertionError):
         mpb.run(args)
+
+
+def test_gblinear_binary_layout_built_from_the_xgboost_0_7_structs(tmp_path):
+    """A ``.save`` file assembled here byte by byte from xgboost 0.7's serialisation code (no shared code with
+    gblinear.save_binary), with the optional pieces a real file can carry: the "binf" prefix LearnerImpl::Load skips,
+    contain_extra_attrs = 1 with an attribute vector after the booster, and contain_eval_metrics = 1."""
+    import struct
+    rng = np.random.default_rng(8)
+    w = rng.standard_normal(20020).astype("<f4")
+    bias, base_score = np.float32(-0.125), np.float32(0.5)
+
+    def dmlc_string(b):                       # dmlc::Stream::Write(std::string): uint64 length + bytes
+        return struct.pack("<Q", len(b)) + b
+
+    def build(prefix, extra_attrs, eval_metrics):
+        # src/learner.cc: struct LearnerModelParam { float base_score; unsigned num_feature; int num_class;
+        #                 int contain_extra_attrs; int contain_eval_metrics; int reserved[29]; }  -> 20 + 116 bytes
+        out = prefix + struct.pack("<fIiii", base_score, w.size, 0, extra_attrs, eval_metrics) + bytes(4 * 29)
+        out += dmlc_string(b"reg:linear") + dmlc_string(b"gblinear")      # name_obj_, name_gbm_
+        # src/gbm/gblinear.cc: struct GBLinearModelParam { unsigned num_feature; int num_output_group;
+        #                      int reserved[32]; } -> 8 + 128 bytes; then std::vector<bst_float> weight with the
+        #                      bias of output group 0 after the num_feature feature weights
+        out += struct.pack("<Ii", w.size, 1) + bytes(4 * 32)
+        out += struct.pack("<Q", w.size + 1) + w.tobytes() + struct.pack("<f", bias)
+        if extra_attrs:                       # std::vector<std::pair<std::string, std::string>>
+            out += struct.pack("<Q", 1) + dmlc_string(b"best_iteration") + dmlc_string(b"99")
+        if eval_metrics:                      # std::vector<std::string>
+            out += struct.pack("<Q", 1) + dmlc_string(b"rmse")
+        return out
+
+    assert len(build(b"", 0, 0)) == 136 + (8 + 10) + (8 + 8) + 136 + 8 + 4 * 20021
+    for i, (prefix, ea, em) in enumerate([(b"", 0, 0), (b"binf", 0, 0), (b"", 1, 1), (b"binf", 1, 0)]):
+        p = tmp_path / f"m{i}.save"
+        p.write_bytes(build(prefix, ea, em))
+        m = gblinear.load_model(str(p))
+        assert np.array_equal(m.weights, w) and m.bias == float(bias) and m.base_score == float(base_score)
+    # the repo's own writer produces the minimal form of the same layout
+    gblinear.save_binary(str(tmp_path / "own.save"), gblinear.GBLinearModel(w, float(bias), float(base_score)))
+    assert (tmp_path / "own.save").read_bytes() == build(b"", 0, 0)
+    bad = bytearray(build(b"", 0, 0))
+    bad[136 + 8 + 10 + 8:136 + 8 + 10 + 8 + 8] = b"gbtree\x00\x00"
+    (tmp_path / "tree.save").write_bytes(bytes(bad))
+    with pytest.raises(ValueError):
+        gblinear.load_model(str(tmp_path / "tree.save"))
+
+
+def test_gblinear_text_dump_matches_the_reference_parser(tmp_path):
+    """The text dump (train.py:158 ``bst.dump_model``) against the reference's own reading of it:
+    predict_by_cluster.py:73-75 takes ``get_dump()[0]``, i.e. the file without its ``booster[0]:`` line, and reads
+    the bias from line 1 and the weights from line 3 on.  The three statements are lifted from the reference with
+    ``ast`` and executed (skipped where /root/reference does not exist)."""
+    import ast
+    ref = "/root/reference/predict_by_cluster.py"
+    if not os.path.exists(ref):
+        pytest.skip("reference checkout only exists in the build container")
+    rng = np.random.default_rng(9)
+    m = gblinear.GBLinearModel(rng.standard_normal(2002 * 10).astype(np.float32) * 1e-3, bias=-0.0625, base_score=0.5)
+    path = tmp_path / "m.dump"
+    gblinear.save_text_dump(str(path), m)
+    back = gblinear.load_model(str(path))
+    assert np.array_equal(back.weights, m.weights) and back.bias == m.bias
+    fn = [n for n in ast.parse(open(ref).read()).body if isinstance(n, ast.FunctionDef) and n.name == "interpret_model"][0]
+    fn.body = fn.body[:3] + [ast.parse("return bias, weights").body[0]]     # dump = ...; bias = ...; weights = ...
+
+    class Booster:
+        def get_dump(self):
+            return [path.read_text().split("\n", 1)[1]]                     # xgboost: one string per booster
+
+    ns = {"np": np}
+    exec(compile(ast.fix_missing_locations(ast.Module(body=[fn], type_ignores=[])), ref, "exec"), ns)
+    bias, weights = ns["interpret_model"](Booster(), None, None)
+    assert bias == m.bias and np.array_equal(weights.astype(np.float32), m.weights)
 
 
 def test_keep_mask_matches_reference_cluster_utils(golden, tmp_path):
