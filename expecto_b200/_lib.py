@@ -53,7 +53,7 @@ EXPORTS = [
     "bx_forward_segments_delta", "bx_fasta_blocks", "bx_fasta_find_headers", "bx_fasta_count", "bx_fasta_pack",
     "bx_chromatin_open", "bx_chromatin_chunk_info", "bx_chromatin_submit", "bx_chromatin_wait",
     "bx_chromatin_submit_device", "bx_chromatin_close", "bx_variant_descs_host",
-    "bx_score_weights_bytes", "bx_score_prepare_weights", "bx_decay_score_variant_tc",
+    "bx_score_weights_bytes", "bx_score_prepare_weights", "bx_decay_score_variant_tc", "bx_fasta_count_noalloc",
 ]
 CHROM_NO_DELTA, CHROM_AVERAGE, CHROM_WINDOWS = 1, 2, 4
 NSTAGES = 10
@@ -140,6 +140,7 @@ def lib() -> C.CDLL:
     L.bx_score_weights_bytes.restype = i64
     L.bx_score_prepare_weights.argtypes = [vp, i32, vp, vp]
     L.bx_decay_score_variant_tc.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
+    L.bx_fasta_count_noalloc.argtypes = [vp, i64, i64, vp, vp, vp]
     L.bx_ctx_profile.argtypes = [vp, i32]
     L.bx_ctx_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), i32]
     for name in EXPORTS:

@@ -1876,3 +1876,68 @@ int bx_variant_descs_host(int kind, int64_t n, const int64_t* gpos, const int32_
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ bx_fasta_count without any allocation
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  bx_fasta_count takes
+// the temporary storage of its CUB scan from cudaMallocAsync and hands the contig length back through a stream
+// synchronise; this variant takes that scratch from a file-scope device array and leaves the length on the device.
+// Every GPU that loads the library holds the array (256 KB) until exit.
+constexpr size_t kFaScratchBytes = 256 * 1024;
+constexpr long long kFaNoAllocMaxBlocks = 1LL << 20;   // 4096-byte blocks: contig bodies of up to 4 GiB of text
+static __device__ __align__(256) unsigned char g_fa_scan_scratch[kFaScratchBytes];
+
+namespace {
+// Device address of g_fa_scan_scratch per device.  In host code the array's name is a host-side stand-in, not a
+// device address, so it is resolved once per device, with that device current, through cudaGetSymbolAddress.
+std::atomic<void*> g_fa_scratch_addr[kMaxDevices];
+
+int fa_scratch_ptr(void** out) {
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(BX_E_ARG, "device index %d out of range", dev);
+  void* p = g_fa_scratch_addr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    CK(cudaGetSymbolAddress(&p, g_fa_scan_scratch));   // the current device's instance of the array
+    if (!p) return fail(BX_E_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_fa_scratch_addr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return 0;
+}
+}  // namespace
+
+extern "C" int bx_fasta_count_noalloc(const uint8_t* text_dev, int64_t body_start, int64_t body_end,
+                                      int64_t* block_offsets_dev, int64_t* n_bases_dev, void* stream) {
+  if (body_start < 0 || body_end < body_start || !block_offsets_dev || !n_bases_dev)
+    return fail(BX_E_ARG, "invalid arguments");
+  if (int r = check_device()) return r;
+  if (!text_dev || (reinterpret_cast<uintptr_t>(text_dev) & 15)) return fail(BX_E_ARG, "text_dev must be 16-byte aligned");
+  const long long n_blocks = bx_fasta_blocks(body_start, body_end);
+  if (n_blocks > kFaNoAllocMaxBlocks)
+    return fail(BX_E_ARG, "contig body of %lld 4096-byte blocks exceeds the %lld blocks (4 GiB of text) the static "
+                          "scratch of bx_fasta_count_noalloc is sized for; use bx_fasta_count",
+                n_blocks, kFaNoAllocMaxBlocks);
+  void* scratch = nullptr;
+  if (int r = fa_scratch_ptr(&scratch)) return r;
+  cudaStream_t st = (cudaStream_t)stream;
+  long long* off = reinterpret_cast<long long*>(block_offsets_dev);
+  // the extra entry must start at zero: the scan turns it into the total.  (The scratch itself needs no clearing:
+  // CUB's scan initialises the tile states it keeps there at the start of every call.)
+  CK(cudaMemsetAsync(off + n_blocks, 0, sizeof(long long), st));
+  if (n_blocks > 0) {
+    fasta_count_kernel<<<grid_for(n_blocks, kFaThreads / 32), kFaThreads, 0, st>>>(text_dev, body_start & ~15LL, body_start,
+                                                                                   body_end, n_blocks, off);
+    g_launches++;
+    CK(cudaGetLastError());
+    size_t tmp_bytes = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, off, off, (int)(n_blocks + 1), st));
+    if (tmp_bytes > kFaScratchBytes)
+      return fail(BX_E_STATE, "the scan of %lld blocks needs %zu bytes of scratch, the static array holds %zu", n_blocks,
+                  tmp_bytes, kFaScratchBytes);
+    CK(cub::DeviceScan::ExclusiveSum(scratch, tmp_bytes, off, off, (int)(n_blocks + 1), st));
+    g_launches++;
+  }
+  CK(cudaMemcpyAsync(n_bases_dev, off + n_blocks, sizeof(long long), cudaMemcpyDeviceToDevice, st));
+  return 0;
+}

@@ -261,6 +261,20 @@ int bx_fasta_pack(const uint8_t* text_dev, int64_t body_start, int64_t body_end,
                   int64_t base_offset, uint32_t* bases2_dev, uint32_t* nmask_dev, int64_t* invalid_dev,
                   int64_t invalid_cap, int64_t* invalid_count_dev, void* stream);
 
+/* bx_fasta_count for callers that cannot allocate.  This entry point has no counterpart in the reference; it was
+ * added (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same result as bx_fasta_count in block_offsets_dev[0 .. bx_fasta_blocks()], but it calls no
+ * cudaMalloc / cudaFree / allocating routine and does not synchronise: the scratch of its scan lives in a file-scope
+ * device array of 256 KB that every GPU holds from the moment it loads the library until exit, and the contig length
+ * is left in *n_bases_dev (a DEVICE int64 of the caller's) instead of being read back to the host.
+ * Limit: contig bodies of at most 2^20 4096-byte blocks (4 GiB of FASTA text); larger ones are refused with BX_E_ARG
+ * — use bx_fasta_count.  Every call on a device shares the one scratch array: calls that overlap on the GPU (two
+ * streams, two threads) race; calls on one stream are safe.  The array keeps the last call's contents between
+ * calls; nothing in it has to be cleared (the scan initialises what it uses), and the one value that must start at
+ * zero, block_offsets_dev[bx_fasta_blocks()], is cleared by the call itself. */
+int bx_fasta_count_noalloc(const uint8_t* text_dev, int64_t body_start, int64_t body_end, int64_t* block_offsets_dev,
+                           int64_t* n_bases_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
