@@ -78,6 +78,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     ]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
+    cmd[1:1] = os.environ.get("BX_NVCC_FLAGS", "").split()   # experiments (e.g. -DBX_SCORE_SPAN=4)
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)

@@ -607,15 +607,23 @@ def predict_all_shifts_gathered(engine, cols: dict, maxshift: int, n_total: int,
     [2 n_local, 2002] tensors until the end:
 
       round k, every rank:  chunk k of its shard -> device buffer [3, S, 2, chunk, 2002] (bx_chromatin_submit_device)
-                            -> ``dist.gather`` to rank 0 on a side stream, overlapping chunk k + 1's compute;
-      rank 0:               the gathered buffers -> pinned host memory on that side stream, then row slabs to
+                            -> ``dist.gather`` to rank 0, in order on the compute stream;
+      rank 0:               the gathered buffers -> pinned host memory on a side stream (copy engine), overlapping
+                            chunk k + 1's compute, then row slabs to
                             ``sinks[shift](name, global_row0, array)`` (rank order == row order inside each strand
                             half of chromatin.py:281-286's layout) through ``writer``.
 
     ``cols``: this rank's columns (windows.variant_columns of its contiguous shard, shard.shard_range order).  Rank 0
     receives 3 x S x 2 x 2002 x 4 bytes = 432 KB per variant of the WHOLE job and must move them over its one PCIe
     link, which is what bounds this mode at 8 GPUs (the timings returned say so); ``--gather file`` has every rank
-    copy and write its own rows instead."""
+    copy and write its own rows instead.
+
+    Why the gather is not overlapped with compute: NCCL's send / receive kernels need SMs, and the forward's GEMM kernels
+    are persistent grids of one CTA per SM with statically strided tiles.  Issued on a side stream, the gather kernels
+    got in only at kernel boundaries and the CTA pairs they displaced then delayed whole GEMM launches: measured at N = 2,
+    65,536 variants: 2.87 s (gather 11.7 GB/s, 42 % of the wall time) against 1.30 s for the no-collective mode
+    (profiles/r02_bench_n2_gather_on_side_stream.json).  In order, the gather has the GPU to itself for the
+    millisecond it needs; only rank 0's device -> host copies, which run on a copy engine, overlap the next chunk."""
     import time
 
     import torch
@@ -631,7 +639,10 @@ def predict_all_shifts_gathered(engine, cols: dict, maxshift: int, n_total: int,
     bounds = shard.shard_bounds(n_total, world)
     if cols["n"] != int(bounds[rank + 1] - bounds[rank]):
         raise ValueError(f"rank {rank} holds {cols['n']} variants, expected {int(bounds[rank + 1] - bounds[rank])}")
-    n_chunks, chunk = engine.chromatin_open(cols, maxshift, delta=delta)
+    # rank 0 stages world x chunk variants per round in pinned memory (two sets): chunks shrink as the world grows so
+    # that a set stays under 768 MB (pinning gigabytes takes seconds)
+    cap = max(64, int(768e6 // (world * 3 * S * 2 * 2002 * 4)))
+    n_chunks, chunk = engine.chromatin_open(cols, maxshift, delta=delta, chunk_variants=cap)
     # every rank takes part in every round, so all agree on the chunk size and the number of rounds
     if world > 1:
         t = torch.tensor([n_chunks, -chunk], dtype=torch.int64, device=dev)
@@ -656,7 +667,6 @@ def predict_all_shifts_gathered(engine, cols: dict, maxshift: int, n_total: int,
     if own_writer:
         writer = SlabWriter(n_sets)
     side = torch.cuda.Stream(device=dev) if cuda else None
-    works = [None, None]
     timing = {"gather_ms": 0.0, "d2h_ms": 0.0, "wait_s": 0.0, "rounds": rounds, "chunk_variants": chunk}
     ev_pairs = []
     # chunk sizes of every rank in every round (shards differ by at most one variant)
@@ -685,52 +695,46 @@ def predict_all_shifts_gathered(engine, cols: dict, maxshift: int, n_total: int,
                 writer.write(sinks[shift], tasks)
 
     pending = None
+    d2h_done = [None, None]
     try:
         for k in range(rounds):
             b = k & 1
-            if works[b] is not None:       # the gather that last read send[b] / wrote recv[b]
-                works[b].wait()
+            if cuda and d2h_done[b] is not None:   # rank 0: recv[b] (send[b] when alone) has left for the host
+                torch.cuda.current_stream(dev).wait_event(d2h_done[b])
             if k < n_chunks:
                 flat = send[b].view(3, -1, 2002)
                 engine.chromatin_submit_device(k, flat[0], flat[1], flat[2], 2 * chunk, chunk, 0)
             if rank == 0:
                 hb = writer.next_set()     # == b: the pinned set's previous contents are on disk
                 assert hb == b
-            if cuda:
-                computed = torch.cuda.Event()
-                computed.record()
-                side.wait_event(computed)
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if (cuda and rank == 0) else None
+            if e:
+                e[0].record()
+            if world > 1:
+                # in order on the compute stream: with every SM free the 113 MB of a chunk cross NVLink in about a
+                # millisecond, where a gather overlapped with the persistent GEMM kernels crawled (docstring)
+                dist.gather(send[b], recv[b] if rank == 0 else None, dst=0)
             done = None
-            with (torch.cuda.stream(side) if cuda else _nullcontext()):
-                e = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if (cuda and rank == 0) else None
-                if e:
-                    e[0].record()
-                if world > 1:
-                    works[b] = dist.gather(send[b], recv[b] if rank == 0 else None, dst=0, async_op=True)
-                if rank == 0:
-                    if world > 1:
-                        works[b].wait()    # the side stream waits for the collective
-                    if e:
-                        e[1].record()
-                    src = recv[b] if world > 1 else [send[b]]
+            if rank == 0:
+                src = recv[b] if world > 1 else [send[b]]
+                if cuda:
+                    e[1].record()
+                    side.wait_event(e[1])
+                with (torch.cuda.stream(side) if cuda else _nullcontext()):
                     for r in range(world):
                         if sizes[k][r]:
                             host[b][r].copy_(src[r], non_blocking=True)
                     if cuda:
                         e[2].record()
-                        done = e[2]
+                        done = d2h_done[b] = e[2]
                         ev_pairs.append(e)
                         for t_ in src:
                             t_.record_stream(side)
-            if rank == 0:
                 if pending is not None:
                     flush(pending)
                 pending = (k, b, done)
         if rank == 0 and pending is not None:
             flush(pending)
-        for w in works:
-            if w is not None:
-                w.wait()
         if cuda:
             torch.cuda.synchronize(dev)
         if rank == 0:
@@ -738,9 +742,11 @@ def predict_all_shifts_gathered(engine, cols: dict, maxshift: int, n_total: int,
                 writer.close()
             else:
                 writer.drain()
-            for e in ev_pairs:
+            for i, e in enumerate(ev_pairs):
                 timing["gather_ms"] += e[0].elapsed_time(e[1])
                 timing["d2h_ms"] += e[1].elapsed_time(e[2])
+                if i:   # compute stream of rank 0 between the end of one gather and the start of the next
+                    timing["compute_ms"] = timing.get("compute_ms", 0.0) + ev_pairs[i - 1][1].elapsed_time(e[0])
     finally:
         engine.chromatin_close()
     timing["gathered_bytes"] = int(3 * S * 2 * 2002 * 4) * (n_total - int(bounds[1] - bounds[0])) if world > 1 else 0
