@@ -554,7 +554,8 @@ def run_gpu(args) -> int:
         "roofline": {"bound": "tensor", "kernel": f"gemm_tc_kernel ({top})", "achieved": top_tf,
                      "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": top_tf / peaks["bf16_tflops"],
                      "traffic": traffic,
-                     "traffic_source": "ncu capture r01 (profiles/dram_traffic.json), static: not measured in this run",
+                     "traffic_source": "ncu --set full captures (profiles/dram_traffic.json: conv2 from round 2 at this chunk size, "
+                                       "other stages round 1), static: not measured in this run",
                      "peak_source": peaks["source"] + ", burst",
                      "peak_sustained": peaks["bf16_tflops_sustained"],
                      "frac_sustained": top_tf / peaks["bf16_tflops_sustained"],
