@@ -143,6 +143,8 @@ struct bx_ctx {
   size_t stage_out_bytes = 0;
   float* probs_scratch = nullptr;
   size_t probs_scratch_bytes = 0;
+  uint8_t* alleles_stage = nullptr;  // bx_chromatin_shift_host: the call's allele codes (grown on demand, kept)
+  size_t alleles_stage_bytes = 0;
   // segment mode: phase-B conv6 output and the dense FC1 operand gathered from the segment activations
   void* act6b = nullptr;
   void* fc_in = nullptr;
@@ -603,6 +605,7 @@ int bx_ctx_destroy(bx_ctx* c) {
     if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
   }
   cudaFree(c->probs_scratch);
+  cudaFree(c->alleles_stage);
   cudaFree(c->act6b); cudaFree(c->fc_in); cudaFree(c->act4h); cudaFree(c->act4b);
   cudaFree(c->patch6a); cudaFree(c->patch6b); cudaFree(c->acc_ref); cudaFree(c->probs_dense);
   cudaFree(c->si_of_k_dev); cudaFree(c->ref_scratch);
@@ -850,10 +853,18 @@ int bx_chromatin_shift_host(bx_ctx* c, const bx_window_desc* descs_host, const u
   const size_t in_chunk = (size_t)4 * vcap * sizeof(bx_window_desc);
   if (int r = ensure_pipe(c, in_chunk, out_chunk, (size_t)4 * vcap * BX_FEATURES * sizeof(float))) return r;
   // allele codes: one upload for the whole call (descriptor aoff values index this table)
-  uint8_t* alleles_dev = nullptr;
-  CK(cudaMalloc(&alleles_dev, (size_t)std::max<int64_t>(n_alleles, 1)));
+  if ((size_t)std::max<int64_t>(n_alleles, 1) > c->alleles_stage_bytes) {  // first call / a longer table only
+    CK(cudaStreamSynchronize(c->s_comp));
+    cudaFree(c->alleles_stage);
+    c->alleles_stage = nullptr; c->alleles_stage_bytes = 0;
+    const size_t want = std::max<size_t>((size_t)n_alleles * 2, 1 << 16);
+    CK(cudaMalloc(&c->alleles_stage, want));
+    c->alleles_stage_bytes = want;
+  }
+  uint8_t* alleles_dev = c->alleles_stage;
+  // the previous call's kernels have finished (every call ends with a synchronise), so the table can be overwritten;
+  // the first chunk's compute waits for this copy through ev_in (same stream, recorded after it)
   if (n_alleles > 0) CK(cudaMemcpyAsync(alleles_dev, alleles_host, (size_t)n_alleles, cudaMemcpyHostToDevice, c->s_in));
-  CK(cudaStreamSynchronize(c->s_in));
   const size_t F = BX_FEATURES;
   int i = 0, rc = 0;
   for (int v0 = 0; v0 < n_var && rc == 0; v0 += vcap, ++i) {
@@ -900,7 +911,6 @@ int bx_chromatin_shift_host(bx_ctx* c, const bx_window_desc* descs_host, const u
   }
   cudaStreamSynchronize(c->s_out);
   cudaError_t e = cudaStreamSynchronize(c->s_comp);
-  cudaFree(alleles_dev);
   if (rc) return rc;
   if (e != cudaSuccess) return fail(BX_E_CUDA, "pipeline failed: %s", cudaGetErrorString(e));
   return 0;

@@ -201,3 +201,36 @@ def test_cli_sinks_device_descriptors_equal_host_descriptors(engine, small_genom
         for k in ("diff", "ref", "alt"):
             assert np.array_equal(res[False][0][s][k], res[True][0][s][k]), (s, k)
             assert not np.isnan(res[False][0][s][k]).any()
+
+
+@pytest.mark.parametrize("average", [False, True])
+def test_fused_epilogue_writes_only_its_own_rows(engine, small_genome, average):
+    """compute-sanitizer is closed on this pool (profiles/r02_sanitizer_memcheck.log), so the FC2 chromatin epilogue is
+    checked with guard rows: the chunk's rows sit inside larger tensors (row0 > 0, strides wider than the chunk,
+    spare rows after every strand block) pre-filled with a sentinel; every row the call does not own must come back
+    intact and every owned row must be written — for all three paths and a partial last chunk."""
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    rows = _variants(small_genome, n_random=12)
+    n = len(rows)
+    SENT = -5.5
+    S, pad0, gap = 9, 3, 2
+    strand_stride = n + gap
+    shift_stride = (1 if average else 2) * strand_stride + gap
+    total = pad0 + S * shift_stride + 4
+    outs = [torch.full((total, 2002), SENT, device=engine.device) for _ in range(3)]
+    n_chunks, _ = engine.chromatin_open(_cols(pg, rows), 800, average=average, chunk_variants=5)
+    for k in range(n_chunks):
+        engine.chromatin_submit_device(k, *outs, shift_stride, strand_stride, pad0 + engine.chromatin_chunk_info(k)["v0"])
+    engine.chromatin_close()
+    torch.cuda.synchronize()
+    owned = torch.zeros(total, dtype=torch.bool, device=engine.device)
+    for si in range(S):
+        for t in range(1 if average else 2):
+            a = pad0 + si * shift_stride + t * strand_stride
+            owned[a:a + n] = True
+    for name, o in zip(("ref", "alt", "diff"), outs):
+        assert bool((o[~owned] == SENT).all()), name
+        assert not bool((o[owned] == SENT).any()), name
+        if name != "diff":
+            assert bool(((o[owned] > 0) & (o[owned] < 1)).all()), name

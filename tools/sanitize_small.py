@@ -42,6 +42,24 @@ def main():
                         np.zeros(3, np.float32), shifts=chromatin_shift_list(200))
     decay_transform_fixed(torch.rand((2, 5, 2, 2002), device="cuda"), np.ones((10, 5)))
     eng.forward_onehot_host(synth.random_onehot(3, seed=1))
+    # round 2: the in-library variant loop (device descriptor builders, delta + full-segment + per-window paths, the
+    # fused FC2 epilogue in both output forms) and the tensor-core scoring kernel
+    from expecto_b200.transform import ScoreModels
+    from expecto_b200.windows import variant_columns
+    g = genome["chr1"]
+    rows = [("chr1", 15000, "A", "C"), ("chr1", 9000, "AC", "A"), ("chr1", 12000, g[11999:12130].upper().replace("N", "A"), "A")]
+    cols = variant_columns(pg, [r[0] for r in rows], np.array([r[1] for r in rows]), [r[2] for r in rows], [r[3] for r in rows])
+    for average in (False, True):
+        rows_per_shift = 3 if average else 6
+        outs = [torch.zeros((9, rows_per_shift, 2002), device="cuda") for _ in range(3)]
+        n_chunks, _ = eng.chromatin_open(cols, 800, average=average, chunk_variants=2)
+        for k in range(n_chunks):
+            eng.chromatin_submit_device(k, *[t.view(-1, 2002) for t in outs], rows_per_shift, 3,
+                                        eng.chromatin_chunk_info(k)["v0"])
+        eng.chromatin_close()
+    x9 = outs[0]
+    models = ScoreModels(np.full((3, 20020), 1e-3, np.float32), np.zeros(3, np.float32), "cuda:0")
+    decay_score_variant(x9, np.array([100.0, -300.0, 0.0]), np.array(["+", "-", "+"]), models)
     torch.cuda.synchronize()
     print("sanitize_small ok" if ok else "sanitize_small MISMATCH")
     eng.close()
