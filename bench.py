@@ -282,7 +282,7 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
         out["fixed"]["traffic"] = out["variant"]["traffic"] = None
     del res
     # ---- transform fused with gblinear scoring (predict.py:120-160) as one tcgen05 GEMM: HBM-bound on the x read
-    from expecto_b200.transform import ScoreModels, decay_score_variant
+    from expecto_b200.transform import X_PITCH, ScoreModels, decay_score_variant, padded_rows
     m = 218                                    # resources/modellist
     rng = np.random.default_rng(5)
     models = ScoreModels((rng.standard_normal((m, 20020)) * 0.01).astype(np.float32), rng.standard_normal(m).astype(np.float32), dev)
@@ -290,7 +290,8 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
     # four full waves of 74 CTA pairs x 256 variants
     del x
     n = 74 * 256 * 4
-    x = torch.rand((9, n, 2002), dtype=torch.float32, device=dev)
+    x = padded_rows((9, n), dev)               # rows X_PITCH floats apart, as FC2's epilogue leaves them for predict
+    x.uniform_()
     dist_d = torch.from_numpy(np.random.default_rng(1).integers(-40000, 40000, size=n).astype(np.float64)).to(dev)
     strand_d = torch.from_numpy(np.where(np.arange(n) % 2 == 0, 1, -1).astype(np.int8)).to(dev)
     t = timed(lambda: decay_score_variant(x, dist_d, strand_d, models, shifts=shifts_d))
@@ -300,7 +301,12 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
                     "unit": "GB/s", "peak": peaks["hbm_gbs"], "frac": b / t / 1e9 / peaks["hbm_gbs"],
                     "variants_per_s": n / t, "kernel": "score_tc_kernel",
                     "algorithmic_tflops": flop / t / 1e12, "executed_tflops": 3 * flop * (20160 / 20020) * (224 / m) / t / 1e12,
-                    "note": "features never leave shared memory; every product is three fp16 MMAs (hi/lo split operands)"}
+                    "x_row_pitch_floats": X_PITCH,
+                    "note": "features never leave shared memory; every product is three fp16 MMAs (hi/lo split operands); "
+                            "bytes are the algorithmic 2002 floats per row, rows are padded to x_row_pitch_floats"}
+    xd = x.contiguous()                        # dense 8008-byte rows (what a caller's own [9, n, 2002] array is)
+    out["score"]["ms_dense_rows"] = timed(lambda: decay_score_variant(xd, dist_d, strand_d, models, shifts=shifts_d)) * 1e3
+    del xd
     t_simt = timed(lambda: decay_score_variant(x[:, :2048].contiguous(), dist_d[:2048], strand_d[:2048], models,
                                                shifts=shifts_d, tensor_cores=False))
     out["score"]["simt_kernel_ms_per_variant"] = t_simt * 1e3 / 2048

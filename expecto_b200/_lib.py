@@ -52,7 +52,7 @@ EXPORTS = [
     "bx_decay_score_variant", "bx_forward_segments", "bx_segment_capacity", "bx_strand_average",
     "bx_forward_segments_delta", "bx_fasta_blocks", "bx_fasta_find_headers", "bx_fasta_count", "bx_fasta_pack",
     "bx_chromatin_open", "bx_chromatin_chunk_info", "bx_chromatin_submit", "bx_chromatin_wait",
-    "bx_chromatin_submit_device", "bx_chromatin_close", "bx_variant_descs_host",
+    "bx_chromatin_submit_device", "bx_chromatin_set_row_pitch", "bx_chromatin_close", "bx_variant_descs_host",
     "bx_score_weights_bytes", "bx_score_prepare_weights", "bx_decay_score_variant_tc", "bx_fasta_count_noalloc",
 ]
 CHROM_NO_DELTA, CHROM_AVERAGE, CHROM_WINDOWS = 1, 2, 4
@@ -135,12 +135,13 @@ def lib() -> C.CDLL:
     L.bx_chromatin_submit.argtypes = [vp, i32, vp, vp, vp]
     L.bx_chromatin_wait.argtypes = [vp, i32]
     L.bx_chromatin_submit_device.argtypes = [vp, i32, vp, vp, vp, i64, i64, i64, vp]
+    L.bx_chromatin_set_row_pitch.argtypes = [vp, i64]
     L.bx_chromatin_close.argtypes = [vp]
     L.bx_variant_descs_host.argtypes = [i32, i64, vp, vp, vp, vp, vp, i32, i32, ip, ip, vp]
     L.bx_score_weights_bytes.argtypes = [i32]
     L.bx_score_weights_bytes.restype = i64
     L.bx_score_prepare_weights.argtypes = [vp, i32, vp, vp]
-    L.bx_decay_score_variant_tc.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
+    L.bx_decay_score_variant_tc.argtypes = [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
     L.bx_fasta_count_noalloc.argtypes = [vp, i64, i64, vp, vp, vp]
     L.bx_ctx_profile.argtypes = [vp, i32]
     L.bx_ctx_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), i32]

@@ -536,12 +536,20 @@ def predict_all_shifts_segments_device(engine, genome, chroms, pos, refs, alts, 
 
 
 def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, maxshift: int, delta: bool = True,
-                                       host_descs: bool = False):
+                                       host_descs: bool = False, padded: bool = False):
     """The chromatin step as ``predict.py`` consumes it, left in HBM: {"ref", "alt", "diff"} -> float32 [S, n, 2002],
     already averaged over the forward / reverse-complement rows (predict.py:186-190).  This is what reading the nine
     ``.diff.h5`` files back and averaging gives, without the 432 KB per variant of file traffic in between.  The
-    averaging happens in FC2's epilogue (BX_CHROM_AVERAGE)."""
+    averaging happens in FC2's epilogue (BX_CHROM_AVERAGE).  ``padded``: the tensors are views of buffers whose rows
+    are ``transform.X_PITCH`` floats apart (128-byte aligned rows: what the scoring kernel reads fastest)."""
     import torch
+
+    from .transform import padded_rows
+
+    def alloc(S, n):
+        if padded:
+            return {k: padded_rows((S, n), engine.device) for k in ("ref", "alt", "diff")}
+        return {k: torch.empty((S, n, 2002), dtype=torch.float32, device=engine.device) for k in ("ref", "alt", "diff")}
 
     from .windows import variant_columns, variant_extent_invalid
 
@@ -549,12 +557,12 @@ def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, 
     if not host_descs and variant_extent_invalid(genome, cols, maxshift) < 0:
         n = cols["n"]
         S = len(shift_list(maxshift))
-        res = {k: torch.empty((S, n, 2002), dtype=torch.float32, device=engine.device) for k in ("ref", "alt", "diff")}
+        res = alloc(S, n)
         n_chunks, _ = engine.chromatin_open(cols, maxshift, delta=delta, average=True, windows_only=maxshift % 200 != 0)
         try:
             with torch.cuda.device(engine.device):
                 for k in range(n_chunks):
-                    engine.chromatin_submit_device(k, *[res[key].view(-1, 2002) for key in ("ref", "alt", "diff")], n, 0,
+                    engine.chromatin_submit_device(k, res["ref"], res["alt"], res["diff"], n, 0,
                                                    engine.chromatin_chunk_info(k)["v0"])
         finally:
             engine.chromatin_close()
@@ -567,7 +575,7 @@ def predict_all_shifts_averaged_device(engine, genome, chroms, pos, refs, alts, 
     shifts = shift_list(maxshift)
     S = len(shifts)
     seg_len = 2000 + 2 * maxshift
-    out = {k: torch.empty((S, n, 2002), dtype=torch.float32, device=engine.device) for k in ("ref", "alt", "diff")}
+    out = alloc(S, n)
     use_segments = maxshift % 200 == 0
     ok = segment_eligible([len(r) for r in refs], [len(a) for a in alts], maxshift) if (n and use_segments) else np.zeros(n, bool)
     elig, rest = np.flatnonzero(ok), np.flatnonzero(~ok)

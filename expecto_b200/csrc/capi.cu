@@ -162,12 +162,13 @@ struct bx_ctx {
   struct ChromPlan* plan = nullptr;  // bx_chromatin_open .. bx_chromatin_close
 };
 
-// Where the variant path's FC2 epilogue puts ref / alt / diff (see ChromEpi): device arrays, rows of 2002 floats.
+// Where the variant path's FC2 epilogue puts ref / alt / diff (see ChromEpi): device arrays, rows ld floats apart.
 struct ChromSink {
   float* ref; float* alt; float* diff;
   const int* dst;                                  // device [group size]: output row of each group member (or null)
   long long shift_stride, strand_stride, row0;
   int average;
+  long long ld = BX_FEATURES;
 };
 
 // RAII-ish stage timer: records an event pair around a stage when profiling is on.
@@ -457,6 +458,7 @@ static ChromEpi make_chrom(const bx_ctx* c, const ChromSink& s, int mode, int ng
   e.dst = s.dst;
   e.si_of_k = c->si_of_k_dev;
   e.shift_stride = s.shift_stride; e.strand_stride = s.strand_stride; e.row0 = s.row0;
+  e.ld = s.ld;
   e.first = first;
   e.mode = mode; e.ng = ng; e.S = n_shifts; e.si_fixed = si_fixed; e.average = s.average;
   return e;
@@ -1078,10 +1080,12 @@ int bx_score_prepare_weights(const float* w_dev, int n_models, void* wp_dev, voi
   return 0;
 }
 
-int bx_decay_score_variant_tc(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const double* dist_dev, const int8_t* strand_dev,
                               const int32_t* shifts_dev, const void* wp_dev, const float* offset_dev, int n,
                               int n_shifts, int n_models, float* out_dev, void* stream) {
   if (n < 0 || n_models < 1) return fail(BX_E_ARG, "invalid arguments");
+  if (x_row_pitch < BX_FEATURES || (x_row_pitch & 1))
+    return fail(BX_E_ARG, "x_row_pitch must be an even number of floats >= %d", BX_FEATURES);
   if (n_shifts != kScShifts)
     return fail(BX_E_ARG, "the tensor-core scoring kernel is built for %d shifts (--maxshift 800); got %d", kScShifts, n_shifts);
   if (n == 0) return 0;
@@ -1098,7 +1102,7 @@ int bx_decay_score_variant_tc(const float* x_dev, const double* dist_dev, const 
   for (int m0 = 0; m0 < n_models; m0 += 256) {
     const int m = std::min(256, n_models - m0), n_pad = score_group_pad(m);
     ScoreParams p = {};
-    p.x = x_dev; p.dist = dist_dev; p.strand = strand_dev; p.shifts = shifts_dev;
+    p.x = x_dev; p.ld_x = x_row_pitch; p.dist = dist_dev; p.strand = strand_dev; p.shifts = shifts_dev;
     p.offset = offset_dev + m0;
     p.out = out_dev + m0;
     p.ld_out = n_models;
@@ -1580,6 +1584,7 @@ struct ChromPlan {
   float* stage[2][3] = {};                   // ref / alt / diff staging, [S][2][chunk][2002] each
   cudaEvent_t ev_done[2] = {}, ev_copied[2] = {};
   int set_chunk[2] = {-1, -1};
+  int64_t out_pitch = BX_FEATURES;           // row pitch of bx_chromatin_submit_device's outputs
   VariantCols cols() const { return VariantCols{gpos, ref_len, alt_len, ref_aoff, alt_aoff}; }
 };
 
@@ -1644,8 +1649,8 @@ int run_plan_chunk(bx_ctx* c, int k, ChromSink sink, cudaStream_t st) {
       const int64_t v0m = std::min<int64_t>(p->chunk, p->n - v0);
       for (float* t : {sink.alt, sink.diff})
         for (int si = 0; si < p->S; ++si)
-          CK(cudaMemsetAsync(t + (size_t)(si * sink.shift_stride + sink.row0) * BX_FEATURES, 0,
-                             (size_t)v0m * BX_FEATURES * sizeof(float), st));
+          CK(cudaMemsetAsync(t + (size_t)(si * sink.shift_stride + sink.row0) * sink.ld, 0,
+                             (size_t)v0m * sink.ld * sizeof(float), st));
     }
     if (int r = forward_segments_impl(c, rd, pd, p->alleles, nd, 4, p->seg_len, p->patch_len, p->patch_row0, p->S,
                                       p->k_of_shift, 1, nullptr, st, &sink))
@@ -1843,7 +1848,16 @@ int bx_chromatin_submit_device(bx_ctx* c, int chunk, float* ref_dev, float* alt_
   sink.strand_stride = strand_stride_rows;
   sink.row0 = row0;
   sink.average = (p->flags & BX_CHROM_AVERAGE) ? 1 : 0;
+  sink.ld = p->out_pitch;
   return run_plan_chunk(c, chunk, sink, (cudaStream_t)stream);
+}
+
+int bx_chromatin_set_row_pitch(bx_ctx* c, int64_t row_pitch) {
+  if (!c || !c->plan) return fail(BX_E_STATE, "no open variant plan (bx_chromatin_open)");
+  if (row_pitch < BX_FEATURES || (row_pitch & 1))
+    return fail(BX_E_ARG, "row_pitch must be an even number of floats >= %d", BX_FEATURES);
+  c->plan->out_pitch = row_pitch;
+  return 0;
 }
 
 int bx_variant_descs_host(int kind, int64_t n, const int64_t* gpos, const int32_t* ref_len, const int32_t* alt_len,

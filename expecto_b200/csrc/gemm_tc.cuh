@@ -42,7 +42,7 @@ enum EpiKind : int {
 
 // Where the rows of an FC2 launch go in the variant path (EPI_CHROMATIN).  Every GEMM row is one window
 // (variant, shift, q) with q = 0 ref fwd, 1 ref rc, 2 alt fwd, 3 alt rc; its probabilities land in
-//   X[(si * shift_stride + (q & 1) * strand_stride + row0 + dst(grp)) * 2002 + feature],  X = ref (q < 2) or alt,
+//   X[(si * shift_stride + (q & 1) * strand_stride + row0 + dst(grp)) * ld + feature],  X = ref (q < 2) or alt,
 // and alt rows also produce diff = alt - ref of the same strand.  Row order of the launch:
 //   mode 0: (si, grp, q) shift-major quads [segment mode, four full segments per variant]
 //   mode 1: delta mode's ref rows  d = (si * ng + grp) * 2 + t
@@ -62,7 +62,8 @@ struct ChromEpi {
   float* ref_scratch;            // average && delta mode: per-strand ref rows [S][2][ng] (dense, dst ignored)
   const int* dst;                // [ng] local output row of each group member, or nullptr = identity
   const int* si_of_k;            // [S] device table (mode 2)
-  long long shift_stride, strand_stride, row0;   // in rows of 2002 floats
+  long long shift_stride, strand_stride, row0;   // in rows of ld floats
+  long long ld;                  // row pitch of ref / alt / diff: 2002, or padded (bx_chromatin_set_row_pitch)
   long long first;               // index of the launch's first row in its mode's row order
   int mode, ng, S, si_fixed, average;
 };
@@ -512,7 +513,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         } else { cq = (int)(d & 3); grp = (int)(d >> 2); si = ce.si_fixed; }
         const int t = cq & 1;
         const long long v = ce.row0 + ((ce.dst != nullptr && valid) ? ce.dst[grp] : grp);
-        crow = (size_t)(si * ce.shift_stride + (ce.average ? 0 : t * ce.strand_stride) + v) * 2002;
+        crow = (size_t)(si * ce.shift_stride + (ce.average ? 0 : t * ce.strand_stride) + v) * (size_t)ce.ld;
         cscr = ((size_t)((size_t)si * 2 + t) * ce.ng + grp) * 2002;
       }
 

@@ -39,7 +39,8 @@ constexpr int kScATile = 128 * 128;          // one [128 x 64] fp16 operand tile
 constexpr int kScThreads = 320;
 
 struct ScoreParams {
-  const float* x;          // [9, n, 2002]
+  const float* x;          // [9, n, ld_x]: row pitch ld_x >= 2002 floats (columns >= 2002 are never read)
+  long long ld_x;
   const double* dist;      // [n] variant - TSS (predict.py:241)
   const int8_t* strand;    // [n] +1 / -1
   const int32_t* shifts;   // [9]
@@ -138,7 +139,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
       for (int ps = 0; ps < 2; ++ps) {
         const long long row = (long long)t * 256 + rank * 128 + warp * 16 + ps * 8 + rw;
         valid[ps] = row < p.n;
-        xrow[ps] = p.x + (size_t)(valid[ps] ? row : 0) * 2002;
+        xrow[ps] = p.x + (size_t)(valid[ps] ? row : 0) * (size_t)p.ld_x;
         const double d = valid[ps] ? p.dist[row] : 0.0;
         const double sgn = (valid[ps] && p.strand[row] > 0) ? 1.0 : -1.0;
         negm[ps] = posm[ps] = 0;
@@ -151,7 +152,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
           y[ps][j] = (float)exp(-0.01 * b);
         }
       }
-      const size_t shift_stride = (size_t)p.n * 2002;
+      const size_t shift_stride = (size_t)p.n * (size_t)p.ld_x;
       auto load_chunk = [&](int f0, float2 (&xv)[2][kScShifts]) {
 #pragma unroll
         for (int ps = 0; ps < 2; ++ps)

@@ -226,10 +226,20 @@ class BelugaEngine:
     def chromatin_submit_device(self, k: int, ref: torch.Tensor, alt: torch.Tensor, diff: torch.Tensor,
                                 shift_stride: int, strand_stride: int, row0: int) -> None:
         """Chunk ``k`` with the results left in HBM on the current stream: row (shift si, strand t, variant v of the
-        chunk) goes to row ``si * shift_stride + t * strand_stride + row0 + v`` of each [rows, 2002] device tensor."""
+        chunk) goes to row ``si * shift_stride + t * strand_stride + row0 + v`` of each [..., 2002] device tensor.
+        The tensors are dense, or dense apart from a common row padding (``transform.padded_rows``: the row pitch is
+        handed to the library with bx_chromatin_set_row_pitch)."""
+        pitches = set()
         for t in (ref, alt, diff):
-            if not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
-                raise ValueError("chromatin_submit_device takes contiguous float32 CUDA tensors")
+            if not t.is_cuda or t.dtype != torch.float32 or t.dim() < 2 or t.shape[-1] != N_FEATURES or t.stride(-1) != 1:
+                raise ValueError("chromatin_submit_device takes float32 CUDA tensors [..., 2002]")
+            pitch = t.stride(-2) if t.shape[-2] > 1 or t.dim() == 2 else N_FEATURES
+            if any(t.shape[i] > 1 and t.stride(i) != t.stride(i + 1) * t.shape[i + 1] for i in range(t.dim() - 2)):
+                raise ValueError("chromatin_submit_device: only the rows may be padded")
+            pitches.add(int(pitch))
+        if len(pitches) != 1:
+            raise ValueError("ref / alt / diff must share one row pitch")
+        check(lib().bx_chromatin_set_row_pitch(self._ctx, pitches.pop()))
         check(lib().bx_chromatin_submit_device(self._ctx, k, ref.data_ptr(), alt.data_ptr(), diff.data_ptr(),
                                                int(shift_stride), int(strand_stride), int(row0), _stream_ptr(self.device)))
 

@@ -144,7 +144,7 @@ def load_strand_averaged(pattern: str, maxshift: int, keys=("diff", "ref", "alt"
     import torch
 
     from . import hdf5
-    from .transform import strand_average
+    from .transform import padded_rows, strand_average
 
     shifts = shift_list(maxshift)
     out = {}
@@ -157,7 +157,7 @@ def load_strand_averaged(pattern: str, maxshift: int, keys=("diff", "ref", "alt"
                     d = f[k]
                     n = int(d.shape[0] / 2)
                     if k not in out:
-                        out[k] = torch.empty((len(shifts), n, 2002), dtype=torch.float32, device=device)
+                        out[k] = padded_rows((len(shifts), n), device)   # rows on 128-byte boundaries for the scoring kernel
                     x = torch.empty((2 * n, 2002), dtype=torch.float32, device=device)
                     jobs = []
                     for r0 in range(0, 2 * n, slab_rows):
@@ -178,7 +178,7 @@ def load_strand_averaged(pattern: str, maxshift: int, keys=("diff", "ref", "alt"
                         x[a0:a1].copy_(ring[sl][0][:a1 - a0], non_blocking=True)
                         ring[sl][1] = torch.cuda.Event()
                         ring[sl][1].record(torch.cuda.current_stream(device))
-                    strand_average(x, out=out[k][si])
+                    out[k][si].copy_(strand_average(x))
                     del x
     torch.cuda.synchronize(device)
     return out
@@ -289,7 +289,7 @@ def _chromatin_blocks(args, dev, engine=None, genome=None):
     for v0 in range(0, n, args.vcf_block):
         v1 = min(n, v0 + args.vcf_block)
         data = chromatin.predict_all_shifts_averaged_device(engine, genome, chroms[v0:v1], pos[v0:v1], refs[v0:v1],
-                                                            alts[v0:v1], int(args.maxshift))
+                                                            alts[v0:v1], int(args.maxshift), padded=True)
         data.pop("diff")
         yield v0, v1, data
         del data
@@ -300,7 +300,7 @@ def run(args, engine=None, genome=None) -> dict:
     import torch
 
     from .gblinear import load_model
-    from .transform import ScoreModels, decay_score_variant
+    from .transform import ScoreModels, decay_score_variant, select_variants
 
     if not torch.cuda.is_available():
         raise RuntimeError("predict needs a CUDA device (B200); there is no CPU fallback")
@@ -366,7 +366,7 @@ def run(args, engine=None, genome=None) -> dict:
             identity = len(local) == v1 - v0 and bool(np.array_equal(local, np.arange(v1 - v0)))
             sel = None if identity else torch.from_numpy(local).to(dev)
             for key in ("ref", "alt"):
-                x = data[key] if identity else data[key].index_select(1, sel)
+                x = data[key] if identity else select_variants(data[key], sel)
                 scores[key][rows] = decay_score_variant(x, dist[rows], strand[rows], models, shifts=shifts).cpu().numpy()
         del data
         lap("chromatin_and_score_s" if args.vcf else "score_s")

@@ -71,9 +71,40 @@ def chromatin_shifts(maxshift: int = 800) -> list[int]:
     return [0] + list(range(-200, -maxshift - 1, -200)) + list(range(200, maxshift + 1, 200))  # predict.py:173
 
 
-def _variant_args(x: torch.Tensor, dist, strand, shifts):
+X_PITCH = 2016   # row pitch (floats) of averaged chromatin effects kept for scoring: rows on 128-byte boundaries
+
+
+def padded_rows(shape_prefix, device) -> torch.Tensor:
+    """float32 [..., 2002] view of a buffer whose rows are X_PITCH floats apart (what ``decay_score_variant``'s
+    tensor-core kernel reads fastest: 8008-byte rows make most of its 32-byte reads straddle two DRAM sectors)."""
+    buf = torch.empty(tuple(shape_prefix) + (X_PITCH,), dtype=torch.float32, device=device)
+    return buf[..., :N_FEATURES]
+
+
+def select_variants(x: torch.Tensor, sel: torch.Tensor) -> torch.Tensor:
+    """``x.index_select(1, sel)`` of a [S, n, 2002] tensor that keeps the row padding of ``padded_rows`` tensors (the
+    result of a plain index_select is dense, i.e. back on 8008-byte rows)."""
+    S, n, f = x.shape
+    pitch = _row_pitch(x)
+    if pitch <= f or x.stride(0) != n * pitch:
+        return x.index_select(1, sel)
+    return x.as_strided((S, n, pitch), (n * pitch, pitch, 1)).index_select(1, sel)[..., :f]
+
+
+def _row_pitch(x: torch.Tensor) -> int:
+    """Row pitch of a [S,n,2002] tensor that is dense apart from row padding, or 0."""
+    S, n, f = x.shape
+    st = x.stride()
+    if st[2] != 1 or st[1] < f or (n > 1 and S > 1 and st[0] != st[1] * n):
+        return 0
+    return int(st[1]) if n > 1 else (int(st[0]) if S > 1 and st[0] >= f else f)
+
+
+def _variant_args(x: torch.Tensor, dist, strand, shifts, allow_pitch: bool = False):
     if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 3 or x.shape[2] != N_FEATURES:
         raise ValueError("x must be a CUDA float32 tensor [S,n,2002]")
+    if not (allow_pitch and _row_pitch(x) >= N_FEATURES and _row_pitch(x) % 2 == 0):
+        x = x.contiguous()
     S, n = x.shape[:2]
     shifts_dev = shifts if isinstance(shifts, torch.Tensor) and shifts.is_cuda else None
     if shifts_dev is None:
@@ -87,7 +118,7 @@ def _variant_args(x: torch.Tensor, dist, strand, shifts):
         if dist.dtype != torch.float64 or strand.dtype != torch.int8 or dist.numel() != n or strand.numel() != n:
             raise ValueError("device-resident dist/strand must be float64 / int8 (+1, -1) with one entry per variant")
         sh = shifts_dev if shifts_dev is not None else torch.tensor(shifts, dtype=torch.int32, device=x.device)
-        return x.contiguous(), dist.contiguous(), strand.contiguous(), sh.contiguous(), n, S
+        return x, dist.contiguous(), strand.contiguous(), sh.contiguous(), n, S
     st = np.asarray(strand)
     if st.dtype.kind in "USO":  # '+' / '-' as predict.py:90 compares them (pandas 3 hands back object arrays)
         sgn = np.where(np.asarray([str(v) for v in st.ravel()]) == "+", 1, -1).astype(np.int8)
@@ -98,7 +129,7 @@ def _variant_args(x: torch.Tensor, dist, strand, shifts):
     sh = shifts_dev if shifts_dev is not None else torch.tensor(shifts, dtype=torch.int32, device=x.device)
     if d.numel() != n or sg.numel() != n:
         raise ValueError("dist/strand must have one entry per variant")
-    return x.contiguous(), d, sg, sh, n, S
+    return x, d, sg, sh, n, S
 
 
 def decay_transform_variant(x: torch.Tensor, dist, strand, shifts=None, out: torch.Tensor | None = None) -> torch.Tensor:
@@ -146,16 +177,17 @@ def decay_score_variant(x: torch.Tensor, dist, strand, weights, offsets=None, sh
     never materialised.  With the nine shifts of --maxshift 800 the contraction runs as one tcgen05 GEMM whose feature
     tiles are generated in shared memory (bx_decay_score_variant_tc); other shift counts, or ``tensor_cores=False``,
     use the SIMT kernel (bx_decay_score_variant)."""
-    x, d, sg, sh, n, S = _variant_args(x, dist, strand, shifts)
+    use_tc = (x.shape[0] == 9) if tensor_cores is None else bool(tensor_cores)
+    x, d, sg, sh, n, S = _variant_args(x, dist, strand, shifts, allow_pitch=use_tc)
     models = weights if isinstance(weights, ScoreModels) else ScoreModels(weights, offsets, x.device)
     if models.device != x.device:
         raise ValueError("models are staged on another device")
     m = models.m
     out = torch.empty((n, m), dtype=torch.float32, device=x.device)
-    use_tc = (S == 9) if tensor_cores is None else bool(tensor_cores)
     with torch.cuda.device(x.device):
         if use_tc:
-            check(lib().bx_decay_score_variant_tc(x.data_ptr(), d.data_ptr(), sg.data_ptr(), sh.data_ptr(),
+            pitch = _row_pitch(x) if x.numel() else N_FEATURES
+            check(lib().bx_decay_score_variant_tc(x.data_ptr(), pitch, d.data_ptr(), sg.data_ptr(), sh.data_ptr(),
                                                   models.prepared().data_ptr(), models.off.data_ptr(), n, S, m,
                                                   out.data_ptr(), _stream(x)))
         else:

@@ -213,6 +213,11 @@ int bx_chromatin_wait(bx_ctx* ctx, int chunk);
  * tensors the decay transform reads. */
 int bx_chromatin_submit_device(bx_ctx* ctx, int chunk, float* ref_dev, float* alt_dev, float* diff_dev,
                                int64_t shift_stride_rows, int64_t strand_stride_rows, int64_t row0, void* stream);
+/* Row pitch, in floats, of the device arrays bx_chromatin_submit_device writes (default 2002 = dense rows; even,
+ * >= 2002; the padding columns are left untouched, except that averaged plans zero whole rows first).  The drop-in's
+ * predict path keeps its averaged effects at 2016 so that rows start on 128-byte boundaries, which is what
+ * bx_decay_score_variant_tc reads fastest.  Applies to the open plan; the host-buffer path is always dense. */
+int bx_chromatin_set_row_pitch(bx_ctx* ctx, int64_t row_pitch);
 int bx_chromatin_close(bx_ctx* ctx);
 /* Test hook: the device descriptor builders on HOST columns.  kind 0: four full segments per variant (ref fwd, ref
  * rc, alt fwd, alt rc); kind 1: delta mode, out_host[0 .. 2n) the ref segments and out_host[2n .. 4n) the alt patches,
@@ -227,10 +232,13 @@ int bx_variant_descs_host(int kind, int64_t n, const int64_t* gpos, const int32_
  * to the kernel's operand layout — fp16 (hi, lo) pairs, K axis permuted to the order the feature tiles are generated
  * in — with bx_score_prepare_weights into a caller-owned device buffer of bx_score_weights_bytes(n_models) bytes;
  * bx_decay_score_variant_tc then takes that buffer.  n_shifts must be 9 (--maxshift 800); every product is
- * Ah*Wh + Ah*Wl + Al*Wh with fp32 accumulation, so scores agree with the float64 reference to ~1e-6 relative. */
+ * Ah*Wh + Ah*Wl + Al*Wh with fp32 accumulation, so scores agree with the float64 reference to ~5e-5 of their scale.
+ * x_dev is [9, n, x_row_pitch] floats, x_row_pitch >= 2002 (even): rows of exactly 2002 floats work, but they are
+ * 8008 bytes apart, so three in four of the kernel's 32-byte reads straddle two DRAM sectors; a pitch of 2016 floats
+ * (rows on 128-byte boundaries) is what the drop-in's own producers use and about 1.4x as fast. */
 int64_t bx_score_weights_bytes(int n_models);
 int bx_score_prepare_weights(const float* w_dev, int n_models, void* wp_dev, void* stream);
-int bx_decay_score_variant_tc(const float* x_dev, const double* dist_dev, const int8_t* strand_dev,
+int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const double* dist_dev, const int8_t* strand_dev,
                               const int32_t* shifts_dev, const void* wp_dev, const float* offset_dev, int n,
                               int n_shifts, int n_models, float* out_dev, void* stream);
 

@@ -234,3 +234,42 @@ def test_fused_epilogue_writes_only_its_own_rows(engine, small_genome, average):
         assert not bool((o[owned] == SENT).any()), name
         if name != "diff":
             assert bool(((o[owned] > 0) & (o[owned] < 1)).all()), name
+
+
+@pytest.mark.parametrize("average", [False, True])
+def test_device_outputs_with_padded_rows_equal_dense_outputs(engine, small_genome, average):
+    """bx_chromatin_set_row_pitch: the FC2 epilogue writing rows 2016 floats apart (what predict keeps for the scoring
+    kernel) gives the dense call's values bit for bit; the padding columns keep their sentinel, except that averaged
+    plans zero whole rows before delta mode's alt rows add their halves (alt / diff padding reads 0 or the sentinel)."""
+    from expecto_b200.transform import X_PITCH
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    rows = _variants(small_genome, n_random=12)
+    n = len(rows)
+    S, SENT = 9, -5.5
+    rows_per_shift = n if average else 2 * n
+    res = {}
+    for pitch in (2002, X_PITCH):
+        bufs = [torch.full((S * rows_per_shift, pitch), SENT, device=engine.device) for _ in range(3)]
+        outs = [b[:, :2002].view(S, rows_per_shift, 2002) if pitch == 2002 else b[:, :2002].unflatten(0, (S, rows_per_shift))
+                for b in bufs]
+        n_chunks, _ = engine.chromatin_open(_cols(pg, rows), 800, average=average, chunk_variants=7)
+        for k in range(n_chunks):
+            engine.chromatin_submit_device(k, *outs, rows_per_shift, n, engine.chromatin_chunk_info(k)["v0"])
+        engine.chromatin_close()
+        torch.cuda.synchronize()
+        res[pitch] = (bufs, outs)
+    for name, d, p_, pb in zip(("ref", "alt", "diff"), res[2002][1], res[X_PITCH][1], res[X_PITCH][0]):
+        assert not bool((d == SENT).any()) and torch.equal(d, p_), name
+        tail = pb[:, 2002:]
+        assert bool(((tail == SENT) | ((tail == 0) if (average and name != "ref") else False)).all()), name
+    # a later dense call on the same context is dense again (the pitch belongs to the plan)
+    dense2 = [torch.empty((S, rows_per_shift, 2002), device=engine.device) for _ in range(3)]
+    n_chunks, _ = engine.chromatin_open(_cols(pg, rows), 800, average=average)
+    for k in range(n_chunks):
+        engine.chromatin_submit_device(k, *dense2, rows_per_shift, n, engine.chromatin_chunk_info(k)["v0"])
+    engine.chromatin_close()
+    for a, b in zip(dense2, res[2002][1]):
+        assert torch.equal(a, b)
+    with pytest.raises(ValueError):
+        engine.chromatin_submit_device(0, res[2002][1][0], res[X_PITCH][1][1], res[X_PITCH][1][2], rows_per_shift, n, 0)

@@ -256,6 +256,37 @@ def test_tensor_core_scoring_kernel_vs_float64_oracle(n, m):
     assert np.array_equal(decay_score_variant(xd, dist, strand, models).cpu().numpy(), tc)
 
 
+def test_tensor_core_scoring_padded_rows_equal_dense_rows_bitwise():
+    """x with rows X_PITCH floats apart (transform.padded_rows: what FC2's epilogue leaves for predict) against the same
+    values in dense 8008-byte rows: identical scores, the padding columns (NaN here) are never read; select_variants
+    keeps the padding through a gene-row gather; odd pitches and pitches below 2002 are refused by the library."""
+    import ctypes as C
+
+    from expecto_b200 import _lib
+    from expecto_b200.transform import X_PITCH, ScoreModels, decay_score_variant, padded_rows, select_variants, _row_pitch
+    rng = np.random.default_rng(17)
+    n, m = 300, 37
+    buf = torch.full((9, n, X_PITCH), float("nan"), device="cuda")
+    x = buf[..., :2002]
+    x.copy_(torch.from_numpy(rng.random((9, n, 2002)).astype(np.float32)))
+    assert _row_pitch(x) == X_PITCH and _row_pitch(padded_rows((9, 5), "cuda")) == X_PITCH
+    dist = rng.integers(-3000, 3000, size=n).astype(np.float64)
+    strand = np.where(rng.random(n) < 0.5, "+", "-")
+    models = ScoreModels((rng.standard_normal((m, 20020)) * 0.01).astype(np.float32), rng.standard_normal(m).astype(np.float32), "cuda:0")
+    padded = decay_score_variant(x, dist, strand, models)
+    dense = decay_score_variant(x.contiguous(), dist, strand, models)
+    assert torch.isfinite(padded).all() and torch.equal(padded, dense)
+    sel = torch.from_numpy(rng.integers(0, n, size=211)).cuda()
+    xs = select_variants(x, sel)
+    assert _row_pitch(xs) == X_PITCH and torch.equal(xs, x.index_select(1, sel))
+    assert torch.equal(decay_score_variant(xs, dist[sel.cpu().numpy()], strand[sel.cpu().numpy()], models), dense[sel])
+    L = _lib.lib()
+    out = torch.empty((n, m), device="cuda")
+    for bad in (2001, 2003, 0):
+        assert L.bx_decay_score_variant_tc(x.data_ptr(), bad, None, None, None, None, None, n, 9, m, out.data_ptr(), None) == _lib.BX_E_ARG
+        assert b"x_row_pitch" in L.bx_last_error()
+
+
 def test_predict_cli_matches_predict_script(engine, cfg1_genome, golden, tmp_path):
     """chromatin CLI -> predict CLI (fused transform + scoring) vs the reference predict.py's sed.tsv."""
     import pandas as pd

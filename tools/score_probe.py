@@ -7,7 +7,8 @@ from expecto_b200.transform import ScoreModels, decay_score_variant, chromatin_s
 n, m = 74 * 256 * int(sys.argv[1] if len(sys.argv) > 1 else 1), 218
 rng = np.random.default_rng(0)
 dev = torch.device("cuda:0")
-x = torch.rand((9, n, 2002), dtype=torch.float32, device=dev)
+pitch = int(sys.argv[2]) if len(sys.argv) > 2 else 2002
+x = torch.rand((9, n, pitch), dtype=torch.float32, device=dev)[..., :2002]
 dist = torch.from_numpy(rng.integers(-40000, 40000, size=n).astype(np.float64)).to(dev)
 strand = torch.from_numpy(np.where(np.arange(n) % 2 == 0, 1, -1).astype(np.int8)).to(dev)
 shifts = torch.tensor(chromatin_shifts(800), dtype=torch.int32, device=dev)
@@ -22,4 +23,4 @@ for _ in range(5):
     out = decay_score_variant(x, dist, strand, models, shifts=shifts)
 e1.record()
 torch.cuda.synchronize()
-print("ms per launch", e0.elapsed_time(e1) / 5, "variants", n)
+print("pitch", pitch, "ms per launch", e0.elapsed_time(e1) / 5, "variants", n)
