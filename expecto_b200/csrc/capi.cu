@@ -1099,6 +1099,24 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
   int sms = 0;
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const __half* wp = reinterpret_cast<const __half*>(wp_dev);
+  // Rows on 16-byte boundaries: x is staged by TMA (score_tma_kernel).  Otherwise (e.g. dense 8008-byte rows) the
+  // kernel that loads x through registers (score_tc_kernel); same operand layout, same results.
+#ifndef BX_SC_L2PROMO
+#define BX_SC_L2PROMO CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+#endif
+  const bool x_tma = (x_row_pitch % 4 == 0) && (reinterpret_cast<uintptr_t>(x_dev) % 16 == 0) && !getenv("BX_SCORE_NO_TMA");
+  CUtensorMap tmX;
+  if (x_tma) {
+    cuuint64_t dims[3] = {(cuuint64_t)BX_FEATURES, (cuuint64_t)n, (cuuint64_t)kScShifts};
+    cuuint64_t strides[2] = {(cuuint64_t)x_row_pitch * 4, (cuuint64_t)n * (cuuint64_t)x_row_pitch * 4};
+    cuuint32_t box[3] = {8, 128, (cuuint32_t)kScShifts};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = g_encode(&tmX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(x_dev), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, BX_SC_L2PROMO,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+      return fail(BX_E_CUDA, "cuTensorMapEncodeTiled failed for x: %d (n=%d pitch=%lld)", (int)r, n, (long long)x_row_pitch);
+  }
   for (int m0 = 0; m0 < n_models; m0 += 256) {
     const int m = std::min(256, n_models - m0), n_pad = score_group_pad(m);
     ScoreParams p = {};
@@ -1109,20 +1127,29 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
     p.n = n; p.m = m; p.n_pad = n_pad;
     p.tiles = (n + 255) / 256;
     p.idesc = make_idesc_f16(0, 256, n_pad);
-    p.sb_stages = 3;
-    const size_t smem = (size_t)(2 + 2) * 2 * kScATile + (size_t)p.sb_stages * 2 * (n_pad / 2) * 128 + 256 + 1024;
+    const size_t b_stage = (size_t)2 * (n_pad / 2) * 128;
+    size_t smem;
+    if (x_tma) {   // x stages + A ring (2) + K stage, the rest of the 227 KB for the weight ring
+      const size_t fixed = (size_t)kScXStages * kScXStage + (size_t)3 * 2 * kScATile + 256 + 1024;
+      p.sb_stages = (int)std::min<size_t>(4, (232448 - fixed) / b_stage);
+      smem = fixed + p.sb_stages * b_stage;
+    } else {
+      p.sb_stages = 3;
+      smem = (size_t)(2 + 2) * 2 * kScATile + (size_t)p.sb_stages * b_stage + 256 + 1024;
+    }
     CUtensorMap tmW;
     if (int r = make_tmap(&tmW, BX_DTYPE_F16, wp, (uint64_t)n_pad, (uint64_t)2 * kScK, (uint64_t)2 * kScK, (uint32_t)(n_pad / 2)))
       return r;
-    static std::atomic<size_t> attr_smem[kMaxDevices];
-    if (attr_smem[dev].load(std::memory_order_acquire) < smem) {
-      CK(cudaFuncSetAttribute(score_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_smem[dev].store(smem, std::memory_order_release);
+    static std::atomic<size_t> attr_smem[2][kMaxDevices];
+    if (attr_smem[x_tma][dev].load(std::memory_order_acquire) < smem) {
+      if (x_tma) CK(cudaFuncSetAttribute(score_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      else CK(cudaFuncSetAttribute(score_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_smem[x_tma][dev].store(smem, std::memory_order_release);
     }
     const int clusters = std::max(1, std::min(p.tiles, sms / 2));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(clusters * 2);
-    cfg.blockDim = dim3(kScThreads);
+    cfg.blockDim = dim3(x_tma ? kScTmaThreads : kScThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
@@ -1130,7 +1157,8 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CK(cudaLaunchKernelEx(&cfg, score_tc_kernel, tmW, p));
+    if (x_tma) CK(cudaLaunchKernelEx(&cfg, score_tma_kernel, tmW, tmX, p));
+    else CK(cudaLaunchKernelEx(&cfg, score_tc_kernel, tmW, p));
     g_launches++;
     wp += (size_t)n_pad * 2 * kScK;
   }

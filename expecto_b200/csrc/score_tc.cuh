@@ -37,6 +37,9 @@ constexpr int kScK = kScKBlocks * 64;        // 20160 permuted K columns (2016 f
 constexpr int kScShifts = 9;                 // chromatin.py:243 with the default --maxshift 800
 constexpr int kScATile = 128 * 128;          // one [128 x 64] fp16 operand tile
 constexpr int kScThreads = 320;
+#ifndef BX_SC_XPF
+#define BX_SC_XPF 0   // experiment: L2 prefetch of the x chunk this many chunks ahead of its TMA load
+#endif
 
 struct ScoreParams {
   const float* x;          // [9, n, ld_x]: row pitch ld_x >= 2002 floats (columns >= 2002 are never read)
@@ -312,6 +315,375 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
         accum = 1;
         if (++rb.idx == (uint32_t)p.sb_stages) { rb.idx = 0; rb.phase ^= 1; }
         if (k89) rk.advance<SK>(); else ra.advance<SA>();
+      }
+      if (elect_one()) umma_commit<2>(tfull);
+      __syncwarp();
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc<2>(tmem_base, 512);
+  }
+}
+
+
+// ====================================================================================================================
+// The same GEMM with x staged through shared memory by TMA (rows on 16-byte boundaries: row pitch a multiple of four
+// floats — what the drop-in's own producers write, transform.padded_rows).  The kernel above keeps its loads in
+// registers one chunk ahead, which is all the latency hiding 168 registers allow, and spends its time in
+// long-scoreboard stalls (profiles/r02_ncu_score_tc.txt).  Here a producer lane copies each chunk — the box
+// [8 features x 128 rows x 9 shifts] = 36 KB per CTA — with one cp.async.bulk.tensor two chunks ahead of its use, at no
+// register or issue cost to the generators; rows past n and features past 2002 arrive as zeros (TMA bounds), and the
+// shared-memory budget is met by a one-stage ring for the k = 8, 9 K-blocks and a two-stage weight ring.  The
+// generators' arithmetic is packed (FFMA2) and takes a five-sum path when every row of a warp has its nine shifts on
+// one side of the TSS (|distance| > 800: all but ~2 % of variants).  Operand layout, weight permutation, MMA order and
+// therefore every bit of the result are those of the kernel above.
+constexpr int kScXStage = kScShifts * 128 * 32;   // one chunk of one CTA: [9 shifts][128 rows][8 floats]
+constexpr int kScXStages = 2;
+constexpr int kScTmaThreads = 352;                // + warp 10: x producer
+
+__device__ __forceinline__ uint64_t pack2f(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ float2 unpack2f(uint64_t v) {
+  float2 r;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+  return r;
+}
+// Packed fp32 pairs (FMUL2 / FFMA2 on sm_100): each half is the scalar .rn operation.
+__device__ __forceinline__ uint64_t fmul2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// (v, v) as a packed pair.  volatile: pins the powers of y that are formed from it to the place they are used
+// (hoisted out of the chunk loop they would cost 180 registers).
+__device__ __forceinline__ uint64_t dup2f(float v) {
+  uint64_t r;
+  asm volatile("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(v));
+  return r;
+}
+
+__global__ void __launch_bounds__(kScTmaThreads, 1)
+score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const ScoreParams p) {
+  constexpr int SA = 2;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t b_half = (uint32_t)(p.n_pad / 2) * 128u;          // one weight tile (hi or lo) of this CTA
+  const uint32_t sX = base;                                        // kScXStages chunks of x
+  const uint32_t sA = sX + kScXStages * kScXStage;                 // SA x (hi, lo)
+  const uint32_t sK = sA + SA * 2 * kScATile;                      // (hi, lo): the k = 8, 9 K-block of a super-block
+  const uint32_t sB = sK + 2 * kScATile;                           // sb_stages x (hi, lo)
+  const uint32_t bars = sB + (uint32_t)p.sb_stages * 2 * b_half;
+  auto fullA = [&](uint32_t i) { return bars + 8u * i; };
+  auto emptyA = [&](uint32_t i) { return bars + 8u * (2 + i); };
+  const uint32_t fullK = bars + 8u * 4, emptyK = bars + 8u * 5;
+  auto fullX = [&](uint32_t i) { return bars + 8u * (6 + i); };
+  auto emptyX = [&](uint32_t i) { return bars + 8u * (8 + i); };
+  auto fullB = [&](uint32_t i) { return bars + 8u * (10 + i); };
+  auto emptyB = [&](uint32_t i) { return bars + 8u * (14 + i); };
+  const uint32_t tfull = bars + 8u * 18, tempty = bars + 8u * 19, tmem_slot = bars + 8u * 20;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int num_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
+
+  if (warp == 8 && lane == 0) {
+    prefetch_tensormap(&tmW);
+    prefetch_tensormap(&tmX);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(fullA(i), 16); mbar_init(emptyA(i), 1);     // 8 generator warps in each CTA of the pair
+      mbar_init(fullX(i), 1); mbar_init(emptyX(i), 8);      // per CTA: its own 128 rows of x
+    }
+    mbar_init(fullK, 16); mbar_init(emptyK, 1);
+    for (int i = 0; i < 4; ++i) { mbar_init(fullB(i), 1); mbar_init(emptyB(i), 1); }
+    mbar_init(tfull, 1);
+    mbar_init(tempty, 16);
+    fence_barrier_init();
+  }
+  if (warp == 9) tmem_alloc<2>(tmem_slot, 512);   // columns [0, n_pad): Ah*Wh; [256, 256 + n_pad): Ah*Wl + Al*Wh
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  if (warp < 8) {
+    // ------------------------------------------------------------------ feature generators + epilogue
+    // Lane (rw, sub) of warp w: rows w*16 + {0, 8} + rw of this CTA, feature pair 2*sub, 2*sub + 1 of every chunk.
+    const int sub = lane & 3, rw = lane >> 2;
+    RingState ra, rx;
+    uint32_t kphase = 0, tphase = 0;
+    for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      // y = exp(-0.01 * floor(|pos| / 200)) per shift (fp64 like numpy, predict.py:87-109); the five decay rates are
+      // its powers y, y^2, y^5, y^10, y^20.  y and y^5 are kept, the others formed where they are used (same products
+      // in the same order as the kernel above: y2 = y*y, y4 = y2*y2, y5 = y4*y, y10 = y5*y5, y20 = y10*y10).
+      float y[2][kScShifts], y5[2][kScShifts];
+      uint32_t negm[2], posm[2];
+#pragma unroll
+      for (int ps = 0; ps < 2; ++ps) {
+        const long long row = (long long)t * 256 + rank * 128 + warp * 16 + ps * 8 + rw;
+        const bool valid = row < p.n;
+        const double d = valid ? p.dist[row] : 0.0;
+        const double sgn = (valid && p.strand[row] > 0) ? 1.0 : -1.0;
+        negm[ps] = posm[ps] = 0;
+#pragma unroll
+        for (int j = 0; j < kScShifts; ++j) {
+          const double pos = d * sgn + (double)p.shifts[j] * sgn;
+          const double b = floor(fabs(pos / 200.0));
+          if (valid && pos <= 0.0) negm[ps] |= 1u << j;
+          if (valid && pos >= 0.0) posm[ps] |= 1u << j;
+          y[ps][j] = (float)exp(-0.01 * b);
+          const float y2 = y[ps][j] * y[ps][j], y4 = y2 * y2;
+          y5[ps][j] = y4 * y[ps][j];
+        }
+      }
+      // warp-uniform: each of this warp's sixteen rows has all its shifts on one side (or is padding: x reads as zeros)
+      const bool one_sided =
+          __all_sync(0xffffffffu, ((negm[0] == 0) || (posm[0] == 0)) && ((negm[1] == 0) || (posm[1] == 0)));
+      uint32_t late[2][2][2] = {};
+      for (int sb = 0; sb < kScSuper; ++sb) {
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          // this chunk of x: shared memory -> registers, and the stage goes back to the producer at once
+          uint64_t xv[2][kScShifts];
+          mbar_wait(fullX(rx.idx), rx.phase, 21);
+          {
+            const uint8_t* xs = smem_raw + (sX - raw) + rx.idx * kScXStage + (warp * 16 + rw) * 32 + sub * 8;
+#pragma unroll
+            for (int ps = 0; ps < 2; ++ps)
+#pragma unroll
+              for (int j = 0; j < kScShifts; ++j)
+                xv[ps][j] = *reinterpret_cast<const uint64_t*>(xs + j * (128 * 32) + ps * (8 * 32));
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive_local(emptyX(rx.idx));
+          rx.advance<kScXStages>();
+
+          uint8_t* st[2];
+          uint8_t* sk[2];
+          uint32_t swz[2];
+#pragma unroll
+          for (int ps = 0; ps < 2; ++ps) {
+            const int r = warp * 16 + ps * 8 + rw;
+            swz[ps] = (uint32_t)(r & 7);
+            st[ps] = smem_raw + (sA - raw) + ra.idx * 2 * kScATile + r * 128 + sub * 4;
+            sk[ps] = smem_raw + (sK - raw) + r * 128 + sub * 4;
+          }
+          // K-block 5*sb + c holds bases 0..7 (piece k); K-block 5*sb + 4 bases 8, 9 (piece (k - 8) * 4 + chunk)
+          auto put = [&](int ps, int k, uint32_t hi, uint32_t lo) {
+            uint8_t* dst = st[ps] + (((uint32_t)k ^ swz[ps]) << 4);
+            *reinterpret_cast<uint32_t*>(dst) = hi;
+            *reinterpret_cast<uint32_t*>(dst + kScATile) = lo;
+          };
+          auto put89 = [&](int ps, int k, int chunk, uint32_t hi, uint32_t lo) {
+            uint8_t* dst = sk[ps] + (((uint32_t)((k - 8) * 4 + chunk) ^ swz[ps]) << 4);
+            *reinterpret_cast<uint32_t*>(dst) = hi;
+            *reinterpret_cast<uint32_t*>(dst + kScATile) = lo;
+          };
+          // The k = 8, 9 K-block has ONE stage: the MMA hands it back two K-blocks after the previous super-block's
+          // last chunk.  Chunk 0 therefore keeps its four k = 8, 9 pieces in registers (late[]) and chunk 1 stores
+          // them, by which time the stage is free and nobody waits.
+          auto out89 = [&](int ps, int k, uint32_t hi, uint32_t lo) {
+            if (c == 0) { late[ps][k - 8][0] = hi; late[ps][k - 8][1] = lo; }
+            else put89(ps, k, c, hi, lo);
+          };
+          // chunk 1, before any of its own k = 8, 9 stores: wait for the stage, then chunk 0's pieces
+          auto flush_late = [&]() {
+            if (c != 1) return;
+            mbar_wait(emptyK, kphase ^ 1, 12);
+#pragma unroll
+            for (int ps = 0; ps < 2; ++ps)
+#pragma unroll
+              for (int k = 8; k < 10; ++k) put89(ps, k, 0, late[ps][k - 8][0], late[ps][k - 8][1]);
+          };
+          // sums over the shifts selected by mask, for the five decay rates
+          auto side_sums = [&](int ps, bool masked, uint32_t mask, uint64_t (&acc)[5]) {
+#pragma unroll
+            for (int q = 0; q < 5; ++q) acc[q] = 0ull;
+#pragma unroll
+            for (int j = 0; j < kScShifts; ++j) {
+              const uint64_t xsel = (!masked || ((mask >> j) & 1u)) ? xv[ps][j] : 0ull;
+              const uint64_t y1 = dup2f(y[ps][j]), y5p = dup2f(y5[ps][j]);
+              const uint64_t y2 = fmul2(y1, y1), y10 = fmul2(y5p, y5p), y20 = fmul2(y10, y10);
+              const uint64_t e[5] = {y1, y2, y5p, y10, y20};
+#pragma unroll
+              for (int q = 0; q < 5; ++q) acc[q] = ffma2(e[q], xsel, acc[q]);
+            }
+          };
+          if (one_sided) {
+            // one set of five sums per row; the other side's bases are exact zeros, as the two-sided sums would be
+            uint32_t hi[2][5], lo[2][5];
+#pragma unroll
+            for (int ps = 0; ps < 2; ++ps) {
+              uint64_t acc[5];
+              side_sums(ps, false, 0u, acc);
+#pragma unroll
+              for (int q = 0; q < 5; ++q) {
+                const float2 a = unpack2f(acc[q]);
+                split2<__half>(a.x, a.y, hi[ps][q], lo[ps][q]);
+              }
+            }
+            // the waits come after the arithmetic: the MMA has that long to hand the stages back
+            mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
+            flush_late();
+#pragma unroll
+            for (int ps = 0; ps < 2; ++ps) {
+              const bool up = negm[ps] != 0;
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                const bool mine = (k < 5) == up;
+                put(ps, k, mine ? hi[ps][k % 5] : 0u, mine ? lo[ps][k % 5] : 0u);
+              }
+#pragma unroll
+              for (int k = 8; k < 10; ++k) out89(ps, k, up ? 0u : hi[ps][k - 5], up ? 0u : lo[ps][k - 5]);
+            }
+          } else {
+            mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
+            flush_late();
+#pragma unroll
+            for (int ps = 0; ps < 2; ++ps) {
+#pragma unroll 1
+              for (int side = 0; side < 2; ++side) {
+                uint64_t acc[5];
+                side_sums(ps, true, side ? posm[ps] : negm[ps], acc);
+                uint32_t h[5], l[5];
+#pragma unroll
+                for (int q = 0; q < 5; ++q) {
+                  const float2 a = unpack2f(acc[q]);
+                  split2<__half>(a.x, a.y, h[q], l[q]);
+                }
+                if (side == 0) {
+#pragma unroll
+                  for (int q = 0; q < 5; ++q) put(ps, q, h[q], l[q]);
+                } else {
+#pragma unroll
+                  for (int q = 0; q < 3; ++q) put(ps, 5 + q, h[q], l[q]);
+                  out89(ps, 8, h[3], l[3]);
+                  out89(ps, 9, h[4], l[4]);
+                }
+              }
+            }
+          }
+          fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive_remote(mapa(fullA(ra.idx), 0));
+            if (c == 3) mbar_arrive_remote(mapa(fullK, 0));
+          }
+          __syncwarp();
+          ra.advance<SA>();
+        }
+        kphase ^= 1;
+      }
+      // ---- epilogue: TMEM -> + offset -> out[row, model]; warp handles its lane quarter and every other 16-column chunk
+      mbar_wait(tfull, tphase, 13);
+      tphase ^= 1;
+      tc_fence_after();
+      {
+        const int q = warp & 3;
+        const long long orow = (long long)t * 256 + rank * 128 + q * 32 + lane;
+        const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16);
+        for (int c16 = warp >> 2; c16 < p.n_pad / 16; c16 += 2) {
+          uint32_t v[16], u[16];
+          tmem_ld16(t0 + c16 * 16, v);
+          tmem_ld16(t0 + 256 + c16 * 16, u);
+          tmem_ld_wait();
+          if (orow < p.n) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int col = c16 * 16 + i;
+              if (col < p.m)
+                p.out[(size_t)orow * p.ld_out + col] = (__uint_as_float(v[i]) + __uint_as_float(u[i])) + __ldg(p.offset + col);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(mapa(tempty, 0));
+    }
+  } else if (warp == 8) {
+    // ------------------------------------------------------------------ weight tiles by TMA (both CTAs, own half of N)
+    RingState rb;
+    const int row0 = (int)rank * (p.n_pad / 2);
+    for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      for (int kb = 0; kb < kScKBlocks; ++kb) {
+        mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 14);
+        if (elect_one()) {
+          if (rank == 0) mbar_arrive_expect_tx(fullB(rb.idx), 4 * b_half);
+          const uint32_t bar = mapa(fullB(rb.idx), 0);
+          const uint32_t dst = sB + rb.idx * 2 * b_half;
+          tma_load_2d_pair(dst, &tmW, bar, kb * 64, row0);
+          tma_load_2d_pair(dst + b_half, &tmW, bar, kScK + kb * 64, row0);
+        }
+        __syncwarp();
+        if (++rb.idx == (uint32_t)p.sb_stages) { rb.idx = 0; rb.phase ^= 1; }
+      }
+    }
+  } else if (warp == 10) {
+    // ------------------------------------------------------------------ x chunks by TMA (each CTA its own 128 rows)
+    RingState rx;
+    for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      const int row0 = t * 256 + (int)rank * 128;
+      for (int ch = 0; ch < kScSuper * 4; ++ch) {
+        mbar_wait(emptyX(rx.idx), rx.phase ^ 1, 22);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(fullX(rx.idx), kScXStage);
+          tma_load_3d(sX + rx.idx * kScXStage, &tmX, fullX(rx.idx), ch * 8, row0, 0);
+#if BX_SC_XPF > 0
+          if (ch + BX_SC_XPF < kScSuper * 4) tma_prefetch_3d(&tmX, (ch + BX_SC_XPF) * 8, row0, 0);
+#endif
+        }
+        __syncwarp();
+        rx.advance<kScXStages>();
+      }
+    }
+  } else if (warp == 9 && rank == 0) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA)
+    RingState ra, rb;
+    uint32_t kphase = 0, tphase = 0;
+    for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      mbar_wait(tempty, tphase ^ 1, 15);   // the previous tile's epilogue has read the accumulator
+      tphase ^= 1;
+      tc_fence_after();
+      uint32_t accum = 0;
+      for (int kb = 0; kb < kScKBlocks; ++kb) {
+        const bool k89 = (kb % 5) == 4;
+        uint32_t a_hi;
+        if (k89) { mbar_wait(fullK, kphase, 16); a_hi = sK; }
+        else { mbar_wait(fullA(ra.idx), ra.phase, 17); a_hi = sA + ra.idx * 2 * kScATile; }
+        mbar_wait(fullB(rb.idx), rb.phase, 18);
+        tc_fence_after();
+        const uint32_t b_hi = sB + rb.idx * 2 * b_half;
+        if (elect_one()) {
+          const uint32_t ah = sw128_desc_lo(a_hi), al = sw128_desc_lo(a_hi + kScATile);
+          const uint32_t bh = sw128_desc_lo(b_hi), bl = sw128_desc_lo(b_hi + b_half);
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            umma_f16<2>(tmem_base, sw128_desc(ah + 2 * ks), sw128_desc(bh + 2 * ks), p.idesc, accum);
+            umma_f16<2>(tmem_base + 256, sw128_desc(ah + 2 * ks), sw128_desc(bl + 2 * ks), p.idesc, accum);
+            umma_f16<2>(tmem_base + 256, sw128_desc(al + 2 * ks), sw128_desc(bh + 2 * ks), p.idesc, 1u);
+            accum = 1;
+          }
+          umma_commit<2>(emptyB(rb.idx));
+          umma_commit<2>(k89 ? emptyK : emptyA(ra.idx));
+        }
+        __syncwarp();
+        accum = 1;
+        if (++rb.idx == (uint32_t)p.sb_stages) { rb.idx = 0; rb.phase ^= 1; }
+        if (k89) kphase ^= 1; else ra.advance<SA>();
       }
       if (elect_one()) umma_commit<2>(tfull);
       __syncwarp();

@@ -280,6 +280,18 @@ def test_tensor_core_scoring_padded_rows_equal_dense_rows_bitwise():
     xs = select_variants(x, sel)
     assert _row_pitch(xs) == X_PITCH and torch.equal(xs, x.index_select(1, sel))
     assert torch.equal(decay_score_variant(xs, dist[sel.cpu().numpy()], strand[sel.cpu().numpy()], models), dense[sel])
+    # several tiles per CTA pair and 218 models: the kernel that stages x by TMA (aligned rows) against the one that
+    # loads it through registers (dense rows) — same operand layout and MMA order, so every bit agrees
+    n2 = 256 * 2 * 74 + 77
+    big = padded_rows((9, n2), "cuda")
+    big.uniform_()
+    d2 = torch.from_numpy(rng.integers(-20000, 20000, size=n2).astype(np.float64)).cuda()
+    s2 = torch.from_numpy(np.where(rng.random(n2) < 0.5, 1, -1).astype(np.int8)).cuda()
+    m2 = ScoreModels((rng.standard_normal((218, 20020)) * 0.01).astype(np.float32), rng.standard_normal(218).astype(np.float32), "cuda:0")
+    a = decay_score_variant(big, d2, s2, m2)
+    assert torch.equal(a, decay_score_variant(big.contiguous(), d2, s2, m2))
+    assert torch.equal(a, decay_score_variant(big, d2, s2, m2))
+    del big
     L = _lib.lib()
     out = torch.empty((n, m), device="cuda")
     for bad in (2001, 2003, 0):

@@ -11,6 +11,6 @@ for v in expecto_b200/lib/var/lib_*.so; do
     timeout 300 python tools/score_probe.py 4 $pitch 2>&1 | tail -1 >> gpurun_out/score_sweep.log
   done
 done
-cp ${TESTLIB:-expecto_b200/lib/var/lib_G1.so} $L; touch $L
+cp ${TESTLIB:-expecto_b200/lib/var/lib_A.so} $L; touch $L
 timeout 900 python -m pytest tests/test_gpu_transform.py -x -q -k "scoring or transform" 2>&1 | tail -5 >> gpurun_out/score_sweep.log
 cp /tmp/lib_keep.so $L
