@@ -367,12 +367,11 @@ __device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
   return r;
 }
-// (v, v) as a packed pair.  volatile: pins the powers of y that are formed from it to the place they are used
-// (hoisted out of the chunk loop they would cost 180 registers).
-__device__ __forceinline__ uint64_t dup2f(float v) {
-  uint64_t r;
-  asm volatile("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(v));
-  return r;
+// The value, opaque to the optimiser: pins what is computed from it (the powers of y) to the place it is used —
+// hoisted out of the chunk loop they would cost 180 registers.
+__device__ __forceinline__ float pinned(float v) {
+  asm volatile("" : "+f"(v));
+  return v;
 }
 
 __global__ void __launch_bounds__(kScTmaThreads, 1)
@@ -449,9 +448,23 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
           y5[ps][j] = y4 * y[ps][j];
         }
       }
-      // warp-uniform: each of this warp's sixteen rows has all its shifts on one side (or is padding: x reads as zeros)
-      const bool one_sided =
-          __all_sync(0xffffffffu, ((negm[0] == 0) || (posm[0] == 0)) && ((negm[1] == 0) || (posm[1] == 0)));
+      // A row whose shifts straddle the TSS (|distance| <= 800, ~2 % of variants) needs two sets of sums.  Pass A sums
+      // the larger side of such a row — for every other row simply all nine shifts — and pass B the smaller side, over
+      // just the shifts some row of this 8-row set has there (warp-uniform skip).  A set without such rows runs pass A
+      // unmasked and nothing else.  Terms left out are exact zeros in the two-sided formulation, so the sums are the
+      // same bits whichever way a row is processed and never depend on the rows it shares a warp with.
+      uint32_t maskA[2], maskB[2], unionB[2];
+      bool up[2], mixed[2];     // up: pass A's sums belong to the upstream bases 0..4
+#pragma unroll
+      for (int ps = 0; ps < 2; ++ps) {
+        const bool two = negm[ps] != 0 && posm[ps] != 0;
+        const bool neg_major = __popc(negm[ps]) >= __popc(posm[ps]);
+        up[ps] = two ? neg_major : negm[ps] != 0;
+        maskA[ps] = two ? (neg_major ? negm[ps] : posm[ps]) : 0x1ffu;
+        maskB[ps] = two ? (neg_major ? posm[ps] : negm[ps]) : 0u;
+        unionB[ps] = __reduce_or_sync(0xffffffffu, maskB[ps]);
+        mixed[ps] = unionB[ps] != 0;
+      }
       uint32_t late[2][2][2] = {};
       for (int sb = 0; sb < kScSuper; ++sb) {
 #pragma unroll 1
@@ -508,73 +521,55 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
 #pragma unroll
               for (int k = 8; k < 10; ++k) put89(ps, k, 0, late[ps][k - 8][0], late[ps][k - 8][1]);
           };
-          // sums over the shifts selected by mask, for the five decay rates
-          auto side_sums = [&](int ps, bool masked, uint32_t mask, uint64_t (&acc)[5]) {
+          // Five sums (decay rates) over the shifts of `mask`; MASKED = false: all nine, no selects; `skip`: shifts no
+          // row of the set has (warp-uniform).  y2, y10, y20 are formed here from the kept y and y^5.
+          auto sums = [&](int ps, auto MASKED, uint32_t mask, uint32_t skip_unless, uint64_t (&acc)[5]) {
 #pragma unroll
             for (int q = 0; q < 5; ++q) acc[q] = 0ull;
 #pragma unroll
             for (int j = 0; j < kScShifts; ++j) {
-              const uint64_t xsel = (!masked || ((mask >> j) & 1u)) ? xv[ps][j] : 0ull;
-              const uint64_t y1 = dup2f(y[ps][j]), y5p = dup2f(y5[ps][j]);
-              const uint64_t y2 = fmul2(y1, y1), y10 = fmul2(y5p, y5p), y20 = fmul2(y10, y10);
-              const uint64_t e[5] = {y1, y2, y5p, y10, y20};
+              if (decltype(MASKED)::value && !((skip_unless >> j) & 1u)) continue;
+              const uint64_t xsel = (!decltype(MASKED)::value || ((mask >> j) & 1u)) ? xv[ps][j] : 0ull;
+              const float y1 = pinned(y[ps][j]), y5f = pinned(y5[ps][j]);
+              const float y2 = y1 * y1, y10 = y5f * y5f, y20 = y10 * y10;
+              const float e[5] = {y1, y2, y5f, y10, y20};
 #pragma unroll
-              for (int q = 0; q < 5; ++q) acc[q] = ffma2(e[q], xsel, acc[q]);
+              for (int q = 0; q < 5; ++q) acc[q] = ffma2(pack2f(e[q], e[q]), xsel, acc[q]);
             }
           };
-          if (one_sided) {
-            // one set of five sums per row; the other side's bases are exact zeros, as the two-sided sums would be
-            uint32_t hi[2][5], lo[2][5];
+          auto split5 = [&](const uint64_t (&acc)[5], uint32_t (&hi)[5], uint32_t (&lo)[5]) {
 #pragma unroll
-            for (int ps = 0; ps < 2; ++ps) {
+            for (int q = 0; q < 5; ++q) {
+              const float2 a = unpack2f(acc[q]);
+              split2<__half>(a.x, a.y, hi[q], lo[q]);
+            }
+          };
+#pragma unroll
+          for (int ps = 0; ps < 2; ++ps) {
+            uint32_t hiA[5], loA[5], hiB[5] = {0, 0, 0, 0, 0}, loB[5] = {0, 0, 0, 0, 0};
+            {
               uint64_t acc[5];
-              side_sums(ps, false, 0u, acc);
-#pragma unroll
-              for (int q = 0; q < 5; ++q) {
-                const float2 a = unpack2f(acc[q]);
-                split2<__half>(a.x, a.y, hi[ps][q], lo[ps][q]);
-              }
+              if (mixed[ps]) sums(ps, std::true_type{}, maskA[ps], 0x1ffu, acc);
+              else sums(ps, std::false_type{}, 0u, 0u, acc);
+              split5(acc, hiA, loA);
             }
-            // the waits come after the arithmetic: the MMA has that long to hand the stages back
-            mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
-            flush_late();
-#pragma unroll
-            for (int ps = 0; ps < 2; ++ps) {
-              const bool up = negm[ps] != 0;
-#pragma unroll
-              for (int k = 0; k < 8; ++k) {
-                const bool mine = (k < 5) == up;
-                put(ps, k, mine ? hi[ps][k % 5] : 0u, mine ? lo[ps][k % 5] : 0u);
-              }
-#pragma unroll
-              for (int k = 8; k < 10; ++k) out89(ps, k, up ? 0u : hi[ps][k - 5], up ? 0u : lo[ps][k - 5]);
+            if (mixed[ps]) {
+              uint64_t acc[5];
+              sums(ps, std::true_type{}, maskB[ps], unionB[ps], acc);
+              split5(acc, hiB, loB);
             }
-          } else {
-            mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
-            flush_late();
-#pragma unroll
-            for (int ps = 0; ps < 2; ++ps) {
-#pragma unroll 1
-              for (int side = 0; side < 2; ++side) {
-                uint64_t acc[5];
-                side_sums(ps, true, side ? posm[ps] : negm[ps], acc);
-                uint32_t h[5], l[5];
-#pragma unroll
-                for (int q = 0; q < 5; ++q) {
-                  const float2 a = unpack2f(acc[q]);
-                  split2<__half>(a.x, a.y, h[q], l[q]);
-                }
-                if (side == 0) {
-#pragma unroll
-                  for (int q = 0; q < 5; ++q) put(ps, q, h[q], l[q]);
-                } else {
-#pragma unroll
-                  for (int q = 0; q < 3; ++q) put(ps, 5 + q, h[q], l[q]);
-                  out89(ps, 8, h[3], l[3]);
-                  out89(ps, 9, h[4], l[4]);
-                }
-              }
+            // the waits come after the first row set's arithmetic: the MMA has that long to hand the stages back
+            if (ps == 0) {
+              mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
+              flush_late();
             }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const bool a_side = (k < 5) == up[ps];
+              put(ps, k, a_side ? hiA[k % 5] : hiB[k % 5], a_side ? loA[k % 5] : loB[k % 5]);
+            }
+#pragma unroll
+            for (int k = 8; k < 10; ++k) out89(ps, k, up[ps] ? hiB[k - 5] : hiA[k - 5], up[ps] ? loB[k - 5] : loA[k - 5]);
           }
           fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
           __syncwarp();
