@@ -75,12 +75,13 @@ __global__ void score_prep_weights_kernel(const float* __restrict__ w, int m, in
   out[(size_t)row * 2 * kScK + kScK + col] = __float2half_rn(v - __half2float(h));
 }
 
-// Memory behaviour (profiles/r02_ncu_score_tc.txt): a tile walks 256 variants x 9 shift rows in parallel, 32 bytes of
-// each per chunk, and the rows are 8008 bytes apart — not a multiple of the 32-byte sector — so DRAM sees scattered
-// sector reads (1.5 TB/s, long-scoreboard stalls) and most pieces straddle two sectors.  L2::128B / L2::256B fill hints
-// on the loads made it slower (4.6 / 5.2 ms against 3.9 ms per 75,776 variants); an L2 prefetch of each row's next
-// 128 bytes one super-block ahead plus a one-chunk register double buffer is the best of what was tried.  The remedy
-// is a tile-major layout of x written by the producing epilogue (what comes next).
+// This kernel loads x through registers and serves rows that are NOT on 16-byte boundaries (a caller's dense
+// [9, n, 2002] array: 8008-byte rows); score_tma_kernel below is the one the drop-in's own path runs.  Memory behaviour
+// (profiles/r02_ncu_score_tc.txt): a tile walks 256 variants x 9 shift rows in parallel, 32 bytes of each per chunk;
+// with 8008-byte rows most pieces straddle two DRAM sectors (1.5 TB/s, long-scoreboard stalls: 3.9 ms per 75,776
+// variants; 2.8 ms once the rows are 2016 floats apart).  L2::128B / L2::256B fill hints on the loads made it slower
+// (4.6 / 5.2 ms); an L2 prefetch of each row's next 128 bytes one super-block ahead plus a one-chunk register double
+// buffer is the best of what 168 registers allow.
 __global__ void __launch_bounds__(kScThreads, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
   constexpr int SA = 2, SK = 2;
@@ -333,18 +334,30 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
 
 // ====================================================================================================================
 // The same GEMM with x staged through shared memory by TMA (rows on 16-byte boundaries: row pitch a multiple of four
-// floats — what the drop-in's own producers write, transform.padded_rows).  The kernel above keeps its loads in
-// registers one chunk ahead, which is all the latency hiding 168 registers allow, and spends its time in
-// long-scoreboard stalls (profiles/r02_ncu_score_tc.txt).  Here a producer lane copies each chunk — the box
+// floats — what the drop-in's own producers write, transform.padded_rows).  A producer lane copies each chunk — the box
 // [8 features x 128 rows x 9 shifts] = 36 KB per CTA — with one cp.async.bulk.tensor two chunks ahead of its use, at no
-// register or issue cost to the generators; rows past n and features past 2002 arrive as zeros (TMA bounds), and the
-// shared-memory budget is met by a one-stage ring for the k = 8, 9 K-blocks and a two-stage weight ring.  The
-// generators' arithmetic is packed (FFMA2) and takes a five-sum path when every row of a warp has its nine shifts on
-// one side of the TSS (|distance| > 800: all but ~2 % of variants).  Operand layout, weight permutation, MMA order and
-// therefore every bit of the result are those of the kernel above.
+// register or issue cost to the generators (tools/tma_box_bench.cu: one SM streams such boxes at 5.7 TB/s chip-wide with
+// two in flight, so x delivery is not the limit); rows past n and features past 2002 arrive as zeros (TMA bounds).  The
+// shared-memory budget (227 KB) is met by a one-stage ring for the k = 8, 9 K-blocks — chunk 0 keeps its four pieces of
+// that block in registers for one chunk, so nobody waits for the stage — and a two-stage weight ring.
+//   * Sixteen generator warps, one 8-row set each (four warps per scheduler instead of two, 94 registers).
+//   * Packed arithmetic (FFMA2, scalar powers broadcast), y and y^5 kept, y^2, y^10, y^20 formed where used.
+//   * Rows whose shifts straddle the TSS (|distance| <= 800, ~2 % of variants) need sums for both sides.  Pass A sums
+//     the larger side of such a row — for every other row simply all nine shifts, unmasked when the set has no such
+//     row — and pass B the smaller side over just the shifts the set has there.  Terms left out are exact zeros of the
+//     two-sided formulation, so a row's bits never depend on the rows it shares a warp with.
+// Operand layout, weight permutation, MMA order and therefore every bit of the result are those of the kernel above
+// (tests/test_gpu_transform.py compares the two).  What bounds it now (profiles/r02_ncu_score_tma.txt): shared-memory
+// bandwidth — per K-block the tensor core reads 90 KB of operands (three MMAs per K step), TMA writes 57 KB and the
+// generators move 54 KB, ~200 KB against 128 B/clk — with the tensor pipe 61 % and the issue slots 50 % busy.
 constexpr int kScXStage = kScShifts * 128 * 32;   // one chunk of one CTA: [9 shifts][128 rows][8 floats]
 constexpr int kScXStages = 2;
-constexpr int kScTmaThreads = 352;                // + warp 10: x producer
+#ifndef BX_SC_SETS
+#define BX_SC_SETS 1
+#endif
+constexpr int kScSets = BX_SC_SETS;               // 8-row sets per generator warp: 1 -> sixteen generator warps, 2 -> eight
+constexpr int kScGenWarps = 16 / kScSets;
+constexpr int kScTmaThreads = (kScGenWarps + 3) * 32;   // + W producer, MMA issuer, x producer
 
 __device__ __forceinline__ uint64_t pack2f(float lo, float hi) {
   uint64_t r;
@@ -399,28 +412,29 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
   const uint32_t rank = cluster_ctarank();
   const int num_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
 
-  if (warp == 8 && lane == 0) {
+  if (warp == kScGenWarps && lane == 0) {
     prefetch_tensormap(&tmW);
     prefetch_tensormap(&tmX);
     for (int i = 0; i < 2; ++i) {
-      mbar_init(fullA(i), 16); mbar_init(emptyA(i), 1);     // 8 generator warps in each CTA of the pair
-      mbar_init(fullX(i), 1); mbar_init(emptyX(i), 8);      // per CTA: its own 128 rows of x
+      mbar_init(fullA(i), 2 * kScGenWarps); mbar_init(emptyA(i), 1);     // the generator warps of both CTAs
+      mbar_init(fullX(i), 1); mbar_init(emptyX(i), kScGenWarps);      // per CTA: its own 128 rows of x
     }
-    mbar_init(fullK, 16); mbar_init(emptyK, 1);
+    mbar_init(fullK, 2 * kScGenWarps); mbar_init(emptyK, 1);
     for (int i = 0; i < 4; ++i) { mbar_init(fullB(i), 1); mbar_init(emptyB(i), 1); }
     mbar_init(tfull, 1);
-    mbar_init(tempty, 16);
+    mbar_init(tempty, 2 * kScGenWarps);
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc<2>(tmem_slot, 512);   // columns [0, n_pad): Ah*Wh; [256, 256 + n_pad): Ah*Wl + Al*Wh
+  if (warp == kScGenWarps + 1) tmem_alloc<2>(tmem_slot, 512);   // columns [0, n_pad): Ah*Wh; [256, 256 + n_pad): Ah*Wl + Al*Wh
   tc_fence_before();
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
 
-  if (warp < 8) {
+  if (warp < kScGenWarps) {
     // ------------------------------------------------------------------ feature generators + epilogue
-    // Lane (rw, sub) of warp w: rows w*16 + {0, 8} + rw of this CTA, feature pair 2*sub, 2*sub + 1 of every chunk.
+    // Lane (rw, sub) of warp w: rows w * 8 * kScSets + ps * 8 + rw of this CTA (ps < kScSets), feature pair 2*sub,
+    // 2*sub + 1 of every chunk.
     const int sub = lane & 3, rw = lane >> 2;
     RingState ra, rx;
     uint32_t kphase = 0, tphase = 0;
@@ -428,11 +442,11 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
       // y = exp(-0.01 * floor(|pos| / 200)) per shift (fp64 like numpy, predict.py:87-109); the five decay rates are
       // its powers y, y^2, y^5, y^10, y^20.  y and y^5 are kept, the others formed where they are used (same products
       // in the same order as the kernel above: y2 = y*y, y4 = y2*y2, y5 = y4*y, y10 = y5*y5, y20 = y10*y10).
-      float y[2][kScShifts], y5[2][kScShifts];
-      uint32_t negm[2], posm[2];
+      float y[kScSets][kScShifts], y5[kScSets][kScShifts];
+      uint32_t negm[kScSets], posm[kScSets];
 #pragma unroll
-      for (int ps = 0; ps < 2; ++ps) {
-        const long long row = (long long)t * 256 + rank * 128 + warp * 16 + ps * 8 + rw;
+      for (int ps = 0; ps < kScSets; ++ps) {
+        const long long row = (long long)t * 256 + rank * 128 + warp * (8 * kScSets) + ps * 8 + rw;
         const bool valid = row < p.n;
         const double d = valid ? p.dist[row] : 0.0;
         const double sgn = (valid && p.strand[row] > 0) ? 1.0 : -1.0;
@@ -453,10 +467,10 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
       // just the shifts some row of this 8-row set has there (warp-uniform skip).  A set without such rows runs pass A
       // unmasked and nothing else.  Terms left out are exact zeros in the two-sided formulation, so the sums are the
       // same bits whichever way a row is processed and never depend on the rows it shares a warp with.
-      uint32_t maskA[2], maskB[2], unionB[2];
-      bool up[2], mixed[2];     // up: pass A's sums belong to the upstream bases 0..4
+      uint32_t maskA[kScSets], maskB[kScSets], unionB[kScSets];
+      bool up[kScSets], mixed[kScSets];     // up: pass A's sums belong to the upstream bases 0..4
 #pragma unroll
-      for (int ps = 0; ps < 2; ++ps) {
+      for (int ps = 0; ps < kScSets; ++ps) {
         const bool two = negm[ps] != 0 && posm[ps] != 0;
         const bool neg_major = __popc(negm[ps]) >= __popc(posm[ps]);
         up[ps] = two ? neg_major : negm[ps] != 0;
@@ -465,17 +479,20 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
         unionB[ps] = __reduce_or_sync(0xffffffffu, maskB[ps]);
         mixed[ps] = unionB[ps] != 0;
       }
-      uint32_t late[2][2][2] = {};
+      bool any_mixed = false;
+#pragma unroll
+      for (int ps = 0; ps < kScSets; ++ps) any_mixed = any_mixed || mixed[ps];
+      uint32_t late[kScSets][2][2] = {};
       for (int sb = 0; sb < kScSuper; ++sb) {
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
           // this chunk of x: shared memory -> registers, and the stage goes back to the producer at once
-          uint64_t xv[2][kScShifts];
+          uint64_t xv[kScSets][kScShifts];
           mbar_wait(fullX(rx.idx), rx.phase, 21);
           {
-            const uint8_t* xs = smem_raw + (sX - raw) + rx.idx * kScXStage + (warp * 16 + rw) * 32 + sub * 8;
+            const uint8_t* xs = smem_raw + (sX - raw) + rx.idx * kScXStage + (warp * (8 * kScSets) + rw) * 32 + sub * 8;
 #pragma unroll
-            for (int ps = 0; ps < 2; ++ps)
+            for (int ps = 0; ps < kScSets; ++ps)
 #pragma unroll
               for (int j = 0; j < kScShifts; ++j)
                 xv[ps][j] = *reinterpret_cast<const uint64_t*>(xs + j * (128 * 32) + ps * (8 * 32));
@@ -484,12 +501,12 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
           if (lane == 0) mbar_arrive_local(emptyX(rx.idx));
           rx.advance<kScXStages>();
 
-          uint8_t* st[2];
-          uint8_t* sk[2];
-          uint32_t swz[2];
+          uint8_t* st[kScSets];
+          uint8_t* sk[kScSets];
+          uint32_t swz[kScSets];
 #pragma unroll
-          for (int ps = 0; ps < 2; ++ps) {
-            const int r = warp * 16 + ps * 8 + rw;
+          for (int ps = 0; ps < kScSets; ++ps) {
+            const int r = warp * (8 * kScSets) + ps * 8 + rw;
             swz[ps] = (uint32_t)(r & 7);
             st[ps] = smem_raw + (sA - raw) + ra.idx * 2 * kScATile + r * 128 + sub * 4;
             sk[ps] = smem_raw + (sK - raw) + r * 128 + sub * 4;
@@ -517,25 +534,18 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
             if (c != 1) return;
             mbar_wait(emptyK, kphase ^ 1, 12);
 #pragma unroll
-            for (int ps = 0; ps < 2; ++ps)
+            for (int ps = 0; ps < kScSets; ++ps)
 #pragma unroll
               for (int k = 8; k < 10; ++k) put89(ps, k, 0, late[ps][k - 8][0], late[ps][k - 8][1]);
           };
-          // Five sums (decay rates) over the shifts of `mask`; MASKED = false: all nine, no selects; `skip`: shifts no
-          // row of the set has (warp-uniform).  y2, y10, y20 are formed here from the kept y and y^5.
-          auto sums = [&](int ps, auto MASKED, uint32_t mask, uint32_t skip_unless, uint64_t (&acc)[5]) {
+          // One shift's contribution to the five sums (decay rates) of row set ps; y2, y10, y20 are formed here from
+          // the kept y and y^5.
+          auto add_shift = [&](int ps, int j, uint64_t xsel, uint64_t (&acc)[5]) {
+            const float y1 = pinned(y[ps][j]), y5f = pinned(y5[ps][j]);
+            const float y2 = y1 * y1, y10 = y5f * y5f, y20 = y10 * y10;
+            const float e[5] = {y1, y2, y5f, y10, y20};
 #pragma unroll
-            for (int q = 0; q < 5; ++q) acc[q] = 0ull;
-#pragma unroll
-            for (int j = 0; j < kScShifts; ++j) {
-              if (decltype(MASKED)::value && !((skip_unless >> j) & 1u)) continue;
-              const uint64_t xsel = (!decltype(MASKED)::value || ((mask >> j) & 1u)) ? xv[ps][j] : 0ull;
-              const float y1 = pinned(y[ps][j]), y5f = pinned(y5[ps][j]);
-              const float y2 = y1 * y1, y10 = y5f * y5f, y20 = y10 * y10;
-              const float e[5] = {y1, y2, y5f, y10, y20};
-#pragma unroll
-              for (int q = 0; q < 5; ++q) acc[q] = ffma2(pack2f(e[q], e[q]), xsel, acc[q]);
-            }
+            for (int q = 0; q < 5; ++q) acc[q] = ffma2(pack2f(e[q], e[q]), xsel, acc[q]);
           };
           auto split5 = [&](const uint64_t (&acc)[5], uint32_t (&hi)[5], uint32_t (&lo)[5]) {
 #pragma unroll
@@ -544,32 +554,50 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
               split2<__half>(a.x, a.y, hi[q], lo[q]);
             }
           };
+          // Pass A of both row sets in one instruction stream: ten independent accumulator chains (with two warps per
+          // scheduler the chains' latency is what the generators run at).
+          uint32_t hiA[kScSets][5], loA[kScSets][5];
+          {
+            uint64_t acc[kScSets][5];
 #pragma unroll
-          for (int ps = 0; ps < 2; ++ps) {
-            uint32_t hiA[5], loA[5], hiB[5] = {0, 0, 0, 0, 0}, loB[5] = {0, 0, 0, 0, 0};
-            {
-              uint64_t acc[5];
-              if (mixed[ps]) sums(ps, std::true_type{}, maskA[ps], 0x1ffu, acc);
-              else sums(ps, std::false_type{}, 0u, 0u, acc);
-              split5(acc, hiA, loA);
+            for (int ps = 0; ps < kScSets; ++ps)
+#pragma unroll
+              for (int q = 0; q < 5; ++q) acc[ps][q] = 0ull;
+            if (any_mixed) {
+#pragma unroll
+              for (int j = 0; j < kScShifts; ++j)
+#pragma unroll
+                for (int ps = 0; ps < kScSets; ++ps) add_shift(ps, j, ((maskA[ps] >> j) & 1u) ? xv[ps][j] : 0ull, acc[ps]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < kScShifts; ++j)
+#pragma unroll
+                for (int ps = 0; ps < kScSets; ++ps) add_shift(ps, j, xv[ps][j], acc[ps]);
             }
-            if (mixed[ps]) {
-              uint64_t acc[5];
-              sums(ps, std::true_type{}, maskB[ps], unionB[ps], acc);
+#pragma unroll
+            for (int ps = 0; ps < kScSets; ++ps) split5(acc[ps], hiA[ps], loA[ps]);
+          }
+          // the waits come after the arithmetic: the MMA has that long to hand the stages back
+          mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
+          flush_late();
+#pragma unroll
+          for (int ps = 0; ps < kScSets; ++ps) {
+            uint32_t hiB[5] = {0, 0, 0, 0, 0}, loB[5] = {0, 0, 0, 0, 0};
+            if (mixed[ps]) {   // pass B: the smaller side of this set's two-sided rows, over the shifts the set has there
+              uint64_t acc[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
+#pragma unroll
+              for (int j = 0; j < kScShifts; ++j)
+                if ((unionB[ps] >> j) & 1u) add_shift(ps, j, ((maskB[ps] >> j) & 1u) ? xv[ps][j] : 0ull, acc);
               split5(acc, hiB, loB);
-            }
-            // the waits come after the first row set's arithmetic: the MMA has that long to hand the stages back
-            if (ps == 0) {
-              mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
-              flush_late();
             }
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
               const bool a_side = (k < 5) == up[ps];
-              put(ps, k, a_side ? hiA[k % 5] : hiB[k % 5], a_side ? loA[k % 5] : loB[k % 5]);
+              put(ps, k, a_side ? hiA[ps][k % 5] : hiB[k % 5], a_side ? loA[ps][k % 5] : loB[k % 5]);
             }
 #pragma unroll
-            for (int k = 8; k < 10; ++k) out89(ps, k, up[ps] ? hiB[k - 5] : hiA[k - 5], up[ps] ? loB[k - 5] : loA[k - 5]);
+            for (int k = 8; k < 10; ++k)
+              out89(ps, k, up[ps] ? hiB[k - 5] : hiA[ps][k - 5], up[ps] ? loB[k - 5] : loA[ps][k - 5]);
           }
           fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
           __syncwarp();
@@ -590,7 +618,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
         const int q = warp & 3;
         const long long orow = (long long)t * 256 + rank * 128 + q * 32 + lane;
         const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16);
-        for (int c16 = warp >> 2; c16 < p.n_pad / 16; c16 += 2) {
+        for (int c16 = warp >> 2; c16 < p.n_pad / 16; c16 += kScGenWarps / 4) {
           uint32_t v[16], u[16];
           tmem_ld16(t0 + c16 * 16, v);
           tmem_ld16(t0 + 256 + c16 * 16, u);
@@ -609,7 +637,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(mapa(tempty, 0));
     }
-  } else if (warp == 8) {
+  } else if (warp == kScGenWarps) {
     // ------------------------------------------------------------------ weight tiles by TMA (both CTAs, own half of N)
     RingState rb;
     const int row0 = (int)rank * (p.n_pad / 2);
@@ -627,7 +655,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
         if (++rb.idx == (uint32_t)p.sb_stages) { rb.idx = 0; rb.phase ^= 1; }
       }
     }
-  } else if (warp == 10) {
+  } else if (warp == kScGenWarps + 2) {
     // ------------------------------------------------------------------ x chunks by TMA (each CTA its own 128 rows)
     RingState rx;
     for (int t = cluster_id; t < p.tiles; t += num_clusters) {
@@ -645,7 +673,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
         rx.advance<kScXStages>();
       }
     }
-  } else if (warp == 9 && rank == 0) {
+  } else if (warp == kScGenWarps + 1 && rank == 0) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA)
     RingState ra, rb;
     uint32_t kphase = 0, tphase = 0;
@@ -688,7 +716,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
   __syncwarp();
   tc_fence_before();
   cluster_sync_all();
-  if (warp == 9) {
+  if (warp == kScGenWarps + 1) {
     tc_fence_after();
     tmem_dealloc<2>(tmem_base, 512);
   }
