@@ -299,12 +299,12 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
     flop = 2.0 * n * 20020 * m
     out["score"] = {"variants": n, "models": m, "bytes_per_variant": b // n, "ms": t * 1e3, "achieved": b / t / 1e9,
                     "unit": "GB/s", "peak": peaks["hbm_gbs"], "frac": b / t / 1e9 / peaks["hbm_gbs"],
-                    "variants_per_s": n / t, "kernel": "score_tc_kernel",
+                    "variants_per_s": n / t, "kernel": "score_tma_kernel",
                     "algorithmic_tflops": flop / t / 1e12, "executed_tflops": 3 * flop * (20160 / 20020) * (224 / m) / t / 1e12,
                     "x_row_pitch_floats": X_PITCH,
                     "note": "features never leave shared memory; every product is three fp16 MMAs (hi/lo split operands); "
                             "bytes are the algorithmic 2002 floats per row, rows are padded to x_row_pitch_floats"}
-    xd = x.contiguous()                        # dense 8008-byte rows (what a caller's own [9, n, 2002] array is)
+    xd = x.contiguous()                        # dense 8008-byte rows (a caller's own [9, n, 2002] array): score_tc_kernel
     out["score"]["ms_dense_rows"] = timed(lambda: decay_score_variant(xd, dist_d, strand_d, models, shifts=shifts_d)) * 1e3
     del xd
     t_simt = timed(lambda: decay_score_variant(x[:, :2048].contiguous(), dist_d[:2048], strand_d[:2048], models,
