@@ -1132,6 +1132,7 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
     if (x_tma) {   // x stages + A ring (2) + K stage, the rest of the 227 KB for the weight ring
       const size_t fixed = (size_t)kScXStages * kScXStage + (size_t)3 * 2 * kScATile + 256 + 1024;
       p.sb_stages = (int)std::min<size_t>(4, (232448 - fixed) / b_stage);
+      if (const char* e = getenv("BX_SCORE_SB")) p.sb_stages = std::max(1, std::min(p.sb_stages, atoi(e)));   // experiments
       smem = fixed + p.sb_stages * b_stage;
     } else {
       p.sb_stages = 3;

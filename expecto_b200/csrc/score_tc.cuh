@@ -547,6 +547,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
 #pragma unroll
             for (int q = 0; q < 5; ++q) acc[q] = ffma2(pack2f(e[q], e[q]), xsel, acc[q]);
           };
+
           auto split5 = [&](const uint64_t (&acc)[5], uint32_t (&hi)[5], uint32_t (&lo)[5]) {
 #pragma unroll
             for (int q = 0; q < 5; ++q) {

@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from expecto_b200.transform import ScoreModels, decay_score_variant, chromatin_shifts
 
-n, m = 74 * 256 * int(sys.argv[1] if len(sys.argv) > 1 else 1), 218
+n, m = 74 * 256 * int(sys.argv[1] if len(sys.argv) > 1 else 1), int(os.environ.get('PROBE_MODELS', 218))
 rng = np.random.default_rng(0)
 dev = torch.device("cuda:0")
 pitch = int(sys.argv[2]) if len(sys.argv) > 2 else 2002
