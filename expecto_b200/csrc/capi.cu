@@ -1147,7 +1147,8 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
       else CK(cudaFuncSetAttribute(score_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       attr_smem[x_tma][dev].store(smem, std::memory_order_release);
     }
-    const int clusters = std::max(1, std::min(p.tiles, sms / 2));
+    int clusters = std::max(1, std::min(p.tiles, sms / 2));
+    if (const char* e = getenv("BX_SCORE_CLUSTERS")) clusters = std::max(1, std::min(clusters, atoi(e)));   // experiments
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(clusters * 2);
     cfg.blockDim = dim3(x_tma ? kScTmaThreads : kScThreads);

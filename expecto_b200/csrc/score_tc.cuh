@@ -351,7 +351,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
 // bandwidth — per K-block the tensor core reads 90 KB of operands (three MMAs per K step), TMA writes 57 KB and the
 // generators move 54 KB, ~200 KB against 128 B/clk — with the tensor pipe 61 % and the issue slots 50 % busy.
 constexpr int kScXStage = kScShifts * 128 * 32;   // one chunk of one CTA: [9 shifts][128 rows][8 floats]
-constexpr int kScXStages = 2;
+#ifndef BX_SC_XSTAGES
+#define BX_SC_XSTAGES 2
+#endif
+constexpr int kScXStages = BX_SC_XSTAGES;
 #ifndef BX_SC_SETS
 #define BX_SC_SETS 1
 #endif
@@ -403,10 +406,10 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
   auto emptyA = [&](uint32_t i) { return bars + 8u * (2 + i); };
   const uint32_t fullK = bars + 8u * 4, emptyK = bars + 8u * 5;
   auto fullX = [&](uint32_t i) { return bars + 8u * (6 + i); };
-  auto emptyX = [&](uint32_t i) { return bars + 8u * (8 + i); };
-  auto fullB = [&](uint32_t i) { return bars + 8u * (10 + i); };
-  auto emptyB = [&](uint32_t i) { return bars + 8u * (14 + i); };
-  const uint32_t tfull = bars + 8u * 18, tempty = bars + 8u * 19, tmem_slot = bars + 8u * 20;
+  auto emptyX = [&](uint32_t i) { return bars + 8u * (10 + i); };
+  auto fullB = [&](uint32_t i) { return bars + 8u * (14 + i); };
+  auto emptyB = [&](uint32_t i) { return bars + 8u * (18 + i); };
+  const uint32_t tfull = bars + 8u * 22, tempty = bars + 8u * 23, tmem_slot = bars + 8u * 24;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -417,8 +420,8 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
     prefetch_tensormap(&tmX);
     for (int i = 0; i < 2; ++i) {
       mbar_init(fullA(i), 2 * kScGenWarps); mbar_init(emptyA(i), 1);     // the generator warps of both CTAs
-      mbar_init(fullX(i), 1); mbar_init(emptyX(i), kScGenWarps);      // per CTA: its own 128 rows of x
     }
+    for (int i = 0; i < kScXStages; ++i) { mbar_init(fullX(i), 1); mbar_init(emptyX(i), kScGenWarps); }   // per CTA: its own 128 rows of x
     mbar_init(fullK, 2 * kScGenWarps); mbar_init(emptyK, 1);
     for (int i = 0; i < 4; ++i) { mbar_init(fullB(i), 1); mbar_init(emptyB(i), 1); }
     mbar_init(tfull, 1);
