@@ -304,6 +304,12 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
                     "x_row_pitch_floats": X_PITCH,
                     "note": "features never leave shared memory; every product is three fp16 MMAs (hi/lo split operands); "
                             "bytes are the algorithmic 2002 floats per row, rows are padded to x_row_pitch_floats"}
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))["transform"]
+        out["score"]["traffic"] = int(tr["score_per_variant_bytes"] * n)
+        out["score"]["traffic_source"] = "ncu capture r02 (profiles/r02_ncu_score_tma.txt), static: not measured in this run"
+    except Exception:
+        out["score"]["traffic"] = None
     xd = x.contiguous()                        # dense 8008-byte rows (a caller's own [9, n, 2002] array): score_tc_kernel
     out["score"]["ms_dense_rows"] = timed(lambda: decay_score_variant(xd, dist_d, strand_d, models, shifts=shifts_d)) * 1e3
     del xd

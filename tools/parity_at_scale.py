@@ -225,6 +225,54 @@ def run_cfg4(args, make_engine) -> dict:
     return res
 
 
+def run_cfg5_scoring(args) -> dict:
+    """Kernel 5 (transform + gblinear scoring as one tcgen05 GEMM) against the float64 restatement of predict.py:87-160
+    on a cfg5-shaped sample: ``score_variants`` variants (2 % of them within 800 bp of the TSS, a few exactly on it and
+    on the 200-bp bin edges) x 218 models, ref and alt effects that differ as chromatin diffs do (|alt - ref| ~ 1e-3), so
+    that SED = ALT - REF is the difference of scores agreeing to 3 - 4 digits that predict.py:264 prints."""
+    import torch
+
+    from expecto_b200.transform import ScoreModels, decay_score_variant, padded_rows
+    from oracle import beluga_oracle as O
+    n, m = args.score_variants, 218
+    rng = np.random.default_rng(55)
+    ref = rng.random((9, n, 2002)).astype(np.float32) ** 3          # skewed towards 0, as probabilities are
+    alt = np.clip(ref + (rng.standard_normal((9, n, 2002)) * 1e-3).astype(np.float32) * (rng.random((9, n, 2002)) < 0.1), 0, 1).astype(np.float32)
+    dist = rng.integers(-40000, 40000, size=n).astype(np.float64)
+    dist[:12] = [0, 200, -200, 199, -199, 800, -800, 1, -1, 400, 600, -600]
+    strand = np.where(rng.random(n) < 0.5, "+", "-")
+    W = (rng.standard_normal((m, 20020)) * 0.01).astype(np.float32)
+    off = rng.standard_normal(m).astype(np.float32)
+    models = ScoreModels(W, off, "cuda:0")
+    got = {}
+    for name, x in (("ref", ref), ("alt", alt)):
+        xd = padded_rows((9, n), "cuda:0")
+        xd.copy_(torch.from_numpy(x))
+        got[name] = decay_score_variant(xd, dist, strand, models).cpu().numpy().astype(np.float64)
+        del xd
+    want = {}
+    w64 = W.astype(np.float64).T
+    t0 = time.perf_counter()
+    for name, x in (("ref", ref), ("alt", alt)):
+        out = np.empty((n, m))
+        for a in range(0, n, 500):          # predict.py's --batchSize
+            f = O.variant_transform([xx[a:a + 500] for xx in x], O.variant_weights(dist[a:a + 500], strand[a:a + 500]))
+            out[a:a + 500] = f @ w64 + off[None, :]
+        want[name] = out
+    cpu_s = time.perf_counter() - t0
+    scale = float(np.abs(want["ref"]).max())
+    sed_g, sed_w = got["alt"] - got["ref"], want["alt"] - want["ref"]
+    res = {"variants": n, "models": m, "oracle_seconds": cpu_s, "score_scale": scale,
+           "ref_max_err_over_scale": float(np.abs(got["ref"] - want["ref"]).max() / scale),
+           "alt_max_err_over_scale": float(np.abs(got["alt"] - want["alt"]).max() / scale),
+           "sed_max_abs": float(np.abs(sed_w).max()), "sed_max_err": float(np.abs(sed_g - sed_w).max()),
+           "sed_max_err_over_sed_max": float(np.abs(sed_g - sed_w).max() / np.abs(sed_w).max()),
+           "sed_pearson": pearson(sed_g.ravel(), sed_w.ravel()),
+           "bars": {"score_over_scale": 5e-5, "sed_pearson": 0.999}}
+    res["ok"] = bool(max(res["ref_max_err_over_scale"], res["alt_max_err_over_scale"]) <= 5e-5 and res["sed_pearson"] >= 0.999)
+    return res
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "parity_at_scale.json"))
@@ -235,7 +283,8 @@ def main() -> int:
     ap.add_argument("--shifts", default="0,-800,800,-200,-400,-600,200,400,600")
     ap.add_argument("--dtype", default="f16", choices=["f16", "bf16", "f16x3"])
     ap.add_argument("--capacity", type=int, default=4096)
-    ap.add_argument("--skip", default="", help="comma list of cfg2,cfg3,cfg4")
+    ap.add_argument("--skip", default="", help="comma list of cfg2,cfg3,cfg4,cfg5")
+    ap.add_argument("--score_variants", type=int, default=5000)
     args = ap.parse_args()
     args.shifts = [int(s) for s in args.shifts.split(",") if s]
     import torch
@@ -261,6 +310,8 @@ def main() -> int:
         res["cfg3"] = run_cfg3(args, make_engine)
     if "cfg4" not in skip:
         res["cfg4"] = run_cfg4(args, make_engine)
+    if "cfg5" not in skip:
+        res["cfg5_scoring"] = run_cfg5_scoring(args)
     res["seconds"] = time.perf_counter() - t0
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     with open(args.out, "w") as f:
