@@ -347,9 +347,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
 //     row — and pass B the smaller side over just the shifts the set has there.  Terms left out are exact zeros of the
 //     two-sided formulation, so a row's bits never depend on the rows it shares a warp with.
 // Operand layout, weight permutation, MMA order and therefore every bit of the result are those of the kernel above
-// (tests/test_gpu_transform.py compares the two).  What bounds it now (profiles/r02_ncu_score_tma.txt): shared-memory
-// bandwidth — per K-block the tensor core reads 90 KB of operands (three MMAs per K step), TMA writes 57 KB and the
-// generators move 54 KB, ~200 KB against 128 B/clk — with the tensor pipe 61 % and the issue slots 50 % busy.
+// (tests/test_gpu_transform.py compares the two).  What bounds it now (kernel 5;
+// profiles/r02_ncu_score_tma.txt): every unit is 40 - 62 % busy (tensor pipe 61 %, shared-memory pipe 60 %, issue slots
+// 50 %); with the generators' work removed it takes the same time at 218 models, on half the SMs 1.5 x as long: the SMs
+// contend for the L2 -> SM path, which carries x once and the 18 MB of weights once per tile (10.8 GB per 75,776 variants).
 constexpr int kScXStage = kScShifts * 128 * 32;   // one chunk of one CTA: [9 shifts][128 rows][8 floats]
 #ifndef BX_SC_XSTAGES
 #define BX_SC_XSTAGES 2
@@ -372,12 +373,7 @@ __device__ __forceinline__ float2 unpack2f(uint64_t v) {
   asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
   return r;
 }
-// Packed fp32 pairs (FMUL2 / FFMA2 on sm_100): each half is the scalar .rn operation.
-__device__ __forceinline__ uint64_t fmul2(uint64_t a, uint64_t b) {
-  uint64_t r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
+// Packed fp32 pair FMA (FFMA2 on sm_100): each half is the scalar fma.rn.
 __device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
   uint64_t r;
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
