@@ -5,6 +5,7 @@ import numpy as np, torch
 from expecto_b200.transform import ScoreModels, decay_score_variant, chromatin_shifts
 
 n, m = 74 * 256 * int(sys.argv[1] if len(sys.argv) > 1 else 1), int(os.environ.get('PROBE_MODELS', 218))
+n = int(os.environ.get('PROBE_VARIANTS', n))
 rng = np.random.default_rng(0)
 dev = torch.device("cuda:0")
 pitch = int(sys.argv[2]) if len(sys.argv) > 2 else 2002
@@ -19,8 +20,9 @@ for _ in range(3):
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
-for _ in range(5):
+iters = int(os.environ.get('PROBE_ITERS', 5))
+for _ in range(iters):
     out = decay_score_variant(x, dist, strand, models, shifts=shifts)
 e1.record()
 torch.cuda.synchronize()
-print("pitch", pitch, "ms per launch", e0.elapsed_time(e1) / 5, "variants", n)
+print("pitch", pitch, "ms per launch", e0.elapsed_time(e1) / iters, "variants", n)
