@@ -1104,7 +1104,11 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
 #ifndef BX_SC_L2PROMO
 #define BX_SC_L2PROMO CU_TENSOR_MAP_L2_PROMOTION_L2_128B
 #endif
-  const bool x_tma = (x_row_pitch % 4 == 0) && (reinterpret_cast<uintptr_t>(x_dev) % 16 == 0) && !getenv("BX_SCORE_NO_TMA");
+  // measurement switches (tools/score_probe.py), read once: force the register-load kernel, cap the weight ring / grid
+  static const bool no_tma = getenv("BX_SCORE_NO_TMA") != nullptr;
+  static const int sb_cap = getenv("BX_SCORE_SB") ? atoi(getenv("BX_SCORE_SB")) : 0;
+  static const int cluster_cap = getenv("BX_SCORE_CLUSTERS") ? atoi(getenv("BX_SCORE_CLUSTERS")) : 0;
+  const bool x_tma = (x_row_pitch % 4 == 0) && (reinterpret_cast<uintptr_t>(x_dev) % 16 == 0) && !no_tma;
   CUtensorMap tmX;
   if (x_tma) {
     cuuint64_t dims[3] = {(cuuint64_t)BX_FEATURES, (cuuint64_t)n, (cuuint64_t)kScShifts};
@@ -1132,7 +1136,7 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
     if (x_tma) {   // x stages + A ring (2) + K stage, the rest of the 227 KB for the weight ring
       const size_t fixed = (size_t)kScXStages * kScXStage + (size_t)3 * 2 * kScATile + 256 + 1024;
       p.sb_stages = (int)std::min<size_t>(4, (232448 - fixed) / b_stage);
-      if (const char* e = getenv("BX_SCORE_SB")) p.sb_stages = std::max(1, std::min(p.sb_stages, atoi(e)));   // experiments
+      if (sb_cap > 0) p.sb_stages = std::min(p.sb_stages, sb_cap);
       smem = fixed + p.sb_stages * b_stage;
     } else {
       p.sb_stages = 3;
@@ -1148,7 +1152,7 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
       attr_smem[x_tma][dev].store(smem, std::memory_order_release);
     }
     int clusters = std::max(1, std::min(p.tiles, sms / 2));
-    if (const char* e = getenv("BX_SCORE_CLUSTERS")) clusters = std::max(1, std::min(clusters, atoi(e)));   // experiments
+    if (cluster_cap > 0) clusters = std::min(clusters, cluster_cap);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(clusters * 2);
     cfg.blockDim = dim3(x_tma ? kScTmaThreads : kScThreads);
