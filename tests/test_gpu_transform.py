@@ -280,6 +280,13 @@ def test_tensor_core_scoring_padded_rows_equal_dense_rows_bitwise():
     xs = select_variants(x, sel)
     assert _row_pitch(xs) == X_PITCH and torch.equal(xs, x.index_select(1, sel))
     assert torch.equal(decay_score_variant(xs, dist[sel.cpu().numpy()], strand[sel.cpu().numpy()], models), dense[sel])
+    # edge tiles of the TMA-staged kernel: one row, a tile less / more than one row, an empty call
+    for n1 in (1, 255, 257):
+        xe = padded_rows((9, n1), "cuda")
+        xe.copy_(x[:, :n1])
+        assert _row_pitch(xe) == X_PITCH
+        assert torch.equal(decay_score_variant(xe, dist[:n1], strand[:n1], models), dense[:n1])
+    assert decay_score_variant(padded_rows((9, 0), "cuda"), dist[:0], strand[:0], models).shape == (0, m)
     # several tiles per CTA pair and 218 models: the kernel that stages x by TMA (aligned rows) against the one that
     # loads it through registers (dense rows) — same operand layout and MMA order, so every bit agrees
     n2 = 256 * 2 * 74 + 77
