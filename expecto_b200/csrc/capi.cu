@@ -1999,3 +1999,9 @@ extern "C" int bx_fasta_count_noalloc(const uint8_t* text_dev, int64_t body_star
   CK(cudaMemcpyAsync(n_bases_dev, off + n_blocks, sizeof(long long), cudaMemcpyDeviceToDevice, st));
   return 0;
 }
+
+#ifdef BX_SC_TRACE
+extern "C" int bx_debug_score_trace(long long* out_host) {
+  return cudaMemcpyFromSymbol(out_host, bx::g_sc_trace, sizeof(bx::g_sc_trace)) == cudaSuccess ? 0 : -1;
+}
+#endif

@@ -386,6 +386,13 @@ __device__ __forceinline__ float pinned(float v) {
   return v;
 }
 
+#ifdef BX_SC_TRACE   // diagnostic build: cycle stamps of one CTA's pipeline events (tools/score_trace.py)
+__device__ long long g_sc_trace[4][512][8];
+#define SC_TRACE(role, idx, ev) do { if (blockIdx.x == 0 && (idx) < 512) g_sc_trace[role][idx][ev] = clock64(); } while (0)
+#else
+#define SC_TRACE(role, idx, ev) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(kScTmaThreads, 1)
 score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const ScoreParams p) {
   constexpr int SA = 2;
@@ -487,7 +494,11 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
         for (int c = 0; c < 4; ++c) {
           // this chunk of x: shared memory -> registers, and the stage goes back to the producer at once
           uint64_t xv[kScSets][kScShifts];
+          const int tr_i = (t == cluster_id && lane == 0 && (warp == 0 || warp == kScGenWarps - 1)) ? sb * 4 + c : 1 << 20;
+          const int tr_r = warp == 0 ? 0 : 1;
+          SC_TRACE(tr_r, tr_i, 0);
           mbar_wait(fullX(rx.idx), rx.phase, 21);
+          SC_TRACE(tr_r, tr_i, 1);
           {
             const uint8_t* xs = smem_raw + (sX - raw) + rx.idx * kScXStage + (warp * (8 * kScSets) + rw) * 32 + sub * 8;
 #pragma unroll
@@ -578,8 +589,11 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
             for (int ps = 0; ps < kScSets; ++ps) split5(acc[ps], hiA[ps], loA[ps]);
           }
           // the waits come after the arithmetic: the MMA has that long to hand the stages back
+          SC_TRACE(tr_r, tr_i, 2);
           mbar_wait(emptyA(ra.idx), ra.phase ^ 1, 11);
+          SC_TRACE(tr_r, tr_i, 3);
           flush_late();
+          SC_TRACE(tr_r, tr_i, 4);
 #pragma unroll
           for (int ps = 0; ps < kScSets; ++ps) {
             uint32_t hiB[5] = {0, 0, 0, 0, 0}, loB[5] = {0, 0, 0, 0, 0};
@@ -599,13 +613,16 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
             for (int k = 8; k < 10; ++k)
               out89(ps, k, up[ps] ? hiB[k - 5] : hiA[ps][k - 5], up[ps] ? loB[k - 5] : loA[ps][k - 5]);
           }
+          SC_TRACE(tr_r, tr_i, 6);
           fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
+          SC_TRACE(tr_r, tr_i, 7);
           __syncwarp();
           if (lane == 0) {
             mbar_arrive_remote(mapa(fullA(ra.idx), 0));
             if (c == 3) mbar_arrive_remote(mapa(fullK, 0));
           }
           __syncwarp();
+          SC_TRACE(tr_r, tr_i, 5);
           ra.advance<SA>();
         }
         kphase ^= 1;
@@ -661,7 +678,9 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
     for (int t = cluster_id; t < p.tiles; t += num_clusters) {
       const int row0 = t * 256 + (int)rank * 128;
       for (int ch = 0; ch < kScSuper * 4; ++ch) {
+        SC_TRACE(3, (t == cluster_id && lane == 0) ? ch : 1 << 20, 0);
         mbar_wait(emptyX(rx.idx), rx.phase ^ 1, 22);
+        SC_TRACE(3, (t == cluster_id && lane == 0) ? ch : 1 << 20, 1);
         if (elect_one()) {
           mbar_arrive_expect_tx(fullX(rx.idx), kScXStage);
           tma_load_3d(sX + rx.idx * kScXStage, &tmX, fullX(rx.idx), ch * 8, row0, 0);
@@ -684,10 +703,14 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
       uint32_t accum = 0;
       for (int kb = 0; kb < kScKBlocks; ++kb) {
         const bool k89 = (kb % 5) == 4;
+        const int tr_k = (t == cluster_id && lane == 0) ? kb : 1 << 20;
+        SC_TRACE(2, tr_k, 0);
         uint32_t a_hi;
         if (k89) { mbar_wait(fullK, kphase, 16); a_hi = sK; }
         else { mbar_wait(fullA(ra.idx), ra.phase, 17); a_hi = sA + ra.idx * 2 * kScATile; }
+        SC_TRACE(2, tr_k, 1);
         mbar_wait(fullB(rb.idx), rb.phase, 18);
+        SC_TRACE(2, tr_k, 2);
         tc_fence_after();
         const uint32_t b_hi = sB + rb.idx * 2 * b_half;
         if (elect_one()) {
@@ -704,6 +727,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
           umma_commit<2>(k89 ? emptyK : emptyA(ra.idx));
         }
         __syncwarp();
+        SC_TRACE(2, tr_k, 3);
         accum = 1;
         if (++rb.idx == (uint32_t)p.sb_stages) { rb.idx = 0; rb.phase ^= 1; }
         if (k89) kphase ^= 1; else ra.advance<SA>();
