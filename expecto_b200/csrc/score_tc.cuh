@@ -348,9 +348,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
 //     two-sided formulation, so a row's bits never depend on the rows it shares a warp with.
 // Operand layout, weight permutation, MMA order and therefore every bit of the result are those of the kernel above
 // (tests/test_gpu_transform.py compares the two).  What bounds it now (kernel 5;
-// profiles/r02_ncu_score_tma.txt): every unit is 40 - 62 % busy (tensor pipe 61 %, shared-memory pipe 60 %, issue slots
-// 50 %); with the generators' work removed it takes the same time at 218 models, on half the SMs 1.5 x as long: the SMs
-// contend for the L2 -> SM path, which carries x once and the 18 MB of weights once per tile (10.8 GB per 75,776 variants).
+// profiles/r02_ncu_score_tma.txt, r02_score_trace.txt): shared-memory bandwidth.  Per chunk and CTA the tensor core reads
+// 112 KB of operands (three MMAs per K step), TMA writes 35 KB of weights and 36 KB of x, the generators read those 36 KB
+// and write 32 KB of operand tiles: 251 KB per 2,460 cycles = 102 of the SM's 128 B/clk — at the ~1.35 GHz the board's
+// power cap leaves once the kernel runs for more than a burst.
 constexpr int kScXStage = kScShifts * 128 * 32;   // one chunk of one CTA: [9 shifts][128 rows][8 floats]
 #ifndef BX_SC_XSTAGES
 #define BX_SC_XSTAGES 2
