@@ -275,3 +275,27 @@ def test_num_repeats_matches_reference_function(golden):
     for text, want in zip(g["tables"], g["expected"]):
         df = pd.read_csv(io.StringIO(str(text)), sep="\t", header=None, comment="#")
         assert num_repeats(df) == [int(x) for x in str(want).split(",")]
+
+
+def test_padded_rows_and_variant_selection_keep_the_row_pitch():
+    """transform.padded_rows / _row_pitch / select_variants (the row layout FC2's epilogue writes and the scoring kernel
+    reads: rows X_PITCH floats apart): views over padded buffers report their pitch, dense and oddly strided tensors
+    do not, and a gene-row gather keeps the padding while returning what index_select returns."""
+    import torch
+
+    from expecto_b200.transform import N_FEATURES, X_PITCH, _row_pitch, padded_rows, select_variants
+    assert X_PITCH % 32 == 0 and X_PITCH >= N_FEATURES          # rows start on 128-byte boundaries
+    for n in (0, 1, 2, 77):
+        x = padded_rows((9, n), "cpu")
+        assert x.shape == (9, n, N_FEATURES) and _row_pitch(x) == X_PITCH
+    x = padded_rows((9, 40), "cpu")
+    x.copy_(torch.arange(9 * 40 * N_FEATURES, dtype=torch.float32).reshape(9, 40, N_FEATURES))
+    assert _row_pitch(x.contiguous()) == N_FEATURES
+    assert _row_pitch(x[:, ::2]) == 2 * X_PITCH                   # every other row: still one pitch, twice as wide
+    assert _row_pitch(x.transpose(0, 1)) == 0                     # shift-minor layouts are not row-padded tensors
+    assert _row_pitch(x[:, 3:17]) == 0                            # a row slice breaks the shift stride
+    sel = torch.tensor([5, 5, 0, 39, 17])
+    got = select_variants(x, sel)
+    assert _row_pitch(got) == X_PITCH and torch.equal(got, x.index_select(1, sel))
+    dense = x.contiguous()
+    assert torch.equal(select_variants(dense, sel), dense.index_select(1, sel))
