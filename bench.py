@@ -285,7 +285,9 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
     from expecto_b200.transform import X_PITCH, ScoreModels, decay_score_variant, padded_rows
     m = 218                                    # resources/modellist
     rng = np.random.default_rng(5)
-    models = ScoreModels((rng.standard_normal((m, 20020)) * 0.01).astype(np.float32), rng.standard_normal(m).astype(np.float32), dev)
+    models_w = (rng.standard_normal((m, 20020)) * 0.01).astype(np.float32)
+    models_b = rng.standard_normal(m).astype(np.float32)
+    models = ScoreModels(models_w, models_b, dev)
     models.prepared()
     # four full waves of 74 CTA pairs x 256 variants
     del x
@@ -304,6 +306,13 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
                     "x_row_pitch_floats": X_PITCH,
                     "note": "features never leave shared memory; every product is three fp16 MMAs (hi/lo split operands); "
                             "bytes are the algorithmic 2002 floats per row, rows are padded to x_row_pitch_floats"}
+    # one model, as a single predict.py run has it (--model_save_file): the x stream with next to no MMA work
+    one = ScoreModels(np.ascontiguousarray(models_w[:1]), models_b[:1].copy(), dev)
+    one.prepared()
+    t_one = timed(lambda: decay_score_variant(x, dist_d, strand_d, one, shifts=shifts_d))
+    out["score"]["one_model"] = {"ms": t_one * 1e3, "achieved": n * (9 * 2002 * 4 + 4 + 9) / t_one / 1e9,
+                                 "frac": n * (9 * 2002 * 4 + 4 + 9) / t_one / 1e9 / peaks["hbm_gbs"]}
+    del one
     # the same launch back to back for ~2 s: the board reaches its power cap and the SM clock drops (kernel 5)
     e0.record()
     for _ in range(800):
