@@ -325,7 +325,7 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))["transform"]
         out["score"]["traffic"] = int(tr["score_per_variant_bytes"] * n)
-        out["score"]["traffic_source"] = "ncu capture r02 (profiles/r02_ncu_score_tma.txt), static: not measured in this run"
+        out["score"]["traffic_source"] = "ncu launch list r02 (profiles/r02_ncu_score_launches.csv), static: not measured in this run"
     except Exception:
         out["score"]["traffic"] = None
     xd = x.contiguous()                        # dense 8008-byte rows (a caller's own [9, n, 2002] array): score_tc_kernel
