@@ -273,3 +273,26 @@ def test_device_outputs_with_padded_rows_equal_dense_outputs(engine, small_genom
         assert torch.equal(a, b)
     with pytest.raises(ValueError):
         engine.chromatin_submit_device(0, res[2002][1][0], res[X_PITCH][1][1], res[X_PITCH][1][2], rows_per_shift, n, 0)
+
+
+def test_set_row_pitch_argument_and_state_errors(engine, small_genome):
+    """bx_chromatin_set_row_pitch: refused without an open plan, for odd pitches and for pitches below 2002; a refused
+    call leaves the plan's pitch as it was (dense)."""
+    from expecto_b200 import _lib
+    L = _lib.lib()
+    assert L.bx_chromatin_set_row_pitch(engine._ctx, 2016) == _lib.BX_E_STATE
+    pg = PackedGenome.from_sequences(small_genome)
+    engine.set_genome(pg)
+    rows = _variants(small_genome, n_random=3)
+    n = len(rows)
+    n_chunks, _ = engine.chromatin_open(_cols(pg, rows), 800)
+    for bad in (2001, 2003, 2000, 0, -8):
+        assert L.bx_chromatin_set_row_pitch(engine._ctx, bad) == _lib.BX_E_ARG
+        assert b"row_pitch" in L.bx_last_error()
+    got = [torch.full((9, 2 * n, 2002), -5.5, device=engine.device) for _ in range(3)]
+    for k in range(n_chunks):
+        engine.chromatin_submit_device(k, *got, 2 * n, n, engine.chromatin_chunk_info(k)["v0"])
+    engine.chromatin_close()
+    torch.cuda.synchronize()
+    for g, w in zip(got, _reference_outputs(engine, pg, rows, 800, False)):
+        assert torch.equal(g, w)
