@@ -306,6 +306,13 @@ def transform_rooflines(dev, peaks, iters: int = 10, cpu: bool = True):
                     "x_row_pitch_floats": X_PITCH,
                     "note": "features never leave shared memory; every product is three fp16 MMAs (hi/lo split operands); "
                             "bytes are the algorithmic 2002 floats per row, rows are padded to x_row_pitch_floats"}
+    # rows grouped by side of the TSS (transform.side_order; predict hands its rows over like that wherever it gathers
+    # them anyway): whole K steps of the operand are zero for every row of most tiles and the kernel skips them
+    from expecto_b200.transform import side_order
+    so = torch.from_numpy(side_order(dist_d.cpu().numpy(), strand_d.cpu().numpy())).to(dev)
+    dist_s, strand_s = dist_d[so].contiguous(), strand_d[so].contiguous()
+    t_so = timed(lambda: decay_score_variant(x, dist_s, strand_s, models, shifts=shifts_d))
+    out["score"]["rows_ordered_by_side"] = {"ms": t_so * 1e3, "achieved": b / t_so / 1e9, "frac": b / t_so / 1e9 / peaks["hbm_gbs"]}
     # one model, as a single predict.py run has it (--model_save_file): the x stream with next to no MMA work
     one = ScoreModels(np.ascontiguousarray(models_w[:1]), models_b[:1].copy(), dev)
     one.prepared()

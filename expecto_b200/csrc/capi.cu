@@ -1121,9 +1121,12 @@ int bx_decay_score_variant_tc(const float* x_dev, int64_t x_row_pitch, const dou
     if (r != CUDA_SUCCESS)
       return fail(BX_E_CUDA, "cuTensorMapEncodeTiled failed for x: %d (n=%d pitch=%lld)", (int)r, n, (long long)x_row_pitch);
   }
+  // side-pure tiles skip the K steps that are zero for all their rows (score_tile_class); BX_SCORE_NO_SKIP for A/B runs
+  static const bool no_skip = getenv("BX_SCORE_NO_SKIP") != nullptr;
   for (int m0 = 0; m0 < n_models; m0 += 256) {
     const int m = std::min(256, n_models - m0), n_pad = score_group_pad(m);
     ScoreParams p = {};
+    p.skip_zero_steps = no_skip ? 0 : 1;
     p.x = x_dev; p.ld_x = x_row_pitch; p.dist = dist_dev; p.strand = strand_dev; p.shifts = shifts_dev;
     p.offset = offset_dev + m0;
     p.out = out_dev + m0;

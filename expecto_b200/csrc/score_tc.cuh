@@ -48,6 +48,7 @@ struct ScoreParams {
   const int8_t* strand;    // [n] +1 / -1
   const int32_t* shifts;   // [9]
   const float* offset;     // [m] base_score + bias
+  int skip_zero_steps;     // score_tma_kernel: skip the K steps that are zero for every row of a tile (score_tile_class)
   float* out;              // [n, ld_out]: this launch writes columns [0, m)
   int n, m, n_pad, tiles;  // m models in this launch, n_pad: padded to a multiple of 16 (<= 256); tiles = ceil(n / 256)
   int ld_out;
@@ -332,6 +333,32 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmW, const ScoreParams p) {
 }
 
 
+// Side of the TSS of every row of a 256-variant tile (the masks of the generators' prologue, same expressions): 1 = every
+// row has all nine shifts upstream (or is padding), 2 = all downstream, 0 = anything else.  For a one-sided row the five
+// bases of the other side are exact zeros, so in a tile of class 1 or 2 whole K steps of the operand are zero for every
+// row: score_tma_kernel neither stores, loads nor multiplies them (adding an MMA of zeros changes no bit).  Random row
+// orders give class 0 throughout; callers that order their rows by side (transform.side_order: predict does, for free,
+// wherever it gathers rows anyway) get classes 1 and 2 for all but a few tiles.  Every warp that needs the class
+// (generators, weight producer, MMA issuer, in both CTAs) evaluates it itself from dist / strand — eight rows per lane,
+// about a microsecond per 450 us tile — so the roles need no extra synchronisation and run ahead of each other as before.
+__device__ __forceinline__ int score_tile_class(const ScoreParams& p, int t, int lane) {
+  bool neg = false, posi = false;
+  for (int i = 0; i < 8; ++i) {
+    const long long row = (long long)t * 256 + i * 32 + lane;
+    if (row >= p.n) continue;
+    const double d = p.dist[row];
+    const double sgn = p.strand[row] > 0 ? 1.0 : -1.0;
+#pragma unroll
+    for (int j = 0; j < kScShifts; ++j) {
+      const double pos = d * sgn + (double)p.shifts[j] * sgn;
+      if (pos <= 0.0) neg = true;
+      if (pos >= 0.0) posi = true;
+    }
+  }
+  const bool any_pos = __any_sync(0xffffffffu, posi), any_neg = __any_sync(0xffffffffu, neg);
+  return !any_pos ? 1 : (!any_neg ? 2 : 0);
+}
+
 // ====================================================================================================================
 // The same GEMM with x staged through shared memory by TMA (rows on 16-byte boundaries: row pitch a multiple of four
 // floats — what the drop-in's own producers write, transform.padded_rows).  A producer lane copies each chunk — the box
@@ -490,6 +517,11 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
 #pragma unroll
       for (int ps = 0; ps < kScSets; ++ps) any_mixed = any_mixed || mixed[ps];
       uint32_t late[kScSets][2][2] = {};
+      // Tile class (score_tile_class): bases that are zero for every row of the tile are not stored, and a
+      // class-1 tile has no k = 8, 9 K-block at all (the issuer and the weight producer skip it the same way).
+      const int cls = p.skip_zero_steps ? score_tile_class(p, t, lane) : 0;
+      const bool use_k = cls != 1;
+      const int k_lo = cls == 2 ? 4 : 0, k_hi = cls == 1 ? 6 : 8;
       for (int sb = 0; sb < kScSuper; ++sb) {
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
@@ -542,7 +574,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
           };
           // chunk 1, before any of its own k = 8, 9 stores: wait for the stage, then chunk 0's pieces
           auto flush_late = [&]() {
-            if (c != 1) return;
+            if (c != 1 || !use_k) return;
             mbar_wait(emptyK, kphase ^ 1, 12);
 #pragma unroll
             for (int ps = 0; ps < kScSets; ++ps)
@@ -608,11 +640,14 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
               const bool a_side = (k < 5) == up[ps];
-              put(ps, k, a_side ? hiA[ps][k % 5] : hiB[k % 5], a_side ? loA[ps][k % 5] : loB[k % 5]);
+              if (k >= k_lo && k < k_hi)
+                put(ps, k, a_side ? hiA[ps][k % 5] : hiB[k % 5], a_side ? loA[ps][k % 5] : loB[k % 5]);
             }
+            if (use_k) {
 #pragma unroll
-            for (int k = 8; k < 10; ++k)
-              out89(ps, k, up[ps] ? hiB[k - 5] : hiA[ps][k - 5], up[ps] ? loB[k - 5] : loA[ps][k - 5]);
+              for (int k = 8; k < 10; ++k)
+                out89(ps, k, up[ps] ? hiB[k - 5] : hiA[ps][k - 5], up[ps] ? loB[k - 5] : loA[ps][k - 5]);
+            }
           }
           SC_TRACE(tr_r, tr_i, 6);
           fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
@@ -620,13 +655,13 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
           __syncwarp();
           if (lane == 0) {
             mbar_arrive_remote(mapa(fullA(ra.idx), 0));
-            if (c == 3) mbar_arrive_remote(mapa(fullK, 0));
+            if (c == 3 && use_k) mbar_arrive_remote(mapa(fullK, 0));
           }
           __syncwarp();
           SC_TRACE(tr_r, tr_i, 5);
           ra.advance<SA>();
         }
-        kphase ^= 1;
+        if (use_k) kphase ^= 1;
       }
       // ---- epilogue: TMEM -> + offset -> out[row, model]; warp handles its lane quarter and every other 16-column chunk
       mbar_wait(tfull, tphase, 13);
@@ -660,7 +695,9 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
     RingState rb;
     const int row0 = (int)rank * (p.n_pad / 2);
     for (int t = cluster_id; t < p.tiles; t += num_clusters) {
+      const bool use_k = !(p.skip_zero_steps && score_tile_class(p, t, lane) == 1);
       for (int kb = 0; kb < kScKBlocks; ++kb) {
+        if (!use_k && kb % 5 == 4) continue;
         mbar_wait(emptyB(rb.idx), rb.phase ^ 1, 14);
         if (elect_one()) {
           if (rank == 0) mbar_arrive_expect_tx(fullB(rb.idx), 4 * b_half);
@@ -702,8 +739,12 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
       tphase ^= 1;
       tc_fence_after();
       uint32_t accum = 0;
+      const int cls = p.skip_zero_steps ? score_tile_class(p, t, lane) : 0;
       for (int kb = 0; kb < kScKBlocks; ++kb) {
         const bool k89 = (kb % 5) == 4;
+        if (k89 && cls == 1) continue;
+        // K steps whose bases are zero for every row of the tile: bases 6..9 in class 1, bases 0..3 in class 2
+        const int ks_lo = (cls == 2 && !k89) ? 2 : 0, ks_hi = (cls == 1) ? 3 : 4;
         const int tr_k = (t == cluster_id && lane == 0) ? kb : 1 << 20;
         SC_TRACE(2, tr_k, 0);
         uint32_t a_hi;
@@ -719,6 +760,7 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
           const uint32_t bh = sw128_desc_lo(b_hi), bl = sw128_desc_lo(b_hi + b_half);
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks) {
+            if (ks < ks_lo || ks >= ks_hi) continue;
             umma_f16<2>(tmem_base, sw128_desc(ah + 2 * ks), sw128_desc(bh + 2 * ks), p.idesc, accum);
             umma_f16<2>(tmem_base + 256, sw128_desc(ah + 2 * ks), sw128_desc(bl + 2 * ks), p.idesc, accum);
             umma_f16<2>(tmem_base + 256, sw128_desc(al + 2 * ks), sw128_desc(bh + 2 * ks), p.idesc, 1u);

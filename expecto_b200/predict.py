@@ -300,7 +300,7 @@ def run(args, engine=None, genome=None) -> dict:
     import torch
 
     from .gblinear import load_model
-    from .transform import ScoreModels, decay_score_variant, select_variants
+    from .transform import ScoreModels, decay_score_variant, select_variants, side_order
 
     if not torch.cuda.is_available():
         raise RuntimeError("predict needs a CUDA device (B200); there is no CPU fallback")
@@ -364,6 +364,11 @@ def run(args, engine=None, genome=None) -> dict:
         if rows.size:
             local = idx[rows] - v0
             identity = len(local) == v1 - v0 and bool(np.array_equal(local, np.arange(v1 - v0)))
+            if not identity:
+                # the rows are gathered anyway: gather them grouped by side of the TSS, which lets the scoring kernel
+                # skip the operand columns that are zero for whole tiles (transform.side_order; same scores bit for bit)
+                order = side_order(dist[rows], strand[rows], shifts)
+                rows, local = rows[order], local[order]
             sel = None if identity else torch.from_numpy(local).to(dev)
             for key in ("ref", "alt"):
                 x = data[key] if identity else select_variants(data[key], sel)

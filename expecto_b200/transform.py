@@ -91,6 +91,24 @@ def select_variants(x: torch.Tensor, sel: torch.Tensor) -> torch.Tensor:
     return x.as_strided((S, n, pitch), (n * pitch, pitch, 1)).index_select(1, sel)[..., :f]
 
 
+def side_order(dist, strand, shifts=None) -> np.ndarray:
+    """Row order that groups variants by the side of the TSS their shifted positions fall on (predict.py:87-109:
+    ``pos = (dist + shift) * sgn``): all nine upstream, straddling, all nine downstream — a stable sort, so rows keep
+    their order within a group.  The scoring kernel skips the operand columns that are zero for every row of a
+    256-variant tile; rows handed over in this order make all but a few tiles one-sided (about a fifth less time).
+    Any order gives the same scores bit for bit."""
+    d = np.asarray(dist, dtype=np.float64).reshape(-1)
+    st = np.asarray(strand).reshape(-1)
+    if st.dtype.kind in "USO":
+        sgn = np.where(np.asarray([str(v) for v in st]) == "+", 1.0, -1.0)
+    else:
+        sgn = np.where(st.astype(np.float64) > 0, 1.0, -1.0)
+    sh = np.asarray(chromatin_shifts(800) if shifts is None else shifts, dtype=np.float64)
+    pos = d[:, None] * sgn[:, None] + sh[None, :] * sgn[:, None]
+    key = np.where((pos < 0).all(axis=1), 0, np.where((pos > 0).all(axis=1), 2, 1))
+    return np.argsort(key, kind="stable")
+
+
 def _row_pitch(x: torch.Tensor) -> int:
     """Row pitch of a [S,n,2002] tensor that is dense apart from row padding, or 0."""
     S, n, f = x.shape

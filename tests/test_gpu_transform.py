@@ -299,6 +299,23 @@ def test_tensor_core_scoring_padded_rows_equal_dense_rows_bitwise():
     assert torch.equal(a, decay_score_variant(big.contiguous(), d2, s2, m2))
     assert torch.equal(a, decay_score_variant(big, d2, s2, m2))
     del big
+    # rows grouped by side of the TSS: whole K steps are zero for every row of most tiles and are skipped (tile classes
+    # 1 and 2, score_tile_class_kernel) — the scores are those of the unsorted run, bit for bit
+    from expecto_b200.transform import side_order
+    d2h, s2h = d2.cpu().numpy(), s2.cpu().numpy()
+    o = side_order(d2h, s2h)
+    pos = (d2h[o, None] + np.array([0, -200, -400, -600, -800, 200, 400, 600, 800])[None, :]) * np.where(s2h[o] > 0, 1, -1)[:, None]
+    cls = np.where((pos < 0).all(1), 0, np.where((pos > 0).all(1), 2, 1))
+    assert (np.diff(cls) >= 0).all() and {0, 1, 2} <= set(cls.tolist())
+    ot = torch.from_numpy(o).cuda()
+    big = padded_rows((9, n2), "cuda")
+    torch.manual_seed(5)
+    big.uniform_()
+    base = decay_score_variant(big, d2, s2, m2)
+    srt = select_variants(big, ot)
+    assert _row_pitch(srt) == X_PITCH
+    assert torch.equal(decay_score_variant(srt, d2[ot], s2[ot], m2), base[ot])
+    del big, srt
     L = _lib.lib()
     out = torch.empty((n, m), device="cuda")
     for bad in (2001, 2003, 0):

@@ -299,3 +299,22 @@ def test_padded_rows_and_variant_selection_keep_the_row_pitch():
     assert _row_pitch(got) == X_PITCH and torch.equal(got, x.index_select(1, sel))
     dense = x.contiguous()
     assert torch.equal(select_variants(dense, sel), dense.index_select(1, sel))
+
+
+def test_side_order_groups_rows_by_side_of_the_tss():
+    """transform.side_order: a stable sort by (all nine shifted positions upstream, straddling, all downstream) with
+    predict.py:87-109's sign convention — the '+' / '-' strings of the gene table or +-1 integers."""
+    from expecto_b200.transform import side_order
+    dist = np.array([5000.0, -5000.0, 0.0, 801.0, -801.0, 800.0, -800.0, 300.0, 12.0, -9000.0])
+    strand = np.array(["+", "+", "-", "+", "+", "-", "-", "+", "-", "-"])
+    sh = np.array(chromatin_shifts(800), dtype=np.float64)
+    sgn = np.where(strand == "+", 1.0, -1.0)
+    pos = (dist[:, None] + sh[None, :]) * sgn[:, None]
+    key = np.where((pos < 0).all(1), 0, np.where((pos > 0).all(1), 2, 1))
+    assert key.tolist() == [2, 0, 1, 2, 0, 1, 1, 1, 1, 2]           # +-800 touch position 0: straddling
+    o = side_order(dist, strand)
+    assert sorted(o.tolist()) == list(range(10)) and (np.diff(key[o]) >= 0).all()
+    for k in (0, 1, 2):                                              # stable within a group
+        assert (np.diff(o[key[o] == k]) > 0).all()
+    assert np.array_equal(side_order(dist, np.where(strand == "+", 1, -1).astype(np.int8)), o)
+    assert side_order(np.zeros(0), np.zeros(0, np.int8)).size == 0

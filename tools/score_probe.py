@@ -11,7 +11,13 @@ dev = torch.device("cuda:0")
 pitch = int(sys.argv[2]) if len(sys.argv) > 2 else 2002
 x = torch.rand((9, n, pitch), dtype=torch.float32, device=dev)[..., :2002]
 dist = torch.from_numpy(rng.integers(-40000, 40000, size=n).astype(np.float64)).to(dev)
-strand = torch.from_numpy(np.where(np.arange(n) % 2 == 0, 1, -1).astype(np.int8)).to(dev)
+st_h = np.where(np.arange(n) % 2 == 0, 1, -1).astype(np.int8)
+if os.environ.get("PROBE_SORTED"):       # rows grouped by side of the TSS (transform.side_order)
+    from expecto_b200.transform import side_order
+    o = side_order(dist.cpu().numpy(), st_h)
+    dist = dist[torch.from_numpy(o).to(dev)]
+    st_h = st_h[o]
+strand = torch.from_numpy(st_h).to(dev)
 shifts = torch.tensor(chromatin_shifts(800), dtype=torch.int32, device=dev)
 models = ScoreModels((rng.standard_normal((m, 20020)) * 0.01).astype(np.float32), rng.standard_normal(m).astype(np.float32), dev)
 models.prepared()
