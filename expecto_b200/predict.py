@@ -285,14 +285,29 @@ def _chromatin_blocks(args, dev, engine=None, genome=None):
     if missing:
         raise KeyError(f"contig(s) {missing} are not in the genome")
     n = len(pos)
-    yield n
+    # The consumer sends, with each request for a block, the order it wants that block's variants in (a permutation of
+    # range(v1 - v0), or None): row i of the block's tensors is then variant v0 + perm[i].  run() asks for them grouped
+    # by side of the TSS (transform.side_order) when every variant has exactly one gene row, so that the scoring
+    # kernel's tiles are one-sided without any gather.
+    perm = yield n
     for v0 in range(0, n, args.vcf_block):
         v1 = min(n, v0 + args.vcf_block)
-        data = chromatin.predict_all_shifts_averaged_device(engine, genome, chroms[v0:v1], pos[v0:v1], refs[v0:v1],
-                                                            alts[v0:v1], int(args.maxshift), padded=True)
+        ii = np.arange(v0, v1) if perm is None else v0 + np.asarray(perm, dtype=np.int64)
+        if len(ii) != v1 - v0 or not np.array_equal(np.sort(ii), np.arange(v0, v1)):
+            raise ValueError("block order must be a permutation of the block's variants")
+        data = chromatin.predict_all_shifts_averaged_device(engine, genome, [chroms[i] for i in ii], pos[ii],
+                                                            [refs[i] for i in ii], [alts[i] for i in ii],
+                                                            int(args.maxshift), padded=True)
         data.pop("diff")
-        yield v0, v1, data
+        perm = yield v0, v1, data
         del data
+
+
+def _file_blocks(n_pred: int, data):
+    """The one block of the file path, behind the same protocol as _chromatin_blocks (the requested order is ignored:
+    the rows are already in HBM in file order)."""
+    yield n_pred
+    yield 0, n_pred, data
 
 
 def run(args, engine=None, genome=None) -> dict:
@@ -333,7 +348,8 @@ def run(args, engine=None, genome=None) -> dict:
         data = load_strand_averaged(args.snpEffectFilePattern, int(args.maxshift), keys=("ref", "alt"), device=dev)
         torch.cuda.synchronize(dev)
         n_pred = int(data["ref"].shape[1])
-        blocks = iter([(0, n_pred, data)])
+        blocks = _file_blocks(n_pred, data)
+        next(blocks)
         del data
     lap("load_h5_s")
     coor = pd.read_csv(args.coorFile_chromatin, sep="\t", header=None, comment="#")
@@ -359,10 +375,21 @@ def run(args, engine=None, genome=None) -> dict:
     shifts = shift_list(int(args.maxshift))
     models = ScoreModels(W, offsets, dev)   # staged (and laid out for the tensor-core kernel) once
     scores = {k: np.empty((len(idx), len(paths)), dtype=np.float32) for k in ("ref", "alt")}
-    for v0, v1, data in blocks:  # one block when reading files; --vcf computes --vcf_block variants at a time
-        rows = np.flatnonzero((idx >= v0) & (idx < v1))   # idx is non-decreasing: a contiguous run of gene rows
+    block_rows = int(args.vcf_block) if args.vcf else max(1, n_pred)
+    for b0 in range(0, n_pred, block_rows):  # one block when reading files; --vcf computes --vcf_block variants at a time
+        b1 = min(n_pred, b0 + block_rows)
+        rows = np.flatnonzero((idx >= b0) & (idx < b1))   # idx is non-decreasing: a contiguous run of gene rows
+        one_to_one = len(rows) == b1 - b0 and bool(np.array_equal(idx[rows] - b0, np.arange(b1 - b0)))
+        want = None
+        if args.vcf and one_to_one and rows.size:
+            # every variant of the block has exactly one gene row: have the block computed in side order (no gather)
+            want = side_order(dist[rows], strand[rows], shifts)
+            rows = rows[want]
+        v0, v1, data = blocks.send(want)
+        if (v0, v1) != (b0, b1):
+            raise RuntimeError("block protocol out of step")
         if rows.size:
-            local = idx[rows] - v0
+            local = idx[rows] - v0 if want is None else np.arange(v1 - v0)
             identity = len(local) == v1 - v0 and bool(np.array_equal(local, np.arange(v1 - v0)))
             if not identity:
                 # the rows are gathered anyway: gather them grouped by side of the TSS, which lets the scoring kernel
