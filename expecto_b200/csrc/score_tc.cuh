@@ -521,7 +521,6 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
       // class-1 tile has no k = 8, 9 K-block at all (the issuer and the weight producer skip it the same way).
       const int cls = p.skip_zero_steps ? score_tile_class(p, t, lane) : 0;
       const bool use_k = cls != 1;
-      const int k_lo = cls == 2 ? 4 : 0, k_hi = cls == 1 ? 6 : 8;
       for (int sb = 0; sb < kScSuper; ++sb) {
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
@@ -637,13 +636,22 @@ score_tma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
                 if ((unionB[ps] >> j) & 1u) add_shift(ps, j, ((maskB[ps] >> j) & 1u) ? xv[ps][j] : 0ull, acc);
               split5(acc, hiB, loB);
             }
+            if (cls == 1) {          // every row upstream: bases 0..4 are the sums, base 5 completes the K step with zeros
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              const bool a_side = (k < 5) == up[ps];
-              if (k >= k_lo && k < k_hi)
+              for (int k = 0; k < 5; ++k) put(ps, k, hiA[ps][k], loA[ps][k]);
+              put(ps, 5, 0u, 0u);
+            } else if (cls == 2) {   // every row downstream: base 4 zero, bases 5..9 the sums
+              put(ps, 4, 0u, 0u);
+#pragma unroll
+              for (int k = 5; k < 8; ++k) put(ps, k, hiA[ps][k - 5], loA[ps][k - 5]);
+#pragma unroll
+              for (int k = 8; k < 10; ++k) out89(ps, k, hiA[ps][k - 5], loA[ps][k - 5]);
+            } else {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                const bool a_side = (k < 5) == up[ps];
                 put(ps, k, a_side ? hiA[ps][k % 5] : hiB[k % 5], a_side ? loA[ps][k % 5] : loB[k % 5]);
-            }
-            if (use_k) {
+              }
 #pragma unroll
               for (int k = 8; k < 10; ++k)
                 out89(ps, k, up[ps] ? hiB[k - 5] : hiA[ps][k - 5], up[ps] ? loB[k - 5] : loA[ps][k - 5]);
